@@ -1,0 +1,144 @@
+// flivo_dev.cuh — device-side data layout and strict-float helpers shared by the kernels of
+// libflivo_b200.so (sm_100a only).
+//
+// Every translation unit that includes this file is compiled with -fmad=false: the reference is built
+// for baseline x86-64 (no FMA, CMakeLists.txt:7,23), and every float that feeds a comparison (kNN
+// distance include/ikd-Tree/ikd_Tree.cpp:1291-1295, plane test include/common_lib.h:694, gates
+// src/laser_mapping.cpp:518,533-535) must round exactly as separate mul / add.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace flivo {
+
+// ------------------------------------------------------------------------------------------------
+// GPU-resident map ("(a) a GPU-resident map" of north_star): a three-level voxel hash.
+//   voxel  : edge ds = KD_TREE::downsample_size; integer key k = floorf(x / ds) per axis — the same float
+//            expression the reference uses to form its downsample box (ikd_Tree.cpp:392-397)
+//   cell   : 2^gshift voxels per axis (search granularity); at most one live point per voxel after
+//            Add_Points(…, true), so a cell of 2x2x2 voxels normally holds <= 8 points = one bucket
+//   block  : 4x4x4 cells; the block directory is an open-addressing hash (linear probing) keyed by the
+//            packed block coordinates; slot s owns cell_tab[s*64 .. s*64+63] (bucket index per cell)
+//            and blk_mask[s] (occupancy bits of its 64 cells)
+//   bucket : 8 x float4 {x, y, z, id-as-bits} = one 128-byte line; empty slot <=> id == -1;
+//            bucket_next[] chains overflow buckets (dense, not-downsampled Build input)
+// Points are never moved once stored; deletes clear the slot in place.
+// ------------------------------------------------------------------------------------------------
+constexpr unsigned long long DIR_EMPTY = 0xFFFFFFFFFFFFFFFFull;
+constexpr uint32_t NONE32 = 0xFFFFFFFFu;
+constexpr int BUCKET_SLOTS = 8;
+constexpr int EMPTY_ID = -1;
+constexpr int COORD_BIAS = 1 << 20;  // voxel keys are biased into [0, 2^21)
+constexpr uint32_t INF_BITS = 0x7F800000u;
+
+struct MapView {
+    unsigned long long* dir_keys;  // [dir_cap]
+    uint32_t* cell_tab;            // [dir_cap * 64]
+    unsigned long long* blk_mask;  // [dir_cap]
+    float4* buckets;               // [bucket_cap * 8]
+    uint32_t* bucket_next;         // [bucket_cap]
+    uint32_t dir_mask;             // dir_cap - 1 (dir_cap is a power of two)
+    uint32_t bucket_cap;
+    float ds;                      // downsample_size
+    int gshift;                    // log2(cell_ratio)
+    float cell_edge;               // ds * 2^gshift (exact)
+};
+
+// Device-side counters of the map (one struct in global memory).
+struct MapCounters {
+    unsigned long long live;       // live points
+    unsigned int blocks_used;      // directory slots in use
+    unsigned int cells_used;
+    unsigned int buckets_used;     // bump allocator
+    int error;                     // sticky: 1 = coordinate out of range, 2 = directory full, 3 = bucket pool full
+    int add_counter;               // tmp_counter of the running Add_Points
+    int del_counter;
+    unsigned int deferred;         // voxel segments deferred to the serial pass
+    unsigned int removed_count;    // entries in the removed-points log
+    unsigned int pad[3];
+};
+
+struct int3s { int x, y, z; };
+
+// ---- strict float helpers (explicit rounding; immune to contraction even without -fmad=false) -----
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
+
+// calc_dist (ikd_Tree.cpp:1291-1295): (dx*dx + dy*dy) + dz*dz in float
+__device__ __forceinline__ float sqdist3(float ax, float ay, float az, float bx, float by, float bz) {
+    float dx = fsub(ax, bx), dy = fsub(ay, by), dz = fsub(az, bz);
+    return fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz));
+}
+
+// voxel key: floor(p / downsample_size) as in Box_of_Point.vertex_min (ikd_Tree.cpp:392-396)
+__device__ __forceinline__ int voxel_key1(float x, float ds) { return (int)floorf(fdiv(x, ds)); }
+
+__device__ __forceinline__ bool key_in_range(int k) { return k > -COORD_BIAS + 8 && k < COORD_BIAS - 8; }
+
+// packed block key from block coordinates (each in about [-2^18, 2^18))
+__device__ __forceinline__ unsigned long long pack_block(int bx, int by, int bz) {
+    return ((unsigned long long)(unsigned)(bx + (1 << 19)) << 40) |
+           ((unsigned long long)(unsigned)(by + (1 << 19)) << 20) |
+           (unsigned long long)(unsigned)(bz + (1 << 19));
+}
+__device__ __forceinline__ void unpack_block(unsigned long long k, int& bx, int& by, int& bz) {
+    bx = (int)((k >> 40) & 0xFFFFF) - (1 << 19);
+    by = (int)((k >> 20) & 0xFFFFF) - (1 << 19);
+    bz = (int)(k & 0xFFFFF) - (1 << 19);
+}
+__device__ __forceinline__ uint32_t hash_block(unsigned long long k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+    return (uint32_t)k;
+}
+__device__ __forceinline__ int cell_off(int cx, int cy, int cz) { return ((cx & 3) << 4) | ((cy & 3) << 2) | (cz & 3); }
+
+// directory lookup: slot index or -1
+__device__ __forceinline__ int dir_find(const MapView& m, unsigned long long key) {
+    uint32_t s = hash_block(key) & m.dir_mask;
+    while (true) {
+        unsigned long long k = __ldg(m.dir_keys + s);
+        if (k == key) return (int)s;
+        if (k == DIR_EMPTY) return -1;
+        s = (s + 1) & m.dir_mask;
+    }
+}
+// find-or-insert; returns slot (never fails while load factor < 1; callers keep it <= 0.5)
+__device__ __forceinline__ int dir_find_or_insert(const MapView& m, unsigned long long key, MapCounters* cnt) {
+    uint32_t s = hash_block(key) & m.dir_mask;
+    for (uint32_t probe = 0; probe <= m.dir_mask; ++probe) {
+        unsigned long long k = m.dir_keys[s];
+        if (k == key) return (int)s;
+        if (k == DIR_EMPTY) {
+            unsigned long long old = atomicCAS(m.dir_keys + s, DIR_EMPTY, key);
+            if (old == DIR_EMPTY) { atomicAdd(&cnt->blocks_used, 1u); return (int)s; }
+            if (old == key) return (int)s;
+        }
+        s = (s + 1) & m.dir_mask;
+    }
+    atomicExch(&cnt->error, 2);
+    return -1;
+}
+// bucket index of a cell or NONE32
+__device__ __forceinline__ uint32_t cell_bucket(const MapView& m, int cx, int cy, int cz) {
+    int slot = dir_find(m, pack_block(cx >> 2, cy >> 2, cz >> 2));
+    if (slot < 0) return NONE32;
+    return __ldg(m.cell_tab + (size_t)slot * 64 + cell_off(cx, cy, cz));
+}
+
+// Box of a voxel key exactly as the reference forms it (ikd_Tree.cpp:392-397): min = k*ds, max = min + ds (float)
+__device__ __forceinline__ void voxel_box1(int k, float ds, float& lo, float& hi) {
+    lo = fmul((float)k, ds);
+    hi = fadd(lo, ds);
+}
+// Search_by_range / Delete_by_range membership (ikd_Tree.cpp:648,1001): min <= p < max
+__device__ __forceinline__ bool in_box1(float p, float lo, float hi) { return lo <= p && hi > p; }
+
+// same_point (ikd_Tree.cpp:1287-1289), EPSS = 1e-6 compared in double
+__device__ __forceinline__ bool same_point3(float ax, float ay, float az, float bx, float by, float bz) {
+    return (double)fabsf(fsub(ax, bx)) < 1e-6 && (double)fabsf(fsub(ay, by)) < 1e-6 && (double)fabsf(fsub(az, bz)) < 1e-6;
+}
+
+}  // namespace flivo

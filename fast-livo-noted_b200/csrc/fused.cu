@@ -1,0 +1,427 @@
+// fused.cu — the per-trip fused kernel of the LIO measurement update (sm_100a) and the batched kNN kernel.
+//
+// One launch = one LaserMapping::h_share_model call (reference src/laser_mapping.cpp:485-645 and
+// src/origin_laserMapping.cpp:916-1048):
+//   a1 world transform (:662-671)            -> per lane, double, narrowed to float
+//   a2 exact 5-NN (ikd_Tree.cpp:350-380)     -> warp per point over the voxel-hash map (search.cuh)
+//   a3 far-neighbour gate (:518)             -> per lane
+//   a4 esti_plane (common_lib.h:670-702)     -> per lane, float, no FMA, fixed operation order
+//   a5 residual + range gate (:532-543)      -> per lane
+//   a6 compaction (:547-561)                 -> replaced by masked accumulation; mask and n_eff are outputs
+//   a7 1x12 Jacobian row (origin:1018-1044)  -> per lane, double
+//   a8 H^T H / H^T z (esekfom.hpp:1781,1801) -> shared-memory transposed Gram per warp, fixed-order block,
+//                                               group and final reductions (no floating-point atomics)
+// Compiled with -fmad=false: see flivo_dev.cuh.
+#include "fused.cuh"
+#include "search.cuh"
+
+namespace flivo {
+
+// (a, b) of the 78 upper-triangle terms, then (a, 12) for H^T z
+__constant__ unsigned char c_term_a[90];
+__constant__ unsigned char c_term_b[90];
+
+void upload_term_table() {
+    unsigned char a[90], b[90];
+    int t = 0;
+    for (int i = 0; i < 12; ++i)
+        for (int j = i; j < 12; ++j) { a[t] = (unsigned char)i; b[t] = (unsigned char)j; ++t; }
+    for (int i = 0; i < 12; ++i) { a[t] = (unsigned char)i; b[t] = 12; ++t; }
+    cudaMemcpyToSymbol(c_term_a, a, 90);
+    cudaMemcpyToSymbol(c_term_b, b, 90);
+}
+
+// ---- esti_plane<float> -----------------------------------------------------------------------------
+// Same operation order as the CPU oracle's restatement of Eigen's ColPivHouseholderQR:
+// 5-element reductions left to right, 3-element ones as x0 + (x1 + x2).  A is column-major A[c][r].
+__device__ __forceinline__ float norm_tail5(const float* col, int from) {
+    float s = col[from] * col[from];
+    for (int i = from + 1; i < 5; ++i) s = s + col[i] * col[i];
+    return sqrtf(s);
+}
+
+__device__ bool esti_plane_dev(const float4 nb[5], float threshold, float pabcd[4]) {
+    float A[3][5];
+#pragma unroll
+    for (int r = 0; r < 5; ++r) { A[0][r] = nb[r].x; A[1][r] = nb[r].y; A[2][r] = nb[r].z; }
+    float cvec[5] = {-1.f, -1.f, -1.f, -1.f, -1.f};
+    float hcoef[3] = {0.f, 0.f, 0.f};
+    int perm[3] = {0, 1, 2};
+    float nrmU[3], nrmD[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { nrmD[c] = norm_tail5(A[c], 0); nrmU[c] = nrmD[c]; }
+    float maxn = nrmU[0];
+    if (nrmU[1] > maxn) maxn = nrmU[1];
+    if (nrmU[2] > maxn) maxn = nrmU[2];
+    const float eps = 1.1920928955078125e-07f;  // FLT_EPSILON
+    float th = maxn * eps;
+    const float threshold_helper = (th * th) / 5.0f;
+    const float downdate_thr = sqrtf(eps);
+    int nonzero_pivots = 3;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        int big = k;
+#pragma unroll
+        for (int j = k + 1; j < 3; ++j)
+            if (nrmU[j] > nrmU[big]) big = j;
+        float big_sq = nrmU[big] * nrmU[big];
+        if (nonzero_pivots == 3 && big_sq < threshold_helper * (float)(5 - k)) nonzero_pivots = k;
+        if (big != k) {
+            // big in {k+1, .., 2}: swap with compile-time indices to keep everything in registers
+#pragma unroll
+            for (int j = k + 1; j < 3; ++j) {
+                if (j == big) {
+#pragma unroll
+                    for (int r = 0; r < 5; ++r) { float t = A[k][r]; A[k][r] = A[j][r]; A[j][r] = t; }
+                    float t = nrmU[k]; nrmU[k] = nrmU[j]; nrmU[j] = t;
+                    t = nrmD[k]; nrmD[k] = nrmD[j]; nrmD[j] = t;
+                    int ti = perm[k]; perm[k] = perm[j]; perm[j] = ti;
+                }
+            }
+        }
+        float tailSq = 0.f;
+        if (k + 1 < 5) {
+            tailSq = A[k][k + 1] * A[k][k + 1];
+#pragma unroll
+            for (int i = k + 2; i < 5; ++i) tailSq = tailSq + A[k][i] * A[k][i];
+        }
+        float c0 = A[k][k], beta, tau;
+        if (tailSq <= 1.17549435e-38f) {  // FLT_MIN
+            tau = 0.f; beta = c0;
+#pragma unroll
+            for (int i = k + 1; i < 5; ++i) A[k][i] = 0.f;
+        } else {
+            beta = sqrtf(c0 * c0 + tailSq);
+            if (c0 >= 0.f) beta = -beta;
+            float den = c0 - beta;
+#pragma unroll
+            for (int i = k + 1; i < 5; ++i) A[k][i] = A[k][i] / den;
+            tau = (beta - c0) / beta;
+        }
+        A[k][k] = beta;
+        hcoef[k] = tau;
+        if (tau != 0.f) {
+#pragma unroll
+            for (int j = k + 1; j < 3; ++j) {
+                float tmp = A[k][k + 1] * A[j][k + 1];
+#pragma unroll
+                for (int i = k + 2; i < 5; ++i) tmp = tmp + A[k][i] * A[j][i];
+                tmp = tmp + A[j][k];
+                A[j][k] = A[j][k] - tau * tmp;
+#pragma unroll
+                for (int i = k + 1; i < 5; ++i) A[j][i] = A[j][i] - (tau * A[k][i]) * tmp;
+            }
+        }
+#pragma unroll
+        for (int j = k + 1; j < 3; ++j) {
+            if (nrmU[j] != 0.f) {
+                float temp = fabsf(A[j][k]) / nrmU[j];
+                temp = (1.f + temp) * (1.f - temp);
+                temp = temp < 0.f ? 0.f : temp;
+                float ratio = nrmU[j] / nrmD[j];
+                float temp2 = temp * (ratio * ratio);
+                if (temp2 <= downdate_thr) {
+                    nrmD[j] = norm_tail5(A[j], k + 1);
+                    nrmU[j] = nrmD[j];
+                } else {
+                    nrmU[j] = nrmU[j] * sqrtf(temp);
+                }
+            }
+        }
+    }
+    float x[3] = {0.f, 0.f, 0.f};
+    if (nonzero_pivots > 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (k < nonzero_pivots) {
+                float tau = hcoef[k];
+                if (tau != 0.f) {
+                    float tmp = A[k][k + 1] * cvec[k + 1];
+#pragma unroll
+                    for (int i = k + 2; i < 5; ++i) tmp = tmp + A[k][i] * cvec[i];
+                    tmp = tmp + cvec[k];
+                    cvec[k] = cvec[k] - tau * tmp;
+#pragma unroll
+                    for (int i = k + 1; i < 5; ++i) cvec[i] = cvec[i] - (tau * A[k][i]) * tmp;
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 2; i >= 0; --i) {
+            if (i < nonzero_pivots) {
+                cvec[i] = cvec[i] / A[i][i];
+#pragma unroll
+                for (int j = 0; j < i; ++j) cvec[j] = cvec[j] - cvec[i] * A[i][j];
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            if (i < nonzero_pivots) {
+                // x[perm[i]] = cvec[i] with compile-time destinations
+                if (perm[i] == 0) x[0] = cvec[i]; else if (perm[i] == 1) x[1] = cvec[i]; else x[2] = cvec[i];
+            }
+        }
+    }
+    float n = sqrtf(x[0] * x[0] + (x[1] * x[1] + x[2] * x[2]));
+    pabcd[0] = x[0] / n;
+    pabcd[1] = x[1] / n;
+    pabcd[2] = x[2] / n;
+    pabcd[3] = (float)(1.0 / (double)n);  // "1.0 / n" in double, common_lib.h:691
+    bool ok = true;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        float v = pabcd[0] * nb[j].x + pabcd[1] * nb[j].y + pabcd[2] * nb[j].z + pabcd[3];
+        if (fabsf(v) > threshold) ok = false;
+    }
+    return ok;
+}
+
+__device__ __forceinline__ double dot3d(const double* a, double b0, double b1, double b2) { return a[0] * b0 + (a[1] * b1 + a[2] * b2); }
+
+// ----------------------------------------------------------------------------------------------------
+// fused kernel
+// ----------------------------------------------------------------------------------------------------
+struct __align__(16) WarpSmem {
+    union {
+        float4 nearp[32 * 5];     // neighbours found for the warp's 32 points (phase A -> B)
+        double rows[32 * 14];     // Jacobian rows h[12], z, pad (phase B -> C)
+    };
+};
+
+__global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
+    __shared__ WarpSmem s_warp[UNIT_WARPS];
+    __shared__ double s_acc[UNIT_WARPS][PSTRIDE];
+    __shared__ double s_state[36];
+    __shared__ unsigned int s_unit;
+    __shared__ int s_last;
+
+    Ctl* ctl = P.ctl;
+    if (ctl->stopped) return;
+    const bool search = (ctl->search != 0) || (P.force_search != 0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < 36) s_state[threadIdx.x] = P.state[threadIdx.x];
+    __syncthreads();
+    const double* Rm = s_state;          // rot
+    const double* tw = s_state + 9;      // pos
+    const double* Rl = s_state + 12;     // offR
+    const double* tl = s_state + 21;     // offT
+    WarpSmem& ws = s_warp[warp];
+
+    while (true) {
+        if (threadIdx.x == 0) s_unit = atomicAdd(&ctl->unit_counter, 1u);
+        __syncthreads();
+        const unsigned int unit = s_unit;
+        if (unit >= (unsigned)P.units) break;
+        const int base = unit * UNIT_POINTS + warp * 32;
+        const int i = base + lane;
+        const bool have = i < P.n;
+
+        // ---- a1: world transform --------------------------------------------------------------------
+        float4 pb = have ? __ldg(P.body + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        double pd[3] = {(double)pb.x, (double)pb.y, (double)pb.z};
+        double pl[3];  // R_LI p + t_LI
+        pl[0] = dot3d(Rl + 0, pd[0], pd[1], pd[2]) + tl[0];
+        pl[1] = dot3d(Rl + 3, pd[0], pd[1], pd[2]) + tl[1];
+        pl[2] = dot3d(Rl + 6, pd[0], pd[1], pd[2]) + tl[2];
+        float wx = (float)(dot3d(Rm + 0, pl[0], pl[1], pl[2]) + tw[0]);
+        float wy = (float)(dot3d(Rm + 3, pl[0], pl[1], pl[2]) + tw[1]);
+        float wz = (float)(dot3d(Rm + 6, pl[0], pl[1], pl[2]) + tw[2]);
+        if (have) P.world[i] = make_float4(wx, wy, wz, pb.w);
+
+        // ---- a2: neighbours ---------------------------------------------------------------------------
+        float4 nb[5];
+        int ncnt = 0;
+        float d5 = INFINITY;
+        if (search) {
+            int npts = min(32, P.n - base);
+            for (int j = 0; j < npts; ++j) {
+                float qx = __shfl_sync(FULL, wx, j), qy = __shfl_sync(FULL, wy, j), qz = __shfl_sync(FULL, wz, j);
+                Cand out;
+                int cnt = warp_knn5(P.map, qx, qy, qz, P.max_sq_bits, lane, out, P.stats);
+                if (lane < 5) {
+                    float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                    if (out.d != INF_BITS) p = __ldg(P.map.buckets + out.addr);
+                    ws.nearp[j * 5 + lane] = p;
+                }
+                float dlast = __uint_as_float(__shfl_sync(FULL, out.d, 4));
+                if (lane == j) { ncnt = cnt; d5 = dlast; }
+            }
+            __syncwarp();
+            // cache Nearest_Points for the re-use trips (coalesced: 160 float4 per warp)
+            for (int t = lane; t < npts * 5; t += 32) P.near[(size_t)base * 5 + t] = ws.nearp[t];
+            if (have) P.near_meta[i] = make_float2(__int_as_float(ncnt), d5);
+#pragma unroll
+            for (int r = 0; r < 5; ++r) nb[r] = ws.nearp[lane * 5 + r];
+        } else {
+            if (have) {
+                float2 meta = __ldg(P.near_meta + i);
+                ncnt = __float_as_int(meta.x);
+                d5 = meta.y;
+#pragma unroll
+                for (int r = 0; r < 5; ++r) nb[r] = __ldg(P.near + (size_t)i * 5 + r);
+            }
+        }
+        __syncwarp();  // nearp is dead from here; the union is reused for the rows
+
+        // ---- a3..a5: gates and plane -----------------------------------------------------------------
+        bool sel;
+        if (P.mode == 1) sel = true;                        // V1: vector<bool>(n, true) each call (:490)
+        else sel = have && (P.sel[i] != 0);                 // V3: persistent flag (origin:963)
+        const bool have5 = have && ncnt >= 5;
+        if (search) sel = have5 && !(d5 > 5.f);             // pointSearchSqDis[4] > 5 ? false : true (:518)
+        bool eff = false;
+        float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
+        float res = 0.f;
+        if (sel && have5) {
+            sel = false;
+            float pabcd[4];
+            if (esti_plane_dev(nb, 0.1f, pabcd)) {
+                float pd2 = pabcd[0] * wx + pabcd[1] * wy + pabcd[2] * wz + pabcd[3];
+                double nrm = sqrt(pd[0] * pd[0] + (pd[1] * pd[1] + pd[2] * pd[2]));
+                float s = (float)(1.0 - 0.9 * (double)fabsf(pd2) / sqrt(nrm));
+                if ((double)s > 0.9) {
+                    sel = true;
+                    nv = make_float4(pabcd[0], pabcd[1], pabcd[2], pd2);
+                    res = fabsf(pd2);
+                    eff = res <= 2.0f;                       // res_last[i] <= 2.0 (:552)
+                }
+            }
+        } else {
+            sel = false;
+        }
+        if (have) {
+            P.sel[i] = sel ? 1 : 0;
+            P.eff[i] = eff ? 1 : 0;
+            P.normvec[i] = nv;
+        }
+
+        // ---- a7: Jacobian row (origin:1018-1044) -------------------------------------------------------
+        double h[13];
+        if (eff) {
+            double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
+            double C0 = Rm[0] * n0 + (Rm[3] * n1 + Rm[6] * n2);   // R^T n
+            double C1 = Rm[1] * n0 + (Rm[4] * n1 + Rm[7] * n2);
+            double C2 = Rm[2] * n0 + (Rm[5] * n1 + Rm[8] * n2);
+            double A0 = pl[1] * C2 - pl[2] * C1, A1 = pl[2] * C0 - pl[0] * C2, A2 = pl[0] * C1 - pl[1] * C0;   // [pt]x C
+            double T0 = Rl[0] * C0 + (Rl[3] * C1 + Rl[6] * C2);   // R_LI^T C
+            double T1 = Rl[1] * C0 + (Rl[4] * C1 + Rl[7] * C2);
+            double T2 = Rl[2] * C0 + (Rl[5] * C1 + Rl[8] * C2);
+            double B0 = pd[1] * T2 - pd[2] * T1, B1 = pd[2] * T0 - pd[0] * T2, B2 = pd[0] * T1 - pd[1] * T0;   // [p]x (...)
+            h[0] = n0; h[1] = n1; h[2] = n2; h[3] = A0; h[4] = A1; h[5] = A2;
+            h[6] = B0; h[7] = B1; h[8] = B2; h[9] = C0; h[10] = C1; h[11] = C2;
+            h[12] = -(double)nv.w;
+        } else {
+#pragma unroll
+            for (int a = 0; a < 13; ++a) h[a] = 0.0;
+        }
+#pragma unroll
+        for (int a = 0; a < 13; ++a) ws.rows[lane * 14 + a] = h[a];
+        __syncwarp();
+
+        // ---- a8: Gram of the warp's 32 rows; lane t owns terms t, t+32, t+64 -----------------------------
+        {
+            const int t0 = lane, t1 = lane + 32, t2 = lane + 64;
+            const int a0 = c_term_a[t0], b0 = c_term_b[t0], a1 = c_term_a[t1], b1 = c_term_b[t1];
+            const bool has2 = t2 < 90;
+            const int a2 = has2 ? c_term_a[t2] : 0, b2 = has2 ? c_term_b[t2] : 0;
+            double v0 = 0.0, v1 = 0.0, v2 = 0.0;
+            const unsigned effmask = __ballot_sync(FULL, eff);
+            for (int r = 0; r < 32; ++r) {
+                if (!((effmask >> r) & 1u)) continue;  // warp-uniform
+                const double* row = ws.rows + r * 14;
+                v0 += row[a0] * row[b0];
+                v1 += row[a1] * row[b1];
+                v2 += row[a2] * row[b2];
+            }
+            double rsum = eff ? (double)res : 0.0;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) rsum += __shfl_xor_sync(FULL, rsum, o);
+            s_acc[warp][t0] = v0;
+            s_acc[warp][t1] = v1;
+            if (has2) s_acc[warp][t2] = v2;
+            if (lane == 0) { s_acc[warp][90] = rsum; s_acc[warp][91] = (double)__popc(effmask); }
+        }
+        __syncthreads();
+        if (threadIdx.x < NTERMS) {
+            double s = s_acc[0][threadIdx.x];
+#pragma unroll
+            for (int w = 1; w < UNIT_WARPS; ++w) s += s_acc[w][threadIdx.x];
+            P.partials[(size_t)unit * PSTRIDE + threadIdx.x] = s;
+        }
+        // ---- group fold by the last-arriving unit (fixed order => deterministic) ---------------------------
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned int g = unit / GROUP_UNITS;
+            unsigned int gsize = min((unsigned)GROUP_UNITS, (unsigned)P.units - g * GROUP_UNITS);
+            unsigned int old = atomicAdd(P.group_cnt + g, 1u);
+            s_last = (old == gsize - 1) ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            unsigned int g = unit / GROUP_UNITS;
+            unsigned int u0 = g * GROUP_UNITS, u1 = min(u0 + GROUP_UNITS, (unsigned)P.units);
+            if (threadIdx.x < NTERMS) {
+                double s = 0.0;
+                for (unsigned int u = u0; u < u1; ++u) s += __ldcg(P.partials + (size_t)u * PSTRIDE + threadIdx.x);
+                P.gpartials[(size_t)g * PSTRIDE + threadIdx.x] = s;
+            }
+            if (threadIdx.x == 0) P.group_cnt[g] = 0;
+        }
+        __syncthreads();
+    }
+}
+
+// ----------------------------------------------------------------------------------------------------
+// batched Nearest_Search for the C ABI (flivo_knn): one warp per query
+// ----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_knn(MapView map, const float4* __restrict__ q, int nq, int k, uint32_t max_sq_bits,
+                                             float* out_xyz, float* out_sqd, int* out_id, int* out_count, SearchStats* stats) {
+    const int lane = threadIdx.x & 31;
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int i = wid; i < nq; i += nwarps) {
+        float4 p = __ldg(q + i);
+        Cand out;
+        int cnt = warp_knn5(map, p.x, p.y, p.z, max_sq_bits, lane, out, stats);
+        int found = min(cnt, k);
+        if (lane < k) {
+            bool ok = lane < found;
+            float4 np = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+            if (ok) np = __ldg(map.buckets + out.addr);
+            if (out_xyz) { out_xyz[((size_t)i * k + lane) * 3 + 0] = np.x; out_xyz[((size_t)i * k + lane) * 3 + 1] = np.y; out_xyz[((size_t)i * k + lane) * 3 + 2] = np.z; }
+            if (out_sqd) out_sqd[(size_t)i * k + lane] = ok ? __uint_as_float(out.d) : INFINITY;
+            if (out_id) out_id[(size_t)i * k + lane] = ok ? (int)out.id : -1;
+        }
+        if (lane == 0 && out_count) out_count[i] = found;
+    }
+}
+
+// world transform only (map_incremental, src/laser_mapping.cpp:343-346): body -> world float4 (w = 0)
+__global__ void k_transform(const float4* __restrict__ body, int n, const double* __restrict__ state, float4* __restrict__ world) {
+    __shared__ double s[36];
+    if (threadIdx.x < 36) s[threadIdx.x] = state[threadIdx.x];
+    __syncthreads();
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 pb = __ldg(body + i);
+    double pd0 = (double)pb.x, pd1 = (double)pb.y, pd2 = (double)pb.z;
+    double l0 = dot3d(s + 12, pd0, pd1, pd2) + s[21], l1 = dot3d(s + 15, pd0, pd1, pd2) + s[22], l2 = dot3d(s + 18, pd0, pd1, pd2) + s[23];
+    world[i] = make_float4((float)(dot3d(s + 0, l0, l1, l2) + s[9]), (float)(dot3d(s + 3, l0, l1, l2) + s[10]),
+                           (float)(dot3d(s + 6, l0, l1, l2) + s[11]), 0.f);
+}
+
+// ---- host launchers ---------------------------------------------------------------------------------
+void launch_fused(const FusedParams& P, int grid, cudaStream_t stream) {
+    k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P);
+}
+void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
+                int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream) {
+    k_knn<<<grid, 128, 0, stream>>>(map, q, nq, k, max_sq_bits, out_xyz, out_sqd, out_id, out_count, stats);
+}
+void launch_transform(const float4* body, int n, const double* state, float4* world, cudaStream_t stream) {
+    k_transform<<<(n + 255) / 256, 256, 0, stream>>>(body, n, state, world);
+}
+
+}  // namespace flivo

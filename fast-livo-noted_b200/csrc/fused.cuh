@@ -1,0 +1,55 @@
+// fused.cuh — parameters shared by the fused per-trip kernel, the batched kNN kernel and the solve kernels.
+#pragma once
+#include "flivo_dev.cuh"
+
+namespace flivo {
+
+constexpr int UNIT_WARPS = 4;                    // warps per CTA of the fused kernel
+constexpr int UNIT_POINTS = UNIT_WARPS * 32;     // scan points per work unit
+constexpr int NTERMS = 92;                       // 78 (H^T H upper) + 12 (H^T z) + res_sum + n_eff
+constexpr int PSTRIDE = 96;                      // doubles per partial record
+constexpr int GROUP_UNITS = 32;                  // units folded by the last-arriving CTA of a group
+constexpr int MAX_TRIPS = 16;
+
+// Device-resident control block of one iterated update (written by the solve kernel, read by the fused kernel).
+struct Ctl {
+    int search;        // 1: this trip runs the kNN (nearest_search_en / dyn_share.converge)
+    int stopped;       // 1: loop finished; later kernels of the captured sequence exit immediately
+    int iter;          // reference loop index (starts at -1)
+    int t;             // V3 converge counter t (esekfom.hpp:1631)
+    int rematch;       // V1 rematch_num (src/laser_mapping.cpp:166)
+    int trips;         // h_share_model calls executed
+    int searches;
+    int converged;
+    int n_eff;
+    int nan_guard;     // 1: a non-finite normal-equation block was seen (update skipped)
+    int trip_searched[MAX_TRIPS];
+    double res_mean;
+    double dx_last[23];
+    unsigned int unit_counter;   // dynamic work-unit scheduler of the fused kernel
+    unsigned int pad;
+};
+
+struct FusedParams {
+    MapView map;
+    const float4* body;        // scan, lidar frame, processing order
+    int n;
+    const double* state;       // device flivo_state (36 doubles): rot, pos, offR, offT, ...
+    float4* near;              // [n*5] cached Nearest_Points (x,y,z,id)
+    float2* near_meta;         // [n] {count as float bits, 5th squared distance}
+    unsigned char* sel;        // [n] point_selected_surf (persistent across trips in V3 mode)
+    unsigned char* eff;        // [n] rows that entered H
+    float4* normvec;           // [n] (nx,ny,nz,pd2)
+    float4* world;             // [n] feats_down_world
+    double* partials;          // [units * PSTRIDE]
+    double* gpartials;         // [groups * PSTRIDE]
+    unsigned int* group_cnt;   // [groups]
+    Ctl* ctl;
+    SearchStats* stats;
+    int mode;                  // FLIVO_MODE_*
+    int force_search;
+    uint32_t max_sq_bits;      // kNN distance bound as float bits (INF_BITS = unbounded)
+    int units, groups;
+};
+
+}  // namespace flivo

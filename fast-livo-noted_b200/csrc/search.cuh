@@ -1,0 +1,301 @@
+// search.cuh — warp-per-query exact k=5 nearest-neighbour search over the voxel-hash map.
+//
+// Semantics reproduced: KD_TREE::Nearest_Search / Search (include/ikd-Tree/ikd_Tree.cpp:350-380, :843-986):
+// the k nearest live points whose float32 squared distance (calc_dist, :1291-1295) is <= max_dist,
+// ascending.  Equal distances at rank k are kept by visiting order in the reference (tree-shape
+// dependent); here the canonical total order (distance bits, insertion id) decides, see DESIGN.md.
+//
+// Exactness argument: cells are unions of voxels whose integer keys come from the same floorf(x/ds)
+// the insert path uses, so a point outside the cell block [cq-n, cq+n]^3 is farther than
+// n*cell_edge minus a rounding slack from the query; a shell is final when the 5th best distance is
+// below that bound (or the bound exceeds max_dist).  Shells: 3^3 cells (fast path, one warp pass),
+// 5^3 cells, then rings of 4x4x4-cell blocks through the block directory, then (unbounded searches
+// only) a sweep of the whole directory pruned by block distance.
+#pragma once
+#include "flivo_dev.cuh"
+
+namespace flivo {
+
+constexpr unsigned FULL = 0xFFFFFFFFu;
+constexpr int FAR_MAX_RING = 3;  // block rings tried before the directory sweep
+
+struct Cand {
+    uint32_t d;     // squared distance bits (positive floats order as unsigned); INF_BITS = empty
+    uint32_t id;    // insertion id (unique)
+    uint32_t addr;  // point slot = bucket * 8 + s
+};
+__device__ __forceinline__ bool cand_less(const Cand& a, const Cand& b) { return a.d < b.d || (a.d == b.d && a.id < b.id); }
+
+// Warp-wide selection state.  c0 carries the current best five (lane r < 5 holds rank r); c1..c3 are the
+// staging slots filled by push(); all slot indices are compile-time so everything stays in registers.
+struct WarpSelect {
+    Cand c0, c1, c2, c3;
+    int fill;        // warp-uniform number of staged batches (0..3)
+    int count;       // warp-uniform: how many of the best five exist
+    uint32_t tau;    // warp-uniform: distance bits of the current 5th best, or the max_dist bound
+    uint32_t bound;  // max_dist as float bits (candidates above it are never staged)
+
+    __device__ __forceinline__ void init(uint32_t bound_bits) {
+        c0.d = c1.d = c2.d = c3.d = INF_BITS;
+        c0.id = c1.id = c2.id = c3.id = 0xFFFFFFFFu;
+        c0.addr = c1.addr = c2.addr = c3.addr = 0;
+        fill = 0; count = 0; bound = bound_bits; tau = bound_bits;
+    }
+    // Extract the five smallest of the 4 x 32 staged candidates into c0 of lanes 0..4.
+    __device__ __forceinline__ void select(int lane) {
+        Cand res; res.d = INF_BITS; res.id = 0xFFFFFFFFu; res.addr = 0;
+        int found = 0;
+#pragma unroll
+        for (int r = 0; r < FLIVO_K_; ++r) {
+            Cand lb = c0; int which = 0;
+            if (cand_less(c1, lb)) { lb = c1; which = 1; }
+            if (cand_less(c2, lb)) { lb = c2; which = 2; }
+            if (cand_less(c3, lb)) { lb = c3; which = 3; }
+            uint32_t dmin = __reduce_min_sync(FULL, lb.d);
+            if (dmin == INF_BITS) break;  // warp-uniform
+            uint32_t idmin = __reduce_min_sync(FULL, lb.d == dmin ? lb.id : 0xFFFFFFFFu);
+            bool win = (lb.d == dmin) && (lb.id == idmin);
+            int wl = __ffs(__ballot_sync(FULL, win)) - 1;
+            uint32_t a = __shfl_sync(FULL, lb.addr, wl);
+            if (win) {
+                if (which == 0) c0.d = INF_BITS; else if (which == 1) c1.d = INF_BITS;
+                else if (which == 2) c2.d = INF_BITS; else c3.d = INF_BITS;
+            }
+            if (lane == r) { res.d = dmin; res.id = idmin; res.addr = a; }
+            ++found;
+        }
+        c0 = res;
+        c1.d = c2.d = c3.d = INF_BITS;
+        fill = 0;
+        count = found;
+        uint32_t d5 = __shfl_sync(FULL, c0.d, FLIVO_K_ - 1);
+        tau = (found == FLIVO_K_) ? d5 : bound;
+    }
+    // Stage one candidate per lane (d == INF_BITS for "none").  Warp-collective.
+    __device__ __forceinline__ void push(int lane, uint32_t d, uint32_t id, uint32_t addr) {
+        if (fill == 0) { c1.d = d; c1.id = id; c1.addr = addr; }
+        else if (fill == 1) { c2.d = d; c2.id = id; c2.addr = addr; }
+        else { c3.d = d; c3.id = id; c3.addr = addr; }
+        if (++fill == 3) select(lane);
+    }
+    __device__ __forceinline__ void flush(int lane) { if (fill) select(lane); }
+    static constexpr int FLIVO_K_ = 5;
+};
+
+struct SearchStats {
+    unsigned long long far_queries;   // queries that left the 27-cell fast path
+    unsigned long long candidates;    // candidate points examined
+    unsigned long long sweeps;        // queries that needed the directory sweep
+};
+
+// squared covered radius (float, conservative) of a cell block reaching n cells beyond the query's cell
+__device__ __forceinline__ float covered_sq(float cell_edge, float n_cells, float qabs) {
+    double r = (double)n_cells * (double)cell_edge * (1.0 - 1e-6) - ((double)qabs + (double)n_cells * (double)cell_edge) * 4.8e-7;
+    if (r <= 0.0) return 0.f;
+    return (float)(r * r * (1.0 - 1e-6));
+}
+
+// Scan the 8 slots of up to four buckets per step (8 lanes per bucket) and stage the candidates.
+// `b` holds one bucket index per lane (NONE32 = nothing); processes the buckets of all lanes whose bit is
+// set in `found`, following overflow chains.
+__device__ __forceinline__ void scan_found_buckets(const MapView& m, WarpSelect& ws, int lane, unsigned found, uint32_t b,
+                                                   float qx, float qy, float qz, unsigned long long& ncand) {
+    int nf = __popc(found);
+    for (int base = 0; base < nf; base += 4) {
+        int my = base + (lane >> 3);
+        bool has = my < nf;
+        unsigned src = has ? __fns(found, 0, my + 1) : 0u;
+        uint32_t bb = __shfl_sync(FULL, b, src & 31);
+        if (!has) bb = NONE32;
+        while (__any_sync(FULL, bb != NONE32)) {
+            uint32_t d = INF_BITS, id = 0xFFFFFFFFu, addr = 0;
+            uint32_t nxt = NONE32;
+            if (bb != NONE32) {
+                addr = bb * BUCKET_SLOTS + (lane & 7);
+                float4 p = __ldg(m.buckets + addr);
+                int pid = __float_as_int(p.w);
+                if (pid >= 0) {
+                    float dd = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                    uint32_t db = __float_as_uint(dd);
+                    if (db <= ws.tau) { d = db; id = (uint32_t)pid; }
+                }
+                nxt = __ldg(m.bucket_next + bb);
+            }
+            ncand += __popc(__ballot_sync(FULL, bb != NONE32));
+            ws.push(lane, d, id, addr);
+            bb = nxt;
+        }
+    }
+}
+
+// Exact 5-NN of (qx,qy,qz).  On return lanes 0..4 hold rank 0..4 in out (d == INF_BITS when absent);
+// returns the number found (warp-uniform).  max_sq_bits: float bits of the largest float <= max_dist
+// (INF_BITS for unbounded).
+__device__ __forceinline__ int warp_knn5(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits, int lane,
+                                         Cand& out, SearchStats* stats) {
+    WarpSelect ws;
+    ws.init(max_sq_bits);
+    unsigned long long ncand = 0;
+    const int g = m.gshift;
+    const int cqx = voxel_key1(qx, m.ds) >> g, cqy = voxel_key1(qy, m.ds) >> g, cqz = voxel_key1(qz, m.ds) >> g;
+    const float qabs = fmaxf(fabsf(qx), fmaxf(fabsf(qy), fabsf(qz)));
+    const float max_sq = __uint_as_float(max_sq_bits);
+    bool far_counted = false;
+
+    // ---- shell 1: 3x3x3 cells; the (at most) 8 distinct blocks are probed by lanes 0..7 -------------
+    {
+        int bx0 = (cqx - 1) >> 2, by0 = (cqy - 1) >> 2, bz0 = (cqz - 1) >> 2;
+        int slot = -1;
+        if (lane < 8) {
+            int bx = (lane & 4) ? ((cqx + 1) >> 2) : bx0, by = (lane & 2) ? ((cqy + 1) >> 2) : by0, bz = (lane & 1) ? ((cqz + 1) >> 2) : bz0;
+            slot = dir_find(m, pack_block(bx, by, bz));
+        }
+        uint32_t b = NONE32;
+        int dx = lane % 3 - 1, dy = (lane / 3) % 3 - 1, dz = lane / 9 - 1;
+        int cx = cqx + dx, cy = cqy + dy, cz = cqz + dz;
+        int which = (((cx >> 2) != bx0) ? 4 : 0) | (((cy >> 2) != by0) ? 2 : 0) | (((cz >> 2) != bz0) ? 1 : 0);
+        int s = __shfl_sync(FULL, slot, which);
+        if (lane < 27 && s >= 0) b = __ldg(m.cell_tab + (size_t)s * 64 + cell_off(cx, cy, cz));
+        unsigned found = __ballot_sync(FULL, b != NONE32);
+        scan_found_buckets(m, ws, lane, found, b, qx, qy, qz, ncand);
+        ws.flush(lane);
+        float cov = covered_sq(m.cell_edge, 1.f, qabs);
+        bool done = (ws.count == WarpSelect::FLIVO_K_ && __uint_as_float(ws.tau) <= cov) || (cov >= max_sq);
+        if (done) goto finish;
+    }
+    far_counted = true;
+    // ---- shell 2: 5x5x5 cells minus the inner 27 ---------------------------------------------------
+    {
+        for (int round = 0; round < 4; ++round) {
+            int ci = round * 32 + lane;
+            uint32_t b = NONE32;
+            if (ci < 125) {
+                int dx = ci % 5 - 2, dy = (ci / 5) % 5 - 2, dz = ci / 25 - 2;
+                if (max(abs(dx), max(abs(dy), abs(dz))) == 2) b = cell_bucket(m, cqx + dx, cqy + dy, cqz + dz);
+            }
+            unsigned found = __ballot_sync(FULL, b != NONE32);
+            scan_found_buckets(m, ws, lane, found, b, qx, qy, qz, ncand);
+        }
+        ws.flush(lane);
+        float cov = covered_sq(m.cell_edge, 2.f, qabs);
+        bool done = (ws.count == WarpSelect::FLIVO_K_ && __uint_as_float(ws.tau) <= cov) || (cov >= max_sq);
+        if (done) goto finish;
+    }
+    // ---- block rings ---------------------------------------------------------------------------------
+    {
+        const int bqx = cqx >> 2, bqy = cqy >> 2, bqz = cqz >> 2;
+        for (int ring = 1; ring <= FAR_MAX_RING; ++ring) {
+            int w = 2 * ring + 1, total = w * w * w;
+            for (int base = 0; base < total; base += 32) {
+                int bi = base + lane;
+                int slot = -1;
+                int bx = 0, by = 0, bz = 0;
+                if (bi < total) {
+                    int dx = bi % w - ring, dy = (bi / w) % w - ring, dz = bi / (w * w) - ring;
+                    int cheb = max(abs(dx), max(abs(dy), abs(dz)));
+                    if (cheb == ring || (ring == 1)) {
+                        bx = bqx + dx; by = bqy + dy; bz = bqz + dz;
+                        slot = dir_find(m, pack_block(bx, by, bz));
+                    }
+                }
+                unsigned fb = __ballot_sync(FULL, slot >= 0);
+                while (fb) {
+                    int src = __ffs(fb) - 1;
+                    fb &= fb - 1;
+                    int s = __shfl_sync(FULL, slot, src);
+                    int sbx = __shfl_sync(FULL, bx, src), sby = __shfl_sync(FULL, by, src), sbz = __shfl_sync(FULL, bz, src);
+                    // lanes cover the 64 cells of the block, two each; skip cells already visited (Chebyshev <= 2)
+                    for (int half = 0; half < 2; ++half) {
+                        int off = lane + 32 * half;
+                        int cx = sbx * 4 + ((off >> 4) & 3), cy = sby * 4 + ((off >> 2) & 3), cz = sbz * 4 + (off & 3);
+                        int cheb = max(abs(cx - cqx), max(abs(cy - cqy), abs(cz - cqz)));
+                        uint32_t bb = (cheb > 2) ? __ldg(m.cell_tab + (size_t)s * 64 + off) : NONE32;
+                        while (__any_sync(FULL, bb != NONE32)) {
+                            for (int sl = 0; sl < BUCKET_SLOTS; ++sl) {
+                                uint32_t d = INF_BITS, id = 0xFFFFFFFFu, addr = 0;
+                                if (bb != NONE32) {
+                                    addr = bb * BUCKET_SLOTS + sl;
+                                    float4 p = __ldg(m.buckets + addr);
+                                    int pid = __float_as_int(p.w);
+                                    if (pid >= 0) {
+                                        uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, p.x, p.y, p.z));
+                                        if (db <= ws.tau) { d = db; id = (uint32_t)pid; }
+                                    }
+                                }
+                                if (__any_sync(FULL, d != INF_BITS)) ws.push(lane, d, id, addr);
+                            }
+                            ncand += 8ull * __popc(__ballot_sync(FULL, bb != NONE32));
+                            bb = (bb != NONE32) ? __ldg(m.bucket_next + bb) : NONE32;
+                        }
+                    }
+                }
+            }
+            ws.flush(lane);
+            float cov = covered_sq(m.cell_edge, 4.f * ring, qabs);
+            bool done = (ws.count == WarpSelect::FLIVO_K_ && __uint_as_float(ws.tau) <= cov) || (cov >= max_sq);
+            if (done) goto finish;
+        }
+        // ---- directory sweep (unbounded searches in sparse regions) --------------------------------
+        if (stats && lane == 0) atomicAdd(&stats->sweeps, 1ull);
+        const float bedge = m.cell_edge * 4.f;
+        for (uint32_t base = 0; base <= m.dir_mask; base += 32) {
+            uint32_t s = base + lane;
+            unsigned long long key = __ldg(m.dir_keys + s);
+            bool want = false;
+            int bx = 0, by = 0, bz = 0;
+            if (key != DIR_EMPTY) {
+                unpack_block(key, bx, by, bz);
+                int cheb = max(abs(bx - bqx), max(abs(by - bqy), abs(bz - bqz)));
+                if (cheb > FAR_MAX_RING) {
+                    // conservative lower bound of the distance from q to the block's box
+                    float gap = 0.f;
+                    float lo, hi, d1;
+                    lo = bx * bedge; hi = lo + bedge; d1 = fmaxf(fmaxf(lo - qx, qx - hi), 0.f); gap += d1 * d1;
+                    lo = by * bedge; hi = lo + bedge; d1 = fmaxf(fmaxf(lo - qy, qy - hi), 0.f); gap += d1 * d1;
+                    lo = bz * bedge; hi = lo + bedge; d1 = fmaxf(fmaxf(lo - qz, qz - hi), 0.f); gap += d1 * d1;
+                    float slack = (qabs + sqrtf(gap) + bedge) * 1e-5f + 1e-6f;
+                    float g2 = fmaxf(sqrtf(gap) - slack, 0.f);
+                    want = (g2 * g2 * 0.9999f) <= __uint_as_float(ws.tau);
+                }
+            }
+            unsigned fb = __ballot_sync(FULL, want);
+            while (fb) {
+                int src = __ffs(fb) - 1;
+                fb &= fb - 1;
+                uint32_t ss = __shfl_sync(FULL, s, src);
+                for (int half = 0; half < 2; ++half) {
+                    int off = lane + 32 * half;
+                    uint32_t bb = __ldg(m.cell_tab + (size_t)ss * 64 + off);
+                    while (__any_sync(FULL, bb != NONE32)) {
+                        for (int sl = 0; sl < BUCKET_SLOTS; ++sl) {
+                            uint32_t d = INF_BITS, id = 0xFFFFFFFFu, addr = 0;
+                            if (bb != NONE32) {
+                                addr = bb * BUCKET_SLOTS + sl;
+                                float4 p = __ldg(m.buckets + addr);
+                                int pid = __float_as_int(p.w);
+                                if (pid >= 0) {
+                                    uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, p.x, p.y, p.z));
+                                    if (db <= ws.tau) { d = db; id = (uint32_t)pid; }
+                                }
+                            }
+                            if (__any_sync(FULL, d != INF_BITS)) ws.push(lane, d, id, addr);
+                        }
+                        ncand += 8ull * __popc(__ballot_sync(FULL, bb != NONE32));
+                        bb = (bb != NONE32) ? __ldg(m.bucket_next + bb) : NONE32;
+                    }
+                }
+                ws.flush(lane);  // tighten tau before judging the next block
+            }
+        }
+        ws.flush(lane);
+    }
+finish:
+    if (stats && lane == 0) {
+        if (far_counted) atomicAdd(&stats->far_queries, 1ull);
+        atomicAdd(&stats->candidates, ncand);
+    }
+    out = ws.c0;
+    return ws.count;
+}
+
+}  // namespace flivo

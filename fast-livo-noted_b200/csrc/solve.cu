@@ -1,0 +1,605 @@
+// solve.cu — "(c) the 12x12 solve and state/covariance update kept on-device in double precision".
+//
+// One single-CTA kernel per trip closes the loop on the device:
+//   * fixed-order final reduction of the fused kernel's group partials into H^T H (12x12) and H^T z;
+//   * V3: one trip of esekf::update_iterated_dyn_share_modified
+//         (reference include/IKFoM_toolkit/esekfom/esekfom.hpp:1619-1928) on the 23-DOF manifold state
+//         (include/use-ikfom.hpp:12-21; SO3 / S2 algebra mtk/types/SOn.hpp:233-238, S2.hpp:128-280,
+//         A_matrix mtk/src/mtkmath.hpp:236-247);
+//   * V1: one trip of the loop body of LaserMapping::Run (src/laser_mapping.cpp:178-238) on the 18-DOF
+//         StatesGroup (include/common_lib.h:552-587, Exp/Log include/so3_math.h:62-91);
+//   * the re-match / stop policy, written to the device control block the next fused
+//     launch reads — no host round trip between trips.
+//
+// Algebra note: the reference forms P_inv = ((P/R)^-1 + [HTH 0;0 0])^-1 with two dense
+// n x n inverses and then only uses its first 12 columns.  By the matrix-inversion lemma those columns are
+// W = Q[:, :12] (I + HTH Q[:12,:12])^-1 with Q = P/R: one 12x12 (V1: 6x6) solve, better conditioned, and
+// identical in exact arithmetic.  Parity with the restated reference is tolerance-checked (dx <= 1e-6).
+#include "fused.cuh"
+#include "search.cuh"
+#include "solve.cuh"
+
+namespace flivo {
+
+// ---- small dense helpers ------------------------------------------------------------------------------
+__device__ void d_hat(const double* v, double* H) {
+    H[0] = 0; H[1] = -v[2]; H[2] = v[1]; H[3] = v[2]; H[4] = 0; H[5] = -v[0]; H[6] = -v[1]; H[7] = v[0]; H[8] = 0;
+}
+__device__ void d_mat3mul(const double* A, const double* B, double* C) {
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) C[i * 3 + j] = A[i * 3] * B[j] + A[i * 3 + 1] * B[3 + j] + A[i * 3 + 2] * B[6 + j];
+}
+// MTK::A_matrix (mtkmath.hpp:236-247)
+__device__ void d_A_matrix(const double* v, double* A) {
+    double sq = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+    double nrm = sqrt(sq);
+    for (int i = 0; i < 9; ++i) A[i] = 0.0;
+    A[0] = A[4] = A[8] = 1.0;
+    if (nrm < 1e-11) return;
+    double H[9], H2[9];
+    d_hat(v, H);
+    d_mat3mul(H, H, H2);
+    double a = (1 - cos(nrm)) / sq, b = (1 - sin(nrm) / nrm) / sq;
+    for (int i = 0; i < 9; ++i) A[i] += a * H[i] + b * H2[i];
+}
+// rotation-matrix form of SO3::exp (SOn.hpp:293-297 via MTK::exp / cos_sinc_sqrt, mtkmath.hpp:139-171,249-256):
+// Rodrigues with series near zero.  The reference composes unit quaternions; identical up to rounding.
+__device__ void d_so3_exp(const double* v, double* R) {
+    double t2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+    double a, b;  // sin(t)/t, (1-cos t)/t^2
+    if (t2 < 1e-8) {
+        a = 1.0 - t2 / 6.0 + t2 * t2 / 120.0;
+        b = 0.5 - t2 / 24.0 + t2 * t2 / 720.0;
+    } else {
+        double t = sqrt(t2);
+        a = sin(t) / t;
+        b = (1.0 - cos(t)) / t2;
+    }
+    double K[9], K2[9];
+    d_hat(v, K);
+    d_mat3mul(K, K, K2);
+    for (int i = 0; i < 9; ++i) R[i] = a * K[i] + b * K2[i];
+    R[0] += 1.0; R[4] += 1.0; R[8] += 1.0;
+}
+// SO3 log of a rotation matrix, accurate for small angles (SOn.hpp:300-304 / MTK::log computes the same
+// vector from the unit quaternion: 2*atan(|v|/w)/|v| * v).
+__device__ void d_so3_log(const double* R, double* o) {
+    double vx = 0.5 * (R[7] - R[5]), vy = 0.5 * (R[2] - R[6]), vz = 0.5 * (R[3] - R[1]);  // sin(t) * axis
+    double s = sqrt(vx * vx + vy * vy + vz * vz);
+    double c = 0.5 * (R[0] + R[4] + R[8] - 1.0);
+    double f;
+    if (s < 1e-11) f = 1.0;
+    else f = atan2(s, c) / s;
+    o[0] = f * vx; o[1] = f * vy; o[2] = f * vz;
+}
+// V1 Exp / Log (include/so3_math.h:62-91)
+__device__ void d_Exp_v1(double v1, double v2, double v3, double* R) {
+    double nrm = sqrt(v1 * v1 + v2 * v2 + v3 * v3);
+    for (int i = 0; i < 9; ++i) R[i] = 0;
+    R[0] = R[4] = R[8] = 1;
+    if (nrm > 0.00001) {
+        double r[3] = {v1 / nrm, v2 / nrm, v3 / nrm};
+        double K[9], K2[9];
+        d_hat(r, K);
+        d_mat3mul(K, K, K2);
+        double s = sin(nrm), c = 1.0 - cos(nrm);
+        for (int i = 0; i < 9; ++i) R[i] += s * K[i] + c * K2[i];
+    }
+}
+__device__ void d_Log_v1(const double* R, double* o) {
+    double tr = R[0] + R[4] + R[8];
+    double theta = (tr > 3.0 - 1e-6) ? 0.0 : acos(0.5 * (tr - 1));
+    double K[3] = {R[7] - R[5], R[2] - R[6], R[3] - R[1]};
+    double f = (fabs(theta) < 0.001) ? 0.5 : (0.5 * theta / sin(theta));
+    for (int i = 0; i < 3; ++i) o[i] = f * K[i];
+}
+
+// ---- S2 (gravity) algebra, MTK::S2<double, 98090, 10000, 1> (use-ikfom.hpp:8; S2.hpp) ----------------------
+#define S2_LEN (98090.0 / 10000.0)
+__device__ void d_s2_Bx(const double* vec, double* Bx) {  // 3x2 row-major, S2_typ == 1 (S2.hpp:213-231)
+    const double len = S2_LEN;
+    if (vec[0] + len > 1e-11) {
+        double d = len + vec[0];
+        Bx[0] = -vec[1];                   Bx[1] = -vec[2];
+        Bx[2] = len - vec[1] * vec[1] / d; Bx[3] = -vec[2] * vec[1] / d;
+        Bx[4] = -vec[2] * vec[1] / d;      Bx[5] = len - vec[2] * vec[2] / d;
+        for (int i = 0; i < 6; ++i) Bx[i] /= len;
+    } else {
+        for (int i = 0; i < 6; ++i) Bx[i] = 0.0;
+        Bx[3] = -1; Bx[4] = 1;
+    }
+}
+__device__ void d_cross(const double* a, const double* b, double* o) {
+    o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
+}
+__device__ void d_s2_boxminus(const double* vec, const double* other, double* res2) {  // S2.hpp:136-160
+    double cr[3];
+    d_cross(vec, other, cr);
+    double v_sin = sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]);
+    double v_cos = vec[0] * other[0] + vec[1] * other[1] + vec[2] * other[2];
+    double theta = atan2(v_sin, v_cos);
+    if (v_sin < 1e-11) {
+        if (fabs(theta) > 1e-11) { res2[0] = 3.1415926; res2[1] = 0; }
+        else { res2[0] = 0; res2[1] = 0; }
+    } else {
+        double Bx[6], hv[3];
+        d_s2_Bx(other, Bx);
+        d_cross(other, vec, hv);
+        double f = theta / v_sin;
+        for (int c = 0; c < 2; ++c) res2[c] = f * (Bx[c] * hv[0] + Bx[2 + c] * hv[1] + Bx[4 + c] * hv[2]);
+    }
+}
+__device__ void d_s2_boxplus(double* vec, const double* delta2) {  // S2.hpp:128-134
+    double Bx[6], Bu[3], R[9], o[3];
+    d_s2_Bx(vec, Bx);
+    for (int r = 0; r < 3; ++r) Bu[r] = Bx[r * 2] * delta2[0] + Bx[r * 2 + 1] * delta2[1];
+    d_so3_exp(Bu, R);
+    for (int r = 0; r < 3; ++r) o[r] = R[r * 3] * vec[0] + R[r * 3 + 1] * vec[1] + R[r * 3 + 2] * vec[2];
+    vec[0] = o[0]; vec[1] = o[1]; vec[2] = o[2];
+}
+__device__ void d_s2_Nx_yy(const double* vec, double* Nx) {  // 2x3, S2.hpp:259-264
+    double Bx[6], H[9];
+    d_s2_Bx(vec, Bx);
+    d_hat(vec, H);
+    for (int r = 0; r < 2; ++r)
+        for (int c = 0; c < 3; ++c)
+            Nx[r * 3 + c] = 1 / S2_LEN / S2_LEN * (Bx[r] * H[c] + Bx[2 + r] * H[3 + c] + Bx[4 + r] * H[6 + c]);
+}
+// S2_Mx (S2.hpp:266-280).  "scalar(1/2)" there is integer division == 0, so exp_delta is the identity.
+__device__ void d_s2_Mx(const double* vec, const double* delta2, double* Mx /*3x2*/) {
+    double Bx[6], H[9];
+    d_s2_Bx(vec, Bx);
+    d_hat(vec, H);
+    double dn = sqrt(delta2[0] * delta2[0] + delta2[1] * delta2[1]);
+    if (dn < 1e-11) {
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 2; ++c) Mx[r * 2 + c] = -(H[r * 3] * Bx[c] + H[r * 3 + 1] * Bx[2 + c] + H[r * 3 + 2] * Bx[4 + c]);
+    } else {
+        double Bu[3], Am[9], T2[9];
+        for (int r = 0; r < 3; ++r) Bu[r] = Bx[r * 2] * delta2[0] + Bx[r * 2 + 1] * delta2[1];
+        d_A_matrix(Bu, Am);
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) T2[i * 3 + j] = H[i * 3] * Am[j * 3] + H[i * 3 + 1] * Am[j * 3 + 1] + H[i * 3 + 2] * Am[j * 3 + 2];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 2; ++c) Mx[r * 2 + c] = -(T2[r * 3] * Bx[c] + T2[r * 3 + 1] * Bx[2 + c] + T2[r * 3 + 2] * Bx[4 + c]);
+    }
+}
+
+// state field offsets inside flivo_state (doubles)
+enum { S_ROT = 0, S_POS = 9, S_OFFR = 12, S_OFFT = 21, S_VEL = 24, S_BG = 27, S_BA = 30, S_GRAV = 33 };
+
+// x (-) y, state_ikfom order pos, rot, offR, offT, vel, bg, ba, grav(S2)
+__device__ void d_boxminus_v3(const double* x, const double* y, double* d) {
+    for (int i = 0; i < 3; ++i) d[i] = x[S_POS + i] - y[S_POS + i];
+    double Rd[9];
+    // other.conjugate() * this  ->  y.rot^T * x.rot
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) Rd[i * 3 + j] = y[S_ROT + i] * x[S_ROT + j] + y[S_ROT + 3 + i] * x[S_ROT + 3 + j] + y[S_ROT + 6 + i] * x[S_ROT + 6 + j];
+    d_so3_log(Rd, d + 3);
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) Rd[i * 3 + j] = y[S_OFFR + i] * x[S_OFFR + j] + y[S_OFFR + 3 + i] * x[S_OFFR + 3 + j] + y[S_OFFR + 6 + i] * x[S_OFFR + 6 + j];
+    d_so3_log(Rd, d + 6);
+    for (int i = 0; i < 3; ++i) d[9 + i] = x[S_OFFT + i] - y[S_OFFT + i];
+    for (int i = 0; i < 3; ++i) d[12 + i] = x[S_VEL + i] - y[S_VEL + i];
+    for (int i = 0; i < 3; ++i) d[15 + i] = x[S_BG + i] - y[S_BG + i];
+    for (int i = 0; i < 3; ++i) d[18 + i] = x[S_BA + i] - y[S_BA + i];
+    d_s2_boxminus(x + S_GRAV, y + S_GRAV, d + 21);
+}
+__device__ void d_boxplus_v3(double* x, const double* d) {
+    for (int i = 0; i < 3; ++i) x[S_POS + i] += d[i];
+    double E[9], Rn[9];
+    d_so3_exp(d + 3, E);
+    d_mat3mul(x + S_ROT, E, Rn);
+    for (int i = 0; i < 9; ++i) x[S_ROT + i] = Rn[i];
+    d_so3_exp(d + 6, E);
+    d_mat3mul(x + S_OFFR, E, Rn);
+    for (int i = 0; i < 9; ++i) x[S_OFFR + i] = Rn[i];
+    for (int i = 0; i < 3; ++i) x[S_OFFT + i] += d[9 + i];
+    for (int i = 0; i < 3; ++i) x[S_VEL + i] += d[12 + i];
+    for (int i = 0; i < 3; ++i) x[S_BG + i] += d[15 + i];
+    for (int i = 0; i < 3; ++i) x[S_BA + i] += d[18 + i];
+    d_s2_boxplus(x + S_GRAV, d + 21);
+}
+
+// T = blockdiag(I3, J3, J6, I.., J2) stored sparsely: apply to rows / columns of an n x n matrix in shared memory
+struct BlockT {
+    double J3[9], J6[9], J2[4];
+};
+// M <- T * M  (rows 3..5, 6..8, 21..22); all threads participate, caller syncs
+__device__ void apply_T_rows(double* M, int n, int ncols, const BlockT& T, int tid, int nthreads) {
+    for (int c = tid; c < ncols; c += nthreads) {
+        double a0 = M[3 * n + c], a1 = M[4 * n + c], a2 = M[5 * n + c];
+        M[3 * n + c] = T.J3[0] * a0 + T.J3[1] * a1 + T.J3[2] * a2;
+        M[4 * n + c] = T.J3[3] * a0 + T.J3[4] * a1 + T.J3[5] * a2;
+        M[5 * n + c] = T.J3[6] * a0 + T.J3[7] * a1 + T.J3[8] * a2;
+        a0 = M[6 * n + c]; a1 = M[7 * n + c]; a2 = M[8 * n + c];
+        M[6 * n + c] = T.J6[0] * a0 + T.J6[1] * a1 + T.J6[2] * a2;
+        M[7 * n + c] = T.J6[3] * a0 + T.J6[4] * a1 + T.J6[5] * a2;
+        M[8 * n + c] = T.J6[6] * a0 + T.J6[7] * a1 + T.J6[8] * a2;
+        a0 = M[21 * n + c]; a1 = M[22 * n + c];
+        M[21 * n + c] = T.J2[0] * a0 + T.J2[1] * a1;
+        M[22 * n + c] = T.J2[2] * a0 + T.J2[3] * a1;
+    }
+}
+// M <- M * T^T  (columns 3..5, 6..8, 21..22)
+__device__ void apply_T_cols(double* M, int n, const BlockT& T, int tid, int nthreads) {
+    for (int r = tid; r < n; r += nthreads) {
+        double* row = M + r * n;
+        double a0 = row[3], a1 = row[4], a2 = row[5];
+        row[3] = a0 * T.J3[0] + a1 * T.J3[1] + a2 * T.J3[2];
+        row[4] = a0 * T.J3[3] + a1 * T.J3[4] + a2 * T.J3[5];
+        row[5] = a0 * T.J3[6] + a1 * T.J3[7] + a2 * T.J3[8];
+        a0 = row[6]; a1 = row[7]; a2 = row[8];
+        row[6] = a0 * T.J6[0] + a1 * T.J6[1] + a2 * T.J6[2];
+        row[7] = a0 * T.J6[3] + a1 * T.J6[4] + a2 * T.J6[5];
+        row[8] = a0 * T.J6[6] + a1 * T.J6[7] + a2 * T.J6[8];
+        a0 = row[21]; a1 = row[22];
+        row[21] = a0 * T.J2[0] + a1 * T.J2[1];
+        row[22] = a0 * T.J2[2] + a1 * T.J2[3];
+    }
+}
+
+// Solve S^T X = B in place by Gauss-Jordan with partial pivoting; one warp.  Aug is m x (m + nrhs) row-major
+// holding [S^T | B]; on return the right part holds X.  Returns false on a zero pivot.
+__device__ bool warp_gauss_jordan(double* Aug, int m, int nrhs, int lane) {
+    const int w = m + nrhs;
+    bool ok = true;
+    for (int k = 0; k < m; ++k) {
+        // pivot: first maximum of |Aug[i][k]|, i >= k (all lanes compute it redundantly from shared memory)
+        int p = k;
+        double best = fabs(Aug[k * w + k]);
+        for (int i = k + 1; i < m; ++i) {
+            double v = fabs(Aug[i * w + k]);
+            if (v > best) { best = v; p = i; }
+        }
+        if (best == 0.0) ok = false;
+        __syncwarp();
+        if (p != k)
+            for (int c = lane; c < w; c += 32) { double t = Aug[k * w + c]; Aug[k * w + c] = Aug[p * w + c]; Aug[p * w + c] = t; }
+        __syncwarp();
+        double piv = Aug[k * w + k];
+        __syncwarp();
+        for (int c = lane; c < w; c += 32) Aug[k * w + c] = Aug[k * w + c] / piv;
+        __syncwarp();
+        // eliminate column k from every other row; lanes own columns, so the factor column is read before it changes
+        for (int i = 0; i < m; ++i) {
+            if (i == k) continue;
+            double f = Aug[i * w + k];
+            __syncwarp();
+            for (int c = lane; c < w; c += 32) Aug[i * w + c] -= f * Aug[k * w + c];
+            __syncwarp();
+        }
+    }
+    return ok;
+}
+
+// ---- fixed-order final reduction of the group partials ------------------------------------------------------
+// out92[t] = sum over groups; deterministic: slices of groups are summed sequentially by fixed threads, then the
+// slice sums are added in slice order.
+__device__ void reduce_groups(const double* __restrict__ gpartials, int groups, double* s_slices /*[8][96]*/, double* out92,
+                              int tid, int nthreads) {
+    const int NS = 8;
+    int slice = tid / PSTRIDE, t = tid % PSTRIDE;
+    if (slice < NS && t < NTERMS) {
+        int g0 = (int)(((long long)groups * slice) / NS), g1 = (int)(((long long)groups * (slice + 1)) / NS);
+        double s = 0.0;
+        for (int g = g0; g < g1; ++g) s += __ldcg(gpartials + (size_t)g * PSTRIDE + t);
+        s_slices[slice * PSTRIDE + t] = s;
+    }
+    __syncthreads();
+    if (tid < NTERMS) {
+        double s = 0.0;
+        for (int sl = 0; sl < NS; ++sl) s += s_slices[sl * PSTRIDE + tid];
+        out92[tid] = s;
+    }
+    __syncthreads();
+}
+
+constexpr int SOLVE_THREADS = 768;  // 8 slices x 96
+
+__global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
+    __shared__ double s_slices[8 * PSTRIDE];
+    __shared__ double s_sum[PSTRIDE];
+    __shared__ double s_H[144];
+    __shared__ double s_z[12];
+    __shared__ double s_P[23 * 23];
+    __shared__ double s_L[23 * 23];
+    __shared__ double s_Aug[12 * 35];
+    __shared__ double s_W[23 * 12];
+    __shared__ double s_Kx[23 * 12];
+    __shared__ double s_x[36], s_xp[36];
+    __shared__ double s_dx[23], s_dxnew[23], s_dxo[23], s_Kh[23];
+    __shared__ BlockT s_T;
+    __shared__ int s_flag[4];  // [0]=stop, [1]=ok
+
+    Ctl* ctl = S.ctl;
+    const int tid = threadIdx.x, NT = blockDim.x;
+    if (S.phase != SOLVE_PHASE_REDUCE_ONLY && ctl->stopped) return;
+
+    // ---- 0. normal equations -------------------------------------------------------------------------
+    if (S.phase == SOLVE_PHASE_FROM_RANKS) {
+        // multi-GPU: every rank's 92-term block was gathered; sum in rank order (bit-identical on all ranks)
+        if (tid < NTERMS) {
+            double s = 0.0;
+            for (int r = 0; r < S.nranks; ++r) s += S.rank_blocks[(size_t)r * PSTRIDE + tid];
+            s_sum[tid] = s;
+        }
+        __syncthreads();
+    } else {
+        reduce_groups(S.gpartials, S.groups, s_slices, s_sum, tid, NT);
+    }
+    if (S.phase == SOLVE_PHASE_REDUCE_ONLY) {
+        if (tid < NTERMS) S.sum_out[tid] = s_sum[tid];
+        if (tid == 0) ctl->unit_counter = 0;
+        return;
+    }
+    if (tid < 144) {
+        int a = tid / 12, b = tid % 12;
+        int i = a < b ? a : b, j = a < b ? b : a;
+        int t = i * 12 - (i * (i - 1)) / 2 + (j - i);  // index of (i, j), i <= j, in the 78 upper terms
+        s_H[tid] = s_sum[t];
+    }
+    if (tid < 12) s_z[tid] = s_sum[78 + tid];
+    if (tid < 36) { s_x[tid] = S.x[tid]; s_xp[tid] = S.x_prop[tid]; }
+    const int mode = S.mode;
+    const int n = (mode == 1) ? 18 : 23;
+    for (int e = tid; e < n * n; e += NT) s_P[e] = S.P_prop[e];
+    __syncthreads();
+    if (tid == 0) {
+        bool finite = true;
+        for (int t = 0; t < NTERMS; ++t) finite = finite && isfinite(s_sum[t]);
+        s_flag[1] = finite ? 1 : 0;
+        int ne = (int)s_sum[91];
+        ctl->n_eff = ne;
+        ctl->res_mean = ne > 0 ? s_sum[90] / (double)ne : 0.0;
+        if (S.sum_out) for (int t = 0; t < NTERMS; ++t) S.sum_out[t] = s_sum[t];
+    }
+    __syncthreads();
+    if (!s_flag[1]) {  // NaN guard: leave x and P untouched and stop the loop
+        if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl->unit_counter = 0; }
+        return;
+    }
+
+    if (mode == 0) {
+        // ================= V3: esekfom.hpp:1633-1927 ==================================================
+        if (tid == 0) {
+            d_boxminus_v3(s_x, s_xp, s_dx);                                   // :1646
+            for (int i = 0; i < 23; ++i) s_dxnew[i] = s_dx[i];
+            double A[9];
+            d_A_matrix(s_dx + 3, A);                                          // :1663
+            for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J3[i * 3 + j] = A[j * 3 + i];
+            d_A_matrix(s_dx + 6, A);
+            for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J6[i * 3 + j] = A[j * 3 + i];
+            double Nx[6], Mx[6];
+            d_s2_Nx_yy(s_x + S_GRAV, Nx);                                     // :1684-1686
+            d_s2_Mx(s_xp + S_GRAV, s_dx + 21, Mx);
+            for (int r = 0; r < 2; ++r) for (int c = 0; c < 2; ++c) s_T.J2[r * 2 + c] = Nx[r * 3] * Mx[c] + Nx[r * 3 + 1] * Mx[2 + c] + Nx[r * 3 + 2] * Mx[4 + c];
+            double t0, t1, t2;
+            t0 = s_T.J3[0] * s_dxnew[3] + s_T.J3[1] * s_dxnew[4] + s_T.J3[2] * s_dxnew[5];
+            t1 = s_T.J3[3] * s_dxnew[3] + s_T.J3[4] * s_dxnew[4] + s_T.J3[5] * s_dxnew[5];
+            t2 = s_T.J3[6] * s_dxnew[3] + s_T.J3[7] * s_dxnew[4] + s_T.J3[8] * s_dxnew[5];
+            s_dxnew[3] = t0; s_dxnew[4] = t1; s_dxnew[5] = t2;
+            t0 = s_T.J6[0] * s_dxnew[6] + s_T.J6[1] * s_dxnew[7] + s_T.J6[2] * s_dxnew[8];
+            t1 = s_T.J6[3] * s_dxnew[6] + s_T.J6[4] * s_dxnew[7] + s_T.J6[5] * s_dxnew[8];
+            t2 = s_T.J6[6] * s_dxnew[6] + s_T.J6[7] * s_dxnew[7] + s_T.J6[8] * s_dxnew[8];
+            s_dxnew[6] = t0; s_dxnew[7] = t1; s_dxnew[8] = t2;
+            t0 = s_T.J2[0] * s_dxnew[21] + s_T.J2[1] * s_dxnew[22];
+            t1 = s_T.J2[2] * s_dxnew[21] + s_T.J2[3] * s_dxnew[22];
+            s_dxnew[21] = t0; s_dxnew[22] = t1;
+        }
+        __syncthreads();
+        apply_T_rows(s_P, 23, 23, s_T, tid, NT);                              // :1665-1672, :1688-1695
+        __syncthreads();
+        apply_T_cols(s_P, 23, s_T, tid, NT);
+        __syncthreads();
+        // Aug = [S^T | Q1^T],  S = I + HTH * Q11,  Q = P / R
+        const double invR = 1.0 / S.R;
+        for (int e = tid; e < 12 * 35; e += NT) {
+            int r = e / 35, c = e % 35;
+            double v;
+            if (c < 12) {  // S^T[r][c] = S[c][r] = delta + sum_k H[c][k] Q[k][r]
+                double s = 0.0;
+                for (int k = 0; k < 12; ++k) s += s_H[c * 12 + k] * (s_P[k * 23 + r] * invR);
+                v = s + (r == c ? 1.0 : 0.0);
+            } else {       // Q1^T[r][i] = Q[i][r]
+                int i = c - 12;
+                v = s_P[i * 23 + r] * invR;
+            }
+            s_Aug[e] = v;
+        }
+        __syncthreads();
+        if (tid < 32) {
+            bool ok = warp_gauss_jordan(s_Aug, 12, 23, tid);
+            if (tid == 0) s_flag[1] = ok ? 1 : 0;
+        }
+        __syncthreads();
+        // W[i][a] = X[a][i];  K_h = W * HTz (:1801);  K_x[:, :12] = W * HTH (:1806)
+        for (int e = tid; e < 23 * 12; e += NT) { int i = e / 12, a = e % 12; s_W[e] = s_Aug[a * 35 + 12 + i]; }
+        __syncthreads();
+        for (int e = tid; e < 23 * 12; e += NT) {
+            int i = e / 12, b = e % 12;
+            double s = 0.0;
+            for (int a = 0; a < 12; ++a) s += s_W[i * 12 + a] * s_H[a * 12 + b];
+            s_Kx[e] = s;
+        }
+        if (tid < 23) {
+            double s = 0.0;
+            for (int a = 0; a < 12; ++a) s += s_W[tid * 12 + a] * s_z[a];
+            s_Kh[tid] = s;
+        }
+        __syncthreads();
+        if (tid < 23) {                                                       // :1812
+            double s = s_Kh[tid];
+            for (int j = 0; j < 12; ++j) s += s_Kx[tid * 12 + j] * s_dxnew[j];
+            s_dxo[tid] = s - s_dxnew[tid];
+        }
+        __syncthreads();
+        if (tid == 0) {
+            d_boxplus_v3(s_x, s_dxo);                                         // :1814
+            int converge = 1;
+            for (int i = 0; i < 23; ++i) if (fabs(s_dxo[i]) > S.limit[i]) { converge = 0; break; }
+            int t = ctl->t, it = ctl->iter;
+            if (converge) t++;
+            if (!t && it == S.max_iter - 2) converge = 1;                    // :1825-1828
+            int stop = (t > 1 || it == S.max_iter - 1) ? 1 : 0;               // :1831
+            ctl->t = t;
+            int trip = ctl->trips;
+            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.force_search) ? 1 : 0;
+            ctl->searches += (ctl->search || S.force_search) ? 1 : 0;
+            ctl->trips = trip + 1;
+            ctl->search = converge;
+            ctl->iter = it + 1;
+            ctl->converged = t > 0 ? 1 : 0;
+            ctl->stopped = stop;
+            ctl->unit_counter = 0;
+            for (int i = 0; i < 23; ++i) ctl->dx_last[i] = s_dxo[i];
+            s_flag[0] = stop;
+            if (stop) {
+                double A[9];
+                d_A_matrix(s_dxo + 3, A);                                     // :1842
+                for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J3[i * 3 + j] = A[j * 3 + i];
+                d_A_matrix(s_dxo + 6, A);
+                for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J6[i * 3 + j] = A[j * 3 + i];
+                double Nx[6], Mx[6];
+                d_s2_Nx_yy(s_x + S_GRAV, Nx);                                 // :1877-1879 (x_ already updated)
+                d_s2_Mx(s_xp + S_GRAV, s_dxo + 21, Mx);
+                for (int r = 0; r < 2; ++r) for (int c = 0; c < 2; ++c) s_T.J2[r * 2 + c] = Nx[r * 3] * Mx[c] + Nx[r * 3 + 1] * Mx[2 + c] + Nx[r * 3 + 2] * Mx[4 + c];
+            }
+        }
+        __syncthreads();
+        if (tid < 36) S.x[tid] = s_x[tid];
+        if (s_flag[0]) {
+            // L = T' P T'^T, P <- P T'^T, K_x <- T' K_x, P_out = L - K_x[:, :12] P[:12, :]   (:1833-1921)
+            apply_T_cols(s_P, 23, s_T, tid, NT);
+            __syncthreads();
+            for (int e = tid; e < 23 * 23; e += NT) s_L[e] = s_P[e];
+            __syncthreads();
+            apply_T_rows(s_L, 23, 23, s_T, tid, NT);
+            apply_T_rows(s_Kx, 12, 12, s_T, tid, NT);
+            __syncthreads();
+            for (int e = tid; e < 23 * 23; e += NT) {
+                int i = e / 23, j = e % 23;
+                double s = 0.0;
+                for (int a = 0; a < 12; ++a) s += s_Kx[i * 12 + a] * s_P[a * 23 + j];
+                S.P_out[e] = s_L[e] - s;
+            }
+        }
+    } else {
+        // ================= V1: src/laser_mapping.cpp:178-238 ==========================================
+        // HPH (6x6) = Hsub^T (1/R) Hsub with Hsub = [A | n] = V3 columns [3:6 | 0:3]  (:584-586)
+        __shared__ double s_H6[36], s_z6[6], s_vec[18], s_sol[18], s_G[18 * 6];
+        const double w = 1.0 / S.R;
+        if (tid < 36) {
+            const int map6[6] = {3, 4, 5, 0, 1, 2};
+            int a = tid / 6, b = tid % 6;
+            s_H6[tid] = s_H[map6[a] * 12 + map6[b]] * w;
+            if (tid < 6) s_z6[tid] = s_z[map6[tid]] * w;
+        }
+        if (tid == 0) {
+            // vec = state_propagat - state (common_lib.h:576-587)
+            double rotd[9];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j)
+                    rotd[i * 3 + j] = s_x[S_ROT + i] * s_xp[S_ROT + j] + s_x[S_ROT + 3 + i] * s_xp[S_ROT + 3 + j] + s_x[S_ROT + 6 + i] * s_xp[S_ROT + 6 + j];
+            d_Log_v1(rotd, s_vec);
+            for (int i = 0; i < 3; ++i) {
+                s_vec[3 + i] = s_xp[S_POS + i] - s_x[S_POS + i];
+                s_vec[6 + i] = s_xp[S_VEL + i] - s_x[S_VEL + i];
+                s_vec[9 + i] = s_xp[S_BG + i] - s_x[S_BG + i];
+                s_vec[12 + i] = s_xp[S_BA + i] - s_x[S_BA + i];
+                s_vec[15 + i] = s_xp[S_GRAV + i] - s_x[S_GRAV + i];
+            }
+        }
+        __syncthreads();
+        // Aug (6 x 24) = [S^T | C1^T],  S = I + H6 * C11,  C = state.cov
+        for (int e = tid; e < 6 * 24; e += NT) {
+            int r = e / 24, c = e % 24;
+            double v;
+            if (c < 6) {
+                double s = 0.0;
+                for (int k = 0; k < 6; ++k) s += s_H6[c * 6 + k] * s_P[k * 18 + r];
+                v = s + (r == c ? 1.0 : 0.0);
+            } else {
+                v = s_P[(c - 6) * 18 + r];
+            }
+            s_Aug[e] = v;
+        }
+        __syncthreads();
+        if (tid < 32) {
+            bool ok = warp_gauss_jordan(s_Aug, 6, 18, tid);
+            if (tid == 0) s_flag[1] = ok ? 1 : 0;
+        }
+        __syncthreads();
+        for (int e = tid; e < 18 * 6; e += NT) { int i = e / 6, a = e % 6; s_W[e] = s_Aug[a * 24 + 6 + i]; }  // K_1[:, :6]
+        __syncthreads();
+        for (int e = tid; e < 18 * 6; e += NT) {                             // G[:, :6] = K_1[:, :6] * HPH (:191)
+            int i = e / 6, b = e % 6;
+            double s = 0.0;
+            for (int a = 0; a < 6; ++a) s += s_W[i * 6 + a] * s_H6[a * 6 + b];
+            s_G[e] = s;
+        }
+        __syncthreads();
+        if (tid < 18) {                                                      // :193
+            double s1 = 0.0, s2 = 0.0;
+            for (int a = 0; a < 6; ++a) { s1 += s_W[tid * 6 + a] * s_z6[a]; s2 += s_G[tid * 6 + a] * s_vec[a]; }
+            s_sol[tid] = s1 + s_vec[tid] - s2;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double E[9], Rn[9];
+            d_Exp_v1(s_sol[0], s_sol[1], s_sol[2], E);                        // state += solution (:204)
+            d_mat3mul(s_x + S_ROT, E, Rn);
+            for (int i = 0; i < 9; ++i) s_x[S_ROT + i] = Rn[i];
+            for (int i = 0; i < 3; ++i) {
+                s_x[S_POS + i] += s_sol[3 + i]; s_x[S_VEL + i] += s_sol[6 + i]; s_x[S_BG + i] += s_sol[9 + i];
+                s_x[S_BA + i] += s_sol[12 + i]; s_x[S_GRAV + i] += s_sol[15 + i];
+            }
+            const double R2D = 180.0 / 3.14159265358979323846;
+            double rn = sqrt(s_sol[0] * s_sol[0] + s_sol[1] * s_sol[1] + s_sol[2] * s_sol[2]);
+            double tn = sqrt(s_sol[3] * s_sol[3] + s_sol[4] * s_sol[4] + s_sol[5] * s_sol[5]);
+            int converged = ((rn * R2D < 0.01) && (tn * 100 < 0.015)) ? 1 : 0;   // :209-212
+            int it = ctl->iter, rematch = ctl->rematch, nse = 0;
+            if (converged || ((rematch == 0) && (it == (S.max_iter - 2)))) { nse = 1; rematch++; }   // :217-222
+            int stop = (rematch >= 2 || (it == S.max_iter - 1)) ? 1 : 0;          // :224
+            int trip = ctl->trips;
+            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.force_search) ? 1 : 0;
+            ctl->searches += (ctl->search || S.force_search) ? 1 : 0;
+            ctl->trips = trip + 1;
+            ctl->rematch = rematch;
+            ctl->search = nse;
+            ctl->iter = it + 1;
+            ctl->converged = converged;
+            ctl->stopped = stop;
+            ctl->unit_counter = 0;
+            for (int i = 0; i < 18; ++i) ctl->dx_last[i] = s_sol[i];
+            s_flag[0] = stop;
+        }
+        __syncthreads();
+        if (tid < 36) S.x[tid] = s_x[tid];
+        if (s_flag[0]) {                                                     // state.cov = (I - G) * state.cov (:229)
+            for (int e = tid; e < 18 * 18; e += NT) {
+                int i = e / 18, j = e % 18;
+                double s = 0.0;
+                for (int a = 0; a < 6; ++a) s += s_G[i * 6 + a] * s_P[a * 18 + j];
+                S.P_out[e] = s_P[e] - s;
+            }
+        }
+    }
+}
+
+void launch_solve(const SolveParams& S, cudaStream_t stream) { k_solve<<<1, SOLVE_THREADS, 0, stream>>>(S); }
+
+// reset the control block at the start of an update
+__global__ void k_ctl_reset(Ctl* ctl, SearchStats* stats) {
+    if (threadIdx.x == 0) {
+        ctl->search = 1; ctl->stopped = 0; ctl->iter = -1; ctl->t = 0; ctl->rematch = 0; ctl->trips = 0;
+        ctl->searches = 0; ctl->converged = 0; ctl->n_eff = 0; ctl->nan_guard = 0; ctl->res_mean = 0.0;
+        ctl->unit_counter = 0;
+        for (int i = 0; i < MAX_TRIPS; ++i) ctl->trip_searched[i] = 0;
+        for (int i = 0; i < 23; ++i) ctl->dx_last[i] = 0.0;
+        if (stats) { stats->far_queries = 0; stats->candidates = 0; stats->sweeps = 0; }
+    }
+}
+void launch_ctl_reset(Ctl* ctl, SearchStats* stats, cudaStream_t stream) { k_ctl_reset<<<1, 32, 0, stream>>>(ctl, stats); }
+
+}  // namespace flivo

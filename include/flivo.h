@@ -1,0 +1,189 @@
+/*
+ * flivo.h — C ABI of libflivo_b200.so: the B200-native (sm_100a) LIO measurement-update hot path of
+ * FAST-LIVO and the GPU-resident map that replaces ikd-Tree underneath it.
+ *
+ * The reference has no FFI layer: the boundary is two C++ classes linked into one
+ * executable.  Every entry point below therefore cites the reference C++ member it stands in for
+ * (paths relative to the reference tree); the ROS-free drop-in classes KD_TREE / LaserMapping in
+ * fast-livo-noted_b200/host/ forward to these calls, and INTEGRATION.md shows the binding a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; caller owns every host buffer, the library owns device memory;
+ *   - every call returns an int status: 0 = FLIVO_OK, negative = error (flivo_last_error(ctx) has text);
+ *   - no exceptions cross the ABI; no CPU fallback exists: without a CUDA device every call that
+ *     needs one fails with FLIVO_E_CUDA;
+ *   - point inputs are strided float triples: stride_bytes = 12 for packed xyz, 16 for float4,
+ *     48 for the reference's pcl::PointXYZINormal AoS (include/ikd-Tree/ikd_Tree.h:21-22);
+ *   - one ctx = one device + one stream; calls on one ctx are not re-entrant, distinct ctxs are independent.
+ */
+#ifndef FLIVO_H_
+#define FLIVO_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLIVO_OK          0
+#define FLIVO_E_CUDA     -1   /* CUDA runtime / no device */
+#define FLIVO_E_ARG      -2   /* bad argument */
+#define FLIVO_E_CAPACITY -3   /* a device table could not grow */
+#define FLIVO_E_NCCL     -4   /* communicator setup / collective failed */
+#define FLIVO_E_STATE    -5   /* call order (e.g. update before scan upload / map build) */
+
+#define FLIVO_K           5   /* NUM_MATCH_POINTS, include/common_lib.h:37 */
+
+/* Jacobian/solve flavour.  V3 = src/origin_laserMapping.cpp:916-1048 + IKFoM
+ * esekf::update_iterated_dyn_share_modified (1x12 row, 23-DOF manifold state; what north_star names).
+ * V1 = the compiled LaserMapping::h_share_model / Run (src/laser_mapping.cpp:485-645,178-238;
+ * 1x6 row = columns [3:6|0:3] of the V3 row, 18-DOF StatesGroup). */
+#define FLIVO_MODE_V3     0
+#define FLIVO_MODE_V1     1
+
+typedef struct flivo_ctx flivo_ctx;
+
+/* Flat state, row-major rotations.  Superset of StatesGroup (include/common_lib.h:518-603) and
+ * state_ikfom (include/use-ikfom.hpp:12-21). 36 doubles. */
+typedef struct flivo_state {
+    double rot[9];   /* state.rot_end            / s.rot            */
+    double pos[3];   /* state.pos_end            / s.pos            */
+    double offR[9];  /* Lidar_rot_to_IMU         / s.offset_R_L_I   */
+    double offT[3];  /* Lidar_offset_to_IMU      / s.offset_T_L_I   */
+    double vel[3];
+    double bg[3];
+    double ba[3];
+    double grav[3];
+} flivo_state;
+
+typedef struct flivo_options {
+    float    downsample_size;   /* KD_TREE box_length / set_downsample_param (ikd_Tree.h:167,171); default 0.2 */
+    int32_t  cell_ratio;        /* search-grid cell edge = cell_ratio * downsample_size; 0 -> 2 */
+    uint64_t initial_points;    /* sizing hint for the device tables; 0 -> 1<<20 */
+    int32_t  sort_scan;         /* 1: process scan points in Morton order of their cells (results are
+                                   reported in the caller's order either way); 0: caller's order */
+    int32_t  reserved;
+} flivo_options;
+
+typedef struct flivo_cfg {
+    int32_t mode;               /* FLIVO_MODE_V3 / FLIVO_MODE_V1 */
+    int32_t max_iter;           /* NUM_MAX_ITERATIONS (src/laser_mapping.cpp:968); the loop runs i = -1 .. max_iter-1 */
+    double  laser_point_cov;    /* LASER_POINT_COV (src/laser_mapping.cpp:975), the R of esekfom.hpp:1619 */
+    double  limit[23];          /* V3 per-component convergence limit (epsi, src/origin_laserMapping.cpp:1231-1233) */
+    int32_t force_search;       /* 1: kNN on every trip (SURVEY §3.2 "worst case"); 0: reference re-match policy */
+    int32_t reserved;
+} flivo_cfg;
+
+typedef struct flivo_report {
+    int32_t trips;              /* h_share_model calls executed */
+    int32_t searches;           /* trips that ran the kNN */
+    int32_t n_eff;              /* effct_feat_num of the last trip (src/laser_mapping.cpp:548-559) */
+    int32_t converged;          /* V1 flg_EKF_converged / V3 t>0 at exit */
+    double  res_mean;           /* res_mean_last of the last trip (:561) */
+    double  dx_last[23];        /* last state increment (V1: first 18 entries, order rot,pos,vel,bg,ba,grav) */
+    float   gpu_ms;             /* device time of the whole loop (CUDA events on the ctx stream) */
+    int32_t kernel_launches;    /* kernels launched by this call */
+} flivo_report;
+
+/* ---- context ------------------------------------------------------------------------------- */
+/* KD_TREE::KD_TREE / InitializeKDTree (include/ikd-Tree/ikd_Tree.cpp:9-16,40-44) */
+int  flivo_ctx_create(int device, const flivo_options* opt, flivo_ctx** out);
+void flivo_ctx_destroy(flivo_ctx* ctx);           /* KD_TREE::~KD_TREE (:18-25) */
+const char* flivo_last_error(const flivo_ctx* ctx);
+const char* flivo_version(void);
+/* cudaStream_t of the ctx as an opaque pointer (for callers that time with their own CUDA events) */
+void* flivo_ctx_stream(flivo_ctx* ctx);
+int  flivo_sync(flivo_ctx* ctx);
+
+/* ---- map: ikd-Tree API surface (include/ikd-Tree/ikd_Tree.h:166-188) ------------------------- */
+/* KD_TREE::set_downsample_param (ikd_Tree.cpp:36-38). Rebuilds the voxel index when the map is non-empty. */
+int flivo_map_set_downsample(flivo_ctx* ctx, float downsample_size);
+/* KD_TREE::Build (ikd_Tree.cpp:337-348): replaces the map; no downsampling; ids = 0..n-1. */
+int flivo_map_build(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes);
+/* KD_TREE::Add_Points (ikd_Tree.cpp:382-457). Every offered point consumes one insertion id.
+ * *n_added = the reference's return value (tmp_counter). */
+int flivo_map_add_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes,
+                         int downsample_on, int32_t* n_added);
+/* KD_TREE::Delete_Point_Boxes (ikd_Tree.cpp:501-521, half-open boxes :648). boxes6 = nboxes x {min xyz, max xyz}. */
+int flivo_map_delete_boxes(flivo_ctx* ctx, const float* boxes6, size_t nboxes, int32_t* n_deleted);
+/* KD_TREE::Add_Point_Boxes (ikd_Tree.cpp:459-479): revives points removed by delete_boxes/delete_points
+ * that have not yet been handed out by flivo_map_acquire_removed. */
+int flivo_map_add_boxes(flivo_ctx* ctx, const float* boxes6, size_t nboxes, int32_t* n_revived);
+/* KD_TREE::Delete_Points (ikd_Tree.cpp:481-499; same_point EPSS 1e-6 :1287-1289). */
+int flivo_map_delete_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes, int32_t* n_deleted);
+/* KD_TREE::size / validnum (ikd_Tree.cpp:74-136): both report live points (the reference's size() also
+ * counts lazily deleted nodes that a rebuild has not purged yet — tree-state dependent). */
+int flivo_map_size(flivo_ctx* ctx, int64_t* n_live);
+/* KD_TREE::tree_range (ikd_Tree.cpp:94-118): out6 = {min xyz, max xyz} over live points (zeros if empty). */
+int flivo_map_range(flivo_ctx* ctx, float out6[6]);
+/* KD_TREE::flatten(Root_Node, Storage, NOT_RECORD) (ikd_Tree.cpp:1238-1263): live points as x,y,z and id.
+ * Call with cap = 0 to obtain *n only. Order is unspecified. */
+int flivo_map_flatten(flivo_ctx* ctx, float* out_xyz, int32_t* out_id, size_t cap, size_t* n);
+/* KD_TREE::acquire_removed_points (ikd_Tree.cpp:523-535): points removed by box/point deletes since the last call. */
+int flivo_map_acquire_removed(flivo_ctx* ctx, float* out_xyz, size_t cap, size_t* n);
+
+/* Batched KD_TREE::Nearest_Search (ikd_Tree.cpp:350-380; Search :843-986): exact k nearest live points
+ * with squared distance <= max_dist, ascending by (float32 squared distance, insertion id).
+ * k <= FLIVO_K.  Rows are padded with id -1 / +inf when fewer than k exist.  out_xyz/out_sqd/out_id may be NULL. */
+int flivo_knn(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t stride_bytes, int k, double max_dist,
+              float* out_xyz /* nq*k*3 */, float* out_sqd /* nq*k */, int32_t* out_id /* nq*k */,
+              int32_t* out_count /* nq */);
+
+/* ---- scan + measurement update ---------------------------------------------------------------- */
+/* feats_down_body (src/laser_mapping.cpp:129-130): lidar-frame scan; copied to the device. */
+int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes);
+/* Same, from a device pointer to n float4 (x,y,z,ignored) already resident in HBM (no copy through the host). */
+int flivo_scan_set_device(flivo_ctx* ctx, const void* dev_xyzw, size_t n);
+
+/* One LaserMapping::h_share_model call (src/laser_mapping.cpp:485-645 / src/origin_laserMapping.cpp:916-1048)
+ * at state `st`: world transform, kNN when do_search (else the cached Nearest_Points), esti_plane, gates,
+ * 1x12 rows, H^T H (12x12 row-major) and H^T z.  Optional outputs may be NULL:
+ *   selected n  : point_selected_surf after this call;  eff n : rows that entered H (:552)
+ *   nbr_id n*5  : neighbour ids (ascending distance; -1 padded); nbr_sqd n*5
+ *   plane n*4   : normvec (nx,ny,nz,pd2), zeros for unselected points;  world n*3 : feats_down_world */
+int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mode, int do_search,
+                        double HTH[144], double HTz[12], int32_t* n_eff, double* res_sum,
+                        uint8_t* selected, uint8_t* eff, int32_t* nbr_id, float* nbr_sqd,
+                        float* plane, float* world);
+/* V1 repack of the same sums: HPH 9x9 row-major, HPL 9 (src/laser_mapping.cpp:564-593). */
+int flivo_repack_v1(const double HTH[144], const double HTz[12], double laser_point_cov,
+                    double HPH[81], double HPL[9]);
+
+/* The whole iterated update on the device, no host round trip between trips:
+ * V3: esekf::update_iterated_dyn_share_modified (include/IKFoM_toolkit/esekfom/esekfom.hpp:1619-1928), P 23x23;
+ * V1: the loop in LaserMapping::Run (src/laser_mapping.cpp:165-242), P = state.cov 18x18.  Row-major, in/out. */
+int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* P, const flivo_cfg* cfg, flivo_report* rep);
+
+/* LaserMapping::map_incremental (src/laser_mapping.cpp:329-389, USE_ikdtree branch :384): world-transform the
+ * uploaded scan with `st` on the device and Add_Points(..., true) without a host round trip. */
+int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t* n_added);
+
+/* ---- multi-GPU (BASELINE configs 4-5; no counterpart in the reference) -------------------------- */
+/* Shard a mega-scan over ranks: every rank holds the full map and a slice of the scan; each trip the
+ * 92-double normal-equation block is combined across ranks in fixed rank order (bit-identical on every
+ * rank) before the replicated on-device solve.  unique_id: 128 bytes from flivo_comm_unique_id on rank 0. */
+int flivo_comm_unique_id(void* out128);
+int flivo_comm_init(flivo_ctx* ctx, const void* unique_id128, int rank, int nranks);
+int flivo_comm_destroy(flivo_ctx* ctx);
+
+/* ---- introspection used by bench.py ------------------------------------------------------------ */
+typedef struct flivo_stats {
+    int64_t map_live;           /* live points */
+    int64_t map_cells;          /* occupied search cells */
+    int64_t map_blocks;         /* occupied 4x4x4-cell blocks */
+    int64_t dir_capacity;       /* block-directory slots */
+    int64_t bucket_capacity;    /* point buckets allocated */
+    int64_t last_far_queries;   /* queries of the last search trip that left the 27-cell fast path */
+    int64_t last_candidates;    /* candidate points examined by the last search trip */
+    float   last_fused_ms[16];  /* per-trip device time of the fused kernel in the last flivo_iekf_update */
+    float   last_solve_ms[16];
+    int32_t last_trip_searched[16];
+} flivo_stats;
+int flivo_get_stats(flivo_ctx* ctx, flivo_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLIVO_H_ */
