@@ -1,0 +1,787 @@
+// api.cu — the C ABI of libflivo_b200.so (include/flivo.h): context, host<->device staging, launch sequences.
+//
+// The reference has no FFI layer; each entry point stands in for the C++ member cited beside its
+// declaration in include/flivo.h.  Everything here is plumbing: the arithmetic lives in map.cu (GPU map),
+// search.cuh + fused.cu (per-trip fused kernel) and solve.cu (on-device reduce + solve + policy).
+// There is no CPU fallback: without a CUDA device every call fails with FLIVO_E_CUDA.
+#include "../../include/flivo.h"
+#include "map.cuh"
+#include "solve.cuh"
+
+#include <cub/cub.cuh>
+#include <dlfcn.h>
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+
+using namespace flivo;
+
+// ---- NCCL through dlopen (no link-time dependency; the process may already carry torch's libnccl) -------
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId_t;
+struct NcclApi {
+    void* h = nullptr;
+    int (*GetUniqueId)(ncclUniqueId_t*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId_t, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool load(std::string& err) {
+        if (h) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) { h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+        if (!h) { err = std::string("dlopen libnccl failed: ") + dlerror(); return false; }
+        GetUniqueId = (decltype(GetUniqueId))dlsym(h, "ncclGetUniqueId");
+        CommInitRank = (decltype(CommInitRank))dlsym(h, "ncclCommInitRank");
+        CommDestroy = (decltype(CommDestroy))dlsym(h, "ncclCommDestroy");
+        AllGather = (decltype(AllGather))dlsym(h, "ncclAllGather");
+        GetErrorString = (decltype(GetErrorString))dlsym(h, "ncclGetErrorString");
+        if (!GetUniqueId || !CommInitRank || !CommDestroy || !AllGather) { err = "libnccl lacks a required symbol"; return false; }
+        return true;
+    }
+};
+static NcclApi g_nccl;
+constexpr int NCCL_DOUBLE = 8;  // ncclFloat64 (nccl.h ncclDataType_t)
+
+struct flivo_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    MapStore map;
+    std::string err;
+    flivo_options opt{};
+    int sm_count = 148;
+    // host staging (pinned)
+    float4* h_stage = nullptr;
+    size_t h_stage_n = 0;
+    double* h_small = nullptr;      // pinned: 36 state + 36 + 529 P + ... (2048 doubles)
+    Ctl* h_ctl = nullptr;           // pinned mirror
+    SearchStats* h_stats = nullptr; // pinned mirror
+    // generic device staging for map / knn inputs
+    float4* d_stage = nullptr;
+    size_t d_stage_n = 0;
+    // scan
+    size_t scan_n = 0, scan_cap = 0;
+    bool scan_external = false;
+    bool scan_sorted = false;
+    float4* d_body = nullptr;       // processing order: d_body_own or the caller's device pointer
+    float4* d_body_own = nullptr;
+    float4* d_body_in = nullptr;    // caller's order (only when sorted)
+    unsigned int* d_perm = nullptr; // processing index -> caller's index
+    unsigned long long *d_skey_a = nullptr, *d_skey_b = nullptr;
+    unsigned int* d_sidx_a = nullptr;
+    void* d_cub = nullptr;
+    size_t cub_bytes = 0;
+    float4* d_near = nullptr;
+    float2* d_near_meta = nullptr;
+    unsigned char *d_sel = nullptr, *d_eff = nullptr;
+    float4 *d_normvec = nullptr, *d_world = nullptr;
+    double *d_partials = nullptr, *d_gpartials = nullptr;
+    unsigned int* d_group_cnt = nullptr;
+    void* d_out = nullptr;          // un-permute scratch for optional outputs
+    size_t d_out_bytes = 0;
+    // loop state
+    Ctl* d_ctl = nullptr;
+    SearchStats* d_stats = nullptr;
+    double *d_x = nullptr, *d_xprop = nullptr, *d_Pprop = nullptr, *d_Pout = nullptr, *d_sum = nullptr, *d_rank_blocks = nullptr;
+    cudaEvent_t ev[2 * MAX_TRIPS + 2] = {};
+    flivo_stats stats{};
+    // multi-GPU
+    ncclComm_t comm = nullptr;
+    int rank = 0, nranks = 1;
+};
+
+#define CKC(call)                                                                        \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);               \
+            return FLIVO_E_CUDA;                                                         \
+        }                                                                                \
+    } while (0)
+#define NEED(cond, code, msg) do { if (!(cond)) { if (ctx) ctx->err = (msg); return (code); } } while (0)
+
+static int map_rc(flivo_ctx* ctx, int rc) {
+    if (rc == 0) return FLIVO_OK;
+    if (rc == -2) return FLIVO_E_ARG;
+    if (rc == -3) return FLIVO_E_CAPACITY;
+    return FLIVO_E_CUDA;
+}
+
+// strided host xyz -> pinned float4 -> device buffer (w = 0)
+static int stage_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes, float4* dst) {
+    if (n == 0) return FLIVO_OK;
+    if (n > ctx->h_stage_n) {
+        if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+        ctx->h_stage = nullptr; ctx->h_stage_n = 0;
+        size_t cap = std::max<size_t>(n + n / 4, 1u << 16);
+        CKC(cudaMallocHost(&ctx->h_stage, cap * sizeof(float4)));
+        ctx->h_stage_n = cap;
+    }
+    const char* src = reinterpret_cast<const char*>(xyz);
+    float4* h = ctx->h_stage;
+    if (stride_bytes == 16) {
+        memcpy(h, src, n * 16);
+    } else {
+        for (size_t i = 0; i < n; ++i) {
+            const float* p = reinterpret_cast<const float*>(src + i * stride_bytes);
+            h[i] = make_float4(p[0], p[1], p[2], 0.f);
+        }
+    }
+    CKC(cudaMemcpyAsync(dst, h, n * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    // the pinned buffer is reused by the next call
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+static int ensure_dstage(flivo_ctx* ctx, size_t n) {
+    if (n <= ctx->d_stage_n) return FLIVO_OK;
+    cudaFree(ctx->d_stage); ctx->d_stage = nullptr; ctx->d_stage_n = 0;
+    size_t cap = std::max<size_t>(n + n / 4, 1u << 16);
+    CKC(cudaMalloc(&ctx->d_stage, cap * sizeof(float4)));
+    ctx->d_stage_n = cap;
+    return FLIVO_OK;
+}
+static bool stride_ok(size_t s) { return s >= 12 && (s % 4) == 0; }
+
+// ---- small kernels of the plumbing layer ------------------------------------------------------------------
+__global__ void k_ctl_set(Ctl* ctl, int search) {
+    if (threadIdx.x == 0) { ctl->search = search; ctl->stopped = 0; ctl->unit_counter = 0; }
+}
+// Morton key of the scan point's cell in the lidar frame (a rigid transform preserves locality, so points
+// that are neighbours here query neighbouring map cells whatever the state is)
+__device__ __forceinline__ unsigned long long spread21(unsigned int v) {
+    unsigned long long x = v & 0x1FFFFF;
+    x = (x | x << 32) & 0x1F00000000FFFFull;
+    x = (x | x << 16) & 0x1F0000FF0000FFull;
+    x = (x | x << 8) & 0x100F00F00F00F00Full;
+    x = (x | x << 4) & 0x10C30C30C30C30C3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+__global__ void k_scan_keys(const float4* __restrict__ body, size_t n, float inv_edge, unsigned long long* keys, unsigned int* idx) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 p = body[i];
+    float fx = fminf(fmaxf(floorf(p.x * inv_edge), -1048575.f), 1048575.f);
+    float fy = fminf(fmaxf(floorf(p.y * inv_edge), -1048575.f), 1048575.f);
+    float fz = fminf(fmaxf(floorf(p.z * inv_edge), -1048575.f), 1048575.f);
+    unsigned int ux = (unsigned int)((int)fx + (1 << 20)), uy = (unsigned int)((int)fy + (1 << 20)), uz = (unsigned int)((int)fz + (1 << 20));
+    keys[i] = (spread21(ux) << 2) | (spread21(uy) << 1) | spread21(uz);
+    idx[i] = (unsigned int)i;
+}
+__global__ void k_gather4(const float4* __restrict__ in, const unsigned int* __restrict__ perm, size_t n, float4* __restrict__ out) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[perm[i]];
+}
+// out[perm[i]*elems + e] = in[i*elems + e]   (processing order -> caller's order); perm == nullptr: identity
+template <class T>
+__global__ void k_scatter(const T* __restrict__ in, const unsigned int* __restrict__ perm, size_t n, int elems, T* __restrict__ out) {
+    size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= n * (size_t)elems) return;
+    size_t i = t / elems;
+    int e = (int)(t % elems);
+    size_t o = perm ? perm[i] : i;
+    out[o * elems + e] = in[t];
+}
+// neighbour ids / squared distances from the cached Nearest_Points (x,y,z,id) and the query
+__global__ void k_near_unpack(const float4* __restrict__ near, const float4* __restrict__ world, const unsigned int* __restrict__ perm,
+                              size_t n, int* out_id, float* out_sqd) {
+    size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= n * 5) return;
+    size_t i = t / 5;
+    int r = (int)(t % 5);
+    float4 p = near[t];
+    int id = __float_as_int(p.w);
+    size_t o = perm ? perm[i] : i;
+    if (out_id) out_id[o * 5 + r] = id;
+    if (out_sqd) {
+        float4 q = world[i];
+        out_sqd[o * 5 + r] = id >= 0 ? sqdist3(q.x, q.y, q.z, p.x, p.y, p.z) : INFINITY;
+    }
+}
+static inline unsigned nblk(size_t n, int t) { return (unsigned)((n + t - 1) / t); }
+
+// ---- context ------------------------------------------------------------------------------------------------
+extern "C" const char* flivo_version(void) { return "flivo_b200 0.1 (sm_100a)"; }
+extern "C" const char* flivo_last_error(const flivo_ctx* ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
+extern "C" void* flivo_ctx_stream(flivo_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" int flivo_sync(flivo_ctx* ctx) {
+    NEED(ctx, FLIVO_E_ARG, "null ctx");
+    CKC(cudaSetDevice(ctx->device));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+
+static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
+    int ndev = 0;
+    CKC(cudaGetDeviceCount(&ndev));
+    NEED(ndev > 0 && device >= 0 && device < ndev, FLIVO_E_CUDA, "no such CUDA device (libflivo_b200 has no CPU fallback)");
+    ctx->device = device;
+    CKC(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CKC(cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    CKC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    flivo_options o{};
+    if (opt) o = *opt;
+    if (!(o.downsample_size > 0.f)) o.downsample_size = 0.2f;
+    if (o.cell_ratio == 0) o.cell_ratio = 2;
+    ctx->opt = o;
+    int rc = ctx->map.init(ctx->stream, o.downsample_size, o.cell_ratio, (size_t)o.initial_points, ctx->err);
+    if (rc) return map_rc(ctx, rc);
+    upload_term_table();
+    CKC(cudaGetLastError());
+    CKC(cudaMalloc(&ctx->d_ctl, sizeof(Ctl)));
+    CKC(cudaMalloc(&ctx->d_stats, sizeof(SearchStats)));
+    CKC(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
+    CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
+    CKC(cudaMalloc(&ctx->d_x, 36 * sizeof(double)));
+    CKC(cudaMalloc(&ctx->d_xprop, 36 * sizeof(double)));
+    CKC(cudaMalloc(&ctx->d_Pprop, 23 * 23 * sizeof(double)));
+    CKC(cudaMalloc(&ctx->d_Pout, 23 * 23 * sizeof(double)));
+    CKC(cudaMalloc(&ctx->d_sum, PSTRIDE * sizeof(double)));
+    CKC(cudaMemsetAsync(ctx->d_sum, 0, PSTRIDE * sizeof(double), ctx->stream));
+    CKC(cudaMallocHost(&ctx->h_small, 2048 * sizeof(double)));
+    CKC(cudaMallocHost(&ctx->h_ctl, sizeof(Ctl)));
+    CKC(cudaMallocHost(&ctx->h_stats, sizeof(SearchStats)));
+    for (auto& e : ctx->ev) CKC(cudaEventCreate(&e));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_ctx_create(int device, const flivo_options* opt, flivo_ctx** out) {
+    if (!out) return FLIVO_E_ARG;
+    *out = nullptr;
+    flivo_ctx* ctx = new (std::nothrow) flivo_ctx();
+    if (!ctx) return FLIVO_E_CAPACITY;
+    int rc = ctx_init(ctx, device, opt);
+    if (rc != FLIVO_OK) {
+        // keep the message reachable for the caller: a failed create returns no ctx, so print it
+        fprintf(stderr, "flivo_ctx_create: %s\n", ctx->err.c_str());
+        flivo_ctx_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return FLIVO_OK;
+}
+
+static void free_scan(flivo_ctx* ctx) {
+    cudaFree(ctx->d_body_own);
+    cudaFree(ctx->d_body_in); cudaFree(ctx->d_perm); cudaFree(ctx->d_skey_a); cudaFree(ctx->d_skey_b); cudaFree(ctx->d_sidx_a);
+    cudaFree(ctx->d_cub); cudaFree(ctx->d_near); cudaFree(ctx->d_near_meta); cudaFree(ctx->d_sel); cudaFree(ctx->d_eff);
+    cudaFree(ctx->d_normvec); cudaFree(ctx->d_world); cudaFree(ctx->d_partials); cudaFree(ctx->d_gpartials); cudaFree(ctx->d_group_cnt);
+    ctx->d_body = ctx->d_body_own = ctx->d_body_in = nullptr; ctx->d_perm = nullptr; ctx->d_skey_a = ctx->d_skey_b = nullptr; ctx->d_sidx_a = nullptr;
+    ctx->d_cub = nullptr; ctx->d_near = nullptr; ctx->d_near_meta = nullptr; ctx->d_sel = ctx->d_eff = nullptr;
+    ctx->d_normvec = ctx->d_world = nullptr; ctx->d_partials = ctx->d_gpartials = nullptr; ctx->d_group_cnt = nullptr;
+    ctx->scan_cap = 0; ctx->scan_n = 0; ctx->cub_bytes = 0;
+}
+
+extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
+    ctx->map.release();
+    free_scan(ctx);
+    cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_ctl); cudaFree(ctx->d_stats); cudaFree(ctx->d_x); cudaFree(ctx->d_xprop);
+    cudaFree(ctx->d_Pprop); cudaFree(ctx->d_Pout); cudaFree(ctx->d_sum); cudaFree(ctx->d_rank_blocks);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
+    if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
+    for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+// ---- map: ikd-Tree API surface ------------------------------------------------------------------------------
+#define ENTER()                                                      \
+    NEED(ctx, FLIVO_E_ARG, "null ctx");                              \
+    CKC(cudaSetDevice(ctx->device));                                 \
+    ctx->err.clear()
+
+extern "C" int flivo_map_set_downsample(flivo_ctx* ctx, float downsample_size) {
+    ENTER();
+    return map_rc(ctx, ctx->map.set_downsample(downsample_size, ctx->err));
+}
+
+extern "C" int flivo_map_build(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes) {
+    ENTER();
+    NEED(n == 0 || (xyz && stride_ok(stride_bytes)), FLIVO_E_ARG, "bad xyz / stride");
+    NEED(n < 0x7FFFFFF0ull, FLIVO_E_ARG, "too many points");
+    int rc = ensure_dstage(ctx, n);
+    if (rc) return rc;
+    if ((rc = stage_points(ctx, xyz, n, stride_bytes, ctx->d_stage))) return rc;
+    return map_rc(ctx, ctx->map.build(ctx->d_stage, n, ctx->err));
+}
+
+extern "C" int flivo_map_add_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes, int downsample_on, int32_t* n_added) {
+    ENTER();
+    if (n_added) *n_added = 0;
+    NEED(n == 0 || (xyz && stride_ok(stride_bytes)), FLIVO_E_ARG, "bad xyz / stride");
+    int rc = ensure_dstage(ctx, n);
+    if (rc) return rc;
+    if ((rc = stage_points(ctx, xyz, n, stride_bytes, ctx->d_stage))) return rc;
+    int added = 0;
+    rc = ctx->map.add_points(ctx->d_stage, n, downsample_on != 0, &added, ctx->err);
+    if (n_added) *n_added = added;
+    return map_rc(ctx, rc);
+}
+
+extern "C" int flivo_map_delete_boxes(flivo_ctx* ctx, const float* boxes6, size_t nboxes, int32_t* n_deleted) {
+    ENTER();
+    if (n_deleted) *n_deleted = 0;
+    NEED(nboxes == 0 || boxes6, FLIVO_E_ARG, "null boxes");
+    int del = 0;
+    int rc = ctx->map.delete_boxes(boxes6, nboxes, &del, ctx->err);
+    if (n_deleted) *n_deleted = del;
+    return map_rc(ctx, rc);
+}
+
+extern "C" int flivo_map_add_boxes(flivo_ctx* ctx, const float* boxes6, size_t nboxes, int32_t* n_revived) {
+    ENTER();
+    if (n_revived) *n_revived = 0;
+    NEED(nboxes == 0 || boxes6, FLIVO_E_ARG, "null boxes");
+    int rev = 0;
+    int rc = ctx->map.add_boxes(boxes6, nboxes, &rev, ctx->err);
+    if (n_revived) *n_revived = rev;
+    return map_rc(ctx, rc);
+}
+
+extern "C" int flivo_map_delete_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes, int32_t* n_deleted) {
+    ENTER();
+    if (n_deleted) *n_deleted = 0;
+    NEED(n == 0 || (xyz && stride_ok(stride_bytes)), FLIVO_E_ARG, "bad xyz / stride");
+    int rc = ensure_dstage(ctx, n);
+    if (rc) return rc;
+    if ((rc = stage_points(ctx, xyz, n, stride_bytes, ctx->d_stage))) return rc;
+    int del = 0;
+    rc = ctx->map.delete_points(ctx->d_stage, n, &del, ctx->err);
+    if (n_deleted) *n_deleted = del;
+    return map_rc(ctx, rc);
+}
+
+extern "C" int flivo_map_size(flivo_ctx* ctx, int64_t* n_live) {
+    ENTER();
+    NEED(n_live, FLIVO_E_ARG, "null out");
+    int rc = ctx->map.refresh_counters(ctx->err);
+    *n_live = ctx->map.live();
+    return map_rc(ctx, rc);
+}
+
+extern "C" int flivo_map_range(flivo_ctx* ctx, float out6[6]) {
+    ENTER();
+    NEED(out6, FLIVO_E_ARG, "null out");
+    return map_rc(ctx, ctx->map.range(out6, ctx->err));
+}
+
+extern "C" int flivo_map_flatten(flivo_ctx* ctx, float* out_xyz, int32_t* out_id, size_t cap, size_t* n) {
+    ENTER();
+    return map_rc(ctx, ctx->map.flatten(out_xyz, out_id, cap, n, ctx->err));
+}
+
+extern "C" int flivo_map_acquire_removed(flivo_ctx* ctx, float* out_xyz, size_t cap, size_t* n) {
+    ENTER();
+    return map_rc(ctx, ctx->map.acquire_removed(out_xyz, cap, n, ctx->err));
+}
+
+// largest float <= max_dist as bits (the reference compares the float distance against a double bound)
+static bool bound_bits(double max_dist, uint32_t* bits) {
+    if (!(max_dist >= 0.0)) return false;  // negative or NaN: nothing can match
+    float f = (float)max_dist;
+    if ((double)f > max_dist) f = nextafterf(f, -INFINITY);
+    memcpy(bits, &f, 4);
+    return true;
+}
+
+static int fetch_stats(flivo_ctx* ctx) {
+    CKC(cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(SearchStats), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    ctx->stats.last_far_queries = (int64_t)ctx->h_stats->far_queries;
+    ctx->stats.last_candidates = (int64_t)ctx->h_stats->candidates;
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_knn(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t stride_bytes, int k, double max_dist,
+                         float* out_xyz, float* out_sqd, int32_t* out_id, int32_t* out_count) {
+    ENTER();
+    NEED(k >= 1 && k <= FLIVO_K, FLIVO_E_ARG, "k must be in 1..5");
+    NEED(nq == 0 || (q_xyz && stride_ok(stride_bytes)), FLIVO_E_ARG, "bad queries / stride");
+    NEED(nq < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "too many queries");
+    if (nq == 0) return FLIVO_OK;
+    uint32_t bits = 0;
+    if (!bound_bits(max_dist, &bits)) {
+        for (size_t i = 0; i < nq * (size_t)k; ++i) {
+            if (out_id) out_id[i] = -1;
+            if (out_sqd) out_sqd[i] = INFINITY;
+            if (out_xyz) out_xyz[3 * i] = out_xyz[3 * i + 1] = out_xyz[3 * i + 2] = 0.f;
+        }
+        if (out_count) memset(out_count, 0, nq * sizeof(int32_t));
+        return FLIVO_OK;
+    }
+    int rc = ensure_dstage(ctx, nq);
+    if (rc) return rc;
+    if ((rc = stage_points(ctx, q_xyz, nq, stride_bytes, ctx->d_stage))) return rc;
+    size_t per = (size_t)k * (3 + 1 + 1) * 4 + 4;
+    size_t bytes = nq * per + 1024;
+    if (bytes > ctx->d_out_bytes) {
+        cudaFree(ctx->d_out); ctx->d_out = nullptr; ctx->d_out_bytes = 0;
+        CKC(cudaMalloc(&ctx->d_out, bytes + bytes / 4));
+        ctx->d_out_bytes = bytes + bytes / 4;
+    }
+    float* d_xyz = (float*)ctx->d_out;
+    float* d_sqd = d_xyz + nq * k * 3;
+    int* d_id = (int*)(d_sqd + nq * k);
+    int* d_cnt = d_id + nq * k;
+    CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
+    int grid = (int)std::min<size_t>((nq + 3) / 4, (size_t)ctx->sm_count * 16);
+    launch_knn(ctx->map.view(), ctx->d_stage, (int)nq, k, bits, d_xyz, d_sqd, d_id, d_cnt, ctx->d_stats, grid, ctx->stream);
+    CKC(cudaGetLastError());
+    if (out_xyz) CKC(cudaMemcpyAsync(out_xyz, d_xyz, nq * k * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_sqd) CKC(cudaMemcpyAsync(out_sqd, d_sqd, nq * k * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_id) CKC(cudaMemcpyAsync(out_id, d_id, nq * k * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_count) CKC(cudaMemcpyAsync(out_count, d_cnt, nq * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    return fetch_stats(ctx);
+}
+
+// ---- scan ---------------------------------------------------------------------------------------------------
+static int ensure_scan(flivo_ctx* ctx, size_t n) {
+    if (n > ctx->scan_cap) {
+        free_scan(ctx);
+        size_t cap = std::max<size_t>(n + n / 8, 1u << 15);
+        size_t units = (cap + UNIT_POINTS - 1) / UNIT_POINTS, groups = (units + GROUP_UNITS - 1) / GROUP_UNITS;
+        CKC(cudaMalloc(&ctx->d_body_in, cap * sizeof(float4)));
+        CKC(cudaMalloc(&ctx->d_body_own, cap * sizeof(float4)));
+        CKC(cudaMalloc(&ctx->d_perm, cap * sizeof(unsigned int)));
+        CKC(cudaMalloc(&ctx->d_skey_a, cap * sizeof(unsigned long long)));
+        CKC(cudaMalloc(&ctx->d_skey_b, cap * sizeof(unsigned long long)));
+        CKC(cudaMalloc(&ctx->d_sidx_a, cap * sizeof(unsigned int)));
+        size_t b = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, b, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)cap, 0, 63, ctx->stream);
+        ctx->cub_bytes = b + 256;
+        CKC(cudaMalloc(&ctx->d_cub, ctx->cub_bytes));
+        CKC(cudaMalloc(&ctx->d_near, cap * 5 * sizeof(float4)));
+        CKC(cudaMalloc(&ctx->d_near_meta, cap * sizeof(float2)));
+        CKC(cudaMalloc(&ctx->d_sel, cap));
+        CKC(cudaMalloc(&ctx->d_eff, cap));
+        CKC(cudaMalloc(&ctx->d_normvec, cap * sizeof(float4)));
+        CKC(cudaMalloc(&ctx->d_world, cap * sizeof(float4)));
+        CKC(cudaMalloc(&ctx->d_partials, units * PSTRIDE * sizeof(double)));
+        CKC(cudaMalloc(&ctx->d_gpartials, groups * PSTRIDE * sizeof(double)));
+        CKC(cudaMalloc(&ctx->d_group_cnt, groups * sizeof(unsigned int)));
+        CKC(cudaMemsetAsync(ctx->d_group_cnt, 0, groups * sizeof(unsigned int), ctx->stream));
+        ctx->scan_cap = cap;
+    }
+    return FLIVO_OK;
+}
+
+// after the caller-order scan is in `src` (device): optionally Morton-sort it into d_body
+static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool external) {
+    const bool sort = ctx->opt.sort_scan != 0;
+    if (sort) {
+        ctx->d_body = ctx->d_body_own;
+        float inv_edge = 1.0f / ctx->map.view().cell_edge;
+        k_scan_keys<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, n, inv_edge, ctx->d_skey_a, ctx->d_sidx_a);
+        size_t tmp = ctx->cub_bytes;
+        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, 0, 63, ctx->stream));
+        k_gather4<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, ctx->d_perm, n, ctx->d_body);
+        CKC(cudaGetLastError());
+    }
+    ctx->scan_external = external;
+    ctx->scan_sorted = sort;
+    ctx->scan_n = n;
+    // point_selected_surf starts true (V3 global array semantics are re-established by the first search trip)
+    CKC(cudaMemsetAsync(ctx->d_sel, 1, n, ctx->stream));
+    CKC(cudaMemsetAsync(ctx->d_eff, 0, n, ctx->stream));
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes) {
+    ENTER();
+    NEED(n > 0 && body_xyz && stride_ok(stride_bytes), FLIVO_E_ARG, "bad scan / stride");
+    NEED(n < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "scan too large");
+    const bool sort = ctx->opt.sort_scan != 0;
+    int rc = ensure_scan(ctx, n);
+    if (rc) return rc;
+    float4* dst = sort ? ctx->d_body_in : ctx->d_body_own;
+    ctx->d_body = ctx->d_body_own;
+    if ((rc = stage_points(ctx, body_xyz, n, stride_bytes, dst))) return rc;
+    return finish_scan(ctx, dst, n, false);
+}
+
+extern "C" int flivo_scan_set_device(flivo_ctx* ctx, const void* dev_xyzw, size_t n) {
+    ENTER();
+    NEED(n > 0 && dev_xyzw, FLIVO_E_ARG, "bad scan");
+    NEED(n < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "scan too large");
+    const bool sort = ctx->opt.sort_scan != 0;
+    int rc = ensure_scan(ctx, n);
+    if (rc) return rc;
+    if (!sort) ctx->d_body = (float4*)dev_xyzw;
+    return finish_scan(ctx, (const float4*)dev_xyzw, n, true);
+}
+
+static FusedParams make_fused(flivo_ctx* ctx, int mode, int force_search, uint32_t max_sq_bits) {
+    FusedParams P{};
+    P.map = ctx->map.view();
+    P.body = ctx->d_body;
+    P.n = (int)ctx->scan_n;
+    P.state = ctx->d_x;
+    P.near = ctx->d_near; P.near_meta = ctx->d_near_meta; P.sel = ctx->d_sel; P.eff = ctx->d_eff;
+    P.normvec = ctx->d_normvec; P.world = ctx->d_world;
+    P.partials = ctx->d_partials; P.gpartials = ctx->d_gpartials; P.group_cnt = ctx->d_group_cnt;
+    P.ctl = ctx->d_ctl; P.stats = ctx->d_stats;
+    P.mode = mode; P.force_search = force_search; P.max_sq_bits = max_sq_bits;
+    P.units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
+    P.groups = (P.units + GROUP_UNITS - 1) / GROUP_UNITS;
+    return P;
+}
+static int fused_grid(flivo_ctx* ctx, int units) { return std::max(1, std::min(units, ctx->sm_count * 8)); }
+// the fused path searches with the reference's own far-neighbour gate (pointSearchSqDis[4] > 5, src/laser_mapping.cpp:518)
+// as the distance bound: a point whose 5th neighbour lies beyond it is masked either way
+static uint32_t gate_bits() { float f = 5.0f; uint32_t b; memcpy(&b, &f, 4); return b; }
+
+// copy a per-point device array to the host in the caller's order
+template <class T>
+static int fetch_rows(flivo_ctx* ctx, const T* d_src, int elems, T* h_dst) {
+    size_t n = ctx->scan_n, bytes = n * elems * sizeof(T);
+    const T* src = d_src;
+    if (ctx->scan_sorted) {
+        if (bytes > ctx->d_out_bytes) {
+            cudaFree(ctx->d_out); ctx->d_out = nullptr; ctx->d_out_bytes = 0;
+            CKC(cudaMalloc(&ctx->d_out, bytes + bytes / 4));
+            ctx->d_out_bytes = bytes + bytes / 4;
+        }
+        k_scatter<T><<<nblk(n * elems, 256), 256, 0, ctx->stream>>>(d_src, ctx->d_perm, n, elems, (T*)ctx->d_out);
+        CKC(cudaGetLastError());
+        src = (const T*)ctx->d_out;
+    }
+    CKC(cudaMemcpyAsync(h_dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+
+// ---- measurement update -----------------------------------------------------------------------------------------
+static void expand_sum(const double* sum, double* HTH, double* HTz) {
+    int t = 0;
+    for (int i = 0; i < 12; ++i)
+        for (int j = i; j < 12; ++j) { HTH[i * 12 + j] = sum[t]; HTH[j * 12 + i] = sum[t]; ++t; }
+    for (int i = 0; i < 12; ++i) HTz[i] = sum[78 + i];
+}
+
+extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mode, int do_search,
+                                   double HTH[144], double HTz[12], int32_t* n_eff, double* res_sum,
+                                   uint8_t* selected, uint8_t* eff, int32_t* nbr_id, float* nbr_sqd,
+                                   float* plane, float* world) {
+    ENTER();
+    NEED(st && HTH && HTz, FLIVO_E_ARG, "null state / outputs");
+    NEED(mode == FLIVO_MODE_V3 || mode == FLIVO_MODE_V1, FLIVO_E_ARG, "bad mode");
+    NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
+    memcpy(ctx->h_small, st, sizeof(flivo_state));
+    CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_small, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
+    k_ctl_set<<<1, 32, 0, ctx->stream>>>(ctx->d_ctl, do_search ? 1 : 0);
+    if (do_search) CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
+    FusedParams P = make_fused(ctx, mode, 0, gate_bits());
+    launch_fused(P, fused_grid(ctx, P.units), ctx->stream);
+    SolveParams S{};
+    S.gpartials = ctx->d_gpartials; S.groups = P.groups; S.phase = SOLVE_PHASE_REDUCE_ONLY; S.mode = mode;
+    S.sum_out = ctx->d_sum; S.ctl = ctx->d_ctl; S.nranks = 1;
+    launch_solve(S, ctx->stream);
+    CKC(cudaGetLastError());
+    double* hs = ctx->h_small + 64;
+    CKC(cudaMemcpyAsync(hs, ctx->d_sum, NTERMS * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    expand_sum(hs, HTH, HTz);
+    if (res_sum) *res_sum = hs[90];
+    if (n_eff) *n_eff = (int32_t)hs[91];
+    int rc;
+    if (selected && (rc = fetch_rows<unsigned char>(ctx, ctx->d_sel, 1, selected))) return rc;
+    if (eff && (rc = fetch_rows<unsigned char>(ctx, ctx->d_eff, 1, eff))) return rc;
+    if (plane && (rc = fetch_rows<float>(ctx, (const float*)ctx->d_normvec, 4, plane))) return rc;
+    if (world) {
+        std::vector<float> tmp(ctx->scan_n * 4);
+        if ((rc = fetch_rows<float>(ctx, (const float*)ctx->d_world, 4, tmp.data()))) return rc;
+        for (size_t i = 0; i < ctx->scan_n; ++i) { world[3 * i] = tmp[4 * i]; world[3 * i + 1] = tmp[4 * i + 1]; world[3 * i + 2] = tmp[4 * i + 2]; }
+    }
+    if (nbr_id || nbr_sqd) {
+        size_t n = ctx->scan_n, bytes = n * 5 * 8;
+        if (bytes > ctx->d_out_bytes) {
+            cudaFree(ctx->d_out); ctx->d_out = nullptr; ctx->d_out_bytes = 0;
+            CKC(cudaMalloc(&ctx->d_out, bytes + bytes / 4));
+            ctx->d_out_bytes = bytes + bytes / 4;
+        }
+        int* d_id = (int*)ctx->d_out;
+        float* d_sq = (float*)(d_id + n * 5);
+        k_near_unpack<<<nblk(n * 5, 256), 256, 0, ctx->stream>>>(ctx->d_near, ctx->d_world, ctx->scan_sorted ? ctx->d_perm : nullptr, n, d_id, d_sq);
+        CKC(cudaGetLastError());
+        if (nbr_id) CKC(cudaMemcpyAsync(nbr_id, d_id, n * 5 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        if (nbr_sqd) CKC(cudaMemcpyAsync(nbr_sqd, d_sq, n * 5 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        CKC(cudaStreamSynchronize(ctx->stream));
+    }
+    if (do_search) return fetch_stats(ctx);
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_repack_v1(const double HTH[144], const double HTz[12], double laser_point_cov, double HPH[81], double HPL[9]) {
+    if (!HTH || !HTz || !HPH || !HPL || !(laser_point_cov > 0.0)) return FLIVO_E_ARG;
+    // Hsub = [A | n] = V3 columns [3:6 | 0:3]; HPH.block<6,6> += Hsub^T (1/R) Hsub (src/laser_mapping.cpp:584-592)
+    static const int map6[6] = {3, 4, 5, 0, 1, 2};
+    const double w = 1.0 / laser_point_cov;
+    for (int i = 0; i < 81; ++i) HPH[i] = 0.0;
+    for (int i = 0; i < 9; ++i) HPL[i] = 0.0;
+    for (int a = 0; a < 6; ++a) {
+        for (int b = 0; b < 6; ++b) HPH[a * 9 + b] = HTH[map6[a] * 12 + map6[b]] * w;
+        HPL[a] = HTz[map6[a]] * w;
+    }
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm, const flivo_cfg* cfg, flivo_report* rep) {
+    ENTER();
+    NEED(inout && Pm && cfg, FLIVO_E_ARG, "null state / P / cfg");
+    NEED(cfg->mode == FLIVO_MODE_V3 || cfg->mode == FLIVO_MODE_V1, FLIVO_E_ARG, "bad mode");
+    NEED(cfg->max_iter >= 1 && cfg->max_iter + 1 <= MAX_TRIPS, FLIVO_E_ARG, "max_iter must be in 1..15");
+    NEED(cfg->laser_point_cov > 0.0, FLIVO_E_ARG, "laser_point_cov must be > 0");
+    NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
+    const int np = cfg->mode == FLIVO_MODE_V1 ? 18 : 23;
+    const int trips = cfg->max_iter + 1;  // loop index -1 .. max_iter-1
+    cudaStream_t s = ctx->stream;
+    double* h = ctx->h_small;
+    memcpy(h, inout, sizeof(flivo_state));
+    memcpy(h + 36, Pm, sizeof(double) * np * np);
+    CKC(cudaEventRecord(ctx->ev[0], s));
+    CKC(cudaMemcpyAsync(ctx->d_x, h, sizeof(flivo_state), cudaMemcpyHostToDevice, s));
+    CKC(cudaMemcpyAsync(ctx->d_xprop, ctx->d_x, sizeof(flivo_state), cudaMemcpyDeviceToDevice, s));
+    CKC(cudaMemcpyAsync(ctx->d_Pprop, h + 36, sizeof(double) * np * np, cudaMemcpyHostToDevice, s));
+    CKC(cudaMemcpyAsync(ctx->d_Pout, ctx->d_Pprop, sizeof(double) * np * np, cudaMemcpyDeviceToDevice, s));
+    launch_ctl_reset(ctx->d_ctl, ctx->d_stats, s);
+    FusedParams P = make_fused(ctx, cfg->mode, cfg->force_search, gate_bits());
+    SolveParams S{};
+    S.gpartials = ctx->d_gpartials; S.groups = P.groups; S.mode = cfg->mode; S.max_iter = cfg->max_iter;
+    S.force_search = cfg->force_search; S.nranks = ctx->nranks; S.R = cfg->laser_point_cov;
+    for (int i = 0; i < 23; ++i) S.limit[i] = cfg->limit[i];
+    S.x = ctx->d_x; S.x_prop = ctx->d_xprop; S.P_prop = ctx->d_Pprop; S.P_out = ctx->d_Pout;
+    S.sum_out = ctx->d_sum; S.rank_blocks = ctx->d_rank_blocks; S.ctl = ctx->d_ctl;
+    const int grid = fused_grid(ctx, P.units);
+    int launches = 1;
+    for (int t = 0; t < trips; ++t) {
+        CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
+        launch_fused(P, grid, s);
+        CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
+        if (ctx->comm) {
+            S.phase = SOLVE_PHASE_REDUCE_ONLY;
+            launch_solve(S, s);
+            int nrc = g_nccl.AllGather(ctx->d_sum, ctx->d_rank_blocks, PSTRIDE, NCCL_DOUBLE, ctx->comm, s);
+            if (nrc != 0) { ctx->err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "error"); return FLIVO_E_NCCL; }
+            S.phase = SOLVE_PHASE_FROM_RANKS;
+            launch_solve(S, s);
+            launches += 3;
+        } else {
+            S.phase = SOLVE_PHASE_FULL;
+            launch_solve(S, s);
+            launches += 2;
+        }
+    }
+    CKC(cudaGetLastError());
+    CKC(cudaEventRecord(ctx->ev[1 + 2 * trips], s));
+    CKC(cudaMemcpyAsync(h, ctx->d_x, sizeof(flivo_state), cudaMemcpyDeviceToHost, s));
+    CKC(cudaMemcpyAsync(h + 36, ctx->d_Pout, sizeof(double) * np * np, cudaMemcpyDeviceToHost, s));
+    CKC(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
+    CKC(cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(SearchStats), cudaMemcpyDeviceToHost, s));
+    CKC(cudaStreamSynchronize(s));
+    memcpy(inout, h, sizeof(flivo_state));
+    memcpy(Pm, h + 36, sizeof(double) * np * np);
+    const Ctl& c = *ctx->h_ctl;
+    ctx->stats.last_far_queries = (int64_t)ctx->h_stats->far_queries;
+    ctx->stats.last_candidates = (int64_t)ctx->h_stats->candidates;
+    for (int t = 0; t < 16; ++t) { ctx->stats.last_fused_ms[t] = 0.f; ctx->stats.last_solve_ms[t] = 0.f; ctx->stats.last_trip_searched[t] = 0; }
+    for (int t = 0; t < trips && t < 16; ++t) {
+        cudaEventElapsedTime(&ctx->stats.last_fused_ms[t], ctx->ev[1 + 2 * t], ctx->ev[2 + 2 * t]);
+        cudaEventElapsedTime(&ctx->stats.last_solve_ms[t], ctx->ev[2 + 2 * t], ctx->ev[3 + 2 * t]);
+        ctx->stats.last_trip_searched[t] = t < c.trips ? c.trip_searched[t] : 0;
+    }
+    if (rep) {
+        memset(rep, 0, sizeof(*rep));
+        rep->trips = c.trips; rep->searches = c.searches; rep->n_eff = c.n_eff; rep->converged = c.converged;
+        rep->res_mean = c.res_mean;
+        for (int i = 0; i < 23; ++i) rep->dx_last[i] = c.dx_last[i];
+        cudaEventElapsedTime(&rep->gpu_ms, ctx->ev[0], ctx->ev[1 + 2 * trips]);
+        rep->kernel_launches = launches;
+    }
+    if (c.nan_guard) { ctx->err = "non-finite normal equations: update skipped"; return FLIVO_E_STATE; }
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t* n_added) {
+    ENTER();
+    if (n_added) *n_added = 0;
+    NEED(st, FLIVO_E_ARG, "null state");
+    NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
+    memcpy(ctx->h_small, st, sizeof(flivo_state));
+    CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_small, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
+    // Add_Points is order dependent only through ties; keep the caller's order (batch index = insertion id order)
+    const float4* src = ctx->scan_sorted ? ctx->d_body_in : ctx->d_body;
+    if (ctx->scan_sorted && ctx->scan_external) {
+        // the caller-order copy was never made for an external sorted scan: un-permute d_body into d_body_in
+        k_scatter<float4><<<nblk(ctx->scan_n, 256), 256, 0, ctx->stream>>>(ctx->d_body, ctx->d_perm, ctx->scan_n, 1, ctx->d_body_in);
+    }
+    launch_transform(src, (int)ctx->scan_n, ctx->d_x, ctx->d_world, ctx->stream);
+    CKC(cudaGetLastError());
+    int added = 0;
+    int rc = ctx->map.add_points(ctx->d_world, ctx->scan_n, true, &added, ctx->err);
+    if (n_added) *n_added = added;
+    return map_rc(ctx, rc);
+}
+
+// ---- multi-GPU ----------------------------------------------------------------------------------------------
+extern "C" int flivo_comm_unique_id(void* out128) {
+    if (!out128) return FLIVO_E_ARG;
+    std::string err;
+    if (!g_nccl.load(err)) { fprintf(stderr, "flivo_comm_unique_id: %s\n", err.c_str()); return FLIVO_E_NCCL; }
+    ncclUniqueId_t id;
+    if (g_nccl.GetUniqueId(&id) != 0) return FLIVO_E_NCCL;
+    memcpy(out128, &id, 128);
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_comm_init(flivo_ctx* ctx, const void* unique_id128, int rank, int nranks) {
+    ENTER();
+    NEED(unique_id128 && nranks >= 1 && rank >= 0 && rank < nranks, FLIVO_E_ARG, "bad rank / nranks / id");
+    NEED(!ctx->comm, FLIVO_E_STATE, "communicator already attached");
+    if (!g_nccl.load(ctx->err)) return FLIVO_E_NCCL;
+    ncclUniqueId_t id;
+    memcpy(&id, unique_id128, 128);
+    int rc = g_nccl.CommInitRank(&ctx->comm, nranks, id, rank);
+    if (rc != 0) { ctx->comm = nullptr; ctx->err = std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"); return FLIVO_E_NCCL; }
+    ctx->rank = rank; ctx->nranks = nranks;
+    cudaFree(ctx->d_rank_blocks); ctx->d_rank_blocks = nullptr;
+    CKC(cudaMalloc(&ctx->d_rank_blocks, (size_t)nranks * PSTRIDE * sizeof(double)));
+    CKC(cudaMemsetAsync(ctx->d_rank_blocks, 0, (size_t)nranks * PSTRIDE * sizeof(double), ctx->stream));
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_comm_destroy(flivo_ctx* ctx) {
+    ENTER();
+    if (ctx->comm) {
+        CKC(cudaStreamSynchronize(ctx->stream));
+        g_nccl.CommDestroy(ctx->comm);
+        ctx->comm = nullptr;
+    }
+    ctx->rank = 0; ctx->nranks = 1;
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_get_stats(flivo_ctx* ctx, flivo_stats* out) {
+    ENTER();
+    NEED(out, FLIVO_E_ARG, "null out");
+    int rc = ctx->map.refresh_counters(ctx->err);
+    const MapCounters& c = ctx->map.counters();
+    ctx->stats.map_live = (int64_t)c.live;
+    ctx->stats.map_cells = c.cells_used;
+    ctx->stats.map_blocks = c.blocks_used;
+    ctx->stats.dir_capacity = (int64_t)ctx->map.dir_cap();
+    ctx->stats.bucket_capacity = (int64_t)ctx->map.bucket_cap();
+    *out = ctx->stats;
+    return map_rc(ctx, rc);
+}

@@ -60,6 +60,14 @@ struct MapCounters {
 
 struct int3s { int x, y, z; };
 
+// counters of the kNN kernels (search.cuh)
+struct SearchStats {
+    unsigned long long far_queries;   // queries that left the 27-cell fast path
+    unsigned long long candidates;    // candidate points examined
+    unsigned long long sweeps;        // queries that needed the directory sweep
+};
+
+
 // ---- strict float helpers (explicit rounding; immune to contraction even without -fmad=false) -----
 __device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }

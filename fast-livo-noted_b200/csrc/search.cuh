@@ -82,12 +82,6 @@ struct WarpSelect {
     static constexpr int FLIVO_K_ = 5;
 };
 
-struct SearchStats {
-    unsigned long long far_queries;   // queries that left the 27-cell fast path
-    unsigned long long candidates;    // candidate points examined
-    unsigned long long sweeps;        // queries that needed the directory sweep
-};
-
 // squared covered radius (float, conservative) of a cell block reaching n cells beyond the query's cell
 __device__ __forceinline__ float covered_sq(float cell_edge, float n_cells, float qabs) {
     double r = (double)n_cells * (double)cell_edge * (1.0 - 1e-6) - ((double)qabs + (double)n_cells * (double)cell_edge) * 4.8e-7;

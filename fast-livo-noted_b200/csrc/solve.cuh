@@ -1,0 +1,40 @@
+// solve.cuh — parameters of the single-CTA reduce + solve kernel (solve.cu) and host launchers of all kernels.
+#pragma once
+#include "fused.cuh"
+
+namespace flivo {
+
+enum {
+    SOLVE_PHASE_FULL = 0,         // reduce the group partials, then solve (single GPU)
+    SOLVE_PHASE_REDUCE_ONLY = 1,  // reduce only: sum_out[92] (flivo_h_share_model; first half of the multi-GPU trip)
+    SOLVE_PHASE_FROM_RANKS = 2    // sum rank_blocks[nranks][96] in rank order, then solve (second half, multi-GPU)
+};
+
+struct SolveParams {
+    const double* gpartials;   // [groups * PSTRIDE]
+    int groups;
+    int phase;
+    int mode;                  // FLIVO_MODE_*
+    int max_iter;
+    int force_search;
+    int nranks;
+    double R;                  // laser_point_cov
+    double limit[23];
+    double* x;                 // device flivo_state, in/out
+    const double* x_prop;      // device flivo_state
+    const double* P_prop;      // n x n
+    double* P_out;             // n x n, written when the loop stops
+    double* sum_out;           // [96] reduced block (may be null in FULL phase)
+    const double* rank_blocks; // [nranks * PSTRIDE]
+    Ctl* ctl;
+};
+
+void upload_term_table();
+void launch_fused(const FusedParams& P, int grid, cudaStream_t stream);
+void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
+                int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream);
+void launch_transform(const float4* body, int n, const double* state, float4* world, cudaStream_t stream);
+void launch_solve(const SolveParams& S, cudaStream_t stream);
+void launch_ctl_reset(Ctl* ctl, SearchStats* stats, cudaStream_t stream);
+
+}  // namespace flivo
