@@ -1,0 +1,151 @@
+"""Parity checks of the CUDA path (through the C ABI) against the CPU oracle.  Used by tests/ (-m gpu) and by
+__graft_entry__.smoke().  The oracle is the checker here, never the thing measured.
+
+Tolerances (BASELINE.json north_star): neighbour index sets and valid-point masks bit-exact; H^T H / H^T z
+within 1e-5 relative per entry (relative to max(|entry|, 1e-12 * ||HTH||_F)); per-trip state
+increment within 1e-6 absolute per component.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+from oracle import pyoracle as orc  # noqa: E402
+
+HTH_RTOL = 1e-5
+DX_ATOL = 1e-6
+GATE_SQ = 5.0   # pointSearchSqDis[4] > 5 (src/laser_mapping.cpp:518): the fused path's search bound
+
+
+def oracle_knn(map_xyz, queries, k=5, max_dist=np.inf, ids=None, alive=None):
+    return orc.knn_bruteforce(map_xyz, queries, k, max_dist, ids, alive)
+
+
+def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids=None):
+    """One h_share_model trip on the CPU.  cache: dict carrying Nearest_Points between trips."""
+    st = orc.State.from_array(x)
+    if searched:
+        wpts = orc.body_to_world(body, st)
+        oid, osq, oxyz, ocnt, ties = oracle_knn(map_xyz, wpts, 5, np.inf, ids=map_ids)
+        cache.update(ids=oid, sqd=osq, xyz=oxyz, cnt=ocnt, ties=ties)
+    d5 = np.where(cache["cnt"] >= 5, cache["sqd"][:, 4], np.inf).astype(np.float32)
+    out = orc.h_share_model(body, st, cache["xyz"], cache["cnt"], d5, searched, mode, mask_prev)
+    return out
+
+
+def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.001, limit=None, force_search=False):
+    """The whole iterated update with the restated reference loop (V3: esekfom.hpp:1619-1928; V1:
+    src/laser_mapping.cpp:165-242).  Returns dict(x, P, trips, searches, dx (per trip), masks, eff, ids)."""
+    limit = np.full(23, 0.001) if limit is None else np.asarray(limit, float)
+    x = orc.State.from_array(x_prior)
+    x_prop = orc.State.from_array(x_prior)
+    P = np.array(P, dtype=np.float64, copy=True)
+    P_prop = P.copy()
+    cache = {}
+    mask = np.ones(len(body), np.uint8)
+    search, t, rematch, stopped = 1, 0, 0, 0
+    trips = searches = 0
+    dxs, trip_out = [], []
+    it = -1
+    out = None
+    while it < max_iter and not stopped:
+        do_search = bool(search or force_search)
+        out = oracle_trip(map_xyz, body, x.as_array(), do_search, cache, mode, mask)
+        mask = out["mask"]
+        searches += int(do_search)
+        if mode == orc.MODE_V1:
+            HPH, HPL = orc.repack_v1(out["HTH"], out["HTz"], laser_point_cov)
+            r = orc.solve_v1(x, x_prop, P, HPH, HPL, it, max_iter, rematch)
+            rematch, search, stopped = r["rematch"], r["search_next"], r["stopped"]
+            dxs.append(r["solution"].copy())
+            if stopped:
+                P = r["cov"]
+        else:
+            r = orc.solve_v3(x, x_prop, P_prop, out["HTH"], out["HTz"], laser_point_cov, it, max_iter, limit, t)
+            t, search, stopped = r["t"], r["converge"], r["stopped"]
+            dxs.append(r["dx"].copy())
+            if stopped:
+                P = r["P"]
+        trip_out.append(dict(searched=do_search, n_eff=out["n_eff"], HTH=out["HTH"].copy(), HTz=out["HTz"].copy(),
+                             x_after=x.as_array()))
+        trips += 1
+        it += 1
+    return dict(x=x.as_array(), P=P, trips=trips, searches=searches, dx=dxs, mask=mask, eff=out["eff"],
+                ids=cache["ids"], cnt=cache["cnt"], sqd=cache["sqd"], ties=cache["ties"], trip_out=trip_out,
+                n_eff=out["n_eff"], borderline=out["borderline"])
+
+
+def rel_err_block(got, want):
+    want = np.asarray(want, float)
+    got = np.asarray(got, float)
+    floor = 1e-12 * np.linalg.norm(want)
+    return np.max(np.abs(got - want) / np.maximum(np.abs(want), max(floor, 1e-300)))
+
+
+def compare_neighbours(gpu_ids, orc_ids, orc_sqd, orc_cnt, bound=GATE_SQ):
+    """GPU ids (searched with `bound` as max squared distance) vs the unbounded oracle list: row by row the GPU
+    list must equal the oracle's entries with d <= bound (a prefix, both ascending), -1 padded.  Returns the
+    number of mismatching rows."""
+    want = np.where((orc_sqd <= np.float32(bound)) & (np.arange(5)[None, :] < orc_cnt[:, None]), orc_ids, -1)
+    return int(np.any(want != gpu_ids, axis=1).sum()), want
+
+
+def check_trip(pkg, F, map_xyz, body, x, mode, verbose=False):
+    """Single searched trip: neighbour ids, masks, planes, world points, H^T H, H^T z."""
+    st = pkg.State.from_array(x)
+    g = F.h_share_model(st, mode, True, want=("selected", "eff", "nbr_id", "nbr_sqd", "plane", "world"))
+    cache = {}
+    o = oracle_trip(map_xyz, body, x, True, cache, mode)
+    assert cache["ties"] == 0, "synthetic data has a float32 tie straddling rank 5; re-seed"
+    bad, want_ids = compare_neighbours(g["nbr_id"], cache["ids"], cache["sqd"], cache["cnt"])
+    assert bad == 0, "%d / %d neighbour rows differ" % (bad, len(body))
+    assert np.array_equal(g["world"], o["world"]), "feats_down_world differs"
+    sqd_want = np.where(want_ids >= 0, cache["sqd"], np.inf).astype(np.float32)
+    assert np.array_equal(g["nbr_sqd"], sqd_want), "neighbour squared distances differ"
+    assert np.array_equal(g["selected"], o["mask"]), "point_selected_surf differs at %d points" % int((g["selected"] != o["mask"]).sum())
+    assert np.array_equal(g["eff"], o["eff"]), "effective-row mask differs"
+    assert g["n_eff"] == o["n_eff"]
+    assert np.array_equal(g["plane"], o["normvec"]), "normvec differs (max %g)" % np.abs(g["plane"] - o["normvec"]).max()
+    e1, e2 = rel_err_block(g["HTH"], o["HTH"]), rel_err_block(g["HTz"], o["HTz"])
+    assert e1 <= HTH_RTOL and e2 <= HTH_RTOL, "HTH / HTz relative error %g / %g" % (e1, e2)
+    assert abs(g["res_sum"] - o["res_sum"]) <= 1e-9 * max(1.0, abs(o["res_sum"]))
+    if verbose:
+        print("trip: n=%d n_eff=%d selected=%d borderline=%d HTH rel err %.2e HTz rel err %.2e" %
+              (len(body), g["n_eff"], int(g["selected"].sum()), o["borderline"], e1, e2))
+    return g, o
+
+
+def check_update_against_oracle(pkg, world, scan, mode=0, max_iter=4, force_search=False, verbose=False,
+                                sort_scan=False, cell_ratio=2):
+    """Build the map on the GPU, run one checked trip and the whole iterated update, compare with the oracle."""
+    map_xyz, body = world["points"], scan["body"]
+    npd = 18 if mode == pkg.MODE_V1 else 23
+    P0 = np.eye(npd) * 1e-4
+    with pkg.Flivo(downsample_size=world["ds"], cell_ratio=cell_ratio, initial_points=len(map_xyz), sort_scan=sort_scan) as F:
+        F.Build(map_xyz)
+        assert F.size() == len(map_xyz)
+        F.scan_upload(body)
+        check_trip(pkg, F, map_xyz, body, scan["x_prior"], mode, verbose)
+        cfg = pkg.make_cfg(mode=mode, max_iter=max_iter, laser_point_cov=0.001, force_search=force_search)
+        xg, Pg, rep = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+        o = oracle_update(map_xyz, body, scan["x_prior"], P0, mode, max_iter, 0.001, None, force_search)
+        assert rep.trips == o["trips"], "trips %d vs oracle %d" % (rep.trips, o["trips"])
+        assert rep.searches == o["searches"], "searches %d vs oracle %d" % (rep.searches, o["searches"])
+        assert rep.n_eff == o["n_eff"], "n_eff %d vs oracle %d" % (rep.n_eff, o["n_eff"])
+        nd = 18 if mode == pkg.MODE_V1 else 23
+        dx_err = np.abs(np.array(rep.dx_last[:nd]) - o["dx"][-1][:nd]).max()
+        assert dx_err <= DX_ATOL, "last state increment differs by %g" % dx_err
+        x_err = np.abs(xg.as_array() - o["x"]).max()
+        assert x_err <= 1e-6, "posterior state differs by %g" % x_err
+        p_err = np.abs(Pg - o["P"]).max() / np.abs(o["P"]).max()
+        assert p_err <= 1e-6, "posterior covariance differs by %g (relative to max entry)" % p_err
+        # the posterior must have moved toward the truth
+        t_err0 = np.linalg.norm(scan["x_prior"][9:12] - scan["x_true"][9:12])
+        t_err1 = np.linalg.norm(xg.as_array()[9:12] - scan["x_true"][9:12])
+        if verbose:
+            print("update: trips=%d searches=%d n_eff=%d dx_err=%.2e x_err=%.2e P_err=%.2e pos err %.4f -> %.4f m gpu %.3f ms" %
+                  (rep.trips, rep.searches, rep.n_eff, dx_err, x_err, p_err, t_err0, t_err1, rep.gpu_ms))
+        return dict(rep=rep, x=xg, P=Pg, oracle=o, pos_err=(t_err0, t_err1))

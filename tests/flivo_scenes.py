@@ -1,0 +1,159 @@
+"""Deterministic synthetic worlds and scans shared by tests/, smoke() and bench.py.
+
+World: "city block" = ground plane + axis-aligned boxes; points sampled on the surfaces with N(0, 0.01 m)
+normal noise and reduced by the Add_Points voxel rule (one point per downsample voxel, the one nearest the
+voxel centre; reference include/ikd-Tree/ikd_Tree.cpp:392-417), to exactly n_points.
+Scan: analytic ray casting of an Avia-like (70.4 x 77.2 deg) or Ouster-128-like (360 x 45 deg) pattern
+against the same geometry, N(0, 0.02 m) range noise, range in [1, 120] m, expressed in the lidar frame.
+Pure numpy; nothing here touches the GPU, the product library or /root/reference.
+"""
+import numpy as np
+
+T_LI = np.array([0.04165, 0.02326, -0.0284])   # lidar -> IMU offset (Avia default style)
+
+
+def _rot(rx, ry, rz):
+    cx, sx, cy, sy, cz, sz = np.cos(rx), np.sin(rx), np.cos(ry), np.sin(ry), np.cos(rz), np.sin(rz)
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    return Rz @ Ry @ Rx
+
+
+def exp_so3(v):
+    th = np.linalg.norm(v)
+    K = np.array([[0, -v[2], v[1]], [v[2], 0, -v[0]], [-v[1], v[0], 0]])
+    if th < 1e-12:
+        return np.eye(3) + K
+    return np.eye(3) + np.sin(th) / th * K + (1 - np.cos(th)) / th ** 2 * (K @ K)
+
+
+def voxel_downsample(pts, ds):
+    """One point per voxel: nearest to the voxel centre, first on ties (float32, reference formulas)."""
+    ds32 = np.float32(ds)
+    k = np.floor(pts / ds32).astype(np.int64)
+    lo = (k.astype(np.float32) * ds32)
+    mid = (lo.astype(np.float64) + (((lo + ds32) - lo).astype(np.float64)) / 2.0).astype(np.float32)
+    d = pts - mid
+    dist = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+    key = ((k[:, 0] + (1 << 20)) << 42) | ((k[:, 1] + (1 << 20)) << 21) | (k[:, 2] + (1 << 20))
+    order = np.lexsort((np.arange(len(pts)), dist, key))
+    ks = key[order]
+    head = np.ones(len(ks), bool)
+    head[1:] = ks[1:] != ks[:-1]
+    return pts[order[head]]
+
+
+def make_world(seed, n_points, ds, pitch=30.0):
+    """-> dict(points (n,3) f32, ds, extent, boxes (B,5) = cx, cy, w, d, h)."""
+    rng = np.random.default_rng(0xF4570000 + seed)
+    area_needed = n_points * ds * ds
+    extent = max(float(np.sqrt(0.42 * area_needed)), 2.2 * pitch)
+    nb = max(int(extent // pitch), 1)
+    cx, cy = np.meshgrid((np.arange(nb) + 0.5) * pitch - nb * pitch / 2, (np.arange(nb) + 0.5) * pitch - nb * pitch / 2)
+    B = cx.size
+    boxes = np.stack([cx.ravel() + rng.uniform(-3, 3, B), cy.ravel() + rng.uniform(-3, 3, B),
+                      rng.uniform(8, 20, B), rng.uniform(8, 20, B), rng.uniform(3, 20, B)], axis=1)
+    # keep the block that holds the origin free so a sensor can stand there
+    boxes = boxes[np.hypot(boxes[:, 0], boxes[:, 1]) > 16.0]
+    # rectangles: origin o, edges u, v, unit normal nrm
+    rects = [(np.array([-extent / 2, -extent / 2, 0.0]), np.array([extent, 0, 0.0]), np.array([0, extent, 0.0]))]
+    for bx, by, w, d, h in boxes:
+        x0, x1, y0, y1 = bx - w / 2, bx + w / 2, by - d / 2, by + d / 2
+        rects += [(np.array([x0, y0, 0.0]), np.array([w, 0, 0.0]), np.array([0, 0, h])),
+                  (np.array([x0, y1, 0.0]), np.array([w, 0, 0.0]), np.array([0, 0, h])),
+                  (np.array([x0, y0, 0.0]), np.array([0, d, 0.0]), np.array([0, 0, h])),
+                  (np.array([x1, y0, 0.0]), np.array([0, d, 0.0]), np.array([0, 0, h])),
+                  (np.array([x0, y0, h]), np.array([w, 0, 0.0]), np.array([0, d, 0.0]))]
+    O = np.array([r[0] for r in rects]); U = np.array([r[1] for r in rects]); V = np.array([r[2] for r in rects])
+    Nn = np.cross(U, V)
+    areas = np.linalg.norm(Nn, axis=1)
+    Nn = Nn / areas[:, None]
+    out = np.zeros((0, 3), np.float32)
+    factor = 1.7
+    for _ in range(6):
+        n_cand = int(factor * areas.sum() / (ds * ds)) + 1000
+        chunks = []
+        left = n_cand
+        while left > 0:                       # chunked to bound memory at 20M+ points
+            m = min(left, 8_000_000)
+            ridx = rng.choice(len(rects), size=m, p=areas / areas.sum())
+            a, b = rng.random(m), rng.random(m)
+            p = O[ridx] + a[:, None] * U[ridx] + b[:, None] * V[ridx] + rng.normal(0, 0.01, m)[:, None] * Nn[ridx]
+            chunks.append(voxel_downsample(p.astype(np.float32), ds))
+            left -= m
+        out = voxel_downsample(np.concatenate([out] + chunks), ds)
+        if len(out) >= n_points:
+            break
+        factor *= 1.5
+    if len(out) < n_points:
+        raise RuntimeError("world generator could not reach %d points (got %d)" % (n_points, len(out)))
+    keep = rng.permutation(len(out))[:n_points]
+    keep.sort()
+    pts = np.ascontiguousarray(out[keep])
+    return dict(points=pts, ds=float(ds), extent=extent, boxes=boxes, seed=seed)
+
+
+def _cast(origin, dirs, world, rmax=120.0):
+    """Nearest hit range of rays against ground z=0 and the boxes (inf = miss)."""
+    n = len(dirs)
+    t = np.full(n, np.inf)
+    dz = dirs[:, 2]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        tg = np.where(dz < -1e-9, -origin[2] / dz, np.inf)
+    half = world["extent"] / 2
+    hit = origin[None, :2] + tg[:, None] * dirs[:, :2]
+    ok = np.isfinite(tg) & (np.abs(hit[:, 0]) < half) & (np.abs(hit[:, 1]) < half)
+    t = np.where(ok, tg, t)
+    boxes = world["boxes"]
+    near = boxes[np.hypot(boxes[:, 0] - origin[0], boxes[:, 1] - origin[1]) < rmax + 30.0]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        inv = 1.0 / dirs
+    for bx, by, w, d, h in near:
+        lo = np.array([bx - w / 2, by - d / 2, 0.0]); hi = np.array([bx + w / 2, by + d / 2, h])
+        t0 = (lo - origin) * inv; t1 = (hi - origin) * inv
+        tn = np.nanmax(np.minimum(t0, t1), axis=1); tf = np.nanmin(np.maximum(t0, t1), axis=1)
+        ok = (tn <= tf) & (tn > 0)
+        t = np.where(ok & (tn < t), tn, t)
+    return t
+
+
+def make_scan(world, seed, n_points, kind="avia", pos=None, prior_noise=True):
+    """-> dict(body (n,3) f32 lidar frame, x_true (36,), x_prior (36,), P (23,23), kind)."""
+    rng = np.random.default_rng(0xF4571000 + seed)
+    R_true = _rot(rng.uniform(-0.03, 0.03), rng.uniform(-0.03, 0.03), rng.uniform(-np.pi, np.pi))
+    t_true = np.array([rng.uniform(-4, 4), rng.uniform(-4, 4), rng.uniform(1.5, 2.2)]) if pos is None else np.asarray(pos, float)
+    origin = R_true @ T_LI + t_true
+    body = np.zeros((0, 3))
+    tries = 0
+    while len(body) < n_points:
+        m = int((n_points - len(body)) * (1.6 if kind == "avia" else 2.6)) + 256
+        if kind == "avia":      # forward-looking cone, rosette-like: dense centre
+            az = np.deg2rad(rng.uniform(-35.2, 35.2, m)); el = np.deg2rad(rng.uniform(-38.6, 38.6, m))
+            order = np.lexsort((az, np.floor(el * 40)))
+            az, el = az[order], el[order]
+        else:                   # Ouster-128-like: 128 rings x columns, column-major like the driver
+            cols = m // 128 + 1
+            azc = (np.arange(cols) + rng.random()) * (2 * np.pi / cols)
+            elr = np.deg2rad(np.linspace(-22.5, 22.5, 128))
+            az = np.repeat(azc, 128)[:m]; el = np.tile(elr, cols)[:m]
+            az = az + rng.normal(0, 1e-4, m); el = el + rng.normal(0, 1e-4, m)
+        d_b = np.stack([np.cos(el) * np.cos(az), np.cos(el) * np.sin(az), np.sin(el)], axis=1)
+        r = _cast(origin, d_b @ R_true.T, world)
+        ok = np.isfinite(r) & (r >= 1.0) & (r <= 120.0)
+        rr = r[ok] + rng.normal(0, 0.02, ok.sum())
+        body = np.concatenate([body, d_b[ok] * rr[:, None]])
+        tries += 1
+        if tries > 20:
+            raise RuntimeError("scan generator starved")
+    body = np.ascontiguousarray(body[:n_points].astype(np.float32))
+    x_true = np.zeros(36)
+    x_true[0:9] = R_true.reshape(9); x_true[9:12] = t_true
+    x_true[12:21] = np.eye(3).reshape(9); x_true[21:24] = T_LI
+    x_true[33:36] = [0.0, 0.0, -9.809]
+    x_prior = x_true.copy()
+    if prior_noise:
+        dth = np.deg2rad(rng.uniform(-0.5, 0.5, 3)); dt = rng.uniform(-0.05, 0.05, 3)
+        x_prior[0:9] = (R_true @ exp_so3(dth)).reshape(9)
+        x_prior[9:12] = t_true + dt
+    return dict(body=body, x_true=x_true, x_prior=x_prior, P=np.eye(23) * 1e-4, kind=kind, seed=seed)
