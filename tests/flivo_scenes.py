@@ -157,3 +157,164 @@ def make_scan(world, seed, n_points, kind="avia", pos=None, prior_noise=True):
         x_prior[0:9] = (R_true @ exp_so3(dth)).reshape(9)
         x_prior[9:12] = t_true + dt
     return dict(body=body, x_true=x_true, x_prior=x_prior, P=np.eye(23) * 1e-4, kind=kind, seed=seed)
+
+
+# ------------------------------------------------------------------------------------------------------
+# torch versions of the same generators for bench-size workloads (20M-point maps, 260k-point scans): the
+# numpy path above takes minutes there.  Same geometry and rules; a different (torch) random stream.
+# `device` may be "cuda" (bench on the GPU box) or "cpu".
+# ------------------------------------------------------------------------------------------------------
+def _voxel_downsample_t(pts, ds):
+    import torch
+    ds32 = torch.tensor(ds, dtype=torch.float32, device=pts.device)
+    kf = torch.floor(pts / ds32)
+    k = kf.to(torch.int64)
+    lo = kf * ds32
+    mid = (lo.double() + ((lo + ds32) - lo).double() / 2.0).float()
+    d = pts - mid
+    dist = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+    key = ((k[:, 0] + (1 << 20)) << 42) | ((k[:, 1] + (1 << 20)) << 21) | (k[:, 2] + (1 << 20))
+    o1 = torch.sort(dist, stable=True).indices
+    o2 = torch.sort(key[o1], stable=True)
+    order = o1[o2.indices]
+    ks = o2.values
+    head = torch.ones(len(ks), dtype=torch.bool, device=pts.device)
+    head[1:] = ks[1:] != ks[:-1]
+    return pts[order[head]]
+
+
+def make_world_torch(seed, n_points, ds, device="cuda", pitch=30.0):
+    """make_world at bench sizes.  -> dict(points: torch (n,3) f32 on `device`, ds, extent, boxes (numpy))."""
+    import torch
+    rng = np.random.default_rng(0xF4570000 + seed)
+    g = torch.Generator(device=device)
+    g.manual_seed(0xF4570000 + seed)
+    area_needed = n_points * ds * ds
+    extent = max(float(np.sqrt(0.42 * area_needed)), 2.2 * pitch)
+    nb = max(int(extent // pitch), 1)
+    cx, cy = np.meshgrid((np.arange(nb) + 0.5) * pitch - nb * pitch / 2, (np.arange(nb) + 0.5) * pitch - nb * pitch / 2)
+    B = cx.size
+    boxes = np.stack([cx.ravel() + rng.uniform(-3, 3, B), cy.ravel() + rng.uniform(-3, 3, B),
+                      rng.uniform(8, 20, B), rng.uniform(8, 20, B), rng.uniform(3, 20, B)], axis=1)
+    boxes = boxes[np.hypot(boxes[:, 0], boxes[:, 1]) > 16.0]
+    O = [np.array([-extent / 2, -extent / 2, 0.0])]; U = [np.array([extent, 0, 0.0])]; V = [np.array([0, extent, 0.0])]
+    for bx, by, w, d, h in boxes:
+        x0, x1, y0, y1 = bx - w / 2, bx + w / 2, by - d / 2, by + d / 2
+        O += [np.array([x0, y0, 0.0]), np.array([x0, y1, 0.0]), np.array([x0, y0, 0.0]), np.array([x1, y0, 0.0]), np.array([x0, y0, h])]
+        U += [np.array([w, 0, 0.0]), np.array([w, 0, 0.0]), np.array([0, d, 0.0]), np.array([0, d, 0.0]), np.array([w, 0, 0.0])]
+        V += [np.array([0, 0, h]), np.array([0, 0, h]), np.array([0, 0, h]), np.array([0, 0, h]), np.array([0, d, 0.0])]
+    O, U, V = np.array(O), np.array(U), np.array(V)
+    Nn = np.cross(U, V)
+    areas = np.linalg.norm(Nn, axis=1)
+    Nn = Nn / areas[:, None]
+    tO, tU, tV, tN = (torch.tensor(a, dtype=torch.float64, device=device) for a in (O, U, V, Nn))
+    cdf = torch.tensor(np.cumsum(areas / areas.sum()), dtype=torch.float64, device=device)
+    out = torch.zeros((0, 3), dtype=torch.float32, device=device)
+    factor = 1.7
+    for _ in range(6):
+        left = int(factor * areas.sum() / (ds * ds)) + 1000
+        chunks = [out]
+        while left > 0:
+            m = min(left, 16_000_000)
+            ridx = torch.searchsorted(cdf, torch.rand(m, generator=g, device=device, dtype=torch.float64)).clamp_(max=len(areas) - 1)
+            a = torch.rand(m, generator=g, device=device, dtype=torch.float64)
+            b = torch.rand(m, generator=g, device=device, dtype=torch.float64)
+            nz = torch.randn(m, generator=g, device=device, dtype=torch.float64) * 0.01
+            p = tO[ridx] + a[:, None] * tU[ridx] + b[:, None] * tV[ridx] + nz[:, None] * tN[ridx]
+            chunks.append(_voxel_downsample_t(p.float(), ds))
+            left -= m
+        out = _voxel_downsample_t(torch.cat(chunks), ds)
+        if len(out) >= n_points:
+            break
+        factor *= 1.5
+    if len(out) < n_points:
+        raise RuntimeError("world generator could not reach %d points (got %d)" % (n_points, len(out)))
+    keep = torch.randperm(len(out), generator=g, device=device)[:n_points].sort().values
+    return dict(points=out[keep].contiguous(), ds=float(ds), extent=extent, boxes=boxes, seed=seed)
+
+
+def _cast_t(origin, dirs, world, rmax=120.0):
+    import torch
+    dev = dirs.device
+    o = torch.tensor(origin, dtype=torch.float64, device=dev)
+    dz = dirs[:, 2]
+    inf = torch.full_like(dz, float("inf"))
+    tg = torch.where(dz < -1e-9, -o[2] / dz, inf)
+    half = world["extent"] / 2
+    hit = o[None, :2] + torch.nan_to_num(tg, posinf=0.0)[:, None] * dirs[:, :2]
+    ok = torch.isfinite(tg) & (hit[:, 0].abs() < half) & (hit[:, 1].abs() < half)
+    t = torch.where(ok, tg, inf)
+    boxes = world["boxes"]
+    near = boxes[np.hypot(boxes[:, 0] - origin[0], boxes[:, 1] - origin[1]) < rmax + 30.0]
+    inv = 1.0 / dirs
+    for bx, by, w, d, h in near:
+        lo = torch.tensor([bx - w / 2, by - d / 2, 0.0], dtype=torch.float64, device=dev)
+        hi = torch.tensor([bx + w / 2, by + d / 2, h], dtype=torch.float64, device=dev)
+        t0 = (lo - o) * inv; t1 = (hi - o) * inv
+        tn = torch.minimum(t0, t1).amax(dim=1); tf = torch.maximum(t0, t1).amin(dim=1)
+        ok = (tn <= tf) & (tn > 0)
+        t = torch.where(ok & (tn < t), tn, t)
+    return t
+
+
+def make_scan_torch(world, seed, n_points, kind="ouster", pos=None, device="cuda", prior_noise=True):
+    """make_scan at bench sizes.  -> dict(body: torch (n,3) f32 on `device`, x_true, x_prior, P, kind)."""
+    import torch
+    rng = np.random.default_rng(0xF4571000 + seed)
+    g = torch.Generator(device=device)
+    g.manual_seed(0xF4571000 + seed)
+    R_true = _rot(rng.uniform(-0.03, 0.03), rng.uniform(-0.03, 0.03), rng.uniform(-np.pi, np.pi))
+    t_true = np.array([rng.uniform(-4, 4), rng.uniform(-4, 4), rng.uniform(1.5, 2.2)]) if pos is None else np.asarray(pos, float)
+    origin = R_true @ T_LI + t_true
+    Rt = torch.tensor(R_true.T, dtype=torch.float64, device=device)
+    body = torch.zeros((0, 3), dtype=torch.float64, device=device)
+    tries = 0
+    while len(body) < n_points:
+        m = int((n_points - len(body)) * (1.6 if kind == "avia" else 2.6)) + 256
+        if kind == "avia":
+            az = torch.deg2rad((torch.rand(m, generator=g, device=device, dtype=torch.float64) * 2 - 1) * 35.2)
+            el = torch.deg2rad((torch.rand(m, generator=g, device=device, dtype=torch.float64) * 2 - 1) * 38.6)
+            o1 = torch.sort(az, stable=True).indices
+            o2 = torch.sort(torch.floor(el[o1] * 40), stable=True).indices
+            order = o1[o2]
+            az, el = az[order], el[order]
+        else:
+            cols = m // 128 + 1
+            azc = (torch.arange(cols, device=device, dtype=torch.float64) + rng.random()) * (2 * np.pi / cols)
+            elr = torch.deg2rad(torch.linspace(-22.5, 22.5, 128, device=device, dtype=torch.float64))
+            az = azc.repeat_interleave(128)[:m]; el = elr.repeat(cols)[:m]
+            az = az + torch.randn(m, generator=g, device=device, dtype=torch.float64) * 1e-4
+            el = el + torch.randn(m, generator=g, device=device, dtype=torch.float64) * 1e-4
+        d_b = torch.stack([torch.cos(el) * torch.cos(az), torch.cos(el) * torch.sin(az), torch.sin(el)], dim=1)
+        r = _cast_t(origin, d_b @ Rt, world)
+        ok = torch.isfinite(r) & (r >= 1.0) & (r <= 120.0)
+        rr = r[ok] + torch.randn(int(ok.sum()), generator=g, device=device, dtype=torch.float64) * 0.02
+        body = torch.cat([body, d_b[ok] * rr[:, None]])
+        tries += 1
+        if tries > 20:
+            raise RuntimeError("scan generator starved")
+    body = body[:n_points].float().contiguous()
+    x_true = np.zeros(36)
+    x_true[0:9] = R_true.reshape(9); x_true[9:12] = t_true
+    x_true[12:21] = np.eye(3).reshape(9); x_true[21:24] = T_LI
+    x_true[33:36] = [0.0, 0.0, -9.809]
+    x_prior = x_true.copy()
+    if prior_noise:
+        dth = np.deg2rad(rng.uniform(-0.5, 0.5, 3)); dt = rng.uniform(-0.05, 0.05, 3)
+        x_prior[0:9] = (R_true @ exp_so3(dth)).reshape(9)
+        x_prior[9:12] = t_true + dt
+    return dict(body=body, x_true=x_true, x_prior=x_prior, P=np.eye(23) * 1e-4, kind=kind, seed=seed)
+
+
+def street_positions(world, count, pitch=30.0):
+    """Sensor positions on street intersections of the box grid (free of buildings), nearest the origin first."""
+    nb = max(int(world["extent"] // pitch), 1)
+    lines = np.arange(nb + 1) * pitch - nb * pitch / 2
+    xs, ys = np.meshgrid(lines, lines)
+    p = np.stack([xs.ravel(), ys.ravel()], axis=1)
+    lim = world["extent"] / 2 - 40.0
+    p = p[(np.abs(p[:, 0]) < lim) & (np.abs(p[:, 1]) < lim)]
+    p = p[np.argsort(np.hypot(p[:, 0], p[:, 1]), kind="stable")]
+    if len(p) == 0:
+        p = np.zeros((1, 2))
+    return [np.array([p[i % len(p), 0], p[i % len(p), 1], 1.8]) for i in range(count)]
