@@ -269,6 +269,7 @@ def run_flivo(args, rank, world_size, local_rank):
             (fused_search_ms if st.last_trip_searched[t] else fused_reuse_ms).append(st.last_fused_ms[t])
             solve_ms.append(st.last_solve_ms[t])
         last = (k % S, x, P, rep)
+        far_q, cand = int(st.last_far_queries), int(st.last_candidates)
     barrier()
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1)
@@ -303,7 +304,8 @@ def run_flivo(args, rank, world_size, local_rank):
     return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
-                trips_per_step=trips_total / args.steps, shard=shard)
+                trips_per_step=trips_total / args.steps, shard=shard,
+                search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
 def peaks():
@@ -393,7 +395,7 @@ def main():
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity,
-            "map_build_s": r["map_build_s"],
+            "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
         }
         print(json.dumps(line), file=out, flush=True)
     r["F"].close()

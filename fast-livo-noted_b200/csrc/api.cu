@@ -79,6 +79,7 @@ struct flivo_ctx {
     float4 *d_normvec = nullptr, *d_world = nullptr;
     double *d_partials = nullptr, *d_gpartials = nullptr;
     unsigned int* d_group_cnt = nullptr;
+    unsigned int* d_far_list = nullptr;
     void* d_out = nullptr;          // un-permute scratch for optional outputs
     size_t d_out_bytes = 0;
     // loop state
@@ -146,7 +147,7 @@ static bool stride_ok(size_t s) { return s >= 12 && (s % 4) == 0; }
 
 // ---- small kernels of the plumbing layer ------------------------------------------------------------------
 __global__ void k_ctl_set(Ctl* ctl, int search) {
-    if (threadIdx.x == 0) { ctl->search = search; ctl->stopped = 0; ctl->unit_counter = 0; }
+    if (threadIdx.x == 0) { ctl->search = search; ctl->stopped = 0; ctl->unit_counter = 0; ctl->far_count = 0; }
 }
 // Morton key of the scan point's cell in the lidar frame (a rigid transform preserves locality, so points
 // that are neighbours here query neighbouring map cells whatever the state is)
@@ -271,10 +272,10 @@ static void free_scan(flivo_ctx* ctx) {
     cudaFree(ctx->d_body_own);
     cudaFree(ctx->d_body_in); cudaFree(ctx->d_perm); cudaFree(ctx->d_skey_a); cudaFree(ctx->d_skey_b); cudaFree(ctx->d_sidx_a);
     cudaFree(ctx->d_cub); cudaFree(ctx->d_near); cudaFree(ctx->d_near_meta); cudaFree(ctx->d_sel); cudaFree(ctx->d_eff);
-    cudaFree(ctx->d_normvec); cudaFree(ctx->d_world); cudaFree(ctx->d_partials); cudaFree(ctx->d_gpartials); cudaFree(ctx->d_group_cnt);
+    cudaFree(ctx->d_normvec); cudaFree(ctx->d_world); cudaFree(ctx->d_partials); cudaFree(ctx->d_gpartials); cudaFree(ctx->d_group_cnt); cudaFree(ctx->d_far_list);
     ctx->d_body = ctx->d_body_own = ctx->d_body_in = nullptr; ctx->d_perm = nullptr; ctx->d_skey_a = ctx->d_skey_b = nullptr; ctx->d_sidx_a = nullptr;
     ctx->d_cub = nullptr; ctx->d_near = nullptr; ctx->d_near_meta = nullptr; ctx->d_sel = ctx->d_eff = nullptr;
-    ctx->d_normvec = ctx->d_world = nullptr; ctx->d_partials = ctx->d_gpartials = nullptr; ctx->d_group_cnt = nullptr;
+    ctx->d_normvec = ctx->d_world = nullptr; ctx->d_partials = ctx->d_gpartials = nullptr; ctx->d_group_cnt = nullptr; ctx->d_far_list = nullptr;
     ctx->scan_cap = 0; ctx->scan_n = 0; ctx->cub_bytes = 0;
 }
 
@@ -471,6 +472,7 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
         CKC(cudaMalloc(&ctx->d_partials, units * PSTRIDE * sizeof(double)));
         CKC(cudaMalloc(&ctx->d_gpartials, groups * PSTRIDE * sizeof(double)));
         CKC(cudaMalloc(&ctx->d_group_cnt, groups * sizeof(unsigned int)));
+        CKC(cudaMalloc(&ctx->d_far_list, cap * sizeof(unsigned int)));
         CKC(cudaMemsetAsync(ctx->d_group_cnt, 0, groups * sizeof(unsigned int), ctx->stream));
         ctx->scan_cap = cap;
     }
@@ -530,7 +532,7 @@ static FusedParams make_fused(flivo_ctx* ctx, int mode, int force_search, uint32
     P.state = ctx->d_x;
     P.near = ctx->d_near; P.near_meta = ctx->d_near_meta; P.sel = ctx->d_sel; P.eff = ctx->d_eff;
     P.normvec = ctx->d_normvec; P.world = ctx->d_world;
-    P.partials = ctx->d_partials; P.gpartials = ctx->d_gpartials; P.group_cnt = ctx->d_group_cnt;
+    P.partials = ctx->d_partials; P.gpartials = ctx->d_gpartials; P.group_cnt = ctx->d_group_cnt; P.far_list = ctx->d_far_list;
     P.ctl = ctx->d_ctl; P.stats = ctx->d_stats;
     P.mode = mode; P.force_search = force_search; P.max_sq_bits = max_sq_bits;
     P.units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
@@ -583,6 +585,7 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
     k_ctl_set<<<1, 32, 0, ctx->stream>>>(ctx->d_ctl, do_search ? 1 : 0);
     if (do_search) CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
     FusedParams P = make_fused(ctx, mode, 0, gate_bits());
+    if (do_search) launch_search(P, ctx->sm_count * 8, ctx->stream);
     launch_fused(P, fused_grid(ctx, P.units), ctx->stream);
     SolveParams S{};
     S.gpartials = ctx->d_gpartials; S.groups = P.groups; S.phase = SOLVE_PHASE_REDUCE_ONLY; S.mode = mode;
@@ -667,6 +670,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     int launches = 1;
     for (int t = 0; t < trips; ++t) {
         CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
+        launch_search(P, ctx->sm_count * 8, s);   // both kernels exit at once on re-use trips
         launch_fused(P, grid, s);
         CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
         if (ctx->comm) {
@@ -676,11 +680,11 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
             if (nrc != 0) { ctx->err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "error"); return FLIVO_E_NCCL; }
             S.phase = SOLVE_PHASE_FROM_RANKS;
             launch_solve(S, s);
-            launches += 3;
+            launches += 5;
         } else {
             S.phase = SOLVE_PHASE_FULL;
             launch_solve(S, s);
-            launches += 2;
+            launches += 4;
         }
     }
     CKC(cudaGetLastError());

@@ -3,7 +3,8 @@
 // One launch = one LaserMapping::h_share_model call (reference src/laser_mapping.cpp:485-645 and
 // src/origin_laserMapping.cpp:916-1048):
 //   a1 world transform (:662-671)            -> per lane, double, narrowed to float
-//   a2 exact 5-NN (ikd_Tree.cpp:350-380)     -> warp per point over the voxel-hash map (search.cuh)
+//   a2 exact 5-NN (ikd_Tree.cpp:350-380)     -> thread per point over the 27-cell shell of the voxel-hash map,
+//                                               warp-cooperative search for the rare far queries (search.cuh)
 //   a3 far-neighbour gate (:518)             -> per lane
 //   a4 esti_plane (common_lib.h:670-702)     -> per lane, float, no FMA, fixed operation order
 //   a5 residual + range gate (:532-543)      -> per lane
@@ -182,10 +183,7 @@ __device__ __forceinline__ double dot3d(const double* a, double b0, double b1, d
 // fused kernel
 // ----------------------------------------------------------------------------------------------------
 struct __align__(16) WarpSmem {
-    union {
-        float4 nearp[32 * 5];     // neighbours found for the warp's 32 points (phase A -> B)
-        double rows[32 * 14];     // Jacobian rows h[12], z, pad (phase B -> C)
-    };
+    double rows[32 * 14];         // Jacobian rows h[12], z, pad of the warp's 32 points
 };
 
 __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
@@ -232,36 +230,14 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         float4 nb[5];
         int ncnt = 0;
         float d5 = INFINITY;
-        if (search) {
-            int npts = min(32, P.n - base);
-            for (int j = 0; j < npts; ++j) {
-                float qx = __shfl_sync(FULL, wx, j), qy = __shfl_sync(FULL, wy, j), qz = __shfl_sync(FULL, wz, j);
-                Cand out;
-                int cnt = warp_knn5(P.map, qx, qy, qz, P.max_sq_bits, lane, out, P.stats);
-                if (lane < 5) {
-                    float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-                    if (out.d != INF_BITS) p = __ldg(P.map.buckets + out.addr);
-                    ws.nearp[j * 5 + lane] = p;
-                }
-                float dlast = __uint_as_float(__shfl_sync(FULL, out.d, 4));
-                if (lane == j) { ncnt = cnt; d5 = dlast; }
-            }
-            __syncwarp();
-            // cache Nearest_Points for the re-use trips (coalesced: 160 float4 per warp)
-            for (int t = lane; t < npts * 5; t += 32) P.near[(size_t)base * 5 + t] = ws.nearp[t];
-            if (have) P.near_meta[i] = make_float2(__int_as_float(ncnt), d5);
+        // (on a search trip k_search / k_far of the same trip have just refreshed the Nearest_Points cache)
+        if (have) {
+            float2 meta = __ldg(P.near_meta + i);
+            ncnt = __float_as_int(meta.x);
+            d5 = meta.y;
 #pragma unroll
-            for (int r = 0; r < 5; ++r) nb[r] = ws.nearp[lane * 5 + r];
-        } else {
-            if (have) {
-                float2 meta = __ldg(P.near_meta + i);
-                ncnt = __float_as_int(meta.x);
-                d5 = meta.y;
-#pragma unroll
-                for (int r = 0; r < 5; ++r) nb[r] = __ldg(P.near + (size_t)i * 5 + r);
-            }
+            for (int r = 0; r < 5; ++r) nb[r] = __ldg(P.near + (size_t)i * 5 + r);
         }
-        __syncwarp();  // nearp is dead from here; the union is reused for the rows
 
         // ---- a3..a5: gates and plane -----------------------------------------------------------------
         bool sel;
@@ -374,6 +350,98 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
 }
 
 // ----------------------------------------------------------------------------------------------------
+// search kernels of a search trip (a1 + a2): refresh the Nearest_Points cache (P.near / P.near_meta)
+//   k_search : thread per point over the 27-cell shell; points it cannot finish go to P.far_list
+//   k_far    : warp per far point (growing cubes of cells), spread over the whole grid so sparse map
+//              regions do not serialise inside one CTA
+// Both exit at once on re-use trips (ctl->search == 0 and no force_search) and after the loop stopped.
+// ----------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void world_of(const double* __restrict__ st, float4 pb, float& wx, float& wy, float& wz) {
+    double pd0 = (double)pb.x, pd1 = (double)pb.y, pd2 = (double)pb.z;
+    double l0 = dot3d(st + 12, pd0, pd1, pd2) + st[21], l1 = dot3d(st + 15, pd0, pd1, pd2) + st[22], l2 = dot3d(st + 18, pd0, pd1, pd2) + st[23];
+    wx = (float)(dot3d(st + 0, l0, l1, l2) + st[9]);
+    wy = (float)(dot3d(st + 3, l0, l1, l2) + st[10]);
+    wz = (float)(dot3d(st + 6, l0, l1, l2) + st[11]);
+}
+
+constexpr int SEARCH_THREADS = 128;
+
+__global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
+    __shared__ double s_state[24];
+    Ctl* ctl = P.ctl;
+    if (ctl->stopped || !(ctl->search != 0 || P.force_search != 0)) return;
+    if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * SEARCH_THREADS + threadIdx.x;
+    const bool have = i < P.n;
+    unsigned nc = 0;
+    bool fin = true;
+    if (have) {
+        float wx, wy, wz;
+        world_of(s_state, __ldg(P.body + i), wx, wy, wz);
+        Top5 best;
+        int cnt = 0;
+        fin = thread_knn5_shell(P.map, wx, wy, wz, P.max_sq_bits, best, cnt, nc);
+        if (fin) {
+#pragma unroll
+            for (int r = 0; r < 5; ++r) {
+                float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                if (r < cnt) p = __ldg(P.map.buckets + best.a[r]);
+                P.near[(size_t)i * 5 + r] = p;
+            }
+            P.near_meta[i] = make_float2(__int_as_float(cnt), (cnt >= 5) ? __uint_as_float((uint32_t)(best.k[4] >> 32)) : INFINITY);
+        }
+    }
+    // far list: one atomic per warp
+    const unsigned pend = __ballot_sync(FULL, have && !fin);
+    if (pend) {
+        unsigned basep = 0;
+        if (lane == 0) basep = atomicAdd(&ctl->far_count, (unsigned)__popc(pend));
+        basep = __shfl_sync(FULL, basep, 0);
+        if (have && !fin) P.far_list[basep + __popc(pend & ((1u << lane) - 1u))] = (unsigned)i;
+    }
+    if (P.stats) {
+        const unsigned tot = __reduce_add_sync(FULL, nc);
+        if (lane == 0) {
+            if (pend) atomicAdd(&P.stats->far_queries, (unsigned long long)__popc(pend));
+            atomicAdd(&P.stats->candidates, (unsigned long long)tot);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128) k_far(FusedParams P) {
+    __shared__ double s_state[24];
+    Ctl* ctl = P.ctl;
+    if (ctl->stopped || !(ctl->search != 0 || P.force_search != 0)) return;
+    const unsigned nfar = ctl->far_count;
+    if (nfar == 0) return;
+    if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    unsigned nc = 0;
+    for (unsigned e = wid; e < nfar; e += nwarps) {
+        const unsigned i = P.far_list[e];
+        float wx, wy, wz;
+        world_of(s_state, __ldg(P.body + i), wx, wy, wz);
+        Cand out;
+        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, P.max_sq_bits, lane, out, nc);
+        if (lane < 5) {
+            float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+            if (out.d != INF_BITS) p = __ldg(P.map.buckets + out.addr);
+            P.near[(size_t)i * 5 + lane] = p;
+        }
+        const uint32_t dlast = __shfl_sync(FULL, out.d, 4);
+        if (lane == 0) P.near_meta[i] = make_float2(__int_as_float(cnt), (cnt >= 5) ? __uint_as_float(dlast) : INFINITY);
+    }
+    if (P.stats) {
+        const unsigned tot = __reduce_add_sync(FULL, nc);
+        if (lane == 0 && tot) atomicAdd(&P.stats->candidates, (unsigned long long)tot);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------------
 // batched Nearest_Search for the C ABI (flivo_knn): one warp per query
 // ----------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_knn(MapView map, const float4* __restrict__ q, int nq, int k, uint32_t max_sq_bits,
@@ -384,7 +452,10 @@ __global__ void __launch_bounds__(128) k_knn(MapView map, const float4* __restri
     for (int i = wid; i < nq; i += nwarps) {
         float4 p = __ldg(q + i);
         Cand out;
-        int cnt = warp_knn5(map, p.x, p.y, p.z, max_sq_bits, lane, out, stats);
+        unsigned nc = 0;
+        int cnt = warp_knn5_rings(map, p.x, p.y, p.z, max_sq_bits, lane, out, nc);
+        const unsigned tot = __reduce_add_sync(FULL, nc);
+        if (stats && lane == 0) atomicAdd(&stats->candidates, (unsigned long long)tot);
         int found = min(cnt, k);
         if (lane < k) {
             bool ok = lane < found;
@@ -415,6 +486,10 @@ __global__ void k_transform(const float4* __restrict__ body, int n, const double
 // ---- host launchers ---------------------------------------------------------------------------------
 void launch_fused(const FusedParams& P, int grid, cudaStream_t stream) {
     k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P);
+}
+void launch_search(const FusedParams& P, int far_grid, cudaStream_t stream) {
+    k_search<<<(P.n + SEARCH_THREADS - 1) / SEARCH_THREADS, SEARCH_THREADS, 0, stream>>>(P);
+    k_far<<<far_grid, 128, 0, stream>>>(P);
 }
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
                 int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream) {

@@ -27,7 +27,7 @@ struct Ctl {
     double res_mean;
     double dx_last[23];
     unsigned int unit_counter;   // dynamic work-unit scheduler of the fused kernel
-    unsigned int pad;
+    unsigned int far_count;      // entries of far_list written by the search kernel of this trip
 };
 
 struct FusedParams {
@@ -41,6 +41,7 @@ struct FusedParams {
     unsigned char* eff;        // [n] rows that entered H
     float4* normvec;           // [n] (nx,ny,nz,pd2)
     float4* world;             // [n] feats_down_world
+    unsigned int* far_list;    // [n] points the 27-cell shell could not finish (k_search -> k_far)
     double* partials;          // [units * PSTRIDE]
     double* gpartials;         // [groups * PSTRIDE]
     unsigned int* group_cnt;   // [groups]

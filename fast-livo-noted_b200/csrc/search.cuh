@@ -292,4 +292,209 @@ finish:
     return ws.count;
 }
 
+// ----------------------------------------------------------------------------------------------------
+// Thread-per-query fast path over the 3x3x3 cell shell (the common case on a downsampled map: the 5th
+// neighbour lies within one cell edge).  Same semantics and the same "final" test as shell 1 of
+// warp_knn5; a query the shell cannot finish is left to the warp-cooperative search above.
+// Per thread: <= 8 directory probes, the occupancy bits of each block pick the non-empty cells of the
+// shell, every bucket is read as 8 independent float4 loads (one 128-byte line).  Neighbouring threads
+// hold neighbouring queries (Morton-ordered scan), so their lines coincide in L1/L2.
+// ----------------------------------------------------------------------------------------------------
+struct Top5 {
+    unsigned long long k[5];   // (distance bits << 32) | id, ascending; ~0 = empty
+    uint32_t a[5];             // point slot
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int r = 0; r < 5; ++r) { k[r] = 0xFFFFFFFFFFFFFFFFull; a[r] = 0; }
+    }
+    // precondition: key < k[4]
+    __device__ __forceinline__ void insert(unsigned long long key, uint32_t addr) {
+        k[4] = key; a[4] = addr;
+#pragma unroll
+        for (int r = 4; r > 0; --r) {
+            bool sw = k[r] < k[r - 1];
+            unsigned long long kt = sw ? k[r - 1] : k[r];
+            uint32_t at = sw ? a[r - 1] : a[r];
+            k[r - 1] = sw ? k[r] : k[r - 1];
+            a[r - 1] = sw ? a[r] : a[r - 1];
+            k[r] = kt; a[r] = at;
+        }
+    }
+};
+
+// bits of the cells of block (bx,by,bz) that lie in [cq-1, cq+1]^3 (cell_off layout: x<<4 | y<<2 | z)
+__device__ __forceinline__ unsigned axis_bits(int cq, int b) {
+    int lo = max(cq - 1, b * 4) - b * 4, hi = min(cq + 1, b * 4 + 3) - b * 4;   // 0 <= lo <= hi <= 3
+    return ((2u << hi) - 1u) & ~((1u << lo) - 1u);
+}
+__device__ __forceinline__ unsigned long long shell_bits(int cqx, int cqy, int cqz, int bx, int by, int bz) {
+    unsigned xm = axis_bits(cqx, bx), ym = axis_bits(cqy, by), zm = axis_bits(cqz, bz);
+    unsigned yz = 0;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) if ((ym >> l) & 1u) yz |= zm << (4 * l);
+    unsigned long long m = 0;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) if ((xm >> l) & 1u) m |= (unsigned long long)yz << (16 * l);
+    return m;
+}
+
+// Returns true when the shell result is final (then best holds the answer; count = number found).
+__device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits,
+                                                  Top5& best, int& count, unsigned& ncand) {
+    best.init();
+    const int g = m.gshift;
+    const int cqx = voxel_key1(qx, m.ds) >> g, cqy = voxel_key1(qy, m.ds) >> g, cqz = voxel_key1(qz, m.ds) >> g;
+    // candidates above the bound never enter: the sentinel key of an empty rank is the bound itself
+    const unsigned long long bound_key = ((unsigned long long)max_sq_bits << 32) | 0xFFFFFFFFull;
+    unsigned long long worst = bound_key;   // key a candidate must beat (<=) to enter
+    int found = 0;
+    const int bx0 = (cqx - 1) >> 2, by0 = (cqy - 1) >> 2, bz0 = (cqz - 1) >> 2;
+    const int nbx = ((cqx + 1) >> 2) - bx0, nby = ((cqy + 1) >> 2) - by0, nbz = ((cqz + 1) >> 2) - bz0;   // 0 or 1
+    for (int ix = 0; ix <= nbx; ++ix)
+        for (int iy = 0; iy <= nby; ++iy)
+            for (int iz = 0; iz <= nbz; ++iz) {
+                const int bx = bx0 + ix, by = by0 + iy, bz = bz0 + iz;
+                const int slot = dir_find(m, pack_block(bx, by, bz));
+                if (slot < 0) continue;
+                unsigned long long occ = __ldg(m.blk_mask + slot) & shell_bits(cqx, cqy, cqz, bx, by, bz);
+                while (occ) {
+                    const int off = __ffsll((long long)occ) - 1;
+                    occ &= occ - 1;
+                    uint32_t b = __ldg(m.cell_tab + (size_t)slot * 64 + off);
+                    while (b != NONE32) {
+                        float4 p[BUCKET_SLOTS];
+#pragma unroll
+                        for (int s = 0; s < BUCKET_SLOTS; ++s) p[s] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
+                        const uint32_t nxt = __ldg(m.bucket_next + b);
+#pragma unroll
+                        for (int s = 0; s < BUCKET_SLOTS; ++s) {
+                            const int pid = __float_as_int(p[s].w);
+                            if (pid < 0) continue;
+                            ++ncand;
+                            const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, p[s].x, p[s].y, p[s].z));
+                            const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
+                            if (key <= worst) {
+                                best.insert(key, b * BUCKET_SLOTS + s);
+                                if (++found >= 5) worst = best.k[4];
+                            }
+                        }
+                        b = nxt;
+                    }
+                }
+            }
+    count = min(found, 5);
+    const float qabs = fmaxf(fabsf(qx), fmaxf(fabsf(qy), fabsf(qz)));
+    const float cov = covered_sq(m.cell_edge, 1.f, qabs);
+    const float max_sq = __uint_as_float(max_sq_bits);
+    return (count == 5 && __uint_as_float((uint32_t)(best.k[4] >> 32)) <= cov) || (cov >= max_sq);
+}
+
+// ----------------------------------------------------------------------------------------------------
+// Warp-per-query search for the queries the 27-cell shell cannot finish (sparse map regions).
+// Cubes of cells of growing radius n = 1, 2, .. around the query's cell; in step n the lanes take the
+// 4x4x4-cell blocks that intersect cube n, mask the block's occupancy bits with (cube n minus cube n-1),
+// and scan the surviving cells into a PER-LANE sorted top five (no shuffles in the scan).  After each
+// step the 32 lists are merged (five rounds of warp-min) to get the global fifth distance, which decides
+// whether the cube is final and tightens every lane's bound for the next step.  Cubes beyond
+// RING_MAX_CELLS (or unbounded searches in empty space) fall back to warp_knn5's directory sweep.
+// Output convention of warp_knn5: lanes 0..4 hold rank 0..4 in `out`; returns the number found.
+// ----------------------------------------------------------------------------------------------------
+constexpr int RING_MAX_CELLS = 8;
+
+__device__ __forceinline__ unsigned axis_bits_n(int cq, int b, int n) {
+    int lo = max(cq - n, b * 4) - b * 4, hi = min(cq + n, b * 4 + 3) - b * 4;
+    if (lo > hi) return 0u;
+    return ((2u << hi) - 1u) & ~((1u << lo) - 1u);
+}
+__device__ __forceinline__ unsigned long long cube_bits(int cqx, int cqy, int cqz, int bx, int by, int bz, int n) {
+    if (n < 0) return 0ull;
+    unsigned xm = axis_bits_n(cqx, bx, n), ym = axis_bits_n(cqy, by, n), zm = axis_bits_n(cqz, bz, n);
+    unsigned yz = 0;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) if ((ym >> l) & 1u) yz |= zm << (4 * l);
+    unsigned long long m = 0;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) if ((xm >> l) & 1u) m |= (unsigned long long)yz << (16 * l);
+    return m;
+}
+
+static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits, int lane,
+                                            Cand& out, unsigned& ncand) {
+    Top5 loc;
+    loc.init();
+    const int g = m.gshift;
+    const int cqx = voxel_key1(qx, m.ds) >> g, cqy = voxel_key1(qy, m.ds) >> g, cqz = voxel_key1(qz, m.ds) >> g;
+    const float qabs = fmaxf(fabsf(qx), fmaxf(fabsf(qy), fabsf(qz)));
+    const float max_sq = __uint_as_float(max_sq_bits);
+    const unsigned long long bound_key = ((unsigned long long)max_sq_bits << 32) | 0xFFFFFFFFull;
+    unsigned long long lworst = bound_key;
+    int lfound = 0;
+    for (int n = 1; n <= RING_MAX_CELLS; ++n) {
+        const int p = (n == 1) ? -1 : n - 1;
+        const int bx0 = (cqx - n) >> 2, by0 = (cqy - n) >> 2, bz0 = (cqz - n) >> 2;
+        const int nbx = ((cqx + n) >> 2) - bx0 + 1, nby = ((cqy + n) >> 2) - by0 + 1, nbz = ((cqz + n) >> 2) - bz0 + 1;
+        const int nb = nbx * nby * nbz;
+        for (int bi = lane; bi < nb; bi += 32) {
+            const int bx = bx0 + bi / (nby * nbz), by = by0 + (bi / nbz) % nby, bz = bz0 + bi % nbz;
+            unsigned long long want = cube_bits(cqx, cqy, cqz, bx, by, bz, n) & ~cube_bits(cqx, cqy, cqz, bx, by, bz, p);
+            if (!want) continue;
+            const int slot = dir_find(m, pack_block(bx, by, bz));
+            if (slot < 0) continue;
+            unsigned long long occ = __ldg(m.blk_mask + slot) & want;
+            while (occ) {
+                const int off = __ffsll((long long)occ) - 1;
+                occ &= occ - 1;
+                uint32_t b = __ldg(m.cell_tab + (size_t)slot * 64 + off);
+                while (b != NONE32) {
+                    const uint32_t nxt = __ldg(m.bucket_next + b);
+#pragma unroll 2
+                    for (int s = 0; s < BUCKET_SLOTS; ++s) {
+                        const float4 pt = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
+                        const int pid = __float_as_int(pt.w);
+                        if (pid < 0) continue;
+                        ++ncand;
+                        const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, pt.x, pt.y, pt.z));
+                        const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
+                        if (key <= lworst) {
+                            loc.insert(key, b * BUCKET_SLOTS + s);
+                            if (++lfound >= 5 && loc.k[4] < lworst) lworst = loc.k[4];
+                        }
+                    }
+                    b = nxt;
+                }
+            }
+        }
+        __syncwarp();
+        // merge the 32 sorted lists: rank r -> lane r
+        int h = 0, count = 0;
+        Cand res; res.d = INF_BITS; res.id = 0xFFFFFFFFu; res.addr = 0;
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+            unsigned long long head = h == 0 ? loc.k[0] : h == 1 ? loc.k[1] : h == 2 ? loc.k[2] : h == 3 ? loc.k[3] : h == 4 ? loc.k[4] : 0xFFFFFFFFFFFFFFFFull;
+            uint32_t ha = h == 0 ? loc.a[0] : h == 1 ? loc.a[1] : h == 2 ? loc.a[2] : h == 3 ? loc.a[3] : h == 4 ? loc.a[4] : 0u;
+            const uint32_t hd = (uint32_t)(head >> 32), hi = (uint32_t)head;
+            const uint32_t dmin = __reduce_min_sync(FULL, hd);
+            if (dmin == 0xFFFFFFFFu) break;  // warp-uniform: nothing left
+            const uint32_t idmin = __reduce_min_sync(FULL, hd == dmin ? hi : 0xFFFFFFFFu);
+            const bool win = (hd == dmin) && (hi == idmin);
+            const int wl = __ffs(__ballot_sync(FULL, win)) - 1;
+            const uint32_t wa = __shfl_sync(FULL, ha, wl);
+            if (lane == r) { res.d = dmin; res.id = idmin; res.addr = wa; }
+            if (win) ++h;
+            ++count;
+        }
+        const uint32_t d5 = __shfl_sync(FULL, res.d, 4);
+        const uint32_t i5 = __shfl_sync(FULL, res.id, 4);
+        const float cov = covered_sq(m.cell_edge, (float)n, qabs);
+        const bool done = (count == 5 && __uint_as_float(d5) <= cov) || (cov >= max_sq);
+        if (done) { out = res; return count; }
+        if (count == 5) {
+            const unsigned long long gk = ((unsigned long long)d5 << 32) | i5;
+            if (gk < lworst) lworst = gk;
+        }
+    }
+    // not final within RING_MAX_CELLS cells: the generic search (block rings + directory sweep)
+    return warp_knn5(m, qx, qy, qz, max_sq_bits, lane, out, nullptr);
+}
+
 }  // namespace flivo
