@@ -13,7 +13,7 @@ SOURCES = ["map.cu", "fused.cu", "solve.cu", "api.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: every float that feeds a comparison must round as separate mul/add (see csrc/flivo_dev.cuh)
 FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
-         "-Xcompiler", "-fPIC", "-I" + CSRC, "-I" + os.path.join(HERE, "..", "include")]
+         "-Xcompiler", "-fPIC,-fopenmp", "-I" + CSRC, "-I" + os.path.join(HERE, "..", "include")]
 
 
 def _newest(paths):
@@ -45,7 +45,7 @@ def build(force=False, verbose=False):
 
     with ThreadPoolExecutor(max_workers=4) as ex:
         objs = list(ex.map(cc, SOURCES))
-    cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-ldl"]
+    cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-ldl", "-lgomp"]
     if verbose:
         print(" ".join(cmd), file=sys.stderr)
     subprocess.check_call(cmd)

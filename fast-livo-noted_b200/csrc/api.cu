@@ -10,6 +10,8 @@
 
 #include <cub/cub.cuh>
 #include <dlfcn.h>
+#include <omp.h>
+#include <stdlib.h>
 #include <math.h>
 #include <string.h>
 #include <algorithm>
@@ -55,6 +57,8 @@ struct flivo_ctx {
     // host staging (pinned)
     float4* h_stage = nullptr;
     size_t h_stage_n = 0;
+    cudaEvent_t stage_ev = nullptr;   // last H2D copy out of h_stage
+    bool stage_pending = false;
     double* h_small = nullptr;      // pinned: 36 state + 36 + 529 P + ... (2048 doubles)
     Ctl* h_ctl = nullptr;           // pinned mirror
     SearchStats* h_stats = nullptr; // pinned mirror
@@ -110,9 +114,23 @@ static int map_rc(flivo_ctx* ctx, int rc) {
     return FLIVO_E_CUDA;
 }
 
-// strided host xyz -> pinned float4 -> device buffer (w = 0)
+// strided host xyz -> pinned float4 -> device buffer (w = 0).  The repack of the caller's AoS (48-byte
+// pcl::PointXYZINormal in the reference) runs on a few host threads, chunk by chunk, each chunk's H2D copy
+// overlapping the repack of the next; the call does not wait for the copies (stream order protects the
+// consumers, stage_ev protects the pinned buffer against the next call).
+static int host_threads() {
+    static int t = 0;
+    if (t == 0) {
+        const char* e = getenv("FLIVO_HOST_THREADS");
+        t = e ? atoi(e) : 4;   // MP_PROC_NUM of the reference on a >5-core host (CMakeLists.txt:33-36)
+        if (t < 1) t = 1;
+        if (t > omp_get_num_procs()) t = omp_get_num_procs();
+    }
+    return t;
+}
 static int stage_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes, float4* dst) {
     if (n == 0) return FLIVO_OK;
+    if (ctx->stage_pending) { CKC(cudaEventSynchronize(ctx->stage_ev)); ctx->stage_pending = false; }
     if (n > ctx->h_stage_n) {
         if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
         ctx->h_stage = nullptr; ctx->h_stage_n = 0;
@@ -122,17 +140,23 @@ static int stage_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t strid
     }
     const char* src = reinterpret_cast<const char*>(xyz);
     float4* h = ctx->h_stage;
-    if (stride_bytes == 16) {
-        memcpy(h, src, n * 16);
-    } else {
-        for (size_t i = 0; i < n; ++i) {
-            const float* p = reinterpret_cast<const float*>(src + i * stride_bytes);
-            h[i] = make_float4(p[0], p[1], p[2], 0.f);
+    const size_t CH = 1u << 16;
+    const int nt = host_threads();
+    for (size_t c0 = 0; c0 < n; c0 += CH) {
+        const size_t m = std::min(CH, n - c0);
+        if (stride_bytes == 16) {
+            memcpy(h + c0, src + c0 * 16, m * 16);
+        } else {
+#pragma omp parallel for num_threads(nt) schedule(static) if (m >= 8192 && nt > 1)
+            for (long i = 0; i < (long)m; ++i) {
+                const float* p = reinterpret_cast<const float*>(src + (c0 + (size_t)i) * stride_bytes);
+                h[c0 + i] = make_float4(p[0], p[1], p[2], 0.f);
+            }
         }
+        CKC(cudaMemcpyAsync(dst + c0, h + c0, m * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
     }
-    CKC(cudaMemcpyAsync(dst, h, n * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
-    // the pinned buffer is reused by the next call
-    CKC(cudaStreamSynchronize(ctx->stream));
+    CKC(cudaEventRecord(ctx->stage_ev, ctx->stream));
+    ctx->stage_pending = true;
     return FLIVO_OK;
 }
 static int ensure_dstage(flivo_ctx* ctx, size_t n) {
@@ -248,6 +272,7 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     CKC(cudaMallocHost(&ctx->h_ctl, sizeof(Ctl)));
     CKC(cudaMallocHost(&ctx->h_stats, sizeof(SearchStats)));
     for (auto& e : ctx->ev) CKC(cudaEventCreate(&e));
+    CKC(cudaEventCreateWithFlags(&ctx->stage_ev, cudaEventDisableTiming));
     CKC(cudaStreamSynchronize(ctx->stream));
     return FLIVO_OK;
 }
@@ -293,6 +318,7 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->stage_ev) cudaEventDestroy(ctx->stage_ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -487,7 +513,7 @@ static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool externa
         float inv_edge = 1.0f / ctx->map.view().cell_edge;
         k_scan_keys<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, n, inv_edge, ctx->d_skey_a, ctx->d_sidx_a);
         size_t tmp = ctx->cub_bytes;
-        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, 0, 63, ctx->stream));
+        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, 0, 30, ctx->stream));   // 10 bits per axis: locality only
         k_gather4<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, ctx->d_perm, n, ctx->d_body);
         CKC(cudaGetLastError());
     }

@@ -30,7 +30,7 @@ __device__ void d_mat3mul(const double* A, const double* B, double* C) {
         for (int j = 0; j < 3; ++j) C[i * 3 + j] = A[i * 3] * B[j] + A[i * 3 + 1] * B[3 + j] + A[i * 3 + 2] * B[6 + j];
 }
 // MTK::A_matrix (mtkmath.hpp:236-247)
-__device__ void d_A_matrix(const double* v, double* A) {
+__device__ __noinline__ void d_A_matrix(const double* v, double* A) {
     double sq = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
     double nrm = sqrt(sq);
     for (int i = 0; i < 9; ++i) A[i] = 0.0;
@@ -44,7 +44,7 @@ __device__ void d_A_matrix(const double* v, double* A) {
 }
 // rotation-matrix form of SO3::exp (SOn.hpp:293-297 via MTK::exp / cos_sinc_sqrt, mtkmath.hpp:139-171,249-256):
 // Rodrigues with series near zero.  The reference composes unit quaternions; identical up to rounding.
-__device__ void d_so3_exp(const double* v, double* R) {
+__device__ __noinline__ void d_so3_exp(const double* v, double* R) {
     double t2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
     double a, b;  // sin(t)/t, (1-cos t)/t^2
     if (t2 < 1e-8) {
@@ -63,7 +63,7 @@ __device__ void d_so3_exp(const double* v, double* R) {
 }
 // SO3 log of a rotation matrix, accurate for small angles (SOn.hpp:300-304 / MTK::log computes the same
 // vector from the unit quaternion: 2*atan(|v|/w)/|v| * v).
-__device__ void d_so3_log(const double* R, double* o) {
+__device__ __noinline__ void d_so3_log(const double* R, double* o) {
     double vx = 0.5 * (R[7] - R[5]), vy = 0.5 * (R[2] - R[6]), vz = 0.5 * (R[3] - R[1]);  // sin(t) * axis
     double s = sqrt(vx * vx + vy * vy + vz * vz);
     double c = 0.5 * (R[0] + R[4] + R[8] - 1.0);
@@ -73,7 +73,7 @@ __device__ void d_so3_log(const double* R, double* o) {
     o[0] = f * vx; o[1] = f * vy; o[2] = f * vz;
 }
 // V1 Exp / Log (include/so3_math.h:62-91)
-__device__ void d_Exp_v1(double v1, double v2, double v3, double* R) {
+__device__ __noinline__ void d_Exp_v1(double v1, double v2, double v3, double* R) {
     double nrm = sqrt(v1 * v1 + v2 * v2 + v3 * v3);
     for (int i = 0; i < 9; ++i) R[i] = 0;
     R[0] = R[4] = R[8] = 1;
@@ -86,7 +86,7 @@ __device__ void d_Exp_v1(double v1, double v2, double v3, double* R) {
         for (int i = 0; i < 9; ++i) R[i] += s * K[i] + c * K2[i];
     }
 }
-__device__ void d_Log_v1(const double* R, double* o) {
+__device__ __noinline__ void d_Log_v1(const double* R, double* o) {
     double tr = R[0] + R[4] + R[8];
     double theta = (tr > 3.0 - 1e-6) ? 0.0 : acos(0.5 * (tr - 1));
     double K[3] = {R[7] - R[5], R[2] - R[6], R[3] - R[1]};
@@ -96,7 +96,7 @@ __device__ void d_Log_v1(const double* R, double* o) {
 
 // ---- S2 (gravity) algebra, MTK::S2<double, 98090, 10000, 1> (use-ikfom.hpp:8; S2.hpp) ----------------------
 #define S2_LEN (98090.0 / 10000.0)
-__device__ void d_s2_Bx(const double* vec, double* Bx) {  // 3x2 row-major, S2_typ == 1 (S2.hpp:213-231)
+__device__ __noinline__ void d_s2_Bx(const double* vec, double* Bx) {  // 3x2 row-major, S2_typ == 1 (S2.hpp:213-231)
     const double len = S2_LEN;
     if (vec[0] + len > 1e-11) {
         double d = len + vec[0];
@@ -112,7 +112,7 @@ __device__ void d_s2_Bx(const double* vec, double* Bx) {  // 3x2 row-major, S2_t
 __device__ void d_cross(const double* a, const double* b, double* o) {
     o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
 }
-__device__ void d_s2_boxminus(const double* vec, const double* other, double* res2) {  // S2.hpp:136-160
+__device__ __noinline__ void d_s2_boxminus(const double* vec, const double* other, double* res2) {  // S2.hpp:136-160
     double cr[3];
     d_cross(vec, other, cr);
     double v_sin = sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]);
@@ -129,7 +129,7 @@ __device__ void d_s2_boxminus(const double* vec, const double* other, double* re
         for (int c = 0; c < 2; ++c) res2[c] = f * (Bx[c] * hv[0] + Bx[2 + c] * hv[1] + Bx[4 + c] * hv[2]);
     }
 }
-__device__ void d_s2_boxplus(double* vec, const double* delta2) {  // S2.hpp:128-134
+__device__ __noinline__ void d_s2_boxplus(double* vec, const double* delta2) {  // S2.hpp:128-134
     double Bx[6], Bu[3], R[9], o[3];
     d_s2_Bx(vec, Bx);
     for (int r = 0; r < 3; ++r) Bu[r] = Bx[r * 2] * delta2[0] + Bx[r * 2 + 1] * delta2[1];
@@ -137,7 +137,7 @@ __device__ void d_s2_boxplus(double* vec, const double* delta2) {  // S2.hpp:128
     for (int r = 0; r < 3; ++r) o[r] = R[r * 3] * vec[0] + R[r * 3 + 1] * vec[1] + R[r * 3 + 2] * vec[2];
     vec[0] = o[0]; vec[1] = o[1]; vec[2] = o[2];
 }
-__device__ void d_s2_Nx_yy(const double* vec, double* Nx) {  // 2x3, S2.hpp:259-264
+__device__ __noinline__ void d_s2_Nx_yy(const double* vec, double* Nx) {  // 2x3, S2.hpp:259-264
     double Bx[6], H[9];
     d_s2_Bx(vec, Bx);
     d_hat(vec, H);
@@ -146,7 +146,7 @@ __device__ void d_s2_Nx_yy(const double* vec, double* Nx) {  // 2x3, S2.hpp:259-
             Nx[r * 3 + c] = 1 / S2_LEN / S2_LEN * (Bx[r] * H[c] + Bx[2 + r] * H[3 + c] + Bx[4 + r] * H[6 + c]);
 }
 // S2_Mx (S2.hpp:266-280).  "scalar(1/2)" there is integer division == 0, so exp_delta is the identity.
-__device__ void d_s2_Mx(const double* vec, const double* delta2, double* Mx /*3x2*/) {
+__device__ __noinline__ void d_s2_Mx(const double* vec, const double* delta2, double* Mx /*3x2*/) {
     double Bx[6], H[9];
     d_s2_Bx(vec, Bx);
     d_hat(vec, H);
@@ -168,37 +168,70 @@ __device__ void d_s2_Mx(const double* vec, const double* delta2, double* Mx /*3x
 // state field offsets inside flivo_state (doubles)
 enum { S_ROT = 0, S_POS = 9, S_OFFR = 12, S_OFFT = 21, S_VEL = 24, S_BG = 27, S_BA = 30, S_GRAV = 33 };
 
-// x (-) y, state_ikfom order pos, rot, offR, offT, vel, bg, ba, grav(S2)
-__device__ void d_boxminus_v3(const double* x, const double* y, double* d) {
-    for (int i = 0; i < 3; ++i) d[i] = x[S_POS + i] - y[S_POS + i];
+// x (-) y, state_ikfom order pos, rot, offR, offT, vel, bg, ba, grav(S2).  The three parts touch disjoint
+// fields (0: pos, rot; 1: offR, offT, vel, bg, ba; 2: grav) so three threads of different warps run them at once.
+__device__ __noinline__ void d_boxminus_v3_part(const double* x, const double* y, double* d, int part) {
     double Rd[9];
-    // other.conjugate() * this  ->  y.rot^T * x.rot
-    for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) Rd[i * 3 + j] = y[S_ROT + i] * x[S_ROT + j] + y[S_ROT + 3 + i] * x[S_ROT + 3 + j] + y[S_ROT + 6 + i] * x[S_ROT + 6 + j];
-    d_so3_log(Rd, d + 3);
-    for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) Rd[i * 3 + j] = y[S_OFFR + i] * x[S_OFFR + j] + y[S_OFFR + 3 + i] * x[S_OFFR + 3 + j] + y[S_OFFR + 6 + i] * x[S_OFFR + 6 + j];
-    d_so3_log(Rd, d + 6);
-    for (int i = 0; i < 3; ++i) d[9 + i] = x[S_OFFT + i] - y[S_OFFT + i];
-    for (int i = 0; i < 3; ++i) d[12 + i] = x[S_VEL + i] - y[S_VEL + i];
-    for (int i = 0; i < 3; ++i) d[15 + i] = x[S_BG + i] - y[S_BG + i];
-    for (int i = 0; i < 3; ++i) d[18 + i] = x[S_BA + i] - y[S_BA + i];
-    d_s2_boxminus(x + S_GRAV, y + S_GRAV, d + 21);
+    if (part == 0) {
+        for (int i = 0; i < 3; ++i) d[i] = x[S_POS + i] - y[S_POS + i];
+        // other.conjugate() * this  ->  y.rot^T * x.rot
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) Rd[i * 3 + j] = y[S_ROT + i] * x[S_ROT + j] + y[S_ROT + 3 + i] * x[S_ROT + 3 + j] + y[S_ROT + 6 + i] * x[S_ROT + 6 + j];
+        d_so3_log(Rd, d + 3);
+    } else if (part == 1) {
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) Rd[i * 3 + j] = y[S_OFFR + i] * x[S_OFFR + j] + y[S_OFFR + 3 + i] * x[S_OFFR + 3 + j] + y[S_OFFR + 6 + i] * x[S_OFFR + 6 + j];
+        d_so3_log(Rd, d + 6);
+        for (int i = 0; i < 3; ++i) d[9 + i] = x[S_OFFT + i] - y[S_OFFT + i];
+        for (int i = 0; i < 3; ++i) d[12 + i] = x[S_VEL + i] - y[S_VEL + i];
+        for (int i = 0; i < 3; ++i) d[15 + i] = x[S_BG + i] - y[S_BG + i];
+        for (int i = 0; i < 3; ++i) d[18 + i] = x[S_BA + i] - y[S_BA + i];
+    } else {
+        d_s2_boxminus(x + S_GRAV, y + S_GRAV, d + 21);
+    }
 }
-__device__ void d_boxplus_v3(double* x, const double* d) {
-    for (int i = 0; i < 3; ++i) x[S_POS + i] += d[i];
+__device__ __noinline__ void d_boxplus_v3_part(double* x, const double* d, int part) {
     double E[9], Rn[9];
-    d_so3_exp(d + 3, E);
-    d_mat3mul(x + S_ROT, E, Rn);
-    for (int i = 0; i < 9; ++i) x[S_ROT + i] = Rn[i];
-    d_so3_exp(d + 6, E);
-    d_mat3mul(x + S_OFFR, E, Rn);
-    for (int i = 0; i < 9; ++i) x[S_OFFR + i] = Rn[i];
-    for (int i = 0; i < 3; ++i) x[S_OFFT + i] += d[9 + i];
-    for (int i = 0; i < 3; ++i) x[S_VEL + i] += d[12 + i];
-    for (int i = 0; i < 3; ++i) x[S_BG + i] += d[15 + i];
-    for (int i = 0; i < 3; ++i) x[S_BA + i] += d[18 + i];
-    d_s2_boxplus(x + S_GRAV, d + 21);
+    if (part == 0) {
+        for (int i = 0; i < 3; ++i) x[S_POS + i] += d[i];
+        d_so3_exp(d + 3, E);
+        d_mat3mul(x + S_ROT, E, Rn);
+        for (int i = 0; i < 9; ++i) x[S_ROT + i] = Rn[i];
+    } else if (part == 1) {
+        d_so3_exp(d + 6, E);
+        d_mat3mul(x + S_OFFR, E, Rn);
+        for (int i = 0; i < 9; ++i) x[S_OFFR + i] = Rn[i];
+        for (int i = 0; i < 3; ++i) x[S_OFFT + i] += d[9 + i];
+        for (int i = 0; i < 3; ++i) x[S_VEL + i] += d[12 + i];
+        for (int i = 0; i < 3; ++i) x[S_BG + i] += d[15 + i];
+        for (int i = 0; i < 3; ++i) x[S_BA + i] += d[18 + i];
+    } else {
+        d_s2_boxplus(x + S_GRAV, d + 21);
+    }
+}
+// J = A_matrix(v)^T and seg <- J * seg  (esekfom.hpp:1663-1672)
+__device__ __noinline__ void d_so3_jac(const double* v, double* J, double* seg) {
+    double A[9];
+    d_A_matrix(v, A);
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) J[i * 3 + j] = A[j * 3 + i];
+    if (seg) {
+        double t0 = J[0] * seg[0] + J[1] * seg[1] + J[2] * seg[2];
+        double t1 = J[3] * seg[0] + J[4] * seg[1] + J[5] * seg[2];
+        double t2 = J[6] * seg[0] + J[7] * seg[1] + J[8] * seg[2];
+        seg[0] = t0; seg[1] = t1; seg[2] = t2;
+    }
+}
+// J2 = Nx(x.grav) * Mx(x_prop.grav, d2) and seg <- J2 * seg  (esekfom.hpp:1684-1695)
+__device__ __noinline__ void d_s2_jac(const double* xg, const double* xpg, const double* d2, double* J2, double* seg) {
+    double Nx[6], Mx[6];
+    d_s2_Nx_yy(xg, Nx);
+    d_s2_Mx(xpg, d2, Mx);
+    for (int r = 0; r < 2; ++r) for (int c = 0; c < 2; ++c) J2[r * 2 + c] = Nx[r * 3] * Mx[c] + Nx[r * 3 + 1] * Mx[2 + c] + Nx[r * 3 + 2] * Mx[4 + c];
+    if (seg) {
+        double t0 = J2[0] * seg[0] + J2[1] * seg[1];
+        double t1 = J2[2] * seg[0] + J2[3] * seg[1];
+        seg[0] = t0; seg[1] = t1;
+    }
 }
 
 // T = blockdiag(I3, J3, J6, I.., J2) stored sparsely: apply to rows / columns of an n x n matrix in shared memory
@@ -239,37 +272,51 @@ __device__ void apply_T_cols(double* M, int n, const BlockT& T, int tid, int nth
     }
 }
 
-// Solve S^T X = B in place by Gauss-Jordan with partial pivoting; one warp.  Aug is m x (m + nrhs) row-major
-// holding [S^T | B]; on return the right part holds X.  Returns false on a zero pivot.
-__device__ bool warp_gauss_jordan(double* Aug, int m, int nrhs, int lane) {
-    const int w = m + nrhs;
+// Solve S^T X = B in place by Gauss-Jordan with partial pivoting; one warp, whole matrix in registers.
+// Aug is M x w (w = M + nrhs <= 64) row-major in shared memory holding [S^T | B]; on return the right part
+// holds X.  Lane l owns columns l and l + 32; the pivot column k (k < M <= 12) lives in lane k, its entries
+// are broadcast by shuffle, so there is no shared-memory traffic or barrier inside the elimination.
+// Operation order per entry is the textbook one (scale the pivot row, then row_i -= f * row_k).
+template <int M>
+__device__ __noinline__ bool warp_gauss_jordan(double* Aug, int w, int lane) {
+    // k_solve is one CTA running cold code once per trip, so instruction fetch dominates: the pivot loop is
+    // kept rolled (one ~250-instruction body) by rotating the register rows so that the current pivot row is
+    // always a[0]; after M steps every row is back at its own index.
+    const unsigned FULLM = 0xFFFFFFFFu;
+    double a[M], b[M];
+    const bool hasa = lane < w, hasb = lane + 32 < w;
+#pragma unroll
+    for (int i = 0; i < M; ++i) { a[i] = hasa ? Aug[i * w + lane] : 0.0; b[i] = hasb ? Aug[i * w + lane + 32] : 0.0; }
     bool ok = true;
-    for (int k = 0; k < m; ++k) {
-        // pivot: first maximum of |Aug[i][k]|, i >= k (all lanes compute it redundantly from shared memory)
-        int p = k;
-        double best = fabs(Aug[k * w + k]);
-        for (int i = k + 1; i < m; ++i) {
-            double v = fabs(Aug[i * w + k]);
-            if (v > best) { best = v; p = i; }
-        }
+#pragma unroll 1
+    for (int k = 0; k < M; ++k) {
+        const int nact = M - k;            // a[0 .. nact) = rows k .. M-1 (not pivoted yet), a[nact .. M) = rows 0 .. k-1
+        int p = 0;
+        double best = fabs(a[0]);
+#pragma unroll
+        for (int i = 1; i < M; ++i) { double v = fabs(a[i]); if (i < nact && v > best) { best = v; p = i; } }
+        p = __shfl_sync(FULLM, p, k);
+        best = __shfl_sync(FULLM, best, k);
         if (best == 0.0) ok = false;
-        __syncwarp();
-        if (p != k)
-            for (int c = lane; c < w; c += 32) { double t = Aug[k * w + c]; Aug[k * w + c] = Aug[p * w + c]; Aug[p * w + c] = t; }
-        __syncwarp();
-        double piv = Aug[k * w + k];
-        __syncwarp();
-        for (int c = lane; c < w; c += 32) Aug[k * w + c] = Aug[k * w + c] / piv;
-        __syncwarp();
-        // eliminate column k from every other row; lanes own columns, so the factor column is read before it changes
-        for (int i = 0; i < m; ++i) {
-            if (i == k) continue;
-            double f = Aug[i * w + k];
-            __syncwarp();
-            for (int c = lane; c < w; c += 32) Aug[i * w + c] -= f * Aug[k * w + c];
-            __syncwarp();
+#pragma unroll
+        for (int i = 1; i < M; ++i)
+            if (i == p) { double t = a[i]; a[i] = a[0]; a[0] = t; t = b[i]; b[i] = b[0]; b[0] = t; }
+        const double piv = __shfl_sync(FULLM, a[0], k);
+        a[0] = a[0] / piv;
+        b[0] = b[0] / piv;
+#pragma unroll
+        for (int i = 1; i < M; ++i) {
+            const double f = __shfl_sync(FULLM, a[i], k);
+            a[i] -= f * a[0];
+            b[i] -= f * b[0];
         }
+        const double ta = a[0], tb = b[0];
+#pragma unroll
+        for (int i = 0; i < M - 1; ++i) { a[i] = a[i + 1]; b[i] = b[i + 1]; }
+        a[M - 1] = ta; b[M - 1] = tb;
     }
+#pragma unroll
+    for (int i = 0; i < M; ++i) { if (hasa) Aug[i * w + lane] = a[i]; if (hasb) Aug[i * w + lane + 32] = b[i]; }
     return ok;
 }
 
@@ -362,30 +409,19 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
 
     if (mode == 0) {
         // ================= V3: esekfom.hpp:1633-1927 ==================================================
-        if (tid == 0) {
-            d_boxminus_v3(s_x, s_xp, s_dx);                                   // :1646
-            for (int i = 0; i < 23; ++i) s_dxnew[i] = s_dx[i];
-            double A[9];
-            d_A_matrix(s_dx + 3, A);                                          // :1663
-            for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J3[i * 3 + j] = A[j * 3 + i];
-            d_A_matrix(s_dx + 6, A);
-            for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J6[i * 3 + j] = A[j * 3 + i];
-            double Nx[6], Mx[6];
-            d_s2_Nx_yy(s_x + S_GRAV, Nx);                                     // :1684-1686
-            d_s2_Mx(s_xp + S_GRAV, s_dx + 21, Mx);
-            for (int r = 0; r < 2; ++r) for (int c = 0; c < 2; ++c) s_T.J2[r * 2 + c] = Nx[r * 3] * Mx[c] + Nx[r * 3 + 1] * Mx[2 + c] + Nx[r * 3 + 2] * Mx[4 + c];
-            double t0, t1, t2;
-            t0 = s_T.J3[0] * s_dxnew[3] + s_T.J3[1] * s_dxnew[4] + s_T.J3[2] * s_dxnew[5];
-            t1 = s_T.J3[3] * s_dxnew[3] + s_T.J3[4] * s_dxnew[4] + s_T.J3[5] * s_dxnew[5];
-            t2 = s_T.J3[6] * s_dxnew[3] + s_T.J3[7] * s_dxnew[4] + s_T.J3[8] * s_dxnew[5];
-            s_dxnew[3] = t0; s_dxnew[4] = t1; s_dxnew[5] = t2;
-            t0 = s_T.J6[0] * s_dxnew[6] + s_T.J6[1] * s_dxnew[7] + s_T.J6[2] * s_dxnew[8];
-            t1 = s_T.J6[3] * s_dxnew[6] + s_T.J6[4] * s_dxnew[7] + s_T.J6[5] * s_dxnew[8];
-            t2 = s_T.J6[6] * s_dxnew[6] + s_T.J6[7] * s_dxnew[7] + s_T.J6[8] * s_dxnew[8];
-            s_dxnew[6] = t0; s_dxnew[7] = t1; s_dxnew[8] = t2;
-            t0 = s_T.J2[0] * s_dxnew[21] + s_T.J2[1] * s_dxnew[22];
-            t1 = s_T.J2[2] * s_dxnew[21] + s_T.J2[3] * s_dxnew[22];
-            s_dxnew[21] = t0; s_dxnew[22] = t1;
+        if ((tid & 31) == 0 && tid < 96) {
+            const int part = tid >> 5;                                        // three warps, one lane each
+            d_boxminus_v3_part(s_x, s_xp, s_dx, part);                        // :1646
+            if (part == 0) {
+                for (int i = 0; i < 6; ++i) s_dxnew[i] = s_dx[i];
+                d_so3_jac(s_dx + 3, s_T.J3, s_dxnew + 3);                     // :1663
+            } else if (part == 1) {
+                for (int i = 6; i < 21; ++i) s_dxnew[i] = s_dx[i];
+                d_so3_jac(s_dx + 6, s_T.J6, s_dxnew + 6);
+            } else {
+                s_dxnew[21] = s_dx[21]; s_dxnew[22] = s_dx[22];
+                d_s2_jac(s_x + S_GRAV, s_xp + S_GRAV, s_dx + 21, s_T.J2, s_dxnew + 21);   // :1684-1686
+            }
         }
         __syncthreads();
         apply_T_rows(s_P, 23, 23, s_T, tid, NT);                              // :1665-1672, :1688-1695
@@ -409,7 +445,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         }
         __syncthreads();
         if (tid < 32) {
-            bool ok = warp_gauss_jordan(s_Aug, 12, 23, tid);
+            bool ok = warp_gauss_jordan<12>(s_Aug, 35, tid);
             if (tid == 0) s_flag[1] = ok ? 1 : 0;
         }
         __syncthreads();
@@ -434,8 +470,8 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_dxo[tid] = s - s_dxnew[tid];
         }
         __syncthreads();
-        if (tid == 0) {
-            d_boxplus_v3(s_x, s_dxo);                                         // :1814
+        if ((tid & 31) == 0 && tid < 96) d_boxplus_v3_part(s_x, s_dxo, tid >> 5);   // :1814
+        if (tid == 128) {
             int converge = 1;
             for (int i = 0; i < 23; ++i) if (fabs(s_dxo[i]) > S.limit[i]) { converge = 0; break; }
             int t = ctl->t, it = ctl->iter;
@@ -454,17 +490,13 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             ctl->unit_counter = 0; ctl->far_count = 0;
             for (int i = 0; i < 23; ++i) ctl->dx_last[i] = s_dxo[i];
             s_flag[0] = stop;
-            if (stop) {
-                double A[9];
-                d_A_matrix(s_dxo + 3, A);                                     // :1842
-                for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J3[i * 3 + j] = A[j * 3 + i];
-                d_A_matrix(s_dxo + 6, A);
-                for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) s_T.J6[i * 3 + j] = A[j * 3 + i];
-                double Nx[6], Mx[6];
-                d_s2_Nx_yy(s_x + S_GRAV, Nx);                                 // :1877-1879 (x_ already updated)
-                d_s2_Mx(s_xp + S_GRAV, s_dxo + 21, Mx);
-                for (int r = 0; r < 2; ++r) for (int c = 0; c < 2; ++c) s_T.J2[r * 2 + c] = Nx[r * 3] * Mx[c] + Nx[r * 3 + 1] * Mx[2 + c] + Nx[r * 3 + 2] * Mx[4 + c];
-            }
+        }
+        __syncthreads();
+        if (s_flag[0] && (tid & 31) == 0 && tid < 96) {
+            const int part = tid >> 5;
+            if (part == 0) d_so3_jac(s_dxo + 3, s_T.J3, nullptr);             // :1842
+            else if (part == 1) d_so3_jac(s_dxo + 6, s_T.J6, nullptr);
+            else d_s2_jac(s_x + S_GRAV, s_xp + S_GRAV, s_dxo + 21, s_T.J2, nullptr);   // :1877-1879 (x_ already updated)
         }
         __syncthreads();
         if (tid < 36) S.x[tid] = s_x[tid];
@@ -526,7 +558,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         }
         __syncthreads();
         if (tid < 32) {
-            bool ok = warp_gauss_jordan(s_Aug, 6, 18, tid);
+            bool ok = warp_gauss_jordan<6>(s_Aug, 24, tid);
             if (tid == 0) s_flag[1] = ok ? 1 : 0;
         }
         __syncthreads();
