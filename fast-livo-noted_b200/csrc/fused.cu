@@ -368,6 +368,8 @@ constexpr int SEARCH_THREADS = 128;
 
 __global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
     __shared__ double s_state[24];
+    __shared__ uint32_t s_idx[SHELL_CELLS * SEARCH_THREADS];   // per-thread work lists of thread_knn5_shell
+    __shared__ float s_gap[SHELL_CELLS * SEARCH_THREADS];
     Ctl* ctl = P.ctl;
     if (ctl->stopped || !(ctl->search != 0 || P.force_search != 0)) return;
     if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
@@ -382,7 +384,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
         world_of(s_state, __ldg(P.body + i), wx, wy, wz);
         Top5 best;
         int cnt = 0;
-        fin = thread_knn5_shell(P.map, wx, wy, wz, P.max_sq_bits, best, cnt, nc);
+        fin = thread_knn5_shell(P.map, wx, wy, wz, P.max_sq_bits, best, cnt, nc, s_idx + threadIdx.x, s_gap + threadIdx.x, SEARCH_THREADS);
         if (fin) {
 #pragma unroll
             for (int r = 0; r < 5; ++r) {

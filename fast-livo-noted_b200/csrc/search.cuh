@@ -307,18 +307,14 @@ struct Top5 {
 #pragma unroll
         for (int r = 0; r < 5; ++r) { k[r] = 0xFFFFFFFFFFFFFFFFull; a[r] = 0; }
     }
-    // precondition: key < k[4]
+    // precondition: key < k[4].  Shift-insert: every rank looks at its left neighbour only.
     __device__ __forceinline__ void insert(unsigned long long key, uint32_t addr) {
-        k[4] = key; a[4] = addr;
-#pragma unroll
-        for (int r = 4; r > 0; --r) {
-            bool sw = k[r] < k[r - 1];
-            unsigned long long kt = sw ? k[r - 1] : k[r];
-            uint32_t at = sw ? a[r - 1] : a[r];
-            k[r - 1] = sw ? k[r] : k[r - 1];
-            a[r - 1] = sw ? a[r] : a[r - 1];
-            k[r] = kt; a[r] = at;
-        }
+        const bool c3 = key < k[3], c2 = key < k[2], c1 = key < k[1], c0 = key < k[0];
+        k[4] = c3 ? k[3] : key;                  a[4] = c3 ? a[3] : addr;
+        k[3] = c3 ? (c2 ? k[2] : key) : k[3];    a[3] = c3 ? (c2 ? a[2] : addr) : a[3];
+        k[2] = c2 ? (c1 ? k[1] : key) : k[2];    a[2] = c2 ? (c1 ? a[1] : addr) : a[2];
+        k[1] = c1 ? (c0 ? k[0] : key) : k[1];    a[1] = c1 ? (c0 ? a[0] : addr) : a[1];
+        k[0] = c0 ? key : k[0];                  a[0] = c0 ? addr : a[0];
     }
 };
 
@@ -339,51 +335,96 @@ __device__ __forceinline__ unsigned long long shell_bits(int cqx, int cqy, int c
 }
 
 // Returns true when the shell result is final (then best holds the answer; count = number found).
+//
+// Two passes.  Pass 1 walks the <= 8 blocks of the shell and writes a per-thread work list of its occupied
+// cells into shared memory (s_idx = cell_tab index, s_gap = conservative squared distance from the query to
+// the cell's box): the cells of the 2x2x2 octant nearest the query go first (gap 0: always visited), the other
+// 19 after.  Pass 2 is ONE flat loop over that list: a cell whose box lies beyond the current fifth distance
+// is skipped without touching memory, otherwise its bucket (8 slots = one 128-byte line, plus overflow chain)
+// is scanned.  The flat loop keeps the lanes of a warp in step far better than nested block/cell loops.
+// s_idx / s_gap: [SHELL_CELLS][blockDim.x], this thread's column = threadIdx.x.
+constexpr int SHELL_CELLS = 27;
+
 __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits,
-                                                  Top5& best, int& count, unsigned& ncand) {
+                                                  Top5& best, int& count, unsigned& ncand,
+                                                  uint32_t* __restrict__ s_idx, float* __restrict__ s_gap, int tstride) {
     best.init();
     const int g = m.gshift;
-    const int cqx = voxel_key1(qx, m.ds) >> g, cqy = voxel_key1(qy, m.ds) >> g, cqz = voxel_key1(qz, m.ds) >> g;
-    // candidates above the bound never enter: the sentinel key of an empty rank is the bound itself
-    const unsigned long long bound_key = ((unsigned long long)max_sq_bits << 32) | 0xFFFFFFFFull;
-    unsigned long long worst = bound_key;   // key a candidate must beat (<=) to enter
-    int found = 0;
+    const int kx = voxel_key1(qx, m.ds), ky = voxel_key1(qy, m.ds), kz = voxel_key1(qz, m.ds);
+    const int cqx = kx >> g, cqy = ky >> g, cqz = kz >> g;
+    const float qabs = fmaxf(fabsf(qx), fmaxf(fabsf(qy), fabsf(qz)));
+    // per-axis squared gaps to the lower / upper neighbour cell (conservative, see cell_gap_sq) and the nearer side
+    const double edge = (double)m.cell_edge, slack = ((double)qabs + 2.0 * edge) * 4.8e-7;
+    float glo[3], ghi[3];
+    int side[3];
+    {
+        const float q3[3] = {qx, qy, qz};
+        const int c3[3] = {cqx, cqy, cqz};
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const double lo = (double)c3[a] * edge;
+            double dl = (double)q3[a] - lo, dh = (lo + edge) - (double)q3[a];
+            side[a] = (dl < dh) ? -1 : 1;
+            dl = fmax(fmax(dl, 0.0) * (1.0 - 1e-6) - slack, 0.0);
+            dh = fmax(fmax(dh, 0.0) * (1.0 - 1e-6) - slack, 0.0);
+            glo[a] = (float)(dl * dl * (1.0 - 2e-6));
+            ghi[a] = (float)(dh * dh * (1.0 - 2e-6));
+        }
+    }
+    // ---- pass 1: work list ------------------------------------------------------------------------------
+    int nA = 0, nB = 0;
     const int bx0 = (cqx - 1) >> 2, by0 = (cqy - 1) >> 2, bz0 = (cqz - 1) >> 2;
     const int nbx = ((cqx + 1) >> 2) - bx0, nby = ((cqy + 1) >> 2) - by0, nbz = ((cqz + 1) >> 2) - bz0;   // 0 or 1
-    for (int ix = 0; ix <= nbx; ++ix)
-        for (int iy = 0; iy <= nby; ++iy)
-            for (int iz = 0; iz <= nbz; ++iz) {
-                const int bx = bx0 + ix, by = by0 + iy, bz = bz0 + iz;
-                const int slot = dir_find(m, pack_block(bx, by, bz));
-                if (slot < 0) continue;
-                unsigned long long occ = __ldg(m.blk_mask + slot) & shell_bits(cqx, cqy, cqz, bx, by, bz);
-                while (occ) {
-                    const int off = __ffsll((long long)occ) - 1;
-                    occ &= occ - 1;
-                    uint32_t b = __ldg(m.cell_tab + (size_t)slot * 64 + off);
-                    while (b != NONE32) {
-                        float4 p[BUCKET_SLOTS];
+    for (int ib = 0; ib < 8; ++ib) {
+        const int ix = ib >> 2, iy = (ib >> 1) & 1, iz = ib & 1;
+        if (ix > nbx || iy > nby || iz > nbz) continue;
+        const int bx = bx0 + ix, by = by0 + iy, bz = bz0 + iz;
+        const int slot = dir_find(m, pack_block(bx, by, bz));
+        if (slot < 0) continue;
+        unsigned long long occ = __ldg(m.blk_mask + slot) & shell_bits(cqx, cqy, cqz, bx, by, bz);
+        while (occ) {
+            const int off = __ffsll((long long)occ) - 1;
+            occ &= occ - 1;
+            const int dx = bx * 4 + ((off >> 4) & 3) - cqx, dy = by * 4 + ((off >> 2) & 3) - cqy, dz = bz * 4 + (off & 3) - cqz;
+            const bool inA = (dx == 0 || dx == side[0]) && (dy == 0 || dy == side[1]) && (dz == 0 || dz == side[2]);
+            const float gap = (dx < 0 ? glo[0] : dx > 0 ? ghi[0] : 0.f) + (dy < 0 ? glo[1] : dy > 0 ? ghi[1] : 0.f) +
+                              (dz < 0 ? glo[2] : dz > 0 ? ghi[2] : 0.f);
+            const int pos = inA ? nA++ : (SHELL_CELLS - 1) - nB++;
+            s_idx[pos * tstride] = (uint32_t)slot * 64u + (uint32_t)off;
+            s_gap[pos * tstride] = inA ? 0.f : gap;
+        }
+    }
+    // ---- pass 2: flat loop ------------------------------------------------------------------------------
+    // candidates above the bound never enter: the sentinel key of an empty rank is the bound itself
+    const unsigned long long bound_key = ((unsigned long long)max_sq_bits << 32) | 0xFFFFFFFFull;
+    unsigned long long worst = bound_key;   // key a candidate must not exceed to enter
+    int found = 0;
+    const int total = nA + nB;
+    for (int t = 0; t < total; ++t) {
+        const int pos = (t < nA) ? t : SHELL_CELLS - 1 - (t - nA);
+        if (s_gap[pos * tstride] > __uint_as_float((uint32_t)(worst >> 32))) continue;
+        uint32_t b = __ldg(m.cell_tab + s_idx[pos * tstride]);
+        while (b != NONE32) {
+            float4 p[BUCKET_SLOTS];
 #pragma unroll
-                        for (int s = 0; s < BUCKET_SLOTS; ++s) p[s] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
-                        const uint32_t nxt = __ldg(m.bucket_next + b);
+            for (int s = 0; s < BUCKET_SLOTS; ++s) p[s] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
+            const uint32_t nxt = __ldg(m.bucket_next + b);
 #pragma unroll
-                        for (int s = 0; s < BUCKET_SLOTS; ++s) {
-                            const int pid = __float_as_int(p[s].w);
-                            if (pid < 0) continue;
-                            ++ncand;
-                            const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, p[s].x, p[s].y, p[s].z));
-                            const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
-                            if (key <= worst) {
-                                best.insert(key, b * BUCKET_SLOTS + s);
-                                if (++found >= 5) worst = best.k[4];
-                            }
-                        }
-                        b = nxt;
-                    }
+            for (int s = 0; s < BUCKET_SLOTS; ++s) {
+                const int pid = __float_as_int(p[s].w);
+                if (pid < 0) continue;
+                ++ncand;
+                const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, p[s].x, p[s].y, p[s].z));
+                const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
+                if (key <= worst) {
+                    best.insert(key, b * BUCKET_SLOTS + s);
+                    if (++found >= 5) worst = best.k[4];
                 }
             }
+            b = nxt;
+        }
+    }
     count = min(found, 5);
-    const float qabs = fmaxf(fabsf(qx), fmaxf(fabsf(qy), fabsf(qz)));
     const float cov = covered_sq(m.cell_edge, 1.f, qabs);
     const float max_sq = __uint_as_float(max_sq_bits);
     return (count == 5 && __uint_as_float((uint32_t)(best.k[4] >> 32)) <= cov) || (cov >= max_sq);
@@ -418,6 +459,15 @@ __device__ __forceinline__ unsigned long long cube_bits(int cqx, int cqy, int cq
     return m;
 }
 
+// conservative lower bound (double) of the squared distance from q to any point stored in cell (cx,cy,cz)
+__device__ __forceinline__ double cell_gap_sq(double edge, int cx, int cy, int cz, float qx, float qy, float qz, double slack) {
+    double g2 = 0.0, lo, d;
+    lo = (double)cx * edge; d = fmax(fmax(lo - (double)qx, (double)qx - (lo + edge)), 0.0); d = fmax(d * (1.0 - 1e-6) - slack, 0.0); g2 += d * d;
+    lo = (double)cy * edge; d = fmax(fmax(lo - (double)qy, (double)qy - (lo + edge)), 0.0); d = fmax(d * (1.0 - 1e-6) - slack, 0.0); g2 += d * d;
+    lo = (double)cz * edge; d = fmax(fmax(lo - (double)qz, (double)qz - (lo + edge)), 0.0); d = fmax(d * (1.0 - 1e-6) - slack, 0.0); g2 += d * d;
+    return g2 * (1.0 - 1e-6);
+}
+
 static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits, int lane,
                                             Cand& out, unsigned& ncand) {
     Top5 loc;
@@ -427,40 +477,62 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
     const float qabs = fmaxf(fabsf(qx), fmaxf(fabsf(qy), fabsf(qz)));
     const float max_sq = __uint_as_float(max_sq_bits);
     const unsigned long long bound_key = ((unsigned long long)max_sq_bits << 32) | 0xFFFFFFFFull;
-    unsigned long long lworst = bound_key;
+    unsigned long long lworst = bound_key;   // per lane: key a candidate must not exceed
+    double gworst = (double)max_sq;          // warp-uniform: squared distance beyond which a whole cell is skipped
     int lfound = 0;
+    const double edge = (double)m.cell_edge;
     for (int n = 1; n <= RING_MAX_CELLS; ++n) {
         const int p = (n == 1) ? -1 : n - 1;
         const int bx0 = (cqx - n) >> 2, by0 = (cqy - n) >> 2, bz0 = (cqz - n) >> 2;
         const int nbx = ((cqx + n) >> 2) - bx0 + 1, nby = ((cqy + n) >> 2) - by0 + 1, nbz = ((cqz + n) >> 2) - bz0 + 1;
         const int nb = nbx * nby * nbz;
-        for (int bi = lane; bi < nb; bi += 32) {
-            const int bx = bx0 + bi / (nby * nbz), by = by0 + (bi / nbz) % nby, bz = bz0 + bi % nbz;
-            unsigned long long want = cube_bits(cqx, cqy, cqz, bx, by, bz, n) & ~cube_bits(cqx, cqy, cqz, bx, by, bz, p);
-            if (!want) continue;
-            const int slot = dir_find(m, pack_block(bx, by, bz));
-            if (slot < 0) continue;
-            unsigned long long occ = __ldg(m.blk_mask + slot) & want;
-            while (occ) {
-                const int off = __ffsll((long long)occ) - 1;
-                occ &= occ - 1;
-                uint32_t b = __ldg(m.cell_tab + (size_t)slot * 64 + off);
-                while (b != NONE32) {
-                    const uint32_t nxt = __ldg(m.bucket_next + b);
-#pragma unroll 2
-                    for (int s = 0; s < BUCKET_SLOTS; ++s) {
-                        const float4 pt = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
-                        const int pid = __float_as_int(pt.w);
-                        if (pid < 0) continue;
-                        ++ncand;
-                        const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, pt.x, pt.y, pt.z));
-                        const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
-                        if (key <= lworst) {
-                            loc.insert(key, b * BUCKET_SLOTS + s);
-                            if (++lfound >= 5 && loc.k[4] < lworst) lworst = loc.k[4];
+        const double slack = ((double)qabs + (double)(n + 1) * edge) * 4.8e-7;
+        for (int base = 0; base < nb; base += 32) {
+            // stage 1: one block per lane -> directory slot and the occupancy bits of its cells in ring n
+            const int bi = base + lane;
+            int slot = -1, bx = 0, by = 0, bz = 0;
+            unsigned long long occ = 0;
+            if (bi < nb) {
+                bx = bx0 + bi / (nby * nbz); by = by0 + (bi / nbz) % nby; bz = bz0 + bi % nbz;
+                const unsigned long long want = cube_bits(cqx, cqy, cqz, bx, by, bz, n) & ~cube_bits(cqx, cqy, cqz, bx, by, bz, p);
+                if (want) {
+                    slot = dir_find(m, pack_block(bx, by, bz));
+                    if (slot >= 0) occ = __ldg(m.blk_mask + slot) & want;
+                }
+            }
+            // stage 2: the cells of each non-empty block are dealt out one per lane
+            unsigned has = __ballot_sync(FULL, occ != 0ull);
+            while (has) {
+                const int o = __ffs(has) - 1;
+                has &= has - 1;
+                const int so = __shfl_sync(FULL, slot, o);
+                const unsigned olo = __shfl_sync(FULL, (unsigned)occ, o), ohi = __shfl_sync(FULL, (unsigned)(occ >> 32), o);
+                const int obx = __shfl_sync(FULL, bx, o), oby = __shfl_sync(FULL, by, o), obz = __shfl_sync(FULL, bz, o);
+                const int clo = __popc(olo), c = clo + __popc(ohi);
+                for (int j = lane; j < c; j += 32) {
+                    const int off = (j < clo) ? (int)__fns(olo, 0, j + 1) : 32 + (int)__fns(ohi, 0, j - clo + 1);
+                    const int cx = obx * 4 + ((off >> 4) & 3), cy = oby * 4 + ((off >> 2) & 3), cz = obz * 4 + (off & 3);
+                    if (cell_gap_sq(edge, cx, cy, cz, qx, qy, qz, slack) > gworst) continue;
+                    uint32_t b = __ldg(m.cell_tab + (size_t)so * 64 + off);
+                    while (b != NONE32) {
+                        float4 pt[BUCKET_SLOTS];
+#pragma unroll
+                        for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) pt[s2] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s2);
+                        const uint32_t nxt = __ldg(m.bucket_next + b);
+#pragma unroll
+                        for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) {
+                            const int pid = __float_as_int(pt[s2].w);
+                            if (pid < 0) continue;
+                            ++ncand;
+                            const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, pt[s2].x, pt[s2].y, pt[s2].z));
+                            const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
+                            if (key <= lworst) {
+                                loc.insert(key, b * BUCKET_SLOTS + s2);
+                                if (++lfound >= 5 && loc.k[4] < lworst) lworst = loc.k[4];
+                            }
                         }
+                        b = nxt;
                     }
-                    b = nxt;
                 }
             }
         }
@@ -491,6 +563,7 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
         if (count == 5) {
             const unsigned long long gk = ((unsigned long long)d5 << 32) | i5;
             if (gk < lworst) lworst = gk;
+            gworst = fmin(gworst, (double)__uint_as_float(d5));
         }
     }
     // not final within RING_MAX_CELLS cells: the generic search (block rings + directory sweep)
