@@ -52,5 +52,18 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def build_host_test(force=False):
+    """Compile the C++ caller of the drop-in classes (tests/cpp/test_dropin.cpp) against the library."""
+    src = os.path.join(HERE, "..", "tests", "cpp", "test_dropin.cpp")
+    out = os.path.join(OBJ, "test_dropin")
+    deps = [src, LIB] + [os.path.join(HERE, "host", f) for f in os.listdir(os.path.join(HERE, "host"))]
+    if not force and os.path.exists(out) and os.path.getmtime(out) >= _newest(deps):
+        return out
+    os.makedirs(OBJ, exist_ok=True)
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-I" + os.path.join(HERE, "host"), "-I" + os.path.join(HERE, "..", "include"),
+                           src, "-o", out, "-L" + HERE, "-lflivo_b200", "-Wl,-rpath," + HERE, "-pthread"])
+    return out
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
