@@ -211,8 +211,8 @@ def run_flivo(args, rank, world_size, local_rank):
         dist.broadcast_object_list(uid, src=0)
         F.comm_init(uid[0], rank, world_size)
         for s in scans:
-            n = len(s["body"])
-            lo, hi = rank * n // world_size, (rank + 1) * n // world_size
+            import importlib
+            lo, hi = importlib.import_module("fast_livo_noted_b200.sharding").shard_range(len(s["body"]), rank, world_size)
             s["body"] = s["body"][lo:hi].contiguous()
     # device-resident scans (float4) and the reference-layout host copies (48-byte PointXYZINormal AoS) for e2e
     dev_scans, host_scans, host_xyz = [], [], []

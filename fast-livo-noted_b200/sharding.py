@@ -1,0 +1,49 @@
+"""Host-side logic of the multi-GPU modes.  No data-path code lives here: the kernels and the
+NCCL allgather are inside libflivo_b200.so (flivo_comm_init / flivo_iekf_update).
+
+  replay mode (BASELINE config 4): independent scan sequences are dealt round-robin to ranks; no collective.
+  sharded mode (config 5): every rank holds the whole map and a contiguous block of the (Morton-ordered) scan;
+      per trip each rank reduces its block to 96 doubles (78 upper H^T H terms, 12 H^T z, res_sum, n_eff, pad),
+      the blocks are all-gathered and summed IN RANK ORDER on every rank, so all replicas of the on-device
+      solve see bit-identical normal equations (no floating-point reduction order depends on the fabric).
+"""
+import numpy as np
+
+NTERMS, PSTRIDE = 92, 96
+
+
+def shard_range(n, rank, world_size):
+    """Contiguous block [lo, hi) of a scan of n points owned by `rank` (same formula as bench.py / the C++ caller)."""
+    return rank * n // world_size, (rank + 1) * n // world_size
+
+
+def sequences_of_rank(n_sequences, rank, world_size):
+    """Round-robin partition of independent scan sequences (config 4): sequence s -> rank s mod G."""
+    return list(range(rank, n_sequences, world_size))
+
+
+def pack_block(HTH, HTz, res_sum, n_eff):
+    """12x12 H^T H, 12 H^T z, residual sum and effective-row count -> the 96-double record the kernels exchange."""
+    b = np.zeros(PSTRIDE)
+    H = np.asarray(HTH, float).reshape(12, 12)
+    b[:78] = H[np.triu_indices(12)]
+    b[78:90] = HTz
+    b[90], b[91] = res_sum, n_eff
+    return b
+
+
+def unpack_block(b):
+    H = np.zeros((12, 12))
+    iu = np.triu_indices(12)
+    H[iu] = b[:78]
+    H = H + np.triu(H, 1).T
+    return H, b[78:90].copy(), float(b[90]), int(b[91])
+
+
+def combine_rank_blocks(blocks):
+    """Sum of the gathered per-rank records in rank order (SOLVE_PHASE_FROM_RANKS in csrc/solve.cu)."""
+    blocks = np.asarray(blocks, float).reshape(-1, PSTRIDE)
+    s = np.zeros(PSTRIDE)
+    for r in range(blocks.shape[0]):
+        s = s + blocks[r]
+    return s
