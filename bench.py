@@ -198,6 +198,7 @@ def run_flivo(args, rank, world_size, local_rank):
     npd = 18 if args.mode == 1 else 23
     P0 = np.eye(npd) * 1e-4
     cfg = pkg.make_cfg(mode=args.mode, max_iter=MAX_ITER, laser_point_cov=LASER_POINT_COV, force_search=bool(args.force_search))
+    cfg_prof = pkg.make_cfg(mode=args.mode, max_iter=MAX_ITER, laser_point_cov=LASER_POINT_COV, force_search=bool(args.force_search), profile=True)
 
     F = pkg.Flivo(device=local_rank, downsample_size=ds, cell_ratio=args.cell_ratio, initial_points=n_map, sort_scan=bool(args.sort_scan))
     wxyz_host = world["points"].cpu().numpy()
@@ -264,12 +265,7 @@ def run_flivo(args, rank, world_size, local_rank):
         ev[k][1].record(ext)
         trips_total += rep.trips
         launches += rep.kernel_launches + (4 if args.sort_scan else 1)
-        st = F.stats()
-        for t in range(rep.trips):
-            (fused_search_ms if st.last_trip_searched[t] else fused_reuse_ms).append(st.last_fused_ms[t])
-            solve_ms.append(st.last_solve_ms[t])
         last = (k % S, x, P, rep)
-        far_q, cand = int(st.last_far_queries), int(st.last_candidates)
     barrier()
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1)
@@ -282,6 +278,18 @@ def run_flivo(args, rank, world_size, local_rank):
     else:
         work = float(tt[1])
     value = work / (dev_ms * 1e-3)
+
+    # ---- per-trip kernel durations for the roofline: same steps in profile mode (per-trip CUDA events, no graph) ----
+    for k in range(min(args.steps, 8)):
+        flush.zero_()
+        torch.cuda.synchronize()
+        F.scan_set_device(dev_scans[k % S].data_ptr(), dev_scans[k % S].shape[0])
+        _, _, repp = F.iekf_update(pkg.State.from_array(scans[k % S]["x_prior"]), P0, cfg_prof)
+        st = F.stats()
+        for t in range(repp.trips):
+            (fused_search_ms if st.last_trip_searched[t] else fused_reuse_ms).append(st.last_fused_ms[t])
+            solve_ms.append(st.last_solve_ms[t])
+        far_q, cand = int(st.last_far_queries), int(st.last_candidates)
 
     # ---- e2e: host buffers through the C ABI, wall clock, H2D + D2H inside ----
     for w in range(min(args.warmup, 2)):

@@ -70,7 +70,7 @@ class Options(C.Structure):
 
 class Cfg(C.Structure):
     _fields_ = [("mode", C.c_int32), ("max_iter", C.c_int32), ("laser_point_cov", C.c_double),
-                ("limit", C.c_double * 23), ("force_search", C.c_int32), ("reserved", C.c_int32)]
+                ("limit", C.c_double * 23), ("force_search", C.c_int32), ("flags", C.c_int32)]
 
 
 class Report(C.Structure):
@@ -153,9 +153,13 @@ def _ptr(a):
     return None if a is None else a.ctypes.data
 
 
-def make_cfg(mode=MODE_V3, max_iter=4, laser_point_cov=0.001, limit=None, force_search=False):
+CFG_PROFILE = 1
+
+
+def make_cfg(mode=MODE_V3, max_iter=4, laser_point_cov=0.001, limit=None, force_search=False, profile=False):
     c = Cfg()
     c.mode, c.max_iter, c.laser_point_cov, c.force_search = mode, max_iter, laser_point_cov, int(force_search)
+    c.flags = CFG_PROFILE if profile else 0
     lim = np.full(23, 0.001) if limit is None else np.asarray(limit, dtype=np.float64)
     c.limit[:] = list(lim)
     return c

@@ -47,6 +47,18 @@ struct NcclApi {
 static NcclApi g_nccl;
 constexpr int NCCL_DOUBLE = 8;  // ncclFloat64 (nccl.h ncclDataType_t)
 
+// Device block of one update.  [job .. x] is the H2D prefix of a call, [x .. stats] the D2H range.
+struct DevBlock {
+    Job job;
+    double P_prop[23 * 23];
+    double x[36];
+    double P_out[23 * 23];
+    Ctl ctl;
+    SearchStats stats;
+    double x_prop[36];
+    double sum[PSTRIDE];
+};
+
 struct flivo_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -60,8 +72,6 @@ struct flivo_ctx {
     cudaEvent_t stage_ev = nullptr;   // last H2D copy out of h_stage
     bool stage_pending = false;
     double* h_small = nullptr;      // pinned: 36 state + 36 + 529 P + ... (2048 doubles)
-    Ctl* h_ctl = nullptr;           // pinned mirror
-    SearchStats* h_stats = nullptr; // pinned mirror
     // generic device staging for map / knn inputs
     float4* d_stage = nullptr;
     size_t d_stage_n = 0;
@@ -87,9 +97,16 @@ struct flivo_ctx {
     void* d_out = nullptr;          // un-permute scratch for optional outputs
     size_t d_out_bytes = 0;
     // loop state
-    Ctl* d_ctl = nullptr;
+    DevBlock* d_blk = nullptr;      // job + state + P + ctl + stats in one allocation (see DevBlock)
+    DevBlock* h_blk = nullptr;      // pinned mirror
+    Ctl* d_ctl = nullptr;           // the pointers below point into d_blk
     SearchStats* d_stats = nullptr;
     double *d_x = nullptr, *d_xprop = nullptr, *d_Pprop = nullptr, *d_Pout = nullptr, *d_sum = nullptr, *d_rank_blocks = nullptr;
+    // captured launch sequence of one update (CUDA graph), re-captured only when a kernel parameter changes
+    cudaGraphExec_t graph_exec = nullptr;
+    FusedParams graph_P{};
+    SolveParams graph_S{};
+    int graph_search_grid = 0, graph_fused_grid = 0, graph_trips = 0, graph_churn = 0;
     cudaEvent_t ev[2 * MAX_TRIPS + 2] = {};
     flivo_stats stats{};
     // multi-GPU
@@ -258,19 +275,14 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     if (rc) return map_rc(ctx, rc);
     upload_term_table();
     CKC(cudaGetLastError());
-    CKC(cudaMalloc(&ctx->d_ctl, sizeof(Ctl)));
-    CKC(cudaMalloc(&ctx->d_stats, sizeof(SearchStats)));
-    CKC(cudaMemsetAsync(ctx->d_ctl, 0, sizeof(Ctl), ctx->stream));
-    CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
-    CKC(cudaMalloc(&ctx->d_x, 36 * sizeof(double)));
-    CKC(cudaMalloc(&ctx->d_xprop, 36 * sizeof(double)));
-    CKC(cudaMalloc(&ctx->d_Pprop, 23 * 23 * sizeof(double)));
-    CKC(cudaMalloc(&ctx->d_Pout, 23 * 23 * sizeof(double)));
-    CKC(cudaMalloc(&ctx->d_sum, PSTRIDE * sizeof(double)));
-    CKC(cudaMemsetAsync(ctx->d_sum, 0, PSTRIDE * sizeof(double), ctx->stream));
+    CKC(cudaMalloc(&ctx->d_blk, sizeof(DevBlock)));
+    CKC(cudaMemsetAsync(ctx->d_blk, 0, sizeof(DevBlock), ctx->stream));
+    CKC(cudaMallocHost(&ctx->h_blk, sizeof(DevBlock)));
+    memset(ctx->h_blk, 0, sizeof(DevBlock));
+    ctx->d_ctl = &ctx->d_blk->ctl; ctx->d_stats = &ctx->d_blk->stats;
+    ctx->d_x = ctx->d_blk->x; ctx->d_xprop = ctx->d_blk->x_prop; ctx->d_Pprop = ctx->d_blk->P_prop; ctx->d_Pout = ctx->d_blk->P_out;
+    ctx->d_sum = ctx->d_blk->sum;
     CKC(cudaMallocHost(&ctx->h_small, 2048 * sizeof(double)));
-    CKC(cudaMallocHost(&ctx->h_ctl, sizeof(Ctl)));
-    CKC(cudaMallocHost(&ctx->h_stats, sizeof(SearchStats)));
     for (auto& e : ctx->ev) CKC(cudaEventCreate(&e));
     CKC(cudaEventCreateWithFlags(&ctx->stage_ev, cudaEventDisableTiming));
     CKC(cudaStreamSynchronize(ctx->stream));
@@ -311,12 +323,11 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
     ctx->map.release();
     free_scan(ctx);
-    cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_ctl); cudaFree(ctx->d_stats); cudaFree(ctx->d_x); cudaFree(ctx->d_xprop);
-    cudaFree(ctx->d_Pprop); cudaFree(ctx->d_Pout); cudaFree(ctx->d_sum); cudaFree(ctx->d_rank_blocks);
+    if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
+    cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_rank_blocks);
+    if (ctx->h_blk) cudaFreeHost(ctx->h_blk);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
-    if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
-    if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->stage_ev) cudaEventDestroy(ctx->stage_ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -424,10 +435,10 @@ static bool bound_bits(double max_dist, uint32_t* bits) {
 }
 
 static int fetch_stats(flivo_ctx* ctx) {
-    CKC(cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(SearchStats), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaMemcpyAsync(&ctx->h_blk->stats, ctx->d_stats, sizeof(SearchStats), cudaMemcpyDeviceToHost, ctx->stream));
     CKC(cudaStreamSynchronize(ctx->stream));
-    ctx->stats.last_far_queries = (int64_t)ctx->h_stats->far_queries;
-    ctx->stats.last_candidates = (int64_t)ctx->h_stats->candidates;
+    ctx->stats.last_far_queries = (int64_t)ctx->h_blk->stats.far_queries;
+    ctx->stats.last_candidates = (int64_t)ctx->h_blk->stats.candidates;
     return FLIVO_OK;
 }
 
@@ -550,22 +561,39 @@ extern "C" int flivo_scan_set_device(flivo_ctx* ctx, const void* dev_xyzw, size_
     return finish_scan(ctx, (const float4*)dev_xyzw, n, true);
 }
 
-static FusedParams make_fused(flivo_ctx* ctx, int mode, int force_search, uint32_t max_sq_bits) {
-    FusedParams P{};
+static FusedParams make_fused(flivo_ctx* ctx) {
+    FusedParams P;
+    memset(&P, 0, sizeof(P));   // padding too: the captured-graph cache compares parameter blocks bytewise
     P.map = ctx->map.view();
     P.body = ctx->d_body;
-    P.n = (int)ctx->scan_n;
+    P.job = &ctx->d_blk->job;
     P.state = ctx->d_x;
     P.near = ctx->d_near; P.near_meta = ctx->d_near_meta; P.sel = ctx->d_sel; P.eff = ctx->d_eff;
     P.normvec = ctx->d_normvec; P.world = ctx->d_world;
     P.partials = ctx->d_partials; P.gpartials = ctx->d_gpartials; P.group_cnt = ctx->d_group_cnt; P.far_list = ctx->d_far_list;
     P.ctl = ctx->d_ctl; P.stats = ctx->d_stats;
-    P.mode = mode; P.force_search = force_search; P.max_sq_bits = max_sq_bits;
-    P.units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
-    P.groups = (P.units + GROUP_UNITS - 1) / GROUP_UNITS;
     return P;
 }
-static int fused_grid(flivo_ctx* ctx, int units) { return std::max(1, std::min(units, ctx->sm_count * 8)); }
+// per-call scalars -> the pinned mirror of the device block (copied with the state by the caller)
+static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, double R, const double* limit23, uint32_t max_sq_bits) {
+    Job& j = ctx->h_blk->job;
+    j.n = (int)ctx->scan_n;
+    j.units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
+    j.groups = (j.units + GROUP_UNITS - 1) / GROUP_UNITS;
+    j.mode = mode; j.max_iter = max_iter; j.force_search = force_search; j.nranks = ctx->nranks; j.max_sq_bits = max_sq_bits;
+    j.R = R;
+    for (int i = 0; i < 23; ++i) j.limit[i] = limit23 ? limit23[i] : 0.001;
+}
+// launch grids are rounded up to capacity buckets so that scans of similar size share one captured graph;
+// surplus CTAs see i >= job->n (k_search) or an exhausted unit counter (k_fused) and leave at once
+static int search_grid(flivo_ctx* ctx) {
+    const int ctas = (int)((ctx->scan_n + 127) / 128);
+    return ((ctas + 255) / 256) * 256;
+}
+static int fused_grid(flivo_ctx* ctx) {
+    const int units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
+    return std::max(1, std::min(((units + 255) / 256) * 256, ctx->sm_count * 8));
+}
 // the fused path searches with the reference's own far-neighbour gate (pointSearchSqDis[4] > 5, src/laser_mapping.cpp:518)
 // as the distance bound: a point whose 5th neighbour lies beyond it is masked either way
 static uint32_t gate_bits() { float f = 5.0f; uint32_t b; memcpy(&b, &f, 4); return b; }
@@ -606,16 +634,18 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
     NEED(st && HTH && HTz, FLIVO_E_ARG, "null state / outputs");
     NEED(mode == FLIVO_MODE_V3 || mode == FLIVO_MODE_V1, FLIVO_E_ARG, "bad mode");
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
-    memcpy(ctx->h_small, st, sizeof(flivo_state));
-    CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_small, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
+    fill_job(ctx, mode, 1, 0, 0.001, nullptr, gate_bits());
+    memcpy(ctx->h_blk->x, st, sizeof(flivo_state));
+    CKC(cudaMemcpyAsync(&ctx->d_blk->job, &ctx->h_blk->job, sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
+    CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_blk->x, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
     k_ctl_set<<<1, 32, 0, ctx->stream>>>(ctx->d_ctl, do_search ? 1 : 0);
     if (do_search) CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
-    FusedParams P = make_fused(ctx, mode, 0, gate_bits());
-    if (do_search) launch_search(P, ctx->sm_count * 8, ctx->stream);
-    launch_fused(P, fused_grid(ctx, P.units), ctx->stream);
+    FusedParams P = make_fused(ctx);
+    if (do_search) launch_search(P, search_grid(ctx), ctx->sm_count * 8, ctx->stream);
+    launch_fused(P, fused_grid(ctx), ctx->stream);
     SolveParams S{};
-    S.gpartials = ctx->d_gpartials; S.groups = P.groups; S.phase = SOLVE_PHASE_REDUCE_ONLY; S.mode = mode;
-    S.sum_out = ctx->d_sum; S.ctl = ctx->d_ctl; S.nranks = 1;
+    S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job; S.phase = SOLVE_PHASE_REDUCE_ONLY;
+    S.sum_out = ctx->d_sum; S.ctl = ctx->d_ctl;
     launch_solve(S, ctx->stream);
     CKC(cudaGetLastError());
     double* hs = ctx->h_small + 64;
@@ -675,30 +705,29 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
     const int np = cfg->mode == FLIVO_MODE_V1 ? 18 : 23;
     const int trips = cfg->max_iter + 1;  // loop index -1 .. max_iter-1
+    const bool timed = (cfg->flags & FLIVO_CFG_PROFILE) != 0;   // per-trip events, plain launches (no graph)
     cudaStream_t s = ctx->stream;
-    double* h = ctx->h_small;
-    memcpy(h, inout, sizeof(flivo_state));
-    memcpy(h + 36, Pm, sizeof(double) * np * np);
+    DevBlock* h = ctx->h_blk;
+    fill_job(ctx, cfg->mode, cfg->max_iter, cfg->force_search, cfg->laser_point_cov, cfg->limit, gate_bits());
+    memcpy(h->x, inout, sizeof(flivo_state));
+    memset(h->P_prop, 0, sizeof(h->P_prop));
+    memcpy(h->P_prop, Pm, sizeof(double) * np * np);
     CKC(cudaEventRecord(ctx->ev[0], s));
-    CKC(cudaMemcpyAsync(ctx->d_x, h, sizeof(flivo_state), cudaMemcpyHostToDevice, s));
-    CKC(cudaMemcpyAsync(ctx->d_xprop, ctx->d_x, sizeof(flivo_state), cudaMemcpyDeviceToDevice, s));
-    CKC(cudaMemcpyAsync(ctx->d_Pprop, h + 36, sizeof(double) * np * np, cudaMemcpyHostToDevice, s));
-    CKC(cudaMemcpyAsync(ctx->d_Pout, ctx->d_Pprop, sizeof(double) * np * np, cudaMemcpyDeviceToDevice, s));
-    launch_ctl_reset(ctx->d_ctl, ctx->d_stats, s);
-    FusedParams P = make_fused(ctx, cfg->mode, cfg->force_search, gate_bits());
-    SolveParams S{};
-    S.gpartials = ctx->d_gpartials; S.groups = P.groups; S.mode = cfg->mode; S.max_iter = cfg->max_iter;
-    S.force_search = cfg->force_search; S.nranks = ctx->nranks; S.R = cfg->laser_point_cov;
-    for (int i = 0; i < 23; ++i) S.limit[i] = cfg->limit[i];
+    CKC(cudaMemcpyAsync(ctx->d_blk, h, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s));   // job + P_prop + x
+    launch_ctl_reset(ctx->d_blk->x, ctx->d_blk->x_prop, ctx->d_blk->P_prop, ctx->d_blk->P_out, ctx->d_ctl, ctx->d_stats, s);
+    FusedParams P = make_fused(ctx);
+    SolveParams S;
+    memset(&S, 0, sizeof(S));
+    S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job;
     S.x = ctx->d_x; S.x_prop = ctx->d_xprop; S.P_prop = ctx->d_Pprop; S.P_out = ctx->d_Pout;
     S.sum_out = ctx->d_sum; S.rank_blocks = ctx->d_rank_blocks; S.ctl = ctx->d_ctl;
-    const int grid = fused_grid(ctx, P.units);
+    const int sgrid = search_grid(ctx), fgrid = fused_grid(ctx), far_grid = ctx->sm_count * 8;
     int launches = 1;
-    for (int t = 0; t < trips; ++t) {
-        CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
-        launch_search(P, ctx->sm_count * 8, s);   // both kernels exit at once on re-use trips
-        launch_fused(P, grid, s);
-        CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
+    auto launch_trip = [&](int t, bool with_events) -> int {
+        if (with_events) CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
+        launch_search(P, sgrid, far_grid, s);   // both kernels exit at once on re-use trips
+        launch_fused(P, fgrid, s);
+        if (with_events) CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
         if (ctx->comm) {
             S.phase = SOLVE_PHASE_REDUCE_ONLY;
             launch_solve(S, s);
@@ -712,23 +741,58 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
             launch_solve(S, s);
             launches += 4;
         }
+        return FLIVO_OK;
+    };
+    bool use_graph = !timed && !ctx->comm;
+    if (use_graph) {
+        // the sequence depends only on (P, S, grids, trips): replay the captured graph unless one of them changed
+        S.phase = SOLVE_PHASE_FULL;
+        const bool same = ctx->graph_exec && memcmp(&P, &ctx->graph_P, sizeof(P)) == 0 && memcmp(&S, &ctx->graph_S, sizeof(S)) == 0 &&
+                          sgrid == ctx->graph_search_grid && fgrid == ctx->graph_fused_grid && trips == ctx->graph_trips;
+        if (!same) {
+            if (++ctx->graph_churn > 3) {
+                use_graph = false;   // parameters keep changing (e.g. a new external scan pointer every call): plain launches
+            } else {
+                if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
+                cudaGraph_t g = nullptr;
+                CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+                int rc = FLIVO_OK;
+                for (int t = 0; t < trips && rc == FLIVO_OK; ++t) rc = launch_trip(t, false);
+                cudaError_t ce = cudaStreamEndCapture(s, &g);
+                if (rc != FLIVO_OK) { if (g) cudaGraphDestroy(g); return rc; }
+                if (ce != cudaSuccess) { ctx->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
+                ce = cudaGraphInstantiate(&ctx->graph_exec, g, 0);
+                cudaGraphDestroy(g);
+                if (ce != cudaSuccess) { ctx->graph_exec = nullptr; ctx->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
+                ctx->graph_P = P; ctx->graph_S = S; ctx->graph_search_grid = sgrid; ctx->graph_fused_grid = fgrid; ctx->graph_trips = trips;
+                launches = 1;
+            }
+        } else {
+            ctx->graph_churn = 0;
+        }
+    }
+    if (use_graph) {
+        CKC(cudaGraphLaunch(ctx->graph_exec, s));
+        launches = 1 + trips * 4;
+    } else {
+        launches = 1;
+        for (int t = 0; t < trips; ++t) { int rc = launch_trip(t, timed); if (rc != FLIVO_OK) return rc; }
     }
     CKC(cudaGetLastError());
     CKC(cudaEventRecord(ctx->ev[1 + 2 * trips], s));
-    CKC(cudaMemcpyAsync(h, ctx->d_x, sizeof(flivo_state), cudaMemcpyDeviceToHost, s));
-    CKC(cudaMemcpyAsync(h + 36, ctx->d_Pout, sizeof(double) * np * np, cudaMemcpyDeviceToHost, s));
-    CKC(cudaMemcpyAsync(ctx->h_ctl, ctx->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
-    CKC(cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(SearchStats), cudaMemcpyDeviceToHost, s));
+    CKC(cudaMemcpyAsync(h->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s));   // x, P_out, ctl, stats
     CKC(cudaStreamSynchronize(s));
-    memcpy(inout, h, sizeof(flivo_state));
-    memcpy(Pm, h + 36, sizeof(double) * np * np);
-    const Ctl& c = *ctx->h_ctl;
-    ctx->stats.last_far_queries = (int64_t)ctx->h_stats->far_queries;
-    ctx->stats.last_candidates = (int64_t)ctx->h_stats->candidates;
+    memcpy(inout, h->x, sizeof(flivo_state));
+    memcpy(Pm, h->P_out, sizeof(double) * np * np);
+    const Ctl& c = h->ctl;
+    ctx->stats.last_far_queries = (int64_t)h->stats.far_queries;
+    ctx->stats.last_candidates = (int64_t)h->stats.candidates;
     for (int t = 0; t < 16; ++t) { ctx->stats.last_fused_ms[t] = 0.f; ctx->stats.last_solve_ms[t] = 0.f; ctx->stats.last_trip_searched[t] = 0; }
     for (int t = 0; t < trips && t < 16; ++t) {
-        cudaEventElapsedTime(&ctx->stats.last_fused_ms[t], ctx->ev[1 + 2 * t], ctx->ev[2 + 2 * t]);
-        cudaEventElapsedTime(&ctx->stats.last_solve_ms[t], ctx->ev[2 + 2 * t], ctx->ev[3 + 2 * t]);
+        if (timed) {
+            cudaEventElapsedTime(&ctx->stats.last_fused_ms[t], ctx->ev[1 + 2 * t], ctx->ev[2 + 2 * t]);
+            cudaEventElapsedTime(&ctx->stats.last_solve_ms[t], ctx->ev[2 + 2 * t], ctx->ev[3 + 2 * t]);
+        }
         ctx->stats.last_trip_searched[t] = t < c.trips ? c.trip_searched[t] : 0;
     }
     if (rep) {
@@ -748,8 +812,8 @@ extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t
     if (n_added) *n_added = 0;
     NEED(st, FLIVO_E_ARG, "null state");
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
-    memcpy(ctx->h_small, st, sizeof(flivo_state));
-    CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_small, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
+    memcpy(ctx->h_blk->x, st, sizeof(flivo_state));
+    CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_blk->x, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
     // Add_Points is order dependent only through ties; keep the caller's order (batch index = insertion id order)
     const float4* src = ctx->scan_sorted ? ctx->d_body_in : ctx->d_body;
     if (ctx->scan_sorted && ctx->scan_external) {

@@ -195,7 +195,8 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
 
     Ctl* ctl = P.ctl;
     if (ctl->stopped) return;
-    const bool search = (ctl->search != 0) || (P.force_search != 0);
+    const int n_pts = P.job->n, n_units = P.job->units, mode = P.job->mode;
+    const bool search = (ctl->search != 0) || (P.job->force_search != 0);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 36) s_state[threadIdx.x] = P.state[threadIdx.x];
     __syncthreads();
@@ -209,10 +210,10 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         if (threadIdx.x == 0) s_unit = atomicAdd(&ctl->unit_counter, 1u);
         __syncthreads();
         const unsigned int unit = s_unit;
-        if (unit >= (unsigned)P.units) break;
+        if (unit >= (unsigned)n_units) break;
         const int base = unit * UNIT_POINTS + warp * 32;
         const int i = base + lane;
-        const bool have = i < P.n;
+        const bool have = i < n_pts;
 
         // ---- a1: world transform --------------------------------------------------------------------
         float4 pb = have ? __ldg(P.body + i) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -241,7 +242,7 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
 
         // ---- a3..a5: gates and plane -----------------------------------------------------------------
         bool sel;
-        if (P.mode == 1) sel = true;                        // V1: vector<bool>(n, true) each call (:490)
+        if (mode == 1) sel = true;                        // V1: vector<bool>(n, true) each call (:490)
         else sel = have && (P.sel[i] != 0);                 // V3: persistent flag (origin:963)
         const bool have5 = have && ncnt >= 5;
         if (search) sel = have5 && !(d5 > 5.f);             // pointSearchSqDis[4] > 5 ? false : true (:518)
@@ -329,7 +330,7 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         __syncthreads();
         if (threadIdx.x == 0) {
             unsigned int g = unit / GROUP_UNITS;
-            unsigned int gsize = min((unsigned)GROUP_UNITS, (unsigned)P.units - g * GROUP_UNITS);
+            unsigned int gsize = min((unsigned)GROUP_UNITS, (unsigned)n_units - g * GROUP_UNITS);
             unsigned int old = atomicAdd(P.group_cnt + g, 1u);
             s_last = (old == gsize - 1) ? 1 : 0;
         }
@@ -337,7 +338,7 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         if (s_last) {
             __threadfence();
             unsigned int g = unit / GROUP_UNITS;
-            unsigned int u0 = g * GROUP_UNITS, u1 = min(u0 + GROUP_UNITS, (unsigned)P.units);
+            unsigned int u0 = g * GROUP_UNITS, u1 = min(u0 + GROUP_UNITS, (unsigned)n_units);
             if (threadIdx.x < NTERMS) {
                 double s = 0.0;
                 for (unsigned int u = u0; u < u1; ++u) s += __ldcg(P.partials + (size_t)u * PSTRIDE + threadIdx.x);
@@ -371,12 +372,13 @@ __global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
     __shared__ uint32_t s_idx[SHELL_CELLS * SEARCH_THREADS];   // per-thread work lists of thread_knn5_shell
     __shared__ float s_gap[SHELL_CELLS * SEARCH_THREADS];
     Ctl* ctl = P.ctl;
-    if (ctl->stopped || !(ctl->search != 0 || P.force_search != 0)) return;
+    if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
     if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * SEARCH_THREADS + threadIdx.x;
-    const bool have = i < P.n;
+    const bool have = i < P.job->n;
+    const uint32_t max_sq_bits = P.job->max_sq_bits;
     unsigned nc = 0;
     bool fin = true;
     if (have) {
@@ -384,7 +386,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
         world_of(s_state, __ldg(P.body + i), wx, wy, wz);
         Top5 best;
         int cnt = 0;
-        fin = thread_knn5_shell(P.map, wx, wy, wz, P.max_sq_bits, best, cnt, nc, s_idx + threadIdx.x, s_gap + threadIdx.x, SEARCH_THREADS);
+        fin = thread_knn5_shell(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, s_idx + threadIdx.x, s_gap + threadIdx.x, SEARCH_THREADS);
         if (fin) {
 #pragma unroll
             for (int r = 0; r < 5; ++r) {
@@ -415,9 +417,10 @@ __global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
 __global__ void __launch_bounds__(128) k_far(FusedParams P) {
     __shared__ double s_state[24];
     Ctl* ctl = P.ctl;
-    if (ctl->stopped || !(ctl->search != 0 || P.force_search != 0)) return;
+    if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
     const unsigned nfar = ctl->far_count;
     if (nfar == 0) return;
+    const uint32_t max_sq_bits = P.job->max_sq_bits;
     if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
     __syncthreads();
     const int lane = threadIdx.x & 31;
@@ -428,7 +431,7 @@ __global__ void __launch_bounds__(128) k_far(FusedParams P) {
         float wx, wy, wz;
         world_of(s_state, __ldg(P.body + i), wx, wy, wz);
         Cand out;
-        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, P.max_sq_bits, lane, out, nc);
+        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, max_sq_bits, lane, out, nc);
         if (lane < 5) {
             float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
             if (out.d != INF_BITS) p = __ldg(P.map.buckets + out.addr);
@@ -489,8 +492,8 @@ __global__ void k_transform(const float4* __restrict__ body, int n, const double
 void launch_fused(const FusedParams& P, int grid, cudaStream_t stream) {
     k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P);
 }
-void launch_search(const FusedParams& P, int far_grid, cudaStream_t stream) {
-    k_search<<<(P.n + SEARCH_THREADS - 1) / SEARCH_THREADS, SEARCH_THREADS, 0, stream>>>(P);
+void launch_search(const FusedParams& P, int search_grid, int far_grid, cudaStream_t stream) {
+    k_search<<<search_grid, SEARCH_THREADS, 0, stream>>>(P);   // CTAs beyond job->n idle: the grid is a capacity bucket
     k_far<<<far_grid, 128, 0, stream>>>(P);
 }
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,

@@ -30,10 +30,24 @@ struct Ctl {
     unsigned int far_count;      // entries of far_list written by the search kernel of this trip
 };
 
+// Per-call scalars, resident in HBM so that the captured launch sequence (CUDA graph) of an update never changes
+// its kernel parameters: a call only rewrites this block (one H2D copy together with the state and P).
+struct Job {
+    int n;                     // scan points
+    int units, groups;         // work units of 128 points / groups of GROUP_UNITS units
+    int mode;                  // FLIVO_MODE_*
+    int max_iter;
+    int force_search;
+    int nranks;
+    uint32_t max_sq_bits;      // kNN distance bound as float bits (INF_BITS = unbounded)
+    double R;                  // laser_point_cov
+    double limit[23];
+};
+
 struct FusedParams {
     MapView map;
     const float4* body;        // scan, lidar frame, processing order
-    int n;
+    const Job* job;
     const double* state;       // device flivo_state (36 doubles): rot, pos, offR, offT, ...
     float4* near;              // [n*5] cached Nearest_Points (x,y,z,id)
     float2* near_meta;         // [n] {count as float bits, 5th squared distance}
@@ -47,10 +61,6 @@ struct FusedParams {
     unsigned int* group_cnt;   // [groups]
     Ctl* ctl;
     SearchStats* stats;
-    int mode;                  // FLIVO_MODE_*
-    int force_search;
-    uint32_t max_sq_bits;      // kNN distance bound as float bits (INF_BITS = unbounded)
-    int units, groups;
 };
 
 }  // namespace flivo

@@ -368,12 +368,12 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         // multi-GPU: every rank's 92-term block was gathered; sum in rank order (bit-identical on all ranks)
         if (tid < NTERMS) {
             double s = 0.0;
-            for (int r = 0; r < S.nranks; ++r) s += S.rank_blocks[(size_t)r * PSTRIDE + tid];
+            for (int r = 0; r < S.job->nranks; ++r) s += S.rank_blocks[(size_t)r * PSTRIDE + tid];
             s_sum[tid] = s;
         }
         __syncthreads();
     } else {
-        reduce_groups(S.gpartials, S.groups, s_slices, s_sum, tid, NT);
+        reduce_groups(S.gpartials, S.job->groups, s_slices, s_sum, tid, NT);
     }
     if (S.phase == SOLVE_PHASE_REDUCE_ONLY) {
         if (tid < NTERMS) S.sum_out[tid] = s_sum[tid];
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     }
     if (tid < 12) s_z[tid] = s_sum[78 + tid];
     if (tid < 36) { s_x[tid] = S.x[tid]; s_xp[tid] = S.x_prop[tid]; }
-    const int mode = S.mode;
+    const int mode = S.job->mode;
     const int n = (mode == 1) ? 18 : 23;
     for (int e = tid; e < n * n; e += NT) s_P[e] = S.P_prop[e];
     __syncthreads();
@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         apply_T_cols(s_P, 23, s_T, tid, NT);
         __syncthreads();
         // Aug = [S^T | Q1^T],  S = I + HTH * Q11,  Q = P / R
-        const double invR = 1.0 / S.R;
+        const double invR = 1.0 / S.job->R;
         for (int e = tid; e < 12 * 35; e += NT) {
             int r = e / 35, c = e % 35;
             double v;
@@ -473,15 +473,15 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         if ((tid & 31) == 0 && tid < 96) d_boxplus_v3_part(s_x, s_dxo, tid >> 5);   // :1814
         if (tid == 128) {
             int converge = 1;
-            for (int i = 0; i < 23; ++i) if (fabs(s_dxo[i]) > S.limit[i]) { converge = 0; break; }
+            for (int i = 0; i < 23; ++i) if (fabs(s_dxo[i]) > S.job->limit[i]) { converge = 0; break; }
             int t = ctl->t, it = ctl->iter;
             if (converge) t++;
-            if (!t && it == S.max_iter - 2) converge = 1;                    // :1825-1828
-            int stop = (t > 1 || it == S.max_iter - 1) ? 1 : 0;               // :1831
+            if (!t && it == S.job->max_iter - 2) converge = 1;                    // :1825-1828
+            int stop = (t > 1 || it == S.job->max_iter - 1) ? 1 : 0;               // :1831
             ctl->t = t;
             int trip = ctl->trips;
-            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.force_search) ? 1 : 0;
-            ctl->searches += (ctl->search || S.force_search) ? 1 : 0;
+            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.job->force_search) ? 1 : 0;
+            ctl->searches += (ctl->search || S.job->force_search) ? 1 : 0;
             ctl->trips = trip + 1;
             ctl->search = converge;
             ctl->iter = it + 1;
@@ -520,7 +520,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         // ================= V1: src/laser_mapping.cpp:178-238 ==========================================
         // HPH (6x6) = Hsub^T (1/R) Hsub with Hsub = [A | n] = V3 columns [3:6 | 0:3]  (:584-586)
         __shared__ double s_H6[36], s_z6[6], s_vec[18], s_sol[18], s_G[18 * 6];
-        const double w = 1.0 / S.R;
+        const double w = 1.0 / S.job->R;
         if (tid < 36) {
             const int map6[6] = {3, 4, 5, 0, 1, 2};
             int a = tid / 6, b = tid % 6;
@@ -591,11 +591,11 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             double tn = sqrt(s_sol[3] * s_sol[3] + s_sol[4] * s_sol[4] + s_sol[5] * s_sol[5]);
             int converged = ((rn * R2D < 0.01) && (tn * 100 < 0.015)) ? 1 : 0;   // :209-212
             int it = ctl->iter, rematch = ctl->rematch, nse = 0;
-            if (converged || ((rematch == 0) && (it == (S.max_iter - 2)))) { nse = 1; rematch++; }   // :217-222
-            int stop = (rematch >= 2 || (it == S.max_iter - 1)) ? 1 : 0;          // :224
+            if (converged || ((rematch == 0) && (it == (S.job->max_iter - 2)))) { nse = 1; rematch++; }   // :217-222
+            int stop = (rematch >= 2 || (it == S.job->max_iter - 1)) ? 1 : 0;          // :224
             int trip = ctl->trips;
-            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.force_search) ? 1 : 0;
-            ctl->searches += (ctl->search || S.force_search) ? 1 : 0;
+            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.job->force_search) ? 1 : 0;
+            ctl->searches += (ctl->search || S.job->force_search) ? 1 : 0;
             ctl->trips = trip + 1;
             ctl->rematch = rematch;
             ctl->search = nse;
@@ -621,8 +621,10 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
 
 void launch_solve(const SolveParams& S, cudaStream_t stream) { k_solve<<<1, SOLVE_THREADS, 0, stream>>>(S); }
 
-// reset the control block at the start of an update
-__global__ void k_ctl_reset(Ctl* ctl, SearchStats* stats) {
+// start of an update: reset the control block, x_prop <- x, P_out <- P_prop (so a loop that never stops returns P unchanged)
+__global__ void k_ctl_reset(const double* x, double* x_prop, const double* P_prop, double* P_out, Ctl* ctl, SearchStats* stats) {
+    for (int e = threadIdx.x; e < 23 * 23; e += blockDim.x) P_out[e] = P_prop[e];
+    if (threadIdx.x < 36) x_prop[threadIdx.x] = x[threadIdx.x];
     if (threadIdx.x == 0) {
         ctl->search = 1; ctl->stopped = 0; ctl->iter = -1; ctl->t = 0; ctl->rematch = 0; ctl->trips = 0;
         ctl->searches = 0; ctl->converged = 0; ctl->n_eff = 0; ctl->nan_guard = 0; ctl->res_mean = 0.0;
@@ -632,6 +634,8 @@ __global__ void k_ctl_reset(Ctl* ctl, SearchStats* stats) {
         if (stats) { stats->far_queries = 0; stats->candidates = 0; stats->sweeps = 0; }
     }
 }
-void launch_ctl_reset(Ctl* ctl, SearchStats* stats, cudaStream_t stream) { k_ctl_reset<<<1, 32, 0, stream>>>(ctl, stats); }
+void launch_ctl_reset(const double* x, double* x_prop, const double* P_prop, double* P_out, Ctl* ctl, SearchStats* stats, cudaStream_t stream) {
+    k_ctl_reset<<<1, 256, 0, stream>>>(x, x_prop, P_prop, P_out, ctl, stats);
+}
 
 }  // namespace flivo

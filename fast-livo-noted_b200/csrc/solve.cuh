@@ -12,14 +12,8 @@ enum {
 
 struct SolveParams {
     const double* gpartials;   // [groups * PSTRIDE]
-    int groups;
+    const Job* job;
     int phase;
-    int mode;                  // FLIVO_MODE_*
-    int max_iter;
-    int force_search;
-    int nranks;
-    double R;                  // laser_point_cov
-    double limit[23];
     double* x;                 // device flivo_state, in/out
     const double* x_prop;      // device flivo_state
     const double* P_prop;      // n x n
@@ -31,11 +25,11 @@ struct SolveParams {
 
 void upload_term_table();
 void launch_fused(const FusedParams& P, int grid, cudaStream_t stream);
-void launch_search(const FusedParams& P, int far_grid, cudaStream_t stream);
+void launch_search(const FusedParams& P, int search_grid, int far_grid, cudaStream_t stream);
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
                 int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream);
 void launch_transform(const float4* body, int n, const double* state, float4* world, cudaStream_t stream);
 void launch_solve(const SolveParams& S, cudaStream_t stream);
-void launch_ctl_reset(Ctl* ctl, SearchStats* stats, cudaStream_t stream);
+void launch_ctl_reset(const double* x, double* x_prop, const double* P_prop, double* P_out, Ctl* ctl, SearchStats* stats, cudaStream_t stream);
 
 }  // namespace flivo

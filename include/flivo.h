@@ -73,8 +73,10 @@ typedef struct flivo_cfg {
     double  laser_point_cov;    /* LASER_POINT_COV (src/laser_mapping.cpp:975), the R of esekfom.hpp:1619 */
     double  limit[23];          /* V3 per-component convergence limit (epsi, src/origin_laserMapping.cpp:1231-1233) */
     int32_t force_search;       /* 1: kNN on every trip (SURVEY §3.2 "worst case"); 0: reference re-match policy */
-    int32_t reserved;
+    int32_t flags;              /* FLIVO_CFG_* */
 } flivo_cfg;
+/* per-trip CUDA events (flivo_stats.last_fused_ms / last_solve_ms) and plain launches instead of the captured graph */
+#define FLIVO_CFG_PROFILE 1
 
 typedef struct flivo_report {
     int32_t trips;              /* h_share_model calls executed */
