@@ -94,6 +94,8 @@ struct flivo_ctx {
     double *d_partials = nullptr, *d_gpartials = nullptr;
     unsigned int* d_group_cnt = nullptr;
     unsigned int* d_far_list = nullptr;
+    float4* d_plane = nullptr;
+    unsigned char* d_pflags = nullptr;
     void* d_out = nullptr;          // un-permute scratch for optional outputs
     size_t d_out_bytes = 0;
     // loop state
@@ -309,10 +311,10 @@ static void free_scan(flivo_ctx* ctx) {
     cudaFree(ctx->d_body_own);
     cudaFree(ctx->d_body_in); cudaFree(ctx->d_perm); cudaFree(ctx->d_skey_a); cudaFree(ctx->d_skey_b); cudaFree(ctx->d_sidx_a);
     cudaFree(ctx->d_cub); cudaFree(ctx->d_near); cudaFree(ctx->d_near_meta); cudaFree(ctx->d_sel); cudaFree(ctx->d_eff);
-    cudaFree(ctx->d_normvec); cudaFree(ctx->d_world); cudaFree(ctx->d_partials); cudaFree(ctx->d_gpartials); cudaFree(ctx->d_group_cnt); cudaFree(ctx->d_far_list);
+    cudaFree(ctx->d_normvec); cudaFree(ctx->d_world); cudaFree(ctx->d_partials); cudaFree(ctx->d_gpartials); cudaFree(ctx->d_group_cnt); cudaFree(ctx->d_far_list); cudaFree(ctx->d_plane); cudaFree(ctx->d_pflags);
     ctx->d_body = ctx->d_body_own = ctx->d_body_in = nullptr; ctx->d_perm = nullptr; ctx->d_skey_a = ctx->d_skey_b = nullptr; ctx->d_sidx_a = nullptr;
     ctx->d_cub = nullptr; ctx->d_near = nullptr; ctx->d_near_meta = nullptr; ctx->d_sel = ctx->d_eff = nullptr;
-    ctx->d_normvec = ctx->d_world = nullptr; ctx->d_partials = ctx->d_gpartials = nullptr; ctx->d_group_cnt = nullptr; ctx->d_far_list = nullptr;
+    ctx->d_normvec = ctx->d_world = nullptr; ctx->d_partials = ctx->d_gpartials = nullptr; ctx->d_group_cnt = nullptr; ctx->d_far_list = nullptr; ctx->d_plane = nullptr; ctx->d_pflags = nullptr;
     ctx->scan_cap = 0; ctx->scan_n = 0; ctx->cub_bytes = 0;
 }
 
@@ -507,9 +509,12 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
         CKC(cudaMalloc(&ctx->d_normvec, cap * sizeof(float4)));
         CKC(cudaMalloc(&ctx->d_world, cap * sizeof(float4)));
         CKC(cudaMalloc(&ctx->d_partials, units * PSTRIDE * sizeof(double)));
-        CKC(cudaMalloc(&ctx->d_gpartials, groups * PSTRIDE * sizeof(double)));
+        (void)groups;
+        CKC(cudaMalloc(&ctx->d_gpartials, (size_t)std::max<size_t>(units, (size_t)ctx->sm_count * 8 + 256) * PSTRIDE * sizeof(double)));   // one record per CTA of k_fused
         CKC(cudaMalloc(&ctx->d_group_cnt, groups * sizeof(unsigned int)));
         CKC(cudaMalloc(&ctx->d_far_list, cap * sizeof(unsigned int)));
+        CKC(cudaMalloc(&ctx->d_plane, cap * sizeof(float4)));
+        CKC(cudaMalloc(&ctx->d_pflags, cap));
         CKC(cudaMemsetAsync(ctx->d_group_cnt, 0, groups * sizeof(unsigned int), ctx->stream));
         ctx->scan_cap = cap;
     }
@@ -534,6 +539,7 @@ static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool externa
     // point_selected_surf starts true (V3 global array semantics are re-established by the first search trip)
     CKC(cudaMemsetAsync(ctx->d_sel, 1, n, ctx->stream));
     CKC(cudaMemsetAsync(ctx->d_eff, 0, n, ctx->stream));
+    CKC(cudaMemsetAsync(ctx->d_pflags, 0, n, ctx->stream));   // no cached neighbours yet: a re-use trip before any search selects nothing
     return FLIVO_OK;
 }
 
@@ -569,18 +575,20 @@ static FusedParams make_fused(flivo_ctx* ctx) {
     P.job = &ctx->d_blk->job;
     P.state = ctx->d_x;
     P.near = ctx->d_near; P.near_meta = ctx->d_near_meta; P.sel = ctx->d_sel; P.eff = ctx->d_eff;
+    P.plane = ctx->d_plane; P.pflags = ctx->d_pflags;
     P.normvec = ctx->d_normvec; P.world = ctx->d_world;
     P.partials = ctx->d_partials; P.gpartials = ctx->d_gpartials; P.group_cnt = ctx->d_group_cnt; P.far_list = ctx->d_far_list;
     P.ctl = ctx->d_ctl; P.stats = ctx->d_stats;
     return P;
 }
+static int fused_grid(flivo_ctx* ctx);
 // per-call scalars -> the pinned mirror of the device block (copied with the state by the caller)
-static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, double R, const double* limit23, uint32_t max_sq_bits) {
+static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, double R, const double* limit23, uint32_t max_sq_bits, int aux_out) {
     Job& j = ctx->h_blk->job;
     j.n = (int)ctx->scan_n;
     j.units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
-    j.groups = (j.units + GROUP_UNITS - 1) / GROUP_UNITS;
-    j.mode = mode; j.max_iter = max_iter; j.force_search = force_search; j.nranks = ctx->nranks; j.max_sq_bits = max_sq_bits;
+    j.groups = fused_grid(ctx);   // per-CTA records of k_fused summed by k_solve
+    j.mode = mode; j.max_iter = max_iter; j.force_search = force_search; j.nranks = ctx->nranks; j.max_sq_bits = max_sq_bits; j.aux_out = aux_out;
     j.R = R;
     for (int i = 0; i < 23; ++i) j.limit[i] = limit23 ? limit23[i] : 0.001;
 }
@@ -634,7 +642,7 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
     NEED(st && HTH && HTz, FLIVO_E_ARG, "null state / outputs");
     NEED(mode == FLIVO_MODE_V3 || mode == FLIVO_MODE_V1, FLIVO_E_ARG, "bad mode");
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
-    fill_job(ctx, mode, 1, 0, 0.001, nullptr, gate_bits());
+    fill_job(ctx, mode, 1, 0, 0.001, nullptr, gate_bits(), 1);
     memcpy(ctx->h_blk->x, st, sizeof(flivo_state));
     CKC(cudaMemcpyAsync(&ctx->d_blk->job, &ctx->h_blk->job, sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
     CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_blk->x, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
@@ -708,7 +716,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     const bool timed = (cfg->flags & FLIVO_CFG_PROFILE) != 0;   // per-trip events, plain launches (no graph)
     cudaStream_t s = ctx->stream;
     DevBlock* h = ctx->h_blk;
-    fill_job(ctx, cfg->mode, cfg->max_iter, cfg->force_search, cfg->laser_point_cov, cfg->limit, gate_bits());
+    fill_job(ctx, cfg->mode, cfg->max_iter, cfg->force_search, cfg->laser_point_cov, cfg->limit, gate_bits(), 0);
     memcpy(h->x, inout, sizeof(flivo_state));
     memset(h->P_prop, 0, sizeof(h->P_prop));
     memcpy(h->P_prop, Pm, sizeof(double) * np * np);

@@ -10,8 +10,8 @@
 //   a5 residual + range gate (:532-543)      -> per lane
 //   a6 compaction (:547-561)                 -> replaced by masked accumulation; mask and n_eff are outputs
 //   a7 1x12 Jacobian row (origin:1018-1044)  -> per lane, double
-//   a8 H^T H / H^T z (esekfom.hpp:1781,1801) -> shared-memory transposed Gram per warp, fixed-order block,
-//                                               group and final reductions (no floating-point atomics)
+//   a8 H^T H / H^T z (esekfom.hpp:1781,1801) -> FP64 tensor-core MMA (DMMA.8x8x4) Gram in registers per warp, fixed-order
+//                                               CTA and final reductions (no floating-point atomics)
 // Compiled with -fmad=false: see flivo_dev.cuh.
 #include "fused.cuh"
 #include "search.cuh"
@@ -180,22 +180,33 @@ __device__ bool esti_plane_dev(const float4 nb[5], float threshold, float pabcd[
 __device__ __forceinline__ double dot3d(const double* a, double b0, double b1, double b2) { return a[0] * b0 + (a[1] * b1 + a[2] * b2); }
 
 // ----------------------------------------------------------------------------------------------------
-// fused kernel
+// fused kernel: a1 (re-transform), a3/a5 gates, a7 row, a8 Gram — everything that depends on the state.
+//
+// Work item = a tile of 32 consecutive scan points per warp, dealt statically (tile = global warp id + k * warps),
+// so the summation order is fixed by (n, grid) alone and results are bit-reproducible.  Each lane builds the row
+// of its point: H[p] = (h[0..11], z, eff ? 1 : 0, |pd2|, 0) — 16 columns; the Gram G = H^T H over the tile is
+// accumulated with FP64 tensor-core MMAs (mma.sync m8n8k4 = SASS DMMA.8x8x4; the only dense contraction on the
+// path) into three 8x8 register blocks per warp that live across ALL tiles of the warp:
+//     G00 = rows 0..7 x cols 0..7,  G08 = rows 0..7 x cols 8..15,  G88 = rows 8..15 x cols 8..15
+// so H^T H (78 upper terms), H^T z = G[:,12], n_eff = G[13][13] and res_sum = G[13][14] come out of the same
+// accumulation, with no per-tile reduction, no barrier and no atomics.  One CTA-level fold at the end writes one
+// 96-double record per CTA; k_solve sums the records in CTA order.
+// Staging: the tile's rows go through shared memory transposed (Ht[col][point], row pitch 36 doubles) so that the
+// MMA fragment loads are bank-conflict-free at the 2-wavefront minimum of a 256-byte request.
 // ----------------------------------------------------------------------------------------------------
-struct __align__(16) WarpSmem {
-    double rows[32 * 14];         // Jacobian rows h[12], z, pad of the warp's 32 points
-};
+constexpr int HT_PITCH = 36;
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
 
 __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
-    __shared__ WarpSmem s_warp[UNIT_WARPS];
-    __shared__ double s_acc[UNIT_WARPS][PSTRIDE];
+    __shared__ double s_ht[UNIT_WARPS][16 * HT_PITCH];   // per warp: Ht[16][36]; reused for the final fold
     __shared__ double s_state[36];
-    __shared__ unsigned int s_unit;
-    __shared__ int s_last;
 
     Ctl* ctl = P.ctl;
     if (ctl->stopped) return;
-    const int n_pts = P.job->n, n_units = P.job->units, mode = P.job->mode;
+    const int n_pts = P.job->n, mode = P.job->mode, aux_out = P.job->aux_out;
     const bool search = (ctl->search != 0) || (P.job->force_search != 0);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 36) s_state[threadIdx.x] = P.state[threadIdx.x];
@@ -204,19 +215,20 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
     const double* tw = s_state + 9;      // pos
     const double* Rl = s_state + 12;     // offR
     const double* tl = s_state + 21;     // offT
-    WarpSmem& ws = s_warp[warp];
+    double* ht = s_ht[warp];
 
-    while (true) {
-        if (threadIdx.x == 0) s_unit = atomicAdd(&ctl->unit_counter, 1u);
-        __syncthreads();
-        const unsigned int unit = s_unit;
-        if (unit >= (unsigned)n_units) break;
-        const int base = unit * UNIT_POINTS + warp * 32;
-        const int i = base + lane;
+    double g00a = 0.0, g00b = 0.0, g08a = 0.0, g08b = 0.0, g88a = 0.0, g88b = 0.0;
+    const int n_tiles = (n_pts + 31) >> 5;
+    const int total_warps = gridDim.x * UNIT_WARPS;
+    for (int tile = blockIdx.x * UNIT_WARPS + warp; tile < n_tiles; tile += total_warps) {
+        const int i = tile * 32 + lane;
         const bool have = i < n_pts;
 
         // ---- a1: world transform --------------------------------------------------------------------
         float4 pb = have ? __ldg(P.body + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 pl4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        unsigned pf = 0, selprev = 0;
+        if (have) { pf = P.pflags[i]; pl4 = __ldg(P.plane + i); selprev = P.sel[i]; }
         double pd[3] = {(double)pb.x, (double)pb.y, (double)pb.z};
         double pl[3];  // R_LI p + t_LI
         pl[0] = dot3d(Rl + 0, pd[0], pd[1], pd[2]) + tl[0];
@@ -225,40 +237,27 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         float wx = (float)(dot3d(Rm + 0, pl[0], pl[1], pl[2]) + tw[0]);
         float wy = (float)(dot3d(Rm + 3, pl[0], pl[1], pl[2]) + tw[1]);
         float wz = (float)(dot3d(Rm + 6, pl[0], pl[1], pl[2]) + tw[2]);
-        if (have) P.world[i] = make_float4(wx, wy, wz, pb.w);
+        if (have && aux_out) P.world[i] = make_float4(wx, wy, wz, pb.w);
 
-        // ---- a2: neighbours ---------------------------------------------------------------------------
-        float4 nb[5];
-        int ncnt = 0;
-        float d5 = INFINITY;
-        // (on a search trip k_search / k_far of the same trip have just refreshed the Nearest_Points cache)
-        if (have) {
-            float2 meta = __ldg(P.near_meta + i);
-            ncnt = __float_as_int(meta.x);
-            d5 = meta.y;
-#pragma unroll
-            for (int r = 0; r < 5; ++r) nb[r] = __ldg(P.near + (size_t)i * 5 + r);
-        }
-
-        // ---- a3..a5: gates and plane -----------------------------------------------------------------
+        // ---- a2..a5: the neighbours enter only through esti_plane, fitted once per search by k_search / k_far
+        // (P.plane, P.pflags); what depends on the state is re-evaluated here on every trip.
         bool sel;
         if (mode == 1) sel = true;                        // V1: vector<bool>(n, true) each call (:490)
-        else sel = have && (P.sel[i] != 0);                 // V3: persistent flag (origin:963)
-        const bool have5 = have && ncnt >= 5;
-        if (search) sel = have5 && !(d5 > 5.f);             // pointSearchSqDis[4] > 5 ? false : true (:518)
+        else sel = have && (selprev != 0);                  // V3: persistent flag (origin:963)
+        const bool have5 = (pf & PF_HAVE5) != 0;
+        if (search) sel = have5 && (pf & PF_GATE);          // pointSearchSqDis[4] > 5 ? false : true (:518)
         bool eff = false;
         float4 nv = make_float4(0.f, 0.f, 0.f, 0.f);
         float res = 0.f;
         if (sel && have5) {
             sel = false;
-            float pabcd[4];
-            if (esti_plane_dev(nb, 0.1f, pabcd)) {
-                float pd2 = pabcd[0] * wx + pabcd[1] * wy + pabcd[2] * wz + pabcd[3];
+            if (pf & PF_PLANE) {                            // esti_plane(pabcd, points_near, 0.1f) (:530)
+                float pd2 = pl4.x * wx + pl4.y * wy + pl4.z * wz + pl4.w;
                 double nrm = sqrt(pd[0] * pd[0] + (pd[1] * pd[1] + pd[2] * pd[2]));
                 float s = (float)(1.0 - 0.9 * (double)fabsf(pd2) / sqrt(nrm));
                 if ((double)s > 0.9) {
                     sel = true;
-                    nv = make_float4(pabcd[0], pabcd[1], pabcd[2], pd2);
+                    nv = make_float4(pl4.x, pl4.y, pl4.z, pd2);
                     res = fabsf(pd2);
                     eff = res <= 2.0f;                       // res_last[i] <= 2.0 (:552)
                 }
@@ -268,85 +267,75 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         }
         if (have) {
             P.sel[i] = sel ? 1 : 0;
-            P.eff[i] = eff ? 1 : 0;
-            P.normvec[i] = nv;
+            if (aux_out) { P.eff[i] = eff ? 1 : 0; P.normvec[i] = nv; }
         }
 
-        // ---- a7: Jacobian row (origin:1018-1044) -------------------------------------------------------
-        double h[13];
+        // ---- a7: Jacobian row (origin:1018-1044), transposed into shared memory -------------------------
+        __syncwarp();   // the previous tile's fragment loads are done
         if (eff) {
             double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
             double C0 = Rm[0] * n0 + (Rm[3] * n1 + Rm[6] * n2);   // R^T n
             double C1 = Rm[1] * n0 + (Rm[4] * n1 + Rm[7] * n2);
             double C2 = Rm[2] * n0 + (Rm[5] * n1 + Rm[8] * n2);
-            double A0 = pl[1] * C2 - pl[2] * C1, A1 = pl[2] * C0 - pl[0] * C2, A2 = pl[0] * C1 - pl[1] * C0;   // [pt]x C
             double T0 = Rl[0] * C0 + (Rl[3] * C1 + Rl[6] * C2);   // R_LI^T C
             double T1 = Rl[1] * C0 + (Rl[4] * C1 + Rl[7] * C2);
             double T2 = Rl[2] * C0 + (Rl[5] * C1 + Rl[8] * C2);
-            double B0 = pd[1] * T2 - pd[2] * T1, B1 = pd[2] * T0 - pd[0] * T2, B2 = pd[0] * T1 - pd[1] * T0;   // [p]x (...)
-            h[0] = n0; h[1] = n1; h[2] = n2; h[3] = A0; h[4] = A1; h[5] = A2;
-            h[6] = B0; h[7] = B1; h[8] = B2; h[9] = C0; h[10] = C1; h[11] = C2;
-            h[12] = -(double)nv.w;
+            ht[0 * HT_PITCH + lane] = n0; ht[1 * HT_PITCH + lane] = n1; ht[2 * HT_PITCH + lane] = n2;
+            ht[3 * HT_PITCH + lane] = pl[1] * C2 - pl[2] * C1;     // A = [R_LI p + t_LI]x C
+            ht[4 * HT_PITCH + lane] = pl[2] * C0 - pl[0] * C2;
+            ht[5 * HT_PITCH + lane] = pl[0] * C1 - pl[1] * C0;
+            ht[6 * HT_PITCH + lane] = pd[1] * T2 - pd[2] * T1;     // B = [p]x R_LI^T C
+            ht[7 * HT_PITCH + lane] = pd[2] * T0 - pd[0] * T2;
+            ht[8 * HT_PITCH + lane] = pd[0] * T1 - pd[1] * T0;
+            ht[9 * HT_PITCH + lane] = C0; ht[10 * HT_PITCH + lane] = C1; ht[11 * HT_PITCH + lane] = C2;
+            ht[12 * HT_PITCH + lane] = -(double)nv.w;              // z = -pd2
+            ht[13 * HT_PITCH + lane] = 1.0;                        // -> n_eff
+            ht[14 * HT_PITCH + lane] = (double)res;                // -> res_sum
+            ht[15 * HT_PITCH + lane] = 0.0;
         } else {
 #pragma unroll
-            for (int a = 0; a < 13; ++a) h[a] = 0.0;
+            for (int c = 0; c < 16; ++c) ht[c * HT_PITCH + lane] = 0.0;
         }
-#pragma unroll
-        for (int a = 0; a < 13; ++a) ws.rows[lane * 14 + a] = h[a];
         __syncwarp();
 
-        // ---- a8: Gram of the warp's 32 rows; lane t owns terms t, t+32, t+64 -----------------------------
-        {
-            const int t0 = lane, t1 = lane + 32, t2 = lane + 64;
-            const int a0 = c_term_a[t0], b0 = c_term_b[t0], a1 = c_term_a[t1], b1 = c_term_b[t1];
-            const bool has2 = t2 < 90;
-            const int a2 = has2 ? c_term_a[t2] : 0, b2 = has2 ? c_term_b[t2] : 0;
-            double v0 = 0.0, v1 = 0.0, v2 = 0.0;
-            const unsigned effmask = __ballot_sync(FULL, eff);
-            for (int r = 0; r < 32; ++r) {
-                if (!((effmask >> r) & 1u)) continue;  // warp-uniform
-                const double* row = ws.rows + r * 14;
-                v0 += row[a0] * row[b0];
-                v1 += row[a1] * row[b1];
-                v2 += row[a2] * row[b2];
-            }
-            double rsum = eff ? (double)res : 0.0;
+        // ---- a8: G += H^T H over the tile's 32 points, 8 k-steps of 4 points ------------------------------
+        if (__any_sync(FULL, eff)) {
+            const int fr = lane >> 2, fk = lane & 3;
 #pragma unroll
-            for (int o = 16; o; o >>= 1) rsum += __shfl_xor_sync(FULL, rsum, o);
-            s_acc[warp][t0] = v0;
-            s_acc[warp][t1] = v1;
-            if (has2) s_acc[warp][t2] = v2;
-            if (lane == 0) { s_acc[warp][90] = rsum; s_acc[warp][91] = (double)__popc(effmask); }
-        }
-        __syncthreads();
-        if (threadIdx.x < NTERMS) {
-            double s = s_acc[0][threadIdx.x];
-#pragma unroll
-            for (int w = 1; w < UNIT_WARPS; ++w) s += s_acc[w][threadIdx.x];
-            P.partials[(size_t)unit * PSTRIDE + threadIdx.x] = s;
-        }
-        // ---- group fold by the last-arriving unit (fixed order => deterministic) ---------------------------
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned int g = unit / GROUP_UNITS;
-            unsigned int gsize = min((unsigned)GROUP_UNITS, (unsigned)n_units - g * GROUP_UNITS);
-            unsigned int old = atomicAdd(P.group_cnt + g, 1u);
-            s_last = (old == gsize - 1) ? 1 : 0;
-        }
-        __syncthreads();
-        if (s_last) {
-            __threadfence();
-            unsigned int g = unit / GROUP_UNITS;
-            unsigned int u0 = g * GROUP_UNITS, u1 = min(u0 + GROUP_UNITS, (unsigned)n_units);
-            if (threadIdx.x < NTERMS) {
-                double s = 0.0;
-                for (unsigned int u = u0; u < u1; ++u) s += __ldcg(P.partials + (size_t)u * PSTRIDE + threadIdx.x);
-                P.gpartials[(size_t)g * PSTRIDE + threadIdx.x] = s;
+            for (int ks = 0; ks < 8; ++ks) {
+                const double f0 = ht[fr * HT_PITCH + ks * 4 + fk];          // H[4 ks + fk][fr]
+                const double f8 = ht[(8 + fr) * HT_PITCH + ks * 4 + fk];    // H[4 ks + fk][8 + fr]
+                dmma884(g00a, g00b, f0, f0);
+                dmma884(g08a, g08b, f0, f8);
+                dmma884(g88a, g88b, f8, f8);
             }
-            if (threadIdx.x == 0) P.group_cnt[g] = 0;
         }
-        __syncthreads();
+    }
+
+    // ---- fold the CTA's warps (fixed order) into one 96-double record ----------------------------------------
+    // accumulator fragment: lane holds G[lane/4][2*(lane%4) + {0,1}] of each 8x8 block
+    __syncthreads();
+    {
+        double* w = s_ht[warp];   // [3][64]
+        const int e = (lane >> 2) * 8 + 2 * (lane & 3);
+        w[e] = g00a; w[e + 1] = g00b;
+        w[64 + e] = g08a; w[64 + e + 1] = g08b;
+        w[128 + e] = g88a; w[128 + e + 1] = g88b;
+    }
+    __syncthreads();
+    if (threadIdx.x < NTERMS) {
+        const int t = threadIdx.x;
+        int r, c;   // position in the 16x16 Gram
+        if (t < 78) { r = c_term_a[t]; c = c_term_b[t]; }
+        else if (t < 90) { r = t - 78; c = 12; }
+        else if (t == 90) { r = 13; c = 14; }                // res_sum
+        else { r = 13; c = 13; }                             // n_eff
+        const int blk = (r < 8) ? ((c < 8) ? 0 : 1) : 2;
+        const int e = blk * 64 + (r & 7) * 8 + (c & 7);
+        double sum = s_ht[0][e];
+#pragma unroll
+        for (int wv = 1; wv < UNIT_WARPS; ++wv) sum += s_ht[wv][e];
+        P.gpartials[(size_t)blockIdx.x * PSTRIDE + t] = sum;
     }
 }
 
@@ -363,6 +352,20 @@ __device__ __forceinline__ void world_of(const double* __restrict__ st, float4 p
     wx = (float)(dot3d(st + 0, l0, l1, l2) + st[9]);
     wy = (float)(dot3d(st + 3, l0, l1, l2) + st[10]);
     wz = (float)(dot3d(st + 6, l0, l1, l2) + st[11]);
+}
+
+// a3 + a4 on the freshly found neighbours: flags and plane of point i (consumed by k_fused on every trip
+// until the next search)
+__device__ __forceinline__ void store_plane(const FusedParams& P, int i, const float4 nbs[5], int cnt, float d5) {
+    unsigned pf = 0;
+    float pabcd[4] = {0.f, 0.f, 0.f, 0.f};
+    if (cnt >= 5) {
+        pf |= PF_HAVE5;
+        if (!(d5 > 5.f)) pf |= PF_GATE;
+        if (esti_plane_dev(nbs, 0.1f, pabcd)) pf |= PF_PLANE;
+    }
+    P.plane[i] = make_float4(pabcd[0], pabcd[1], pabcd[2], pabcd[3]);
+    P.pflags[i] = (unsigned char)pf;
 }
 
 constexpr int SEARCH_THREADS = 128;
@@ -388,13 +391,16 @@ __global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
         int cnt = 0;
         fin = thread_knn5_shell(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, s_idx + threadIdx.x, s_gap + threadIdx.x, SEARCH_THREADS);
         if (fin) {
+            float4 nbs[5];
 #pragma unroll
             for (int r = 0; r < 5; ++r) {
-                float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-                if (r < cnt) p = __ldg(P.map.buckets + best.a[r]);
-                P.near[(size_t)i * 5 + r] = p;
+                nbs[r] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                if (r < cnt) nbs[r] = __ldg(P.map.buckets + best.a[r]);
+                P.near[(size_t)i * 5 + r] = nbs[r];
             }
-            P.near_meta[i] = make_float2(__int_as_float(cnt), (cnt >= 5) ? __uint_as_float((uint32_t)(best.k[4] >> 32)) : INFINITY);
+            const float d5 = (cnt >= 5) ? __uint_as_float((uint32_t)(best.k[4] >> 32)) : INFINITY;
+            P.near_meta[i] = make_float2(__int_as_float(cnt), d5);
+            store_plane(P, i, nbs, cnt, d5);
         }
     }
     // far list: one atomic per warp
@@ -438,7 +444,19 @@ __global__ void __launch_bounds__(128) k_far(FusedParams P) {
             P.near[(size_t)i * 5 + lane] = p;
         }
         const uint32_t dlast = __shfl_sync(FULL, out.d, 4);
-        if (lane == 0) P.near_meta[i] = make_float2(__int_as_float(cnt), (cnt >= 5) ? __uint_as_float(dlast) : INFINITY);
+        float4 pme = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        if (lane < 5 && out.d != INF_BITS) pme = __ldg(P.map.buckets + out.addr);
+        float4 nbs[5];
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+            nbs[r].x = __shfl_sync(FULL, pme.x, r); nbs[r].y = __shfl_sync(FULL, pme.y, r);
+            nbs[r].z = __shfl_sync(FULL, pme.z, r); nbs[r].w = __shfl_sync(FULL, pme.w, r);
+        }
+        if (lane == 0) {
+            const float d5 = (cnt >= 5) ? __uint_as_float(dlast) : INFINITY;
+            P.near_meta[i] = make_float2(__int_as_float(cnt), d5);
+            store_plane(P, (int)i, nbs, cnt, d5);
+        }
     }
     if (P.stats) {
         const unsigned tot = __reduce_add_sync(FULL, nc);

@@ -39,10 +39,15 @@ struct Job {
     int max_iter;
     int force_search;
     int nranks;
+    int aux_out;               // 1: k_fused also writes eff / normvec / world (flivo_h_share_model outputs)
     uint32_t max_sq_bits;      // kNN distance bound as float bits (INF_BITS = unbounded)
     double R;                  // laser_point_cov
     double limit[23];
 };
+
+enum { PF_HAVE5 = 1,    // five neighbours exist (points_near.size() >= NUM_MATCH_POINTS)
+       PF_GATE = 2,     // !(pointSearchSqDis[4] > 5)            (src/laser_mapping.cpp:518)
+       PF_PLANE = 4 };  // esti_plane accepted the five points  (include/common_lib.h:694-699)
 
 struct FusedParams {
     MapView map;
@@ -51,6 +56,9 @@ struct FusedParams {
     const double* state;       // device flivo_state (36 doubles): rot, pos, offR, offT, ...
     float4* near;              // [n*5] cached Nearest_Points (x,y,z,id)
     float2* near_meta;         // [n] {count as float bits, 5th squared distance}
+    float4* plane;             // [n] esti_plane of the cached neighbours (a, b, c, d): a function of the neighbours only,
+                               //     so it is fitted once per search and reused by every trip until the next search
+    unsigned char* pflags;     // [n] PF_* of the cached neighbours
     unsigned char* sel;        // [n] point_selected_surf (persistent across trips in V3 mode)
     unsigned char* eff;        // [n] rows that entered H
     float4* normvec;           // [n] (nx,ny,nz,pd2)
