@@ -272,51 +272,42 @@ __device__ void apply_T_cols(double* M, int n, const BlockT& T, int tid, int nth
     }
 }
 
-// Solve S^T X = B in place by Gauss-Jordan with partial pivoting; one warp, whole matrix in registers.
-// Aug is M x w (w = M + nrhs <= 64) row-major in shared memory holding [S^T | B]; on return the right part
-// holds X.  Lane l owns columns l and l + 32; the pivot column k (k < M <= 12) lives in lane k, its entries
-// are broadcast by shuffle, so there is no shared-memory traffic or barrier inside the elimination.
-// Operation order per entry is the textbook one (scale the pivot row, then row_i -= f * row_k).
-template <int M>
-__device__ __noinline__ bool warp_gauss_jordan(double* Aug, int w, int lane) {
-    // k_solve is one CTA running cold code once per trip, so instruction fetch dominates: the pivot loop is
-    // kept rolled (one ~250-instruction body) by rotating the register rows so that the current pivot row is
-    // always a[0]; after M steps every row is back at its own index.
+// Solve S^T X = B in place by Gauss-Jordan with partial pivoting, the whole CTA on the m x w array in shared
+// memory (w = m + nrhs): one element per thread in the elimination, five barriers per pivot.  (A single warp
+// holding the matrix in registers was measured ~10x slower here: k_solve is one cold CTA and its time is set by
+// dependent-instruction and instruction-fetch latency, so short rolled loops over all threads win.)
+// Aug holds [S^T | B]; on return the right part holds X.  First maximum wins pivot ties.  Returns false on a zero pivot.
+__device__ bool block_gauss_jordan(double* Aug, int m, int w, double* s_f /*[16]*/, int* s_piv, int tid, int NT) {
     const unsigned FULLM = 0xFFFFFFFFu;
-    double a[M], b[M];
-    const bool hasa = lane < w, hasb = lane + 32 < w;
-#pragma unroll
-    for (int i = 0; i < M; ++i) { a[i] = hasa ? Aug[i * w + lane] : 0.0; b[i] = hasb ? Aug[i * w + lane + 32] : 0.0; }
     bool ok = true;
-#pragma unroll 1
-    for (int k = 0; k < M; ++k) {
-        const int nact = M - k;            // a[0 .. nact) = rows k .. M-1 (not pivoted yet), a[nact .. M) = rows 0 .. k-1
-        int p = 0;
-        double best = fabs(a[0]);
+    for (int k = 0; k < m; ++k) {
+        if (tid < 32) {
+            double v = (tid >= k && tid < m) ? fabs(Aug[tid * w + k]) : -1.0;
+            int idx = tid;
 #pragma unroll
-        for (int i = 1; i < M; ++i) { double v = fabs(a[i]); if (i < nact && v > best) { best = v; p = i; } }
-        p = __shfl_sync(FULLM, p, k);
-        best = __shfl_sync(FULLM, best, k);
-        if (best == 0.0) ok = false;
-#pragma unroll
-        for (int i = 1; i < M; ++i)
-            if (i == p) { double t = a[i]; a[i] = a[0]; a[0] = t; t = b[i]; b[i] = b[0]; b[0] = t; }
-        const double piv = __shfl_sync(FULLM, a[0], k);
-        a[0] = a[0] / piv;
-        b[0] = b[0] / piv;
-#pragma unroll
-        for (int i = 1; i < M; ++i) {
-            const double f = __shfl_sync(FULLM, a[i], k);
-            a[i] -= f * a[0];
-            b[i] -= f * b[0];
+            for (int o = 16; o; o >>= 1) {
+                const double ov = __shfl_xor_sync(FULLM, v, o);
+                const int oi = __shfl_xor_sync(FULLM, idx, o);
+                if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
+            }
+            if (tid == 0) { *s_piv = idx; s_f[15] = v; }
         }
-        const double ta = a[0], tb = b[0];
-#pragma unroll
-        for (int i = 0; i < M - 1; ++i) { a[i] = a[i + 1]; b[i] = b[i + 1]; }
-        a[M - 1] = ta; b[M - 1] = tb;
+        __syncthreads();
+        const int p = *s_piv;
+        if (s_f[15] == 0.0) ok = false;
+        if (p != k && tid < w) { const double t = Aug[k * w + tid]; Aug[k * w + tid] = Aug[p * w + tid]; Aug[p * w + tid] = t; }
+        __syncthreads();
+        const double piv = Aug[k * w + k];
+        if (tid < m) s_f[tid] = Aug[tid * w + k];          // column k before it changes
+        __syncthreads();
+        if (tid < w) Aug[k * w + tid] = Aug[k * w + tid] / piv;
+        __syncthreads();
+        for (int e = tid; e < m * w; e += NT) {
+            const int i = e / w, c = e - i * w;
+            if (i != k) Aug[e] -= s_f[i] * Aug[k * w + c];
+        }
+        __syncthreads();
     }
-#pragma unroll
-    for (int i = 0; i < M; ++i) { if (hasa) Aug[i * w + lane] = a[i]; if (hasb) Aug[i * w + lane + 32] = b[i]; }
     return ok;
 }
 
@@ -357,7 +348,8 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     __shared__ double s_x[36], s_xp[36];
     __shared__ double s_dx[23], s_dxnew[23], s_dxo[23], s_Kh[23];
     __shared__ BlockT s_T;
-    __shared__ int s_flag[4];  // [0]=stop, [1]=ok
+    __shared__ int s_flag[4];  // [0]=stop, [1]=ok, [2]=pivot row
+    __shared__ double s_gjf[16];
 
     Ctl* ctl = S.ctl;
     const int tid = threadIdx.x, NT = blockDim.x;
@@ -444,8 +436,8 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_Aug[e] = v;
         }
         __syncthreads();
-        if (tid < 32) {
-            bool ok = warp_gauss_jordan<12>(s_Aug, 35, tid);
+        {
+            const bool ok = block_gauss_jordan(s_Aug, 12, 35, s_gjf, &s_flag[2], tid, NT);
             if (tid == 0) s_flag[1] = ok ? 1 : 0;
         }
         __syncthreads();
@@ -557,8 +549,8 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_Aug[e] = v;
         }
         __syncthreads();
-        if (tid < 32) {
-            bool ok = warp_gauss_jordan<6>(s_Aug, 24, tid);
+        {
+            const bool ok = block_gauss_jordan(s_Aug, 6, 24, s_gjf, &s_flag[2], tid, NT);
             if (tid == 0) s_flag[1] = ok ? 1 : 0;
         }
         __syncthreads();
