@@ -281,31 +281,35 @@ __device__ bool block_gauss_jordan(double* Aug, int m, int w, double* s_f /*[16]
     const unsigned FULLM = 0xFFFFFFFFu;
     bool ok = true;
     for (int k = 0; k < m; ++k) {
+        // pivot row: first maximum of |Aug[i][k]|, i >= k.  Non-negative doubles order like their bit patterns, so three
+        // hardware warp reductions (high word, low word, lowest index) replace a shuffle tree.
         if (tid < 32) {
-            double v = (tid >= k && tid < m) ? fabs(Aug[tid * w + k]) : -1.0;
-            int idx = tid;
-#pragma unroll
-            for (int o = 16; o; o >>= 1) {
-                const double ov = __shfl_xor_sync(FULLM, v, o);
-                const int oi = __shfl_xor_sync(FULLM, idx, o);
-                if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
-            }
-            if (tid == 0) { *s_piv = idx; s_f[15] = v; }
+            const bool cand = tid >= k && tid < m;
+            const unsigned long long bits = cand ? (unsigned long long)__double_as_longlong(fabs(Aug[tid * w + k])) : 0ull;
+            const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
+            const unsigned mhi = __reduce_max_sync(FULLM, cand ? hi : 0u);
+            const unsigned mlo = __reduce_max_sync(FULLM, (cand && hi == mhi) ? lo : 0u);
+            const unsigned idx = __reduce_min_sync(FULLM, (cand && hi == mhi && lo == mlo) ? (unsigned)tid : 0xFFFFFFFFu);
+            if (tid == 0) { *s_piv = (int)idx; s_f[15] = __longlong_as_double((long long)(((unsigned long long)mhi << 32) | mlo)); }
         }
         __syncthreads();
         const int p = *s_piv;
         if (s_f[15] == 0.0) ok = false;
-        if (p != k && tid < w) { const double t = Aug[k * w + tid]; Aug[k * w + tid] = Aug[p * w + tid]; Aug[p * w + tid] = t; }
-        __syncthreads();
-        const double piv = Aug[k * w + k];
-        if (tid < m) s_f[tid] = Aug[tid * w + k];          // column k before it changes
-        __syncthreads();
-        if (tid < w) Aug[k * w + tid] = Aug[k * w + tid] / piv;
-        __syncthreads();
-        for (int e = tid; e < m * w; e += NT) {
+        // every thread computes the new value of its element from the OLD matrix (row swap p <-> k applied by index),
+        // then all write: two barriers instead of one per sub-step.  Same operations per entry as the textbook order:
+        // pivot row scaled by 1/piv (a division), other rows  a_ic - a_ik * (scaled pivot row)_c.
+        const double piv = Aug[p * w + k];
+        double nv[2];
+        int ne = 0;
+        for (int e = tid; e < m * w; e += NT, ++ne) {
             const int i = e / w, c = e - i * w;
-            if (i != k) Aug[e] -= s_f[i] * Aug[k * w + c];
+            const double prow = Aug[p * w + c] / piv;              // scaled pivot row
+            const int src = (i == k) ? p : ((i == p) ? k : i);     // row that sits at position i after the swap
+            nv[ne] = (i == k) ? prow : (Aug[src * w + c] - Aug[src * w + k] * prow);
         }
+        __syncthreads();
+        ne = 0;
+        for (int e = tid; e < m * w; e += NT, ++ne) Aug[e] = nv[ne];
         __syncthreads();
     }
     return ok;
@@ -385,16 +389,13 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     for (int e = tid; e < n * n; e += NT) s_P[e] = S.P_prop[e];
     __syncthreads();
     if (tid == 0) {
-        bool finite = true;
-        for (int t = 0; t < NTERMS; ++t) finite = finite && isfinite(s_sum[t]);
-        s_flag[1] = finite ? 1 : 0;
         int ne = (int)s_sum[91];
         ctl->n_eff = ne;
         ctl->res_mean = ne > 0 ? s_sum[90] / (double)ne : 0.0;
-        if (S.sum_out) for (int t = 0; t < NTERMS; ++t) S.sum_out[t] = s_sum[t];
     }
-    __syncthreads();
-    if (!s_flag[1]) {  // NaN guard: leave x and P untouched and stop the loop
+    if (S.sum_out && tid < NTERMS) S.sum_out[tid] = s_sum[tid];
+    const int all_finite = __syncthreads_and(tid >= NTERMS || isfinite(s_sum[tid]));
+    if (!all_finite) {  // NaN guard: leave x and P untouched and stop the loop
         if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl->unit_counter = 0; ctl->far_count = 0; }
         return;
     }

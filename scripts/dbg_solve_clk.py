@@ -14,5 +14,5 @@ for it in range(3):
     x, P, rep = F.iekf_update(pkg.State.from_array(scan["x_prior"]), np.eye(23) * 1e-4, max_iter=4)
     out = np.zeros(160)
     L.flivo_debug_sum(F.h, out.ctypes.data)
-    t = np.concatenate([out[99:100], out[98:99], out[100:116]])
-    print("trips", rep.trips, "clk deltas:", [int(b - a) for a, b in zip(t[:-1], t[1:])], "total", int(t[-1]-t[0]))
+    t = np.concatenate([out[100:101], out[102:117]])
+    print("trips", rep.trips, "ns deltas (0->2 reduce+load, ->3 finite, ->4 parts, ->5 Trows, ->6 Tcols, ->7 Aug, ->8 GJ, ->9 W, ->10 Kx, ->11 dxo, ->12 boxplus, ->13 stopjac, ...):", [int(b - a) for a, b in zip(t[:-1], t[1:])], "total", int(t[-1]-t[0]))
