@@ -422,6 +422,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
 
 __global__ void __launch_bounds__(128) k_far(FusedParams P) {
     __shared__ double s_state[24];
+    __shared__ uint2 s_queue[4][RING_QCAP];
     Ctl* ctl = P.ctl;
     if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
     const unsigned nfar = ctl->far_count;
@@ -437,7 +438,7 @@ __global__ void __launch_bounds__(128) k_far(FusedParams P) {
         float wx, wy, wz;
         world_of(s_state, __ldg(P.body + i), wx, wy, wz);
         Cand out;
-        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, max_sq_bits, lane, out, nc);
+        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, max_sq_bits, lane, out, nc, s_queue[threadIdx.x >> 5]);
         if (lane < 5) {
             float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
             if (out.d != INF_BITS) p = __ldg(P.map.buckets + out.addr);
@@ -469,6 +470,7 @@ __global__ void __launch_bounds__(128) k_far(FusedParams P) {
 // ----------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_knn(MapView map, const float4* __restrict__ q, int nq, int k, uint32_t max_sq_bits,
                                              float* out_xyz, float* out_sqd, int* out_id, int* out_count, SearchStats* stats) {
+    __shared__ uint2 s_queue[4][RING_QCAP];
     const int lane = threadIdx.x & 31;
     const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -476,7 +478,7 @@ __global__ void __launch_bounds__(128) k_knn(MapView map, const float4* __restri
         float4 p = __ldg(q + i);
         Cand out;
         unsigned nc = 0;
-        int cnt = warp_knn5_rings(map, p.x, p.y, p.z, max_sq_bits, lane, out, nc);
+        int cnt = warp_knn5_rings(map, p.x, p.y, p.z, max_sq_bits, lane, out, nc, s_queue[threadIdx.x >> 5]);
         const unsigned tot = __reduce_add_sync(FULL, nc);
         if (stats && lane == 0) atomicAdd(&stats->candidates, (unsigned long long)tot);
         int found = min(cnt, k);

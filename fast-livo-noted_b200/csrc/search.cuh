@@ -334,6 +334,23 @@ __device__ __forceinline__ unsigned long long shell_bits(int cqx, int cqy, int c
     return m;
 }
 
+// bits of the cells of block (bx,by,bz) inside the cell box [xl,xh] x [yl,yh] x [zl,zh]
+__device__ __forceinline__ unsigned range_bits(int lo_c, int hi_c, int b) {
+    const int lo = max(lo_c, b * 4) - b * 4, hi = min(hi_c, b * 4 + 3) - b * 4;
+    if (lo > hi) return 0u;
+    return ((2u << hi) - 1u) & ~((1u << lo) - 1u);
+}
+__device__ __forceinline__ unsigned long long box_bits(int xl, int xh, int yl, int yh, int zl, int zh, int bx, int by, int bz) {
+    const unsigned xm = range_bits(xl, xh, bx), ym = range_bits(yl, yh, by), zm = range_bits(zl, zh, bz);
+    unsigned yz = 0;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) if ((ym >> l) & 1u) yz |= zm << (4 * l);
+    unsigned long long mm = 0;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) if ((xm >> l) & 1u) mm |= (unsigned long long)yz << (16 * l);
+    return mm;
+}
+
 // Returns true when the shell result is final (then best holds the answer; count = number found).
 //
 // Two passes.  Pass 1 walks the <= 8 blocks of the shell and writes a per-thread work list of its occupied
@@ -372,6 +389,10 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
         }
     }
     // ---- pass 1: work list ------------------------------------------------------------------------------
+    // octant = per axis the query's own cell and the neighbour on its nearer side
+    const int oxl = min(cqx, cqx + side[0]), oxh = max(cqx, cqx + side[0]);
+    const int oyl = min(cqy, cqy + side[1]), oyh = max(cqy, cqy + side[1]);
+    const int ozl = min(cqz, cqz + side[2]), ozh = max(cqz, cqz + side[2]);
     int nA = 0, nB = 0;
     const int bx0 = (cqx - 1) >> 2, by0 = (cqy - 1) >> 2, bz0 = (cqz - 1) >> 2;
     const int nbx = ((cqx + 1) >> 2) - bx0, nby = ((cqy + 1) >> 2) - by0, nbz = ((cqz + 1) >> 2) - bz0;   // 0 or 1
@@ -381,17 +402,28 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
         const int bx = bx0 + ix, by = by0 + iy, bz = bz0 + iz;
         const int slot = dir_find(m, pack_block(bx, by, bz));
         if (slot < 0) continue;
-        unsigned long long occ = __ldg(m.blk_mask + slot) & shell_bits(cqx, cqy, cqz, bx, by, bz);
-        while (occ) {
-            const int off = __ffsll((long long)occ) - 1;
-            occ &= occ - 1;
-            const int dx = bx * 4 + ((off >> 4) & 3) - cqx, dy = by * 4 + ((off >> 2) & 3) - cqy, dz = bz * 4 + (off & 3) - cqz;
-            const bool inA = (dx == 0 || dx == side[0]) && (dy == 0 || dy == side[1]) && (dz == 0 || dz == side[2]);
+        const unsigned long long occ = __ldg(m.blk_mask + slot) & shell_bits(cqx, cqy, cqz, bx, by, bz);
+        if (!occ) continue;
+        const unsigned long long octant = box_bits(oxl, oxh, oyl, oyh, ozl, ozh, bx, by, bz);
+        const uint32_t base_idx = (uint32_t)slot * 64u;
+        unsigned long long oa = occ & octant, ob = occ & ~octant;
+        while (oa) {                                  // nearest octant: always visited, no gap needed
+            const int off = __ffsll((long long)oa) - 1;
+            oa &= oa - 1;
+            s_idx[nA * tstride] = base_idx + (uint32_t)off;
+            ++nA;
+        }
+        const int ox = bx * 4 - cqx, oy = by * 4 - cqy, oz = bz * 4 - cqz;
+        while (ob) {
+            const int off = __ffsll((long long)ob) - 1;
+            ob &= ob - 1;
+            const int dx = ((off >> 4) & 3) + ox, dy = ((off >> 2) & 3) + oy, dz = (off & 3) + oz;
             const float gap = (dx < 0 ? glo[0] : dx > 0 ? ghi[0] : 0.f) + (dy < 0 ? glo[1] : dy > 0 ? ghi[1] : 0.f) +
                               (dz < 0 ? glo[2] : dz > 0 ? ghi[2] : 0.f);
-            const int pos = inA ? nA++ : (SHELL_CELLS - 1) - nB++;
-            s_idx[pos * tstride] = (uint32_t)slot * 64u + (uint32_t)off;
-            s_gap[pos * tstride] = inA ? 0.f : gap;
+            const int pos = (SHELL_CELLS - 1) - nB;
+            ++nB;
+            s_idx[pos * tstride] = base_idx + (uint32_t)off;
+            s_gap[pos * tstride] = gap;
         }
     }
     // ---- pass 2: flat loop ------------------------------------------------------------------------------
@@ -402,7 +434,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
     const int total = nA + nB;
     for (int t = 0; t < total; ++t) {
         const int pos = (t < nA) ? t : SHELL_CELLS - 1 - (t - nA);
-        if (s_gap[pos * tstride] > __uint_as_float((uint32_t)(worst >> 32))) continue;
+        if (t >= nA && s_gap[pos * tstride] > __uint_as_float((uint32_t)(worst >> 32))) continue;
         uint32_t b = __ldg(m.cell_tab + s_idx[pos * tstride]);
         while (b != NONE32) {
             float4 p[BUCKET_SLOTS];
@@ -468,8 +500,41 @@ __device__ __forceinline__ double cell_gap_sq(double edge, int cx, int cy, int c
     return g2 * (1.0 - 1e-6);
 }
 
+// Per-warp cell queue of warp_knn5_rings (shared memory, provided by the caller): RING_QCAP entries of
+// {cell_tab index, packed cell offset from the query's cell}.
+constexpr int RING_QCHUNK = 16;                       // cells a lane enqueues per pass
+constexpr int RING_QCAP = 32 * RING_QCHUNK + 32;
+
+// scan one queued cell into the lane's sorted top five
+__device__ __forceinline__ void ring_scan_cell(const MapView& m, uint2 ent, int cqx, int cqy, int cqz, float qx, float qy, float qz,
+                                               double edge, double slack, double gworst, Top5& loc, unsigned long long& lworst,
+                                               int& lfound, unsigned& ncand) {
+    const int cx = cqx + (int)((ent.y >> 12) & 63) - 32, cy = cqy + (int)((ent.y >> 6) & 63) - 32, cz = cqz + (int)(ent.y & 63) - 32;
+    if (cell_gap_sq(edge, cx, cy, cz, qx, qy, qz, slack) > gworst) return;
+    uint32_t b = __ldg(m.cell_tab + ent.x);
+    while (b != NONE32) {
+        float4 pt[BUCKET_SLOTS];
+#pragma unroll
+        for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) pt[s2] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s2);
+        const uint32_t nxt = __ldg(m.bucket_next + b);
+#pragma unroll
+        for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) {
+            const int pid = __float_as_int(pt[s2].w);
+            if (pid < 0) continue;
+            ++ncand;
+            const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, pt[s2].x, pt[s2].y, pt[s2].z));
+            const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
+            if (key <= lworst) {
+                loc.insert(key, b * BUCKET_SLOTS + s2);
+                if (++lfound >= 5 && loc.k[4] < lworst) lworst = loc.k[4];
+            }
+        }
+        b = nxt;
+    }
+}
+
 static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits, int lane,
-                                            Cand& out, unsigned& ncand) {
+                                            Cand& out, unsigned& ncand, uint2* __restrict__ queue /* [RING_QCAP], this warp's */) {
     Top5 loc;
     loc.init();
     const int g = m.gshift;
@@ -481,12 +546,16 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
     double gworst = (double)max_sq;          // warp-uniform: squared distance beyond which a whole cell is skipped
     int lfound = 0;
     const double edge = (double)m.cell_edge;
-    for (int n = 1; n <= RING_MAX_CELLS; ++n) {
-        const int p = (n == 1) ? -1 : n - 1;
+    // radius schedule: cube 1; then, once five candidates are known, straight to the smallest cube that covers the
+    // fifth distance (one more step, guaranteed final); while fewer than five are known: cube 2, then the cube
+    // that covers the distance bound.  Each step scans cube(n) minus cube(p).
+    int p = -1, n = 1;
+    while (true) {
         const int bx0 = (cqx - n) >> 2, by0 = (cqy - n) >> 2, bz0 = (cqz - n) >> 2;
         const int nbx = ((cqx + n) >> 2) - bx0 + 1, nby = ((cqy + n) >> 2) - by0 + 1, nbz = ((cqz + n) >> 2) - bz0 + 1;
         const int nb = nbx * nby * nbz;
         const double slack = ((double)qabs + (double)(n + 1) * edge) * 4.8e-7;
+        int qn = 0;   // warp-uniform queue length
         for (int base = 0; base < nb; base += 32) {
             // stage 1: one block per lane -> directory slot and the occupancy bits of its cells in ring n
             const int bi = base + lane;
@@ -500,42 +569,31 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
                     if (slot >= 0) occ = __ldg(m.blk_mask + slot) & want;
                 }
             }
-            // stage 2: the cells of each non-empty block are dealt out one per lane
-            unsigned has = __ballot_sync(FULL, occ != 0ull);
-            while (has) {
-                const int o = __ffs(has) - 1;
-                has &= has - 1;
-                const int so = __shfl_sync(FULL, slot, o);
-                const unsigned olo = __shfl_sync(FULL, (unsigned)occ, o), ohi = __shfl_sync(FULL, (unsigned)(occ >> 32), o);
-                const int obx = __shfl_sync(FULL, bx, o), oby = __shfl_sync(FULL, by, o), obz = __shfl_sync(FULL, bz, o);
-                const int clo = __popc(olo), c = clo + __popc(ohi);
-                for (int j = lane; j < c; j += 32) {
-                    const int off = (j < clo) ? (int)__fns(olo, 0, j + 1) : 32 + (int)__fns(ohi, 0, j - clo + 1);
-                    const int cx = obx * 4 + ((off >> 4) & 3), cy = oby * 4 + ((off >> 2) & 3), cz = obz * 4 + (off & 3);
-                    if (cell_gap_sq(edge, cx, cy, cz, qx, qy, qz, slack) > gworst) continue;
-                    uint32_t b = __ldg(m.cell_tab + (size_t)so * 64 + off);
-                    while (b != NONE32) {
-                        float4 pt[BUCKET_SLOTS];
+            // stage 2: the occupied cells of all 32 blocks go through one queue so that every lane scans one cell per
+            // round, whatever block it came from
+            while (__any_sync(FULL, occ != 0ull)) {
+                const int take = min(__popcll(occ), RING_QCHUNK);
+                int pre = take;   // inclusive warp scan
 #pragma unroll
-                        for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) pt[s2] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s2);
-                        const uint32_t nxt = __ldg(m.bucket_next + b);
-#pragma unroll
-                        for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) {
-                            const int pid = __float_as_int(pt[s2].w);
-                            if (pid < 0) continue;
-                            ++ncand;
-                            const uint32_t db = __float_as_uint(sqdist3(qx, qy, qz, pt[s2].x, pt[s2].y, pt[s2].z));
-                            const unsigned long long key = ((unsigned long long)db << 32) | (uint32_t)pid;
-                            if (key <= lworst) {
-                                loc.insert(key, b * BUCKET_SLOTS + s2);
-                                if (++lfound >= 5 && loc.k[4] < lworst) lworst = loc.k[4];
-                            }
-                        }
-                        b = nxt;
-                    }
+                for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(FULL, pre, o); if (lane >= o) pre += v; }
+                const int total = __shfl_sync(FULL, pre, 31);
+                int pos = qn + pre - take;
+                for (int t = 0; t < take; ++t) {
+                    const int off = __ffsll((long long)occ) - 1;
+                    occ &= occ - 1;
+                    const int rx = bx * 4 + ((off >> 4) & 3) - cqx + 32, ry = by * 4 + ((off >> 2) & 3) - cqy + 32, rz = bz * 4 + (off & 3) - cqz + 32;
+                    queue[pos++] = make_uint2((uint32_t)slot * 64u + (uint32_t)off, (uint32_t)((rx << 12) | (ry << 6) | rz));
                 }
+                qn += total;
+                __syncwarp();
+                while (qn >= 32) {
+                    qn -= 32;
+                    ring_scan_cell(m, queue[qn + lane], cqx, cqy, cqz, qx, qy, qz, edge, slack, gworst, loc, lworst, lfound, ncand);
+                }
+                __syncwarp();
             }
         }
+        if (lane < qn) ring_scan_cell(m, queue[lane], cqx, cqy, cqz, qx, qy, qz, edge, slack, gworst, loc, lworst, lfound, ncand);
         __syncwarp();
         // merge the 32 sorted lists: rank r -> lane r
         int h = 0, count = 0;
@@ -560,10 +618,18 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
         const float cov = covered_sq(m.cell_edge, (float)n, qabs);
         const bool done = (count == 5 && __uint_as_float(d5) <= cov) || (cov >= max_sq);
         if (done) { out = res; return count; }
+        if (n >= RING_MAX_CELLS) break;
+        p = n;
         if (count == 5) {
             const unsigned long long gk = ((unsigned long long)d5 << 32) | i5;
             if (gk < lworst) lworst = gk;
             gworst = fmin(gworst, (double)__uint_as_float(d5));
+            const float need = __uint_as_float(d5);
+            do { ++n; } while (n < RING_MAX_CELLS && covered_sq(m.cell_edge, (float)n, qabs) < need);
+        } else if (n < 2) {
+            n = 2;
+        } else {
+            do { ++n; } while (n < RING_MAX_CELLS && covered_sq(m.cell_edge, (float)n, qabs) < max_sq);
         }
     }
     // not final within RING_MAX_CELLS cells: the generic search (block rings + directory sweep)
