@@ -743,11 +743,11 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
             if (nrc != 0) { ctx->err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "error"); return FLIVO_E_NCCL; }
             S.phase = SOLVE_PHASE_FROM_RANKS;
             launch_solve(S, s);
-            launches += 5;
+            launches += 6;
         } else {
             S.phase = SOLVE_PHASE_FULL;
             launch_solve(S, s);
-            launches += 4;
+            launches += 5;
         }
         return FLIVO_OK;
     };
@@ -781,7 +781,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     }
     if (use_graph) {
         CKC(cudaGraphLaunch(ctx->graph_exec, s));
-        launches = 1 + trips * 4;
+        launches = 1 + trips * 5;
     } else {
         launches = 1;
         for (int t = 0; t < trips; ++t) { int rc = launch_trip(t, timed); if (rc != FLIVO_OK) return rc; }

@@ -445,19 +445,7 @@ __global__ void __launch_bounds__(128) k_far(FusedParams P) {
             P.near[(size_t)i * 5 + lane] = p;
         }
         const uint32_t dlast = __shfl_sync(FULL, out.d, 4);
-        float4 pme = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-        if (lane < 5 && out.d != INF_BITS) pme = __ldg(P.map.buckets + out.addr);
-        float4 nbs[5];
-#pragma unroll
-        for (int r = 0; r < 5; ++r) {
-            nbs[r].x = __shfl_sync(FULL, pme.x, r); nbs[r].y = __shfl_sync(FULL, pme.y, r);
-            nbs[r].z = __shfl_sync(FULL, pme.z, r); nbs[r].w = __shfl_sync(FULL, pme.w, r);
-        }
-        if (lane == 0) {
-            const float d5 = (cnt >= 5) ? __uint_as_float(dlast) : INFINITY;
-            P.near_meta[i] = make_float2(__int_as_float(cnt), d5);
-            store_plane(P, (int)i, nbs, cnt, d5);
-        }
+        if (lane == 0) P.near_meta[i] = make_float2(__int_as_float(cnt), (cnt >= 5) ? __uint_as_float(dlast) : INFINITY);
     }
     if (P.stats) {
         const unsigned tot = __reduce_add_sync(FULL, nc);
@@ -512,9 +500,26 @@ __global__ void k_transform(const float4* __restrict__ body, int n, const double
 void launch_fused(const FusedParams& P, int grid, cudaStream_t stream) {
     k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P);
 }
+// plane + flags of the far points (one thread per far point; the warp-per-point search above would leave 31 lanes
+// idle during the fit)
+__global__ void __launch_bounds__(128) k_far_plane(FusedParams P) {
+    Ctl* ctl = P.ctl;
+    if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
+    const unsigned nfar = ctl->far_count;
+    for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < nfar; e += gridDim.x * blockDim.x) {
+        const unsigned i = P.far_list[e];
+        const float2 meta = P.near_meta[i];
+        float4 nbs[5];
+#pragma unroll
+        for (int r = 0; r < 5; ++r) nbs[r] = P.near[(size_t)i * 5 + r];
+        store_plane(P, (int)i, nbs, __float_as_int(meta.x), meta.y);
+    }
+}
+
 void launch_search(const FusedParams& P, int search_grid, int far_grid, cudaStream_t stream) {
     k_search<<<search_grid, SEARCH_THREADS, 0, stream>>>(P);   // CTAs beyond job->n idle: the grid is a capacity bucket
     k_far<<<far_grid, 128, 0, stream>>>(P);
+    k_far_plane<<<148, 128, 0, stream>>>(P);
 }
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
                 int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream) {

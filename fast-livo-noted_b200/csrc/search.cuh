@@ -506,10 +506,14 @@ constexpr int RING_QCHUNK = 16;                       // cells a lane enqueues p
 constexpr int RING_QCAP = 32 * RING_QCHUNK + 32;
 
 // scan one queued cell into the lane's sorted top five
-__device__ __forceinline__ void ring_scan_cell(const MapView& m, uint2 ent, int cqx, int cqy, int cqz, float qx, float qy, float qz,
+__device__ __forceinline__ void ring_scan_cell(const MapView& m, uint2 ent, int bx0, int by0, int bz0, int nby, int nbz,
+                                               float qx, float qy, float qz,
                                                double edge, double slack, double gworst, Top5& loc, unsigned long long& lworst,
                                                int& lfound, unsigned& ncand) {
-    const int cx = cqx + (int)((ent.y >> 12) & 63) - 32, cy = cqy + (int)((ent.y >> 6) & 63) - 32, cz = cqz + (int)(ent.y & 63) - 32;
+    // ent.x = cell_tab index (slot * 64 + cell offset in block), ent.y = linear index of the block in the step's block box
+    const int bi = (int)ent.y, off = (int)(ent.x & 63u);
+    const int cx = (bx0 + bi / (nby * nbz)) * 4 + ((off >> 4) & 3), cy = (by0 + (bi / nbz) % nby) * 4 + ((off >> 2) & 3),
+              cz = (bz0 + bi % nbz) * 4 + (off & 3);
     if (cell_gap_sq(edge, cx, cy, cz, qx, qy, qz, slack) > gworst) return;
     uint32_t b = __ldg(m.cell_tab + ent.x);
     while (b != NONE32) {
@@ -581,19 +585,18 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
                 for (int t = 0; t < take; ++t) {
                     const int off = __ffsll((long long)occ) - 1;
                     occ &= occ - 1;
-                    const int rx = bx * 4 + ((off >> 4) & 3) - cqx + 32, ry = by * 4 + ((off >> 2) & 3) - cqy + 32, rz = bz * 4 + (off & 3) - cqz + 32;
-                    queue[pos++] = make_uint2((uint32_t)slot * 64u + (uint32_t)off, (uint32_t)((rx << 12) | (ry << 6) | rz));
+                    queue[pos++] = make_uint2((uint32_t)slot * 64u + (uint32_t)off, (uint32_t)bi);
                 }
                 qn += total;
                 __syncwarp();
                 while (qn >= 32) {
                     qn -= 32;
-                    ring_scan_cell(m, queue[qn + lane], cqx, cqy, cqz, qx, qy, qz, edge, slack, gworst, loc, lworst, lfound, ncand);
+                    ring_scan_cell(m, queue[qn + lane], bx0, by0, bz0, nby, nbz, qx, qy, qz, edge, slack, gworst, loc, lworst, lfound, ncand);
                 }
                 __syncwarp();
             }
         }
-        if (lane < qn) ring_scan_cell(m, queue[lane], cqx, cqy, cqz, qx, qy, qz, edge, slack, gworst, loc, lworst, lfound, ncand);
+        if (lane < qn) ring_scan_cell(m, queue[lane], bx0, by0, bz0, nby, nbz, qx, qy, qz, edge, slack, gworst, loc, lworst, lfound, ncand);
         __syncwarp();
         // merge the 32 sorted lists: rank r -> lane r
         int h = 0, count = 0;
