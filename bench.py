@@ -267,8 +267,6 @@ def run_flivo(args, rank, world_size, local_rank):
         launches += rep.kernel_launches + (4 if args.sort_scan else 1)
         last = (k % S, x, P, rep)
     barrier()
-    t_wall1 = time.time()
-    clocks = sampler.stop(t_wall0, t_wall1)
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
     tt = torch.tensor([dev_ms, float(trips_total) * pts_per_scan, float(launches)], dtype=torch.float64, device=dev)
     if world_size > 1:
@@ -302,6 +300,8 @@ def run_flivo(args, rank, world_size, local_rank):
         x2, P2, rep2 = step_e2e(k % S)
         e2e_s += time.perf_counter() - t0
         e2e_work += rep2.trips * host_scans[k % S].shape[0]
+    t_wall1 = time.time()
+    clocks = sampler.stop(t_wall0, t_wall1)   # covers the device-resident, profile and e2e timed loops
     te = torch.tensor([e2e_s, e2e_work], dtype=torch.float64, device=dev)
     if world_size > 1:
         mx = te.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
