@@ -288,6 +288,12 @@ def run_flivo(args, rank, world_size, local_rank):
             (fused_search_ms if st.last_trip_searched[t] else fused_reuse_ms).append(st.last_fused_ms[t])
             solve_ms.append(st.last_solve_ms[t])
         far_q, cand = int(st.last_far_queries), int(st.last_candidates)
+        if k == min(args.steps, 8) - 1:
+            stamps = F.solve_stamps(repp.trips)
+            for t in range(repp.trips):
+                row = stamps[t].astype(np.int64)
+                d = [(int(row[i]) - int(row[i - 1])) / 1e3 if row[i] and row[i - 1] else None for i in range(1, 10)]
+                print(f"[solve phases trip {t}] us: reduce={d[0]} load={d[1]} manifold={d[2]} applyT={d[3]} aug={d[4]} gj={d[5]} gain={d[6]} plus+ctl={d[7]} tail={d[8]}", file=sys.stderr)
 
     # ---- e2e: host buffers through the C ABI, wall clock, H2D + D2H inside ----
     for w in range(min(args.warmup, 2)):

@@ -93,7 +93,7 @@ SYMBOLS = [
     "flivo_map_add_boxes", "flivo_map_delete_points", "flivo_map_size", "flivo_map_range", "flivo_map_flatten",
     "flivo_map_acquire_removed", "flivo_knn", "flivo_scan_upload", "flivo_scan_set_device", "flivo_h_share_model",
     "flivo_repack_v1", "flivo_iekf_update", "flivo_map_add_scan", "flivo_comm_unique_id", "flivo_comm_init",
-    "flivo_comm_destroy", "flivo_get_stats",
+    "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps",
 ]
 
 _lib = None
@@ -138,6 +138,7 @@ def lib():
     L.flivo_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
     L.flivo_comm_destroy.argtypes = [vp]
     L.flivo_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.flivo_debug_solve_stamps.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
     _lib = L
     return L
 
@@ -328,6 +329,12 @@ class Flivo:
         s = Stats()
         self._ck(self._L.flivo_get_stats(self.h, C.byref(s)))
         return s
+
+    def solve_stamps(self, trips=16):
+        """[trips][16] device globaltimer stamps (ns) of the solve kernel's phases (profile mode only)."""
+        buf = (C.c_uint64 * (trips * 16))()
+        self._ck(self._L.flivo_debug_solve_stamps(self.h, buf, trips))
+        return np.ctypeslib.as_array(buf).reshape(trips, 16).copy()
 
     def sync(self):
         self._ck(self._L.flivo_sync(self.h))

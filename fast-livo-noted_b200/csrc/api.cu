@@ -103,6 +103,10 @@ struct flivo_ctx {
     DevBlock* h_blk = nullptr;      // pinned mirror
     Ctl* d_ctl = nullptr;           // the pointers below point into d_blk
     SearchStats* d_stats = nullptr;
+    unsigned long long* d_stamps = nullptr;   // [MAX_TRIPS][16] k_solve phase stamps (profile mode)
+    SolvePre* d_pre = nullptr;                // state-only half of a trip's solve (k_solve_pre -> k_solve)
+    cudaStream_t side = nullptr;              // branch of the update graph that runs k_solve_pre beside the search
+    cudaEvent_t ev_fork[MAX_TRIPS + 1] = {}, ev_join[MAX_TRIPS + 1] = {};
     double *d_x = nullptr, *d_xprop = nullptr, *d_Pprop = nullptr, *d_Pout = nullptr, *d_sum = nullptr, *d_rank_blocks = nullptr;
     // captured launch sequence of one update (CUDA graph), re-captured only when a kernel parameter changes
     cudaGraphExec_t graph_exec = nullptr;
@@ -278,6 +282,14 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     upload_term_table();
     CKC(cudaGetLastError());
     CKC(cudaMalloc(&ctx->d_blk, sizeof(DevBlock)));
+    CKC(cudaMalloc(&ctx->d_pre, sizeof(SolvePre)));
+    CKC(cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking));
+    for (int i = 0; i <= MAX_TRIPS; ++i) {
+        CKC(cudaEventCreateWithFlags(&ctx->ev_fork[i], cudaEventDisableTiming));
+        CKC(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
+    }
+    CKC(cudaMalloc(&ctx->d_stamps, MAX_TRIPS * 16 * sizeof(unsigned long long)));
+    CKC(cudaMemset(ctx->d_stamps, 0, MAX_TRIPS * 16 * sizeof(unsigned long long)));
     CKC(cudaMemsetAsync(ctx->d_blk, 0, sizeof(DevBlock), ctx->stream));
     CKC(cudaMallocHost(&ctx->h_blk, sizeof(DevBlock)));
     memset(ctx->h_blk, 0, sizeof(DevBlock));
@@ -326,7 +338,10 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     ctx->map.release();
     free_scan(ctx);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
-    cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_rank_blocks);
+    cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_stamps); cudaFree(ctx->d_pre);
+    for (int i = 0; i <= MAX_TRIPS; ++i) { if (ctx->ev_fork[i]) cudaEventDestroy(ctx->ev_fork[i]); if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]); }
+    if (ctx->side) cudaStreamDestroy(ctx->side);
+    cudaFree(ctx->d_rank_blocks);
     if (ctx->h_blk) cudaFreeHost(ctx->h_blk);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
@@ -508,9 +523,10 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
         CKC(cudaMalloc(&ctx->d_eff, cap));
         CKC(cudaMalloc(&ctx->d_normvec, cap * sizeof(float4)));
         CKC(cudaMalloc(&ctx->d_world, cap * sizeof(float4)));
-        CKC(cudaMalloc(&ctx->d_partials, units * PSTRIDE * sizeof(double)));
-        (void)groups;
-        CKC(cudaMalloc(&ctx->d_gpartials, (size_t)std::max<size_t>(units, (size_t)ctx->sm_count * 8 + 256) * PSTRIDE * sizeof(double)));   // one record per CTA of k_fused
+        const size_t max_grid = (size_t)ctx->sm_count * 8 + 256;   // >= any fused_grid()
+        groups = max_grid / FOLD_CTAS + 1;
+        CKC(cudaMalloc(&ctx->d_partials, max_grid * PSTRIDE * sizeof(double)));   // one record per CTA of k_fused
+        CKC(cudaMalloc(&ctx->d_gpartials, groups * PSTRIDE * sizeof(double)));   // one record per FOLD_CTAS CTAs
         CKC(cudaMalloc(&ctx->d_group_cnt, groups * sizeof(unsigned int)));
         CKC(cudaMalloc(&ctx->d_far_list, cap * sizeof(unsigned int)));
         CKC(cudaMalloc(&ctx->d_plane, cap * sizeof(float4)));
@@ -587,7 +603,7 @@ static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, d
     Job& j = ctx->h_blk->job;
     j.n = (int)ctx->scan_n;
     j.units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
-    j.groups = fused_grid(ctx);   // per-CTA records of k_fused summed by k_solve
+    j.groups = (fused_grid(ctx) + FOLD_CTAS - 1) / FOLD_CTAS;   // group records of k_fused summed by k_solve
     j.mode = mode; j.max_iter = max_iter; j.force_search = force_search; j.nranks = ctx->nranks; j.max_sq_bits = max_sq_bits; j.aux_out = aux_out;
     j.R = R;
     for (int i = 0; i < 23; ++i) j.limit[i] = limit23 ? limit23[i] : 0.001;
@@ -704,6 +720,34 @@ extern "C" int flivo_repack_v1(const double HTH[144], const double HTz[12], doub
     return FLIVO_OK;
 }
 
+// One update as a CUDA graph: the fixed sequence of max_iter+1 trips captured from the stream; kernels of skipped
+// phases (re-use trips, trips after the stop) exit at once.  (A device-side WHILE/IF conditional graph was measured
+// slower, profiles/r1_ab_launch_structure.txt.)
+static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveParams& S0, int sgrid, int fgrid, int far_grid, int trips) {
+    cudaStream_t s = ctx->stream;
+    cudaGraph_t g = nullptr;
+    CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    SolveParams S = S0;
+    S.phase = SOLVE_PHASE_FULL;
+    for (int t = 0; t < trips && t <= MAX_TRIPS; ++t) {
+        // fork: the state-only half of the solve runs beside the search / fused kernels of the trip
+        CKC(cudaEventRecord(ctx->ev_fork[t], s));
+        CKC(cudaStreamWaitEvent(ctx->side, ctx->ev_fork[t], 0));
+        launch_solve_pre(S, ctx->side);
+        CKC(cudaEventRecord(ctx->ev_join[t], ctx->side));
+        launch_search(P, sgrid, far_grid, s);
+        launch_fused(P, fgrid, s);
+        CKC(cudaStreamWaitEvent(s, ctx->ev_join[t], 0));
+        launch_solve(S, s);
+    }
+    cudaError_t ce = cudaStreamEndCapture(s, &g);
+    if (ce != cudaSuccess) { ctx->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
+    ce = cudaGraphInstantiate(&ctx->graph_exec, g, 0);
+    cudaGraphDestroy(g);
+    if (ce != cudaSuccess) { ctx->graph_exec = nullptr; ctx->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
+    return FLIVO_OK;
+}
+
 extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm, const flivo_cfg* cfg, flivo_report* rep) {
     ENTER();
     NEED(inout && Pm && cfg, FLIVO_E_ARG, "null state / P / cfg");
@@ -729,9 +773,12 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job;
     S.x = ctx->d_x; S.x_prop = ctx->d_xprop; S.P_prop = ctx->d_Pprop; S.P_out = ctx->d_Pout;
     S.sum_out = ctx->d_sum; S.rank_blocks = ctx->d_rank_blocks; S.ctl = ctx->d_ctl;
+    S.stamps = timed ? ctx->d_stamps : nullptr;
+    S.pre = ctx->d_pre;
     const int sgrid = search_grid(ctx), fgrid = fused_grid(ctx), far_grid = ctx->sm_count * 8;
     int launches = 1;
     auto launch_trip = [&](int t, bool with_events) -> int {
+        launch_solve_pre(S, s);                 // plain launches: in line (the graph runs it on a parallel branch)
         if (with_events) CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
         launch_search(P, sgrid, far_grid, s);   // both kernels exit at once on re-use trips
         launch_fused(P, fgrid, s);
@@ -743,11 +790,11 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
             if (nrc != 0) { ctx->err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "error"); return FLIVO_E_NCCL; }
             S.phase = SOLVE_PHASE_FROM_RANKS;
             launch_solve(S, s);
-            launches += 6;
+            launches += 7;
         } else {
             S.phase = SOLVE_PHASE_FULL;
             launch_solve(S, s);
-            launches += 5;
+            launches += 6;
         }
         return FLIVO_OK;
     };
@@ -762,16 +809,8 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
                 use_graph = false;   // parameters keep changing (e.g. a new external scan pointer every call): plain launches
             } else {
                 if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
-                cudaGraph_t g = nullptr;
-                CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-                int rc = FLIVO_OK;
-                for (int t = 0; t < trips && rc == FLIVO_OK; ++t) rc = launch_trip(t, false);
-                cudaError_t ce = cudaStreamEndCapture(s, &g);
-                if (rc != FLIVO_OK) { if (g) cudaGraphDestroy(g); return rc; }
-                if (ce != cudaSuccess) { ctx->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
-                ce = cudaGraphInstantiate(&ctx->graph_exec, g, 0);
-                cudaGraphDestroy(g);
-                if (ce != cudaSuccess) { ctx->graph_exec = nullptr; ctx->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
+                int rc = build_update_graph(ctx, P, S, sgrid, fgrid, far_grid, trips);
+                if (rc != FLIVO_OK) return rc;
                 ctx->graph_P = P; ctx->graph_S = S; ctx->graph_search_grid = sgrid; ctx->graph_fused_grid = fgrid; ctx->graph_trips = trips;
                 launches = 1;
             }
@@ -781,7 +820,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     }
     if (use_graph) {
         CKC(cudaGraphLaunch(ctx->graph_exec, s));
-        launches = 1 + trips * 5;
+        launches = 1 + trips * 6;
     } else {
         launches = 1;
         for (int t = 0; t < trips; ++t) { int rc = launch_trip(t, timed); if (rc != FLIVO_OK) return rc; }
@@ -886,4 +925,14 @@ extern "C" int flivo_get_stats(flivo_ctx* ctx, flivo_stats* out) {
     ctx->stats.bucket_capacity = (int64_t)ctx->map.bucket_cap();
     *out = ctx->stats;
     return map_rc(ctx, rc);
+}
+
+// Diagnostic: globaltimer stamps (ns) at the phase boundaries of k_solve for each trip of the last update that ran
+// with FLIVO_CFG_PROFILE.  out: [trips][16]; entries 0..9 are used (see k_solve), 0 where a phase did not run.
+extern "C" int flivo_debug_solve_stamps(flivo_ctx* ctx, uint64_t* out, int trips_cap) {
+    if (!ctx || !out || trips_cap <= 0) return FLIVO_E_ARG;
+    if (trips_cap > MAX_TRIPS) trips_cap = MAX_TRIPS;
+    CKC(cudaMemcpyAsync(out, ctx->d_stamps, (size_t)trips_cap * 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
 }

@@ -335,7 +335,33 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         double sum = s_ht[0][e];
 #pragma unroll
         for (int wv = 1; wv < UNIT_WARPS; ++wv) sum += s_ht[wv][e];
-        P.gpartials[(size_t)blockIdx.x * PSTRIDE + t] = sum;
+        P.partials[(size_t)blockIdx.x * PSTRIDE + t] = sum;
+    }
+    // ---- second level: the last CTA of each group of FOLD_CTAS to arrive adds the group's records in CTA order
+    // (the result does not depend on which CTA that is), so the single-CTA solve reads grid/16 records, not grid.
+    __shared__ unsigned s_last;
+    __threadfence();
+    __syncthreads();
+    const unsigned grp = blockIdx.x / FOLD_CTAS;
+    const unsigned members = min((unsigned)FOLD_CTAS, gridDim.x - grp * FOLD_CTAS);
+    if (threadIdx.x == 0) {
+        const unsigned ticket = atomicAdd(P.group_cnt + grp, 1u);
+        s_last = (ticket == members - 1) ? 1u : 0u;
+        if (s_last) P.group_cnt[grp] = 0;   // ready for the next launch
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        if (threadIdx.x < NTERMS) {
+            const double* src = P.partials + (size_t)grp * FOLD_CTAS * PSTRIDE + threadIdx.x;
+            double v[FOLD_CTAS];
+#pragma unroll
+            for (int m = 0; m < FOLD_CTAS; ++m) v[m] = (m < (int)members) ? __ldcg(src + (size_t)m * PSTRIDE) : 0.0;
+            double sum = v[0];
+#pragma unroll
+            for (int m = 1; m < FOLD_CTAS; ++m) if (m < (int)members) sum += v[m];
+            P.gpartials[(size_t)grp * PSTRIDE + threadIdx.x] = sum;
+        }
     }
 }
 

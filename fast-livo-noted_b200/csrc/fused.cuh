@@ -8,7 +8,8 @@ constexpr int UNIT_WARPS = 4;                    // warps per CTA of the fused k
 constexpr int UNIT_POINTS = UNIT_WARPS * 32;     // scan points per work unit
 constexpr int NTERMS = 92;                       // 78 (H^T H upper) + 12 (H^T z) + res_sum + n_eff
 constexpr int PSTRIDE = 96;                      // doubles per partial record
-constexpr int GROUP_UNITS = 32;                  // units folded by the last-arriving CTA of a group
+constexpr int GROUP_UNITS = 32;                  // (capacity sizing of group_cnt)
+constexpr int FOLD_CTAS = 16;                    // CTA records of k_fused folded into one group record by the last CTA of the group
 constexpr int MAX_TRIPS = 16;
 
 // Device-resident control block of one iterated update (written by the solve kernel, read by the fused kernel).
@@ -34,7 +35,7 @@ struct Ctl {
 // its kernel parameters: a call only rewrites this block (one H2D copy together with the state and P).
 struct Job {
     int n;                     // scan points
-    int units, groups;         // work units of 128 points / groups of GROUP_UNITS units
+    int units, groups;         // work units of 128 points / group records k_solve sums (= ceil(fused grid / FOLD_CTAS))
     int mode;                  // FLIVO_MODE_*
     int max_iter;
     int force_search;
@@ -64,9 +65,9 @@ struct FusedParams {
     float4* normvec;           // [n] (nx,ny,nz,pd2)
     float4* world;             // [n] feats_down_world
     unsigned int* far_list;    // [n] points the 27-cell shell could not finish (k_search -> k_far)
-    double* partials;          // [units * PSTRIDE]
-    double* gpartials;         // [groups * PSTRIDE]
-    unsigned int* group_cnt;   // [groups]
+    double* partials;          // [fused grid * PSTRIDE] one record per CTA of k_fused
+    double* gpartials;         // [groups * PSTRIDE] records folded FOLD_CTAS at a time (fixed order), read by k_solve
+    unsigned int* group_cnt;   // [groups] arrival tickets; the folding CTA resets its entry
     Ctl* ctl;
     SearchStats* stats;
 };

@@ -272,47 +272,50 @@ __device__ void apply_T_cols(double* M, int n, const BlockT& T, int tid, int nth
     }
 }
 
-// Solve S^T X = B in place by Gauss-Jordan with partial pivoting, the whole CTA on the m x w array in shared
-// memory (w = m + nrhs): one element per thread in the elimination, five barriers per pivot.  (A single warp
-// holding the matrix in registers was measured ~10x slower here: k_solve is one cold CTA and its time is set by
-// dependent-instruction and instruction-fetch latency, so short rolled loops over all threads win.)
-// Aug holds [S^T | B]; on return the right part holds X.  First maximum wins pivot ties.  Returns false on a zero pivot.
-__device__ bool block_gauss_jordan(double* Aug, int m, int w, double* s_f /*[16]*/, int* s_piv, int tid, int NT) {
+// Solve S^T X = B by Gauss-Jordan with partial pivoting, the whole CTA on the m x w array [S^T | B] (w = m + nrhs)
+// in shared memory.  k_solve is one cold CTA: its time is dependent-instruction latency, so the step of one pivot is
+// arranged as ONE barrier interval.  Every thread owns one element, computes its new value from the OLD matrix (the
+// row swap p <-> k is applied by index) and writes it to the other of two buffers; the thread -> column mapping
+// rotates with the pivot so that the next pivot column always lands in lanes 0..m-1 of warp 0, which pick the next
+// pivot row straight from registers (three hardware warp reductions: non-negative doubles order like their bit
+// patterns) before the barrier.  Same operations per entry as the textbook order: pivot row scaled by 1/piv (a
+// division), other rows  a_ic - a_ik * (scaled pivot row)_c;  first maximum wins pivot ties.
+// Returns the buffer that holds [ . | X ]; *ok = false on a zero pivot.
+__device__ __forceinline__ void gj_pick(bool cand, double v, int lane, int* s_piv, double* s_mag) {
     const unsigned FULLM = 0xFFFFFFFFu;
+    const unsigned long long bits = cand ? (unsigned long long)__double_as_longlong(fabs(v)) : 0ull;
+    const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
+    const unsigned mhi = __reduce_max_sync(FULLM, cand ? hi : 0u);
+    const unsigned mlo = __reduce_max_sync(FULLM, (cand && hi == mhi) ? lo : 0u);
+    const unsigned idx = __reduce_min_sync(FULLM, (cand && hi == mhi && lo == mlo) ? (unsigned)lane : 0xFFFFFFFFu);
+    if (lane == 0) { *s_piv = (int)idx; *s_mag = __longlong_as_double((long long)(((unsigned long long)mhi << 32) | mlo)); }
+}
+__device__ const double* block_gauss_jordan(double* A0, double* A1, int m, int w, double* s_mag /*[2]*/, int* s_piv /*[2]*/, int tid, bool* ok_out) {
     bool ok = true;
+    if (tid < 32) gj_pick(tid < m, tid < m ? A0[tid * w] : 0.0, tid, &s_piv[0], &s_mag[0]);
+    __syncthreads();
+    const bool active = tid < m * w;
+    const int slot = tid / m, i = tid - slot * m;
+    double* cur = A0;
+    double* nxt = A1;
     for (int k = 0; k < m; ++k) {
-        // pivot row: first maximum of |Aug[i][k]|, i >= k.  Non-negative doubles order like their bit patterns, so three
-        // hardware warp reductions (high word, low word, lowest index) replace a shuffle tree.
-        if (tid < 32) {
-            const bool cand = tid >= k && tid < m;
-            const unsigned long long bits = cand ? (unsigned long long)__double_as_longlong(fabs(Aug[tid * w + k])) : 0ull;
-            const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
-            const unsigned mhi = __reduce_max_sync(FULLM, cand ? hi : 0u);
-            const unsigned mlo = __reduce_max_sync(FULLM, (cand && hi == mhi) ? lo : 0u);
-            const unsigned idx = __reduce_min_sync(FULLM, (cand && hi == mhi && lo == mlo) ? (unsigned)tid : 0xFFFFFFFFu);
-            if (tid == 0) { *s_piv = (int)idx; s_f[15] = __longlong_as_double((long long)(((unsigned long long)mhi << 32) | mlo)); }
-        }
-        __syncthreads();
-        const int p = *s_piv;
-        if (s_f[15] == 0.0) ok = false;
-        // every thread computes the new value of its element from the OLD matrix (row swap p <-> k applied by index),
-        // then all write: two barriers instead of one per sub-step.  Same operations per entry as the textbook order:
-        // pivot row scaled by 1/piv (a division), other rows  a_ic - a_ik * (scaled pivot row)_c.
-        const double piv = Aug[p * w + k];
-        double nv[2];
-        int ne = 0;
-        for (int e = tid; e < m * w; e += NT, ++ne) {
-            const int i = e / w, c = e - i * w;
-            const double prow = Aug[p * w + c] / piv;              // scaled pivot row
+        const int p = s_piv[k & 1];
+        if (s_mag[k & 1] == 0.0) ok = false;
+        double nv = 0.0;
+        if (active) {
+            int c = slot + k + 1;                                  // slot 0 <-> column k+1, the next pivot column
+            if (c >= w) c -= w;
+            const double prow = cur[p * w + c] / cur[p * w + k];   // scaled pivot row
             const int src = (i == k) ? p : ((i == p) ? k : i);     // row that sits at position i after the swap
-            nv[ne] = (i == k) ? prow : (Aug[src * w + c] - Aug[src * w + k] * prow);
+            nv = (i == k) ? prow : (cur[src * w + c] - cur[src * w + k] * prow);
+            nxt[i * w + c] = nv;
         }
+        if (tid < 32 && k + 1 < m) gj_pick(tid < m && tid > k, nv, tid, &s_piv[(k + 1) & 1], &s_mag[(k + 1) & 1]);
         __syncthreads();
-        ne = 0;
-        for (int e = tid; e < m * w; e += NT, ++ne) Aug[e] = nv[ne];
-        __syncthreads();
+        double* t = cur; cur = nxt; nxt = t;
     }
-    return ok;
+    *ok_out = ok;
+    return cur;
 }
 
 // ---- fixed-order final reduction of the group partials ------------------------------------------------------
@@ -339,6 +342,16 @@ __device__ void reduce_groups(const double* __restrict__ gpartials, int groups, 
 
 constexpr int SOLVE_THREADS = 768;  // 8 slices x 96
 
+__device__ __forceinline__ void stamp(const SolveParams& S, const Ctl* ctl, int k, int back = 0) {
+    if (S.stamps && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        int trip = ctl->trips - back;   // back = 1 once this trip has been counted
+        trip = trip < 0 ? 0 : (trip < MAX_TRIPS ? trip : MAX_TRIPS - 1);
+        S.stamps[trip * 16 + k] = t;
+    }
+}
+
 __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     __shared__ double s_slices[8 * PSTRIDE];
     __shared__ double s_sum[PSTRIDE];
@@ -346,17 +359,18 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     __shared__ double s_z[12];
     __shared__ double s_P[23 * 23];
     __shared__ double s_L[23 * 23];
-    __shared__ double s_Aug[12 * 35];
+    __shared__ double s_Aug[12 * 35], s_Aug2[12 * 35];   // Gauss-Jordan ping-pong
     __shared__ double s_W[23 * 12];
     __shared__ double s_Kx[23 * 12];
     __shared__ double s_x[36], s_xp[36];
-    __shared__ double s_dx[23], s_dxnew[23], s_dxo[23], s_Kh[23];
+    __shared__ double s_dxnew[23], s_dxo[23], s_Kh[23];
     __shared__ BlockT s_T;
     __shared__ int s_flag[4];  // [0]=stop, [1]=ok, [2]=pivot row
     __shared__ double s_gjf[16];
 
     Ctl* ctl = S.ctl;
     const int tid = threadIdx.x, NT = blockDim.x;
+    stamp(S, ctl, 0);
     if (S.phase != SOLVE_PHASE_REDUCE_ONLY && ctl->stopped) return;
 
     // ---- 0. normal equations -------------------------------------------------------------------------
@@ -371,6 +385,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     } else {
         reduce_groups(S.gpartials, S.job->groups, s_slices, s_sum, tid, NT);
     }
+    stamp(S, ctl, 1);
     if (S.phase == SOLVE_PHASE_REDUCE_ONLY) {
         if (tid < NTERMS) S.sum_out[tid] = s_sum[tid];
         if (tid == 0) { ctl->unit_counter = 0; ctl->far_count = 0; }
@@ -386,7 +401,11 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     if (tid < 36) { s_x[tid] = S.x[tid]; s_xp[tid] = S.x_prop[tid]; }
     const int mode = S.job->mode;
     const int n = (mode == 1) ? 18 : 23;
-    for (int e = tid; e < n * n; e += NT) s_P[e] = S.P_prop[e];
+    {   // the state-only half of this trip was prepared by k_solve_pre while the search / fused kernels ran
+        const double* Psrc = (mode == 1) ? S.P_prop : S.pre->Pt;
+        for (int e = tid; e < n * n; e += NT) s_P[e] = Psrc[e];
+        if (tid < 23) s_dxnew[tid] = S.pre->dxnew[tid];
+    }
     __syncthreads();
     if (tid == 0) {
         int ne = (int)s_sum[91];
@@ -400,27 +419,11 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         return;
     }
 
+    stamp(S, ctl, 2);
+    stamp(S, ctl, 3);   // (3, 4: the manifold / T P T^T phases moved to k_solve_pre)
+    stamp(S, ctl, 4);
     if (mode == 0) {
         // ================= V3: esekfom.hpp:1633-1927 ==================================================
-        if ((tid & 31) == 0 && tid < 96) {
-            const int part = tid >> 5;                                        // three warps, one lane each
-            d_boxminus_v3_part(s_x, s_xp, s_dx, part);                        // :1646
-            if (part == 0) {
-                for (int i = 0; i < 6; ++i) s_dxnew[i] = s_dx[i];
-                d_so3_jac(s_dx + 3, s_T.J3, s_dxnew + 3);                     // :1663
-            } else if (part == 1) {
-                for (int i = 6; i < 21; ++i) s_dxnew[i] = s_dx[i];
-                d_so3_jac(s_dx + 6, s_T.J6, s_dxnew + 6);
-            } else {
-                s_dxnew[21] = s_dx[21]; s_dxnew[22] = s_dx[22];
-                d_s2_jac(s_x + S_GRAV, s_xp + S_GRAV, s_dx + 21, s_T.J2, s_dxnew + 21);   // :1684-1686
-            }
-        }
-        __syncthreads();
-        apply_T_rows(s_P, 23, 23, s_T, tid, NT);                              // :1665-1672, :1688-1695
-        __syncthreads();
-        apply_T_cols(s_P, 23, s_T, tid, NT);
-        __syncthreads();
         // Aug = [S^T | Q1^T],  S = I + HTH * Q11,  Q = P / R
         const double invR = 1.0 / S.job->R;
         for (int e = tid; e < 12 * 35; e += NT) {
@@ -437,13 +440,13 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_Aug[e] = v;
         }
         __syncthreads();
-        {
-            const bool ok = block_gauss_jordan(s_Aug, 12, 35, s_gjf, &s_flag[2], tid, NT);
-            if (tid == 0) s_flag[1] = ok ? 1 : 0;
-        }
-        __syncthreads();
+        stamp(S, ctl, 5);
+        bool gj_ok;
+        const double* X = block_gauss_jordan(s_Aug, s_Aug2, 12, 35, s_gjf, &s_flag[2], tid, &gj_ok);
+        if (tid == 0) s_flag[1] = gj_ok ? 1 : 0;
+        stamp(S, ctl, 6);
         // W[i][a] = X[a][i];  K_h = W * HTz (:1801);  K_x[:, :12] = W * HTH (:1806)
-        for (int e = tid; e < 23 * 12; e += NT) { int i = e / 12, a = e % 12; s_W[e] = s_Aug[a * 35 + 12 + i]; }
+        for (int e = tid; e < 23 * 12; e += NT) { int i = e / 12, a = e % 12; s_W[e] = X[a * 35 + 12 + i]; }
         __syncthreads();
         for (int e = tid; e < 23 * 12; e += NT) {
             int i = e / 12, b = e % 12;
@@ -463,6 +466,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_dxo[tid] = s - s_dxnew[tid];
         }
         __syncthreads();
+        stamp(S, ctl, 7);
         if ((tid & 31) == 0 && tid < 96) d_boxplus_v3_part(s_x, s_dxo, tid >> 5);   // :1814
         if (tid == 128) {
             int converge = 1;
@@ -485,6 +489,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_flag[0] = stop;
         }
         __syncthreads();
+        stamp(S, ctl, 8, 1);
         if (s_flag[0] && (tid & 31) == 0 && tid < 96) {
             const int part = tid >> 5;
             if (part == 0) d_so3_jac(s_dxo + 3, s_T.J3, nullptr);             // :1842
@@ -509,6 +514,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
                 S.P_out[e] = s_L[e] - s;
             }
         }
+        stamp(S, ctl, 9, 1);
     } else {
         // ================= V1: src/laser_mapping.cpp:178-238 ==========================================
         // HPH (6x6) = Hsub^T (1/R) Hsub with Hsub = [A | n] = V3 columns [3:6 | 0:3]  (:584-586)
@@ -520,21 +526,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_H6[tid] = s_H[map6[a] * 12 + map6[b]] * w;
             if (tid < 6) s_z6[tid] = s_z[map6[tid]] * w;
         }
-        if (tid == 0) {
-            // vec = state_propagat - state (common_lib.h:576-587)
-            double rotd[9];
-            for (int i = 0; i < 3; ++i)
-                for (int j = 0; j < 3; ++j)
-                    rotd[i * 3 + j] = s_x[S_ROT + i] * s_xp[S_ROT + j] + s_x[S_ROT + 3 + i] * s_xp[S_ROT + 3 + j] + s_x[S_ROT + 6 + i] * s_xp[S_ROT + 6 + j];
-            d_Log_v1(rotd, s_vec);
-            for (int i = 0; i < 3; ++i) {
-                s_vec[3 + i] = s_xp[S_POS + i] - s_x[S_POS + i];
-                s_vec[6 + i] = s_xp[S_VEL + i] - s_x[S_VEL + i];
-                s_vec[9 + i] = s_xp[S_BG + i] - s_x[S_BG + i];
-                s_vec[12 + i] = s_xp[S_BA + i] - s_x[S_BA + i];
-                s_vec[15 + i] = s_xp[S_GRAV + i] - s_x[S_GRAV + i];
-            }
-        }
+        if (tid < 18) s_vec[tid] = S.pre->vec[tid];   // state_propagat - state, from k_solve_pre
         __syncthreads();
         // Aug (6 x 24) = [S^T | C1^T],  S = I + H6 * C11,  C = state.cov
         for (int e = tid; e < 6 * 24; e += NT) {
@@ -550,12 +542,10 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             s_Aug[e] = v;
         }
         __syncthreads();
-        {
-            const bool ok = block_gauss_jordan(s_Aug, 6, 24, s_gjf, &s_flag[2], tid, NT);
-            if (tid == 0) s_flag[1] = ok ? 1 : 0;
-        }
-        __syncthreads();
-        for (int e = tid; e < 18 * 6; e += NT) { int i = e / 6, a = e % 6; s_W[e] = s_Aug[a * 24 + 6 + i]; }  // K_1[:, :6]
+        bool gj_ok;
+        const double* X = block_gauss_jordan(s_Aug, s_Aug2, 6, 24, s_gjf, &s_flag[2], tid, &gj_ok);
+        if (tid == 0) s_flag[1] = gj_ok ? 1 : 0;
+        for (int e = tid; e < 18 * 6; e += NT) { int i = e / 6, a = e % 6; s_W[e] = X[a * 24 + 6 + i]; }  // K_1[:, :6]
         __syncthreads();
         for (int e = tid; e < 18 * 6; e += NT) {                             // G[:, :6] = K_1[:, :6] * HPH (:191)
             int i = e / 6, b = e % 6;
@@ -611,6 +601,61 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         }
     }
 }
+
+
+// ---- state-only half of the solve (see SolvePre) ---------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_solve_pre(SolveParams S) {
+    __shared__ double s_P[23 * 23];
+    __shared__ double s_x[36], s_xp[36];
+    __shared__ double s_dx[23], s_dxnew[23];
+    __shared__ BlockT s_T;
+    const Ctl* ctl = S.ctl;
+    if (ctl->stopped) return;
+    const int tid = threadIdx.x, NT = blockDim.x;
+    const int mode = S.job->mode;
+    if (tid < 36) { s_x[tid] = S.x[tid]; s_xp[tid] = S.x_prop[tid]; }
+    if (mode == 0) for (int e = tid; e < 23 * 23; e += NT) s_P[e] = S.P_prop[e];
+    __syncthreads();
+    if (mode == 0) {
+        if ((tid & 31) == 0 && tid < 96) {
+            const int part = tid >> 5;                                        // three warps, one lane each
+            d_boxminus_v3_part(s_x, s_xp, s_dx, part);                        // esekfom.hpp:1646
+            if (part == 0) {
+                for (int i = 0; i < 6; ++i) s_dxnew[i] = s_dx[i];
+                d_so3_jac(s_dx + 3, s_T.J3, s_dxnew + 3);                     // :1663
+            } else if (part == 1) {
+                for (int i = 6; i < 21; ++i) s_dxnew[i] = s_dx[i];
+                d_so3_jac(s_dx + 6, s_T.J6, s_dxnew + 6);
+            } else {
+                s_dxnew[21] = s_dx[21]; s_dxnew[22] = s_dx[22];
+                d_s2_jac(s_x + S_GRAV, s_xp + S_GRAV, s_dx + 21, s_T.J2, s_dxnew + 21);   // :1684-1686
+            }
+        }
+        __syncthreads();
+        apply_T_rows(s_P, 23, 23, s_T, tid, NT);                              // :1665-1672, :1688-1695
+        __syncthreads();
+        apply_T_cols(s_P, 23, s_T, tid, NT);
+        __syncthreads();
+        for (int e = tid; e < 23 * 23; e += NT) S.pre->Pt[e] = s_P[e];
+        if (tid < 23) S.pre->dxnew[tid] = s_dxnew[tid];
+    } else if (tid == 0) {
+        // vec = state_propagat - state (common_lib.h:576-587)
+        double rotd[9], vec[18];
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j)
+                rotd[i * 3 + j] = s_x[S_ROT + i] * s_xp[S_ROT + j] + s_x[S_ROT + 3 + i] * s_xp[S_ROT + 3 + j] + s_x[S_ROT + 6 + i] * s_xp[S_ROT + 6 + j];
+        d_Log_v1(rotd, vec);
+        for (int i = 0; i < 3; ++i) {
+            vec[3 + i] = s_xp[S_POS + i] - s_x[S_POS + i];
+            vec[6 + i] = s_xp[S_VEL + i] - s_x[S_VEL + i];
+            vec[9 + i] = s_xp[S_BG + i] - s_x[S_BG + i];
+            vec[12 + i] = s_xp[S_BA + i] - s_x[S_BA + i];
+            vec[15 + i] = s_xp[S_GRAV + i] - s_x[S_GRAV + i];
+        }
+        for (int i = 0; i < 18; ++i) S.pre->vec[i] = vec[i];
+    }
+}
+void launch_solve_pre(const SolveParams& S, cudaStream_t stream) { k_solve_pre<<<1, 256, 0, stream>>>(S); }
 
 void launch_solve(const SolveParams& S, cudaStream_t stream) { k_solve<<<1, SOLVE_THREADS, 0, stream>>>(S); }
 

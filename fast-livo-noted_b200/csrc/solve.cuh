@@ -10,6 +10,15 @@ enum {
     SOLVE_PHASE_FROM_RANKS = 2    // sum rank_blocks[nranks][96] in rank order, then solve (second half, multi-GPU)
 };
 
+// State-only half of a trip's solve, computed by k_solve_pre on a parallel branch of the update graph while the
+// search / fused kernels of the same trip run (it needs x and P_prop, not H^T H).
+struct SolvePre {
+    double Pt[23 * 23];   // V3: P_prop with the manifold Jacobians applied, T P T^T (esekfom.hpp:1665-1695)
+    double dxnew[23];     // V3: J^{-1}-corrected x (-) x_prop (:1646-1686)
+    double vec[18];       // V1: state_propagat - state (common_lib.h:576-587)
+    double pad;
+};
+
 struct SolveParams {
     const double* gpartials;   // [groups * PSTRIDE]
     const Job* job;
@@ -21,6 +30,8 @@ struct SolveParams {
     double* sum_out;           // [96] reduced block (may be null in FULL phase)
     const double* rank_blocks; // [nranks * PSTRIDE]
     Ctl* ctl;
+    SolvePre* pre;             // written by k_solve_pre, read by k_solve of the same trip
+    unsigned long long* stamps;       // profile mode only: [MAX_TRIPS][16] globaltimer values at the phase boundaries of k_solve
 };
 
 void upload_term_table();
@@ -29,6 +40,7 @@ void launch_search(const FusedParams& P, int search_grid, int far_grid, cudaStre
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
                 int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream);
 void launch_transform(const float4* body, int n, const double* state, float4* world, cudaStream_t stream);
+void launch_solve_pre(const SolveParams& S, cudaStream_t stream);   // before launch_solve of the same trip (FULL / FROM_RANKS)
 void launch_solve(const SolveParams& S, cudaStream_t stream);
 void launch_ctl_reset(const double* x, double* x_prop, const double* P_prop, double* P_out, Ctl* ctl, SearchStats* stats, cudaStream_t stream);
 

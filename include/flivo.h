@@ -184,6 +184,9 @@ typedef struct flivo_stats {
     int32_t last_trip_searched[16];
 } flivo_stats;
 int flivo_get_stats(flivo_ctx* ctx, flivo_stats* out);
+/* Diagnostic only (no reference counterpart): device globaltimer stamps (ns) at the phase boundaries of the solve
+ * kernel, [trips_cap][16], of the last flivo_iekf_update that ran with FLIVO_CFG_PROFILE. */
+int flivo_debug_solve_stamps(flivo_ctx* ctx, uint64_t* out, int trips_cap);
 
 #ifdef __cplusplus
 }
