@@ -93,7 +93,7 @@ struct flivo_ctx {
     float4 *d_normvec = nullptr, *d_world = nullptr;
     double *d_partials = nullptr, *d_gpartials = nullptr;
     unsigned int* d_group_cnt = nullptr;
-    unsigned int* d_far_list = nullptr;
+    unsigned long long* d_far_list = nullptr;
     float4* d_plane = nullptr;
     unsigned char* d_pflags = nullptr;
     void* d_out = nullptr;          // un-permute scratch for optional outputs
@@ -112,6 +112,7 @@ struct flivo_ctx {
     cudaGraphExec_t graph_exec = nullptr;
     FusedParams graph_P{};
     SolveParams graph_S{};
+    int search_resident = 0;        // CTAs of k_search resident on the whole GPU
     int graph_search_grid = 0, graph_fused_grid = 0, graph_trips = 0, graph_churn = 0;
     cudaEvent_t ev[2 * MAX_TRIPS + 2] = {};
     flivo_stats stats{};
@@ -194,7 +195,7 @@ static bool stride_ok(size_t s) { return s >= 12 && (s % 4) == 0; }
 
 // ---- small kernels of the plumbing layer ------------------------------------------------------------------
 __global__ void k_ctl_set(Ctl* ctl, int search) {
-    if (threadIdx.x == 0) { ctl->search = search; ctl->stopped = 0; ctl->unit_counter = 0; ctl->far_count = 0; }
+    if (threadIdx.x == 0) { ctl->search = search; ctl->stopped = 0; ctl_next_trip(ctl); }
 }
 // Morton key of the scan point's cell in the lidar frame (a rigid transform preserves locality, so points
 // that are neighbours here query neighbouring map cells whatever the state is)
@@ -528,7 +529,8 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
         CKC(cudaMalloc(&ctx->d_partials, max_grid * PSTRIDE * sizeof(double)));   // one record per CTA of k_fused
         CKC(cudaMalloc(&ctx->d_gpartials, groups * PSTRIDE * sizeof(double)));   // one record per FOLD_CTAS CTAs
         CKC(cudaMalloc(&ctx->d_group_cnt, groups * sizeof(unsigned int)));
-        CKC(cudaMalloc(&ctx->d_far_list, cap * sizeof(unsigned int)));
+        CKC(cudaMalloc(&ctx->d_far_list, cap * sizeof(unsigned long long)));
+        CKC(cudaMemsetAsync(ctx->d_far_list, 0, cap * sizeof(unsigned long long), ctx->stream));   // tag 0 = never valid
         CKC(cudaMalloc(&ctx->d_plane, cap * sizeof(float4)));
         CKC(cudaMalloc(&ctx->d_pflags, cap));
         CKC(cudaMemsetAsync(ctx->d_group_cnt, 0, groups * sizeof(unsigned int), ctx->stream));
@@ -611,8 +613,9 @@ static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, d
 // launch grids are rounded up to capacity buckets so that scans of similar size share one captured graph;
 // surplus CTAs see i >= job->n (k_search) or an exhausted unit counter (k_fused) and leave at once
 static int search_grid(flivo_ctx* ctx) {
-    const int ctas = (int)((ctx->scan_n + 127) / 128);
-    return ((ctas + 255) / 256) * 256;
+    const int tiles = (int)((ctx->scan_n + 127) / 128);
+    if (ctx->search_resident <= 0) ctx->search_resident = ctx->sm_count * search_ctas_per_sm();
+    return std::max(1, std::min(((tiles + 255) / 256) * 256, ctx->search_resident));   // tiles are dealt dynamically
 }
 static int fused_grid(flivo_ctx* ctx) {
     const int units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
@@ -665,7 +668,7 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
     k_ctl_set<<<1, 32, 0, ctx->stream>>>(ctx->d_ctl, do_search ? 1 : 0);
     if (do_search) CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
     FusedParams P = make_fused(ctx);
-    if (do_search) launch_search(P, search_grid(ctx), ctx->sm_count * 8, ctx->stream);
+    if (do_search) launch_search(P, search_grid(ctx), ctx->stream);
     launch_fused(P, fused_grid(ctx), ctx->stream);
     SolveParams S{};
     S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job; S.phase = SOLVE_PHASE_REDUCE_ONLY;
@@ -723,7 +726,7 @@ extern "C" int flivo_repack_v1(const double HTH[144], const double HTz[12], doub
 // One update as a CUDA graph: the fixed sequence of max_iter+1 trips captured from the stream; kernels of skipped
 // phases (re-use trips, trips after the stop) exit at once.  (A device-side WHILE/IF conditional graph was measured
 // slower, profiles/r1_ab_launch_structure.txt.)
-static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveParams& S0, int sgrid, int fgrid, int far_grid, int trips) {
+static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveParams& S0, int sgrid, int fgrid, int trips) {
     cudaStream_t s = ctx->stream;
     cudaGraph_t g = nullptr;
     CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
@@ -735,7 +738,7 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
         CKC(cudaStreamWaitEvent(ctx->side, ctx->ev_fork[t], 0));
         launch_solve_pre(S, ctx->side);
         CKC(cudaEventRecord(ctx->ev_join[t], ctx->side));
-        launch_search(P, sgrid, far_grid, s);
+        launch_search(P, sgrid, s);
         launch_fused(P, fgrid, s);
         CKC(cudaStreamWaitEvent(s, ctx->ev_join[t], 0));
         launch_solve(S, s);
@@ -775,12 +778,12 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     S.sum_out = ctx->d_sum; S.rank_blocks = ctx->d_rank_blocks; S.ctl = ctx->d_ctl;
     S.stamps = timed ? ctx->d_stamps : nullptr;
     S.pre = ctx->d_pre;
-    const int sgrid = search_grid(ctx), fgrid = fused_grid(ctx), far_grid = ctx->sm_count * 8;
+    const int sgrid = search_grid(ctx), fgrid = fused_grid(ctx);
     int launches = 1;
     auto launch_trip = [&](int t, bool with_events) -> int {
         launch_solve_pre(S, s);                 // plain launches: in line (the graph runs it on a parallel branch)
         if (with_events) CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
-        launch_search(P, sgrid, far_grid, s);   // both kernels exit at once on re-use trips
+        launch_search(P, sgrid, s);   // exits at once on re-use trips
         launch_fused(P, fgrid, s);
         if (with_events) CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
         if (ctx->comm) {
@@ -790,11 +793,11 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
             if (nrc != 0) { ctx->err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "error"); return FLIVO_E_NCCL; }
             S.phase = SOLVE_PHASE_FROM_RANKS;
             launch_solve(S, s);
-            launches += 7;
+            launches += 5;
         } else {
             S.phase = SOLVE_PHASE_FULL;
             launch_solve(S, s);
-            launches += 6;
+            launches += 4;
         }
         return FLIVO_OK;
     };
@@ -809,7 +812,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
                 use_graph = false;   // parameters keep changing (e.g. a new external scan pointer every call): plain launches
             } else {
                 if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
-                int rc = build_update_graph(ctx, P, S, sgrid, fgrid, far_grid, trips);
+                int rc = build_update_graph(ctx, P, S, sgrid, fgrid, trips);
                 if (rc != FLIVO_OK) return rc;
                 ctx->graph_P = P; ctx->graph_S = S; ctx->graph_search_grid = sgrid; ctx->graph_fused_grid = fgrid; ctx->graph_trips = trips;
                 launches = 1;
@@ -820,7 +823,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     }
     if (use_graph) {
         CKC(cudaGraphLaunch(ctx->graph_exec, s));
-        launches = 1 + trips * 6;
+        launches = 1 + trips * 4;
     } else {
         launches = 1;
         for (int t = 0; t < trips; ++t) { int rc = launch_trip(t, timed); if (rc != FLIVO_OK) return rc; }

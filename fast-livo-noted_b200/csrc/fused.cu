@@ -395,87 +395,169 @@ __device__ __forceinline__ void store_plane(const FusedParams& P, int i, const f
 }
 
 constexpr int SEARCH_THREADS = 128;
+constexpr int SEARCH_WARPS = SEARCH_THREADS / 32;
+constexpr int FAR_BATCH = 32;   // far points a warp finishes before its lanes fit their planes (one lane per point)
 
-__global__ void __launch_bounds__(SEARCH_THREADS) k_search(FusedParams P) {
-    __shared__ double s_state[24];
-    __shared__ uint32_t s_idx[SHELL_CELLS * SEARCH_THREADS];   // per-thread work lists of thread_knn5_shell
-    __shared__ float s_gap[SHELL_CELLS * SEARCH_THREADS];
-    Ctl* ctl = P.ctl;
-    if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
-    if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
-    __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const int i = blockIdx.x * SEARCH_THREADS + threadIdx.x;
-    const bool have = i < P.job->n;
-    const uint32_t max_sq_bits = P.job->max_sq_bits;
-    unsigned nc = 0;
-    bool fin = true;
-    if (have) {
-        float wx, wy, wz;
-        world_of(s_state, __ldg(P.body + i), wx, wy, wz);
-        Top5 best;
-        int cnt = 0;
-        fin = thread_knn5_shell(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, s_idx + threadIdx.x, s_gap + threadIdx.x, SEARCH_THREADS);
-        if (fin) {
-            float4 nbs[5];
-#pragma unroll
-            for (int r = 0; r < 5; ++r) {
-                nbs[r] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-                if (r < cnt) nbs[r] = __ldg(P.map.buckets + best.a[r]);
-                P.near[(size_t)i * 5 + r] = nbs[r];
-            }
-            const float d5 = (cnt >= 5) ? __uint_as_float((uint32_t)(best.k[4] >> 32)) : INFINITY;
-            P.near_meta[i] = make_float2(__int_as_float(cnt), d5);
-            store_plane(P, i, nbs, cnt, d5);
-        }
-    }
-    // far list: one atomic per warp
-    const unsigned pend = __ballot_sync(FULL, have && !fin);
-    if (pend) {
-        unsigned basep = 0;
-        if (lane == 0) basep = atomicAdd(&ctl->far_count, (unsigned)__popc(pend));
-        basep = __shfl_sync(FULL, basep, 0);
-        if (have && !fin) P.far_list[basep + __popc(pend & ((1u << lane) - 1u))] = (unsigned)i;
-    }
-    if (P.stats) {
-        const unsigned tot = __reduce_add_sync(FULL, nc);
-        if (lane == 0) {
-            if (pend) atomicAdd(&P.stats->far_queries, (unsigned long long)__popc(pend));
-            atomicAdd(&P.stats->candidates, (unsigned long long)tot);
-        }
-    }
+// shared memory of k_search: the two phases of a CTA never overlap, so their buffers share the space
+union SearchSmem {
+    struct {
+        uint32_t idx[SHELL_CELLS * SEARCH_THREADS];   // per-thread work lists of thread_knn5_shell
+        float gap[SHELL_CELLS * SEARCH_THREADS];
+    } p1;
+    struct {
+        uint2 queue[SEARCH_WARPS][RING_QCAP];         // per-warp cell queue of warp_knn5_rings
+        float4 near[SEARCH_WARPS][FAR_BATCH][5];      // neighbours of the warp's current batch of far points
+    } p2;
+};
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
 
-__global__ void __launch_bounds__(128) k_far(FusedParams P) {
+// One kernel per search trip (a1 + a2 + a3/a4 of the plane cache).  Two phases, work dealt dynamically:
+//   phase 1  a CTA takes tiles of 128 consecutive (spatially sorted) scan points from ctl->tile_counter; thread per
+//            point over the 27-cell shell; points the shell cannot finish are published to P.far_list;
+//   phase 2  once the tiles are dealt out, every warp turns consumer: it takes tickets from ctl->far_taken and runs
+//            the warp-per-query growing-cube search on the published far points, while other CTAs may still be in
+//            phase 1.  A ticket whose entry is not there yet is awaited until every tile has been published
+//            (ctl->tiles_done); only CTAs that hold a tile are ever waited for and those are running, so the wait
+//            cannot deadlock whatever the grid size.  Entries carry the epoch of the trip, so the list never needs
+//            clearing.  After FAR_BATCH finished queries the warp's lanes fit the planes of the batch, one lane each.
+// Exits at once on re-use trips (ctl->search == 0 and no force_search) and after the loop stopped.
+__global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
     __shared__ double s_state[24];
-    __shared__ uint2 s_queue[4][RING_QCAP];
+    __shared__ SearchSmem S;
+    __shared__ unsigned s_tile;
+    __shared__ unsigned s_bid[SEARCH_WARPS][FAR_BATCH];
+    __shared__ float2 s_bmeta[SEARCH_WARPS][FAR_BATCH];
     Ctl* ctl = P.ctl;
     if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
-    const unsigned nfar = ctl->far_count;
-    if (nfar == 0) return;
-    const uint32_t max_sq_bits = P.job->max_sq_bits;
     if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
-    __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const unsigned wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-    unsigned nc = 0;
-    for (unsigned e = wid; e < nfar; e += nwarps) {
-        const unsigned i = P.far_list[e];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = P.job->n;
+    const unsigned n_tiles = (unsigned)((n + SEARCH_THREADS - 1) / SEARCH_THREADS);
+    const uint32_t max_sq_bits = P.job->max_sq_bits;
+    const unsigned tag = ctl->epoch + 1u;
+    unsigned nc = 0, nfar = 0;
+
+    // ---- phase 1 ------------------------------------------------------------------------------------
+    bool had_tile = false;
+    for (;;) {
+        __syncthreads();   // the tile's far points are published (and s_tile has been read by everyone)
+        if (threadIdx.x == 0) {
+            if (had_tile) atomicAdd(&ctl->tiles_done, 1u);
+            s_tile = atomicAdd(&ctl->tile_counter, 1u);
+        }
+        __syncthreads();
+        const unsigned tile = s_tile;
+        if (tile >= n_tiles) break;
+        had_tile = true;
+        const int i = (int)(tile * SEARCH_THREADS) + threadIdx.x;
+        const bool have = i < n;
+        bool fin = true;
+        if (have) {
+            float wx, wy, wz;
+            world_of(s_state, __ldg(P.body + i), wx, wy, wz);
+            Top5 best;
+            int cnt = 0;
+            fin = thread_knn5_shell(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, S.p1.idx + threadIdx.x, S.p1.gap + threadIdx.x, SEARCH_THREADS);
+            if (fin) {
+                float4 nbs[5];
+#pragma unroll
+                for (int r = 0; r < 5; ++r) {
+                    nbs[r] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                    if (r < cnt) nbs[r] = __ldg(P.map.buckets + best.a[r]);
+                    P.near[(size_t)i * 5 + r] = nbs[r];
+                }
+                const float d5 = (cnt >= 5) ? __uint_as_float((uint32_t)(best.k[4] >> 32)) : INFINITY;
+                P.near_meta[i] = make_float2(__int_as_float(cnt), d5);
+                store_plane(P, i, nbs, cnt, d5);
+            }
+        }
+        // publish the far points: one atomic per warp
+        const unsigned pend = __ballot_sync(FULL, have && !fin);
+        if (pend) {
+            unsigned basep = 0;
+            if (lane == 0) basep = atomicAdd(&ctl->far_count, (unsigned)__popc(pend));
+            basep = __shfl_sync(FULL, basep, 0);
+            if (have && !fin) {
+                P.far_list[basep + __popc(pend & ((1u << lane) - 1u))] = ((unsigned long long)tag << 32) | (unsigned)i;
+                __threadfence();   // before this CTA counts the tile as done
+            }
+            nfar += (unsigned)__popc(pend);
+        }
+    }
+
+    // ---- phase 2 (the barrier that ended phase 1 makes the shared buffers free) ---------------------------
+    uint2* queue = S.p2.queue[warp];
+    int nb = 0;
+    for (;;) {
+        unsigned long long v = 0ull;
+        if (lane == 0) {
+            const unsigned e = atomicAdd(&ctl->far_taken, 1u);
+            if (e < (unsigned)n) {
+                for (;;) {
+                    v = ld_volatile_u64(P.far_list + e);
+                    if ((unsigned)(v >> 32) == tag) break;
+                    if (ld_volatile_u32(&ctl->tiles_done) >= n_tiles) {   // nothing more will be published
+                        __threadfence();
+                        v = ld_volatile_u64(P.far_list + e);
+                        break;
+                    }
+                    __nanosleep(256);
+                }
+            }
+        }
+        v = __shfl_sync(FULL, v, 0);
+        if ((unsigned)(v >> 32) != tag) break;
+        const unsigned i = (unsigned)v;
         float wx, wy, wz;
         world_of(s_state, __ldg(P.body + i), wx, wy, wz);
         Cand out;
-        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, max_sq_bits, lane, out, nc, s_queue[threadIdx.x >> 5]);
+        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, max_sq_bits, lane, out, nc, queue);
         if (lane < 5) {
             float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
             if (out.d != INF_BITS) p = __ldg(P.map.buckets + out.addr);
             P.near[(size_t)i * 5 + lane] = p;
+            S.p2.near[warp][nb][lane] = p;
         }
         const uint32_t dlast = __shfl_sync(FULL, out.d, 4);
-        if (lane == 0) P.near_meta[i] = make_float2(__int_as_float(cnt), (cnt >= 5) ? __uint_as_float(dlast) : INFINITY);
+        if (lane == 0) {
+            const float2 meta = make_float2(__int_as_float(cnt), (cnt >= 5) ? __uint_as_float(dlast) : INFINITY);
+            P.near_meta[i] = meta;
+            s_bid[warp][nb] = i; s_bmeta[warp][nb] = meta;
+        }
+        ++nb;
+        if (nb == FAR_BATCH) {
+            __syncwarp();
+            float4 nbs[5];
+#pragma unroll
+            for (int r = 0; r < 5; ++r) nbs[r] = S.p2.near[warp][lane][r];
+            store_plane(P, (int)s_bid[warp][lane], nbs, __float_as_int(s_bmeta[warp][lane].x), s_bmeta[warp][lane].y);
+            nb = 0;
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (lane < nb) {
+        float4 nbs[5];
+#pragma unroll
+        for (int r = 0; r < 5; ++r) nbs[r] = S.p2.near[warp][lane][r];
+        store_plane(P, (int)s_bid[warp][lane], nbs, __float_as_int(s_bmeta[warp][lane].x), s_bmeta[warp][lane].y);
     }
     if (P.stats) {
         const unsigned tot = __reduce_add_sync(FULL, nc);
-        if (lane == 0 && tot) atomicAdd(&P.stats->candidates, (unsigned long long)tot);
+        if (lane == 0) {
+            if (nfar) atomicAdd(&P.stats->far_queries, (unsigned long long)nfar);
+            if (tot) atomicAdd(&P.stats->candidates, (unsigned long long)tot);
+        }
     }
 }
 
@@ -526,26 +608,14 @@ __global__ void k_transform(const float4* __restrict__ body, int n, const double
 void launch_fused(const FusedParams& P, int grid, cudaStream_t stream) {
     k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P);
 }
-// plane + flags of the far points (one thread per far point; the warp-per-point search above would leave 31 lanes
-// idle during the fit)
-__global__ void __launch_bounds__(128) k_far_plane(FusedParams P) {
-    Ctl* ctl = P.ctl;
-    if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
-    const unsigned nfar = ctl->far_count;
-    for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < nfar; e += gridDim.x * blockDim.x) {
-        const unsigned i = P.far_list[e];
-        const float2 meta = P.near_meta[i];
-        float4 nbs[5];
-#pragma unroll
-        for (int r = 0; r < 5; ++r) nbs[r] = P.near[(size_t)i * 5 + r];
-        store_plane(P, (int)i, nbs, __float_as_int(meta.x), meta.y);
-    }
+void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream) {
+    k_search<<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
 }
-
-void launch_search(const FusedParams& P, int search_grid, int far_grid, cudaStream_t stream) {
-    k_search<<<search_grid, SEARCH_THREADS, 0, stream>>>(P);   // CTAs beyond job->n idle: the grid is a capacity bucket
-    k_far<<<far_grid, 128, 0, stream>>>(P);
-    k_far_plane<<<148, 128, 0, stream>>>(P);
+// CTAs of k_search that fit on one SM (its grid never needs to exceed the resident set: tiles are dealt dynamically)
+int search_ctas_per_sm() {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_search, SEARCH_THREADS, 0) != cudaSuccess || nb < 1) nb = 4;
+    return nb;
 }
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
                 int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream) {

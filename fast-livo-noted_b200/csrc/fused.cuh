@@ -27,9 +27,20 @@ struct Ctl {
     int trip_searched[MAX_TRIPS];
     double res_mean;
     double dx_last[23];
-    unsigned int unit_counter;   // dynamic work-unit scheduler of the fused kernel
-    unsigned int far_count;      // entries of far_list written by the search kernel of this trip
+    // work counters of the search kernel of the current trip (see k_search); ctl_next_trip() rearms them
+    unsigned int tile_counter;   // next tile of 128 scan points to deal
+    unsigned int tiles_done;     // tiles whose far points have all been published
+    unsigned int far_count;      // far_list entries published
+    unsigned int far_taken;      // far_list tickets handed to consumer warps
+    unsigned int epoch;          // bumped whenever the counters are rearmed; far_list entries carry epoch+1 as their tag
+    unsigned int pad_epoch;
 };
+#ifdef __CUDACC__
+__device__ __forceinline__ void ctl_next_trip(Ctl* ctl) {
+    ctl->tile_counter = 0; ctl->tiles_done = 0; ctl->far_count = 0; ctl->far_taken = 0;
+    ctl->epoch += 1;
+}
+#endif
 
 // Per-call scalars, resident in HBM so that the captured launch sequence (CUDA graph) of an update never changes
 // its kernel parameters: a call only rewrites this block (one H2D copy together with the state and P).
@@ -64,7 +75,8 @@ struct FusedParams {
     unsigned char* eff;        // [n] rows that entered H
     float4* normvec;           // [n] (nx,ny,nz,pd2)
     float4* world;             // [n] feats_down_world
-    unsigned int* far_list;    // [n] points the 27-cell shell could not finish (k_search -> k_far)
+    unsigned long long* far_list;   // [n] (tag << 32 | point) of points the 27-cell shell could not finish: queue between the
+                               //     two phases of k_search, entries valid when tag == ctl->epoch + 1
     double* partials;          // [fused grid * PSTRIDE] one record per CTA of k_fused
     double* gpartials;         // [groups * PSTRIDE] records folded FOLD_CTAS at a time (fixed order), read by k_solve
     unsigned int* group_cnt;   // [groups] arrival tickets; the folding CTA resets its entry

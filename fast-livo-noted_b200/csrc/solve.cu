@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     stamp(S, ctl, 1);
     if (S.phase == SOLVE_PHASE_REDUCE_ONLY) {
         if (tid < NTERMS) S.sum_out[tid] = s_sum[tid];
-        if (tid == 0) { ctl->unit_counter = 0; ctl->far_count = 0; }
+        if (tid == 0) { ctl_next_trip(ctl); }
         return;
     }
     if (tid < 144) {
@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     if (S.sum_out && tid < NTERMS) S.sum_out[tid] = s_sum[tid];
     const int all_finite = __syncthreads_and(tid >= NTERMS || isfinite(s_sum[tid]));
     if (!all_finite) {  // NaN guard: leave x and P untouched and stop the loop
-        if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl->unit_counter = 0; ctl->far_count = 0; }
+        if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl_next_trip(ctl); }
         return;
     }
 
@@ -484,7 +484,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             ctl->iter = it + 1;
             ctl->converged = t > 0 ? 1 : 0;
             ctl->stopped = stop;
-            ctl->unit_counter = 0; ctl->far_count = 0;
+            ctl_next_trip(ctl);
             for (int i = 0; i < 23; ++i) ctl->dx_last[i] = s_dxo[i];
             s_flag[0] = stop;
         }
@@ -585,7 +585,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             ctl->iter = it + 1;
             ctl->converged = converged;
             ctl->stopped = stop;
-            ctl->unit_counter = 0; ctl->far_count = 0;
+            ctl_next_trip(ctl);
             for (int i = 0; i < 18; ++i) ctl->dx_last[i] = s_sol[i];
             s_flag[0] = stop;
         }
@@ -666,7 +666,7 @@ __global__ void k_ctl_reset(const double* x, double* x_prop, const double* P_pro
     if (threadIdx.x == 0) {
         ctl->search = 1; ctl->stopped = 0; ctl->iter = -1; ctl->t = 0; ctl->rematch = 0; ctl->trips = 0;
         ctl->searches = 0; ctl->converged = 0; ctl->n_eff = 0; ctl->nan_guard = 0; ctl->res_mean = 0.0;
-        ctl->unit_counter = 0; ctl->far_count = 0;
+        ctl_next_trip(ctl);
         for (int i = 0; i < MAX_TRIPS; ++i) ctl->trip_searched[i] = 0;
         for (int i = 0; i < 23; ++i) ctl->dx_last[i] = 0.0;
         if (stats) { stats->far_queries = 0; stats->candidates = 0; stats->sweeps = 0; }
