@@ -105,6 +105,9 @@ def lib():
     if _lib is not None:
         return _lib
     path = _build.build()
+    alt = os.environ.get("FLIVO_LIB")   # development only: A/B another build of the same ABI on one GPU box
+    if alt:
+        path = alt if os.path.isabs(alt) else os.path.join(HERE, alt)
     L = C.CDLL(path)
     vp, sz, i32, f32 = C.c_void_p, C.c_size_t, C.c_int32, C.c_float
     L.flivo_ctx_create.argtypes = [C.c_int, C.POINTER(Options), C.POINTER(vp)]
