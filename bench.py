@@ -360,7 +360,7 @@ def main():
     ms_r = float(np.mean(r["fused_reuse_ms"])) if r["fused_reuse_ms"] else None
     n_local = r["pts_per_scan"]
     ach = SEARCH_BYTES * n_local / (ms_s * 1e-3) / 1e9 if ms_s else None
-    roof = {"bound": "hbm", "kernel": "k_fused (search trip)", "achieved": ach, "peak": peak, "unit": "GB/s",
+    roof = {"bound": "hbm", "kernel": "k_search + k_fused (search trip)", "achieved": ach, "peak": peak, "unit": "GB/s",
             "frac": (ach / peak) if ach else None, "traffic": None, "peak_source": peak_src,
             "bytes_per_point_trip": SEARCH_BYTES, "points_per_launch": n_local, "avg_launch_ms": ms_s,
             "reuse_trip": {"bytes_per_point_trip": REUSE_BYTES, "avg_launch_ms": ms_r,

@@ -1,0 +1,6 @@
+# one gpurun call: plain bench, launch list (gpu__time_duration), one ncu --set full capture of the first two trips' kernels
+mkdir -p gpurun_out
+CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline"
+timeout 300 python bench.py --steps 20 --warmup 3 > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; echo bench rc=$?
+$CMD > gpurun_out/plain.log 2>&1 || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:"flivo|cub::|k_" -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1; tail -1 gpurun_out/ncu1.log | cut -c1-100
