@@ -214,6 +214,7 @@ def run_flivo(args, rank, world_size, local_rank):
         for s in scans:
             import importlib
             lo, hi = importlib.import_module("fast_livo_noted_b200.sharding").shard_range(len(s["body"]), rank, world_size)
+            s["body_full"] = s["body"]
             s["body"] = s["body"][lo:hi].contiguous()
     # device-resident scans (float4) and the reference-layout host copies (48-byte PointXYZINormal AoS) for e2e
     dev_scans, host_scans, host_xyz = [], [], []
@@ -313,12 +314,30 @@ def run_flivo(args, rank, world_size, local_rank):
         mx = te.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = te.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         e2e_s, e2e_work = float(mx[0]), float(sm[1])
+    # sharded mode: the posterior of the sharded update must be the single-GPU posterior of the whole scan
+    shard_check = None
+    if shard:
+        barrier()
+        xs, Ps, reps = step_resident(0)
+        barrier()
+        if rank == 0:
+            F1 = pkg.Flivo(device=local_rank, downsample_size=ds, cell_ratio=args.cell_ratio, initial_points=n_map, sort_scan=bool(args.sort_scan))
+            F1.Build(wxyz_host)
+            full = np.ascontiguousarray(scans[0]["body_full"].cpu().numpy())
+            F1.scan_upload(full)
+            x1, P1, rep1 = F1.iekf_update(pkg.State.from_array(scans[0]["x_prior"]), P0, cfg)
+            shard_check = {"x_max_abs_diff_vs_single_gpu": float(np.abs(xs.as_array() - x1.as_array()).max()),
+                           "P_max_abs_diff_vs_single_gpu": float(np.abs(np.asarray(Ps) - np.asarray(P1)).max()),
+                           "n_eff_sharded": int(reps.n_eff), "n_eff_single": int(rep1.n_eff),
+                           "trips_sharded": int(reps.trips), "trips_single": int(rep1.trips)}
+            del F1
+        barrier()
     h2d = int(pts_per_scan * 16 + 36 * 8 + npd * npd * 8)
     d2h = int(36 * 8 + npd * npd * 8 + 512)
     return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
-                trips_per_step=trips_total / args.steps, shard=shard,
+                trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check,
                 search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
@@ -408,7 +427,7 @@ def main():
                                      "map replica + own scans per rank, no collective")},
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
-            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity,
+            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
         }
         print(json.dumps(line), file=out, flush=True)
