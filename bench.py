@@ -103,7 +103,15 @@ class ClockSampler:
                 smax = float(f[1])
             except ValueError:
                 continue
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "samples": len(sm), "reasons": sorted(reasons)}
+        out = {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "samples": len(sm), "reasons": sorted(reasons)}
+        if not sm and self.rows:   # timed region shorter than the sampling period: report the closest sample and say so
+            ts, line = min(self.rows, key=lambda r: abs(r[0] - t1))
+            f = [x.strip() for x in line.split(",")]
+            try:
+                out["sm_mhz"] = float(f[0]); out["note"] = "no sample inside the %.2f s timed region; closest sample %.2f s away" % (t1 - t0, abs(ts - t1))
+            except ValueError:
+                pass
+        return out
 
 
 def make_workload(name, rank, n_scans, device):
@@ -201,6 +209,9 @@ def run_flivo(args, rank, world_size, local_rank):
     cfg_prof = pkg.make_cfg(mode=args.mode, max_iter=MAX_ITER, laser_point_cov=LASER_POINT_COV, force_search=bool(args.force_search), profile=True)
 
     F = pkg.Flivo(device=local_rank, downsample_size=ds, cell_ratio=args.cell_ratio, initial_points=n_map, sort_scan=bool(args.sort_scan))
+    # clocks of rank 0's GPU, sampled by nvidia-smi every 100 ms; started here so that it is up before the timed loops
+    sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else
+                           os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local_rank]) if rank == 0 else None
     wxyz_host = world["points"].cpu().numpy()
     t0 = time.time()
     F.Build(wxyz_host)
@@ -253,8 +264,6 @@ def run_flivo(args, rank, world_size, local_rank):
     for w in range(args.warmup):
         step_resident(w % S)
     barrier()
-    sampler = ClockSampler(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ else
-                           os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local_rank])
     t_wall0 = time.time()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     trips_total, launches, fused_search_ms, fused_reuse_ms, solve_ms, last = 0, 0, [], [], [], None
@@ -308,7 +317,7 @@ def run_flivo(args, rank, world_size, local_rank):
         e2e_s += time.perf_counter() - t0
         e2e_work += rep2.trips * host_scans[k % S].shape[0]
     t_wall1 = time.time()
-    clocks = sampler.stop(t_wall0, t_wall1)   # covers the device-resident, profile and e2e timed loops
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None   # covers the device-resident, profile and e2e timed loops
     te = torch.tensor([e2e_s, e2e_work], dtype=torch.float64, device=dev)
     if world_size > 1:
         mx = te.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)

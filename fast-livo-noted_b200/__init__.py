@@ -86,6 +86,12 @@ class Stats(C.Structure):
                 ("last_trip_searched", C.c_int32 * 16)]
 
 
+class Pose6D(C.Structure):
+    """flivo_pose6d (msg/Pose6D.msg)."""
+    _fields_ = [("offset_time", C.c_double), ("acc", C.c_double * 3), ("gyr", C.c_double * 3), ("vel", C.c_double * 3),
+                ("pos", C.c_double * 3), ("rot", C.c_double * 9)]
+
+
 # every symbol include/flivo.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "flivo_ctx_create", "flivo_ctx_destroy", "flivo_last_error", "flivo_version", "flivo_ctx_stream", "flivo_sync",
@@ -94,6 +100,8 @@ SYMBOLS = [
     "flivo_map_acquire_removed", "flivo_knn", "flivo_scan_upload", "flivo_scan_set_device", "flivo_h_share_model",
     "flivo_repack_v1", "flivo_iekf_update", "flivo_map_add_scan", "flivo_comm_unique_id", "flivo_comm_init",
     "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps",
+    "flivo_raw_upload", "flivo_raw_set_device", "flivo_raw_undistort", "flivo_raw_downsample", "flivo_raw_download",
+    "flivo_scan_download",
 ]
 
 _lib = None
@@ -142,6 +150,13 @@ def lib():
     L.flivo_comm_destroy.argtypes = [vp]
     L.flivo_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.flivo_debug_solve_stamps.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
+    L.flivo_raw_upload.argtypes = [vp, vp, sz, sz, C.c_int, C.c_int]
+    L.flivo_raw_set_device.argtypes = [vp, vp, vp, sz]
+    L.flivo_raw_undistort.argtypes = [vp, C.POINTER(Pose6D), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                      C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.flivo_raw_downsample.argtypes = [vp, C.c_float, C.POINTER(sz)]
+    L.flivo_raw_download.argtypes = [vp, C.POINTER(C.c_float), sz, C.POINTER(sz)]
+    L.flivo_scan_download.argtypes = [vp, C.POINTER(C.c_float), sz, C.POINTER(sz)]
     _lib = L
     return L
 
@@ -332,6 +347,42 @@ class Flivo:
         s = Stats()
         self._ck(self._L.flivo_get_stats(self.h, C.byref(s)))
         return s
+
+    # ---- front end: raw scan -> undistort -> voxel grid (device resident) ----
+    def raw_upload(self, rec, time_col=None, intensity_col=None):
+        """rec: (n, k) float32 records, xyz in columns 0..2; time_col / intensity_col: column indices or None."""
+        rec = np.ascontiguousarray(rec, np.float32)
+        self._keep_raw = rec
+        self._ck(self._L.flivo_raw_upload(self.h, rec.ctypes.data, rec.shape[0], rec.strides[0],
+                                          -1 if time_col is None else 4 * time_col, -1 if intensity_col is None else 4 * intensity_col))
+
+    def raw_undistort(self, poses, rot_end, pos_end, R_LI, t_LI):
+        """poses: (m, 22) float64 rows [offset_time, acc3, gyr3, vel3, pos3, rot9]."""
+        poses = np.ascontiguousarray(poses, np.float64)
+        arr = (Pose6D * poses.shape[0]).from_buffer_copy(poses.tobytes())
+        d = lambda a: np.ascontiguousarray(a, np.float64).ctypes.data_as(C.POINTER(C.c_double))
+        a, b, c, e = (np.ascontiguousarray(v, np.float64) for v in (rot_end, pos_end, R_LI, t_LI))
+        self._ck(self._L.flivo_raw_undistort(self.h, arr, poses.shape[0], d(a), d(b), d(c), d(e)))
+
+    def raw_downsample(self, leaf):
+        n = C.c_size_t(0)
+        self._ck(self._L.flivo_raw_downsample(self.h, float(leaf), C.byref(n)))
+        self.n_scan = n.value
+        return n.value
+
+    def _download(self, fn):
+        n = C.c_size_t(0)
+        self._ck(fn(self.h, None, 0, C.byref(n)))
+        out = np.zeros((n.value, 4), np.float32)
+        if n.value:
+            self._ck(fn(self.h, out.ctypes.data_as(C.POINTER(C.c_float)), n.value, C.byref(n)))
+        return out
+
+    def raw_download(self):
+        return self._download(self._L.flivo_raw_download)
+
+    def scan_download(self):
+        return self._download(self._L.flivo_scan_download)
 
     def solve_stamps(self, trips=16):
         """[trips][16] device globaltimer stamps (ns) of the solve kernel's phases (profile mode only)."""

@@ -7,6 +7,7 @@
 #include "../../include/flivo.h"
 #include "map.cuh"
 #include "solve.cuh"
+#include "frontend.cuh"
 
 #include <cub/cub.cuh>
 #include <dlfcn.h>
@@ -96,6 +97,18 @@ struct flivo_ctx {
     unsigned long long* d_far_list = nullptr;
     float4* d_plane = nullptr;
     unsigned char* d_pflags = nullptr;
+    // front end (raw scan -> undistort -> voxel grid), see frontend.cu
+    float4* d_raw = nullptr;        // x, y, z, intensity
+    float* d_raw_t = nullptr;       // per-point time offset in ms (PointXYZINormal::curvature)
+    size_t raw_n = 0, raw_cap = 0;
+    bool raw_has_t = false;
+    float4* d_ds = nullptr;         // voxel-grid output (x, y, z, intensity), leaf order
+    float* d_ds_t = nullptr;
+    unsigned *d_vg_keys_a = nullptr, *d_vg_keys_b = nullptr, *d_vg_idx_a = nullptr, *d_vg_idx_b = nullptr, *d_vg_head = nullptr, *d_vg_pos = nullptr;
+    void* d_vg_tmp = nullptr;
+    size_t vg_tmp_bytes = 0;
+    VoxelGridState* d_vg_state = nullptr;
+    PoseDev* d_poses = nullptr;
     void* d_out = nullptr;          // un-permute scratch for optional outputs
     size_t d_out_bytes = 0;
     // loop state
@@ -331,6 +344,7 @@ static void free_scan(flivo_ctx* ctx) {
     ctx->scan_cap = 0; ctx->scan_n = 0; ctx->cub_bytes = 0;
 }
 
+static void free_raw(flivo_ctx* ctx);
 extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
@@ -338,6 +352,8 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
     ctx->map.release();
     free_scan(ctx);
+    free_raw(ctx);
+    cudaFree(ctx->d_vg_state); cudaFree(ctx->d_poses);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
     cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_stamps); cudaFree(ctx->d_pre);
     for (int i = 0; i <= MAX_TRIPS; ++i) { if (ctx->ev_fork[i]) cudaEventDestroy(ctx->ev_fork[i]); if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]); }
@@ -936,6 +952,193 @@ extern "C" int flivo_debug_solve_stamps(flivo_ctx* ctx, uint64_t* out, int trips
     if (!ctx || !out || trips_cap <= 0) return FLIVO_E_ARG;
     if (trips_cap > MAX_TRIPS) trips_cap = MAX_TRIPS;
     CKC(cudaMemcpyAsync(out, ctx->d_stamps, (size_t)trips_cap * 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+
+// =====================================================================================================================
+// Front end of the path: raw scan -> motion compensation -> voxel-grid down-sampling, on the device
+// =====================================================================================================================
+static void free_raw(flivo_ctx* ctx) {
+    cudaFree(ctx->d_raw); cudaFree(ctx->d_raw_t); cudaFree(ctx->d_ds); cudaFree(ctx->d_ds_t);
+    cudaFree(ctx->d_vg_keys_a); cudaFree(ctx->d_vg_keys_b); cudaFree(ctx->d_vg_idx_a); cudaFree(ctx->d_vg_idx_b);
+    cudaFree(ctx->d_vg_head); cudaFree(ctx->d_vg_pos); cudaFree(ctx->d_vg_tmp);
+    ctx->d_raw = ctx->d_ds = nullptr; ctx->d_raw_t = ctx->d_ds_t = nullptr;
+    ctx->d_vg_keys_a = ctx->d_vg_keys_b = ctx->d_vg_idx_a = ctx->d_vg_idx_b = ctx->d_vg_head = ctx->d_vg_pos = nullptr;
+    ctx->d_vg_tmp = nullptr; ctx->vg_tmp_bytes = 0; ctx->raw_cap = 0; ctx->raw_n = 0;
+}
+static int ensure_raw(flivo_ctx* ctx, size_t n) {
+    if (!ctx->d_vg_state) {
+        CKC(cudaMalloc(&ctx->d_vg_state, sizeof(VoxelGridState)));
+        CKC(cudaMemset(ctx->d_vg_state, 0, sizeof(VoxelGridState)));
+        CKC(cudaMalloc(&ctx->d_poses, UNDISTORT_MAX_POSES * sizeof(PoseDev)));
+    }
+    if (n <= ctx->raw_cap) return FLIVO_OK;
+    CKC(cudaStreamSynchronize(ctx->stream));
+    free_raw(ctx);
+    const size_t cap = std::max<size_t>(n + n / 8, 1u << 16);
+    CKC(cudaMalloc(&ctx->d_raw, cap * sizeof(float4)));
+    CKC(cudaMalloc(&ctx->d_raw_t, cap * sizeof(float)));
+    CKC(cudaMalloc(&ctx->d_ds, cap * sizeof(float4)));
+    CKC(cudaMalloc(&ctx->d_ds_t, cap * sizeof(float)));
+    unsigned** u[6] = {&ctx->d_vg_keys_a, &ctx->d_vg_keys_b, &ctx->d_vg_idx_a, &ctx->d_vg_idx_b, &ctx->d_vg_head, &ctx->d_vg_pos};
+    for (auto pp : u) CKC(cudaMalloc(pp, cap * sizeof(unsigned)));
+    ctx->vg_tmp_bytes = voxel_grid_temp_bytes(cap);
+    CKC(cudaMalloc(&ctx->d_vg_tmp, ctx->vg_tmp_bytes));
+    ctx->raw_cap = cap;
+    return FLIVO_OK;
+}
+
+// lidar_meas.lidar->points as the pre-processing step leaves them (PointXYZINormal: xyz at byte 0, intensity at 32,
+// curvature = time offset in ms at 36): copied to the device once; the following two calls work in HBM.
+extern "C" int flivo_raw_upload(flivo_ctx* ctx, const void* pts, size_t n, size_t stride_bytes, int time_offset_bytes, int intensity_offset_bytes) {
+    ENTER();
+    NEED(n > 0 && pts && stride_ok(stride_bytes), FLIVO_E_ARG, "bad raw scan / stride");
+    NEED(n < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "raw scan too large");
+    NEED(time_offset_bytes < 0 || ((size_t)time_offset_bytes + 4 <= stride_bytes && time_offset_bytes % 4 == 0), FLIVO_E_ARG, "bad time offset");
+    NEED(intensity_offset_bytes < 0 || ((size_t)intensity_offset_bytes + 4 <= stride_bytes && intensity_offset_bytes % 4 == 0), FLIVO_E_ARG, "bad intensity offset");
+    int rc = ensure_raw(ctx, n);
+    if (rc) return rc;
+    if (ctx->stage_pending) { CKC(cudaEventSynchronize(ctx->stage_ev)); ctx->stage_pending = false; }
+    const size_t need = n + (n + 3) / 4;   // float4 points followed by the float times in the same pinned buffer
+    if (need > ctx->h_stage_n) {
+        if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+        ctx->h_stage = nullptr; ctx->h_stage_n = 0;
+        const size_t cap = std::max<size_t>(need + need / 4, 1u << 16);
+        CKC(cudaMallocHost(&ctx->h_stage, cap * sizeof(float4)));
+        ctx->h_stage_n = cap;
+    }
+    const char* src = reinterpret_cast<const char*>(pts);
+    float4* h = ctx->h_stage;
+    float* ht = reinterpret_cast<float*>(ctx->h_stage + n);
+    const int nt = host_threads();
+    const size_t CH = 1u << 16;
+    for (size_t c0 = 0; c0 < n; c0 += CH) {
+        const size_t m = std::min(CH, n - c0);
+#pragma omp parallel for num_threads(nt) schedule(static) if (m >= 8192 && nt > 1)
+        for (long i = 0; i < (long)m; ++i) {
+            const char* rec = src + (c0 + (size_t)i) * stride_bytes;
+            const float* p = reinterpret_cast<const float*>(rec);
+            const float inten = intensity_offset_bytes >= 0 ? *reinterpret_cast<const float*>(rec + intensity_offset_bytes) : 0.f;
+            h[c0 + i] = make_float4(p[0], p[1], p[2], inten);
+            ht[c0 + i] = time_offset_bytes >= 0 ? *reinterpret_cast<const float*>(rec + time_offset_bytes) : 0.f;
+        }
+        CKC(cudaMemcpyAsync(ctx->d_raw + c0, h + c0, m * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+        CKC(cudaMemcpyAsync(ctx->d_raw_t + c0, ht + c0, m * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CKC(cudaEventRecord(ctx->stage_ev, ctx->stream));
+    ctx->stage_pending = true;
+    ctx->raw_n = n;
+    ctx->raw_has_t = time_offset_bytes >= 0;
+    return FLIVO_OK;
+}
+
+// Same, from device pointers (n float4 x,y,z,intensity and n float times in ms, may be NULL): copied device to device.
+extern "C" int flivo_raw_set_device(flivo_ctx* ctx, const void* dev_xyzi, const void* dev_time_ms, size_t n) {
+    ENTER();
+    NEED(n > 0 && dev_xyzi, FLIVO_E_ARG, "bad raw scan");
+    NEED(n < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "raw scan too large");
+    int rc = ensure_raw(ctx, n);
+    if (rc) return rc;
+    CKC(cudaMemcpyAsync(ctx->d_raw, dev_xyzi, n * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
+    if (dev_time_ms) CKC(cudaMemcpyAsync(ctx->d_raw_t, dev_time_ms, n * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+    ctx->raw_n = n;
+    ctx->raw_has_t = dev_time_ms != nullptr;
+    return FLIVO_OK;
+}
+
+// The per-point loop of ImuProcess::UndistortPcl (src/IMU_Processing.cpp:336-376), in place on the raw scan.
+extern "C" int flivo_raw_undistort(flivo_ctx* ctx, const flivo_pose6d* poses, int n_poses, const double rot_end[9], const double pos_end[3],
+                                   const double R_LI[9], const double t_LI[3]) {
+    ENTER();
+    NEED(ctx->raw_n > 0, FLIVO_E_STATE, "no raw scan uploaded");
+    NEED(ctx->raw_has_t, FLIVO_E_STATE, "raw scan has no per-point times");
+    NEED(poses && n_poses >= 2 && n_poses <= UNDISTORT_MAX_POSES, FLIVO_E_ARG, "need 2..256 IMU poses");
+    NEED(rot_end && pos_end && R_LI && t_LI, FLIVO_E_ARG, "null argument");
+    static_assert(sizeof(flivo_pose6d) == sizeof(PoseDev), "pose layout");
+    UndistortParams U;
+    memset(&U, 0, sizeof(U));
+    U.poses = ctx->d_poses; U.n_poses = n_poses;
+    // (a copy from pageable host memory is staged by the driver before the call returns: the caller's array is free at once)
+    CKC(cudaMemcpyAsync(ctx->d_poses, poses, (size_t)n_poses * sizeof(PoseDev), cudaMemcpyHostToDevice, ctx->stream));
+    for (int i = 0; i < 3; ++i) { U.pos_end[i] = pos_end[i]; U.t_LI[i] = t_LI[i]; }
+    for (int i = 0; i < 9; ++i) U.R_LI[i] = R_LI[i];
+    // extR_Ri = R_LI^T * rot_end^T ; exrR_extT = R_LI^T * t_LI   (:336-337)
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) {
+            double sacc = 0.0;
+            for (int k = 0; k < 3; ++k) sacc += R_LI[k * 3 + r] * rot_end[c * 3 + k];
+            U.extR_Ri[r * 3 + c] = sacc;
+        }
+        double t = 0.0;
+        for (int k = 0; k < 3; ++k) t += R_LI[k * 3 + r] * t_LI[k];
+        U.exrR_extT[r] = t;
+    }
+    launch_undistort(ctx->d_raw, ctx->d_raw_t, ctx->raw_n, U, ctx->stream);
+    CKC(cudaGetLastError());
+    return FLIVO_OK;
+}
+
+// downSizeFilterSurf.setInputCloud(feats_undistort); downSizeFilterSurf.filter(*feats_down_body) (src/laser_mapping.cpp:129-130)
+// on the raw scan in HBM; the result becomes the current scan exactly as after flivo_scan_upload (feats_down_body).
+extern "C" int flivo_raw_downsample(flivo_ctx* ctx, float leaf_size, size_t* n_out) {
+    ENTER();
+    NEED(ctx->raw_n > 0, FLIVO_E_STATE, "no raw scan uploaded");
+    NEED(leaf_size > 0.f, FLIVO_E_ARG, "leaf size must be positive");
+    const size_t n = ctx->raw_n;
+    const float* tms = ctx->raw_has_t ? ctx->d_raw_t : nullptr;
+    CKC(launch_voxel_grid(ctx->d_raw, tms, n, leaf_size, ctx->d_vg_state, ctx->d_vg_keys_a, ctx->d_vg_keys_b, ctx->d_vg_idx_a, ctx->d_vg_idx_b,
+                          ctx->d_vg_head, ctx->d_vg_pos, ctx->d_vg_tmp, ctx->vg_tmp_bytes, ctx->d_ds, ctx->d_ds_t, ctx->stream));
+    VoxelGridState* hs = reinterpret_cast<VoxelGridState*>(ctx->h_small);
+    CKC(cudaMemcpyAsync(hs, ctx->d_vg_state, sizeof(VoxelGridState), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    if (hs->overflow) {   // PCL: "Leaf size is too small for the input dataset. Integer indices would overflow." -> output = input
+        CKC(launch_voxel_passthrough(ctx->d_raw, tms, n, ctx->d_vg_state, ctx->d_ds, ctx->d_ds_t, ctx->stream));
+        hs->n_out = (unsigned)n;
+    }
+    const size_t m = hs->n_out;
+    if (n_out) *n_out = m;
+    if (m == 0) { ctx->scan_n = 0; return FLIVO_OK; }
+    int rc = ensure_scan(ctx, m);
+    if (rc) return rc;
+    if (!ctx->opt.sort_scan) ctx->d_body = ctx->d_ds;
+    return finish_scan(ctx, ctx->d_ds, m, true);
+}
+
+// feats_down_body back to the host in the caller's (= leaf) order: n x (x, y, z, intensity)
+extern "C" int flivo_scan_download(flivo_ctx* ctx, float* out_xyzi, size_t cap, size_t* n_out) {
+    ENTER();
+    NEED(out_xyzi || cap == 0, FLIVO_E_ARG, "null output");
+    const size_t n = ctx->scan_n;
+    if (n_out) *n_out = n;
+    if (n == 0 || cap == 0) return FLIVO_OK;
+    NEED(cap >= n, FLIVO_E_CAPACITY, "output too small");
+    const float4* src = ctx->d_body;
+    if (ctx->scan_sorted) {   // processing order -> caller's order
+        const size_t bytes = n * sizeof(float4);
+        if (bytes > ctx->d_out_bytes) {
+            cudaFree(ctx->d_out); ctx->d_out = nullptr; ctx->d_out_bytes = 0;
+            CKC(cudaMalloc(&ctx->d_out, bytes + bytes / 4));
+            ctx->d_out_bytes = bytes + bytes / 4;
+        }
+        k_scatter<float4><<<nblk(n, 256), 256, 0, ctx->stream>>>(ctx->d_body, ctx->d_perm, n, 1, (float4*)ctx->d_out);
+        CKC(cudaGetLastError());
+        src = (const float4*)ctx->d_out;
+    }
+    CKC(cudaMemcpyAsync(out_xyzi, src, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+
+// the raw scan (after flivo_raw_undistort: feats_undistort) back to the host: n x (x, y, z, intensity)
+extern "C" int flivo_raw_download(flivo_ctx* ctx, float* out_xyzi, size_t cap, size_t* n_out) {
+    ENTER();
+    NEED(out_xyzi || cap == 0, FLIVO_E_ARG, "null output");
+    const size_t n = ctx->raw_n;
+    if (n_out) *n_out = n;
+    if (n == 0 || cap == 0) return FLIVO_OK;
+    NEED(cap >= n, FLIVO_E_CAPACITY, "output too small");
+    CKC(cudaMemcpyAsync(out_xyzi, ctx->d_raw, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     CKC(cudaStreamSynchronize(ctx->stream));
     return FLIVO_OK;
 }

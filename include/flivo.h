@@ -139,6 +139,36 @@ int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t st
 /* Same, from a device pointer to n float4 (x,y,z,ignored) already resident in HBM (no copy through the host). */
 int flivo_scan_set_device(flivo_ctx* ctx, const void* dev_xyzw, size_t n);
 
+/* ---- front end of the path: the two steps right before it, device resident --------- */
+/* msg/Pose6D.msg as filled by set_pose6d (include/common_lib.h:618-633): pose of the IMU at each IMU sample of the scan */
+typedef struct flivo_pose6d {
+    double offset_time;   /* seconds since the first lidar point of the scan */
+    double acc[3];        /* total acceleration, global frame */
+    double gyr[3];        /* unbiased angular velocity, body frame */
+    double vel[3];
+    double pos[3];
+    double rot[9];        /* row-major */
+} flivo_pose6d;
+/* lidar_meas.lidar->points (the raw, time-stamped scan): xyz at byte 0 of every record; time_offset_bytes = byte offset
+ * of the per-point time in milliseconds (pcl::PointXYZINormal::curvature = 36), < 0: none; intensity_offset_bytes
+ * (PointXYZINormal::intensity = 32) or < 0.  Copied to the device once. */
+int flivo_raw_upload(flivo_ctx* ctx, const void* pts, size_t n, size_t stride_bytes, int time_offset_bytes, int intensity_offset_bytes);
+/* Same from device memory: n float4 (x,y,z,intensity) and n float times in ms (may be NULL). */
+int flivo_raw_set_device(flivo_ctx* ctx, const void* dev_xyzi, const void* dev_time_ms, size_t n);
+/* The per-point back-propagation loop of ImuProcess::UndistortPcl (src/IMU_Processing.cpp:336-376): every point is moved
+ * to the scan-end frame with the last IMU pose before its time stamp; in place on the raw scan (-> feats_undistort).
+ * poses: IMUpose (offset_time ascending, first = 0); rot_end / pos_end: the propagated state at the scan end;
+ * R_LI / t_LI: Lid_rot_to_IMU / Lid_offset_to_IMU.  Points must be ordered by time like the reference's. */
+int flivo_raw_undistort(flivo_ctx* ctx, const flivo_pose6d* poses, int n_poses, const double rot_end[9], const double pos_end[3],
+                        const double R_LI[9], const double t_LI[3]);
+/* downSizeFilterSurf.filter(*feats_down_body) (pcl::VoxelGrid, src/laser_mapping.cpp:129-130, leaf size :1111): centroid
+ * (x, y, z, intensity, time) of the points of every occupied leaf, ordered by leaf index.  The result becomes the
+ * current scan as if passed to flivo_scan_upload; *n_out = its size. */
+int flivo_raw_downsample(flivo_ctx* ctx, float leaf_size, size_t* n_out);
+/* Read back n x (x, y, z, intensity): the raw scan (feats_undistort) / the current scan (feats_down_body), caller's order. */
+int flivo_raw_download(flivo_ctx* ctx, float* out_xyzi, size_t cap, size_t* n_out);
+int flivo_scan_download(flivo_ctx* ctx, float* out_xyzi, size_t cap, size_t* n_out);
+
 /* One LaserMapping::h_share_model call (src/laser_mapping.cpp:485-645 / src/origin_laserMapping.cpp:916-1048)
  * at state `st`: world transform, kNN when do_search (else the cached Nearest_Points), esti_plane, gates,
  * 1x12 rows, H^T H (12x12 row-major) and H^T z.  Optional outputs may be NULL:

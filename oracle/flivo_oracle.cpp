@@ -960,3 +960,136 @@ extern "C" size_t orc_map_live(orc_map* m, float* xyz, int32_t* ids, size_t cap)
     }
     return c;
 }
+
+// =====================================================================================================================
+// Front end: motion compensation, voxel-grid down-sampling, local-map sliding
+// =====================================================================================================================
+namespace {
+// Exp(ang_vel, dt), include/so3_math.h:30-52; row-major 3x3
+void exp_rate(const double w[3], double dt, double R[9]) {
+    const double nrm = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+    for (int e = 0; e < 9; ++e) R[e] = (e % 4 == 0) ? 1.0 : 0.0;
+    if (nrm > 0.0000001) {
+        const double a[3] = {w[0] / nrm, w[1] / nrm, w[2] / nrm};
+        const double K[9] = {0.0, -a[2], a[1], a[2], 0.0, -a[0], -a[1], a[0], 0.0};
+        const double ang = nrm * dt;
+        const double s = sin(ang), c1 = 1.0 - cos(ang);
+        double cK[9], KK[9];
+        for (int e = 0; e < 9; ++e) cK[e] = c1 * K[e];
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) KK[i * 3 + j] = cK[i * 3] * K[j] + cK[i * 3 + 1] * K[3 + j] + cK[i * 3 + 2] * K[6 + j];
+        for (int e = 0; e < 9; ++e) R[e] = (R[e] + s * K[e]) + KK[e];
+    }
+}
+void mv3(const double* M, const double v[3], double o[3]) {
+    for (int r = 0; r < 3; ++r) o[r] = M[r * 3] * v[0] + M[r * 3 + 1] * v[1] + M[r * 3 + 2] * v[2];
+}
+}  // namespace
+
+// The backward loop of ImuProcess::UndistortPcl, src/IMU_Processing.cpp:336-376, restated literally (two nested
+// loops walking the scan from its last point, `break` at the first point).  pts: n records of stride_floats floats,
+// xyz first, modified in place; t_ms[i] = curvature of point i.
+extern "C" void orc_undistort(float* pts, size_t n, size_t stride_floats, const float* t_ms, const orc_pose6d* IMUpose, int n_poses,
+                              const double rot_end[9], const double pos_end[3], const double R_LI[9], const double t_LI[3]) {
+    double extR_Ri[9], exrR_extT[3];
+    for (int r = 0; r < 3; ++r) {   // Lid_rot_to_IMU^T * rot_end^T ; Lid_rot_to_IMU^T * Lid_offset_to_IMU  (:336-337)
+        for (int c = 0; c < 3; ++c) {
+            double s = 0.0;
+            for (int k = 0; k < 3; ++k) s += R_LI[k * 3 + r] * rot_end[c * 3 + k];
+            extR_Ri[r * 3 + c] = s;
+        }
+        double t = 0.0;
+        for (int k = 0; k < 3; ++k) t += R_LI[k * 3 + r] * t_LI[k];
+        exrR_extT[r] = t;
+    }
+    if (n < 1) return;                                            // :339
+    long it_pcl = (long)n - 1;                                    // :342
+    for (int it_kp = n_poses - 1; it_kp != 0; it_kp--) {          // :343
+        const orc_pose6d* head = &IMUpose[it_kp - 1];
+        for (; (double)t_ms[it_pcl] / double(1000) > head->offset_time; it_pcl--) {   // :354
+            const double dt = (double)t_ms[it_pcl] / double(1000) - head->offset_time;
+            double E[9], R_i[9], T_ei[3];
+            exp_rate(head->gyr, dt, E);
+            for (int r = 0; r < 3; ++r)
+                for (int c = 0; c < 3; ++c) R_i[r * 3 + c] = head->rot[r * 3] * E[c] + head->rot[r * 3 + 1] * E[3 + c] + head->rot[r * 3 + 2] * E[6 + c];
+            for (int a = 0; a < 3; ++a) T_ei[a] = ((head->pos[a] + head->vel[a] * dt) + 0.5 * head->acc[a] * dt * dt) - pos_end[a];
+            float* p = pts + (size_t)it_pcl * stride_floats;
+            const double P_i[3] = {(double)p[0], (double)p[1], (double)p[2]};
+            double a3[3], b3[3], c3[3];
+            mv3(R_LI, P_i, a3);
+            for (int a = 0; a < 3; ++a) a3[a] += t_LI[a];
+            mv3(R_i, a3, b3);
+            for (int a = 0; a < 3; ++a) b3[a] += T_ei[a];
+            mv3(extR_Ri, b3, c3);
+            p[0] = (float)(c3[0] - exrR_extT[0]);
+            p[1] = (float)(c3[1] - exrR_extT[1]);
+            p[2] = (float)(c3[2] - exrR_extT[2]);
+            if (it_pcl == 0) break;                               // :373
+        }
+    }
+}
+
+// pcl::VoxelGrid<PointXYZINormal>::applyFilter as called at src/laser_mapping.cpp:129-130 (PCL is not in the reference tree:
+// restated from pcl/filters/impl/voxel_grid.hpp; downsample_all_data = true, min_points_per_voxel = 0, no field filter).
+// in: n x (x, y, z, intensity) and n times (may be NULL).  out buffers hold up to `cap` leaves.  Returns the number of
+// output points; when the leaf is too small for the extent PCL returns the input unchanged — same here.
+// Points of one leaf are accumulated in input order (PCL sorts (leaf, index) pairs with std::sort, which leaves the order
+// inside a leaf unspecified: parity unpinned at the ulp level of the float sums).
+extern "C" long orc_voxel_grid(const float* xyzi, const float* t_ms, size_t n, float leaf, float* out_xyzi, float* out_t, size_t cap) {
+    const float inv = 1.0f / leaf;
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    size_t nfin = 0;
+    for (size_t i = 0; i < n; ++i) {
+        const float* p = xyzi + 4 * i;
+        if (!std::isfinite(p[0]) || !std::isfinite(p[1]) || !std::isfinite(p[2])) continue;
+        for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], p[a]); mx[a] = std::max(mx[a], p[a]); }
+        ++nfin;
+    }
+    auto passthrough = [&]() -> long {
+        for (size_t i = 0; i < n && i < cap; ++i) {
+            memcpy(out_xyzi + 4 * i, xyzi + 4 * i, 16);
+            if (out_t) out_t[i] = t_ms ? t_ms[i] : 0.f;
+        }
+        return (long)n;
+    };
+    if (nfin == 0) return 0;
+    const int64_t dx = (int64_t)((mx[0] - mn[0]) * inv) + 1, dy = (int64_t)((mx[1] - mn[1]) * inv) + 1, dz = (int64_t)((mx[2] - mn[2]) * inv) + 1;
+    if (dx * dy * dz > (int64_t)INT32_MAX) return passthrough();
+    int min_b[3], div_b[3];
+    for (int a = 0; a < 3; ++a) {
+        min_b[a] = (int)floorf(mn[a] * inv);
+        const int max_b = (int)floorf(mx[a] * inv);
+        div_b[a] = max_b - min_b[a] + 1;
+    }
+    const int mul[3] = {1, div_b[0], div_b[0] * div_b[1]};
+    std::vector<std::pair<unsigned, unsigned>> iv;   // (leaf index, point index)
+    iv.reserve(nfin);
+    for (size_t i = 0; i < n; ++i) {
+        const float* p = xyzi + 4 * i;
+        if (!std::isfinite(p[0]) || !std::isfinite(p[1]) || !std::isfinite(p[2])) continue;
+        const int i0 = (int)(floorf(p[0] * inv) - (float)min_b[0]);
+        const int i1 = (int)(floorf(p[1] * inv) - (float)min_b[1]);
+        const int i2 = (int)(floorf(p[2] * inv) - (float)min_b[2]);
+        iv.emplace_back((unsigned)(i0 * mul[0] + i1 * mul[1] + i2 * mul[2]), (unsigned)i);
+    }
+    std::stable_sort(iv.begin(), iv.end(), [](const std::pair<unsigned, unsigned>& a, const std::pair<unsigned, unsigned>& b) { return a.first < b.first; });
+    size_t out = 0;
+    for (size_t s = 0; s < iv.size();) {
+        size_t e = s;
+        float sx = 0.f, sy = 0.f, sz = 0.f, si = 0.f, st = 0.f;
+        while (e < iv.size() && iv[e].first == iv[s].first) {
+            const float* p = xyzi + 4 * (size_t)iv[e].second;
+            sx += p[0]; sy += p[1]; sz += p[2]; si += p[3];
+            if (t_ms) st += t_ms[iv[e].second];
+            ++e;
+        }
+        const float fn = (float)(e - s);
+        if (out < cap) {
+            out_xyzi[4 * out] = sx / fn; out_xyzi[4 * out + 1] = sy / fn; out_xyzi[4 * out + 2] = sz / fn; out_xyzi[4 * out + 3] = si / fn;
+            if (out_t) out_t[out] = st / fn;
+        }
+        ++out;
+        s = e;
+    }
+    return (long)out;
+}

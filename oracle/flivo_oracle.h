@@ -95,6 +95,17 @@ int  orc_map_add_points(orc_map*, const float* xyz, size_t n, int downsample_on)
 int  orc_map_delete_boxes(orc_map*, const float* boxes6, size_t nboxes);        // :501-521, :626-688 half-open
 size_t orc_map_live(orc_map*, float* xyz /* cap*3 or NULL */, int32_t* ids /* or NULL */, size_t cap);
 
+// ---- front end ----
+// msg/Pose6D.msg (set_pose6d, include/common_lib.h:618-633)
+typedef struct orc_pose6d {
+    double offset_time, acc[3], gyr[3], vel[3], pos[3], rot[9];
+} orc_pose6d;
+// ImuProcess::UndistortPcl, backward loop (src/IMU_Processing.cpp:336-376), in place
+void orc_undistort(float* pts, size_t n, size_t stride_floats, const float* t_ms, const orc_pose6d* IMUpose, int n_poses,
+                   const double rot_end[9], const double pos_end[3], const double R_LI[9], const double t_LI[3]);
+// pcl::VoxelGrid::filter (src/laser_mapping.cpp:129-130); returns the number of output points
+long orc_voxel_grid(const float* xyzi, const float* t_ms, size_t n, float leaf, float* out_xyzi, float* out_t, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -106,6 +106,9 @@ def lib():
         L.orc_map_delete_boxes.restype = C.c_int
         L.orc_map_live.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
         L.orc_map_live.restype = C.c_size_t
+        L.orc_undistort.argtypes = [f32p, C.c_size_t, C.c_size_t, f32p, f64p, C.c_int, f64p, f64p, f64p, f64p]
+        L.orc_voxel_grid.argtypes = [f32p, C.c_void_p, C.c_size_t, C.c_float, f32p, C.c_void_p, C.c_size_t]
+        L.orc_voxel_grid.restype = C.c_long
         _lib = L
     return _lib
 
@@ -331,3 +334,27 @@ class RefTree:
                                       None if nid is None else nid.ctypes.data)
         return dict(x=x, P=P, trips=trips, searches=searches.value, n_eff=n_eff.value, timings=timings,
                     eff=eff, near_id=nid)
+
+
+# ---- front end ----
+def undistort(xyz, t_ms, poses, rot_end, pos_end, R_LI, t_LI):
+    """ImuProcess::UndistortPcl backward loop.  xyz (n,3) float32, t_ms (n,) float32 ascending, poses (m,22) float64
+    rows [offset_time, acc3, gyr3, vel3, pos3, rot9].  Returns the compensated (n,3) float32."""
+    out = np.ascontiguousarray(xyz, np.float32).copy()
+    t = _c(t_ms, np.float32)
+    P = _c(poses, np.float64)
+    a, b, c, d = (_c(np.asarray(v).reshape(-1), np.float64) for v in (rot_end, pos_end, R_LI, t_LI))
+    lib().orc_undistort(out, out.shape[0], 3, t, P.reshape(-1), P.shape[0], a, b, c, d)
+    return out
+
+
+def voxel_grid(xyzi, leaf, t_ms=None):
+    """pcl::VoxelGrid::filter.  xyzi (n,4) float32.  Returns (out (m,4) float32, out_t (m,) float32 or None)."""
+    x = _c(xyzi, np.float32)
+    n = x.shape[0]
+    out = np.zeros((max(n, 1), 4), np.float32)
+    t = _c(t_ms, np.float32) if t_ms is not None else None
+    ot = np.zeros(max(n, 1), np.float32) if t is not None else None
+    m = lib().orc_voxel_grid(x, t.ctypes.data if t is not None else None, n, float(leaf),
+                             out, ot.ctypes.data if ot is not None else None, n)
+    return out[:m].copy(), (ot[:m].copy() if ot is not None else None)
