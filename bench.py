@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument("--sort-scan", type=int, default=1)
     ap.add_argument("--cell-ratio", type=int, default=0, help="search cell edge / downsample size (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-frontend", action="store_true", help="skip the informational front-end (undistort + voxel grid) timing")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5)")
     return ap.parse_args()
@@ -323,6 +324,45 @@ def run_flivo(args, rank, world_size, local_rank):
         mx = te.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = te.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         e2e_s, e2e_work = float(mx[0]), float(sm[1])
+    # ---- front end, informational: raw scan (4 returns per down-sampled point, time-stamped) ->
+    # undistort -> voxel grid on the device, timed with CUDA events; the same two steps in the CPU oracle beside it ----
+    frontend = None
+    if rank == 0 and world_size == 1 and not args.no_frontend:
+        import flivo_frontend as fe
+        g = torch.Generator(device=dev); g.manual_seed(1234)
+        base = dev_scans[0][:, :3]
+        raw = base.repeat_interleave(4, dim=0) + 0.02 * torch.randn((4 * base.shape[0], 3), device=dev, generator=g)
+        n_raw = raw.shape[0]
+        raw4 = torch.zeros((n_raw, 4), dtype=torch.float32, device=dev); raw4[:, :3] = raw
+        t_ms = torch.linspace(0.0, 100.0, n_raw, device=dev, dtype=torch.float32)
+        poses, rot_end, pos_end = fe.make_poses(9)
+        R_LI, t_LI = np.eye(3), np.array([0.04165, 0.02326, -0.0284])
+        leaf = max(ds, 0.05)
+        und, dsm, n_out = [], [], 0
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        for k in range(6):
+            F._ck(L.flivo_raw_set_device(F.h, C.c_void_p(raw4.data_ptr()), C.c_void_p(t_ms.data_ptr()), n_raw))
+            torch.cuda.synchronize()
+            with torch.cuda.stream(ext):
+                e0.record(ext)
+                F.raw_undistort(poses, rot_end, pos_end, R_LI, t_LI)
+                e1.record(ext)
+                n_out = F.raw_downsample(leaf)
+                e2.record(ext)
+            torch.cuda.synchronize()
+            if k >= 2:
+                und.append(e0.elapsed_time(e1)); dsm.append(e1.elapsed_time(e2))
+        frontend = {"raw_points": int(n_raw), "leaf": leaf, "scan_points_out": int(n_out), "undistort_ms": float(np.median(und)),
+                    "voxel_grid_ms": float(np.median(dsm)), "note": "voxel_grid_ms includes the Morton sort that makes the result the current scan"}
+        if not args.no_cpu_baseline:
+            from oracle import pyoracle as orc
+            rh = raw.cpu().numpy(); th = t_ms.cpu().numpy()
+            t0 = time.perf_counter(); uh = orc.undistort(rh, th, poses, rot_end, pos_end, R_LI, t_LI); t1 = time.perf_counter()
+            orc.voxel_grid(np.c_[uh, np.zeros(len(uh), np.float32)].astype(np.float32), leaf, t_ms=th); t2 = time.perf_counter()
+            frontend["cpu_undistort_ms"] = (t1 - t0) * 1e3
+            frontend["cpu_voxel_grid_ms"] = (t2 - t1) * 1e3
+            frontend["cpu_kind"] = "port (oracle restatement, 1 thread)"
+        del raw, raw4, t_ms
     # sharded mode: the posterior of the sharded update must be the single-GPU posterior of the whole scan
     shard_check = None
     if shard:
@@ -346,7 +386,7 @@ def run_flivo(args, rank, world_size, local_rank):
     return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
-                trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check,
+                trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend,
                 search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
@@ -436,7 +476,7 @@ def main():
                                      "map replica + own scans per rank, no collective")},
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
-            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"],
+            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "frontend": r["frontend"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
         }
         print(json.dumps(line), file=out, flush=True)

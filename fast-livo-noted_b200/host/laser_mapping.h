@@ -5,6 +5,10 @@
 //                     otherwise the iterated update (on the device, one call) and map_incremental()
 //   h_share_model()   src/laser_mapping.cpp:485-645: one trip; returns the 9x9 HPH / 9 HPL of the compiled V1 path
 //   map_incremental() src/laser_mapping.cpp:329-389, ikd-Tree branch (:384)
+//   downsample_on_device()   downSizeFilterSurf.filter (:129-130) on the raw scan already in HBM (after
+//                            ImuProcess::UndistortPcl of host/imu_processing.h, or flivo_raw_upload)
+//   lasermap_fov_segment()   the sliding local map of the upstream-style main (src/origin_laserMapping.cpp:367-429):
+//                            which boxes leave the cube around the lidar, ikdtree.Delete_Point_Boxes, removed-point cache
 // Everything ROS (InitROS, callbacks, publishers), IMU propagation, VIO, GNSS and loop closure stay with the
 // caller: it fills `state` (the propagated prior) and `feats_down_body` (the down-sampled, undistorted scan in the
 // lidar frame) before Run(), exactly the two inputs the reference's step 5 reads.
@@ -21,6 +25,9 @@ struct LaserMappingOptions {          // the rosparams the path reads (src/laser
     int    max_iteration = 4;         // NUM_MAX_ITERATIONS (:968)
     double laser_point_cov = 0.001;   // LASER_POINT_COV (:975)
     double filter_size_map = 0.2;     // filter_size_map_min (:983) -> KD_TREE downsample size
+    double filter_size_surf = 0.5;    // filter_size_surf_min (:982) -> leaf of downSizeFilterSurf (:1111)
+    double cube_side_length = 200;    // cube_len (:984)
+    float  det_range = 300.0f;        // DET_RANGE (src/origin_laserMapping.cpp:89)
     double extrinsic_T[3] = {0, 0, 0};                   // Lidar_offset_to_IMU
     double extrinsic_R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; // Lidar_rot_to_IMU
     int    device = 0;
@@ -30,6 +37,7 @@ class LaserMapping {
 public:
     explicit LaserMapping(const LaserMappingOptions& opt = LaserMappingOptions())
         : NUM_MAX_ITERATIONS(opt.max_iteration), LASER_POINT_COV(opt.laser_point_cov), filter_size_map_min(opt.filter_size_map),
+          filter_size_surf_min(opt.filter_size_surf), cube_len(opt.cube_side_length), DET_RANGE(opt.det_range),
           ikdtree(0.5f, 0.6f, (float)opt.filter_size_map, opt.device) {
         memcpy(Lidar_offset_to_IMU, opt.extrinsic_T, sizeof(Lidar_offset_to_IMU));
         memcpy(Lidar_rot_to_IMU, opt.extrinsic_R, sizeof(Lidar_rot_to_IMU));
@@ -37,10 +45,14 @@ public:
 
     // One LiDAR frame through step 5 (src/laser_mapping.cpp:129-251).  Returns false when the frame only built the map.
     bool Run() {
-        feats_down_size = (int)feats_down_body.size();
+        if (!scan_on_device_) {
+            feats_down_size = (int)feats_down_body.size();
+            if (feats_down_size == 0) return false;
+            upload_scan();
+        }
         if (feats_down_size == 0) return false;
+        scan_on_device_ = false;   // consumed by this frame
         state_propagat = state;                                                      // :59
-        upload_scan();
         if (ikdtree.Root_Node == nullptr) {                                          // :134-142 first scan: world points, Build
             flivo_state st = to_flivo(state);
             std::vector<float> w((size_t)feats_down_size * 3);
@@ -49,7 +61,10 @@ public:
             ck(flivo_h_share_model(ikdtree.ctx(), &st, FLIVO_MODE_V1, 1, HTH, HTz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
                                    nullptr, w.data()), "Run/first scan");
             PointVector world(feats_down_size);
-            for (int i = 0; i < feats_down_size; ++i) { world[i] = feats_down_body[i]; world[i].x = w[3 * i]; world[i].y = w[3 * i + 1]; world[i].z = w[3 * i + 2]; }
+            for (int i = 0; i < feats_down_size; ++i) {
+                if ((size_t)i < feats_down_body.size()) world[i] = feats_down_body[i];
+                world[i].x = w[3 * i]; world[i].y = w[3 * i + 1]; world[i].z = w[3 * i + 2];
+            }
             ikdtree.Build(world);
             return false;
         }
@@ -97,6 +112,79 @@ public:
         if (added > 0 && ikdtree.Root_Node == nullptr) { PointVector none; ikdtree.Add_Points(none, true); }
     }
 
+    // downSizeFilterSurf.setInputCloud(feats_undistort); downSizeFilterSurf.filter(*feats_down_body) (:129-130) on the raw
+    // scan resident in HBM; the result is the scan of the next Run().  want_host_copy fills feats_down_body as well.
+    int downsample_on_device(bool want_host_copy = false) {
+        size_t n = 0;
+        ck(flivo_raw_downsample(ikdtree.ctx(), (float)filter_size_surf_min, &n), "downsample");
+        feats_down_size = (int)n;
+        scan_uploaded_ = true;
+        scan_on_device_ = true;
+        feats_down_body.clear();
+        if (want_host_copy && n) {
+            std::vector<float> buf(n * 4);
+            ck(flivo_scan_download(ikdtree.ctx(), buf.data(), n, &n), "scan download");
+            feats_down_body.resize(n);
+            for (size_t i = 0; i < n; ++i) {
+                feats_down_body[i].x = buf[4 * i]; feats_down_body[i].y = buf[4 * i + 1]; feats_down_body[i].z = buf[4 * i + 2];
+                feats_down_body[i].intensity = buf[4 * i + 3];
+            }
+        }
+        return (int)n;
+    }
+
+    // src/origin_laserMapping.cpp:367-429.  pos_LiD: position of the lidar in the world (state.pos_end in the non-IKFOM
+    // branch, :381).  Slides the local-map cube when the lidar comes within MOV_THRESHOLD * DET_RANGE of a face and
+    // deletes the slabs that left it.
+    void lasermap_fov_segment(const double pos_LiD[3]) {
+        const float MOV_THRESHOLD = 1.5f;                                            // :96
+        cub_needrm.clear();
+        kdtree_delete_counter = 0;
+        if (!Localmap_Initialized) {                                                 // :383-390
+            for (int i = 0; i < 3; i++) {
+                LocalMap_Points.vertex_min[i] = pos_LiD[i] - cube_len / 2.0;
+                LocalMap_Points.vertex_max[i] = pos_LiD[i] + cube_len / 2.0;
+            }
+            Localmap_Initialized = true;
+            return;
+        }
+        float dist_to_map_edge[3][2];
+        bool need_move = false;
+        for (int i = 0; i < 3; i++) {                                                // :394-399
+            dist_to_map_edge[i][0] = fabs(pos_LiD[i] - LocalMap_Points.vertex_min[i]);
+            dist_to_map_edge[i][1] = fabs(pos_LiD[i] - LocalMap_Points.vertex_max[i]);
+            if (dist_to_map_edge[i][0] <= MOV_THRESHOLD * DET_RANGE || dist_to_map_edge[i][1] <= MOV_THRESHOLD * DET_RANGE) need_move = true;
+        }
+        if (!need_move) return;
+        BoxPointType New_LocalMap_Points, tmp_boxpoints;
+        New_LocalMap_Points = LocalMap_Points;
+        const double a = (cube_len - 2.0 * MOV_THRESHOLD * DET_RANGE) * 0.5 * 0.9, b = double(DET_RANGE * (MOV_THRESHOLD - 1));
+        float mov_dist = (float)(a > b ? a : b);                                     // :403
+        for (int i = 0; i < 3; i++) {                                                // :404-419
+            tmp_boxpoints = LocalMap_Points;
+            if (dist_to_map_edge[i][0] <= MOV_THRESHOLD * DET_RANGE) {
+                New_LocalMap_Points.vertex_max[i] -= mov_dist;
+                New_LocalMap_Points.vertex_min[i] -= mov_dist;
+                tmp_boxpoints.vertex_min[i] = LocalMap_Points.vertex_max[i] - mov_dist;
+                cub_needrm.push_back(tmp_boxpoints);
+            } else if (dist_to_map_edge[i][1] <= MOV_THRESHOLD * DET_RANGE) {
+                New_LocalMap_Points.vertex_max[i] += mov_dist;
+                New_LocalMap_Points.vertex_min[i] += mov_dist;
+                tmp_boxpoints.vertex_max[i] = LocalMap_Points.vertex_min[i] + mov_dist;
+                cub_needrm.push_back(tmp_boxpoints);
+            }
+        }
+        LocalMap_Points = New_LocalMap_Points;
+        points_cache_collect();                                                      // :422
+        if (cub_needrm.size() > 0) kdtree_delete_counter = ikdtree.Delete_Point_Boxes(cub_needrm);   // :424
+    }
+    // src/origin_laserMapping.cpp:332-337
+    void points_cache_collect() {
+        PointVector points_history;
+        ikdtree.acquire_removed_points(points_history);
+        points_cache_size = (int)points_history.size();
+    }
+
     void Finish() {}
 
     // ---- data members the reference's step 5 reads / writes (same names) ------------------------------------
@@ -108,6 +196,14 @@ public:
     int NUM_MAX_ITERATIONS;
     double LASER_POINT_COV;
     double filter_size_map_min;
+    double filter_size_surf_min;
+    double cube_len;
+    float DET_RANGE;
+    BoxPointType LocalMap_Points{};
+    bool Localmap_Initialized = false;
+    std::vector<BoxPointType> cub_needrm;
+    int kdtree_delete_counter = 0;
+    int points_cache_size = 0;
     bool nearest_search_en = true;
     bool flg_EKF_inited = true, flg_EKF_converged = false;
     int effct_feat_num = 0;
@@ -141,4 +237,5 @@ private:
         if (rc != FLIVO_OK) throw std::runtime_error(std::string("LaserMapping::") + what + ": " + flivo_last_error(ikdtree.ctx()));
     }
     bool scan_uploaded_ = false;
+    bool scan_on_device_ = false;   // the current scan came from downsample_on_device(): feats_down_body may be empty
 };

@@ -4,11 +4,14 @@
 // tests/test_dropin_cpp.py and prints results as "key value..." lines for the Python side to compare with the oracle.
 //   test_dropin <scene.bin>         run on cuda:0
 //   test_dropin --no-gpu            only check that construction fails loudly without a device
+//   test_dropin --frontend <in.bin> <out.bin>   ImuProcess::UndistortPcl -> LaserMapping::downsample_on_device -> Run,
+//                                   then a walk through lasermap_fov_segment (tests/test_frontend_cpp.py)
 #include <stdio.h>
 #include <string.h>
 #include <stdexcept>
 #include <vector>
 
+#include "imu_processing.h"
 #include "laser_mapping.h"
 
 static std::vector<float> read_f32(FILE* f, size_t n) {
@@ -22,7 +25,81 @@ static std::vector<double> read_f64(FILE* f, size_t n) {
     return v;
 }
 
+// front end through the drop-in classes, the way the upstream-style main chains them (src/origin_laserMapping.cpp:1290-1376)
+static int run_frontend(const char* in_path, const char* out_path) {
+    FILE* f = fopen(in_path, "rb");
+    if (!f) { perror("open"); return 2; }
+    int32_t hdr[4];   // n_raw, n_imu, n_map, n_walk
+    if (fread(hdr, 4, 4, f) != 4) return 2;
+    std::vector<double> par = read_f64(f, 5);   // ds_map, leaf, cube_len, det_range, lidar_beg_time
+    std::vector<double> x = read_f64(f, 36);
+    std::vector<double> imu = read_f64(f, (size_t)(hdr[1] + 1) * 7);   // last_imu_ first, then the frame's samples
+    std::vector<float> raw = read_f32(f, (size_t)hdr[0] * 5);
+    std::vector<float> map = read_f32(f, (size_t)hdr[2] * 3);
+    std::vector<double> walk = read_f64(f, (size_t)hdr[3] * 3);
+    fclose(f);
+    FILE* o = fopen(out_path, "wb");
+    if (!o) { perror("open out"); return 2; }
+    try {
+        LaserMappingOptions opt;
+        opt.filter_size_map = par[0]; opt.filter_size_surf = par[1]; opt.cube_side_length = par[2]; opt.det_range = (float)par[3];
+        memcpy(opt.extrinsic_R, &x[12], 72); memcpy(opt.extrinsic_T, &x[21], 24);
+        LaserMapping lm(opt);
+        ImuProcess p_imu;
+        p_imu.set_extrinsic(opt.extrinsic_T, opt.extrinsic_R);
+        auto to_msg = [&](int k) { ImuMsg m; m.stamp = imu[7 * k]; memcpy(m.angular_velocity, &imu[7 * k + 1], 24); memcpy(m.linear_acceleration, &imu[7 * k + 4], 24); return m; };
+        p_imu.last_imu_ = to_msg(0);
+        p_imu.last_lidar_end_time_ = par[4];
+        memcpy(p_imu.mean_acc, &x[33], 24);   // |gravity|-sized mean acceleration: scale factor G_m_s2/|mean_acc| ~ 1
+        LidarMeasureGroup meas;
+        meas.lidar_beg_time = par[4];
+        for (int k = 1; k <= hdr[1]; ++k) meas.imu.push_back(to_msg(k));
+        meas.lidar.resize(hdr[0]);
+        for (int i = 0; i < hdr[0]; ++i) {
+            meas.lidar[i].x = raw[5 * i]; meas.lidar[i].y = raw[5 * i + 1]; meas.lidar[i].z = raw[5 * i + 2];
+            meas.lidar[i].intensity = raw[5 * i + 3]; meas.lidar[i].curvature = raw[5 * i + 4];
+        }
+        memcpy(lm.state.rot_end, &x[0], 72); memcpy(lm.state.pos_end, &x[9], 24);
+        memcpy(lm.state.vel_end, &x[24], 24); memcpy(lm.state.bias_g, &x[27], 24); memcpy(lm.state.bias_a, &x[30], 24);
+        memcpy(lm.state.gravity, &x[33], 24);
+        p_imu.UndistortPcl(lm.ikdtree.ctx(), meas, lm.state);
+        // out: n_poses, poses, state (rot9 pos3 vel3), cov 324, undistorted n*4, n_down, down n*4
+        int32_t np = (int32_t)p_imu.IMUpose.size();
+        fwrite(&np, 4, 1, o);
+        fwrite(p_imu.IMUpose.data(), sizeof(flivo_pose6d), np, o);
+        fwrite(lm.state.rot_end, 8, 9, o); fwrite(lm.state.pos_end, 8, 3, o); fwrite(lm.state.vel_end, 8, 3, o);
+        fwrite(lm.state.cov, 8, 324, o);
+        PointVector und;
+        p_imu.download_undistorted(lm.ikdtree.ctx(), und, meas);
+        for (auto& q : und) { float v[4] = {q.x, q.y, q.z, q.intensity}; fwrite(v, 4, 4, o); }
+        int32_t nd = lm.downsample_on_device(true);
+        fwrite(&nd, 4, 1, o);
+        for (auto& q : lm.feats_down_body) { float v[4] = {q.x, q.y, q.z, q.intensity}; fwrite(v, 4, 4, o); }
+        printf("frontend raw %d poses %d down %d\n", hdr[0], np, nd);
+        // first frame builds the map from the down-sampled scan (device-resident scan, no host copy needed)
+        bool updated = lm.Run();
+        printf("run updated %d size %d root %d\n", (int)updated, lm.ikdtree.size(), lm.ikdtree.Root_Node != nullptr);
+        // sliding local map over a separate, larger cloud
+        PointVector cloud(hdr[2]);
+        for (int i = 0; i < hdr[2]; ++i) { cloud[i].x = map[3 * i]; cloud[i].y = map[3 * i + 1]; cloud[i].z = map[3 * i + 2]; }
+        lm.ikdtree.Build(cloud);
+        for (int k = 0; k < hdr[3]; ++k) {
+            lm.lasermap_fov_segment(&walk[3 * k]);
+            printf("fov %d boxes %zu deleted %d valid %d cache %d box %.9g %.9g %.9g %.9g %.9g %.9g\n", k, lm.cub_needrm.size(), lm.kdtree_delete_counter,
+                   lm.ikdtree.validnum(), lm.points_cache_size, lm.LocalMap_Points.vertex_min[0], lm.LocalMap_Points.vertex_min[1],
+                   lm.LocalMap_Points.vertex_min[2], lm.LocalMap_Points.vertex_max[0], lm.LocalMap_Points.vertex_max[1], lm.LocalMap_Points.vertex_max[2]);
+        }
+    } catch (const std::exception& e) {
+        printf("error: %s\n", e.what());
+        fclose(o);
+        return 1;
+    }
+    fclose(o);
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc >= 4 && strcmp(argv[1], "--frontend") == 0) return run_frontend(argv[2], argv[3]);
     if (argc >= 2 && strcmp(argv[1], "--no-gpu") == 0) {
         try {
             KD_TREE t(0.5f, 0.6f, 0.5f);
