@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--no-frontend", action="store_true", help="skip the informational front-end (undistort + voxel grid) timing")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="sharded mode: how the per-trip 96-double records travel")
     return ap.parse_args()
 
 
@@ -220,9 +221,14 @@ def run_flivo(args, rank, world_size, local_rank):
     map_build_s = time.time() - t0
     del world
     if shard:   # config 5: contiguous block of every scan per rank + allgather of the normal-equation block per trip
-        uid = [pkg.Flivo.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        F.comm_init(uid[0], rank, world_size)
+        if args.exchange == "peer":   # records written straight into the peers' HBM by the solve kernel (NVLink)
+            handles = [None] * world_size
+            dist.all_gather_object(handles, F.peer_export())
+            F.peer_attach(handles, rank, world_size)
+        else:                         # NCCL all-gather between two solve-kernel launches
+            uid = [pkg.Flivo.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            F.comm_init(uid[0], rank, world_size)
         for s in scans:
             import importlib
             lo, hi = importlib.import_module("fast_livo_noted_b200.sharding").shard_range(len(s["body"]), rank, world_size)
@@ -472,7 +478,7 @@ def main():
                        "policy": "force_search" if args.force_search else "reference_rematch", "scans_rotated": args.scans,
                        "trips_per_step": r["trips_per_step"], "sort_scan": bool(args.sort_scan),
                        "l2": "512 MiB buffer written between timed steps (untimed); map 20M pts > L2",
-                       "multi_gpu": ("one scan sharded over ranks, allgather of 96 doubles per trip" if r["shard"] else
+                       "multi_gpu": (("one scan sharded over ranks; per trip 96 doubles per rank, " + ("stored into the peers' HBM by the solve kernel (NVLink peer memory)" if args.exchange == "peer" else "ncclAllGather")) if r["shard"] else
                                      "map replica + own scans per rank, no collective")},
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},

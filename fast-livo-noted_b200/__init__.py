@@ -101,7 +101,7 @@ SYMBOLS = [
     "flivo_repack_v1", "flivo_iekf_update", "flivo_map_add_scan", "flivo_comm_unique_id", "flivo_comm_init",
     "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps",
     "flivo_raw_upload", "flivo_raw_set_device", "flivo_raw_undistort", "flivo_raw_downsample", "flivo_raw_download",
-    "flivo_scan_download",
+    "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach",
 ]
 
 _lib = None
@@ -150,6 +150,9 @@ def lib():
     L.flivo_comm_destroy.argtypes = [vp]
     L.flivo_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.flivo_debug_solve_stamps.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
+    L.flivo_peer_export.argtypes = [vp, vp]
+    L.flivo_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
+    L.flivo_peer_detach.argtypes = [vp]
     L.flivo_raw_upload.argtypes = [vp, vp, sz, sz, C.c_int, C.c_int]
     L.flivo_raw_set_device.argtypes = [vp, vp, vp, sz]
     L.flivo_raw_undistort.argtypes = [vp, C.POINTER(Pose6D), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
@@ -408,6 +411,20 @@ class Flivo:
     def comm_init(self, uid, rank, nranks):
         buf = (C.c_char * 128).from_buffer_copy(uid)
         self._ck(self._L.flivo_comm_init(self.h, buf, rank, nranks))
+
+    def peer_export(self):
+        buf = (C.c_char * 64)()
+        self._ck(self._L.flivo_peer_export(self.h, buf))
+        return bytes(buf)
+
+    def peer_attach(self, handles, rank, nranks):
+        """handles: the 64-byte handles of all ranks, in rank order."""
+        blob = b"".join(handles)
+        buf = (C.c_char * len(blob)).from_buffer_copy(blob)
+        self._ck(self._L.flivo_peer_attach(self.h, buf, rank, nranks))
+
+    def peer_detach(self):
+        self._ck(self._L.flivo_peer_detach(self.h))
 
     def comm_destroy(self):
         self._ck(self._L.flivo_comm_destroy(self.h))

@@ -132,6 +132,11 @@ struct flivo_ctx {
     // multi-GPU
     ncclComm_t comm = nullptr;
     int rank = 0, nranks = 1;
+    // peer-memory exchange (NVLink): own buffer + the peers' buffers mapped through cudaIpc
+    PeerSlot* d_xchg = nullptr;
+    unsigned long long* d_xseq = nullptr;
+    PeerSlot* peer_base[PEER_MAX_RANKS] = {};
+    bool peer_on = false;
 };
 
 #define CKC(call)                                                                        \
@@ -159,7 +164,7 @@ static int host_threads() {
     static int t = 0;
     if (t == 0) {
         const char* e = getenv("FLIVO_HOST_THREADS");
-        t = e ? atoi(e) : 4;   // MP_PROC_NUM of the reference on a >5-core host (CMakeLists.txt:33-36)
+        t = e ? atoi(e) : 8;   // (the reference's own loop runs MP_PROC_NUM = 4 threads on a >5-core host, CMakeLists.txt:33-36)
         if (t < 1) t = 1;
         if (t > omp_get_num_procs()) t = omp_get_num_procs();
     }
@@ -177,7 +182,7 @@ static int stage_points(flivo_ctx* ctx, const float* xyz, size_t n, size_t strid
     }
     const char* src = reinterpret_cast<const char*>(xyz);
     float4* h = ctx->h_stage;
-    const size_t CH = 1u << 16;
+    const size_t CH = 1u << 15;
     const int nt = host_threads();
     for (size_t c0 = 0; c0 < n; c0 += CH) {
         const size_t m = std::min(CH, n - c0);
@@ -354,6 +359,8 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     free_scan(ctx);
     free_raw(ctx);
     cudaFree(ctx->d_vg_state); cudaFree(ctx->d_poses);
+    if (ctx->peer_on) for (int r = 0; r < ctx->nranks; ++r) if (r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
+    cudaFree(ctx->d_xchg); cudaFree(ctx->d_xseq);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
     cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_stamps); cudaFree(ctx->d_pre);
     for (int i = 0; i <= MAX_TRIPS; ++i) { if (ctx->ev_fork[i]) cudaEventDestroy(ctx->ev_fork[i]); if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]); }
@@ -746,8 +753,7 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
     cudaStream_t s = ctx->stream;
     cudaGraph_t g = nullptr;
     CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-    SolveParams S = S0;
-    S.phase = SOLVE_PHASE_FULL;
+    SolveParams S = S0;   // S0.phase: FULL, or PEER when the peer-memory exchange is attached
     for (int t = 0; t < trips && t <= MAX_TRIPS; ++t) {
         // fork: the state-only half of the solve runs beside the search / fused kernels of the trip
         CKC(cudaEventRecord(ctx->ev_fork[t], s));
@@ -794,6 +800,11 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     S.sum_out = ctx->d_sum; S.rank_blocks = ctx->d_rank_blocks; S.ctl = ctx->d_ctl;
     S.stamps = timed ? ctx->d_stamps : nullptr;
     S.pre = ctx->d_pre;
+    if (ctx->peer_on) {
+        for (int r = 0; r < ctx->nranks; ++r) S.peer.base[r] = ctx->peer_base[r];
+        S.peer.seq = ctx->d_xseq; S.peer.rank = ctx->rank; S.peer.nranks = ctx->nranks;
+    }
+    const int full_phase = ctx->peer_on ? SOLVE_PHASE_PEER : SOLVE_PHASE_FULL;
     const int sgrid = search_grid(ctx), fgrid = fused_grid(ctx);
     int launches = 1;
     auto launch_trip = [&](int t, bool with_events) -> int {
@@ -802,7 +813,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
         launch_search(P, sgrid, s);   // exits at once on re-use trips
         launch_fused(P, fgrid, s);
         if (with_events) CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
-        if (ctx->comm) {
+        if (ctx->comm && !ctx->peer_on) {
             S.phase = SOLVE_PHASE_REDUCE_ONLY;
             launch_solve(S, s);
             int nrc = g_nccl.AllGather(ctx->d_sum, ctx->d_rank_blocks, PSTRIDE, NCCL_DOUBLE, ctx->comm, s);
@@ -811,16 +822,16 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
             launch_solve(S, s);
             launches += 5;
         } else {
-            S.phase = SOLVE_PHASE_FULL;
+            S.phase = full_phase;
             launch_solve(S, s);
             launches += 4;
         }
         return FLIVO_OK;
     };
-    bool use_graph = !timed && !ctx->comm;
+    bool use_graph = !timed && (!ctx->comm || ctx->peer_on);   // an NCCL call between the kernels is not captured
     if (use_graph) {
         // the sequence depends only on (P, S, grids, trips): replay the captured graph unless one of them changed
-        S.phase = SOLVE_PHASE_FULL;
+        S.phase = full_phase;
         const bool same = ctx->graph_exec && memcmp(&P, &ctx->graph_P, sizeof(P)) == 0 && memcmp(&S, &ctx->graph_S, sizeof(S)) == 0 &&
                           sgrid == ctx->graph_search_grid && fgrid == ctx->graph_fused_grid && trips == ctx->graph_trips;
         if (!same) {
@@ -869,7 +880,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
         cudaEventElapsedTime(&rep->gpu_ms, ctx->ev[0], ctx->ev[1 + 2 * trips]);
         rep->kernel_launches = launches;
     }
-    if (c.nan_guard) { ctx->err = "non-finite normal equations: update skipped"; return FLIVO_E_STATE; }
+    if (c.nan_guard) { ctx->err = ctx->peer_on ? "non-finite normal equations or peer exchange timed out: update skipped" : "non-finite normal equations: update skipped"; return FLIVO_E_STATE; }
     return FLIVO_OK;
 }
 
@@ -929,6 +940,66 @@ extern "C" int flivo_comm_destroy(flivo_ctx* ctx) {
         ctx->comm = nullptr;
     }
     ctx->rank = 0; ctx->nranks = 1;
+    return FLIVO_OK;
+}
+
+// ---- peer-memory exchange over NVLink / NVSwitch (replaces the NCCL all-gather of the sharded update) ---------------
+// Every rank allocates one exchange buffer ([2 parities][PEER_MAX_RANKS] records + flags), exports it as a cudaIpc
+// handle, and maps the buffers of all ranks; k_solve (SOLVE_PHASE_PEER) then writes its 96-double record straight into
+// every peer's buffer, publishes a sequence number, waits for the peers' sequence numbers in its own buffer and sums
+// the records in rank order — compute, exchange and solve in one kernel, and the whole update stays one CUDA graph.
+extern "C" int flivo_peer_export(flivo_ctx* ctx, void* handle_out64) {
+    ENTER();
+    NEED(handle_out64, FLIVO_E_ARG, "null handle");
+    static_assert(sizeof(cudaIpcMemHandle_t) == FLIVO_PEER_HANDLE_BYTES, "ipc handle size");
+    if (!ctx->d_xchg) {
+        const size_t bytes = sizeof(PeerSlot) * 2 * PEER_MAX_RANKS;
+        CKC(cudaMalloc(&ctx->d_xchg, bytes));
+        CKC(cudaMemset(ctx->d_xchg, 0, bytes));
+        CKC(cudaMalloc(&ctx->d_xseq, sizeof(unsigned long long)));
+        CKC(cudaMemset(ctx->d_xseq, 0, sizeof(unsigned long long)));
+    }
+    cudaIpcMemHandle_t h;
+    CKC(cudaIpcGetMemHandle(&h, ctx->d_xchg));
+    memcpy(handle_out64, &h, sizeof(h));
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_peer_attach(flivo_ctx* ctx, const void* handles, int rank, int nranks) {
+    ENTER();
+    NEED(handles && nranks >= 1 && nranks <= PEER_MAX_RANKS && rank >= 0 && rank < nranks, FLIVO_E_ARG, "bad rank / nranks (<= 8) / handles");
+    NEED(ctx->d_xchg, FLIVO_E_STATE, "call flivo_peer_export first");
+    NEED(!ctx->peer_on, FLIVO_E_STATE, "peers already attached");
+    const char* hp = static_cast<const char*>(handles);
+    for (int r = 0; r < nranks; ++r) {
+        if (r == rank) { ctx->peer_base[r] = ctx->d_xchg; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, hp + (size_t)r * sizeof(h), sizeof(h));
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            ctx->err = std::string("cudaIpcOpenMemHandle (rank ") + std::to_string(r) + "): " + cudaGetErrorString(e);
+            for (int q = 0; q < r; ++q) if (q != rank && ctx->peer_base[q]) { cudaIpcCloseMemHandle(ctx->peer_base[q]); ctx->peer_base[q] = nullptr; }
+            return FLIVO_E_CUDA;
+        }
+        ctx->peer_base[r] = static_cast<PeerSlot*>(p);
+    }
+    ctx->rank = rank; ctx->nranks = nranks;
+    ctx->peer_on = true;
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_peer_detach(flivo_ctx* ctx) {
+    ENTER();
+    if (ctx->peer_on) {
+        CKC(cudaStreamSynchronize(ctx->stream));
+        for (int r = 0; r < ctx->nranks; ++r) {
+            if (r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
+            ctx->peer_base[r] = nullptr;
+        }
+        ctx->peer_on = false;
+        if (!ctx->comm) { ctx->rank = 0; ctx->nranks = 1; }
+    }
     return FLIVO_OK;
 }
 

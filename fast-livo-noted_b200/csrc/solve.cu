@@ -374,7 +374,49 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     if (S.phase != SOLVE_PHASE_REDUCE_ONLY && ctl->stopped) return;
 
     // ---- 0. normal equations -------------------------------------------------------------------------
-    if (S.phase == SOLVE_PHASE_FROM_RANKS) {
+    if (S.phase == SOLVE_PHASE_PEER) {
+        // ---- fused reduce + exchange over peer memory ------------------------------------------------------
+        // Every rank holds the same state, so all ranks run the same trips and their exchange counters agree.
+        __shared__ unsigned long long s_seq;
+        __shared__ int s_timeout;
+        reduce_groups(S.gpartials, S.job->groups, s_slices, s_sum, tid, NT);
+        if (tid == 0) { s_seq = *S.peer.seq + 1ull; s_timeout = 0; }
+        __syncthreads();
+        const unsigned long long seq = s_seq;
+        const int par = (int)(seq & 1ull), me = S.peer.rank, nr = S.peer.nranks;
+        for (int e = tid; e < nr * PSTRIDE; e += NT) {                 // my record -> every rank's buffer (NVLink stores)
+            const int r = e / PSTRIDE, t = e - r * PSTRIDE;
+            S.peer.base[r][par * PEER_MAX_RANKS + me].rec[t] = (t < NTERMS) ? s_sum[t] : 0.0;
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (tid < nr) {
+            unsigned long long* f = &S.peer.base[tid][par * PEER_MAX_RANKS + me].flag;
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(seq) : "memory");
+            // wait for rank `tid`'s record in my own buffer (bounded: a lost peer must not hang the GPU)
+            const unsigned long long* g = &S.peer.base[me][par * PEER_MAX_RANKS + tid].flag;
+            unsigned long long t0, t1, v;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            for (;;) {
+                asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(g) : "memory");
+                if (v == seq) break;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 2000000000ull) { s_timeout = 1; break; }      // 2 s
+            }
+        }
+        __syncthreads();
+        if (tid < NTERMS) {                                             // fixed rank order: bit-identical on all ranks
+            double s = 0.0;
+            for (int r = 0; r < nr; ++r) {
+                double v;
+                asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(&S.peer.base[me][par * PEER_MAX_RANKS + r].rec[tid]) : "memory");
+                s += v;
+            }
+            s_sum[tid] = s_timeout ? __longlong_as_double(0x7FF8000000000000ll) : s;   // NaN -> the guard below stops the update
+        }
+        if (tid == 0) *S.peer.seq = seq;
+        __syncthreads();
+    } else if (S.phase == SOLVE_PHASE_FROM_RANKS) {
         // multi-GPU: every rank's 92-term block was gathered; sum in rank order (bit-identical on all ranks)
         if (tid < NTERMS) {
             double s = 0.0;

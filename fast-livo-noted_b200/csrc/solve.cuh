@@ -7,7 +7,22 @@ namespace flivo {
 enum {
     SOLVE_PHASE_FULL = 0,         // reduce the group partials, then solve (single GPU)
     SOLVE_PHASE_REDUCE_ONLY = 1,  // reduce only: sum_out[92] (flivo_h_share_model; first half of the multi-GPU trip)
-    SOLVE_PHASE_FROM_RANKS = 2    // sum rank_blocks[nranks][96] in rank order, then solve (second half, multi-GPU)
+    SOLVE_PHASE_FROM_RANKS = 2,   // sum rank_blocks[nranks][96] in rank order, then solve (second half, multi-GPU, NCCL)
+    SOLVE_PHASE_PEER = 3          // multi-GPU, fused: reduce, write the record into every peer's exchange buffer over
+                                  // NVLink, wait for the peers' records, sum in rank order, solve — one kernel
+};
+
+// Exchange buffer of one rank, mapped into every peer (cudaIpc): slots[parity][source rank].
+constexpr int PEER_MAX_RANKS = 8;
+struct PeerSlot {
+    double rec[PSTRIDE];
+    unsigned long long flag;      // sequence number of the exchange that filled rec
+    unsigned long long pad[7];
+};
+struct PeerXchg {
+    PeerSlot* base[PEER_MAX_RANKS];   // base[r]: rank r's buffer ([2][PEER_MAX_RANKS] slots) as mapped into this process
+    unsigned long long* seq;          // this rank's exchange counter (device memory, never reset)
+    int rank, nranks;
 };
 
 // State-only half of a trip's solve, computed by k_solve_pre on a parallel branch of the update graph while the
@@ -31,6 +46,7 @@ struct SolveParams {
     const double* rank_blocks; // [nranks * PSTRIDE]
     Ctl* ctl;
     SolvePre* pre;             // written by k_solve_pre, read by k_solve of the same trip
+    PeerXchg peer;             // SOLVE_PHASE_PEER
     unsigned long long* stamps;       // profile mode only: [MAX_TRIPS][16] globaltimer values at the phase boundaries of k_solve
 };
 

@@ -199,6 +199,14 @@ int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t* n_added);
 int flivo_comm_unique_id(void* out128);
 int flivo_comm_init(flivo_ctx* ctx, const void* unique_id128, int rank, int nranks);
 int flivo_comm_destroy(flivo_ctx* ctx);
+/* Peer-memory exchange over NVLink / NVSwitch for the sharded update (one process per GPU, one node, <= 8 ranks):
+ * replaces the NCCL all-gather by stores into the peers' memory from inside the solve kernel, so that reduce, exchange and
+ * solve are one kernel and the update one CUDA graph.  Every rank: flivo_peer_export -> the caller gathers the 64-byte
+ * handles of all ranks in rank order (any transport, e.g. torch.distributed.all_gather_object) -> flivo_peer_attach. */
+#define FLIVO_PEER_HANDLE_BYTES 64
+int flivo_peer_export(flivo_ctx* ctx, void* handle_out64);
+int flivo_peer_attach(flivo_ctx* ctx, const void* handles /* nranks * 64 bytes */, int rank, int nranks);
+int flivo_peer_detach(flivo_ctx* ctx);
 
 /* ---- introspection used by bench.py ------------------------------------------------------------ */
 typedef struct flivo_stats {
