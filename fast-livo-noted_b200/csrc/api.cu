@@ -164,7 +164,16 @@ static int host_threads() {
     static int t = 0;
     if (t == 0) {
         const char* e = getenv("FLIVO_HOST_THREADS");
-        t = e ? atoi(e) : 8;   // (the reference's own loop runs MP_PROC_NUM = 4 threads on a >5-core host, CMakeLists.txt:33-36)
+        if (e) {
+            t = atoi(e);
+        } else {
+            // up to 8 repack threads, but never more than this process's share of the host when several ranks
+            // (one per GPU, LOCAL_WORLD_SIZE of torchrun) stage scans at the same time: oversubscribed OpenMP
+            // teams spin against each other.  (The reference's own loop runs MP_PROC_NUM = 4, CMakeLists.txt:33-36.)
+            const char* lw = getenv("LOCAL_WORLD_SIZE");
+            const int ranks = lw ? std::max(1, atoi(lw)) : 1;
+            t = std::min(8, std::max(1, omp_get_num_procs() / ranks));
+        }
         if (t < 1) t = 1;
         if (t > omp_get_num_procs()) t = omp_get_num_procs();
     }
