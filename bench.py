@@ -306,6 +306,16 @@ def run_flivo(args, rank, world_size, local_rank):
             solve_ms.append(st.last_solve_ms[t])
         far_q, cand = int(st.last_far_queries), int(st.last_candidates)
         if k == min(args.steps, 8) - 1:
+            ss = F.search_stamps().astype(np.int64)
+            ss = ss[ss[:, 2] > 0]
+            if len(ss):
+                t0 = ss[:, 0].min()
+                p1 = (ss[:, 1] - t0) / 1e3; en = (ss[:, 2] - t0) / 1e3; st0 = (ss[:, 0] - t0) / 1e3
+                q = lambda a: "p50=%.1f p90=%.1f max=%.1f" % (np.percentile(a, 50), np.percentile(a, 90), a.max())
+                print(f"[search CTAs, first search trip, us since first CTA start] ctas={len(ss)} start: {q(st0)} | end of tile phase: {q(p1)} | end: {q(en)} | far queries per CTA: max={int(ss[:, 3].max())} sum={int(ss[:, 3].sum())}", file=sys.stderr)
+                ft = F.far_totals.astype(np.int64)
+                if ft[1]:
+                    print(f"[far queries, first search trip] n={ft[1]} mean {ft[0] / ft[1] / 1e3:.1f} us, {ft[2] / ft[1]:.2f} steps; final radius histogram (cells) {dict((r, int(ft[3 + r])) for r in range(13) if ft[3 + r])}; seeded candidates histogram {dict((c, int(ft[16 + c])) for c in range(6) if ft[16 + c])}; max {ft[22] / 1e3:.1f} us; mean us by final radius {dict((r, round(ft[23 + r] / max(ft[3 + r], 1) / 1e3, 1)) for r in range(9) if ft[3 + r])}", file=sys.stderr)
             stamps = F.solve_stamps(repp.trips)
             for t in range(repp.trips):
                 row = stamps[t].astype(np.int64)

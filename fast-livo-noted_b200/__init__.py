@@ -99,7 +99,7 @@ SYMBOLS = [
     "flivo_map_add_boxes", "flivo_map_delete_points", "flivo_map_size", "flivo_map_range", "flivo_map_flatten",
     "flivo_map_acquire_removed", "flivo_knn", "flivo_scan_upload", "flivo_scan_set_device", "flivo_h_share_model",
     "flivo_repack_v1", "flivo_iekf_update", "flivo_map_add_scan", "flivo_comm_unique_id", "flivo_comm_init",
-    "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps",
+    "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps", "flivo_debug_search_stamps",
     "flivo_raw_upload", "flivo_raw_set_device", "flivo_raw_undistort", "flivo_raw_downsample", "flivo_raw_download",
     "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach",
 ]
@@ -150,6 +150,7 @@ def lib():
     L.flivo_comm_destroy.argtypes = [vp]
     L.flivo_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.flivo_debug_solve_stamps.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
+    L.flivo_debug_search_stamps.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int, C.POINTER(C.c_int)]
     L.flivo_peer_export.argtypes = [vp, vp]
     L.flivo_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
     L.flivo_peer_detach.argtypes = [vp]
@@ -392,6 +393,16 @@ class Flivo:
         buf = (C.c_uint64 * (trips * 16))()
         self._ck(self._L.flivo_debug_solve_stamps(self.h, buf, trips))
         return np.ctypeslib.as_array(buf).reshape(trips, 16).copy()
+
+    def search_stamps(self):
+        """[ctas][4] per-CTA stamps (ns) of the first search trip of the last profile-mode update."""
+        cap = 4096
+        buf = (C.c_uint64 * ((cap + 8) * 4))()
+        n = C.c_int(0)
+        self._ck(self._L.flivo_debug_search_stamps(self.h, buf, cap + 8, C.byref(n)))
+        a = np.ctypeslib.as_array(buf)
+        self.far_totals = a[cap * 4:cap * 4 + 32].copy()   # [sum ns, queries, sum steps, radius histogram 3.., seed-count histogram 16..]
+        return a[:cap * 4].reshape(cap, 4)[:min(n.value, cap)].copy()
 
     def sync(self):
         self._ck(self._L.flivo_sync(self.h))

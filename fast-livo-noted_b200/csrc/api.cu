@@ -60,6 +60,8 @@ struct DevBlock {
     double sum[PSTRIDE];
 };
 
+constexpr int SSTAMP_CTAS = 4096;
+
 struct flivo_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -117,6 +119,7 @@ struct flivo_ctx {
     Ctl* d_ctl = nullptr;           // the pointers below point into d_blk
     SearchStats* d_stats = nullptr;
     unsigned long long* d_stamps = nullptr;   // [MAX_TRIPS][16] k_solve phase stamps (profile mode)
+    unsigned long long* d_sstamps = nullptr;  // [SSTAMP_CTAS][4] k_search per-CTA stamps (profile mode)
     SolvePre* d_pre = nullptr;                // state-only half of a trip's solve (k_solve_pre -> k_solve)
     cudaStream_t side = nullptr;              // branch of the update graph that runs k_solve_pre beside the search
     cudaEvent_t ev_fork[MAX_TRIPS + 1] = {}, ev_join[MAX_TRIPS + 1] = {};
@@ -310,6 +313,7 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     upload_term_table();
     CKC(cudaGetLastError());
     CKC(cudaMalloc(&ctx->d_blk, sizeof(DevBlock)));
+    CKC(cudaMalloc(&ctx->d_sstamps, ((size_t)SSTAMP_CTAS * 4 + 32) * sizeof(unsigned long long)));
     CKC(cudaMalloc(&ctx->d_pre, sizeof(SolvePre)));
     CKC(cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking));
     for (int i = 0; i <= MAX_TRIPS; ++i) {
@@ -371,7 +375,7 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     if (ctx->peer_on) for (int r = 0; r < ctx->nranks; ++r) if (r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
     cudaFree(ctx->d_xchg); cudaFree(ctx->d_xseq);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
-    cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_stamps); cudaFree(ctx->d_pre);
+    cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_stamps); cudaFree(ctx->d_sstamps); cudaFree(ctx->d_pre);
     for (int i = 0; i <= MAX_TRIPS; ++i) { if (ctx->ev_fork[i]) cudaEventDestroy(ctx->ev_fork[i]); if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]); }
     if (ctx->side) cudaStreamDestroy(ctx->side);
     cudaFree(ctx->d_rank_blocks);
@@ -645,7 +649,8 @@ static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, d
 // launch grids are rounded up to capacity buckets so that scans of similar size share one captured graph;
 // surplus CTAs see i >= job->n (k_search) or an exhausted unit counter (k_fused) and leave at once
 static int search_grid(flivo_ctx* ctx) {
-    const int tiles = (int)((ctx->scan_n + 127) / 128);
+    const int tp = search_tile_points();
+    const int tiles = (int)((ctx->scan_n + tp - 1) / tp);
     if (ctx->search_resident <= 0) ctx->search_resident = ctx->sm_count * search_ctas_per_sm();
     return std::max(1, std::min(((tiles + 255) / 256) * 256, ctx->search_resident));   // tiles are dealt dynamically
 }
@@ -802,6 +807,10 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     CKC(cudaMemcpyAsync(ctx->d_blk, h, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s));   // job + P_prop + x
     launch_ctl_reset(ctx->d_blk->x, ctx->d_blk->x_prop, ctx->d_blk->P_prop, ctx->d_blk->P_out, ctx->d_ctl, ctx->d_stats, s);
     FusedParams P = make_fused(ctx);
+    if (timed && search_grid(ctx) <= SSTAMP_CTAS) {
+        CKC(cudaMemsetAsync(ctx->d_sstamps, 0, ((size_t)SSTAMP_CTAS * 4 + 32) * sizeof(unsigned long long), s));
+        P.search_stamps = ctx->d_sstamps;
+    }
     SolveParams S;
     memset(&S, 0, sizeof(S));
     S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job;
@@ -1219,6 +1228,20 @@ extern "C" int flivo_raw_download(flivo_ctx* ctx, float* out_xyzi, size_t cap, s
     if (n == 0 || cap == 0) return FLIVO_OK;
     NEED(cap >= n, FLIVO_E_CAPACITY, "output too small");
     CKC(cudaMemcpyAsync(out_xyzi, ctx->d_raw, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+
+// Diagnostic: per-CTA globaltimer stamps of the FIRST search trip of the last profile-mode update:
+// out[cta][4] = {start, end of phase 1 (tiles), end, far queries finished by the CTA}; *n_ctas = launch grid.
+extern "C" int flivo_debug_search_stamps(flivo_ctx* ctx, uint64_t* out, int ctas_cap, int* n_ctas) {
+    if (!ctx || !out || ctas_cap <= 0) return FLIVO_E_ARG;
+    const int g = search_grid(ctx);
+    if (n_ctas) *n_ctas = g;
+    const int m = std::min(std::min(g, ctas_cap), SSTAMP_CTAS);
+    CKC(cudaMemcpyAsync(out, ctx->d_sstamps, (size_t)m * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctas_cap >= SSTAMP_CTAS + 8)   // far-search totals ride behind the per-CTA rows: out[SSTAMP_CTAS*4 .. +32]
+        CKC(cudaMemcpyAsync(out + (size_t)SSTAMP_CTAS * 4, ctx->d_sstamps + (size_t)SSTAMP_CTAS * 4, 32 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
     CKC(cudaStreamSynchronize(ctx->stream));
     return FLIVO_OK;
 }

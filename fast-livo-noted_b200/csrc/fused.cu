@@ -431,7 +431,7 @@ __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) {
 //            cannot deadlock whatever the grid size.  Entries carry the epoch of the trip, so the list never needs
 //            clearing.  After FAR_BATCH finished queries the warp's lanes fit the planes of the batch, one lane each.
 // Exits at once on re-use trips (ctl->search == 0 and no force_search) and after the loop stopped.
-__global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
+__global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search(FusedParams P) {
     __shared__ double s_state[24];
     __shared__ SearchSmem S;
     __shared__ unsigned s_tile;
@@ -439,6 +439,9 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
     __shared__ float2 s_bmeta[SEARCH_WARPS][FAR_BATCH];
     Ctl* ctl = P.ctl;
     if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
+    unsigned long long t_start = 0, t_p1 = 0;
+    const bool stamp_on = P.search_stamps != nullptr && ctl->searches == 0;   // first search trip of the update
+    if (stamp_on && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
     if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = P.job->n;
@@ -479,6 +482,15 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
                 const float d5 = (cnt >= 5) ? __uint_as_float((uint32_t)(best.k[4] >> 32)) : INFINITY;
                 P.near_meta[i] = make_float2(__int_as_float(cnt), d5);
                 store_plane(P, i, nbs, cnt, d5);
+            } else {
+                // hand the cube-1 result to the warp that will finish this point: (distance bits, id, address) per rank,
+                // parked in the point's own slots of P.near until the final neighbours overwrite them
+                uint4* seed = reinterpret_cast<uint4*>(P.near + (size_t)i * 5);
+#pragma unroll
+                for (int r = 0; r < 5; ++r)
+                    seed[r] = (r < cnt) ? make_uint4((uint32_t)(best.k[r] >> 32), (uint32_t)best.k[r], best.a[r], 0u) : make_uint4(INF_BITS, 0xFFFFFFFFu, 0u, 0u);
+                P.near_meta[i] = make_float2(__int_as_float(cnt), INFINITY);
+                __threadfence();   // the seed is visible before the queue entry that announces the point
             }
         }
         // publish the far points: one atomic per warp
@@ -495,6 +507,8 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
         }
     }
 
+    if (stamp_on && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_p1));
+    unsigned nfar_done = 0;
     // ---- phase 2 (the barrier that ended phase 1 makes the shared buffers free) ---------------------------
     uint2* queue = S.p2.queue[warp];
     int nb = 0;
@@ -518,10 +532,27 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
         v = __shfl_sync(FULL, v, 0);
         if ((unsigned)(v >> 32) != tag) break;
         const unsigned i = (unsigned)v;
+        __threadfence();   // the producer's seed stores precede the entry this warp just saw
         float wx, wy, wz;
         world_of(s_state, __ldg(P.body + i), wx, wy, wz);
+        uint4 sd = make_uint4(INF_BITS, 0xFFFFFFFFu, 0u, 0u);
+        if (lane < 5) sd = __ldcg(reinterpret_cast<const uint4*>(P.near + (size_t)i * 5) + lane);
+        const int seed_cnt = __float_as_int(__ldcg(&P.near_meta[i].x));
         Cand out;
-        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, max_sq_bits, lane, out, nc, queue);
+        int dbg = 0;
+        unsigned long long tq0 = 0;
+        if (stamp_on) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tq0));
+        const int cnt = warp_knn5_rings(P.map, wx, wy, wz, max_sq_bits, lane, out, nc, queue, seed_cnt, sd.x, sd.y, sd.z, stamp_on ? &dbg : nullptr);
+        if (stamp_on && lane == 0) {
+            unsigned long long tq1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tq1));
+            unsigned long long* G = P.search_stamps + (size_t)4096 * 4;
+            atomicAdd(G + 0, tq1 - tq0); atomicAdd(G + 1, 1ull); atomicAdd(G + 2, (unsigned long long)(dbg >> 8));
+            atomicAdd(G + 3 + min(dbg & 255, 12), 1ull);
+            atomicAdd(G + 16 + min(seed_cnt, 5), 1ull);
+            atomicMax(G + 22, tq1 - tq0);
+            atomicAdd(G + 23 + min(dbg & 255, 8), tq1 - tq0);   // duration by final radius
+        }
         if (lane < 5) {
             float4 p = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
             if (out.d != INF_BITS) p = __ldg(P.map.buckets + out.addr);
@@ -534,7 +565,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
             P.near_meta[i] = meta;
             s_bid[warp][nb] = i; s_bmeta[warp][nb] = meta;
         }
-        ++nb;
+        ++nb; ++nfar_done;
         if (nb == FAR_BATCH) {
             __syncwarp();
             float4 nbs[5];
@@ -551,6 +582,15 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 6) k_search(FusedParams P) {
 #pragma unroll
         for (int r = 0; r < 5; ++r) nbs[r] = S.p2.near[warp][lane][r];
         store_plane(P, (int)s_bid[warp][lane], nbs, __float_as_int(s_bmeta[warp][lane].x), s_bmeta[warp][lane].y);
+    }
+    if (stamp_on) {
+        __syncthreads();
+        if (lane == 0 && nfar_done) atomicAdd(&P.search_stamps[blockIdx.x * 4 + 3], (unsigned long long)nfar_done);
+        if (threadIdx.x == 0) {
+            unsigned long long t_end;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+            P.search_stamps[blockIdx.x * 4 + 0] = t_start; P.search_stamps[blockIdx.x * 4 + 1] = t_p1; P.search_stamps[blockIdx.x * 4 + 2] = t_end;
+        }
     }
     if (P.stats) {
         const unsigned tot = __reduce_add_sync(FULL, nc);
@@ -612,6 +652,7 @@ void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream) {
     k_search<<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
 }
 // CTAs of k_search that fit on one SM (its grid never needs to exceed the resident set: tiles are dealt dynamically)
+int search_tile_points() { return SEARCH_THREADS; }
 int search_ctas_per_sm() {
     int nb = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_search, SEARCH_THREADS, 0) != cudaSuccess || nb < 1) nb = 4;

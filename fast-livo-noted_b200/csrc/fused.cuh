@@ -82,6 +82,7 @@ struct FusedParams {
     unsigned int* group_cnt;   // [groups] arrival tickets; the folding CTA resets its entry
     Ctl* ctl;
     SearchStats* stats;
+    unsigned long long* search_stamps;   // profile mode only: [grid][4] globaltimer of CTA start / end of phase 1 / end, far queries done
 };
 
 }  // namespace flivo

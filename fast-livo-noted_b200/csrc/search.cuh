@@ -537,8 +537,13 @@ __device__ __forceinline__ void ring_scan_cell(const MapView& m, uint2 ent, int 
     }
 }
 
+// seed (optional): the sorted best candidates already found in cube 1 by thread_knn5_shell — lane r < seed_cnt passes
+// candidate r as (distance bits, id, bucket address); the search then starts at cube 2 (or straight at the cube that
+// covers the seeded fifth distance) instead of scanning the 27 inner cells again.
 static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits, int lane,
-                                            Cand& out, unsigned& ncand, uint2* __restrict__ queue /* [RING_QCAP], this warp's */) {
+                                            Cand& out, unsigned& ncand, uint2* __restrict__ queue /* [RING_QCAP], this warp's */,
+                                            int seed_cnt = -1, uint32_t seed_d = 0, uint32_t seed_id = 0, uint32_t seed_addr = 0,
+                                            int* dbg = nullptr /* steps << 8 | last radius */) {
     Top5 loc;
     loc.init();
     const int g = m.gshift;
@@ -554,7 +559,23 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
     // fifth distance (one more step, guaranteed final); while fewer than five are known: cube 2, then the cube
     // that covers the distance bound.  Each step scans cube(n) minus cube(p).
     int p = -1, n = 1;
+    if (seed_cnt >= 0) {   // cube 1 is done
+        if (lane < seed_cnt) { loc.insert(((unsigned long long)seed_d << 32) | seed_id, seed_addr); lfound = 1; }
+        p = 1;
+        if (seed_cnt == 5) {
+            const uint32_t d5 = __shfl_sync(FULL, seed_d, 4), i5 = __shfl_sync(FULL, seed_id, 4);
+            lworst = ((unsigned long long)d5 << 32) | i5;
+            gworst = fmin(gworst, (double)__uint_as_float(d5));
+            const float need = __uint_as_float(d5);
+            do { ++n; } while (n < RING_MAX_CELLS && covered_sq(m.cell_edge, (float)n, qabs) < need);
+        } else {
+            n = 2;
+        }
+    }
+    int steps = 0;
     while (true) {
+        ++steps;
+        if (dbg) *dbg = (steps << 8) | n;
         const int bx0 = (cqx - n) >> 2, by0 = (cqy - n) >> 2, bz0 = (cqz - n) >> 2;
         const int nbx = ((cqx + n) >> 2) - bx0 + 1, nby = ((cqy + n) >> 2) - by0 + 1, nbz = ((cqz + n) >> 2) - bz0 + 1;
         const int nb = nbx * nby * nbz;

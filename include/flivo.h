@@ -225,6 +225,8 @@ int flivo_get_stats(flivo_ctx* ctx, flivo_stats* out);
 /* Diagnostic only (no reference counterpart): device globaltimer stamps (ns) at the phase boundaries of the solve
  * kernel, [trips_cap][16], of the last flivo_iekf_update that ran with FLIVO_CFG_PROFILE. */
 int flivo_debug_solve_stamps(flivo_ctx* ctx, uint64_t* out, int trips_cap);
+/* Same for the search kernel: per CTA {start, end of the tile phase, end, far queries finished} of the first search trip. */
+int flivo_debug_search_stamps(flivo_ctx* ctx, uint64_t* out, int ctas_cap, int* n_ctas);
 
 #ifdef __cplusplus
 }
