@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument("--sort-scan", type=int, default=1)
     ap.add_argument("--cell-ratio", type=int, default=0, help="search cell edge / downsample size (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-map-add", action="store_true", help="skip the informational map_incremental timing (it grows the map)")
     ap.add_argument("--no-frontend", action="store_true", help="skip the informational front-end (undistort + voxel grid) timing")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5)")
@@ -156,9 +157,15 @@ def cpu_reference_run(world_xyz, scans_host, ds, mode, force_search, steps, warm
             total_s += dt
             results.append(dict(x=r["x"].as_array(), n_eff=r["n_eff"], trips=r["trips"], searches=r["searches"],
                                 timings=[float(v) for v in r["timings"]], scan=it % len(scans_host)))
+    # map_incremental of the last scan (src/laser_mapping.cpp:329-389): world transform with the posterior + Add_Points(true)
+    sc = scans_host[results[-1]["scan"]]
+    wpts = orc.body_to_world(sc["body"], orc.State.from_array(results[-1]["x"]))
+    t0 = time.perf_counter()
+    added = tree.add_points(wpts, True)
+    add_ms = (time.perf_counter() - t0) * 1e3
     tree.close()
     return dict(points_per_s=total_pts / total_s, ms_per_step=1e3 * total_s / steps, kind=kind, cores=threads,
-                build_s=build_s, results=results)
+                build_s=build_s, results=results, add_points_ms=add_ms, add_points_added=int(added))
 
 
 def run_reference(args, rank, world_size):
@@ -379,6 +386,21 @@ def run_flivo(args, rank, world_size, local_rank):
             frontend["cpu_voxel_grid_ms"] = (t2 - t1) * 1e3
             frontend["cpu_kind"] = "port (oracle restatement, 1 thread)"
         del raw, raw4, t_ms
+    # ---- map_incremental (flivo_map_add_scan: world transform with the posterior + Add_Points with down-sampling),
+    # informational, BASELINE config 2 style: each scan is inserted once, after its update ----
+    map_add = None
+    if rank == 0 and world_size == 1 and not args.no_map_add:
+        ms, added = [], []
+        for i in range(S):
+            F.scan_set_device(dev_scans[i].data_ptr(), dev_scans[i].shape[0])
+            xi, _, _ = F.iekf_update(pkg.State.from_array(scans[i]["x_prior"]), P0, cfg)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            added.append(F.map_add_scan(xi))
+            F.sync()
+            ms.append((time.perf_counter() - t0) * 1e3)
+        map_add = {"ms_per_scan_median": float(np.median(ms)), "ms_per_scan": [float(v) for v in ms], "points_added": [int(a) for a in added],
+                   "scan_points": int(pts_per_scan), "note": "wall clock around flivo_map_add_scan + sync; the map grows by the added points"}
     # sharded mode: the posterior of the sharded update must be the single-GPU posterior of the whole scan
     shard_check = None
     if shard:
@@ -402,7 +424,7 @@ def run_flivo(args, rank, world_size, local_rank):
     return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
-                trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend,
+                trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add,
                 search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
@@ -464,7 +486,8 @@ def main():
         c = cpu_reference_run(r["wxyz_host"], scans_host, ds, args.mode, args.force_search, args.cpu_steps, 1, threads)
         cpu = {"value": c["points_per_s"], "unit": "points/s", "cores": threads, "kind": c["kind"],
                "sample": "%d full %d-pt scans x full %d-pt ikd-Tree (tree build %.1f s untimed), all trips" % (args.cpu_steps, n_scan, n_map, c["build_s"]),
-               "ms_per_scan": c["ms_per_step"], "stage_s_last": c["results"][-1]["timings"]}
+               "ms_per_scan": c["ms_per_step"], "stage_s_last": c["results"][-1]["timings"],
+               "add_points_ms": c["add_points_ms"], "add_points_added": c["add_points_added"]}
         # parity side-check on the bench workload itself: GPU posterior of scan j vs the reference CPU path's
         j, xg, Pg, rep = r["last"]
         cands = [q for q in c["results"] if q["scan"] == j]
@@ -492,7 +515,7 @@ def main():
                                      "map replica + own scans per rank, no collective")},
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
-            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "frontend": r["frontend"],
+            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "frontend": r["frontend"], "map_add": r["map_add"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
         }
         print(json.dumps(line), file=out, flush=True)
