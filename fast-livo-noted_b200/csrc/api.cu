@@ -583,7 +583,7 @@ static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool externa
         float inv_edge = 1.0f / ctx->map.view().cell_edge;
         k_scan_keys<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, n, inv_edge, ctx->d_skey_a, ctx->d_sidx_a);
         size_t tmp = ctx->cub_bytes;
-        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, 0, 30, ctx->stream));   // 10 bits per axis: locality only
+        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, 6, 30, ctx->stream));   // 10 bits per axis, the lowest 2 per axis left unsorted: locality only
         k_gather4<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, ctx->d_perm, n, ctx->d_body);
         CKC(cudaGetLastError());
     }
