@@ -63,9 +63,12 @@ class State(C.Structure):
         return State.from_array(self.as_array())
 
 
+IVOX_OFF, IVOX_CENTER, IVOX_NEARBY6, IVOX_NEARBY18, IVOX_NEARBY26 = 0, 1, 7, 19, 27
+
+
 class Options(C.Structure):
     _fields_ = [("downsample_size", C.c_float), ("cell_ratio", C.c_int32), ("initial_points", C.c_uint64),
-                ("sort_scan", C.c_int32), ("reserved", C.c_int32)]
+                ("sort_scan", C.c_int32), ("ivox_nearby", C.c_int32)]
 
 
 class Cfg(C.Structure):
@@ -191,9 +194,11 @@ def make_cfg(mode=MODE_V3, max_iter=4, laser_point_cov=0.001, limit=None, force_
 class Flivo:
     """One flivo_ctx (one device + one stream).  Method names follow the C ABI / the reference members."""
 
-    def __init__(self, device=0, downsample_size=0.2, cell_ratio=2, initial_points=0, sort_scan=False):
+    def __init__(self, device=0, downsample_size=0.2, cell_ratio=2, initial_points=0, sort_scan=False, ivox_nearby=0):
+        """ivox_nearby = 0: ikd-Tree semantics.  1 / 7 / 19 / 27 (IVOX_*): the map behaves as the reference's
+        faster_lio::IVox (include/ivox3d/ivox3d.h) with downsample_size as its voxel resolution."""
         self._L = lib()
-        opt = Options(downsample_size, cell_ratio, initial_points, int(sort_scan), 0)
+        opt = Options(downsample_size, cell_ratio, initial_points, int(sort_scan), int(ivox_nearby))
         h = C.c_void_p()
         rc = self._L.flivo_ctx_create(device, C.byref(opt), C.byref(h))
         if rc != OK:
@@ -282,6 +287,14 @@ class Flivo:
         if n.value:
             self._ck(self._L.flivo_map_acquire_removed(self.h, _ptr(xyz), n.value, C.byref(n)))
         return xyz
+
+    def AddPoints(self, xyz):
+        """IVox::AddPoints (include/ivox3d/ivox3d.h:247-276): every point is kept."""
+        return self.Add_Points(xyz, downsample_on=False)
+
+    def GetClosestPoint(self, queries, max_num=K, max_range=5.0):
+        """Batched IVox::GetClosestPoint (include/ivox3d/ivox3d.h:132-204) -> (ids, sqd, xyz, count)."""
+        return self.Nearest_Search(queries, max_num, float(max_range) * float(max_range))
 
     def Nearest_Search(self, queries, k=K, max_dist=np.inf):
         """Batched KD_TREE::Nearest_Search -> (ids, sqd, xyz, count)."""

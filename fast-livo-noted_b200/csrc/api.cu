@@ -132,6 +132,11 @@ struct flivo_ctx {
     int graph_search_grid = 0, graph_fused_grid = 0, graph_trips = 0, graph_churn = 0;
     cudaEvent_t ev[2 * MAX_TRIPS + 2] = {};
     flivo_stats stats{};
+    // iVox mode (flivo_options::ivox_nearby != 0)
+    double ivox_filter = 0.0;                 // filter_size_map_min of map_incremental's add rule
+    unsigned char* d_ivox_flags = nullptr;    // [2][cap] add / no-need-downsample flags in the caller's order
+    float4* d_ivox_sel = nullptr;             // [2][cap] the two selected point lists
+    size_t ivox_cap = 0;
     // multi-GPU
     ncclComm_t comm = nullptr;
     int rank = 0, nranks = 1;
@@ -265,7 +270,7 @@ __global__ void k_scatter(const T* __restrict__ in, const unsigned int* __restri
 }
 // neighbour ids / squared distances from the cached Nearest_Points (x,y,z,id) and the query
 __global__ void k_near_unpack(const float4* __restrict__ near, const float4* __restrict__ world, const unsigned int* __restrict__ perm,
-                              size_t n, int* out_id, float* out_sqd) {
+                              size_t n, int* out_id, float* out_sqd, int ivox) {
     size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (t >= n * 5) return;
     size_t i = t / 5;
@@ -276,7 +281,7 @@ __global__ void k_near_unpack(const float4* __restrict__ near, const float4* __r
     if (out_id) out_id[o * 5 + r] = id;
     if (out_sqd) {
         float4 q = world[i];
-        out_sqd[o * 5 + r] = id >= 0 ? sqdist3(q.x, q.y, q.z, p.x, p.y, p.z) : INFINITY;
+        out_sqd[o * 5 + r] = id >= 0 ? (ivox ? sqdist3_eigen(p.x, p.y, p.z, q.x, q.y, q.z) : sqdist3(q.x, q.y, q.z, p.x, p.y, p.z)) : INFINITY;
     }
 }
 static inline unsigned nblk(size_t n, int t) { return (unsigned)((n + t - 1) / t); }
@@ -308,7 +313,8 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     if (!(o.downsample_size > 0.f)) o.downsample_size = 0.2f;
     if (o.cell_ratio == 0) o.cell_ratio = 2;
     ctx->opt = o;
-    int rc = ctx->map.init(ctx->stream, o.downsample_size, o.cell_ratio, (size_t)o.initial_points, ctx->err);
+    if (o.ivox_nearby) { o.cell_ratio = 1; ctx->ivox_filter = (double)o.downsample_size; ctx->opt = o; }
+    int rc = ctx->map.init(ctx->stream, o.downsample_size, o.cell_ratio, (size_t)o.initial_points, o.ivox_nearby, ctx->err);
     if (rc) return map_rc(ctx, rc);
     upload_term_table();
     CKC(cudaGetLastError());
@@ -374,6 +380,7 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     cudaFree(ctx->d_vg_state); cudaFree(ctx->d_poses);
     if (ctx->peer_on) for (int r = 0; r < ctx->nranks; ++r) if (r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
     cudaFree(ctx->d_xchg); cudaFree(ctx->d_xseq);
+    cudaFree(ctx->d_ivox_flags); cudaFree(ctx->d_ivox_sel);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
     cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_stamps); cudaFree(ctx->d_sstamps); cudaFree(ctx->d_pre);
     for (int i = 0; i <= MAX_TRIPS; ++i) { if (ctx->ev_fork[i]) cudaEventDestroy(ctx->ev_fork[i]); if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]); }
@@ -396,6 +403,11 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
 
 extern "C" int flivo_map_set_downsample(flivo_ctx* ctx, float downsample_size) {
     ENTER();
+    if (ctx->opt.ivox_nearby) {
+        NEED(downsample_size > 0.f, FLIVO_E_ARG, "filter_size_map_min must be > 0");
+        ctx->ivox_filter = (double)downsample_size;
+        return FLIVO_OK;
+    }
     return map_rc(ctx, ctx->map.set_downsample(downsample_size, ctx->err));
 }
 
@@ -529,7 +541,8 @@ extern "C" int flivo_knn(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t s
     int* d_cnt = d_id + nq * k;
     CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
     int grid = (int)std::min<size_t>((nq + 3) / 4, (size_t)ctx->sm_count * 16);
-    launch_knn(ctx->map.view(), ctx->d_stage, (int)nq, k, bits, d_xyz, d_sqd, d_id, d_cnt, ctx->d_stats, grid, ctx->stream);
+    if (ctx->opt.ivox_nearby) launch_knn_ivox(ctx->map.view(), ctx->d_stage, (int)nq, k, max_dist, d_xyz, d_sqd, d_id, d_cnt, ctx->d_stats, ctx->stream);
+    else launch_knn(ctx->map.view(), ctx->d_stage, (int)nq, k, bits, d_xyz, d_sqd, d_id, d_cnt, ctx->d_stats, grid, ctx->stream);
     CKC(cudaGetLastError());
     if (out_xyz) CKC(cudaMemcpyAsync(out_xyz, d_xyz, nq * k * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     if (out_sqd) CKC(cudaMemcpyAsync(out_sqd, d_sqd, nq * k * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
@@ -594,6 +607,11 @@ static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool externa
     CKC(cudaMemsetAsync(ctx->d_sel, 1, n, ctx->stream));
     CKC(cudaMemsetAsync(ctx->d_eff, 0, n, ctx->stream));
     CKC(cudaMemsetAsync(ctx->d_pflags, 0, n, ctx->stream));   // no cached neighbours yet: a re-use trip before any search selects nothing
+    // iVox mode reads the cached count outside the search (empty-result rule of GetClosestPoint, map_incremental's add rule)
+    if (ctx->opt.ivox_nearby) {
+        CKC(cudaMemsetAsync(ctx->d_near_meta, 0, n * sizeof(float2), ctx->stream));
+        CKC(cudaMemsetAsync(ctx->d_near, 0xFF, n * 5 * sizeof(float4), ctx->stream));   // id -1 everywhere: a point that never finds a candidate reports an empty list
+    }
     return FLIVO_OK;
 }
 
@@ -736,7 +754,7 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
         }
         int* d_id = (int*)ctx->d_out;
         float* d_sq = (float*)(d_id + n * 5);
-        k_near_unpack<<<nblk(n * 5, 256), 256, 0, ctx->stream>>>(ctx->d_near, ctx->d_world, ctx->scan_sorted ? ctx->d_perm : nullptr, n, d_id, d_sq);
+        k_near_unpack<<<nblk(n * 5, 256), 256, 0, ctx->stream>>>(ctx->d_near, ctx->d_world, ctx->scan_sorted ? ctx->d_perm : nullptr, n, d_id, d_sq, ctx->opt.ivox_nearby);
         CKC(cudaGetLastError());
         if (nbr_id) CKC(cudaMemcpyAsync(nbr_id, d_id, n * 5 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         if (nbr_sqd) CKC(cudaMemcpyAsync(nbr_sqd, d_sq, n * 5 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
@@ -902,6 +920,49 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     return FLIVO_OK;
 }
 
+// iVox branch of map_incremental (src/laser_mapping.cpp:340-387); the state is already in d_x
+static int ivox_add_scan(flivo_ctx* ctx, int32_t* n_added) {
+    const size_t n = ctx->scan_n;
+    if (n > ctx->ivox_cap) {
+        cudaFree(ctx->d_ivox_flags); cudaFree(ctx->d_ivox_sel);
+        ctx->d_ivox_flags = nullptr; ctx->d_ivox_sel = nullptr; ctx->ivox_cap = 0;
+        const size_t cap = n + n / 8;
+        CKC(cudaMalloc(&ctx->d_ivox_flags, 2 * cap));
+        CKC(cudaMalloc(&ctx->d_ivox_sel, (2 * cap + 4) * sizeof(float4)));
+        ctx->ivox_cap = cap;
+    }
+    const size_t cap = ctx->ivox_cap;
+    unsigned char *f_add = ctx->d_ivox_flags, *f_non = ctx->d_ivox_flags + cap;
+    float4 *sel_add = ctx->d_ivox_sel, *sel_non = ctx->d_ivox_sel + cap;
+    int* d_counts = reinterpret_cast<int*>(ctx->d_ivox_sel + 2 * cap);
+    launch_ivox_map_filter(ctx->d_body, (int)n, ctx->d_x, ctx->d_near, ctx->d_near_meta, ctx->scan_sorted ? ctx->d_perm : nullptr,
+                           ctx->ivox_filter, ctx->d_world, f_add, f_non, ctx->stream);
+    CKC(cudaGetLastError());
+    size_t tmp = ctx->cub_bytes;
+    size_t need = 0;
+    CKC(cub::DeviceSelect::Flagged(nullptr, need, ctx->d_world, f_add, sel_add, d_counts, (int)n, ctx->stream));
+    if (need > tmp) {
+        cudaFree(ctx->d_cub); ctx->d_cub = nullptr; ctx->cub_bytes = 0;
+        CKC(cudaMalloc(&ctx->d_cub, need + 256));
+        ctx->cub_bytes = need + 256;
+    }
+    tmp = ctx->cub_bytes;
+    CKC(cub::DeviceSelect::Flagged(ctx->d_cub, tmp, ctx->d_world, f_add, sel_add, d_counts, (int)n, ctx->stream));
+    tmp = ctx->cub_bytes;
+    CKC(cub::DeviceSelect::Flagged(ctx->d_cub, tmp, ctx->d_world, f_non, sel_non, d_counts + 1, (int)n, ctx->stream));
+    int h[2] = {0, 0};
+    CKC(cudaMemcpyAsync(h, d_counts, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    // ivox_->AddPoints(points_to_add); ivox_->AddPoints(point_no_need_downsample); (:386-387) — one concatenated batch
+    // stores the same points with the same insertion ids
+    if (h[1] > 0) CKC(cudaMemcpyAsync(sel_add + h[0], sel_non, (size_t)h[1] * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
+    const size_t total = (size_t)h[0] + (size_t)h[1];
+    int added = 0;
+    int rc = total ? ctx->map.add_points(sel_add, total, false, &added, ctx->err) : 0;
+    if (n_added) *n_added = (int32_t)total;
+    return map_rc(ctx, rc);
+}
+
 extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t* n_added) {
     ENTER();
     if (n_added) *n_added = 0;
@@ -909,6 +970,7 @@ extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
     memcpy(ctx->h_blk->x, st, sizeof(flivo_state));
     CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_blk->x, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->opt.ivox_nearby) return ivox_add_scan(ctx, n_added);
     // Add_Points is order dependent only through ties; keep the caller's order (batch index = insertion id order)
     const float4* src = ctx->scan_sorted ? ctx->d_body_in : ctx->d_body;
     if (ctx->scan_sorted && ctx->scan_external) {

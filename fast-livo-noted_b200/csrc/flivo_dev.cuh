@@ -42,6 +42,10 @@ struct MapView {
     float ds;                      // downsample_size
     int gshift;                    // log2(cell_ratio)
     float cell_edge;               // ds * 2^gshift (exact)
+    // iVox-compatible mode (include/ivox3d/ivox3d.h): ds = Options::resolution_, cell = voxel
+    // (gshift 0), voxel key = round(p * inv_resolution_) (Pos2Grid, ivox3d.h:278-281), every point of a voxel kept
+    int ivox;                      // 0 = ikd-Tree semantics; else the number of voxels of the nearby stencil (1, 7, 19, 27)
+    float inv_res;                 // (float)(1.0 / resolution_) (ivox3d.h:63)
 };
 
 // Device-side counters of the map (one struct in global memory).
@@ -81,8 +85,22 @@ __device__ __forceinline__ float sqdist3(float ax, float ay, float az, float bx,
     return fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz));
 }
 
+// distance2 of the iVox node (ivox3d_node.hpp:13-16): (pt1 - pt2).squaredNorm() on Vector3f; Eigen's unrolled
+// reduction of a 3-vector adds x*x + (y*y + z*z) (Eigen is not in the reference tree: order unpinned, the oracle
+// restates the same)
+__device__ __forceinline__ float sqdist3_eigen(float ax, float ay, float az, float bx, float by, float bz) {
+    float dx = fsub(ax, bx), dy = fsub(ay, by), dz = fsub(az, bz);
+    return fadd(fmul(dx, dx), fadd(fmul(dy, dy), fmul(dz, dz)));
+}
+
 // voxel key: floor(p / downsample_size) as in Box_of_Point.vertex_min (ikd_Tree.cpp:392-396)
 __device__ __forceinline__ int voxel_key1(float x, float ds) { return (int)floorf(fdiv(x, ds)); }
+
+// key of the voxel that stores p: Box_of_Point (ikd_Tree.cpp:392-396) or, in iVox mode, IVox::Pos2Grid
+// (ivox3d.h:278-281): (pt * inv_resolution_).array().round().cast<int>() — std::round, half away from zero
+__device__ __forceinline__ int voxel_key(const MapView& m, float x) {
+    return m.ivox ? (int)roundf(fmul(x, m.inv_res)) : (int)floorf(fdiv(x, m.ds));
+}
 
 __device__ __forceinline__ bool key_in_range(int k) { return k > -COORD_BIAS + 8 && k < COORD_BIAS - 8; }
 

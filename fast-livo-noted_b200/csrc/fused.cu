@@ -387,13 +387,15 @@ __device__ __forceinline__ void store_plane(const FusedParams& P, int i, const f
     float pabcd[4] = {0.f, 0.f, 0.f, 0.f};
     if (cnt >= 5) {
         pf |= PF_HAVE5;
-        if (!(d5 > 5.f)) pf |= PF_GATE;
+        // the iVox branch has no far-neighbour gate: GetClosestPoint bounds the range itself (src/laser_mapping.cpp:516-521)
+        if (P.map.ivox || !(d5 > 5.f)) pf |= PF_GATE;
         if (esti_plane_dev(nbs, 0.1f, pabcd)) pf |= PF_PLANE;
     }
     P.plane[i] = make_float4(pabcd[0], pabcd[1], pabcd[2], pabcd[3]);
     P.pflags[i] = (unsigned char)pf;
 }
 
+constexpr double IVOX_MAX_RANGE_SQ = 25.0;   // max_range = 5.0 default of GetClosestPoint (ivox3d.h:79), squared in double (ivox3d_node.hpp:162)
 constexpr int SEARCH_THREADS = 128;
 constexpr int SEARCH_WARPS = SEARCH_THREADS / 32;
 constexpr int FAR_BATCH = 32;   // far points a warp finishes before its lanes fit their planes (one lane per point)
@@ -470,8 +472,17 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search
             world_of(s_state, __ldg(P.body + i), wx, wy, wz);
             Top5 best;
             int cnt = 0;
-            fin = thread_knn5_shell(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, S.p1.idx + threadIdx.x, S.p1.gap + threadIdx.x, SEARCH_THREADS);
-            if (fin) {
+            bool keep_old = false;
+            if (P.map.ivox) {
+                thread_knn5_ivox(P.map, wx, wy, wz, IVOX_MAX_RANGE_SQ, best, cnt, nc);
+                // no candidate at all: GetClosestPoint returns before touching closest_pt (ivox3d.h:168-170), so the
+                // point keeps the neighbours of the previous search of this scan
+                keep_old = cnt == 0;
+            } else {
+                fin = thread_knn5_shell(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, S.p1.idx + threadIdx.x, S.p1.gap + threadIdx.x, SEARCH_THREADS);
+            }
+            if (keep_old) {
+            } else if (fin) {
                 float4 nbs[5];
 #pragma unroll
                 for (int r = 0; r < 5; ++r) {
@@ -630,6 +641,32 @@ __global__ void __launch_bounds__(128) k_knn(MapView map, const float4* __restri
     }
 }
 
+// iVox mode: thread per query, IVox::GetClosestPoint semantics; max_range_sq = max_range * max_range (strict <)
+__global__ void __launch_bounds__(128) k_knn_ivox(MapView map, const float4* __restrict__ q, int nq, int k, double max_range_sq,
+                                                  float* out_xyz, float* out_sqd, int* out_id, int* out_count, SearchStats* stats) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned nc = 0;
+    if (i < nq) {
+        const float4 p = __ldg(q + i);
+        Top5 best;
+        int cnt = 0;
+        thread_knn5_ivox(map, p.x, p.y, p.z, max_range_sq, best, cnt, nc);
+        const int found = min(cnt, k);
+        for (int r = 0; r < k; ++r) {
+            const bool ok = r < found;
+            float4 np = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+            if (ok) np = __ldg(map.buckets + best.a[r]);
+            const size_t o = (size_t)i * k + r;
+            if (out_xyz) { out_xyz[o * 3 + 0] = np.x; out_xyz[o * 3 + 1] = np.y; out_xyz[o * 3 + 2] = np.z; }
+            if (out_sqd) out_sqd[o] = ok ? __uint_as_float((uint32_t)(best.k[r] >> 32)) : INFINITY;
+            if (out_id) out_id[o] = ok ? (int)(uint32_t)best.k[r] : -1;
+        }
+        if (out_count) out_count[i] = found;
+    }
+    const unsigned tot = __reduce_add_sync(FULL, nc);
+    if (stats && (threadIdx.x & 31) == 0 && tot) atomicAdd(&stats->candidates, (unsigned long long)tot);
+}
+
 // world transform only (map_incremental, src/laser_mapping.cpp:343-346): body -> world float4 (w = 0)
 __global__ void k_transform(const float4* __restrict__ body, int n, const double* __restrict__ state, float4* __restrict__ world) {
     __shared__ double s[36];
@@ -642,6 +679,49 @@ __global__ void k_transform(const float4* __restrict__ body, int n, const double
     double l0 = dot3d(s + 12, pd0, pd1, pd2) + s[21], l1 = dot3d(s + 15, pd0, pd1, pd2) + s[22], l2 = dot3d(s + 18, pd0, pd1, pd2) + s[23];
     world[i] = make_float4((float)(dot3d(s + 0, l0, l1, l2) + s[9]), (float)(dot3d(s + 3, l0, l1, l2) + s[10]),
                            (float)(dot3d(s + 6, l0, l1, l2) + s[11]), 0.f);
+}
+
+// map_incremental of the iVox branch (src/laser_mapping.cpp:329-389): world transform with the final state, then per
+// point the decision "add / add without down-sampling / drop" from its cached Nearest_Points and the centre of its
+// filter_size_map_min voxel.  Thread per point in processing order; results land at the caller's index (perm).
+//   flag 1 = points_to_add, 2 = point_no_need_downsample, 0 = dropped
+// Eigen float vector arithmetic restated: (pw / fs).floor() + 0.5) * fs in float; calc_dist(Vector3f, Vector3f) =
+// (p1 - p2).norm() (include/common_lib.h:85).
+__global__ void k_ivox_map_filter(const float4* __restrict__ body, int n, const double* __restrict__ state,
+                                  const float4* __restrict__ near, const float2* __restrict__ near_meta,
+                                  const unsigned int* __restrict__ perm, double fs, float4* __restrict__ world_out,
+                                  unsigned char* __restrict__ flag_add, unsigned char* __restrict__ flag_noneed) {
+    __shared__ double s[24];
+    if (threadIdx.x < 24) s[threadIdx.x] = state[threadIdx.x];
+    __syncthreads();
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    float wx, wy, wz;
+    world_of(s, __ldg(body + j), wx, wy, wz);
+    const unsigned o = perm ? perm[j] : (unsigned)j;
+    const int cnt = __float_as_int(near_meta[j].x);
+    int flag = 1;
+    if (cnt > 0) {                                           // !Nearest_Points[i].empty() (:349)
+        const float fsf = (float)fs;
+        const float cx = fmul(fadd(floorf(fdiv(wx, fsf)), 0.5f), fsf), cy = fmul(fadd(floorf(fdiv(wy, fsf)), 0.5f), fsf),
+                    cz = fmul(fadd(floorf(fdiv(wz, fsf)), 0.5f), fsf);
+        const float4 n0 = near[(size_t)j * 5];
+        const double half = 0.5 * fs;
+        if ((double)fabsf(fsub(n0.x, cx)) > half && (double)fabsf(fsub(n0.y, cy)) > half && (double)fabsf(fsub(n0.z, cz)) > half) {
+            flag = 2;                                        // nearest neighbour far from the voxel centre (:358-363)
+        } else {
+            const float dist = fsqrt(sqdist3_eigen(wx, wy, wz, cx, cy, cz));
+            if (cnt >= 5) {
+                for (int r = 0; r < 5; ++r) {
+                    const float4 q = near[(size_t)j * 5 + r];
+                    if ((double)fsqrt(sqdist3_eigen(q.x, q.y, q.z, cx, cy, cz)) < (double)dist + 1e-6) { flag = 0; break; }
+                }
+            }
+        }
+    }
+    world_out[o] = make_float4(wx, wy, wz, 0.f);
+    flag_add[o] = flag == 1;
+    flag_noneed[o] = flag == 2;
 }
 
 // ---- host launchers ---------------------------------------------------------------------------------
@@ -661,6 +741,15 @@ int search_ctas_per_sm() {
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
                 int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream) {
     k_knn<<<grid, 128, 0, stream>>>(map, q, nq, k, max_sq_bits, out_xyz, out_sqd, out_id, out_count, stats);
+}
+void launch_knn_ivox(const MapView& map, const float4* q, int nq, int k, double max_range_sq, float* out_xyz, float* out_sqd,
+                     int* out_id, int* out_count, SearchStats* stats, cudaStream_t stream) {
+    k_knn_ivox<<<(nq + 127) / 128, 128, 0, stream>>>(map, q, nq, k, max_range_sq, out_xyz, out_sqd, out_id, out_count, stats);
+}
+void launch_ivox_map_filter(const float4* body, int n, const double* state, const float4* near, const float2* near_meta,
+                            const unsigned int* perm, double fs, float4* world_out, unsigned char* flag_add,
+                            unsigned char* flag_noneed, cudaStream_t stream) {
+    k_ivox_map_filter<<<(n + 255) / 256, 256, 0, stream>>>(body, n, state, near, near_meta, perm, fs, world_out, flag_add, flag_noneed);
 }
 void launch_transform(const float4* body, int n, const double* state, float4* world, cudaStream_t stream) {
     k_transform<<<(n + 255) / 256, 256, 0, stream>>>(body, n, state, world);

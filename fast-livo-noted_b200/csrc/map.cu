@@ -56,7 +56,7 @@ __device__ __forceinline__ void decode_sort_key(unsigned long long key, int gshi
 __device__ __forceinline__ bool cell_in_range(int c) { return c > -(1 << 18) + 8 && c < (1 << 18) - 8; }
 constexpr unsigned long long INVALID_KEY = 0x7FFFFFFFFFFFFFFFull;  // sorts last; skipped by every stage
 __device__ __forceinline__ bool point_ok(const MapView& m, float4 p, int& kx, int& ky, int& kz) {
-    kx = voxel_key1(p.x, m.ds); ky = voxel_key1(p.y, m.ds); kz = voxel_key1(p.z, m.ds);
+    kx = voxel_key(m, p.x); ky = voxel_key(m, p.y); kz = voxel_key(m, p.z);
     return isfinite(p.x) && isfinite(p.y) && isfinite(p.z) && fabsf(p.x / m.ds) < 1.0e6f && fabsf(p.y / m.ds) < 1.0e6f &&
            fabsf(p.z / m.ds) < 1.0e6f && cell_in_range(kx >> m.gshift) && cell_in_range(ky >> m.gshift) && cell_in_range(kz >> m.gshift);
 }
@@ -702,9 +702,16 @@ int MapStore::alloc_tables(size_t dir_cap, size_t bucket_cap, std::string& err) 
     return 0;
 }
 
-int MapStore::init(cudaStream_t stream, float ds, int cell_ratio, size_t initial_points, std::string& err) {
+int MapStore::init(cudaStream_t stream, float ds, int cell_ratio, size_t initial_points, int ivox_nearby, std::string& err) {
     stream_ = stream;
     if (!(ds > 0.f)) { err = "downsample_size must be > 0"; return -2; }
+    if (ivox_nearby != 0) {
+        // iVox mode: ds is IVox::Options::resolution_, one cell per voxel, Pos2Grid keys (flivo_dev.cuh)
+        if (ivox_nearby != 1 && ivox_nearby != 7 && ivox_nearby != 19 && ivox_nearby != 27) { err = "ivox_nearby must be 0, 1, 7, 19 or 27"; return -2; }
+        cell_ratio = 1;
+        v_.ivox = ivox_nearby;
+        v_.inv_res = (float)(1.0 / (double)ds);
+    }
     if (cell_ratio != 1 && cell_ratio != 2 && cell_ratio != 4) { err = "cell_ratio must be 1, 2 or 4"; return -2; }
     cell_ratio_ = cell_ratio;
     v_.ds = ds;
@@ -905,6 +912,7 @@ int MapStore::add_points(const float4* d_pts, size_t n, bool downsample_on, int*
     if (n_added) *n_added = 0;
     if (n == 0) return 0;
     if ((size_t)next_id_ + n > 0x7FFFFFF0ull) { err = "insertion ids exhausted (2^31)"; return -3; }
+    if (v_.ivox && downsample_on) { err = "iVox mode: AddPoints keeps every point (no voxel down-sampling)"; return -2; }
     if (stamp_ids(d_pts, n, next_id_, err)) return -1;
     next_id_ += (int)n;
     return insert_batch(scratch_pts_, n, downsample_on, n_added, err);
@@ -929,6 +937,7 @@ int MapStore::delete_boxes(const float* h_boxes6, size_t nb, int* n_deleted, std
 int MapStore::delete_points(const float4* d_pts, size_t n, int* n_deleted, std::string& err) {
     if (n_deleted) *n_deleted = 0;
     if (n == 0) return 0;
+    if (v_.ivox) { err = "iVox mode: Delete_Points is an ikd-Tree operation"; return -2; }
     k_delete_points<<<1, 32, 0, stream_>>>(d_pts, n, v_, d_cnt_, d_removed_, (unsigned)removed_cap_);
     CK(cudaGetLastError());
     int rc = refresh_counters(err);
@@ -1021,6 +1030,7 @@ int MapStore::acquire_removed(float* h_xyz, size_t cap, size_t* n, std::string& 
 
 int MapStore::set_downsample(float ds, std::string& err) {
     if (!(ds > 0.f)) { err = "downsample_size must be > 0"; return -2; }
+    if (v_.ivox) { err = "iVox mode: the voxel resolution is fixed at context creation"; return -2; }
     if (ds == v_.ds) return 0;
     if (refresh_counters(err)) return -1;
     size_t live = (size_t)h_cnt_.live;

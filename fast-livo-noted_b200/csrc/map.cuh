@@ -19,7 +19,7 @@ public:
     MapStore() = default;
     ~MapStore();
     // all calls return cudaError_t-like int (0 ok) and leave a message in err on failure
-    int init(cudaStream_t stream, float ds, int cell_ratio, size_t initial_points, std::string& err);
+    int init(cudaStream_t stream, float ds, int cell_ratio, size_t initial_points, int ivox_nearby, std::string& err);
     void release();
 
     int set_downsample(float ds, std::string& err);

@@ -660,4 +660,57 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, f
     return warp_knn5(m, qx, qy, qz, max_sq_bits, lane, out, nullptr);
 }
 
+// ----------------------------------------------------------------------------------------------------
+// iVox-compatible search: IVox::GetClosestPoint(pt, closest_pt, max_num = 5, max_range = 5.0)
+// (include/ivox3d/ivox3d.h:132-204) over IVoxNode::KNNPointByCondition (include/ivox3d/ivox3d_node.hpp:141-206).
+// Candidates = the points of the voxels key + delta, delta running over nearby_grids_ (ivox3d.h:213-243): CENTER,
+// NEARBY6, NEARBY18 and NEARBY26 are the offsets with at most 0, 1, 2 and 3 non-zero components (1, 7, 19, 27
+// voxels; the visiting order does not matter for the result), whose float squared distance is < max_range^2 compared in double.  The reference truncates every voxel to its K
+// nearest (nth_element) and then takes the K nearest of the union: the same SET as the K nearest of all
+// candidates.  Its output order is whatever two std::nth_element calls leave (only [0] is the minimum); here the
+// list is ascending under the canonical (distance, insertion id) order — stated in DESIGN.md.
+// Thread per query; consecutive deltas mostly fall into the same 4x4x4 block, whose directory slot is reused.
+// ----------------------------------------------------------------------------------------------------
+static __device__ __constant__ signed char c_ivox_delta[27][3] = {   // sorted by the number of non-zero components
+    {0, 0, 0}, {-1, 0, 0}, {0, -1, 0}, {0, 0, -1}, {0, 0, 1}, {0, 1, 0}, {1, 0, 0},
+    {-1, -1, 0}, {-1, 0, -1}, {-1, 0, 1}, {-1, 1, 0}, {0, -1, -1}, {0, -1, 1}, {0, 1, -1},
+    {0, 1, 1}, {1, -1, 0}, {1, 0, -1}, {1, 0, 1}, {1, 1, 0}, {-1, -1, -1}, {-1, -1, 1},
+    {-1, 1, -1}, {-1, 1, 1}, {1, -1, -1}, {1, -1, 1}, {1, 1, -1}, {1, 1, 1}};
+
+__device__ __forceinline__ void thread_knn5_ivox(const MapView& m, float qx, float qy, float qz, double max_range_sq,
+                                                 Top5& best, int& count, unsigned& ncand) {
+    best.init();
+    const int kx = voxel_key(m, qx), ky = voxel_key(m, qy), kz = voxel_key(m, qz);
+    unsigned long long last_key = DIR_EMPTY, worst = 0xFFFFFFFFFFFFFFFFull;
+    int last_slot = -1, found = 0;
+    for (int t = 0; t < m.ivox; ++t) {
+        const int cx = kx + c_ivox_delta[t][0], cy = ky + c_ivox_delta[t][1], cz = kz + c_ivox_delta[t][2];
+        const unsigned long long bk = pack_block(cx >> 2, cy >> 2, cz >> 2);
+        if (bk != last_key) { last_key = bk; last_slot = dir_find(m, bk); }
+        if (last_slot < 0) continue;
+        uint32_t b = __ldg(m.cell_tab + (size_t)last_slot * 64 + cell_off(cx, cy, cz));
+        while (b != NONE32) {
+            float4 p[BUCKET_SLOTS];
+#pragma unroll
+            for (int s = 0; s < BUCKET_SLOTS; ++s) p[s] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
+            const uint32_t nxt = __ldg(m.bucket_next + b);
+#pragma unroll
+            for (int s = 0; s < BUCKET_SLOTS; ++s) {
+                const int pid = __float_as_int(p[s].w);
+                if (pid < 0) continue;
+                ++ncand;
+                const float d = sqdist3_eigen(p[s].x, p[s].y, p[s].z, qx, qy, qz);
+                if (!((double)d < max_range_sq)) continue;
+                const unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | (uint32_t)pid;
+                if (key <= worst) {
+                    best.insert(key, b * BUCKET_SLOTS + s);
+                    if (++found >= 5) worst = best.k[4];
+                }
+            }
+            b = nxt;
+        }
+    }
+    count = min(found, 5);
+}
+
 }  // namespace flivo

@@ -58,6 +58,11 @@ int search_tile_points();
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
                 int* out_id, int* out_count, SearchStats* stats, int grid, cudaStream_t stream);
 void launch_transform(const float4* body, int n, const double* state, float4* world, cudaStream_t stream);
+void launch_knn_ivox(const MapView& map, const float4* q, int nq, int k, double max_range_sq, float* out_xyz, float* out_sqd,
+                     int* out_id, int* out_count, SearchStats* stats, cudaStream_t stream);
+void launch_ivox_map_filter(const float4* body, int n, const double* state, const float4* near, const float2* near_meta,
+                            const unsigned int* perm, double fs, float4* world_out, unsigned char* flag_add,
+                            unsigned char* flag_noneed, cudaStream_t stream);
 void launch_solve_pre(const SolveParams& S, cudaStream_t stream);   // before launch_solve of the same trip (FULL / FROM_RANKS)
 void launch_solve(const SolveParams& S, cudaStream_t stream);
 void launch_ctl_reset(const double* x, double* x_prop, const double* P_prop, double* P_out, Ctl* ctl, SearchStats* stats, cudaStream_t stream);

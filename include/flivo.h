@@ -64,8 +64,15 @@ typedef struct flivo_options {
     uint64_t initial_points;    /* sizing hint for the device tables; 0 -> 1<<20 */
     int32_t  sort_scan;         /* 1: process scan points in Morton order of their cells (results are
                                    reported in the caller's order either way); 0: caller's order */
-    int32_t  reserved;
+    int32_t  ivox_nearby;       /* 0: ikd-Tree semantics (exact kNN, Add_Points voxel rule).  FLIVO_IVOX_*: the map
+                                   behaves as faster_lio::IVox<3, DEFAULT> (include/ivox3d/ivox3d.h, the structure
+                                   the reference builds when USE_ikdtree is off, CMakeLists.txt:15): downsample_size
+                                   is Options::resolution_ (ivox_grid_resolution, src/laser_mapping.cpp:1021) and
+                                   the value is the size of the nearby stencil (ivox_nearby_type, :1022-1035) */
 } flivo_options;
+
+/* IVox::NearbyType (include/ivox3d/ivox3d.h:46-51) as the number of voxels searched */
+enum { FLIVO_IVOX_OFF = 0, FLIVO_IVOX_CENTER = 1, FLIVO_IVOX_NEARBY6 = 7, FLIVO_IVOX_NEARBY18 = 19, FLIVO_IVOX_NEARBY26 = 27 };
 
 typedef struct flivo_cfg {
     int32_t mode;               /* FLIVO_MODE_V3 / FLIVO_MODE_V1 */
@@ -100,7 +107,9 @@ void* flivo_ctx_stream(flivo_ctx* ctx);
 int  flivo_sync(flivo_ctx* ctx);
 
 /* ---- map: ikd-Tree API surface (include/ikd-Tree/ikd_Tree.h:166-188) ------------------------- */
-/* KD_TREE::set_downsample_param (ikd_Tree.cpp:36-38). Rebuilds the voxel index when the map is non-empty. */
+/* KD_TREE::set_downsample_param (ikd_Tree.cpp:36-38). Rebuilds the voxel index when the map is non-empty.
+ * iVox mode: sets filter_size_map_min of map_incremental's add rule (src/laser_mapping.cpp:353-375; default = the
+ * voxel resolution); the voxel resolution itself is fixed at context creation. */
 int flivo_map_set_downsample(flivo_ctx* ctx, float downsample_size);
 /* KD_TREE::Build (ikd_Tree.cpp:337-348): replaces the map; no downsampling; ids = 0..n-1. */
 int flivo_map_build(flivo_ctx* ctx, const float* xyz, size_t n, size_t stride_bytes);
@@ -128,7 +137,10 @@ int flivo_map_acquire_removed(flivo_ctx* ctx, float* out_xyz, size_t cap, size_t
 
 /* Batched KD_TREE::Nearest_Search (ikd_Tree.cpp:350-380; Search :843-986): exact k nearest live points
  * with squared distance <= max_dist, ascending by (float32 squared distance, insertion id).
- * k <= FLIVO_K.  Rows are padded with id -1 / +inf when fewer than k exist.  out_xyz/out_sqd/out_id may be NULL. */
+ * k <= FLIVO_K.  Rows are padded with id -1 / +inf when fewer than k exist.  out_xyz/out_sqd/out_id may be NULL.
+ * iVox mode: batched IVox::GetClosestPoint(pt, closest_pt, max_num = k, max_range) (include/ivox3d/ivox3d.h:132-204):
+ * the k nearest among the points of the nearby voxels with squared distance < max_dist (= max_range * max_range,
+ * strict), ascending by (distance, insertion id); the reference leaves the order after element 0 to std::nth_element. */
 int flivo_knn(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t stride_bytes, int k, double max_dist,
               float* out_xyz /* nq*k*3 */, float* out_sqd /* nq*k */, int32_t* out_id /* nq*k */,
               int32_t* out_count /* nq */);
@@ -189,7 +201,10 @@ int flivo_repack_v1(const double HTH[144], const double HTz[12], double laser_po
 int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* P, const flivo_cfg* cfg, flivo_report* rep);
 
 /* LaserMapping::map_incremental (src/laser_mapping.cpp:329-389, USE_ikdtree branch :384): world-transform the
- * uploaded scan with `st` on the device and Add_Points(..., true) without a host round trip. */
+ * uploaded scan with `st` on the device and Add_Points(..., true) without a host round trip.
+ * iVox mode: the other branch of the same function (:340-387): per point, from the neighbours cached by the last
+ * search of this scan, add / add without down-sampling / drop; then AddPoints(points_to_add) and
+ * AddPoints(point_no_need_downsample).  A scan that was never searched is added whole (Nearest_Points empty). */
 int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t* n_added);
 
 /* ---- multi-GPU (BASELINE configs 4-5; no counterpart in the reference) -------------------------- */

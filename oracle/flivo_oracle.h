@@ -106,6 +106,23 @@ void orc_undistort(float* pts, size_t n, size_t stride_floats, const float* t_ms
 // pcl::VoxelGrid::filter (src/laser_mapping.cpp:129-130); returns the number of output points
 long orc_voxel_grid(const float* xyzi, const float* t_ms, size_t n, float leaf, float* out_xyzi, float* out_t, size_t cap);
 
+// ---- iVox branch (oracle/ivox_oracle.cpp) ----
+// faster_lio::IVox<3, DEFAULT> (include/ivox3d/ivox3d.h): nearby = 1, 7, 19, 27 voxels (CENTER, NEARBY6/18/26);
+// capacity 0 -> Options::capacity_ default (1 000 000 voxels)
+typedef struct orc_ivox orc_ivox;
+orc_ivox* orc_ivox_create(float resolution, int nearby, size_t capacity);
+void orc_ivox_destroy(orc_ivox*);
+void orc_ivox_add_points(orc_ivox*, const float* xyz, size_t n);                       // AddPoints (:247-276)
+size_t orc_ivox_num_grids(orc_ivox*);                                                  // NumValidGrids (:206-209)
+size_t orc_ivox_evicted(orc_ivox*);
+size_t orc_ivox_points(orc_ivox*, float* xyz, int32_t* ids, size_t cap);
+// batched GetClosestPoint(pt, closest_pt, k, max_range) (:132-204); out_count = -1: no candidate (list untouched)
+void orc_ivox_knn(orc_ivox*, const float* q_xyz, size_t nq, int k, double max_range,
+                  int32_t* out_id, float* out_sqd, float* out_xyz, int32_t* out_count, int64_t* tie_straddles);
+// map_incremental's add rule (src/laser_mapping.cpp:340-381): 1 = points_to_add, 2 = point_no_need_downsample, 0 = dropped
+void orc_ivox_map_filter(const float* world_xyz, size_t n, const float* near_xyz, const int32_t* near_cnt,
+                         double filter_size_map_min, uint8_t* flag_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -61,8 +61,8 @@ class State(C.Structure):
 def build(force=False):
     """Compile the oracle (and oracle/_ref when /root/reference is present). Building the checker
     is not using it."""
-    if force or not os.path.exists(LIB_PATH) or \
-            os.path.getmtime(LIB_PATH) < os.path.getmtime(os.path.join(HERE, "flivo_oracle.cpp")):
+    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < max(
+            os.path.getmtime(os.path.join(HERE, f)) for f in ("flivo_oracle.cpp", "ivox_oracle.cpp", "flivo_oracle.h")):
         subprocess.check_call(["make", "-C", HERE, os.path.join(HERE, "liboracle.so")],
                               stdout=subprocess.DEVNULL)
     ref_src = "/root/reference/include/ikd-Tree/ikd_Tree.cpp"
@@ -109,6 +109,19 @@ def lib():
         L.orc_undistort.argtypes = [f32p, C.c_size_t, C.c_size_t, f32p, f64p, C.c_int, f64p, f64p, f64p, f64p]
         L.orc_voxel_grid.argtypes = [f32p, C.c_void_p, C.c_size_t, C.c_float, f32p, C.c_void_p, C.c_size_t]
         L.orc_voxel_grid.restype = C.c_long
+        L.orc_ivox_create.argtypes = [C.c_float, C.c_int, C.c_size_t]
+        L.orc_ivox_create.restype = C.c_void_p
+        L.orc_ivox_destroy.argtypes = [C.c_void_p]
+        L.orc_ivox_add_points.argtypes = [C.c_void_p, f32p, C.c_size_t]
+        L.orc_ivox_num_grids.argtypes = [C.c_void_p]
+        L.orc_ivox_num_grids.restype = C.c_size_t
+        L.orc_ivox_evicted.argtypes = [C.c_void_p]
+        L.orc_ivox_evicted.restype = C.c_size_t
+        L.orc_ivox_points.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.orc_ivox_points.restype = C.c_size_t
+        L.orc_ivox_knn.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_int, C.c_double, i32p, f32p, f32p, i32p,
+                                   C.POINTER(C.c_int64)]
+        L.orc_ivox_map_filter.argtypes = [f32p, C.c_size_t, f32p, i32p, C.c_double, u8p]
         _lib = L
     return _lib
 
@@ -262,6 +275,54 @@ class OracleMap:
         ids = np.empty(n, np.int32)
         lib().orc_map_live(self.h, xyz.ctypes.data, ids.ctypes.data, n)
         return xyz, ids
+
+
+class OracleIVox:
+    """Restated faster_lio::IVox<3, DEFAULT> (oracle/ivox_oracle.cpp)."""
+
+    def __init__(self, resolution, nearby=19, capacity=0):
+        self.h = lib().orc_ivox_create(resolution, nearby, capacity)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_ivox_destroy(self.h)
+            self.h = None
+
+    def add_points(self, xyz):
+        xyz = _c(xyz, np.float32)
+        lib().orc_ivox_add_points(self.h, xyz, xyz.shape[0])
+
+    def num_grids(self):
+        return lib().orc_ivox_num_grids(self.h)
+
+    def evicted(self):
+        return lib().orc_ivox_evicted(self.h)
+
+    def points(self):
+        n = lib().orc_ivox_points(self.h, None, None, 0)
+        xyz = np.empty((n, 3), np.float32)
+        ids = np.empty(n, np.int32)
+        lib().orc_ivox_points(self.h, xyz.ctypes.data, ids.ctypes.data, n)
+        return xyz, ids
+
+    def knn(self, queries, k=5, max_range=5.0):
+        """-> (ids, sqd, xyz, count, ties); count = -1 where GetClosestPoint found no candidate."""
+        q = _c(queries, np.float32)
+        n = q.shape[0]
+        oid = np.empty((n, k), np.int32)
+        osq = np.empty((n, k), np.float32)
+        oxyz = np.empty((n, k, 3), np.float32)
+        ocnt = np.empty(n, np.int32)
+        ties = C.c_int64(0)
+        lib().orc_ivox_knn(self.h, q, n, k, float(max_range), oid, osq, oxyz, ocnt, C.byref(ties))
+        return oid, osq, oxyz, ocnt, ties.value
+
+
+def ivox_map_filter(world_xyz, near_xyz, near_cnt, filter_size_map_min):
+    w = _c(world_xyz, np.float32)
+    flags = np.empty(w.shape[0], np.uint8)
+    lib().orc_ivox_map_filter(w, w.shape[0], _c(near_xyz, np.float32), _c(near_cnt, np.int32), float(filter_size_map_min), flags)
+    return flags
 
 
 class RefTree:

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "imu_processing.h"
+#include "ivox3d.h"
 #include "laser_mapping.h"
 
 static std::vector<float> read_f32(FILE* f, size_t n) {
@@ -98,8 +99,66 @@ static int run_frontend(const char* in_path, const char* out_path) {
     return 0;
 }
 
+// faster_lio::IVox drop-in (host/ivox3d.h), used the way src/laser_mapping.cpp:145-148,520 uses ivox_: AddPoints in two
+// batches, then GetClosestPoint for every query (single-query form for the first few, batched form for all)
+static int run_ivox(const char* in_path, const char* out_path) {
+    FILE* f = fopen(in_path, "rb");
+    if (!f) { perror("open"); return 2; }
+    int32_t hdr[4];   // n_map, n_queries, nearby (0, 6, 18, 26), unused
+    if (fread(hdr, 4, 4, f) != 4) return 2;
+    const double res = read_f64(f, 1)[0];
+    std::vector<float> map = read_f32(f, (size_t)hdr[0] * 3), qs = read_f32(f, (size_t)hdr[1] * 3);
+    fclose(f);
+    using IVoxType = faster_lio::IVox<3, faster_lio::IVoxNodeType::DEFAULT, PointType>;   // include/laser_mapping.h:65
+    try {
+        IVoxType::Options o;
+        o.resolution_ = (float)res;
+        o.nearby_type_ = hdr[2] == 0 ? IVoxType::NearbyType::CENTER : hdr[2] == 6 ? IVoxType::NearbyType::NEARBY6
+                       : hdr[2] == 18 ? IVoxType::NearbyType::NEARBY18 : IVoxType::NearbyType::NEARBY26;
+        IVoxType ivox(o);
+        PointVector a(hdr[0] / 2), b(hdr[0] - hdr[0] / 2), q(hdr[1]);
+        for (int i = 0; i < hdr[0]; ++i) {
+            PointType& p = i < hdr[0] / 2 ? a[i] : b[i - hdr[0] / 2];
+            p.x = map[3 * i]; p.y = map[3 * i + 1]; p.z = map[3 * i + 2];
+        }
+        for (int i = 0; i < hdr[1]; ++i) { q[i].x = qs[3 * i]; q[i].y = qs[3 * i + 1]; q[i].z = qs[3 * i + 2]; }
+        ivox.AddPoints(a);
+        ivox.AddPoints(b);
+        std::vector<float> xyz, sqd;
+        std::vector<int32_t> ids, cnt;
+        ivox.GetClosestPointBatch(q, 5, 5.0, xyz, sqd, ids, cnt);
+        // the single-query form must agree with the batch rows and leave the list untouched when nothing is near
+        int single_ok = 1;
+        for (int i = 0; i < hdr[1] && i < 64; ++i) {
+            PointVector near(1);
+            near[0].x = 123.f;
+            const bool got = ivox.GetClosestPoint(q[i], near, 5);
+            if (got != (cnt[i] > 0)) single_ok = 0;
+            if (!got && !(near.size() == 1 && near[0].x == 123.f)) single_ok = 0;
+            if (got) {
+                if ((int)near.size() != cnt[i]) single_ok = 0;
+                for (int r = 0; r < cnt[i] && r < (int)near.size(); ++r)
+                    if (near[r].x != xyz[(i * 5 + r) * 3] || near[r].y != xyz[(i * 5 + r) * 3 + 1] || near[r].z != xyz[(i * 5 + r) * 3 + 2]) single_ok = 0;
+            }
+        }
+        FILE* out = fopen(out_path, "wb");
+        if (!out) { perror("open out"); return 2; }
+        int32_t oh[4] = {(int32_t)ivox.NumPoints(), (int32_t)ivox.NumValidGrids(), single_ok, 0};
+        fwrite(oh, 4, 4, out);
+        fwrite(ids.data(), 4, ids.size(), out);
+        fwrite(cnt.data(), 4, cnt.size(), out);
+        fwrite(sqd.data(), 4, sqd.size(), out);
+        fclose(out);
+    } catch (const std::exception& e) {
+        printf("error: %s\n", e.what());
+        return 3;
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc >= 4 && strcmp(argv[1], "--frontend") == 0) return run_frontend(argv[2], argv[3]);
+    if (argc >= 4 && strcmp(argv[1], "--ivox") == 0) return run_ivox(argv[2], argv[3]);
     if (argc >= 2 && strcmp(argv[1], "--no-gpu") == 0) {
         try {
             KD_TREE t(0.5f, 0.6f, 0.5f);

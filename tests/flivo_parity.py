@@ -24,19 +24,35 @@ def oracle_knn(map_xyz, queries, k=5, max_dist=np.inf, ids=None, alive=None):
     return orc.knn_bruteforce(map_xyz, queries, k, max_dist, ids, alive)
 
 
-def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids=None):
-    """One h_share_model trip on the CPU.  cache: dict carrying Nearest_Points between trips."""
+def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids=None, ivox=None):
+    """One h_share_model trip on the CPU.  cache: dict carrying Nearest_Points between trips.
+    ivox: an orc.OracleIVox — the search is then IVox::GetClosestPoint (src/laser_mapping.cpp:520) and the
+    far-neighbour gate of the ikd-Tree branch (:518) does not exist."""
     st = orc.State.from_array(x)
-    if searched:
+    if searched and ivox is not None:
+        wpts = orc.body_to_world(body, st)
+        oid, osq, oxyz, ocnt, ties = ivox.knn(wpts, 5, 5.0)
+        none = ocnt < 0                       # no candidate: the list keeps its previous content (ivox3d.h:168-170)
+        if "ids" in cache:
+            for new, key in ((oid, "ids"), (osq, "sqd"), (oxyz, "xyz"), (ocnt, "cnt")):
+                new[none] = cache[key][none]
+        else:
+            ocnt[none] = 0
+        cache.update(ids=oid, sqd=osq, xyz=oxyz, cnt=ocnt, ties=ties + cache.get("ties", 0))
+    elif searched:
         wpts = orc.body_to_world(body, st)
         oid, osq, oxyz, ocnt, ties = oracle_knn(map_xyz, wpts, 5, np.inf, ids=map_ids)
         cache.update(ids=oid, sqd=osq, xyz=oxyz, cnt=ocnt, ties=ties)
-    d5 = np.where(cache["cnt"] >= 5, cache["sqd"][:, 4], np.inf).astype(np.float32)
+    if ivox is not None:
+        d5 = np.zeros(len(body), np.float32)
+    else:
+        d5 = np.where(cache["cnt"] >= 5, cache["sqd"][:, 4], np.inf).astype(np.float32)
     out = orc.h_share_model(body, st, cache["xyz"], cache["cnt"], d5, searched, mode, mask_prev)
     return out
 
 
-def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.001, limit=None, force_search=False):
+def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.001, limit=None, force_search=False,
+                  ivox=None):
     """The whole iterated update with the restated reference loop (V3: esekfom.hpp:1619-1928; V1:
     src/laser_mapping.cpp:165-242).  Returns dict(x, P, trips, searches, dx (per trip), masks, eff, ids)."""
     limit = np.full(23, 0.001) if limit is None else np.asarray(limit, float)
@@ -53,7 +69,7 @@ def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.0
     out = None
     while it < max_iter and not stopped:
         do_search = bool(search or force_search)
-        out = oracle_trip(map_xyz, body, x.as_array(), do_search, cache, mode, mask)
+        out = oracle_trip(map_xyz, body, x.as_array(), do_search, cache, mode, mask, ivox=ivox)
         mask = out["mask"]
         searches += int(do_search)
         if mode == orc.MODE_V1:
@@ -74,7 +90,7 @@ def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.0
         trips += 1
         it += 1
     return dict(x=x.as_array(), P=P, trips=trips, searches=searches, dx=dxs, mask=mask, eff=out["eff"],
-                ids=cache["ids"], cnt=cache["cnt"], sqd=cache["sqd"], ties=cache["ties"], trip_out=trip_out,
+                ids=cache["ids"], cnt=cache["cnt"], sqd=cache["sqd"], xyz=cache["xyz"], ties=cache["ties"], trip_out=trip_out,
                 n_eff=out["n_eff"], borderline=out["borderline"])
 
 
@@ -149,3 +165,48 @@ def check_update_against_oracle(pkg, world, scan, mode=0, max_iter=4, force_sear
             print("update: trips=%d searches=%d n_eff=%d dx_err=%.2e x_err=%.2e P_err=%.2e pos err %.4f -> %.4f m gpu %.3f ms" %
                   (rep.trips, rep.searches, rep.n_eff, dx_err, x_err, p_err, t_err0, t_err1, rep.gpu_ms))
         return dict(rep=rep, x=xg, P=Pg, oracle=o, pos_err=(t_err0, t_err1))
+
+
+# ---- iVox mode --------------------------------------------------------------------------------
+def check_trip_ivox(pkg, F, ivox, body, x, mode, verbose=False):
+    """Single searched trip in iVox mode against the restated IVox (oracle/ivox_oracle.cpp)."""
+    st = pkg.State.from_array(x)
+    g = F.h_share_model(st, mode, True, want=("selected", "eff", "nbr_id", "nbr_sqd", "plane", "world"))
+    cache = {}
+    o = oracle_trip(None, body, x, True, cache, mode, ivox=ivox)
+    assert cache["ties"] == 0, "synthetic data has a float32 distance tie across rank 5; re-seed"
+    want_ids = np.where(np.arange(5)[None, :] < cache["cnt"][:, None], cache["ids"], -1)
+    bad = int(np.any(want_ids != g["nbr_id"], axis=1).sum())
+    assert bad == 0, "%d / %d neighbour rows differ" % (bad, len(body))
+    assert np.array_equal(g["world"], o["world"]), "feats_down_world differs"
+    assert np.array_equal(g["nbr_sqd"], np.where(want_ids >= 0, cache["sqd"], np.inf).astype(np.float32))
+    assert np.array_equal(g["selected"], o["mask"]), "point_selected_surf differs at %d points" % int((g["selected"] != o["mask"]).sum())
+    assert np.array_equal(g["eff"], o["eff"]), "effective-row mask differs"
+    assert g["n_eff"] == o["n_eff"]
+    assert np.array_equal(g["plane"], o["normvec"]), "normvec differs"
+    e1, e2 = rel_err_block(g["HTH"], o["HTH"]), rel_err_block(g["HTz"], o["HTz"])
+    assert e1 <= HTH_RTOL and e2 <= HTH_RTOL, "HTH / HTz relative error %g / %g" % (e1, e2)
+    if verbose:
+        print("ivox trip: n=%d n_eff=%d five-neighbour rows=%d HTH rel err %.2e" % (len(body), g["n_eff"], int((cache["cnt"] >= 5).sum()), e1))
+    return g, o, cache
+
+
+def check_update_ivox(pkg, F, ivox, body, x_prior, mode, max_iter=4, verbose=False):
+    """Whole iterated update in iVox mode against the restated loop."""
+    npd = 18 if mode == pkg.MODE_V1 else 23
+    P0 = np.eye(npd) * 1e-4
+    cfg = pkg.make_cfg(mode=mode, max_iter=max_iter, laser_point_cov=0.001)
+    xg, Pg, rep = F.iekf_update(pkg.State.from_array(x_prior), P0, cfg)
+    o = oracle_update(None, body, x_prior, P0, mode, max_iter, 0.001, None, False, ivox=ivox)
+    assert o["ties"] == 0
+    assert rep.trips == o["trips"] and rep.searches == o["searches"], "trips/searches %d/%d vs oracle %d/%d" % (rep.trips, rep.searches, o["trips"], o["searches"])
+    assert rep.n_eff == o["n_eff"], "n_eff %d vs oracle %d" % (rep.n_eff, o["n_eff"])
+    dx_err = np.abs(np.array(rep.dx_last[:npd]) - o["dx"][-1][:npd]).max()
+    assert dx_err <= DX_ATOL, "last state increment differs by %g" % dx_err
+    x_err = np.abs(xg.as_array() - o["x"]).max()
+    assert x_err <= 1e-6, "posterior state differs by %g" % x_err
+    p_err = np.abs(Pg - o["P"]).max() / np.abs(o["P"]).max()
+    assert p_err <= 1e-6
+    if verbose:
+        print("ivox update: trips=%d searches=%d n_eff=%d dx_err=%.2e x_err=%.2e" % (rep.trips, rep.searches, rep.n_eff, dx_err, x_err))
+    return xg, Pg, rep, o

@@ -1,0 +1,115 @@
+"""CPU (-m "not gpu"): the restated faster_lio::IVox (oracle/ivox_oracle.cpp) against an independent
+numpy restatement, its edge cases, and map_incremental's add rule on hand-made cases.  Parity of this branch is
+"unpinned" (ivox3d.h needs Eigen / glog / TBB, absent here; the reference has no tests for it)."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle as orc
+
+
+def _round_half_away(x):
+    return (np.sign(x) * np.floor(np.abs(x) + np.float32(0.5))).astype(np.int64)
+
+
+def _numpy_ivox_knn(pts, q, res, nearby, k=5, max_range=5.0):
+    """Brute force: candidates = points whose Pos2Grid key differs from the query's by an offset with at most
+    {1:0, 7:1, 19:2, 27:3}[nearby] non-zero components; k nearest by (float32 distance, index)."""
+    inv = np.float32(1.0 / res)
+    pk = _round_half_away(pts * inv)
+    qk = _round_half_away(q * inv)
+    max_nz = {1: 0, 7: 1, 19: 2, 27: 3}[nearby]
+    ids = np.full((len(q), k), -1, np.int32)
+    sqd = np.full((len(q), k), np.inf, np.float32)
+    cnt = np.zeros(len(q), np.int32)
+    for i in range(len(q)):
+        dk = pk - qk[i]
+        ok = (np.abs(dk).max(1) <= 1) & ((dk != 0).sum(1) <= max_nz)
+        idx = np.nonzero(ok)[0]
+        if len(idx) == 0:
+            cnt[i] = -1
+            continue
+        d = pts[idx] - q[i]
+        d2 = (d[:, 0] * d[:, 0] + (d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2])).astype(np.float32)
+        keep = d2.astype(np.float64) < max_range * max_range
+        idx, d2 = idx[keep], d2[keep]
+        if len(idx) == 0:
+            cnt[i] = -1
+            continue
+        o = np.lexsort((idx, d2))[:k]
+        cnt[i] = len(o)
+        ids[i, :len(o)] = idx[o]
+        sqd[i, :len(o)] = d2[o]
+    return ids, sqd, cnt
+
+
+@pytest.mark.parametrize("nearby", [1, 7, 19, 27])
+def test_ivox_knn_matches_numpy(nearby):
+    rng = np.random.default_rng(100 + nearby)
+    pts = rng.uniform(-6, 6, (6000, 3)).astype(np.float32)
+    pts[:, 2] = (0.05 * rng.standard_normal(6000)).astype(np.float32)     # a noisy ground plane: dense voxels
+    q = pts[rng.integers(0, len(pts), 400)] + rng.normal(0, 0.05, (400, 3)).astype(np.float32)
+    q = np.vstack([q, rng.uniform(-8, 8, (50, 3)).astype(np.float32)])   # some queries off the surface
+    v = orc.OracleIVox(0.5, nearby)
+    v.add_points(pts[:3000])
+    v.add_points(pts[3000:])                                              # ids continue across calls
+    ids, sqd, xyz, cnt, ties = v.knn(q, 5, 5.0)
+    wi, ws, wc = _numpy_ivox_knn(pts, q.astype(np.float32), 0.5, nearby)
+    assert ties == 0
+    assert np.array_equal(cnt, wc)
+    assert np.array_equal(ids, wi)
+    assert np.array_equal(sqd, ws)
+    got = ids >= 0
+    assert np.array_equal(xyz[got], pts[ids[got]])
+    assert (cnt == -1).any() and (cnt == 5).any()
+
+
+def test_ivox_max_range_and_small_k():
+    pts = np.array([[0, 0, 0], [0.1, 0, 0], [0.2, 0, 0], [0.3, 0, 0]], np.float32)
+    v = orc.OracleIVox(1.0, 27)
+    v.add_points(pts)
+    ids, sqd, _, cnt, _ = v.knn(np.array([[0.0, 0, 0]], np.float32), 3, 0.25)   # strict d < 0.0625: 0.0, 0.01, 0.04
+    assert cnt[0] == 3 and list(ids[0]) == [0, 1, 2]
+    ids, sqd, _, cnt, _ = v.knn(np.array([[0.0, 0, 0]], np.float32), 5, 0.2)    # 0.04 is not < 0.04 (float 0.2f^2 > 0.04?)
+    assert cnt[0] in (2, 3)
+    ids, _, _, cnt, _ = v.knn(np.array([[9.0, 9, 9]], np.float32), 5, 5.0)
+    assert cnt[0] == -1 and (ids[0] == -1).all()
+
+
+def test_ivox_pos2grid_rounds_half_away_from_zero():
+    # keys: round(-0.5) = -1, round(0.5) = 1, round(1.5) = 2 (std::round), resolution 1
+    pts = np.array([[-0.5, 0, 0], [0.5, 0, 0], [1.5, 0, 0]], np.float32)
+    v = orc.OracleIVox(1.0, 1)     # CENTER: only the query's own voxel
+    v.add_points(pts)
+    assert v.num_grids() == 3
+    ids, _, _, cnt, _ = v.knn(np.array([[-1.2, 0, 0], [1.2, 0, 0], [2.2, 0, 0], [0.2, 0, 0]], np.float32), 5, 5.0)
+    assert list(ids[:, 0]) == [0, 1, 2, -1] and list(cnt) == [1, 1, 1, -1]
+
+
+def test_ivox_lru_eviction_restated():
+    # capacity 4: the 4th new voxel triggers the eviction of the least recently touched one (ivox3d.h:262-265)
+    v = orc.OracleIVox(1.0, 1, capacity=4)
+    v.add_points(np.array([[0, 0, 0], [5, 0, 0], [10, 0, 0]], np.float32))
+    v.add_points(np.array([[0.1, 0, 0]], np.float32))           # touches voxel 0: now most recent
+    v.add_points(np.array([[15, 0, 0]], np.float32))            # 4th voxel -> size >= capacity -> evict voxel of x=5
+    assert v.evicted() == 1 and v.num_grids() == 3
+    _, _, _, cnt, _ = v.knn(np.array([[5, 0, 0], [0, 0, 0], [10, 0, 0], [15, 0, 0]], np.float32), 5, 5.0)
+    assert list(cnt) == [-1, 2, 1, 1]
+
+
+def test_ivox_map_filter_rule():
+    fs = 0.5
+    # point in voxel [0,0.5)^3, centre (0.25,0.25,0.25)
+    pw = np.array([[0.30, 0.30, 0.30]] * 5, np.float32)
+    near = np.zeros((5, 5, 3), np.float32)
+    cnt = np.zeros(5, np.int32)
+    # 0: no cached neighbours -> add
+    # 1: nearest neighbour farther than fs/2 from the centre on every axis -> no-need-downsample list
+    near[1, :] = [0.9, 0.9, 0.9]; cnt[1] = 5
+    # 2: five neighbours, one of them closer to the centre than the point -> dropped
+    near[2, :] = [0.6, 0.3, 0.3]; near[2, 3] = [0.26, 0.25, 0.25]; cnt[2] = 5
+    # 3: five neighbours, all farther from the centre than the point -> add
+    near[3, :] = [0.6, 0.3, 0.3]; cnt[3] = 5
+    # 4: fewer than five neighbours (and near[0] not far on every axis) -> add whatever their distance
+    near[4, 0] = [0.25, 0.25, 0.25]; cnt[4] = 2
+    flags = orc.ivox_map_filter(pw, near, cnt, fs)
+    assert list(flags) == [1, 2, 0, 1, 1]
