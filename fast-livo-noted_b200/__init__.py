@@ -104,7 +104,7 @@ SYMBOLS = [
     "flivo_repack_v1", "flivo_iekf_update", "flivo_map_add_scan", "flivo_comm_unique_id", "flivo_comm_init",
     "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps", "flivo_debug_search_stamps",
     "flivo_raw_upload", "flivo_raw_set_device", "flivo_raw_undistort", "flivo_raw_downsample", "flivo_raw_download",
-    "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach",
+    "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach", "flivo_set_gnss",
 ]
 
 _lib = None
@@ -148,6 +148,7 @@ def lib():
     L.flivo_repack_v1.argtypes = [vp, vp, C.c_double, vp, vp]
     L.flivo_iekf_update.argtypes = [vp, C.POINTER(State), vp, C.POINTER(Cfg), C.POINTER(Report)]
     L.flivo_map_add_scan.argtypes = [vp, C.POINTER(State), C.POINTER(i32)]
+    L.flivo_set_gnss.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.flivo_comm_unique_id.argtypes = [vp]
     L.flivo_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
     L.flivo_comm_destroy.argtypes = [vp]
@@ -354,6 +355,16 @@ class Flivo:
         rep = Report()
         self._ck(self._L.flivo_iekf_update(self.h, C.byref(x), _ptr(Pm), C.byref(cfg), C.byref(rep)))
         return x, Pm, rep
+
+    def set_gnss(self, pos_global=None, antlever=(0.0, 0.0, 0.0), std=(1.0, 1.0, 1.0)):
+        """GNSS observation folded into the following V1 updates (src/laser_mapping.cpp:612-617); None clears it."""
+        if pos_global is None:
+            self._ck(self._L.flivo_set_gnss(self.h, None, None, None))
+            return
+        a = (C.c_double * 3)(*[float(v) for v in pos_global])
+        b = (C.c_double * 3)(*[float(v) for v in antlever])
+        c = (C.c_double * 3)(*[float(v) for v in std])
+        self._ck(self._L.flivo_set_gnss(self.h, a, b, c))
 
     def map_add_scan(self, st):
         out = C.c_int32(0)

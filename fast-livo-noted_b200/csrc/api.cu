@@ -132,6 +132,9 @@ struct flivo_ctx {
     int graph_search_grid = 0, graph_fused_grid = 0, graph_trips = 0, graph_churn = 0;
     cudaEvent_t ev[2 * MAX_TRIPS + 2] = {};
     flivo_stats stats{};
+    // GNSS observation of the next updates (flivo_set_gnss)
+    bool gnss_on = false;
+    double gnss[9] = {};
     // iVox mode (flivo_options::ivox_nearby != 0)
     double ivox_filter = 0.0;                 // filter_size_map_min of map_incremental's add rule
     unsigned char* d_ivox_flags = nullptr;    // [2][cap] add / no-need-downsample flags in the caller's order
@@ -663,6 +666,8 @@ static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, d
     j.mode = mode; j.max_iter = max_iter; j.force_search = force_search; j.nranks = ctx->nranks; j.max_sq_bits = max_sq_bits; j.aux_out = aux_out;
     j.R = R;
     for (int i = 0; i < 23; ++i) j.limit[i] = limit23 ? limit23[i] : 0.001;
+    j.gnss_on = (ctx->gnss_on && mode == FLIVO_MODE_V1) ? 1 : 0; j.gnss_pad = 0;
+    for (int i = 0; i < 3; ++i) { j.gnss_pos[i] = ctx->gnss[i]; j.gnss_lever[i] = ctx->gnss[3 + i]; j.gnss_std[i] = ctx->gnss[6 + i]; }
 }
 // launch grids are rounded up to capacity buckets so that scans of similar size share one captured graph;
 // surplus CTAs see i >= job->n (k_search) or an exhausted unit counter (k_fused) and leave at once
@@ -961,6 +966,16 @@ static int ivox_add_scan(flivo_ctx* ctx, int32_t* n_added) {
     int rc = total ? ctx->map.add_points(sel_add, total, false, &added, ctx->err) : 0;
     if (n_added) *n_added = (int32_t)total;
     return map_rc(ctx, rc);
+}
+
+extern "C" int flivo_set_gnss(flivo_ctx* ctx, const double pos_global[3], const double antlever[3], const double std3[3]) {
+    ENTER();
+    if (!pos_global) { ctx->gnss_on = false; return FLIVO_OK; }
+    NEED(antlever && std3, FLIVO_E_ARG, "null antlever / std");
+    NEED(std3[0] > 0.0 && std3[1] > 0.0 && std3[2] > 0.0, FLIVO_E_ARG, "gnss std must be > 0");
+    for (int i = 0; i < 3; ++i) { ctx->gnss[i] = pos_global[i]; ctx->gnss[3 + i] = antlever[i]; ctx->gnss[6 + i] = std3[i]; }
+    ctx->gnss_on = true;
+    return FLIVO_OK;
 }
 
 extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t* n_added) {

@@ -55,6 +55,12 @@ struct Job {
     uint32_t max_sq_bits;      // kNN distance bound as float bits (INF_BITS = unbounded)
     double R;                  // laser_point_cov
     double limit[23];
+    // GNSS position observation folded into the V1 normal equations (src/laser_mapping.cpp:612-617,
+    // GNSSProcessing::computeH src/GNSS_Processing.cpp:204-237); see flivo_set_gnss
+    int gnss_on, gnss_pad;
+    double gnss_pos[3];        // antenna position in the global frame (rot_enu2global_^T * blh + delta_pos_)
+    double gnss_lever[3];      // antlever_
+    double gnss_std[3];        // gnss_.std
 };
 
 enum { PF_HAVE5 = 1,    // five neighbours exist (points_near.size() >= NUM_MATCH_POINTS)

@@ -570,6 +570,36 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         }
         if (tid < 18) s_vec[tid] = S.pre->vec[tid];   // state_propagat - state, from k_solve_pre
         __syncthreads();
+        if (S.job->gnss_on) {
+            // HPH.block<6,6>(0,0) += gnss_HPH; HPL.block<6,1>(0,0) += gnss_HPL (src/laser_mapping.cpp:612-617) with
+            // computeH (src/GNSS_Processing.cpp:204-237) evaluated at the current iterate: Hsub = [R [l]x | -I] (3x6),
+            // error = p_gnss - pos + R l, dropped when |error| > 2 m, weights diag(1/std0, 1/std1, 100/std2)
+            if (tid == 0) {
+                const double* R = s_x + S_ROT;
+                const double* l = S.job->gnss_lever;
+                const double K[9] = {0.0, -l[2], l[1], l[2], 0.0, -l[0], -l[1], l[0], 0.0};   // SKEW_SYM_MATRX (so3_math.h:9)
+                double Hs[18], RK[9], err[3];
+                d_mat3mul(R, K, RK);
+                for (int r = 0; r < 3; ++r) {
+                    for (int c = 0; c < 3; ++c) { Hs[r * 6 + c] = RK[r * 3 + c]; Hs[r * 6 + 3 + c] = (r == c) ? -1.0 : 0.0; }
+                    err[r] = S.job->gnss_pos[r] - s_x[S_POS + r] + (R[r * 3] * l[0] + R[r * 3 + 1] * l[1] + R[r * 3 + 2] * l[2]);
+                }
+                if (!(sqrt(err[0] * err[0] + err[1] * err[1] + err[2] * err[2]) > 2.0)) {
+                    const double wg[3] = {1.0 / S.job->gnss_std[0], 1.0 / S.job->gnss_std[1], 100.0 / S.job->gnss_std[2]};
+                    for (int a = 0; a < 6; ++a) {
+                        for (int b = 0; b < 6; ++b) {
+                            double acc = 0.0;
+                            for (int k = 0; k < 3; ++k) acc += (Hs[k * 6 + a] * wg[k]) * Hs[k * 6 + b];
+                            s_H6[a * 6 + b] += acc;
+                        }
+                        double acc = 0.0;
+                        for (int k = 0; k < 3; ++k) acc += (Hs[k * 6 + a] * wg[k]) * err[k];
+                        s_z6[a] += acc;
+                    }
+                }
+            }
+            __syncthreads();
+        }
         // Aug (6 x 24) = [S^T | C1^T],  S = I + H6 * C11,  C = state.cov
         for (int e = tid; e < 6 * 24; e += NT) {
             int r = e / 24, c = e % 24;

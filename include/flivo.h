@@ -200,6 +200,13 @@ int flivo_repack_v1(const double HTH[144], const double HTz[12], double laser_po
  * V1: the loop in LaserMapping::Run (src/laser_mapping.cpp:165-242), P = state.cov 18x18.  Row-major, in/out. */
 int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* P, const flivo_cfg* cfg, flivo_report* rep);
 
+/* The GNSS position observation of the compiled (V1) path: `if (bgnss_en && p_gnss->new_gnss_) { computeH(...);
+ * HPH.block<6,6>(0,0) += gnss_HPH; HPL.block<6,1>(0,0) += gnss_HPL; }` (src/laser_mapping.cpp:612-617) with
+ * GNSSProcessing::computeH (src/GNSS_Processing.cpp:204-237) evaluated on the device at every trip's iterate.
+ * pos_global = rot_enu2global_^T * gnss_.blh + delta_pos_ (:206-207, host side), antlever = antlever_, std3 = gnss_.std.
+ * Applies to every following FLIVO_MODE_V1 update until cleared with pos_global = NULL (new_gnss_ = false). */
+int flivo_set_gnss(flivo_ctx* ctx, const double pos_global[3], const double antlever[3], const double std3[3]);
+
 /* LaserMapping::map_incremental (src/laser_mapping.cpp:329-389, USE_ikdtree branch :384): world-transform the
  * uploaded scan with `st` on the device and Add_Points(..., true) without a host round trip.
  * iVox mode: the other branch of the same function (:340-387): per point, from the neighbours cached by the last

@@ -123,6 +123,10 @@ void orc_ivox_knn(orc_ivox*, const float* q_xyz, size_t nq, int k, double max_ra
 void orc_ivox_map_filter(const float* world_xyz, size_t n, const float* near_xyz, const int32_t* near_cnt,
                          double filter_size_map_min, uint8_t* flag_out);
 
+// GNSSProcessing::computeH (src/GNSS_Processing.cpp:204-237): the 6x6 / 6 block added to HPH / HPL (src/laser_mapping.cpp:612-617)
+void orc_gnss_block(const double* rot, const double* pos, const double* gnss_pos, const double* antlever,
+                    const double* std3, double* HTH36, double* HTL6);
+
 #ifdef __cplusplus
 }
 #endif

@@ -210,3 +210,29 @@ extern "C" void orc_ivox_map_filter(const float* world_xyz, size_t n, const floa
         flag_out[i] = (uint8_t)flag;
     }
 }
+
+// GNSSProcessing::computeH (src/GNSS_Processing.cpp:204-237), the block LaserMapping::h_share_model adds to HPH / HPL
+// (src/laser_mapping.cpp:612-617).  gnss_pos is already in the global frame (:206-207).  rot row-major.
+// HTH 6x6 row-major, HTL 6; both zero when |error| > 2 (:221-222).
+extern "C" void orc_gnss_block(const double* rot, const double* pos, const double* gnss_pos, const double* antlever,
+                               const double* std3, double* HTH36, double* HTL6) {
+    for (int i = 0; i < 36; ++i) HTH36[i] = 0.0;
+    for (int i = 0; i < 6; ++i) HTL6[i] = 0.0;
+    const double* l = antlever;
+    const double K[9] = {0.0, -l[2], l[1], l[2], 0.0, -l[0], -l[1], l[0], 0.0};   // SKEW_SYM_MATRX, include/so3_math.h:9
+    double H[3][6], err[3];
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) {
+            H[r][c] = rot[r * 3] * K[c] + rot[r * 3 + 1] * K[3 + c] + rot[r * 3 + 2] * K[6 + c];   // rot_end * [antlever]x
+            H[r][3 + c] = (r == c) ? -1.0 : 0.0;
+        }
+        err[r] = gnss_pos[r] - pos[r] + (rot[r * 3] * l[0] + rot[r * 3 + 1] * l[1] + rot[r * 3 + 2] * l[2]);
+    }
+    if (sqrt(err[0] * err[0] + err[1] * err[1] + err[2] * err[2]) > 2.0) return;
+    const double w[3] = {1.0 / std3[0], 1.0 / std3[1], 100.0 / std3[2]};
+    for (int a = 0; a < 6; ++a) {
+        for (int b = 0; b < 6; ++b)
+            for (int k = 0; k < 3; ++k) HTH36[a * 6 + b] += H[k][a] * w[k] * H[k][b];
+        for (int k = 0; k < 3; ++k) HTL6[a] += H[k][a] * w[k] * err[k];
+    }
+}

@@ -122,6 +122,7 @@ def lib():
         L.orc_ivox_knn.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_int, C.c_double, i32p, f32p, f32p, i32p,
                                    C.POINTER(C.c_int64)]
         L.orc_ivox_map_filter.argtypes = [f32p, C.c_size_t, f32p, i32p, C.c_double, u8p]
+        L.orc_gnss_block.argtypes = [f64p, f64p, f64p, f64p, f64p, f64p, f64p]
         _lib = L
     return _lib
 
@@ -323,6 +324,15 @@ def ivox_map_filter(world_xyz, near_xyz, near_cnt, filter_size_map_min):
     flags = np.empty(w.shape[0], np.uint8)
     lib().orc_ivox_map_filter(w, w.shape[0], _c(near_xyz, np.float32), _c(near_cnt, np.int32), float(filter_size_map_min), flags)
     return flags
+
+
+def gnss_block(st, gnss_pos, antlever, std):
+    """Restated GNSSProcessing::computeH -> (HTH 6x6, HTL 6) at state st."""
+    x = st.as_array()
+    HTH, HTL = np.zeros(36), np.zeros(6)
+    lib().orc_gnss_block(_c(x[0:9], np.float64), _c(x[9:12], np.float64), _c(gnss_pos, np.float64), _c(antlever, np.float64),
+                         _c(std, np.float64), HTH, HTL)
+    return HTH.reshape(6, 6), HTL
 
 
 class RefTree:

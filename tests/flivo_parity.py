@@ -52,7 +52,7 @@ def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids
 
 
 def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.001, limit=None, force_search=False,
-                  ivox=None):
+                  ivox=None, gnss=None):
     """The whole iterated update with the restated reference loop (V3: esekfom.hpp:1619-1928; V1:
     src/laser_mapping.cpp:165-242).  Returns dict(x, P, trips, searches, dx (per trip), masks, eff, ids)."""
     limit = np.full(23, 0.001) if limit is None else np.asarray(limit, float)
@@ -74,6 +74,11 @@ def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.0
         searches += int(do_search)
         if mode == orc.MODE_V1:
             HPH, HPL = orc.repack_v1(out["HTH"], out["HTz"], laser_point_cov)
+            if gnss is not None:                      # src/laser_mapping.cpp:612-617
+                gH, gL = orc.gnss_block(x, *gnss)
+                HPH = HPH.copy(); HPL = HPL.copy()
+                HPH[:6, :6] += gH
+                HPL[:6] += gL
             r = orc.solve_v1(x, x_prop, P, HPH, HPL, it, max_iter, rematch)
             rematch, search, stopped = r["rematch"], r["search_next"], r["stopped"]
             dxs.append(r["solution"].copy())

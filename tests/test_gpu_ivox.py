@@ -177,3 +177,42 @@ def test_ivox_dropin_class_cpp(pkg, tmp_path):
     assert ties == 0 and single_ok == 1
     assert n_pts == len(pts) and n_grids == v.num_grids()
     assert np.array_equal(cnt, np.maximum(ocnt, 0)) and np.array_equal(ids, oid) and np.array_equal(sqd, osq)
+
+
+@pytest.mark.parametrize("ivox_nearby", [0, 19])
+def test_gnss_block_folded_into_v1_update(pkg, ivox_nearby):
+    """src/laser_mapping.cpp:612-617: the GNSS position block is added to HPH / HPL on every trip, on the device."""
+    w = _dense_world(35, 80000, 0.2) if ivox_nearby else scenes.make_world(seed=35, n_points=60000, ds=0.5)
+    scan = scenes.make_scan(w, seed=36, n_points=5000)
+    lever, std = np.array([0.05, -0.1, 0.3]), np.array([0.05, 0.05, 0.1])
+    xt = np.array(scan["x_true"], float)
+    gpos = xt[9:12] - xt[0:9].reshape(3, 3) @ lever + np.array([0.04, -0.03, 0.02])   # antenna fix with a few cm of error
+    v = None
+    P0 = np.eye(18) * 1e-4
+    with pkg.Flivo(downsample_size=0.5, initial_points=len(w["points"]), sort_scan=True, ivox_nearby=ivox_nearby) as F:
+        if ivox_nearby:
+            v = orc.OracleIVox(0.5, ivox_nearby)
+            v.add_points(w["points"])
+            F.AddPoints(w["points"])
+        else:
+            F.Build(w["points"])
+        F.scan_upload(scan["body"])
+        cfg = pkg.make_cfg(mode=pkg.MODE_V1, max_iter=4, laser_point_cov=0.001)
+        x_plain, _, rep0 = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+        F.set_gnss(gpos, lever, std)
+        xg, Pg, rep = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+        o = par.oracle_update(w["points"], scan["body"], scan["x_prior"], P0, orc.MODE_V1, 4, 0.001, None, False, ivox=v,
+                              gnss=(gpos, lever, std))
+        assert rep.trips == o["trips"] and rep.searches == o["searches"] and rep.n_eff == o["n_eff"]
+        assert np.abs(np.array(rep.dx_last[:18]) - o["dx"][-1][:18]).max() <= par.DX_ATOL
+        assert np.abs(xg.as_array() - o["x"]).max() <= 1e-6
+        assert np.abs(Pg - o["P"]).max() / np.abs(o["P"]).max() <= 1e-6
+        assert np.abs(xg.as_array() - x_plain.as_array()).max() > 1e-7, "the GNSS block changed nothing"
+        # V3 ignores it (the block belongs to the compiled 18-DOF path); clearing restores the plain result
+        F.set_gnss(None)
+        x_again, _, _ = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+        assert np.array_equal(x_again.as_array(), x_plain.as_array())
+        # an observation farther than 2 m from the state is dropped (src/GNSS_Processing.cpp:221-222)
+        F.set_gnss(gpos + np.array([5.0, 0, 0]), lever, std)
+        x_far, _, _ = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+        assert np.array_equal(x_far.as_array(), x_plain.as_array())

@@ -113,3 +113,27 @@ def test_ivox_map_filter_rule():
     near[4, 0] = [0.25, 0.25, 0.25]; cnt[4] = 2
     flags = orc.ivox_map_filter(pw, near, cnt, fs)
     assert list(flags) == [1, 2, 0, 1, 1]
+
+
+def test_gnss_block_matches_numpy():
+    """Restated GNSSProcessing::computeH (src/GNSS_Processing.cpp:204-237) against the matrix formula in numpy."""
+    rng = np.random.default_rng(7)
+    a = rng.normal(0, 0.4, 3)
+    th = np.linalg.norm(a)
+    Kx = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    R = np.eye(3) + np.sin(th) / th * Kx + (1 - np.cos(th)) / th ** 2 * Kx @ Kx
+    pos = rng.normal(0, 5, 3)
+    lever = np.array([0.1, -0.2, 0.5])
+    std = np.array([0.02, 0.03, 0.05])
+    gpos = pos - R @ lever + np.array([0.3, -0.1, 0.2])
+    st = orc.State.make(R=R, t=pos)
+    H, L = orc.gnss_block(st, gpos, lever, std)
+    S = np.array([[0, -lever[2], lever[1]], [lever[2], 0, -lever[0]], [-lever[1], lever[0], 0]])
+    Hsub = np.hstack([R @ S, -np.eye(3)])
+    W = np.diag([1 / std[0], 1 / std[1], 100 / std[2]])
+    err = gpos - pos + R @ lever
+    assert np.allclose(H, Hsub.T @ W @ Hsub, rtol=1e-13, atol=1e-12)
+    assert np.allclose(L, Hsub.T @ W @ err, rtol=1e-13, atol=1e-12)
+    # observation farther than 2 m from the state: ignored (:221-222)
+    H, L = orc.gnss_block(st, gpos + np.array([2.5, 0, 0]), lever, std)
+    assert not H.any() and not L.any()
