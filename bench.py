@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument("--cell-ratio", type=int, default=0, help="search cell edge / downsample size (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-map-add", action="store_true", help="skip the informational map_incremental timing (it grows the map)")
+    ap.add_argument("--no-ivox", action="store_true", help="skip the informational iVox-mode (SURVEY 8f rank 4) timing")
     ap.add_argument("--no-frontend", action="store_true", help="skip the informational front-end (undistort + voxel grid) timing")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5)")
@@ -401,6 +402,54 @@ def run_flivo(args, rank, world_size, local_rank):
             ms.append((time.perf_counter() - t0) * 1e3)
         map_add = {"ms_per_scan_median": float(np.median(ms)), "ms_per_scan": [float(v) for v in ms], "points_added": [int(a) for a in added],
                    "scan_points": int(pts_per_scan), "note": "wall clock around flivo_map_add_scan + sync; the map grows by the added points"}
+    # ---- iVox-compatible mode (the local map the reference compiles by default), informational:
+    # the same scans, V1 (compiled 18-DOF) update, against an iVox map (resolution 0.5, NEARBY18) holding the map points
+    # within lidar range of the sensor; the CPU arm is the restated IVox + loop on all host threads (parity unpinned).
+    ivox = None
+    if rank == 0 and world_size == 1 and not args.no_ivox:
+        import flivo_parity as par
+        from oracle import pyoracle as orc
+        near = wxyz_host[(np.abs(wxyz_host[:, 0]) < 130.0) & (np.abs(wxyz_host[:, 1]) < 130.0)]
+        res, nearby = 0.5, 19
+        Fv = pkg.Flivo(device=local_rank, downsample_size=res, initial_points=len(near), sort_scan=bool(args.sort_scan), ivox_nearby=nearby)
+        Fv.AddPoints(near)
+        Fv.sync()
+        P18 = np.eye(18) * 1e-4
+        cfg1 = pkg.make_cfg(mode=pkg.MODE_V1, max_iter=MAX_ITER, laser_point_cov=LASER_POINT_COV)
+        extv = torch.cuda.ExternalStream(Fv.stream(), device=dev)
+        ms, trips_v, rep_v, x_v = [], 0, None, None
+        for k in range(args.warmup + min(args.steps, 10)):
+            i = k % S
+            flush.zero_()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(extv)
+            Fv.scan_set_device(dev_scans[i].data_ptr(), dev_scans[i].shape[0])
+            x_v, _, rep_v = Fv.iekf_update(pkg.State.from_array(scans[i]["x_prior"]), P18, cfg1)
+            e1.record(extv)
+            torch.cuda.synchronize()
+            if k >= args.warmup:
+                ms.append(e0.elapsed_time(e1)); trips_v += rep_v.trips
+        i_last = (args.warmup + min(args.steps, 10) - 1) % S
+        t0 = time.perf_counter()
+        n_add = Fv.map_add_scan(x_v)
+        Fv.sync()
+        add_ms = (time.perf_counter() - t0) * 1e3
+        ivox = {"resolution": res, "nearby": "NEARBY18", "map_points": int(len(near)), "mode": "V1", "ms_per_update_median": float(np.median(ms)),
+                "points_per_sec": float(pts_per_scan * trips_v / (sum(ms) * 1e-3)), "trips_per_update": trips_v / len(ms),
+                "map_incremental_ms": add_ms, "map_incremental_added": int(n_add)}
+        if not args.no_cpu_baseline:
+            v = orc.OracleIVox(res, nearby)
+            t0 = time.perf_counter(); v.add_points(near); t_build = time.perf_counter() - t0
+            body = host_xyz[i_last]
+            t0 = time.perf_counter()
+            o = par.oracle_update(None, body, scans[i_last]["x_prior"], P18, orc.MODE_V1, MAX_ITER, LASER_POINT_COV, None, False, ivox=v)
+            t_cpu = time.perf_counter() - t0
+            ivox.update(cpu_ms_per_update=t_cpu * 1e3, cpu_map_build_s=t_build, cpu_kind="port (restated IVox + loop, OpenMP search, %d threads)" % (os.cpu_count() or 1),
+                        parity={"x_max_abs_diff": float(np.abs(x_v.as_array() - o["x"]).max()), "n_eff_gpu": int(rep_v.n_eff), "n_eff_cpu": int(o["n_eff"]),
+                                "trips_gpu": int(rep_v.trips), "trips_cpu": int(o["trips"]), "distance_ties": int(o["ties"])})
+            del v
+        del Fv
     # sharded mode: the posterior of the sharded update must be the single-GPU posterior of the whole scan
     shard_check = None
     if shard:
@@ -424,7 +473,7 @@ def run_flivo(args, rank, world_size, local_rank):
     return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
-                trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add,
+                trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add, ivox=ivox,
                 search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
@@ -515,7 +564,7 @@ def main():
                                      "map replica + own scans per rank, no collective")},
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
-            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "frontend": r["frontend"], "map_add": r["map_add"],
+            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
         }
         print(json.dumps(line), file=out, flush=True)
