@@ -178,12 +178,14 @@ static int host_threads() {
         if (e) {
             t = atoi(e);
         } else {
-            // up to 8 repack threads, but never more than this process's share of the host when several ranks
+            // up to 16 repack threads (the repack is host-memory bound: a 260 k-point 48-byte AoS scan stages in ~125 us at
+            // 16 threads, ~220 us at 8; a single parallel region with a copy-issuing thread was measured slower than
+            // this chunk loop: profiles/r1_ab_launch_structure.txt), but never more than this process's share of the host when several ranks
             // (one per GPU, LOCAL_WORLD_SIZE of torchrun) stage scans at the same time: oversubscribed OpenMP
             // teams spin against each other.  (The reference's own loop runs MP_PROC_NUM = 4, CMakeLists.txt:33-36.)
             const char* lw = getenv("LOCAL_WORLD_SIZE");
             const int ranks = lw ? std::max(1, atoi(lw)) : 1;
-            t = std::min(8, std::max(1, omp_get_num_procs() / ranks));
+            t = std::min(16, std::max(1, omp_get_num_procs() / ranks));
         }
         if (t < 1) t = 1;
         if (t > omp_get_num_procs()) t = omp_get_num_procs();
