@@ -373,6 +373,18 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     stamp(S, ctl, 0);
     if (S.phase != SOLVE_PHASE_REDUCE_ONLY && ctl->stopped) return;
 
+    // the state, P and the state-only half prepared by k_solve_pre do not depend on the sums: their global loads are
+    // issued here, ahead of the reduction, and land in registers while the group records are being summed
+    const int mode = S.job->mode;
+    const int n = (mode == 1) ? 18 : 23;
+    double r_P = 0.0, r_x = 0.0, r_xp = 0.0, r_dx = 0.0;
+    if (S.phase != SOLVE_PHASE_REDUCE_ONLY) {
+        const double* Psrc = (mode == 1) ? S.P_prop : S.pre->Pt;
+        if (tid < n * n) r_P = Psrc[tid];
+        if (tid < 36) { r_x = S.x[tid]; r_xp = S.x_prop[tid]; }
+        if (tid < 23) r_dx = S.pre->dxnew[tid];
+    }
+
     // ---- 0. normal equations -------------------------------------------------------------------------
     if (S.phase == SOLVE_PHASE_PEER) {
         // ---- fused reduce + exchange over peer memory ------------------------------------------------------
@@ -440,13 +452,12 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         s_H[tid] = s_sum[t];
     }
     if (tid < 12) s_z[tid] = s_sum[78 + tid];
-    if (tid < 36) { s_x[tid] = S.x[tid]; s_xp[tid] = S.x_prop[tid]; }
-    const int mode = S.job->mode;
-    const int n = (mode == 1) ? 18 : 23;
+    if (tid < 36) { s_x[tid] = r_x; s_xp[tid] = r_xp; }
     {   // the state-only half of this trip was prepared by k_solve_pre while the search / fused kernels ran
         const double* Psrc = (mode == 1) ? S.P_prop : S.pre->Pt;
-        for (int e = tid; e < n * n; e += NT) s_P[e] = Psrc[e];
-        if (tid < 23) s_dxnew[tid] = S.pre->dxnew[tid];
+        if (tid < n * n) s_P[tid] = r_P;
+        for (int e = tid + NT; e < n * n; e += NT) s_P[e] = Psrc[e];   // (only when launched with fewer than n*n threads)
+        if (tid < 23) s_dxnew[tid] = r_dx;
     }
     __syncthreads();
     if (tid == 0) {
