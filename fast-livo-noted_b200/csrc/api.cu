@@ -12,6 +12,7 @@
 #include <cub/cub.cuh>
 #include <dlfcn.h>
 #include <omp.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <math.h>
 #include <string.h>
@@ -601,7 +602,13 @@ static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool externa
         float inv_edge = 1.0f / ctx->map.view().cell_edge;
         k_scan_keys<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, n, inv_edge, ctx->d_skey_a, ctx->d_sidx_a);
         size_t tmp = ctx->cub_bytes;
-        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, 6, 30, ctx->stream));   // 10 bits per axis, the lowest 2 per axis left unsorted: locality only
+        static int sb0 = -1, sb1 = -1;
+        if (sb0 < 0) { const char* e = getenv("FLIVO_SORT_BITS"); if (!e || sscanf(e, "%d,%d", &sb0, &sb1) != 2) { sb0 = 6; sb1 = 22; } }
+        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, sb0, sb1, ctx->stream));
+        // 16 of the Morton bits = two radix passes: cell bits 2..6 of x and y, 2..7 of z.  The two lowest bits per axis carry no
+        // locality a 128-point tile can use; the bits above repeat every 51 m (102 m in z), so a tile may mix two or three
+        // far-apart regions, which costs less than a third pass (0.5257 vs 0.5279 ms per 260 k-point update, 0.325 vs 0.334 at
+        // 24 k points; dropping fine bits instead — 9..25 — loses 8 us of search time).  FLIVO_SORT_BITS=lo,hi overrides.
         k_gather4<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, ctx->d_perm, n, ctx->d_body);
         CKC(cudaGetLastError());
     }
