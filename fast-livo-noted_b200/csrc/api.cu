@@ -260,9 +260,14 @@ __global__ void k_scan_keys(const float4* __restrict__ body, size_t n, float inv
     keys[i] = (spread21(ux) << 2) | (spread21(uy) << 1) | spread21(uz);
     idx[i] = (unsigned int)i;
 }
-__global__ void k_gather4(const float4* __restrict__ in, const unsigned int* __restrict__ perm, size_t n, float4* __restrict__ out) {
+// gather the scan into processing order and (when the arrays are given) reset the per-point flags of a fresh scan in
+// the same pass: sel = 1, eff = 0, pflags = 0 (see finish_scan)
+__global__ void k_gather4(const float4* __restrict__ in, const unsigned int* __restrict__ perm, size_t n, float4* __restrict__ out,
+                          unsigned char* __restrict__ sel, unsigned char* __restrict__ eff, unsigned char* __restrict__ pflags) {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i < n) out[i] = in[perm[i]];
+    if (i >= n) return;
+    out[i] = in[perm[i]];
+    if (sel) { sel[i] = 1; eff[i] = 0; pflags[i] = 0; }
 }
 // out[perm[i]*elems + e] = in[i*elems + e]   (processing order -> caller's order); perm == nullptr: identity
 template <class T>
@@ -609,16 +614,19 @@ static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool externa
         // locality a 128-point tile can use; the bits above repeat every 51 m (102 m in z), so a tile may mix two or three
         // far-apart regions, which costs less than a third pass (0.5257 vs 0.5279 ms per 260 k-point update, 0.325 vs 0.334 at
         // 24 k points; dropping fine bits instead — 9..25 — loses 8 us of search time).  FLIVO_SORT_BITS=lo,hi overrides.
-        k_gather4<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, ctx->d_perm, n, ctx->d_body);
+        k_gather4<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, ctx->d_perm, n, ctx->d_body, ctx->d_sel, ctx->d_eff, ctx->d_pflags);
         CKC(cudaGetLastError());
     }
     ctx->scan_external = external;
     ctx->scan_sorted = sort;
     ctx->scan_n = n;
-    // point_selected_surf starts true (V3 global array semantics are re-established by the first search trip)
-    CKC(cudaMemsetAsync(ctx->d_sel, 1, n, ctx->stream));
-    CKC(cudaMemsetAsync(ctx->d_eff, 0, n, ctx->stream));
-    CKC(cudaMemsetAsync(ctx->d_pflags, 0, n, ctx->stream));   // no cached neighbours yet: a re-use trip before any search selects nothing
+    // point_selected_surf starts true (V3 global array semantics are re-established by the first search trip); no cached
+    // neighbours yet: a re-use trip before any search selects nothing.  (Sorted scans: done inside k_gather4.)
+    if (!sort) {
+        CKC(cudaMemsetAsync(ctx->d_sel, 1, n, ctx->stream));
+        CKC(cudaMemsetAsync(ctx->d_eff, 0, n, ctx->stream));
+        CKC(cudaMemsetAsync(ctx->d_pflags, 0, n, ctx->stream));
+    }
     // iVox mode reads the cached count outside the search (empty-result rule of GetClosestPoint, map_incremental's add rule)
     if (ctx->opt.ivox_nearby) {
         CKC(cudaMemsetAsync(ctx->d_near_meta, 0, n * sizeof(float2), ctx->stream));
