@@ -63,6 +63,17 @@ struct DevBlock {
 
 constexpr int SSTAMP_CTAS = 4096;
 
+// Per-scan scalars of the staging sequence (keys -> radix sort -> gather), resident in HBM so that the captured graph of
+// the sequence never changes its kernel parameters: a call rewrites this block through the graph's own H2D copy node.
+struct ScanJob {
+    const float4* src;    // the scan in the caller's order
+    unsigned int n;       // scan points
+    unsigned int n_pad;   // items handed to the radix sort: n rounded up to SCAN_PAD (padding keys sort last)
+    float inv_edge;
+    int pad;
+};
+constexpr unsigned int SCAN_PAD = 8192;
+
 struct flivo_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -91,6 +102,12 @@ struct flivo_ctx {
     unsigned int* d_sidx_a = nullptr;
     void* d_cub = nullptr;
     size_t cub_bytes = 0;
+    ScanJob* d_sjob = nullptr;          // staging scalars (device) and their pinned mirror
+    ScanJob* h_sjob = nullptr;
+    cudaGraphExec_t sort_exec = nullptr;   // captured staging sequence, keyed by (n_pad, sort bits)
+    unsigned int sort_npad = 0;
+    cudaEvent_t sjob_ev = nullptr;      // the last staging graph has consumed h_sjob
+    bool sjob_pending = false;
     float4* d_near = nullptr;
     float2* d_near_meta = nullptr;
     unsigned char *d_sel = nullptr, *d_eff = nullptr;
@@ -249,25 +266,28 @@ __device__ __forceinline__ unsigned long long spread21(unsigned int v) {
     x = (x | x << 2) & 0x1249249249249249ull;
     return x;
 }
-__global__ void k_scan_keys(const float4* __restrict__ body, size_t n, float inv_edge, unsigned long long* keys, unsigned int* idx) {
-    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float4 p = body[i];
+__global__ void k_scan_keys(const ScanJob* __restrict__ J, unsigned long long* keys, unsigned int* idx) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const unsigned n = J->n;
+    if (i >= J->n_pad) return;
+    idx[i] = (unsigned int)i;
+    if (i >= n) { keys[i] = 0xFFFFFFFFFFFFFFFFull; return; }   // padding: largest key, and (stable sort) behind every real point
+    const float inv_edge = J->inv_edge;
+    float4 p = J->src[i];
     float fx = fminf(fmaxf(floorf(p.x * inv_edge), -1048575.f), 1048575.f);
     float fy = fminf(fmaxf(floorf(p.y * inv_edge), -1048575.f), 1048575.f);
     float fz = fminf(fmaxf(floorf(p.z * inv_edge), -1048575.f), 1048575.f);
     unsigned int ux = (unsigned int)((int)fx + (1 << 20)), uy = (unsigned int)((int)fy + (1 << 20)), uz = (unsigned int)((int)fz + (1 << 20));
     keys[i] = (spread21(ux) << 2) | (spread21(uy) << 1) | spread21(uz);
-    idx[i] = (unsigned int)i;
 }
 // gather the scan into processing order and (when the arrays are given) reset the per-point flags of a fresh scan in
 // the same pass: sel = 1, eff = 0, pflags = 0 (see finish_scan)
-__global__ void k_gather4(const float4* __restrict__ in, const unsigned int* __restrict__ perm, size_t n, float4* __restrict__ out,
+__global__ void k_gather4(const ScanJob* __restrict__ J, const unsigned int* __restrict__ perm, float4* __restrict__ out,
                           unsigned char* __restrict__ sel, unsigned char* __restrict__ eff, unsigned char* __restrict__ pflags) {
-    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    out[i] = in[perm[i]];
-    if (sel) { sel[i] = 1; eff[i] = 0; pflags[i] = 0; }
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= J->n) return;
+    out[i] = J->src[perm[i]];
+    sel[i] = 1; eff[i] = 0; pflags[i] = 0;
 }
 // out[perm[i]*elems + e] = in[i*elems + e]   (processing order -> caller's order); perm == nullptr: identity
 template <class T>
@@ -346,6 +366,9 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     ctx->d_x = ctx->d_blk->x; ctx->d_xprop = ctx->d_blk->x_prop; ctx->d_Pprop = ctx->d_blk->P_prop; ctx->d_Pout = ctx->d_blk->P_out;
     ctx->d_sum = ctx->d_blk->sum;
     CKC(cudaMallocHost(&ctx->h_small, 2048 * sizeof(double)));
+    CKC(cudaMalloc(&ctx->d_sjob, sizeof(ScanJob)));
+    CKC(cudaMallocHost(&ctx->h_sjob, sizeof(ScanJob)));
+    CKC(cudaEventCreateWithFlags(&ctx->sjob_ev, cudaEventDisableTiming));
     for (auto& e : ctx->ev) CKC(cudaEventCreate(&e));
     CKC(cudaEventCreateWithFlags(&ctx->stage_ev, cudaEventDisableTiming));
     CKC(cudaStreamSynchronize(ctx->stream));
@@ -369,6 +392,7 @@ extern "C" int flivo_ctx_create(int device, const flivo_options* opt, flivo_ctx*
 }
 
 static void free_scan(flivo_ctx* ctx) {
+    if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; ctx->sort_npad = 0; }   // holds the old pointers
     cudaFree(ctx->d_body_own);
     cudaFree(ctx->d_body_in); cudaFree(ctx->d_perm); cudaFree(ctx->d_skey_a); cudaFree(ctx->d_skey_b); cudaFree(ctx->d_sidx_a);
     cudaFree(ctx->d_cub); cudaFree(ctx->d_near); cudaFree(ctx->d_near_meta); cudaFree(ctx->d_sel); cudaFree(ctx->d_eff);
@@ -400,6 +424,9 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     if (ctx->h_blk) cudaFreeHost(ctx->h_blk);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    cudaFree(ctx->d_sjob);
+    if (ctx->h_sjob) cudaFreeHost(ctx->h_sjob);
+    if (ctx->sjob_ev) cudaEventDestroy(ctx->sjob_ev);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->stage_ev) cudaEventDestroy(ctx->stage_ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -567,6 +594,7 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
     if (n > ctx->scan_cap) {
         free_scan(ctx);
         size_t cap = std::max<size_t>(n + n / 8, 1u << 15);
+        cap = ((cap + SCAN_PAD - 1) / SCAN_PAD) * SCAN_PAD;   // the staging sort runs on n rounded up to SCAN_PAD
         size_t units = (cap + UNIT_POINTS - 1) / UNIT_POINTS, groups = (units + GROUP_UNITS - 1) / GROUP_UNITS;
         CKC(cudaMalloc(&ctx->d_body_in, cap * sizeof(float4)));
         CKC(cudaMalloc(&ctx->d_body_own, cap * sizeof(float4)));
@@ -603,19 +631,43 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
 static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool external) {
     const bool sort = ctx->opt.sort_scan != 0;
     if (sort) {
+        // keys -> radix sort -> gather as ONE captured graph (H2D of the ScanJob block, k_scan_keys, the CUB kernels,
+        // k_gather4): a single launch instead of seven, no launch gaps between the short kernels.  The graph depends only
+        // on the padded item count and the device pointers of this context; the scan pointer and n travel in ScanJob.
         ctx->d_body = ctx->d_body_own;
-        float inv_edge = 1.0f / ctx->map.view().cell_edge;
-        k_scan_keys<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, n, inv_edge, ctx->d_skey_a, ctx->d_sidx_a);
-        size_t tmp = ctx->cub_bytes;
         static int sb0 = -1, sb1 = -1;
         if (sb0 < 0) { const char* e = getenv("FLIVO_SORT_BITS"); if (!e || sscanf(e, "%d,%d", &sb0, &sb1) != 2) { sb0 = 6; sb1 = 22; } }
-        CKC(cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n, sb0, sb1, ctx->stream));
         // 16 of the Morton bits = two radix passes: cell bits 2..6 of x and y, 2..7 of z.  The two lowest bits per axis carry no
         // locality a 128-point tile can use; the bits above repeat every 51 m (102 m in z), so a tile may mix two or three
         // far-apart regions, which costs less than a third pass (0.5257 vs 0.5279 ms per 260 k-point update, 0.325 vs 0.334 at
         // 24 k points; dropping fine bits instead — 9..25 — loses 8 us of search time).  FLIVO_SORT_BITS=lo,hi overrides.
-        k_gather4<<<nblk(n, 256), 256, 0, ctx->stream>>>(src, ctx->d_perm, n, ctx->d_body, ctx->d_sel, ctx->d_eff, ctx->d_pflags);
-        CKC(cudaGetLastError());
+        const unsigned n_pad = (unsigned)(((n + SCAN_PAD - 1) / SCAN_PAD) * SCAN_PAD);
+        if (ctx->sjob_pending) { CKC(cudaEventSynchronize(ctx->sjob_ev)); ctx->sjob_pending = false; }
+        ScanJob* J = ctx->h_sjob;
+        J->src = src; J->n = (unsigned)n; J->n_pad = n_pad; J->inv_edge = 1.0f / ctx->map.view().cell_edge; J->pad = 0;
+        if (!ctx->sort_exec || ctx->sort_npad != n_pad) {
+            if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; }
+            cudaGraph_t g = nullptr;
+            CKC(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+            cudaError_t ce = cudaMemcpyAsync(ctx->d_sjob, ctx->h_sjob, sizeof(ScanJob), cudaMemcpyHostToDevice, ctx->stream);
+            k_scan_keys<<<nblk(n_pad, 256), 256, 0, ctx->stream>>>(ctx->d_sjob, ctx->d_skey_a, ctx->d_sidx_a);
+            size_t tmp = ctx->cub_bytes;
+            if (ce == cudaSuccess) ce = cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n_pad, sb0, sb1, ctx->stream);
+            k_gather4<<<nblk(n_pad, 256), 256, 0, ctx->stream>>>(ctx->d_sjob, ctx->d_perm, ctx->d_body, ctx->d_sel, ctx->d_eff, ctx->d_pflags);
+            cudaError_t ce2 = cudaStreamEndCapture(ctx->stream, &g);
+            if (ce != cudaSuccess || ce2 != cudaSuccess) {
+                if (g) cudaGraphDestroy(g);
+                ctx->err = std::string("capture of the scan staging graph: ") + cudaGetErrorString(ce != cudaSuccess ? ce : ce2);
+                return FLIVO_E_CUDA;
+            }
+            ce = cudaGraphInstantiate(&ctx->sort_exec, g, 0);
+            cudaGraphDestroy(g);
+            if (ce != cudaSuccess) { ctx->sort_exec = nullptr; ctx->err = std::string("cudaGraphInstantiate (scan staging): ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
+            ctx->sort_npad = n_pad;
+        }
+        CKC(cudaGraphLaunch(ctx->sort_exec, ctx->stream));
+        CKC(cudaEventRecord(ctx->sjob_ev, ctx->stream));
+        ctx->sjob_pending = true;
     }
     ctx->scan_external = external;
     ctx->scan_sorted = sort;
@@ -808,6 +860,10 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
     cudaGraph_t g = nullptr;
     CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
     SolveParams S = S0;   // S0.phase: FULL, or PEER when the peer-memory exchange is attached
+    // the call's inputs (job + P_prop + x, from the pinned mirror), the control-block reset and, at the end, the results
+    // (x, P_out, ctl, stats -> pinned mirror) are nodes of the same graph: one launch per update
+    cudaError_t cio = cudaMemcpyAsync(ctx->d_blk, ctx->h_blk, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s);
+    launch_ctl_reset(ctx->d_blk->x, ctx->d_blk->x_prop, ctx->d_blk->P_prop, ctx->d_blk->P_out, ctx->d_ctl, ctx->d_stats, s);
     for (int t = 0; t < trips && t <= MAX_TRIPS; ++t) {
         // fork: the state-only half of the solve runs beside the search / fused kernels of the trip
         CKC(cudaEventRecord(ctx->ev_fork[t], s));
@@ -819,7 +875,10 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
         CKC(cudaStreamWaitEvent(s, ctx->ev_join[t], 0));
         launch_solve(S, s);
     }
+    if (cio == cudaSuccess)
+        cio = cudaMemcpyAsync(ctx->h_blk->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s);
     cudaError_t ce = cudaStreamEndCapture(s, &g);
+    if (ce == cudaSuccess && cio != cudaSuccess) { ce = cio; if (g) cudaGraphDestroy(g); g = nullptr; }
     if (ce != cudaSuccess) { ctx->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
     ce = cudaGraphInstantiate(&ctx->graph_exec, g, 0);
     cudaGraphDestroy(g);
@@ -844,8 +903,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     memset(h->P_prop, 0, sizeof(h->P_prop));
     memcpy(h->P_prop, Pm, sizeof(double) * np * np);
     CKC(cudaEventRecord(ctx->ev[0], s));
-    CKC(cudaMemcpyAsync(ctx->d_blk, h, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s));   // job + P_prop + x
-    launch_ctl_reset(ctx->d_blk->x, ctx->d_blk->x_prop, ctx->d_blk->P_prop, ctx->d_blk->P_out, ctx->d_ctl, ctx->d_stats, s);
+    bool use_graph = !timed && (!ctx->comm || ctx->peer_on);   // an NCCL call between the kernels is not captured
     FusedParams P = make_fused(ctx);
     if (timed && search_grid(ctx) <= SSTAMP_CTAS) {
         CKC(cudaMemsetAsync(ctx->d_sstamps, 0, ((size_t)SSTAMP_CTAS * 4 + 32) * sizeof(unsigned long long), s));
@@ -886,7 +944,6 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
         }
         return FLIVO_OK;
     };
-    bool use_graph = !timed && (!ctx->comm || ctx->peer_on);   // an NCCL call between the kernels is not captured
     if (use_graph) {
         // the sequence depends only on (P, S, grids, trips): replay the captured graph unless one of them changed
         S.phase = full_phase;
@@ -907,15 +964,17 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
         }
     }
     if (use_graph) {
-        CKC(cudaGraphLaunch(ctx->graph_exec, s));
+        CKC(cudaGraphLaunch(ctx->graph_exec, s));   // H2D of the inputs, control reset, the trips, D2H of the results
         launches = 1 + trips * 4;
     } else {
+        CKC(cudaMemcpyAsync(ctx->d_blk, h, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s));   // job + P_prop + x
+        launch_ctl_reset(ctx->d_blk->x, ctx->d_blk->x_prop, ctx->d_blk->P_prop, ctx->d_blk->P_out, ctx->d_ctl, ctx->d_stats, s);
         launches = 1;
         for (int t = 0; t < trips; ++t) { int rc = launch_trip(t, timed); if (rc != FLIVO_OK) return rc; }
     }
     CKC(cudaGetLastError());
     CKC(cudaEventRecord(ctx->ev[1 + 2 * trips], s));
-    CKC(cudaMemcpyAsync(h->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s));   // x, P_out, ctl, stats
+    if (!use_graph) CKC(cudaMemcpyAsync(h->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s));   // x, P_out, ctl, stats
     CKC(cudaStreamSynchronize(s));
     memcpy(inout, h->x, sizeof(flivo_state));
     memcpy(Pm, h->P_out, sizeof(double) * np * np);
@@ -964,6 +1023,7 @@ static int ivox_add_scan(flivo_ctx* ctx, int32_t* n_added) {
     size_t need = 0;
     CKC(cub::DeviceSelect::Flagged(nullptr, need, ctx->d_world, f_add, sel_add, d_counts, (int)n, ctx->stream));
     if (need > tmp) {
+        if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; ctx->sort_npad = 0; }   // captured with the old buffer
         cudaFree(ctx->d_cub); ctx->d_cub = nullptr; ctx->cub_bytes = 0;
         CKC(cudaMalloc(&ctx->d_cub, need + 256));
         ctx->cub_bytes = need + 256;
