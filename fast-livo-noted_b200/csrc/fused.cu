@@ -440,7 +440,11 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search
     __shared__ unsigned s_bid[SEARCH_WARPS][FAR_BATCH];
     __shared__ float2 s_bmeta[SEARCH_WARPS][FAR_BATCH];
     Ctl* ctl = P.ctl;
-    if (ctl->stopped || !(ctl->search != 0 || P.job->force_search != 0)) return;
+    {   // exit test of re-use trips and stopped trips: the three words are fetched by independent loads, one latency
+        const int2 ss = *reinterpret_cast<const int2*>(&ctl->search);   // {search, stopped}: the first two words of Ctl
+        const int fs = P.job->force_search;
+        if (ss.y || !(ss.x != 0 || fs != 0)) return;
+    }
     unsigned long long t_start = 0, t_p1 = 0;
     const bool stamp_on = P.search_stamps != nullptr && ctl->searches == 0;   // first search trip of the update
     if (stamp_on && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));

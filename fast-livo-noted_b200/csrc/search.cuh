@@ -540,7 +540,7 @@ __device__ __forceinline__ void ring_scan_cell(const MapView& m, uint2 ent, int 
 // seed (optional): the sorted best candidates already found in cube 1 by thread_knn5_shell — lane r < seed_cnt passes
 // candidate r as (distance bits, id, bucket address); the search then starts at cube 2 (or straight at the cube that
 // covers the seeded fifth distance) instead of scanning the 27 inner cells again.
-static __device__ __noinline__ int warp_knn5_rings(const MapView& m, float qx, float qy, float qz, uint32_t max_sq_bits, int lane,
+static __device__ __noinline__ int warp_knn5_rings(const MapView m /* by value: a reference would make every caller keep an addressable copy of its whole parameter block */, float qx, float qy, float qz, uint32_t max_sq_bits, int lane,
                                             Cand& out, unsigned& ncand, uint2* __restrict__ queue /* [RING_QCAP], this warp's */,
                                             int seed_cnt = -1, uint32_t seed_d = 0, uint32_t seed_id = 0, uint32_t seed_addr = 0,
                                             int* dbg = nullptr /* steps << 8 | last radius */) {
