@@ -205,11 +205,15 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
     __shared__ double s_state[36];
 
     Ctl* ctl = P.ctl;
-    if (ctl->stopped) return;
-    const int n_pts = P.job->n, mode = P.job->mode, aux_out = P.job->aux_out;
-    const bool search = (ctl->search != 0) || (P.job->force_search != 0);
+    // every word the prologue needs is fetched before the exit test: independent loads, one global-memory latency
+    const int2 ss = *reinterpret_cast<const int2*>(&ctl->search);   // {search, stopped}
+    const int n_pts = P.job->n, mode = P.job->mode, aux_out = P.job->aux_out, fsearch = P.job->force_search;
+    double st0 = 0.0;
+    if (threadIdx.x < 36) st0 = P.state[threadIdx.x];
+    if (ss.y) return;
+    const bool search = (ss.x != 0) || (fsearch != 0);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x < 36) s_state[threadIdx.x] = P.state[threadIdx.x];
+    if (threadIdx.x < 36) s_state[threadIdx.x] = st0;
     __syncthreads();
     const double* Rm = s_state;          // rot
     const double* tw = s_state + 9;      // pos
@@ -440,20 +444,23 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search
     __shared__ unsigned s_bid[SEARCH_WARPS][FAR_BATCH];
     __shared__ float2 s_bmeta[SEARCH_WARPS][FAR_BATCH];
     Ctl* ctl = P.ctl;
-    {   // exit test of re-use trips and stopped trips: the three words are fetched by independent loads, one latency
-        const int2 ss = *reinterpret_cast<const int2*>(&ctl->search);   // {search, stopped}: the first two words of Ctl
-        const int fs = P.job->force_search;
-        if (ss.y || !(ss.x != 0 || fs != 0)) return;
-    }
-    unsigned long long t_start = 0, t_p1 = 0;
-    const bool stamp_on = P.search_stamps != nullptr && ctl->searches == 0;   // first search trip of the update
-    if (stamp_on && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-    if (threadIdx.x < 24) s_state[threadIdx.x] = P.state[threadIdx.x];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // exit test of re-use trips and stopped trips; every word of the prologue is fetched ahead of it by independent
+    // loads (one global-memory latency instead of three)
+    const int2 ss = *reinterpret_cast<const int2*>(&ctl->search);   // {search, stopped}: the first two words of Ctl
+    const int fs = P.job->force_search;
     const int n = P.job->n;
-    const unsigned n_tiles = (unsigned)((n + SEARCH_THREADS - 1) / SEARCH_THREADS);
     const uint32_t max_sq_bits = P.job->max_sq_bits;
     const unsigned tag = ctl->epoch + 1u;
+    const int searches_before = ctl->searches;
+    double st0 = 0.0;
+    if (threadIdx.x < 24) st0 = P.state[threadIdx.x];
+    if (ss.y || !(ss.x != 0 || fs != 0)) return;
+    unsigned long long t_start = 0, t_p1 = 0;
+    const bool stamp_on = P.search_stamps != nullptr && searches_before == 0;   // first search trip of the update
+    if (stamp_on && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+    if (threadIdx.x < 24) s_state[threadIdx.x] = st0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned n_tiles = (unsigned)((n + SEARCH_THREADS - 1) / SEARCH_THREADS);
     unsigned nc = 0, nfar = 0;
 
     // ---- phase 1 ------------------------------------------------------------------------------------

@@ -371,19 +371,21 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
     Ctl* ctl = S.ctl;
     const int tid = threadIdx.x, NT = blockDim.x;
     stamp(S, ctl, 0);
-    if (S.phase != SOLVE_PHASE_REDUCE_ONLY && ctl->stopped) return;
-
-    // the state, P and the state-only half prepared by k_solve_pre do not depend on the sums: their global loads are
-    // issued here, ahead of the reduction, and land in registers while the group records are being summed
+    // the state, P and the state-only half prepared by k_solve_pre do not depend on the sums, nor on the exit test: all of
+    // their global loads are issued here, together with the test's own words, and land in registers while the group
+    // records are being summed (P: both flavours' sources are read, the mode picks one afterwards)
+    const int stopped = ctl->stopped;
     const int mode = S.job->mode;
-    const int n = (mode == 1) ? 18 : 23;
-    double r_P = 0.0, r_x = 0.0, r_xp = 0.0, r_dx = 0.0;
+    double r_P1 = 0.0, r_P3 = 0.0, r_x = 0.0, r_xp = 0.0, r_dx = 0.0;
     if (S.phase != SOLVE_PHASE_REDUCE_ONLY) {
-        const double* Psrc = (mode == 1) ? S.P_prop : S.pre->Pt;
-        if (tid < n * n) r_P = Psrc[tid];
+        if (tid < 18 * 18) r_P1 = S.P_prop[tid];
+        if (tid < 23 * 23) r_P3 = S.pre->Pt[tid];
         if (tid < 36) { r_x = S.x[tid]; r_xp = S.x_prop[tid]; }
         if (tid < 23) r_dx = S.pre->dxnew[tid];
     }
+    if (S.phase != SOLVE_PHASE_REDUCE_ONLY && stopped) return;
+    const int n = (mode == 1) ? 18 : 23;
+    const double r_P = (mode == 1) ? r_P1 : r_P3;
 
     // ---- 0. normal equations -------------------------------------------------------------------------
     if (S.phase == SOLVE_PHASE_PEER) {
