@@ -79,3 +79,34 @@ def test_two_contexts_are_independent(pkg, small_world, small_scan):
         xa2, _, ra2 = A.iekf_update(st, P0, mode=0, max_iter=4)
         assert np.array_equal(xa.as_array(), xa2.as_array()) and ra.n_eff == ra2.n_eff
         assert ra.n_eff != rb.n_eff                      # B's map is thinner
+
+
+def test_staging_graph_across_scan_sizes(pkg, small_world):
+    """The scan staging (keys, sort on n padded to 8192, gather) is a captured graph keyed by the padded size: sizes
+    inside one bucket, on its edges and in other buckets, uploads that are overwritten before any update, and both
+    upload paths (host AoS, device pointer) must give the posterior of the unsorted path."""
+    big = scenes.make_scan(small_world, seed=77, n_points=17000)
+    P0 = np.eye(23) * 1e-4
+    st = pkg.State.from_array(big["x_prior"])
+    with pkg.Flivo(downsample_size=small_world["ds"], sort_scan=True) as F, \
+            pkg.Flivo(downsample_size=small_world["ds"], sort_scan=False) as G:
+        F.Build(small_world["points"]); G.Build(small_world["points"])
+        for n in (3000, 8191, 8192, 8193, 3000, 17000, 16385, 1):
+            body = np.ascontiguousarray(big["body"][:n])
+            F.scan_upload(np.ascontiguousarray(big["body"][: max(1, n // 2)]))   # overwritten at once: never used
+            if n % 2:
+                F.scan_upload(body)
+                keep = None
+            else:
+                keep = torch.zeros((n, 4), dtype=torch.float32, device="cuda")
+                keep[:, :3] = torch.from_numpy(body).cuda()
+                torch.cuda.synchronize()
+                F.scan_set_device(keep.data_ptr(), n)
+            G.scan_upload(body)
+            xf, Pf, rf = F.iekf_update(st, P0, mode=0, max_iter=4)
+            xg, Pg, rg = G.iekf_update(st, P0, mode=0, max_iter=4)
+            assert (rf.trips, rf.searches, rf.n_eff) == (rg.trips, rg.searches, rg.n_eff), n
+            assert np.abs(xf.as_array() - xg.as_array()).max() < 1e-9, n
+            hf = F.h_share_model(st, 0, True, want=("nbr_id", "selected"))
+            hg = G.h_share_model(st, 0, True, want=("nbr_id", "selected"))
+            assert np.array_equal(hf["nbr_id"], hg["nbr_id"]) and np.array_equal(hf["selected"], hg["selected"]), n
