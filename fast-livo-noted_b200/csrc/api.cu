@@ -746,6 +746,10 @@ static int search_grid(flivo_ctx* ctx) {
     if (ctx->search_resident <= 0) ctx->search_resident = ctx->sm_count * search_ctas_per_sm();
     return std::max(1, std::min(((tiles + 255) / 256) * 256, ctx->search_resident));   // tiles are dealt dynamically
 }
+// scans whose tiles fill at most half of the resident CTAs leave the GPU under-filled: the search is then bound by each
+// thread's chain of dependent loads and the probe-all-blocks-at-once flavour wins (search.cuh, PAR_PROBES).  A function
+// of the search grid alone, so the captured graph's cache key covers it.
+static bool par_probes(flivo_ctx* ctx, int sgrid) { return sgrid * 2 <= ctx->search_resident; }
 static int fused_grid(flivo_ctx* ctx) {
     const int units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
     return std::max(1, std::min(((units + 255) / 256) * 256, ctx->sm_count * 8));
@@ -797,7 +801,7 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
     k_ctl_set<<<1, 32, 0, ctx->stream>>>(ctx->d_ctl, do_search ? 1 : 0);
     if (do_search) CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
     FusedParams P = make_fused(ctx);
-    if (do_search) launch_search(P, search_grid(ctx), ctx->stream);
+    if (do_search) { const int sg = search_grid(ctx); launch_search(P, sg, ctx->stream, par_probes(ctx, sg)); }
     launch_fused(P, fused_grid(ctx), ctx->stream);
     SolveParams S{};
     S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job; S.phase = SOLVE_PHASE_REDUCE_ONLY;
@@ -870,7 +874,7 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
         CKC(cudaStreamWaitEvent(ctx->side, ctx->ev_fork[t], 0));
         launch_solve_pre(S, ctx->side);
         CKC(cudaEventRecord(ctx->ev_join[t], ctx->side));
-        launch_search(P, sgrid, s);
+        launch_search(P, sgrid, s, par_probes(ctx, sgrid));
         launch_fused(P, fgrid, s);
         CKC(cudaStreamWaitEvent(s, ctx->ev_join[t], 0));
         launch_solve(S, s);
@@ -926,7 +930,7 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     auto launch_trip = [&](int t, bool with_events) -> int {
         launch_solve_pre(S, s);                 // plain launches: in line (the graph runs it on a parallel branch)
         if (with_events) CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
-        launch_search(P, sgrid, s);   // exits at once on re-use trips
+        launch_search(P, sgrid, s, par_probes(ctx, sgrid));   // exits at once on re-use trips
         launch_fused(P, fgrid, s);
         if (with_events) CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
         if (ctx->comm && !ctx->peer_on) {

@@ -437,6 +437,10 @@ __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) {
 //            cannot deadlock whatever the grid size.  Entries carry the epoch of the trip, so the list never needs
 //            clearing.  After FAR_BATCH finished queries the warp's lanes fit the planes of the batch, one lane each.
 // Exits at once on re-use trips (ctl->search == 0 and no force_search) and after the loop stopped.
+// IVOX: the iVox-compatible flavour (thread_knn5_ivox, no far phase) is a separate instantiation so that the exact-search
+// kernel does not carry its code: k_search is instruction-fetch sensitive (ncu: no_instruction stalls).
+// PAR: thread_knn5_shell<PAR_PROBES>, chosen by the launcher for scans that leave the GPU under-filled.
+template <bool IVOX, bool PAR>
 __global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search(FusedParams P) {
     __shared__ double s_state[24];
     __shared__ SearchSmem S;
@@ -484,13 +488,13 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search
             Top5 best;
             int cnt = 0;
             bool keep_old = false;
-            if (P.map.ivox) {
+            if (IVOX) {
                 thread_knn5_ivox(P.map, wx, wy, wz, IVOX_MAX_RANGE_SQ, best, cnt, nc);
                 // no candidate at all: GetClosestPoint returns before touching closest_pt (ivox3d.h:168-170), so the
                 // point keeps the neighbours of the previous search of this scan
                 keep_old = cnt == 0;
             } else {
-                fin = thread_knn5_shell(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, S.p1.idx + threadIdx.x, S.p1.gap + threadIdx.x, SEARCH_THREADS);
+                fin = thread_knn5_shell<PAR>(P.map, wx, wy, wz, max_sq_bits, best, cnt, nc, S.p1.idx + threadIdx.x, S.p1.gap + threadIdx.x, SEARCH_THREADS);
             }
             if (keep_old) {
             } else if (fin) {
@@ -531,6 +535,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search
 
     if (stamp_on && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_p1));
     unsigned nfar_done = 0;
+    if (!IVOX) {   // (the iVox search is always final: nothing is ever published to far_list)
     // ---- phase 2 (the barrier that ended phase 1 makes the shared buffers free) ---------------------------
     uint2* queue = S.p2.queue[warp];
     int nb = 0;
@@ -605,6 +610,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search
         for (int r = 0; r < 5; ++r) nbs[r] = S.p2.near[warp][lane][r];
         store_plane(P, (int)s_bid[warp][lane], nbs, __float_as_int(s_bmeta[warp][lane].x), s_bmeta[warp][lane].y);
     }
+    }   // !IVOX
     if (stamp_on) {
         __syncthreads();
         if (lane == 0 && nfar_done) atomicAdd(&P.search_stamps[blockIdx.x * 4 + 3], (unsigned long long)nfar_done);
@@ -739,14 +745,16 @@ __global__ void k_ivox_map_filter(const float4* __restrict__ body, int n, const 
 void launch_fused(const FusedParams& P, int grid, cudaStream_t stream) {
     k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P);
 }
-void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream) {
-    k_search<<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
+void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, bool par_probes) {
+    if (P.map.ivox) k_search<true, false><<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
+    else if (par_probes) k_search<false, true><<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
+    else k_search<false, false><<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
 }
 // CTAs of k_search that fit on one SM (its grid never needs to exceed the resident set: tiles are dealt dynamically)
 int search_tile_points() { return SEARCH_THREADS; }
 int search_ctas_per_sm() {
     int nb = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_search, SEARCH_THREADS, 0) != cudaSuccess || nb < 1) nb = 4;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_search<false, false>, SEARCH_THREADS, 0) != cudaSuccess || nb < 1) nb = 4;
     return nb;
 }
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
