@@ -318,20 +318,25 @@ struct Top5 {
     }
 };
 
+// 64-bit occupancy mask of the cells (x in xm) x (y in ym) x (z in zm) of one block, xm/ym/zm 4-bit masks
+// (cell_off layout: x<<4 | y<<2 | z).  Outer product by two multiplications: ym spread to one bit per nibble times zm gives
+// the 16-bit yz plane (the partial products occupy distinct nibbles, so no carries), xm spread to one bit per 16-bit lane
+// times that plane gives the block mask.
+__device__ __forceinline__ unsigned long long mask3(unsigned xm, unsigned ym, unsigned zm) {
+    unsigned ys = (ym | (ym << 6)) & 0x0303u;
+    ys = (ys | (ys << 3)) & 0x1111u;
+    const unsigned yz = ys * zm;
+    const unsigned long long xs = ((unsigned long long)xm * 0x0000200040008001ull) & 0x0001000100010001ull;
+    return xs * (unsigned long long)yz;
+}
+
 // bits of the cells of block (bx,by,bz) that lie in [cq-1, cq+1]^3 (cell_off layout: x<<4 | y<<2 | z)
 __device__ __forceinline__ unsigned axis_bits(int cq, int b) {
     int lo = max(cq - 1, b * 4) - b * 4, hi = min(cq + 1, b * 4 + 3) - b * 4;   // 0 <= lo <= hi <= 3
     return ((2u << hi) - 1u) & ~((1u << lo) - 1u);
 }
 __device__ __forceinline__ unsigned long long shell_bits(int cqx, int cqy, int cqz, int bx, int by, int bz) {
-    unsigned xm = axis_bits(cqx, bx), ym = axis_bits(cqy, by), zm = axis_bits(cqz, bz);
-    unsigned yz = 0;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) if ((ym >> l) & 1u) yz |= zm << (4 * l);
-    unsigned long long m = 0;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) if ((xm >> l) & 1u) m |= (unsigned long long)yz << (16 * l);
-    return m;
+    return mask3(axis_bits(cqx, bx), axis_bits(cqy, by), axis_bits(cqz, bz));
 }
 
 // bits of the cells of block (bx,by,bz) inside the cell box [xl,xh] x [yl,yh] x [zl,zh]
@@ -341,14 +346,7 @@ __device__ __forceinline__ unsigned range_bits(int lo_c, int hi_c, int b) {
     return ((2u << hi) - 1u) & ~((1u << lo) - 1u);
 }
 __device__ __forceinline__ unsigned long long box_bits(int xl, int xh, int yl, int yh, int zl, int zh, int bx, int by, int bz) {
-    const unsigned xm = range_bits(xl, xh, bx), ym = range_bits(yl, yh, by), zm = range_bits(zl, zh, bz);
-    unsigned yz = 0;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) if ((ym >> l) & 1u) yz |= zm << (4 * l);
-    unsigned long long mm = 0;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) if ((xm >> l) & 1u) mm |= (unsigned long long)yz << (16 * l);
-    return mm;
+    return mask3(range_bits(xl, xh, bx), range_bits(yl, yh, by), range_bits(zl, zh, bz));
 }
 
 // Returns true when the shell result is final (then best holds the answer; count = number found).
@@ -529,14 +527,7 @@ __device__ __forceinline__ unsigned axis_bits_n(int cq, int b, int n) {
 }
 __device__ __forceinline__ unsigned long long cube_bits(int cqx, int cqy, int cqz, int bx, int by, int bz, int n) {
     if (n < 0) return 0ull;
-    unsigned xm = axis_bits_n(cqx, bx, n), ym = axis_bits_n(cqy, by, n), zm = axis_bits_n(cqz, bz, n);
-    unsigned yz = 0;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) if ((ym >> l) & 1u) yz |= zm << (4 * l);
-    unsigned long long m = 0;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) if ((xm >> l) & 1u) m |= (unsigned long long)yz << (16 * l);
-    return m;
+    return mask3(axis_bits_n(cqx, bx, n), axis_bits_n(cqy, by, n), axis_bits_n(cqz, bz, n));
 }
 
 // conservative lower bound (double) of the squared distance from q to any point stored in cell (cx,cy,cz)
