@@ -307,7 +307,8 @@ def run_flivo(args, rank, world_size, local_rank):
         launches += rep.kernel_launches + (2 if args.sort_scan else 0)   # own kernels: the update graph's + k_scan_keys, k_gather4 (the four CUB radix-sort kernels of the staging graph are library code and not counted)
         last = (k % S, x, P, rep)
     barrier()
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    step_ms = sorted(a.elapsed_time(b) for a, b in ev)   # this rank's per-step device times (median + p99)
+    dev_ms = sum(step_ms)
     tt = torch.tensor([dev_ms, float(trips_total) * pts_per_scan, float(launches)], dtype=torch.float64, device=dev)
     if world_size > 1:
         mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -489,6 +490,7 @@ def run_flivo(args, rank, world_size, local_rank):
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
                 trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add, ivox=ivox,
+                step_ms_median=float(np.median(step_ms)), step_ms_p99=float(np.percentile(step_ms, 99)), step_ms_min=float(step_ms[0]),
                 search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
@@ -581,6 +583,8 @@ def main():
                        "multi_gpu": (("one scan sharded over ranks; per trip 96 doubles per rank, " + ("stored into the peers' HBM by the solve kernel (NVLink peer memory)" if args.exchange == "peer" else "ncclAllGather")) if r["shard"] else
                                      "map replica + own scans per rank, no collective")},
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
+            "latency_ms_per_scan_stats": {"median": r["step_ms_median"], "p99": r["step_ms_p99"], "min": r["step_ms_min"],
+                                          "note": "per-step CUDA-event times of rank 0 over the timed steps"},
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
