@@ -383,6 +383,18 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         if (tid < 36) { r_x = S.x[tid]; r_xp = S.x_prop[tid]; }
         if (tid < 23) r_dx = S.pre->dxnew[tid];
     }
+    // the V3 loop decision is taken by warp 4: lane i owns component i's convergence limit, lane 0 the loop counters
+    double r_lim = 0.0;
+    int c_t = 0, c_iter = 0, c_trips = 0, c_search = 0, c_searches = 0, j_max_iter = 0, j_force = 0;
+    int c_rematch = 0;
+    if (S.phase != SOLVE_PHASE_REDUCE_ONLY) {
+        if ((tid >> 5) == 4 && tid - 128 < 23) r_lim = S.job->limit[tid - 128];
+        if (tid == 128 || tid == 0) {   // (thread 0 takes the V1 decision)
+            c_t = ctl->t; c_iter = ctl->iter; c_trips = ctl->trips; c_search = ctl->search; c_searches = ctl->searches;
+            c_rematch = ctl->rematch;
+            j_max_iter = S.job->max_iter; j_force = S.job->force_search;
+        }
+    }
     if (S.phase != SOLVE_PHASE_REDUCE_ONLY && stopped) return;
     const int n = (mode == 1) ? 18 : 23;
     const double r_P = (mode == 1) ? r_P1 : r_P3;
@@ -523,25 +535,28 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
         __syncthreads();
         stamp(S, ctl, 7);
         if ((tid & 31) == 0 && tid < 96) d_boxplus_v3_part(s_x, s_dxo, tid >> 5);   // :1814
-        if (tid == 128) {
-            int converge = 1;
-            for (int i = 0; i < 23; ++i) if (fabs(s_dxo[i]) > S.job->limit[i]) { converge = 0; break; }
-            int t = ctl->t, it = ctl->iter;
+        if ((tid >> 5) == 4) {
+            const int lane = tid & 31;
+            // esekfom.hpp:1816-1823: every component of dx below its limit (one lane each; the limits were loaded up front)
+            int converge = __all_sync(0xffffffffu, lane >= 23 || !(fabs(s_dxo[lane < 23 ? lane : 0]) > r_lim));
+            if (lane < 23) ctl->dx_last[lane] = s_dxo[lane];
+            if (lane == 0) {
+            int t = c_t, it = c_iter;
             if (converge) t++;
-            if (!t && it == S.job->max_iter - 2) converge = 1;                    // :1825-1828
-            int stop = (t > 1 || it == S.job->max_iter - 1) ? 1 : 0;               // :1831
+            if (!t && it == j_max_iter - 2) converge = 1;                         // :1825-1828
+            int stop = (t > 1 || it == j_max_iter - 1) ? 1 : 0;                    // :1831
             ctl->t = t;
-            int trip = ctl->trips;
-            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.job->force_search) ? 1 : 0;
-            ctl->searches += (ctl->search || S.job->force_search) ? 1 : 0;
+            int trip = c_trips;
+            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (c_search || j_force) ? 1 : 0;
+            ctl->searches = c_searches + ((c_search || j_force) ? 1 : 0);
             ctl->trips = trip + 1;
             ctl->search = converge;
             ctl->iter = it + 1;
             ctl->converged = t > 0 ? 1 : 0;
             ctl->stopped = stop;
             ctl_next_trip(ctl);
-            for (int i = 0; i < 23; ++i) ctl->dx_last[i] = s_dxo[i];
             s_flag[0] = stop;
+            }
         }
         __syncthreads();
         stamp(S, ctl, 8, 1);
@@ -658,12 +673,12 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_solve(SolveParams S) {
             double rn = sqrt(s_sol[0] * s_sol[0] + s_sol[1] * s_sol[1] + s_sol[2] * s_sol[2]);
             double tn = sqrt(s_sol[3] * s_sol[3] + s_sol[4] * s_sol[4] + s_sol[5] * s_sol[5]);
             int converged = ((rn * R2D < 0.01) && (tn * 100 < 0.015)) ? 1 : 0;   // :209-212
-            int it = ctl->iter, rematch = ctl->rematch, nse = 0;
-            if (converged || ((rematch == 0) && (it == (S.job->max_iter - 2)))) { nse = 1; rematch++; }   // :217-222
-            int stop = (rematch >= 2 || (it == S.job->max_iter - 1)) ? 1 : 0;          // :224
-            int trip = ctl->trips;
-            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (ctl->search || S.job->force_search) ? 1 : 0;
-            ctl->searches += (ctl->search || S.job->force_search) ? 1 : 0;
+            int it = c_iter, rematch = c_rematch, nse = 0;
+            if (converged || ((rematch == 0) && (it == (j_max_iter - 2)))) { nse = 1; rematch++; }   // :217-222
+            int stop = (rematch >= 2 || (it == j_max_iter - 1)) ? 1 : 0;          // :224
+            int trip = c_trips;
+            if (trip < MAX_TRIPS) ctl->trip_searched[trip] = (c_search || j_force) ? 1 : 0;
+            ctl->searches = c_searches + ((c_search || j_force) ? 1 : 0);
             ctl->trips = trip + 1;
             ctl->rematch = rematch;
             ctl->search = nse;
