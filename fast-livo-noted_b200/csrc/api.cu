@@ -743,7 +743,7 @@ static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, d
 static int search_grid(flivo_ctx* ctx) {
     const int tp = search_tile_points();
     const int tiles = (int)((ctx->scan_n + tp - 1) / tp);
-    if (ctx->search_resident <= 0) ctx->search_resident = ctx->sm_count * search_ctas_per_sm();
+    if (ctx->search_resident <= 0) ctx->search_resident = ctx->sm_count * search_ctas_per_sm(ctx->opt.ivox_nearby != 0);
     return std::max(1, std::min(((tiles + 255) / 256) * 256, ctx->search_resident));   // tiles are dealt dynamically
 }
 // scans whose tiles fill at most half of the resident CTAs leave the GPU under-filled: the search is then bound by each

@@ -402,6 +402,9 @@ __device__ __forceinline__ void store_plane(const FusedParams& P, int i, const f
 constexpr double IVOX_MAX_RANGE_SQ = 25.0;   // max_range = 5.0 default of GetClosestPoint (ivox3d.h:79), squared in double (ivox3d_node.hpp:162)
 constexpr int SEARCH_THREADS = 128;
 constexpr int SEARCH_WARPS = SEARCH_THREADS / 32;
+// register budget of k_search: 5 CTAs/SM = 96 registers (68 B of spills); 6 (80 registers, 140 B) and 4 (116, none) measured
+// 1-2 % slower, 7 (72 registers, 112 B) 4 % slower (profiles/r1_ab_launch_structure.txt)
+constexpr int SEARCH_CTAS_PER_SM = 5;
 constexpr int FAR_BATCH = 32;   // far points a warp finishes before its lanes fit their planes (one lane per point)
 
 // shared memory of k_search: the two phases of a CTA never overlap, so their buffers share the space
@@ -441,7 +444,7 @@ __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) {
 // kernel does not carry its code: k_search is instruction-fetch sensitive (ncu: no_instruction stalls).
 // PAR: thread_knn5_shell<PAR_PROBES>, chosen by the launcher for scans that leave the GPU under-filled.
 template <bool IVOX, bool PAR>
-__global__ void __launch_bounds__(SEARCH_THREADS, 768 / SEARCH_THREADS) k_search(FusedParams P) {
+__global__ void __launch_bounds__(SEARCH_THREADS, IVOX ? 6 : SEARCH_CTAS_PER_SM) k_search(FusedParams P) {
     __shared__ double s_state[24];
     __shared__ SearchSmem S;
     __shared__ unsigned s_tile;
@@ -752,9 +755,11 @@ void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, b
 }
 // CTAs of k_search that fit on one SM (its grid never needs to exceed the resident set: tiles are dealt dynamically)
 int search_tile_points() { return SEARCH_THREADS; }
-int search_ctas_per_sm() {
+int search_ctas_per_sm(bool ivox) {
     int nb = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_search<false, false>, SEARCH_THREADS, 0) != cudaSuccess || nb < 1) nb = 4;
+    const cudaError_t e = ivox ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_search<true, false>, SEARCH_THREADS, 0)
+                               : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_search<false, false>, SEARCH_THREADS, 0);
+    if (e != cudaSuccess || nb < 1) nb = 4;
     return nb;
 }
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
