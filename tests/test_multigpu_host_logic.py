@@ -94,3 +94,83 @@ def test_partition_helpers(pkg):
     b = sh.pack_block(H, np.arange(12.0), 3.5, 17)
     H2, z2, rs, ne = sh.unpack_block(b)
     assert np.array_equal(H, H2) and np.array_equal(z2, np.arange(12.0)) and rs == 3.5 and ne == 17
+
+
+class _FakeReport:
+    trips = 4
+
+
+class _FakeState:
+    def __init__(self, a):
+        self.a = np.asarray(a, dtype=np.float64)
+
+    @staticmethod
+    def from_array(a):
+        return _FakeState(a)
+
+    def as_array(self):
+        return self.a
+
+
+class _FakeFlivo:
+    """Records the calls of sharding.replay_sequences (no device): the call order per sequence is the contract."""
+    log = []
+
+    def __init__(self, **kw):
+        self.kw, self.n, self.calls = kw, 0, []
+        _FakeFlivo.log.append(self.calls)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.calls.append("close")
+
+    def scan_upload(self, body):
+        self.calls.append(("upload", len(body)))
+
+    def h_share_model(self, st, mode, do_search, want):
+        self.calls.append("trip")
+        return {"world": np.zeros((3, 3), np.float32)}
+
+    def Build(self, w):
+        self.calls.append("build")
+        self.n += len(w)
+
+    def iekf_update(self, st, P0, cfg):
+        self.calls.append("update")
+        return _FakeState(st.as_array() + 1.0), P0, _FakeReport()
+
+    def map_add_scan(self, x):
+        self.calls.append("add")
+        self.n += 2
+        return 2
+
+    def size(self):
+        return self.n
+
+
+def test_replay_sequences_control_flow(pkg):
+    """config 4: sequence s -> rank s mod G, own context per sequence, first scan builds, later scans update + add."""
+    import importlib
+    import types
+    sh = importlib.import_module("fast_livo_noted_b200.sharding")
+    fake = types.SimpleNamespace(Flivo=_FakeFlivo, State=_FakeState)
+    cfg = types.SimpleNamespace(mode=1)
+    seqs = [[{"body": np.zeros((10 + s, 3), np.float32), "x_prior": np.full(24, float(s))} for _ in range(3 + s % 2)] for s in range(5)]
+    seen = {}
+    for rank in range(2):
+        _FakeFlivo.log = []
+        r = sh.replay_sequences(fake, seqs, rank, 2, np.eye(18), cfg, ds=0.5)
+        assert sorted(r) == list(range(rank, 5, 2))
+        assert len(_FakeFlivo.log) == len(r)          # one context per sequence
+        for calls, s in zip(_FakeFlivo.log, sorted(r)):
+            frames = len(seqs[s])
+            assert calls[:3] == [("upload", 10 + s), "trip", "build"]
+            assert calls[3:] == [("upload", 10 + s), "update", "add"] * (frames - 1) + ["close"]
+            assert r[s]["updates"] == frames - 1 and r[s]["trips"] == 4 * (frames - 1)
+            assert r[s]["work"] == 4 * (frames - 1) * (10 + s) and r[s]["added"] == [2] * (frames - 1)
+            assert r[s]["map_points"] == 3 + 2 * (frames - 1)
+            assert np.array_equal(r[s]["x"], np.full(24, float(s) + 1.0))
+        seen.update(r)
+    assert sorted(seen) == list(range(5))
