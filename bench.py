@@ -420,7 +420,7 @@ def run_flivo(args, rank, world_size, local_rank):
                    "scan_points": int(pts_per_scan), "note": "wall clock around flivo_map_add_scan + sync; the map grows by the added points"}
     # ---- iVox-compatible mode (the local map the reference compiles by default), informational:
     # the same scans, V1 (compiled 18-DOF) update, against an iVox map (resolution 0.5, NEARBY18) holding the map points
-    # within lidar range of the sensor; the CPU arm is the restated IVox + loop on all host threads (parity unpinned).
+    # within lidar range of the sensor; the CPU arm is the restated IVox + loop on all host threads (the restatement is pinned on the reference's compiled header: tests/test_ivox_cpu.py).
     ivox = None
     if rank == 0 and world_size == 1 and not args.no_ivox:
         import flivo_parity as par

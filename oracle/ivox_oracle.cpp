@@ -4,9 +4,13 @@
 // builds when USE_ikdtree is off (CMakeLists.txt:15), faster_lio::IVox<3, IVoxNodeType::DEFAULT, PointType>
 // (include/laser_mapping.h:65).  All citations are relative to /root/reference/.
 //
-// PARITY UNPINNED: ivox3d.h needs Eigen, glog and <execution>/TBB, none of which are in this image or in the
-// reference tree, so it cannot be compiled here; the reference holds no test or golden vector for it.  This
-// file restates the algorithm and DEFINES the expected results:
+// PARITY: PINNED ON THE CONTAINER LOGIC, not on three Eigen calls.  The reference holds no test or golden vector for
+// this branch, and ivox3d.h needs Eigen, glog and pcl, which are not in this image.  Its headers do compile UNMODIFIED
+// against the small stand-ins of oracle/shim (Eigen column vectors, pcl point types, glog): oracle/ivox_ref_wrap.cpp ->
+// oracle/_ref/libivox_ref.so, and tests/test_ivox_cpu.py holds this file to that library for all four stencils — voxel
+// count, found / not found, neighbour count, neighbour set, nearest element, LRU eviction at capacity_.  What stays a
+// restatement (the stand-in and this file share my reading of Eigen) is the arithmetic of squaredNorm, array().round()
+// and cast<int>():
 //   * Pos2Grid (ivox3d.h:278-281): (pt * inv_resolution_).array().round().cast<int>(), inv_resolution_ a float
 //     holding 1.0 / resolution_ (ivox3d.h:56,63); std::round semantics (half away from zero).
 //   * distance2 (ivox3d_node.hpp:13-16): (pt1 - pt2).squaredNorm() on Vector3f; Eigen's unrolled reduction of a

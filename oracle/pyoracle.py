@@ -13,6 +13,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "liboracle.so")
 REF_PATH = os.path.join(HERE, "_ref", "libflivo_ref.so")
+IVOX_REF_PATH = os.path.join(HERE, "_ref", "libivox_ref.so")
 
 f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
@@ -69,7 +70,10 @@ def build(force=False):
     if os.path.exists(ref_src):
         newest = max(os.path.getmtime(os.path.join(HERE, f)) for f in
                      ("flivo_oracle.cpp", "ikd_ref_wrap.cpp", "flivo_oracle.h"))
-        if force or not os.path.exists(REF_PATH) or os.path.getmtime(REF_PATH) < newest:
+        ivox_newest = max([os.path.getmtime(os.path.join(HERE, "ivox_ref_wrap.cpp"))] +
+                          [os.path.getmtime(os.path.join(dp, f)) for dp, _, fs in os.walk(os.path.join(HERE, "shim")) for f in fs])
+        if (force or not os.path.exists(REF_PATH) or os.path.getmtime(REF_PATH) < newest
+                or not os.path.exists(IVOX_REF_PATH) or os.path.getmtime(IVOX_REF_PATH) < ivox_newest):
             subprocess.check_call(["make", "-C", HERE, "ref"], stdout=subprocess.DEVNULL)
 
 
@@ -333,6 +337,59 @@ def gnss_block(st, gnss_pos, antlever, std):
     lib().orc_gnss_block(_c(x[0:9], np.float64), _c(x[9:12], np.float64), _c(gnss_pos, np.float64), _c(antlever, np.float64),
                          _c(std, np.float64), HTH, HTL)
     return HTH.reshape(6, 6), HTL
+
+
+_ivox_ref = None
+
+
+def have_ivox_ref():
+    build()
+    return os.path.exists(IVOX_REF_PATH)
+
+
+def ivox_ref():
+    global _ivox_ref
+    if _ivox_ref is None:
+        build()
+        L = C.CDLL(IVOX_REF_PATH)
+        L.ref_ivox_create.argtypes = [C.c_float, C.c_int, C.c_longlong]
+        L.ref_ivox_create.restype = C.c_void_p
+        L.ref_ivox_destroy.argtypes = [C.c_void_p]
+        L.ref_ivox_add_points.argtypes = [C.c_void_p, f32p, C.c_longlong]
+        L.ref_ivox_num_grids.argtypes = [C.c_void_p]
+        L.ref_ivox_num_grids.restype = C.c_longlong
+        L.ref_ivox_knn.argtypes = [C.c_void_p, f32p, C.c_longlong, C.c_int, C.c_double, f32p, i32p]
+        _ivox_ref = L
+    return _ivox_ref
+
+
+class RefIVox:
+    """The reference's own faster_lio::IVox<3, DEFAULT> (include/ivox3d headers compiled unmodified into
+    oracle/_ref/libivox_ref.so against the Eigen / pcl stand-ins of oracle/shim).  nearby: 1 / 7 / 19 / 27."""
+
+    def __init__(self, resolution, nearby=19, capacity=1000000):
+        self.h = ivox_ref().ref_ivox_create(resolution, {1: 0, 7: 1, 19: 2, 27: 3}[nearby], capacity)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            ivox_ref().ref_ivox_destroy(self.h)
+            self.h = None
+
+    def add_points(self, xyz):
+        xyz = _c(xyz, np.float32)
+        ivox_ref().ref_ivox_add_points(self.h, xyz, xyz.shape[0])
+
+    def num_grids(self):
+        return ivox_ref().ref_ivox_num_grids(self.h)
+
+    def knn(self, queries, k=5, max_range=5.0):
+        """-> (xyz [n][k][3] in the order GetClosestPoint returned them, count; -1 = returned false)."""
+        q = _c(queries, np.float32)
+        n = q.shape[0]
+        oxyz = np.zeros((n, k, 3), np.float32)
+        ocnt = np.empty(n, np.int32)
+        ivox_ref().ref_ivox_knn(self.h, q, n, k, float(max_range), oxyz, ocnt)
+        return oxyz, ocnt
 
 
 class RefTree:

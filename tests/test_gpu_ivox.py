@@ -39,6 +39,19 @@ def test_addpoints_getclosestpoint_match_oracle(pkg, nearby):
         assert np.array_equal(gcnt, np.maximum(ocnt, 0))
         assert np.array_equal(gid, oid) and np.array_equal(gsq, osq) and np.array_equal(gxyz, oxyz)
         assert (ocnt == 5).sum() > 1000 and (ocnt < 0).sum() > 100
+        if orc.have_ivox_ref():
+            # the same against faster_lio::IVox ITSELF (include/ivox3d headers compiled unmodified, oracle/_ref/libivox_ref.so):
+            # found / not found, count, nearest element and the neighbour set (the reference's order is nth_element's)
+            R = orc.RefIVox(0.5, nearby)
+            for part in np.array_split(pts, 3):
+                R.add_points(part)
+            rxyz, rcnt = R.knn(q, 5, 5.0)
+            assert np.array_equal(gcnt, np.maximum(rcnt, 0)) and R.num_grids() == F.stats().map_cells
+            has = gcnt > 0
+            assert np.array_equal(gxyz[has, 0], rxyz[has, 0])
+            for i in np.nonzero(has)[0]:
+                a, b = gxyz[i, :gcnt[i]], rxyz[i, :gcnt[i]]
+                assert np.array_equal(a[np.lexsort((a[:, 2], a[:, 1], a[:, 0]))], b[np.lexsort((b[:, 2], b[:, 1], b[:, 0]))]), i
         # voxels holding more than one bucket (8 slots) exist in this world: the overflow chains are exercised
         xyz, ids = F.flatten()
         key = np.round(xyz.astype(np.float32) * np.float32(1.0 / 0.5)).astype(np.int64)

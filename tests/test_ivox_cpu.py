@@ -1,6 +1,7 @@
 """CPU (-m "not gpu"): the restated faster_lio::IVox (oracle/ivox_oracle.cpp) against an independent
-numpy restatement, its edge cases, and map_incremental's add rule on hand-made cases.  Parity of this branch is
-"unpinned" (ivox3d.h needs Eigen / glog / TBB, absent here; the reference has no tests for it)."""
+numpy restatement, its edge cases, map_incremental's add rule on hand-made cases, and — the pin — against the
+reference's own include/ivox3d headers compiled unmodified behind stand-ins for Eigen / pcl / glog
+(oracle/_ref/libivox_ref.so, oracle/ivox_ref_wrap.cpp).  The reference has no tests for this branch."""
 import numpy as np
 import pytest
 
@@ -137,3 +138,71 @@ def test_gnss_block_matches_numpy():
     # observation farther than 2 m from the state: ignored (:221-222)
     H, L = orc.gnss_block(st, gpos + np.array([2.5, 0, 0]), lever, std)
     assert not H.any() and not L.any()
+
+
+# ---- the restatement against the reference's own header (oracle/_ref/libivox_ref.so) -------------------------------
+def _rows_as_sets(xyz, cnt):
+    """Each row's points sorted lexicographically (the reference returns them in nth_element order)."""
+    out = []
+    for i in range(len(cnt)):
+        c = max(int(cnt[i]), 0)
+        r = xyz[i, :c]
+        out.append(r[np.lexsort((r[:, 2], r[:, 1], r[:, 0]))] if c else r)
+    return out
+
+
+needs_ref = pytest.mark.skipif(not orc.have_ivox_ref(), reason="oracle/_ref/libivox_ref.so not built (reference tree absent)")
+
+
+@needs_ref
+@pytest.mark.parametrize("nearby", [1, 7, 19, 27])
+def test_restatement_matches_the_compiled_reference_header(nearby):
+    """Same AddPoints batches, same queries: voxel count, found/not-found, neighbour count and the neighbour SET of every
+    query must be those of faster_lio::IVox itself (include/ivox3d/ivox3d.h compiled unmodified)."""
+    rng = np.random.default_rng(100 + nearby)
+    res = 0.5
+    pts = (rng.random((60000, 3)) * np.array([24.0, 24.0, 6.0]) - np.array([12.0, 12.0, 3.0])).astype(np.float32)
+    # points exactly half-way between voxel centres (p / res = n + 0.5) and on negative coordinates: the rounding rule
+    edge = (np.round(rng.random((500, 3)) * 40 - 20) * res + res / 2).astype(np.float32)
+    edge[:, 1:] += (rng.random((500, 2)) * 0.2).astype(np.float32)      # (x stays on the boundary; no two points coincide)
+    edge = np.unique(edge, axis=0)
+    O, R = orc.OracleIVox(res, nearby), orc.RefIVox(res, nearby)
+    for batch in (pts[:25000], edge, pts[25000:]):
+        O.add_points(batch)
+        R.add_points(batch)
+    assert O.num_grids() == R.num_grids()
+    q = (rng.random((5000, 3)) * np.array([30.0, 30.0, 9.0]) - np.array([15.0, 15.0, 4.5])).astype(np.float32)
+    q[:200] = edge[:200] + (rng.random((200, 3)) * 0.05).astype(np.float32)
+    for k, max_range in ((5, 5.0), (3, 5.0), (1, 5.0), (5, 0.3)):
+        oid, osq, oxyz, ocnt, ties = O.knn(q, k, max_range)
+        rxyz, rcnt = R.knn(q, k, max_range)
+        assert ties == 0
+        assert np.array_equal(ocnt, rcnt), (k, max_range)
+        assert (ocnt == -1).any() and (ocnt == k).any()
+        a, b = _rows_as_sets(oxyz, ocnt), _rows_as_sets(rxyz, rcnt)
+        bad = [i for i in range(len(q)) if not np.array_equal(a[i], b[i])]
+        assert not bad, (k, max_range, len(bad), bad[:5])
+        # element 0 of the reference's list is the nearest point (the final nth_element at position 0, ivox3d.h:178)
+        has = ocnt > 0
+        assert np.array_equal(rxyz[has, 0], oxyz[has, 0])
+
+
+@needs_ref
+def test_lru_eviction_matches_the_compiled_reference_header():
+    """capacity_ voxels (ivox3d.h:262-265): a new voxel that fills the map evicts the least recently TOUCHED one."""
+    rng = np.random.default_rng(7)
+    res, cap = 0.5, 300
+    O, R = orc.OracleIVox(res, 19, cap), orc.RefIVox(res, 19, cap)
+    for b in range(12):
+        centre = rng.random(3) * 10 - 5
+        batch = (centre + rng.normal(0, 1.5, (800, 3))).astype(np.float32)
+        O.add_points(batch)
+        R.add_points(batch)
+        assert O.num_grids() == R.num_grids() and O.num_grids() < cap
+    assert O.evicted() > 0
+    q = (rng.random((3000, 3)) * 14 - 7).astype(np.float32)
+    oid, osq, oxyz, ocnt, ties = O.knn(q, 5, 5.0)
+    rxyz, rcnt = R.knn(q, 5, 5.0)
+    assert ties == 0 and np.array_equal(ocnt, rcnt)
+    a, b = _rows_as_sets(oxyz, ocnt), _rows_as_sets(rxyz, rcnt)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
