@@ -215,3 +215,33 @@ def check_update_ivox(pkg, F, ivox, body, x_prior, mode, max_iter=4, verbose=Fal
     if verbose:
         print("ivox update: trips=%d searches=%d n_eff=%d dx_err=%.2e x_err=%.2e" % (rep.trips, rep.searches, rep.n_eff, dx_err, x_err))
     return xg, Pg, rep, o
+
+
+# ---- iVox golden vectors (tests/golden/ivox_reference.npz: outputs of the reference's own compiled header) -----------
+def lexsorted_rows(xyz, cnt):
+    """Every row's first cnt points in lexicographic order, the rest zero (same helper as tests/golden/make_golden.py)."""
+    out = np.zeros_like(xyz)
+    for i in range(len(cnt)):
+        c = max(int(cnt[i]), 0)
+        r = xyz[i, :c]
+        out[i, :c] = r[np.lexsort((r[:, 2], r[:, 1], r[:, 0]))]
+    return out
+
+
+def check_ivox_golden(gold, nearby, add_points, num_grids, knn):
+    """add_points(xyz), num_grids() -> int, knn(q, k, max_range) -> (xyz [n][k][3], count with <= 0 meaning none) of a map
+    created for stencil `nearby` at gold['resolution'].  Found / not found, count, nearest element and neighbour set must
+    be the reference's."""
+    for part in np.array_split(gold["map"], 3):
+        add_points(part)
+    assert num_grids() == int(gold["grids_%d" % nearby])
+    q = gold["queries"]
+    for tag, k, max_range in (("k5", 5, 5.0), ("k3r02", 3, 0.2)):
+        xyz, cnt = knn(q, k, max_range)
+        cnt = np.maximum(np.asarray(cnt), 0)
+        gcnt = np.maximum(gold["cnt_%d_%s" % (nearby, tag)], 0)
+        assert np.array_equal(cnt, gcnt), (nearby, tag)
+        has = cnt > 0
+        assert has.sum() > 300 and (~has).sum() > 20
+        assert np.array_equal(xyz[has, 0], gold["first_%d_%s" % (nearby, tag)][has]), (nearby, tag)
+        assert np.array_equal(lexsorted_rows(xyz, cnt), gold["set_%d_%s" % (nearby, tag)]), (nearby, tag)

@@ -1,8 +1,9 @@
 #!/usr/bin/env python
 """Generates the committed golden vectors under tests/golden/ by RUNNING THE REFERENCE'S OWN CODE in this
-container: include/ikd-Tree/ikd_Tree.cpp compiled unmodified into oracle/_ref/libflivo_ref.so (oracle/Makefile).
+container: include/ikd-Tree/ikd_Tree.cpp compiled unmodified into oracle/_ref/libflivo_ref.so, and the header-only
+include/ivox3d/ivox3d.h compiled unmodified into oracle/_ref/libivox_ref.so (oracle/Makefile).
 The reference ships no tests or fixtures of its own, so these pin the kNN / Add_Points /
-Delete_Point_Boxes half of the path.  /root/reference is needed to (re)generate, never to run the tests.
+Delete_Point_Boxes half of the path and the iVox branch.  /root/reference is needed to (re)generate, never to run the tests.
 
     python tests/golden/make_golden.py
 """
@@ -72,10 +73,57 @@ def map_case():
     np.savez_compressed(os.path.join(HERE, "map_ops_ikdtree.npz"), **out)
 
 
+def lexsorted_rows(xyz, cnt):
+    """Every row's first cnt points in lexicographic order, the rest zero (the reference returns nth_element's order)."""
+    out = np.zeros_like(xyz)
+    for i in range(len(cnt)):
+        c = max(int(cnt[i]), 0)
+        r = xyz[i, :c]
+        out[i, :c] = r[np.lexsort((r[:, 2], r[:, 1], r[:, 0]))]
+    return out
+
+
+def ivox_case():
+    """faster_lio::IVox<3, DEFAULT> itself: the reference's include/ivox3d headers compiled unmodified against the
+    Eigen / pcl / glog stand-ins of oracle/shim (oracle/ivox_ref_wrap.cpp -> oracle/_ref/libivox_ref.so)."""
+    res = 0.5
+    world = scenes.make_world(seed=23, n_points=40000, ds=0.2)
+    pts = world["points"]
+    rng = np.random.default_rng(8)
+    q = pts[rng.choice(len(pts), 700, replace=False)] + rng.normal(0, 0.04, (700, 3)).astype(np.float32)
+    q = np.concatenate([q, rng.uniform(-30, 30, (100, 3)).astype(np.float32)]).astype(np.float32)
+    out = dict(map=pts, queries=q, resolution=np.float32(res))
+    for nearby in (1, 7, 19, 27):
+        R = orc.RefIVox(res, nearby)
+        for part in np.array_split(pts, 3):     # three AddPoints calls
+            R.add_points(part)
+        out["grids_%d" % nearby] = np.int64(R.num_grids())
+        for tag, k, rng_m in (("k5", 5, 5.0), ("k3r02", 3, 0.2)):
+            xyz, cnt = R.knn(q, k, rng_m)
+            out["cnt_%d_%s" % (nearby, tag)] = cnt
+            out["first_%d_%s" % (nearby, tag)] = xyz[:, 0].copy()
+            out["set_%d_%s" % (nearby, tag)] = lexsorted_rows(xyz, cnt)
+    # LRU eviction at a small capacity_ (ivox3d.h:262-265)
+    cap = 300
+    R = orc.RefIVox(res, 19, cap)
+    batches = []
+    for b in range(10):
+        centre = rng.random(3) * 10 - 5
+        batches.append((centre + rng.normal(0, 1.5, (600, 3))).astype(np.float32))
+        R.add_points(batches[-1])
+    ql = (rng.random((500, 3)) * 14 - 7).astype(np.float32)
+    xyz, cnt = R.knn(ql, 5, 5.0)
+    out.update(lru_capacity=np.int64(cap), lru_batches=np.stack(batches), lru_queries=ql, lru_grids=np.int64(R.num_grids()),
+               lru_cnt=cnt, lru_set=lexsorted_rows(xyz, cnt))
+    np.savez_compressed(os.path.join(HERE, "ivox_reference.npz"), **out)
+
+
 if __name__ == "__main__":
     assert orc.have_ref(), "oracle/_ref/libflivo_ref.so missing: needs /root/reference"
+    assert orc.have_ivox_ref(), "oracle/_ref/libivox_ref.so missing: needs /root/reference"
     knn_case()
     map_case()
+    ivox_case()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

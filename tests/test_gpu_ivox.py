@@ -64,6 +64,18 @@ def test_addpoints_getclosestpoint_match_oracle(pkg, nearby):
         assert np.array_equal(gcnt, np.maximum(ocnt, 0)) and np.array_equal(gid, oid) and np.array_equal(gsq, osq)
 
 
+@pytest.mark.parametrize("nearby", [1, 7, 19, 27])
+def test_getclosestpoint_matches_reference_golden(pkg, nearby):
+    """tests/golden/ivox_reference.npz: outputs of faster_lio::IVox itself (the reference's header compiled unmodified,
+    tests/golden/make_golden.py) — found / not found, count, nearest element, neighbour set."""
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ivox_reference.npz"))
+    with pkg.Flivo(downsample_size=float(gold["resolution"]), ivox_nearby=nearby) as F:
+        def knn(q, k, max_range):
+            _, _, xyz, cnt = F.GetClosestPoint(q, k, max_range)
+            return xyz, cnt
+        par.check_ivox_golden(gold, nearby, F.AddPoints, lambda: F.stats().map_cells, knn)
+
+
 def test_ivox_mode_rejects_ikdtree_only_operations(pkg):
     pts = np.random.default_rng(3).uniform(-2, 2, (100, 3)).astype(np.float32)
     with pkg.Flivo(downsample_size=0.5, ivox_nearby=19) as F:

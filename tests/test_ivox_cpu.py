@@ -206,3 +206,34 @@ def test_lru_eviction_matches_the_compiled_reference_header():
     assert ties == 0 and np.array_equal(ocnt, rcnt)
     a, b = _rows_as_sets(oxyz, ocnt), _rows_as_sets(rxyz, rcnt)
     assert all(np.array_equal(x, y) for x, y in zip(a, b))
+
+
+# ---- the restatement against the committed outputs of the compiled reference header (runs without /root/reference) --
+import os  # noqa: E402
+
+import flivo_parity as par  # noqa: E402
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ivox_reference.npz")
+
+
+@pytest.mark.parametrize("nearby", [1, 7, 19, 27])
+def test_restatement_matches_reference_golden(nearby):
+    gold = np.load(GOLD)
+    O = orc.OracleIVox(float(gold["resolution"]), nearby)
+
+    def knn(q, k, max_range):
+        _, _, xyz, cnt, ties = O.knn(q, k, max_range)
+        assert ties == 0
+        return xyz, cnt
+    par.check_ivox_golden(gold, nearby, O.add_points, O.num_grids, knn)
+
+
+def test_restated_lru_matches_reference_golden():
+    gold = np.load(GOLD)
+    O = orc.OracleIVox(float(gold["resolution"]), 19, int(gold["lru_capacity"]))
+    for b in gold["lru_batches"]:
+        O.add_points(b)
+    assert O.num_grids() == int(gold["lru_grids"]) and O.evicted() > 0
+    _, _, xyz, cnt, ties = O.knn(gold["lru_queries"], 5, 5.0)
+    assert ties == 0 and np.array_equal(cnt, gold["lru_cnt"])
+    assert np.array_equal(par.lexsorted_rows(xyz, cnt), gold["lru_set"])
