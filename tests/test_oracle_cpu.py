@@ -133,3 +133,56 @@ def test_h_share_model_properties(small_world, small_scan):
         HPH, HPL = orc.repack_v1(o["HTH"], o["HTz"], 0.001)
         assert np.allclose(HPH[:3, :3], H[3:6, 3:6] / 0.001) and np.allclose(HPH[3:6, 3:6], H[:3, :3] / 0.001)
         assert np.all(HPH[6:, :] == 0) and np.all(HPL[6:] == 0)
+
+
+@pytest.mark.skipif(not orc.have_ref(), reason="oracle/_ref not built (needs /root/reference at build time)")
+def test_edge_cases_against_live_reference_ikdtree():
+    """Ragged and degenerate inputs on the reference tree run live: fewer than k points, a tight max_dist (0..k
+    neighbours per query), coincident map points (distance ties: compared as distance lists), the half-open box of
+    Delete_Point_Boxes, a query set of one, deleting everything."""
+    rng = np.random.default_rng(11)
+    # (1) fewer points than k
+    few = rng.uniform(-1, 1, (3, 3)).astype(np.float32)
+    T = orc.RefTree(0.5)
+    T.build(few)
+    q = rng.uniform(-2, 2, (50, 3)).astype(np.float32)
+    rid, rsq, _, rcnt = T.knn(q, 5, np.inf)
+    oid, osq, _, ocnt, _ = orc.knn_bruteforce(few, q, 5, np.inf)
+    assert (rcnt == 3).all() and np.array_equal(rcnt, ocnt)
+    assert np.array_equal(rid[:, :3], oid[:, :3]) and np.array_equal(rsq[:, :3], osq[:, :3])
+    T.close()
+    # (2) tight max_dist: ragged counts, and (3) coincident points
+    pts = rng.uniform(-5, 5, (4000, 3)).astype(np.float32)
+    pts[100:140] = pts[60:100]                                  # 40 exact duplicates
+    T = orc.RefTree(0.5)
+    T.build(pts)
+    q = (pts[rng.integers(0, len(pts), 600)] + rng.normal(0, 0.05, (600, 3))).astype(np.float32)
+    q[:40] = pts[60:100]                                        # queries on the duplicated points: distance 0 twice
+    for md in (0.02, 0.2, np.inf):
+        rid, rsq, _, rcnt = T.knn(q, 5, md)
+        oid, osq, _, ocnt, ties = orc.knn_bruteforce(pts, q, 5, md)
+        assert np.array_equal(rcnt, ocnt), md
+        for i in range(len(q)):
+            assert np.array_equal(rsq[i, :rcnt[i]], osq[i, :ocnt[i]]), (md, i)
+        if md == 0.02:
+            assert len(set(rcnt.tolist())) >= 4                 # really ragged
+    one = T.knn(q[:1], 5, np.inf)
+    assert one[3][0] == 5 and np.array_equal(one[1][0], orc.knn_bruteforce(pts, q[:1], 5, np.inf)[1][0])
+    T.close()
+    # (4) half-open delete box: min <= p < max per axis (ikd_Tree.cpp:648)
+    grid = np.stack(np.meshgrid(np.arange(5), np.arange(5), np.arange(5), indexing="ij"), -1).reshape(-1, 3).astype(np.float32)
+    T, M = orc.RefTree(0.5), orc.OracleMap(0.5)
+    T.build(grid)
+    M.build(grid)
+    box = np.array([[1, 1, 1, 3, 3, 3]], np.float32)            # faces on the lattice: planes 1 and 2 go, plane 3 stays
+    assert T.delete_boxes(box) == M.delete_boxes(box) == 8
+    rx, _ = T.flatten()
+    ox, _ = M.live()
+    key = lambda a: a[np.lexsort((a[:, 2], a[:, 1], a[:, 0]))]
+    assert np.array_equal(key(rx), key(ox)) and len(ox) == 125 - 8
+    assert not ((ox >= 1).all(1) & (ox < 3).all(1)).any() and ((ox == 3).any(1)).sum() > 0
+    # (5) deleting everything, then searching
+    allbox = np.array([[-10, -10, -10, 10, 10, 10]], np.float32)
+    assert T.delete_boxes(allbox) == M.delete_boxes(allbox) == 117
+    assert len(M.live()[0]) == 0 and (T.knn(grid[:5], 5, np.inf)[3] == 0).all()
+    T.close()
