@@ -49,7 +49,8 @@ def combine_rank_blocks(blocks):
     return s
 
 
-def replay_sequences(pkg, sequences, rank, world_size, P0, cfg, ds, device=0, initial_points=0, cell_ratio=2, sort_scan=True):
+def replay_sequences(pkg, sequences, rank, world_size, P0, cfg, ds, device=0, initial_points=0, cell_ratio=2, sort_scan=True,
+                     concurrent=1):
     """Batched replay of independent scan sequences (BASELINE config 4): sequence s belongs to rank
     s mod G, every sequence gets its own context (its own map in HBM) and no rank ever talks to another.
 
@@ -60,24 +61,36 @@ def replay_sequences(pkg, sequences, rank, world_size, P0, cfg, ds, device=0, in
     sequences[s] is an iterable of scans, each a dict with "body" ((n, 3) float32, lidar frame) and "x_prior" (the
     flat state handed to the update).  Returns {s: dict(x=posterior of the last scan, map_points, updates, trips,
     work=sum of trips x scan points, added=[points added per frame])} for this rank's sequences.
+
+    concurrent > 1 drives that many of the rank's sequences at a time, one host thread and one context (one stream) each:
+    contexts share nothing, so the results are those of concurrent = 1; the GPU then overlaps the single-CTA solve and
+    the search tails of one sequence with the kernels of another.
     """
-    out = {}
-    for s in sequences_of_rank(len(sequences), rank, world_size):
-        with pkg.Flivo(device=device, downsample_size=ds, cell_ratio=cell_ratio, initial_points=initial_points, sort_scan=sort_scan) as F:
-            res = dict(x=None, map_points=0, updates=0, trips=0, work=0, added=[])
-            for k, scan in enumerate(sequences[s]):
-                st = pkg.State.from_array(scan["x_prior"])
-                F.scan_upload(scan["body"])
-                if k == 0:
-                    w = F.h_share_model(st, mode=cfg.mode, do_search=True, want=("world",))["world"]
-                    F.Build(w)
-                    continue
-                x, _, rep = F.iekf_update(st, P0, cfg)
-                res["added"].append(F.map_add_scan(x))
-                res["updates"] += 1
-                res["trips"] += rep.trips
-                res["work"] += rep.trips * len(scan["body"])
-                res["x"] = x.as_array()
-            res["map_points"] = F.size()
-            out[s] = res
-    return out
+    mine = sequences_of_rank(len(sequences), rank, world_size)
+    if concurrent > 1 and len(mine) > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=concurrent) as ex:
+            parts = list(ex.map(lambda s: _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_ratio, sort_scan), mine))
+        return dict(zip(mine, parts))
+    return {s: _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_ratio, sort_scan) for s in mine}
+
+
+def _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_ratio, sort_scan):
+    """One sequence through its own context (see replay_sequences)."""
+    with pkg.Flivo(device=device, downsample_size=ds, cell_ratio=cell_ratio, initial_points=initial_points, sort_scan=sort_scan) as F:
+        res = dict(x=None, map_points=0, updates=0, trips=0, work=0, added=[])
+        for k, scan in enumerate(sequences[s]):
+            st = pkg.State.from_array(scan["x_prior"])
+            F.scan_upload(scan["body"])
+            if k == 0:
+                w = F.h_share_model(st, mode=cfg.mode, do_search=True, want=("world",))["world"]
+                F.Build(w)
+                continue
+            x, _, rep = F.iekf_update(st, P0, cfg)
+            res["added"].append(F.map_add_scan(x))
+            res["updates"] += 1
+            res["trips"] += rep.trips
+            res["work"] += rep.trips * len(scan["body"])
+            res["x"] = x.as_array()
+        res["map_points"] = F.size()
+    return res

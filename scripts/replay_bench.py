@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--pool", type=int, default=24)
     ap.add_argument("--scan-points", type=int, default=24000)
     ap.add_argument("--mode", type=int, default=1)
+    ap.add_argument("--concurrent", type=int, default=1, help="sequences of a rank driven at a time (host threads)")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     dev = int(os.environ.get("LOCAL_RANK", 0))
@@ -50,7 +51,7 @@ def main():
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    r = sh.replay_sequences(pkg, seqs, rank, world, P0, cfg, ds=0.5, device=dev)
+    r = sh.replay_sequences(pkg, seqs, rank, world, P0, cfg, ds=0.5, device=dev, concurrent=a.concurrent)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     t = torch.tensor([dt, float(sum(v["work"] for v in r.values())), float(sum(v["updates"] for v in r.values()))], dtype=torch.float64, device=torch.device("cuda", dev))
@@ -63,7 +64,7 @@ def main():
         dt, work, upd = float(t[0]), float(t[1]), float(t[2])
     if rank == 0:
         print(json.dumps({"metric": "replay_points_per_sec", "value": work / dt, "unit": "points/s", "n_gpus": world,
-                          "sequences": a.sequences, "frames_per_sequence": a.frames, "scan_points": a.scan_points, "updates": int(upd),
+                          "sequences": a.sequences, "frames_per_sequence": a.frames, "scan_points": a.scan_points, "concurrent_per_rank": a.concurrent, "updates": int(upd),
                           "ms_per_frame_wall": 1e3 * dt * world / max(upd, 1.0), "mode": "V1" if a.mode == 1 else "V3",
                           "map_points_seq0": r[min(r)]["map_points"], "scaling": "weak per sequence, no collective",
                           "note": "wall clock through the public API (host scans, upload, update, map_incremental, per-sequence context create/destroy)"}))

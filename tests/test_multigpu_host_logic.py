@@ -174,3 +174,11 @@ def test_replay_sequences_control_flow(pkg):
             assert np.array_equal(r[s]["x"], np.full(24, float(s) + 1.0))
         seen.update(r)
     assert sorted(seen) == list(range(5))
+    # concurrent sequences of one rank (one host thread and context each): same results, one context per sequence
+    _FakeFlivo.log = []
+    r = sh.replay_sequences(fake, seqs, 0, 1, np.eye(18), cfg, ds=0.5, concurrent=3)
+    assert sorted(r) == list(range(5)) and len(_FakeFlivo.log) == 5
+    for s in range(5):
+        assert r[s]["updates"] == seen[s]["updates"] and r[s]["work"] == seen[s]["work"] and np.array_equal(r[s]["x"], seen[s]["x"])
+    for calls in _FakeFlivo.log:
+        assert calls[1:3] == ["trip", "build"] and calls[-1] == "close"      # no interleaving inside a context
