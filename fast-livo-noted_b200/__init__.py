@@ -105,6 +105,9 @@ SYMBOLS = [
     "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps", "flivo_debug_search_stamps",
     "flivo_raw_upload", "flivo_raw_set_device", "flivo_raw_undistort", "flivo_raw_downsample", "flivo_raw_download",
     "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach", "flivo_set_gnss",
+    "flivo_peer_local_base", "flivo_peer_attach_local", "flivo_peer_set_timeout", "flivo_peer_reset",
+    "flivo_scan_upload_async", "flivo_scan_commit", "flivo_host_register", "flivo_host_unregister",
+    "flivo_iekf_update_begin", "flivo_iekf_update_end",
 ]
 
 _lib = None
@@ -143,6 +146,12 @@ def lib():
     L.flivo_knn.argtypes = [vp, vp, sz, sz, C.c_int, C.c_double, vp, vp, vp, vp]
     L.flivo_scan_upload.argtypes = [vp, vp, sz, sz]
     L.flivo_scan_set_device.argtypes = [vp, vp, sz]
+    L.flivo_scan_upload_async.argtypes = [vp, vp, sz, sz]
+    L.flivo_scan_commit.argtypes = [vp]
+    L.flivo_host_register.argtypes = [vp, sz]
+    L.flivo_host_unregister.argtypes = [vp]
+    L.flivo_iekf_update_begin.argtypes = [vp, C.POINTER(State), vp, C.POINTER(Cfg)]
+    L.flivo_iekf_update_end.argtypes = [vp, C.POINTER(State), vp, C.POINTER(Report)]
     L.flivo_h_share_model.argtypes = [vp, C.POINTER(State), C.c_int, C.c_int, vp, vp, C.POINTER(i32),
                                       C.POINTER(C.c_double), vp, vp, vp, vp, vp, vp]
     L.flivo_repack_v1.argtypes = [vp, vp, C.c_double, vp, vp]
@@ -158,6 +167,10 @@ def lib():
     L.flivo_peer_export.argtypes = [vp, vp]
     L.flivo_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
     L.flivo_peer_detach.argtypes = [vp]
+    L.flivo_peer_local_base.argtypes = [vp, C.POINTER(vp)]
+    L.flivo_peer_attach_local.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int]
+    L.flivo_peer_set_timeout.argtypes = [vp, C.c_double]
+    L.flivo_peer_reset.argtypes = [vp]
     L.flivo_raw_upload.argtypes = [vp, vp, sz, sz, C.c_int, C.c_int]
     L.flivo_raw_set_device.argtypes = [vp, vp, vp, sz]
     L.flivo_raw_undistort.argtypes = [vp, C.POINTER(Pose6D), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
@@ -313,6 +326,28 @@ class Flivo:
         self._ck(self._L.flivo_scan_upload(self.h, _ptr(a), n, st))
         self.n_scan = n
 
+    def scan_upload_async(self, rec, stride_bytes=None):
+        """Stage the NEXT scan (any (n, k) float32 records with xyz first; pinned / registered arrays travel by DMA as they
+        are).  The array must stay alive until scan_commit()."""
+        assert rec.dtype == np.float32 and rec.flags["C_CONTIGUOUS"] and rec.ndim == 2
+        self._next_scan = rec
+        self._ck(self._L.flivo_scan_upload_async(self.h, rec.ctypes.data, rec.shape[0], stride_bytes or rec.strides[0]))
+
+    def scan_commit(self):
+        self._ck(self._L.flivo_scan_commit(self.h))
+        self.n_scan = self._next_scan.shape[0]
+
+    def iekf_update_begin(self, st, P, cfg):
+        np_ = 18 if cfg.mode == MODE_V1 else 23
+        self._upd = (st.copy(), np.ascontiguousarray(P, dtype=np.float64).reshape(np_, np_).copy(), cfg)
+        self._ck(self._L.flivo_iekf_update_begin(self.h, C.byref(self._upd[0]), _ptr(self._upd[1]), C.byref(cfg)))
+
+    def iekf_update_end(self):
+        x, Pm, _ = self._upd
+        rep = Report()
+        self._ck(self._L.flivo_iekf_update_end(self.h, C.byref(x), _ptr(Pm), C.byref(rep)))
+        return x, Pm, rep
+
     def scan_set_device(self, dev_ptr, n):
         self._ck(self._L.flivo_scan_set_device(self.h, C.c_void_p(dev_ptr), n))
         self.n_scan = n
@@ -460,6 +495,22 @@ class Flivo:
 
     def peer_detach(self):
         self._ck(self._L.flivo_peer_detach(self.h))
+
+    def peer_local_base(self):
+        """Device pointer of this context's exchange buffer (ranks that live in one process)."""
+        out = C.c_void_p()
+        self._ck(self._L.flivo_peer_local_base(self.h, C.byref(out)))
+        return out.value
+
+    def peer_attach_local(self, bases, rank, nranks):
+        arr = (C.c_void_p * nranks)(*bases)
+        self._ck(self._L.flivo_peer_attach_local(self.h, arr, rank, nranks))
+
+    def peer_set_timeout(self, seconds):
+        self._ck(self._L.flivo_peer_set_timeout(self.h, float(seconds)))
+
+    def peer_reset(self):
+        self._ck(self._L.flivo_peer_reset(self.h))
 
     def comm_destroy(self):
         self._ck(self._L.flivo_comm_destroy(self.h))

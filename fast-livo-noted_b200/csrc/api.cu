@@ -66,13 +66,26 @@ constexpr int SSTAMP_CTAS = 4096;
 // Per-scan scalars of the staging sequence (keys -> radix sort -> gather), resident in HBM so that the captured graph of
 // the sequence never changes its kernel parameters: a call rewrites this block through the graph's own H2D copy node.
 struct ScanJob {
-    const float4* src;    // the scan in the caller's order
+    const char* src;      // the scan in the caller's order: n records of `stride` bytes, x y z in the first 12
+    unsigned int stride;
     unsigned int n;       // scan points
     unsigned int n_pad;   // items handed to the radix sort: n rounded up to SCAN_PAD (padding keys sort last)
     float inv_edge;
-    int pad;
 };
 constexpr unsigned int SCAN_PAD = 8192;
+
+// One of the two landing buffers of flivo_scan_upload_async: while the update of the current scan runs on the context's
+// stream, the next scan travels host -> device on the copy stream into the other slot.
+struct ScanSlot {
+    char* d_in = nullptr;           // device copy of the caller's records (their own stride when the source is pinned
+    size_t d_bytes = 0;             //   memory, else the float4 repack)
+    float4* h_pin = nullptr;        // pinned repack buffer (pageable sources only)
+    size_t h_n = 0;
+    cudaEvent_t copied = nullptr;   // the H2D copy into d_in has finished (copy stream)
+    cudaEvent_t consumed = nullptr; // the staging sequence that reads d_in has run (context stream)
+    bool copy_pending = false, filled = false;
+    size_t n = 0, stride = 0;
+};
 
 struct flivo_ctx {
     int device = 0;
@@ -96,7 +109,20 @@ struct flivo_ctx {
     bool scan_sorted = false;
     float4* d_body = nullptr;       // processing order: d_body_own or the caller's device pointer
     float4* d_body_own = nullptr;
-    float4* d_body_in = nullptr;    // caller's order (only when sorted)
+    float4* d_body_in = nullptr;    // caller's order, float4 (written by k_scan_prepare)
+    ScanSlot slot[2];               // flivo_scan_upload_async landing buffers; `back` is the one the next upload fills
+    int back = 0;
+    cudaStream_t copy = nullptr;    // H2D copies of scans, beside the update running on `stream`
+    // a committed / set scan is staged (keys, sort, gather, flag reset) lazily, right before its first consumer, so that
+    // the staging graph and the update graph are launched back to back from inside one call
+    bool stage_todo = false;
+    const char* todo_src = nullptr;
+    size_t todo_stride = 0;
+    int todo_slot = -1;
+    cudaEvent_t ev_stage0 = nullptr, ev_upd0 = nullptr, ev_upd1 = nullptr;   // in-graph time stamps (external event nodes)
+    // an update launched by flivo_iekf_update_begin and not yet collected by flivo_iekf_update_end
+    struct { bool active = false; int np = 0, trips = 0, launches = 0; bool timed = false, staged = false; } upd;
+    int graph_skip = 0;             // calls left on plain launches after the graph cache kept missing
     unsigned int* d_perm = nullptr; // processing index -> caller's index
     unsigned long long *d_skey_a = nullptr, *d_skey_b = nullptr;
     unsigned int* d_sidx_a = nullptr;
@@ -114,6 +140,7 @@ struct flivo_ctx {
     float4 *d_normvec = nullptr, *d_world = nullptr;
     double *d_partials = nullptr, *d_gpartials = nullptr;
     unsigned int* d_group_cnt = nullptr;
+    size_t group_slots = 0;
     unsigned long long* d_far_list = nullptr;
     float4* d_plane = nullptr;
     unsigned char* d_pflags = nullptr;
@@ -138,9 +165,7 @@ struct flivo_ctx {
     SearchStats* d_stats = nullptr;
     unsigned long long* d_stamps = nullptr;   // [MAX_TRIPS][16] k_solve phase stamps (profile mode)
     unsigned long long* d_sstamps = nullptr;  // [SSTAMP_CTAS][4] k_search per-CTA stamps (profile mode)
-    SolvePre* d_pre = nullptr;                // state-only half of a trip's solve (k_solve_pre -> k_solve)
-    cudaStream_t side = nullptr;              // branch of the update graph that runs k_solve_pre beside the search
-    cudaEvent_t ev_fork[MAX_TRIPS + 1] = {}, ev_join[MAX_TRIPS + 1] = {};
+    SolvePre* d_pre = nullptr;                // state-only half of a trip's solve (solve_pre -> next trip's solve_trip)
     double *d_x = nullptr, *d_xprop = nullptr, *d_Pprop = nullptr, *d_Pout = nullptr, *d_sum = nullptr, *d_rank_blocks = nullptr;
     // captured launch sequence of one update (CUDA graph), re-captured only when a kernel parameter changes
     cudaGraphExec_t graph_exec = nullptr;
@@ -166,6 +191,9 @@ struct flivo_ctx {
     unsigned long long* d_xseq = nullptr;
     PeerSlot* peer_base[PEER_MAX_RANKS] = {};
     bool peer_on = false;
+    bool peer_local = false;                  // peers attached by device pointer (same process), nothing to close
+    bool peer_broken = false;                 // an exchange timed out: updates are refused until flivo_peer_reset
+    unsigned long long peer_timeout_ns = 2000000000ull;
 };
 
 #define CKC(call)                                                                        \
@@ -266,14 +294,25 @@ __device__ __forceinline__ unsigned long long spread21(unsigned int v) {
     x = (x | x << 2) & 0x1249249249249249ull;
     return x;
 }
-__global__ void k_scan_keys(const ScanJob* __restrict__ J, unsigned long long* keys, unsigned int* idx) {
+// caller's records (any stride: the 48-byte PointXYZINormal AoS arrives as it is) -> float4 in the caller's order, plus,
+// when the scan is sorted (keys != nullptr), the Morton key of the point's cell and the identity index
+__global__ void k_scan_prepare(const ScanJob* __restrict__ J, float4* __restrict__ in4, unsigned long long* keys, unsigned int* idx) {
     const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     const unsigned n = J->n;
     if (i >= J->n_pad) return;
-    idx[i] = (unsigned int)i;
-    if (i >= n) { keys[i] = 0xFFFFFFFFFFFFFFFFull; return; }   // padding: largest key, and (stable sort) behind every real point
+    if (keys) idx[i] = (unsigned int)i;
+    if (i >= n) { if (keys) keys[i] = 0xFFFFFFFFFFFFFFFFull; return; }   // padding: largest key, and (stable sort) behind every real point
     const float inv_edge = J->inv_edge;
-    float4 p = J->src[i];
+    const unsigned stride = J->stride;
+    float4 p;
+    if (stride == 16) {
+        p = reinterpret_cast<const float4*>(J->src)[i];
+    } else {
+        const float* r = reinterpret_cast<const float*>(J->src + i * (size_t)stride);
+        p = make_float4(r[0], r[1], r[2], 0.f);
+    }
+    in4[i] = p;
+    if (!keys) return;
     float fx = fminf(fmaxf(floorf(p.x * inv_edge), -1048575.f), 1048575.f);
     float fy = fminf(fmaxf(floorf(p.y * inv_edge), -1048575.f), 1048575.f);
     float fz = fminf(fmaxf(floorf(p.z * inv_edge), -1048575.f), 1048575.f);
@@ -282,11 +321,11 @@ __global__ void k_scan_keys(const ScanJob* __restrict__ J, unsigned long long* k
 }
 // gather the scan into processing order and (when the arrays are given) reset the per-point flags of a fresh scan in
 // the same pass: sel = 1, eff = 0, pflags = 0 (see finish_scan)
-__global__ void k_gather4(const ScanJob* __restrict__ J, const unsigned int* __restrict__ perm, float4* __restrict__ out,
+__global__ void k_gather4(const ScanJob* __restrict__ J, const float4* __restrict__ in4, const unsigned int* __restrict__ perm, float4* __restrict__ out,
                           unsigned char* __restrict__ sel, unsigned char* __restrict__ eff, unsigned char* __restrict__ pflags) {
     const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= J->n) return;
-    out[i] = J->src[perm[i]];
+    out[i] = in4[perm[i]];
     sel[i] = 1; eff[i] = 0; pflags[i] = 0;
 }
 // out[perm[i]*elems + e] = in[i*elems + e]   (processing order -> caller's order); perm == nullptr: identity
@@ -352,11 +391,6 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     CKC(cudaMalloc(&ctx->d_blk, sizeof(DevBlock)));
     CKC(cudaMalloc(&ctx->d_sstamps, ((size_t)SSTAMP_CTAS * 4 + 32) * sizeof(unsigned long long)));
     CKC(cudaMalloc(&ctx->d_pre, sizeof(SolvePre)));
-    CKC(cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking));
-    for (int i = 0; i <= MAX_TRIPS; ++i) {
-        CKC(cudaEventCreateWithFlags(&ctx->ev_fork[i], cudaEventDisableTiming));
-        CKC(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
-    }
     CKC(cudaMalloc(&ctx->d_stamps, MAX_TRIPS * 16 * sizeof(unsigned long long)));
     CKC(cudaMemset(ctx->d_stamps, 0, MAX_TRIPS * 16 * sizeof(unsigned long long)));
     CKC(cudaMemsetAsync(ctx->d_blk, 0, sizeof(DevBlock), ctx->stream));
@@ -371,6 +405,12 @@ static int ctx_init(flivo_ctx* ctx, int device, const flivo_options* opt) {
     CKC(cudaEventCreateWithFlags(&ctx->sjob_ev, cudaEventDisableTiming));
     for (auto& e : ctx->ev) CKC(cudaEventCreate(&e));
     CKC(cudaEventCreateWithFlags(&ctx->stage_ev, cudaEventDisableTiming));
+    CKC(cudaStreamCreateWithFlags(&ctx->copy, cudaStreamNonBlocking));
+    for (auto& sl : ctx->slot) {
+        CKC(cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming));
+        CKC(cudaEventCreateWithFlags(&sl.consumed, cudaEventDisableTiming));
+    }
+    CKC(cudaEventCreate(&ctx->ev_stage0)); CKC(cudaEventCreate(&ctx->ev_upd0)); CKC(cudaEventCreate(&ctx->ev_upd1));
     CKC(cudaStreamSynchronize(ctx->stream));
     return FLIVO_OK;
 }
@@ -413,13 +453,11 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     free_scan(ctx);
     free_raw(ctx);
     cudaFree(ctx->d_vg_state); cudaFree(ctx->d_poses);
-    if (ctx->peer_on) for (int r = 0; r < ctx->nranks; ++r) if (r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
+    if (ctx->peer_on && !ctx->peer_local) for (int r = 0; r < ctx->nranks; ++r) if (r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
     cudaFree(ctx->d_xchg); cudaFree(ctx->d_xseq);
     cudaFree(ctx->d_ivox_flags); cudaFree(ctx->d_ivox_sel);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
     cudaFree(ctx->d_stage); cudaFree(ctx->d_out); cudaFree(ctx->d_blk); cudaFree(ctx->d_stamps); cudaFree(ctx->d_sstamps); cudaFree(ctx->d_pre);
-    for (int i = 0; i <= MAX_TRIPS; ++i) { if (ctx->ev_fork[i]) cudaEventDestroy(ctx->ev_fork[i]); if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]); }
-    if (ctx->side) cudaStreamDestroy(ctx->side);
     cudaFree(ctx->d_rank_blocks);
     if (ctx->h_blk) cudaFreeHost(ctx->h_blk);
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
@@ -429,6 +467,14 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     if (ctx->sjob_ev) cudaEventDestroy(ctx->sjob_ev);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->stage_ev) cudaEventDestroy(ctx->stage_ev);
+    if (ctx->copy) { cudaStreamSynchronize(ctx->copy); cudaStreamDestroy(ctx->copy); }
+    for (auto& sl : ctx->slot) {
+        cudaFree(sl.d_in);
+        if (sl.h_pin) cudaFreeHost(sl.h_pin);
+        if (sl.copied) cudaEventDestroy(sl.copied);
+        if (sl.consumed) cudaEventDestroy(sl.consumed);
+    }
+    for (cudaEvent_t e : {ctx->ev_stage0, ctx->ev_upd0, ctx->ev_upd1}) if (e) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -616,99 +662,209 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
         groups = max_grid / FOLD_CTAS + 1;
         CKC(cudaMalloc(&ctx->d_partials, max_grid * PSTRIDE * sizeof(double)));   // one record per CTA of k_fused
         CKC(cudaMalloc(&ctx->d_gpartials, groups * PSTRIDE * sizeof(double)));   // one record per FOLD_CTAS CTAs
-        CKC(cudaMalloc(&ctx->d_group_cnt, groups * sizeof(unsigned int)));
+        CKC(cudaMalloc(&ctx->d_group_cnt, (groups + 1) * sizeof(unsigned int)));   // + the ticket of the group folders
         CKC(cudaMalloc(&ctx->d_far_list, cap * sizeof(unsigned long long)));
         CKC(cudaMemsetAsync(ctx->d_far_list, 0, cap * sizeof(unsigned long long), ctx->stream));   // tag 0 = never valid
         CKC(cudaMalloc(&ctx->d_plane, cap * sizeof(float4)));
         CKC(cudaMalloc(&ctx->d_pflags, cap));
-        CKC(cudaMemsetAsync(ctx->d_group_cnt, 0, groups * sizeof(unsigned int), ctx->stream));
+        CKC(cudaMemsetAsync(ctx->d_group_cnt, 0, (groups + 1) * sizeof(unsigned int), ctx->stream));
+        ctx->group_slots = groups;
         ctx->scan_cap = cap;
     }
     return FLIVO_OK;
 }
 
-// after the caller-order scan is in `src` (device): optionally Morton-sort it into d_body
-static int finish_scan(flivo_ctx* ctx, const float4* src, size_t n, bool external) {
-    const bool sort = ctx->opt.sort_scan != 0;
-    if (sort) {
-        // keys -> radix sort -> gather as ONE captured graph (H2D of the ScanJob block, k_scan_keys, the CUB kernels,
-        // k_gather4): a single launch instead of seven, no launch gaps between the short kernels.  The graph depends only
-        // on the padded item count and the device pointers of this context; the scan pointer and n travel in ScanJob.
-        ctx->d_body = ctx->d_body_own;
+// A new current scan: n records of `stride` bytes at `src` (device memory; slot >= 0: the landing buffer they sit in).
+// Nothing is launched here: the staging sequence runs right before the scan's first consumer (ensure_staged), so that the
+// staging graph and the update graph are launched back to back from inside one call.
+static int finish_scan(flivo_ctx* ctx, const char* src, size_t stride, size_t n, bool external, int slot) {
+    ctx->scan_external = external;
+    ctx->scan_sorted = ctx->opt.sort_scan != 0;
+    ctx->scan_n = n;
+    ctx->stage_todo = true;
+    ctx->todo_src = src; ctx->todo_stride = stride; ctx->todo_slot = slot;
+    ctx->d_body = ctx->d_body_own;
+    if (!ctx->scan_sorted && external && stride == 16) ctx->d_body = (float4*)src;   // used in place, no copy
+    return FLIVO_OK;
+}
+
+// The staging sequence of the current scan, if it has not run yet:
+//   sorted scans : k_scan_prepare (records -> float4 in the caller's order + Morton keys) -> radix sort -> k_gather4
+//                  (processing order + flag reset) as ONE captured graph (H2D of the ScanJob block included): a single
+//                  launch, no launch gaps between the short kernels.  The graph depends only on the padded item count and
+//                  the device pointers of this context; source pointer, stride and n travel in ScanJob.
+//   unsorted     : k_scan_prepare alone (nothing at all for a float4 device pointer, which is used in place).
+// *staged tells the caller whether anything was enqueued (its time stamp ev_stage0 is then valid).
+static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
+    if (staged) *staged = false;
+    if (!ctx->stage_todo) return FLIVO_OK;
+    ctx->stage_todo = false;
+    const size_t n = ctx->scan_n;
+    const bool sort = ctx->scan_sorted;
+    cudaStream_t s = ctx->stream;
+    if (ctx->todo_slot >= 0) CKC(cudaStreamWaitEvent(s, ctx->slot[ctx->todo_slot].copied, 0));   // the records have landed
+    const bool in_place = !sort && ctx->d_body != ctx->d_body_own;
+    if (!in_place) {
         static int sb0 = -1, sb1 = -1;
         if (sb0 < 0) { const char* e = getenv("FLIVO_SORT_BITS"); if (!e || sscanf(e, "%d,%d", &sb0, &sb1) != 2) { sb0 = 6; sb1 = 22; } }
         // 16 of the Morton bits = two radix passes: cell bits 2..6 of x and y, 2..7 of z.  The two lowest bits per axis carry no
         // locality a 128-point tile can use; the bits above repeat every 51 m (102 m in z), so a tile may mix two or three
         // far-apart regions, which costs less than a third pass (0.5257 vs 0.5279 ms per 260 k-point update, 0.325 vs 0.334 at
         // 24 k points; dropping fine bits instead — 9..25 — loses 8 us of search time).  FLIVO_SORT_BITS=lo,hi overrides.
-        const unsigned n_pad = (unsigned)(((n + SCAN_PAD - 1) / SCAN_PAD) * SCAN_PAD);
+        const unsigned n_pad = sort ? (unsigned)(((n + SCAN_PAD - 1) / SCAN_PAD) * SCAN_PAD) : (unsigned)n;
         if (ctx->sjob_pending) { CKC(cudaEventSynchronize(ctx->sjob_ev)); ctx->sjob_pending = false; }
         ScanJob* J = ctx->h_sjob;
-        J->src = src; J->n = (unsigned)n; J->n_pad = n_pad; J->inv_edge = 1.0f / ctx->map.view().cell_edge; J->pad = 0;
-        if (!ctx->sort_exec || ctx->sort_npad != n_pad) {
-            if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; }
-            cudaGraph_t g = nullptr;
-            CKC(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
-            cudaError_t ce = cudaMemcpyAsync(ctx->d_sjob, ctx->h_sjob, sizeof(ScanJob), cudaMemcpyHostToDevice, ctx->stream);
-            k_scan_keys<<<nblk(n_pad, 256), 256, 0, ctx->stream>>>(ctx->d_sjob, ctx->d_skey_a, ctx->d_sidx_a);
-            size_t tmp = ctx->cub_bytes;
-            if (ce == cudaSuccess) ce = cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n_pad, sb0, sb1, ctx->stream);
-            k_gather4<<<nblk(n_pad, 256), 256, 0, ctx->stream>>>(ctx->d_sjob, ctx->d_perm, ctx->d_body, ctx->d_sel, ctx->d_eff, ctx->d_pflags);
-            cudaError_t ce2 = cudaStreamEndCapture(ctx->stream, &g);
-            if (ce != cudaSuccess || ce2 != cudaSuccess) {
-                if (g) cudaGraphDestroy(g);
-                ctx->err = std::string("capture of the scan staging graph: ") + cudaGetErrorString(ce != cudaSuccess ? ce : ce2);
-                return FLIVO_E_CUDA;
+        J->src = ctx->todo_src; J->stride = (unsigned)ctx->todo_stride; J->n = (unsigned)n; J->n_pad = n_pad;
+        J->inv_edge = 1.0f / ctx->map.view().cell_edge;
+        if (sort) {
+            if (!ctx->sort_exec || ctx->sort_npad != n_pad) {
+                if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; }
+                cudaGraph_t g = nullptr;
+                CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+                cudaError_t ce = cudaEventRecordWithFlags(ctx->ev_stage0, s, cudaEventRecordExternal);
+                if (ce == cudaSuccess) ce = cudaMemcpyAsync(ctx->d_sjob, ctx->h_sjob, sizeof(ScanJob), cudaMemcpyHostToDevice, s);
+                k_scan_prepare<<<nblk(n_pad, 256), 256, 0, s>>>(ctx->d_sjob, ctx->d_body_in, ctx->d_skey_a, ctx->d_sidx_a);
+                size_t tmp = ctx->cub_bytes;
+                if (ce == cudaSuccess) ce = cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n_pad, sb0, sb1, s);
+                k_gather4<<<nblk(n_pad, 256), 256, 0, s>>>(ctx->d_sjob, ctx->d_body_in, ctx->d_perm, ctx->d_body_own, ctx->d_sel, ctx->d_eff, ctx->d_pflags);
+                cudaError_t ce2 = cudaStreamEndCapture(s, &g);
+                if (ce != cudaSuccess || ce2 != cudaSuccess) {
+                    if (g) cudaGraphDestroy(g);
+                    ctx->err = std::string("capture of the scan staging graph: ") + cudaGetErrorString(ce != cudaSuccess ? ce : ce2);
+                    return FLIVO_E_CUDA;
+                }
+                ce = cudaGraphInstantiate(&ctx->sort_exec, g, 0);
+                cudaGraphDestroy(g);
+                if (ce != cudaSuccess) { ctx->sort_exec = nullptr; ctx->err = std::string("cudaGraphInstantiate (scan staging): ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
+                ctx->sort_npad = n_pad;
             }
-            ce = cudaGraphInstantiate(&ctx->sort_exec, g, 0);
-            cudaGraphDestroy(g);
-            if (ce != cudaSuccess) { ctx->sort_exec = nullptr; ctx->err = std::string("cudaGraphInstantiate (scan staging): ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
-            ctx->sort_npad = n_pad;
+            CKC(cudaGraphLaunch(ctx->sort_exec, s));
+        } else {
+            CKC(cudaEventRecord(ctx->ev_stage0, s));
+            CKC(cudaMemcpyAsync(ctx->d_sjob, ctx->h_sjob, sizeof(ScanJob), cudaMemcpyHostToDevice, s));
+            k_scan_prepare<<<nblk(n, 256), 256, 0, s>>>(ctx->d_sjob, ctx->d_body_own, nullptr, nullptr);
+            CKC(cudaGetLastError());
         }
-        CKC(cudaGraphLaunch(ctx->sort_exec, ctx->stream));
-        CKC(cudaEventRecord(ctx->sjob_ev, ctx->stream));
+        CKC(cudaEventRecord(ctx->sjob_ev, s));
         ctx->sjob_pending = true;
+        if (staged) *staged = true;
     }
-    ctx->scan_external = external;
-    ctx->scan_sorted = sort;
-    ctx->scan_n = n;
+    if (ctx->todo_slot >= 0) CKC(cudaEventRecord(ctx->slot[ctx->todo_slot].consumed, s));   // the slot may be refilled
     // point_selected_surf starts true (V3 global array semantics are re-established by the first search trip); no cached
     // neighbours yet: a re-use trip before any search selects nothing.  (Sorted scans: done inside k_gather4.)
     if (!sort) {
-        CKC(cudaMemsetAsync(ctx->d_sel, 1, n, ctx->stream));
-        CKC(cudaMemsetAsync(ctx->d_eff, 0, n, ctx->stream));
-        CKC(cudaMemsetAsync(ctx->d_pflags, 0, n, ctx->stream));
+        CKC(cudaMemsetAsync(ctx->d_sel, 1, n, s));
+        CKC(cudaMemsetAsync(ctx->d_eff, 0, n, s));
+        CKC(cudaMemsetAsync(ctx->d_pflags, 0, n, s));
     }
     // iVox mode reads the cached count outside the search (empty-result rule of GetClosestPoint, map_incremental's add rule)
     if (ctx->opt.ivox_nearby) {
-        CKC(cudaMemsetAsync(ctx->d_near_meta, 0, n * sizeof(float2), ctx->stream));
-        CKC(cudaMemsetAsync(ctx->d_near, 0xFF, n * 5 * sizeof(float4), ctx->stream));   // id -1 everywhere: a point that never finds a candidate reports an empty list
+        CKC(cudaMemsetAsync(ctx->d_near_meta, 0, n * sizeof(float2), s));
+        CKC(cudaMemsetAsync(ctx->d_near, 0xFF, n * 5 * sizeof(float4), s));   // id -1 everywhere: a point that never finds a candidate reports an empty list
     }
     return FLIVO_OK;
 }
 
-extern "C" int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes) {
+// ---- host -> device scan transfer, double buffered ------------------------------------------------------------------
+static bool host_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// feats_down_body of the NEXT frame (src/laser_mapping.cpp:129-130,165-167 hands one over per frame): the records travel on
+// the copy stream into the back slot while the update of the current scan runs.  Pinned / registered sources
+// (cudaHostRegister, flivo_host_register) are copied as they are — whole records, one DMA, no host work; the xyz gather
+// happens on the device (k_scan_prepare).  Pageable sources are repacked to float4 into a pinned buffer by a few host
+// threads first (chunked, each chunk's copy overlapping the repack of the next).
+extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes) {
     ENTER();
     NEED(n > 0 && body_xyz && stride_ok(stride_bytes), FLIVO_E_ARG, "bad scan / stride");
     NEED(n < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "scan too large");
-    const bool sort = ctx->opt.sort_scan != 0;
-    int rc = ensure_scan(ctx, n);
+    ScanSlot& sl = ctx->slot[ctx->back];
+    const bool pinned = host_pinned(body_xyz);
+    const size_t stride = pinned ? stride_bytes : 16, bytes = n * stride;
+    if (sl.copy_pending) { CKC(cudaEventSynchronize(sl.copied)); sl.copy_pending = false; }
+    if (bytes > sl.d_bytes) {
+        CKC(cudaEventSynchronize(sl.consumed));                 // (no-op for a never recorded event)
+        cudaFree(sl.d_in); sl.d_in = nullptr; sl.d_bytes = 0;
+        const size_t cap = std::max<size_t>(bytes + bytes / 8, 1u << 20);
+        CKC(cudaMalloc(&sl.d_in, cap));
+        sl.d_bytes = cap;
+    }
+    CKC(cudaStreamWaitEvent(ctx->copy, sl.consumed, 0));        // the staging that read this slot's previous content has run
+    if (pinned) {
+        CKC(cudaMemcpyAsync(sl.d_in, body_xyz, bytes, cudaMemcpyHostToDevice, ctx->copy));
+    } else {
+        if (n > sl.h_n) {
+            if (sl.h_pin) cudaFreeHost(sl.h_pin);
+            sl.h_pin = nullptr; sl.h_n = 0;
+            const size_t cap = std::max<size_t>(n + n / 4, 1u << 16);
+            CKC(cudaMallocHost(&sl.h_pin, cap * sizeof(float4)));
+            sl.h_n = cap;
+        }
+        const char* src = reinterpret_cast<const char*>(body_xyz);
+        float4* h = sl.h_pin;
+        const size_t CH = 1u << 15;
+        const int nt = host_threads();
+        for (size_t c0 = 0; c0 < n; c0 += CH) {
+            const size_t m = std::min(CH, n - c0);
+            if (stride_bytes == 16) {
+                memcpy(h + c0, src + c0 * 16, m * 16);
+            } else {
+#pragma omp parallel for num_threads(nt) schedule(static) if (m >= 8192 && nt > 1)
+                for (long i = 0; i < (long)m; ++i) {
+                    const float* p = reinterpret_cast<const float*>(src + (c0 + (size_t)i) * stride_bytes);
+                    h[c0 + i] = make_float4(p[0], p[1], p[2], 0.f);
+                }
+            }
+            CKC(cudaMemcpyAsync(sl.d_in + c0 * 16, h + c0, m * sizeof(float4), cudaMemcpyHostToDevice, ctx->copy));
+        }
+    }
+    CKC(cudaEventRecord(sl.copied, ctx->copy));
+    sl.copy_pending = true; sl.filled = true; sl.n = n; sl.stride = stride;
+    return FLIVO_OK;
+}
+
+// The scan uploaded last becomes the current scan (the update after this call works on it).
+extern "C" int flivo_scan_commit(flivo_ctx* ctx) {
+    ENTER();
+    ScanSlot& sl = ctx->slot[ctx->back];
+    NEED(sl.filled, FLIVO_E_STATE, "no scan uploaded since the last commit");
+    NEED(!ctx->upd.active, FLIVO_E_STATE, "an update is in flight (flivo_iekf_update_end first)");
+    int rc = ensure_scan(ctx, sl.n);
     if (rc) return rc;
-    float4* dst = sort ? ctx->d_body_in : ctx->d_body_own;
-    ctx->d_body = ctx->d_body_own;
-    if ((rc = stage_points(ctx, body_xyz, n, stride_bytes, dst))) return rc;
-    return finish_scan(ctx, dst, n, false);
+    sl.filled = false;
+    const int slot = ctx->back;
+    ctx->back ^= 1;
+    return finish_scan(ctx, sl.d_in, sl.stride, sl.n, false, slot);
+}
+
+extern "C" int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes) {
+    int rc = flivo_scan_upload_async(ctx, body_xyz, n, stride_bytes);
+    if (rc != FLIVO_OK) return rc;
+    return flivo_scan_commit(ctx);
+}
+
+// cudaHostRegister / cudaHostUnregister for callers without the CUDA headers: a registered scan buffer is copied by DMA
+// as it is (flivo_scan_upload_async), with no host-side repack.
+extern "C" int flivo_host_register(void* ptr, size_t bytes) {
+    if (!ptr || !bytes) return FLIVO_E_ARG;
+    return cudaHostRegister(ptr, bytes, cudaHostRegisterPortable) == cudaSuccess ? FLIVO_OK : (cudaGetLastError(), FLIVO_E_CUDA);
+}
+extern "C" int flivo_host_unregister(void* ptr) {
+    if (!ptr) return FLIVO_E_ARG;
+    return cudaHostUnregister(ptr) == cudaSuccess ? FLIVO_OK : (cudaGetLastError(), FLIVO_E_CUDA);
 }
 
 extern "C" int flivo_scan_set_device(flivo_ctx* ctx, const void* dev_xyzw, size_t n) {
     ENTER();
     NEED(n > 0 && dev_xyzw, FLIVO_E_ARG, "bad scan");
     NEED(n < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "scan too large");
-    const bool sort = ctx->opt.sort_scan != 0;
+    NEED(!ctx->upd.active, FLIVO_E_STATE, "an update is in flight (flivo_iekf_update_end first)");
     int rc = ensure_scan(ctx, n);
     if (rc) return rc;
-    if (!sort) ctx->d_body = (float4*)dev_xyzw;
-    return finish_scan(ctx, (const float4*)dev_xyzw, n, true);
+    return finish_scan(ctx, (const char*)dev_xyzw, 16, n, true, -1);
 }
 
 static FusedParams make_fused(flivo_ctx* ctx) {
@@ -722,6 +878,7 @@ static FusedParams make_fused(flivo_ctx* ctx) {
     P.plane = ctx->d_plane; P.pflags = ctx->d_pflags;
     P.normvec = ctx->d_normvec; P.world = ctx->d_world;
     P.partials = ctx->d_partials; P.gpartials = ctx->d_gpartials; P.group_cnt = ctx->d_group_cnt; P.far_list = ctx->d_far_list;
+    P.total_cnt = ctx->d_group_cnt + ctx->group_slots;
     P.ctl = ctx->d_ctl; P.stats = ctx->d_stats;
     return P;
 }
@@ -757,6 +914,16 @@ static int fused_grid(flivo_ctx* ctx) {
 // the fused path searches with the reference's own far-neighbour gate (pointSearchSqDis[4] > 5, src/laser_mapping.cpp:518)
 // as the distance bound: a point whose 5th neighbour lies beyond it is masked either way
 static uint32_t gate_bits() { float f = 5.0f; uint32_t b; memcpy(&b, &f, 4); return b; }
+// ... in V3 only.  There point_selected_surf is a persistent array, so a point gated out on a search trip stays out until
+// the next search (origin:963).  In V1 (the compiled path) the flags are a LOCAL vector<bool>(n, true) rebuilt on every call
+// (src/laser_mapping.cpp:490) and the gate is applied on search trips only (:518): on re-use trips a point whose fifth
+// neighbour lies beyond the gate still enters with its cached Nearest_Points if esti_plane accepts them.  V1 therefore
+// searches unbounded, exactly as the reference's Nearest_Search call (max_dist = INFINITY, ikd_Tree.h:174), keeps the five
+// neighbours and records the gate in PF_GATE alone.  (Sparse-fringe queries then walk more cells; iVox mode bounds the
+// range itself.)
+static uint32_t search_bound_bits(const flivo_ctx* ctx, int mode) {
+    return (mode == FLIVO_MODE_V1 && !ctx->opt.ivox_nearby) ? INF_BITS : gate_bits();
+}
 
 // copy a per-point device array to the host in the caller's order
 template <class T>
@@ -794,7 +961,9 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
     NEED(st && HTH && HTz, FLIVO_E_ARG, "null state / outputs");
     NEED(mode == FLIVO_MODE_V3 || mode == FLIVO_MODE_V1, FLIVO_E_ARG, "bad mode");
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
-    fill_job(ctx, mode, 1, 0, 0.001, nullptr, gate_bits(), 1);
+    NEED(!ctx->upd.active, FLIVO_E_STATE, "an update is in flight (flivo_iekf_update_end first)");
+    { int rcs = ensure_staged(ctx); if (rcs) return rcs; }
+    fill_job(ctx, mode, 1, 0, 0.001, nullptr, search_bound_bits(ctx, mode), 1);
     memcpy(ctx->h_blk->x, st, sizeof(flivo_state));
     CKC(cudaMemcpyAsync(&ctx->d_blk->job, &ctx->h_blk->job, sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
     CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_blk->x, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
@@ -802,11 +971,11 @@ extern "C" int flivo_h_share_model(flivo_ctx* ctx, const flivo_state* st, int mo
     if (do_search) CKC(cudaMemsetAsync(ctx->d_stats, 0, sizeof(SearchStats), ctx->stream));
     FusedParams P = make_fused(ctx);
     if (do_search) { const int sg = search_grid(ctx); launch_search(P, sg, ctx->stream, par_probes(ctx, sg)); }
-    launch_fused(P, fused_grid(ctx), ctx->stream);
-    SolveParams S{};
-    S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job; S.phase = SOLVE_PHASE_REDUCE_ONLY;
+    SolveParams S;
+    memset(&S, 0, sizeof(S));
+    S.job = &ctx->d_blk->job; S.phase = SOLVE_PHASE_REDUCE_ONLY;
     S.sum_out = ctx->d_sum; S.ctl = ctx->d_ctl;
-    launch_solve(S, ctx->stream);
+    launch_fused(P, S, fused_grid(ctx), ctx->stream);   // the CTA that folds the last record writes the sums (no solve)
     CKC(cudaGetLastError());
     double* hs = ctx->h_small + 64;
     CKC(cudaMemcpyAsync(hs, ctx->d_sum, NTERMS * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -863,24 +1032,22 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
     cudaStream_t s = ctx->stream;
     cudaGraph_t g = nullptr;
     CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-    SolveParams S = S0;   // S0.phase: FULL, or PEER when the peer-memory exchange is attached
+    const SolveParams& S = S0;   // S0.phase: FULL, or PEER when the peer-memory exchange is attached
     // the call's inputs (job + P_prop + x, from the pinned mirror), the control-block reset and, at the end, the results
-    // (x, P_out, ctl, stats -> pinned mirror) are nodes of the same graph: one launch per update
-    cudaError_t cio = cudaMemcpyAsync(ctx->d_blk, ctx->h_blk, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s);
-    launch_ctl_reset(ctx->d_blk->x, ctx->d_blk->x_prop, ctx->d_blk->P_prop, ctx->d_blk->P_out, ctx->d_ctl, ctx->d_stats, s);
+    // (x, P_out, ctl, stats -> pinned mirror) are nodes of the same graph: one launch per update.  A trip is two kernels:
+    // the solve runs inside k_fused (the CTA that folds the last record).
+    // The first and last nodes are event records (external events): the device time of an update is read between two
+    // stamps taken by the GPU itself, so it does not move when the host thread that launched the graph is descheduled.
+    cudaError_t cio = cudaEventRecordWithFlags(ctx->ev_upd0, s, cudaEventRecordExternal);
+    if (cio == cudaSuccess) cio = cudaMemcpyAsync(ctx->d_blk, ctx->h_blk, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s);
+    launch_ctl_reset(S, ctx->d_blk->x_prop, ctx->d_stats, s);
     for (int t = 0; t < trips && t <= MAX_TRIPS; ++t) {
-        // fork: the state-only half of the solve runs beside the search / fused kernels of the trip
-        CKC(cudaEventRecord(ctx->ev_fork[t], s));
-        CKC(cudaStreamWaitEvent(ctx->side, ctx->ev_fork[t], 0));
-        launch_solve_pre(S, ctx->side);
-        CKC(cudaEventRecord(ctx->ev_join[t], ctx->side));
         launch_search(P, sgrid, s, par_probes(ctx, sgrid));
-        launch_fused(P, fgrid, s);
-        CKC(cudaStreamWaitEvent(s, ctx->ev_join[t], 0));
-        launch_solve(S, s);
+        launch_fused(P, S, fgrid, s);
     }
     if (cio == cudaSuccess)
         cio = cudaMemcpyAsync(ctx->h_blk->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s);
+    if (cio == cudaSuccess) cio = cudaEventRecordWithFlags(ctx->ev_upd1, s, cudaEventRecordExternal);
     cudaError_t ce = cudaStreamEndCapture(s, &g);
     if (ce == cudaSuccess && cio != cudaSuccess) { ce = cio; if (g) cudaGraphDestroy(g); g = nullptr; }
     if (ce != cudaSuccess) { ctx->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce); return FLIVO_E_CUDA; }
@@ -890,23 +1057,28 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
     return FLIVO_OK;
 }
 
-extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm, const flivo_cfg* cfg, flivo_report* rep) {
+// The update in two halves, so that the caller can do host work (stage the next scan: flivo_scan_upload_async) while
+// the GPU runs this one: _begin launches everything and returns, _end waits and hands the results back.
+extern "C" int flivo_iekf_update_begin(flivo_ctx* ctx, const flivo_state* inout, const double* Pm, const flivo_cfg* cfg) {
     ENTER();
     NEED(inout && Pm && cfg, FLIVO_E_ARG, "null state / P / cfg");
+    NEED(!ctx->upd.active, FLIVO_E_STATE, "an update is already in flight (flivo_iekf_update_end first)");
     NEED(cfg->mode == FLIVO_MODE_V3 || cfg->mode == FLIVO_MODE_V1, FLIVO_E_ARG, "bad mode");
     NEED(cfg->max_iter >= 1 && cfg->max_iter + 1 <= MAX_TRIPS, FLIVO_E_ARG, "max_iter must be in 1..15");
     NEED(cfg->laser_point_cov > 0.0, FLIVO_E_ARG, "laser_point_cov must be > 0");
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
+    NEED(!(ctx->peer_on && ctx->peer_broken), FLIVO_E_STATE, "an earlier peer exchange timed out: call flivo_peer_reset on every rank (after a barrier) first");
     const int np = cfg->mode == FLIVO_MODE_V1 ? 18 : 23;
     const int trips = cfg->max_iter + 1;  // loop index -1 .. max_iter-1
     const bool timed = (cfg->flags & FLIVO_CFG_PROFILE) != 0;   // per-trip events, plain launches (no graph)
     cudaStream_t s = ctx->stream;
     DevBlock* h = ctx->h_blk;
-    fill_job(ctx, cfg->mode, cfg->max_iter, cfg->force_search, cfg->laser_point_cov, cfg->limit, gate_bits(), 0);
+    bool staged = false;
+    { int rcs = ensure_staged(ctx, &staged); if (rcs) return rcs; }   // staging graph and update graph go out back to back
+    fill_job(ctx, cfg->mode, cfg->max_iter, cfg->force_search, cfg->laser_point_cov, cfg->limit, search_bound_bits(ctx, cfg->mode), 0);
     memcpy(h->x, inout, sizeof(flivo_state));
     memset(h->P_prop, 0, sizeof(h->P_prop));
     memcpy(h->P_prop, Pm, sizeof(double) * np * np);
-    CKC(cudaEventRecord(ctx->ev[0], s));
     bool use_graph = !timed && (!ctx->comm || ctx->peer_on);   // an NCCL call between the kernels is not captured
     FusedParams P = make_fused(ctx);
     if (timed && search_grid(ctx) <= SSTAMP_CTAS) {
@@ -915,36 +1087,34 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     }
     SolveParams S;
     memset(&S, 0, sizeof(S));
-    S.gpartials = ctx->d_gpartials; S.job = &ctx->d_blk->job;
+    S.job = &ctx->d_blk->job;
     S.x = ctx->d_x; S.x_prop = ctx->d_xprop; S.P_prop = ctx->d_Pprop; S.P_out = ctx->d_Pout;
     S.sum_out = ctx->d_sum; S.rank_blocks = ctx->d_rank_blocks; S.ctl = ctx->d_ctl;
     S.stamps = timed ? ctx->d_stamps : nullptr;
     S.pre = ctx->d_pre;
     if (ctx->peer_on) {
         for (int r = 0; r < ctx->nranks; ++r) S.peer.base[r] = ctx->peer_base[r];
-        S.peer.seq = ctx->d_xseq; S.peer.rank = ctx->rank; S.peer.nranks = ctx->nranks;
+        S.peer.seq = ctx->d_xseq; S.peer.rank = ctx->rank; S.peer.nranks = ctx->nranks; S.peer.timeout_ns = ctx->peer_timeout_ns;
     }
     const int full_phase = ctx->peer_on ? SOLVE_PHASE_PEER : SOLVE_PHASE_FULL;
     const int sgrid = search_grid(ctx), fgrid = fused_grid(ctx);
     int launches = 1;
     auto launch_trip = [&](int t, bool with_events) -> int {
-        launch_solve_pre(S, s);                 // plain launches: in line (the graph runs it on a parallel branch)
         if (with_events) CKC(cudaEventRecord(ctx->ev[1 + 2 * t], s));
         launch_search(P, sgrid, s, par_probes(ctx, sgrid));   // exits at once on re-use trips
-        launch_fused(P, fgrid, s);
         if (with_events) CKC(cudaEventRecord(ctx->ev[2 + 2 * t], s));
         if (ctx->comm && !ctx->peer_on) {
-            S.phase = SOLVE_PHASE_REDUCE_ONLY;
-            launch_solve(S, s);
+            S.phase = SOLVE_PHASE_REDUCE_ONLY;          // k_fused leaves this rank's sums in d_sum
+            launch_fused(P, S, fgrid, s);
             int nrc = g_nccl.AllGather(ctx->d_sum, ctx->d_rank_blocks, PSTRIDE, NCCL_DOUBLE, ctx->comm, s);
             if (nrc != 0) { ctx->err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "error"); return FLIVO_E_NCCL; }
             S.phase = SOLVE_PHASE_FROM_RANKS;
-            launch_solve(S, s);
-            launches += 5;
+            launch_solve_ranks(S, s);
+            launches += 4;
         } else {
             S.phase = full_phase;
-            launch_solve(S, s);
-            launches += 4;
+            launch_fused(P, S, fgrid, s);              // Gram + (in its last CTA) the solve
+            launches += 2;
         }
         return FLIVO_OK;
     };
@@ -954,8 +1124,14 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
         const bool same = ctx->graph_exec && memcmp(&P, &ctx->graph_P, sizeof(P)) == 0 && memcmp(&S, &ctx->graph_S, sizeof(S)) == 0 &&
                           sgrid == ctx->graph_search_grid && fgrid == ctx->graph_fused_grid && trips == ctx->graph_trips;
         if (!same) {
-            if (++ctx->graph_churn > 3) {
-                use_graph = false;   // parameters keep changing (e.g. a new external scan pointer every call): plain launches
+            // parameters that keep changing (e.g. a new external unsorted scan pointer every call) would re-capture on every
+            // call: after three misses in a row fall back to plain launches for 16 calls, then try the graph again
+            if (ctx->graph_skip > 0) {
+                --ctx->graph_skip;
+                use_graph = false;
+            } else if (++ctx->graph_churn > 3) {
+                use_graph = false;
+                ctx->graph_churn = 0; ctx->graph_skip = 16;
             } else {
                 if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
                 int rc = build_update_graph(ctx, P, S, sgrid, fgrid, trips);
@@ -969,26 +1145,47 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
     }
     if (use_graph) {
         CKC(cudaGraphLaunch(ctx->graph_exec, s));   // H2D of the inputs, control reset, the trips, D2H of the results
-        launches = 1 + trips * 4;
+        launches = 1 + trips * 2;
     } else {
+        CKC(cudaEventRecord(ctx->ev_upd0, s));
         CKC(cudaMemcpyAsync(ctx->d_blk, h, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s));   // job + P_prop + x
-        launch_ctl_reset(ctx->d_blk->x, ctx->d_blk->x_prop, ctx->d_blk->P_prop, ctx->d_blk->P_out, ctx->d_ctl, ctx->d_stats, s);
+        S.phase = full_phase;
+        launch_ctl_reset(S, ctx->d_blk->x_prop, ctx->d_stats, s);
         launches = 1;
         for (int t = 0; t < trips; ++t) { int rc = launch_trip(t, timed); if (rc != FLIVO_OK) return rc; }
     }
     CKC(cudaGetLastError());
-    CKC(cudaEventRecord(ctx->ev[1 + 2 * trips], s));
-    if (!use_graph) CKC(cudaMemcpyAsync(h->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s));   // x, P_out, ctl, stats
-    CKC(cudaStreamSynchronize(s));
-    memcpy(inout, h->x, sizeof(flivo_state));
-    memcpy(Pm, h->P_out, sizeof(double) * np * np);
+    if (!use_graph) {
+        CKC(cudaEventRecord(ctx->ev[1 + 2 * trips], s));
+        CKC(cudaMemcpyAsync(h->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s));   // x, P_out, ctl, stats
+        CKC(cudaEventRecord(ctx->ev_upd1, s));
+    }
+    ctx->upd.active = true; ctx->upd.np = np; ctx->upd.trips = trips; ctx->upd.launches = launches + (staged ? 2 : 0);
+    ctx->upd.timed = timed; ctx->upd.staged = staged;
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_iekf_update_end(flivo_ctx* ctx, flivo_state* inout, double* Pm, flivo_report* rep) {
+    ENTER();
+    NEED(inout && Pm, FLIVO_E_ARG, "null state / P");
+    NEED(ctx->upd.active, FLIVO_E_STATE, "no update in flight (flivo_iekf_update_begin first)");
+    ctx->upd.active = false;
+    const int np = ctx->upd.np, trips = ctx->upd.trips, launches = ctx->upd.launches;
+    const bool timed = ctx->upd.timed;
+    DevBlock* h = ctx->h_blk;
+    CKC(cudaStreamSynchronize(ctx->stream));
     const Ctl& c = h->ctl;
+    if (c.nan_guard != 2) {   // (a timed-out peer exchange may have stopped the loop after some trips: nothing is handed back)
+        memcpy(inout, h->x, sizeof(flivo_state));
+        memcpy(Pm, h->P_out, sizeof(double) * np * np);
+    }
     ctx->stats.last_far_queries = (int64_t)h->stats.far_queries;
     ctx->stats.last_candidates = (int64_t)h->stats.candidates;
     for (int t = 0; t < 16; ++t) { ctx->stats.last_fused_ms[t] = 0.f; ctx->stats.last_solve_ms[t] = 0.f; ctx->stats.last_trip_searched[t] = 0; }
     for (int t = 0; t < trips && t < 16; ++t) {
         if (timed) {
-            cudaEventElapsedTime(&ctx->stats.last_fused_ms[t], ctx->ev[1 + 2 * t], ctx->ev[2 + 2 * t]);
+            // (profile mode) last_fused_ms = the whole trip: k_search + k_fused incl. its solve; last_solve_ms = the k_fused part
+            cudaEventElapsedTime(&ctx->stats.last_fused_ms[t], ctx->ev[1 + 2 * t], ctx->ev[3 + 2 * t]);
             cudaEventElapsedTime(&ctx->stats.last_solve_ms[t], ctx->ev[2 + 2 * t], ctx->ev[3 + 2 * t]);
         }
         ctx->stats.last_trip_searched[t] = t < c.trips ? c.trip_searched[t] : 0;
@@ -998,11 +1195,23 @@ extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm,
         rep->trips = c.trips; rep->searches = c.searches; rep->n_eff = c.n_eff; rep->converged = c.converged;
         rep->res_mean = c.res_mean;
         for (int i = 0; i < 23; ++i) rep->dx_last[i] = c.dx_last[i];
-        cudaEventElapsedTime(&rep->gpu_ms, ctx->ev[0], ctx->ev[1 + 2 * trips]);
-        rep->kernel_launches = launches;
+        // device time from the first staging node (when this update staged its scan) to the last node of the update
+        cudaEventElapsedTime(&rep->gpu_ms, ctx->upd.staged ? ctx->ev_stage0 : ctx->ev_upd0, ctx->ev_upd1);
+        rep->kernel_launches = launches;   // own kernels: k_ctl_reset + 2 per trip (+ k_scan_prepare, k_gather4 when the scan was staged here)
     }
-    if (c.nan_guard) { ctx->err = ctx->peer_on ? "non-finite normal equations or peer exchange timed out: update skipped" : "non-finite normal equations: update skipped"; return FLIVO_E_STATE; }
+    if (c.nan_guard == 2) {
+        ctx->peer_broken = true;
+        ctx->err = "peer exchange timed out: update skipped; the ranks are out of step until every rank calls flivo_peer_reset (after a barrier)";
+        return FLIVO_E_STATE;
+    }
+    if (c.nan_guard) { ctx->err = "non-finite normal equations: update skipped"; return FLIVO_E_STATE; }
     return FLIVO_OK;
+}
+
+extern "C" int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* Pm, const flivo_cfg* cfg, flivo_report* rep) {
+    int rc = flivo_iekf_update_begin(ctx, inout, Pm, cfg);
+    if (rc != FLIVO_OK) return rc;
+    return flivo_iekf_update_end(ctx, inout, Pm, rep);
 }
 
 // iVox branch of map_incremental (src/laser_mapping.cpp:340-387); the state is already in d_x
@@ -1064,15 +1273,13 @@ extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t
     if (n_added) *n_added = 0;
     NEED(st, FLIVO_E_ARG, "null state");
     NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
+    NEED(!ctx->upd.active, FLIVO_E_STATE, "an update is in flight (flivo_iekf_update_end first)");
+    { int rcs = ensure_staged(ctx); if (rcs) return rcs; }
     memcpy(ctx->h_blk->x, st, sizeof(flivo_state));
     CKC(cudaMemcpyAsync(ctx->d_x, ctx->h_blk->x, sizeof(flivo_state), cudaMemcpyHostToDevice, ctx->stream));
     if (ctx->opt.ivox_nearby) return ivox_add_scan(ctx, n_added);
     // Add_Points is order dependent only through ties; keep the caller's order (batch index = insertion id order)
-    const float4* src = ctx->scan_sorted ? ctx->d_body_in : ctx->d_body;
-    if (ctx->scan_sorted && ctx->scan_external) {
-        // the caller-order copy was never made for an external sorted scan: un-permute d_body into d_body_in
-        k_scatter<float4><<<nblk(ctx->scan_n, 256), 256, 0, ctx->stream>>>(ctx->d_body, ctx->d_perm, ctx->scan_n, 1, ctx->d_body_in);
-    }
+    const float4* src = ctx->scan_sorted ? ctx->d_body_in : ctx->d_body;   // (k_scan_prepare keeps the caller-order float4 copy)
     launch_transform(src, (int)ctx->scan_n, ctx->d_x, ctx->d_world, ctx->stream);
     CKC(cudaGetLastError());
     int added = 0;
@@ -1161,7 +1368,53 @@ extern "C" int flivo_peer_attach(flivo_ctx* ctx, const void* handles, int rank, 
         ctx->peer_base[r] = static_cast<PeerSlot*>(p);
     }
     ctx->rank = rank; ctx->nranks = nranks;
-    ctx->peer_on = true;
+    ctx->peer_on = true; ctx->peer_local = false; ctx->peer_broken = false;
+    return FLIVO_OK;
+}
+
+// Same exchange between contexts of ONE process (several GPUs driven by one process, or several ranks on one GPU as the
+// tests and the sanitizer runs do): cudaIpc handles cannot be opened by the process that exported them, so the ranks
+// pass each other their buffers as device pointers.  With distinct devices, peer access must be enabled by the caller.
+extern "C" int flivo_peer_local_base(flivo_ctx* ctx, void** base_out) {
+    ENTER();
+    NEED(base_out, FLIVO_E_ARG, "null out");
+    char h[FLIVO_PEER_HANDLE_BYTES];
+    int rc = flivo_peer_export(ctx, h);   // allocates the buffer on first use
+    if (rc != FLIVO_OK) return rc;
+    *base_out = ctx->d_xchg;
+    return FLIVO_OK;
+}
+extern "C" int flivo_peer_attach_local(flivo_ctx* ctx, void* const* bases, int rank, int nranks) {
+    ENTER();
+    NEED(bases && nranks >= 1 && nranks <= PEER_MAX_RANKS && rank >= 0 && rank < nranks, FLIVO_E_ARG, "bad rank / nranks (<= 8) / bases");
+    NEED(ctx->d_xchg, FLIVO_E_STATE, "call flivo_peer_local_base first");
+    NEED(!ctx->peer_on, FLIVO_E_STATE, "peers already attached");
+    NEED(bases[rank] == (void*)ctx->d_xchg, FLIVO_E_ARG, "bases[rank] is not this context's buffer");
+    for (int r = 0; r < nranks; ++r) { NEED(bases[r], FLIVO_E_ARG, "null base"); ctx->peer_base[r] = static_cast<PeerSlot*>(bases[r]); }
+    ctx->rank = rank; ctx->nranks = nranks;
+    ctx->peer_on = true; ctx->peer_local = true; ctx->peer_broken = false;
+    return FLIVO_OK;
+}
+
+// Re-arm the exchange after a time-out (or before reusing a set of ranks): zeroes this rank's sequence counter and its
+// exchange buffer.  Every rank must call it, with a barrier of the caller's before (no update in flight anywhere) and
+// after (no rank starts an update while another still clears its buffer).
+extern "C" int flivo_peer_reset(flivo_ctx* ctx) {
+    ENTER();
+    NEED(ctx->d_xchg, FLIVO_E_STATE, "no exchange buffer (flivo_peer_export first)");
+    CKC(cudaStreamSynchronize(ctx->stream));
+    CKC(cudaMemsetAsync(ctx->d_xchg, 0, sizeof(PeerSlot) * 2 * PEER_MAX_RANKS, ctx->stream));
+    CKC(cudaMemsetAsync(ctx->d_xseq, 0, sizeof(unsigned long long), ctx->stream));
+    CKC(cudaStreamSynchronize(ctx->stream));
+    ctx->peer_broken = false;
+    return FLIVO_OK;
+}
+
+// How long a rank waits for a peer's record before it gives the update up (default 2 s).
+extern "C" int flivo_peer_set_timeout(flivo_ctx* ctx, double seconds) {
+    ENTER();
+    NEED(seconds > 0.0 && seconds < 3600.0, FLIVO_E_ARG, "timeout must be in (0, 3600) s");
+    ctx->peer_timeout_ns = (unsigned long long)(seconds * 1e9);
     return FLIVO_OK;
 }
 
@@ -1170,10 +1423,10 @@ extern "C" int flivo_peer_detach(flivo_ctx* ctx) {
     if (ctx->peer_on) {
         CKC(cudaStreamSynchronize(ctx->stream));
         for (int r = 0; r < ctx->nranks; ++r) {
-            if (r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
+            if (!ctx->peer_local && r != ctx->rank && ctx->peer_base[r]) cudaIpcCloseMemHandle(ctx->peer_base[r]);
             ctx->peer_base[r] = nullptr;
         }
-        ctx->peer_on = false;
+        ctx->peer_on = false; ctx->peer_local = false;
         if (!ctx->comm) { ctx->rank = 0; ctx->nranks = 1; }
     }
     return FLIVO_OK;
@@ -1348,8 +1601,7 @@ extern "C" int flivo_raw_downsample(flivo_ctx* ctx, float leaf_size, size_t* n_o
     if (m == 0) { ctx->scan_n = 0; return FLIVO_OK; }
     int rc = ensure_scan(ctx, m);
     if (rc) return rc;
-    if (!ctx->opt.sort_scan) ctx->d_body = ctx->d_ds;
-    return finish_scan(ctx, ctx->d_ds, m, true);
+    return finish_scan(ctx, (const char*)ctx->d_ds, 16, m, true, -1);
 }
 
 // feats_down_body back to the host in the caller's (= leaf) order: n x (x, y, z, intensity)
@@ -1360,6 +1612,7 @@ extern "C" int flivo_scan_download(flivo_ctx* ctx, float* out_xyzi, size_t cap, 
     if (n_out) *n_out = n;
     if (n == 0 || cap == 0) return FLIVO_OK;
     NEED(cap >= n, FLIVO_E_CAPACITY, "output too small");
+    { int rcs = ensure_staged(ctx); if (rcs) return rcs; }
     const float4* src = ctx->d_body;
     if (ctx->scan_sorted) {   // processing order -> caller's order
         const size_t bytes = n * sizeof(float4);

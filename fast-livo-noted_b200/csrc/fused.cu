@@ -15,6 +15,7 @@
 // Compiled with -fmad=false: see flivo_dev.cuh.
 #include "fused.cuh"
 #include "search.cuh"
+#include "solve_dev.cuh"
 
 namespace flivo {
 
@@ -190,7 +191,10 @@ __device__ __forceinline__ double dot3d(const double* a, double b0, double b1, d
 //     G00 = rows 0..7 x cols 0..7,  G08 = rows 0..7 x cols 8..15,  G88 = rows 8..15 x cols 8..15
 // so H^T H (78 upper terms), H^T z = G[:,12], n_eff = G[13][13] and res_sum = G[13][14] come out of the same
 // accumulation, with no per-tile reduction, no barrier and no atomics.  One CTA-level fold at the end writes one
-// 96-double record per CTA; k_solve sums the records in CTA order.
+// 96-double record per CTA; the records are folded 16 at a time by the last CTA of each group to arrive, and the CTA
+// that folds the LAST group record sums the group records (fixed order) and runs the trip's solve on the spot
+// (solve_dev.cuh: reduce, exchange with the peers in sharded mode, 12x12 solve, state update, stop policy, and the
+// state-only half of the next trip) — a trip has no solve kernel and no kernel boundary between Gram and solve.
 // Staging: the tile's rows go through shared memory transposed (Ht[col][point], row pitch 36 doubles) so that the
 // MMA fragment loads are bank-conflict-free at the 2-wavefront minimum of a 256-byte request.
 // ----------------------------------------------------------------------------------------------------
@@ -200,8 +204,12 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-__global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
-    __shared__ double s_ht[UNIT_WARPS][16 * HT_PITCH];   // per warp: Ht[16][36]; reused for the final fold
+constexpr size_t FUSED_SMEM_DOUBLES = (sizeof(SolveSmem) + 7) / 8 > (size_t)UNIT_WARPS * 16 * HT_PITCH ? (sizeof(SolveSmem) + 7) / 8 : (size_t)UNIT_WARPS * 16 * HT_PITCH;
+
+__global__ void __launch_bounds__(UNIT_POINTS, 8) k_fused(const __grid_constant__ FusedParams P, const __grid_constant__ SolveParams SP) {
+    // per warp: Ht[16][36]; reused for the final fold and, in the one CTA that solves, as the solve's workspace
+    __shared__ __align__(16) double s_raw[FUSED_SMEM_DOUBLES];
+    double (*s_ht)[16 * HT_PITCH] = reinterpret_cast<double (*)[16 * HT_PITCH]>(s_raw);
     __shared__ double s_state[36];
 
     Ctl* ctl = P.ctl;
@@ -354,19 +362,39 @@ __global__ void __launch_bounds__(UNIT_POINTS) k_fused(FusedParams P) {
         if (s_last) P.group_cnt[grp] = 0;   // ready for the next launch
     }
     __syncthreads();
-    if (s_last) {
-        __threadfence();
-        if (threadIdx.x < NTERMS) {
-            const double* src = P.partials + (size_t)grp * FOLD_CTAS * PSTRIDE + threadIdx.x;
-            double v[FOLD_CTAS];
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x < NTERMS) {
+        const double* src = P.partials + (size_t)grp * FOLD_CTAS * PSTRIDE + threadIdx.x;
+        double v[FOLD_CTAS];
 #pragma unroll
-            for (int m = 0; m < FOLD_CTAS; ++m) v[m] = (m < (int)members) ? __ldcg(src + (size_t)m * PSTRIDE) : 0.0;
-            double sum = v[0];
+        for (int m = 0; m < FOLD_CTAS; ++m) v[m] = (m < (int)members) ? __ldcg(src + (size_t)m * PSTRIDE) : 0.0;
+        double sum = v[0];
 #pragma unroll
-            for (int m = 1; m < FOLD_CTAS; ++m) if (m < (int)members) sum += v[m];
-            P.gpartials[(size_t)grp * PSTRIDE + threadIdx.x] = sum;
-        }
+        for (int m = 1; m < FOLD_CTAS; ++m) if (m < (int)members) sum += v[m];
+        P.gpartials[(size_t)grp * PSTRIDE + threadIdx.x] = sum;
     }
+    // ---- third level: the group folder that arrives last sums the group records in group order and solves ----------
+    const unsigned ngroups = (gridDim.x + FOLD_CTAS - 1) / FOLD_CTAS;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned ticket = atomicAdd(P.total_cnt, 1u);
+        s_last = (ticket == ngroups - 1) ? 1u : 0u;
+        if (s_last) *P.total_cnt = 0;       // ready for the next launch
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    SolveSmem& M = *reinterpret_cast<SolveSmem*>(s_raw);
+    if (threadIdx.x < NTERMS) {
+        const double* src = P.gpartials + threadIdx.x;
+        double sum = 0.0;
+        for (unsigned g = 0; g < ngroups; ++g) sum += __ldcg(src + (size_t)g * PSTRIDE);
+        M.sum[threadIdx.x] = sum;
+    }
+    __syncthreads();
+    solve_trip(SP, M, threadIdx.x, UNIT_POINTS);
 }
 
 // ----------------------------------------------------------------------------------------------------
@@ -745,8 +773,8 @@ __global__ void k_ivox_map_filter(const float4* __restrict__ body, int n, const 
 }
 
 // ---- host launchers ---------------------------------------------------------------------------------
-void launch_fused(const FusedParams& P, int grid, cudaStream_t stream) {
-    k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P);
+void launch_fused(const FusedParams& P, const SolveParams& S, int grid, cudaStream_t stream) {
+    k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P, S);
 }
 void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, bool par_probes) {
     if (P.map.ivox) k_search<true, false><<<search_grid, SEARCH_THREADS, 0, stream>>>(P);

@@ -23,7 +23,7 @@ struct Ctl {
     int searches;
     int converged;
     int n_eff;
-    int nan_guard;     // 1: a non-finite normal-equation block was seen (update skipped)
+    int nan_guard;     // 1: a non-finite normal-equation block was seen (update skipped); 2: a peer exchange timed out
     int trip_searched[MAX_TRIPS];
     double res_mean;
     double dx_last[23];
@@ -63,6 +63,54 @@ struct Job {
     double gnss_std[3];        // gnss_.std
 };
 
+// What the CTA of k_fused that folds the last group record does with the trip's sums (solve_dev.cuh: solve_trip)
+enum {
+    SOLVE_PHASE_FULL = 0,         // solve (single GPU)
+    SOLVE_PHASE_REDUCE_ONLY = 1,  // sum_out[92] only (flivo_h_share_model; first half of the multi-GPU trip, NCCL variant)
+    SOLVE_PHASE_FROM_RANKS = 2,   // sum rank_blocks[nranks][96] in rank order, then solve (k_solve_ranks: second half of
+                                  // the multi-GPU trip, NCCL variant)
+    SOLVE_PHASE_PEER = 3          // multi-GPU, fused: write the record into every peer's exchange buffer over NVLink,
+                                  // wait for the peers' records, sum in rank order, solve — inside k_fused
+};
+
+// Exchange buffer of one rank, mapped into every peer (cudaIpc): slots[parity][source rank].
+constexpr int PEER_MAX_RANKS = 8;
+struct PeerSlot {
+    double rec[PSTRIDE];
+    unsigned long long flag;      // sequence number of the exchange that filled rec
+    unsigned long long pad[7];
+};
+struct PeerXchg {
+    PeerSlot* base[PEER_MAX_RANKS];   // base[r]: rank r's buffer ([2][PEER_MAX_RANKS] slots) as mapped into this process
+    unsigned long long* seq;          // this rank's exchange counter (device memory; reset only by flivo_peer_reset)
+    unsigned long long timeout_ns;    // a peer's record is awaited this long before the update is given up (nan_guard = 2)
+    int rank, nranks;
+};
+
+// State-only half of a trip's solve (it needs x and P_prop, not H^T H): prepared at the end of the previous trip's
+// solve (for the first trip: by k_ctl_reset), solve_dev.cuh: solve_pre.
+struct SolvePre {
+    double Pt[23 * 23];   // V3: P_prop with the manifold Jacobians applied, T P T^T (esekfom.hpp:1665-1695)
+    double dxnew[23];     // V3: J^{-1}-corrected x (-) x_prop (:1646-1686)
+    double vec[18];       // V1: state_propagat - state (common_lib.h:576-587)
+    double pad;
+};
+
+struct SolveParams {
+    const Job* job;
+    int phase;
+    double* x;                 // device flivo_state, in/out
+    const double* x_prop;      // device flivo_state
+    const double* P_prop;      // n x n
+    double* P_out;             // n x n, written when the loop stops
+    double* sum_out;           // [96] reduced block (may be null in FULL phase)
+    const double* rank_blocks; // [nranks * PSTRIDE]
+    Ctl* ctl;
+    SolvePre* pre;             // written by solve_pre, read by the next trip's solve
+    PeerXchg peer;             // SOLVE_PHASE_PEER
+    unsigned long long* stamps;       // profile mode only: [MAX_TRIPS][16] globaltimer values at the phase boundaries of the solve
+};
+
 enum { PF_HAVE5 = 1,    // five neighbours exist (points_near.size() >= NUM_MATCH_POINTS)
        PF_GATE = 2,     // !(pointSearchSqDis[4] > 5)            (src/laser_mapping.cpp:518)
        PF_PLANE = 4 };  // esti_plane accepted the five points  (include/common_lib.h:694-699)
@@ -84,8 +132,9 @@ struct FusedParams {
     unsigned long long* far_list;   // [n] (tag << 32 | point) of points the 27-cell shell could not finish: queue between the
                                //     two phases of k_search, entries valid when tag == ctl->epoch + 1
     double* partials;          // [fused grid * PSTRIDE] one record per CTA of k_fused
-    double* gpartials;         // [groups * PSTRIDE] records folded FOLD_CTAS at a time (fixed order), read by k_solve
+    double* gpartials;         // [groups * PSTRIDE] records folded FOLD_CTAS at a time (fixed order)
     unsigned int* group_cnt;   // [groups] arrival tickets; the folding CTA resets its entry
+    unsigned int* total_cnt;   // arrival ticket of the group folders: the last one sums the group records and solves
     Ctl* ctl;
     SearchStats* stats;
     unsigned long long* search_stamps;   // profile mode only: [grid][4] globaltimer of CTA start / end of phase 1 / end, far queries done

@@ -148,6 +148,18 @@ int flivo_knn(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t stride_bytes
 /* ---- scan + measurement update ---------------------------------------------------------------- */
 /* feats_down_body (src/laser_mapping.cpp:129-130): lidar-frame scan; copied to the device. */
 int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes);
+/* Double-buffered form (the reference hands one feats_down_body over per frame, src/laser_mapping.cpp:129-130,165-167):
+ * flivo_scan_upload_async copies the NEXT scan into the context's back buffer on a copy stream and returns without
+ * waiting — the current scan and an update in flight are not touched; the caller's buffer must stay valid until the
+ * following flivo_scan_commit (or any later synchronous call) returns.  A source in pinned / registered host memory
+ * travels as it is, whole records, by one DMA (the xyz gather happens on the device); a pageable source is first
+ * repacked by a few host threads.  flivo_scan_commit makes the uploaded scan the current one.
+ * flivo_scan_upload == flivo_scan_upload_async + flivo_scan_commit. */
+int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes);
+int flivo_scan_commit(flivo_ctx* ctx);
+/* cudaHostRegister / cudaHostUnregister for callers without the CUDA headers (e.g. the PointVector the node reuses). */
+int flivo_host_register(void* ptr, size_t bytes);
+int flivo_host_unregister(void* ptr);
 /* Same, from a device pointer to n float4 (x,y,z,ignored) already resident in HBM (no copy through the host). */
 int flivo_scan_set_device(flivo_ctx* ctx, const void* dev_xyzw, size_t n);
 
@@ -199,6 +211,11 @@ int flivo_repack_v1(const double HTH[144], const double HTz[12], double laser_po
  * V3: esekf::update_iterated_dyn_share_modified (include/IKFoM_toolkit/esekfom/esekfom.hpp:1619-1928), P 23x23;
  * V1: the loop in LaserMapping::Run (src/laser_mapping.cpp:165-242), P = state.cov 18x18.  Row-major, in/out. */
 int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* P, const flivo_cfg* cfg, flivo_report* rep);
+/* The same update in two halves: _begin launches it and returns at once, _end waits and hands back state, P and the
+ * report.  Between the two the caller may stage the NEXT frame's scan (flivo_scan_upload_async), which then travels to
+ * the device while this update runs; no other call on the ctx is allowed in between. */
+int flivo_iekf_update_begin(flivo_ctx* ctx, const flivo_state* x, const double* P, const flivo_cfg* cfg);
+int flivo_iekf_update_end(flivo_ctx* ctx, flivo_state* x_out, double* P_out, flivo_report* rep);
 
 /* The GNSS position observation of the compiled (V1) path: `if (bgnss_en && p_gnss->new_gnss_) { computeH(...);
  * HPH.block<6,6>(0,0) += gnss_HPH; HPL.block<6,1>(0,0) += gnss_HPL; }` (src/laser_mapping.cpp:612-617) with
@@ -229,6 +246,17 @@ int flivo_comm_destroy(flivo_ctx* ctx);
 int flivo_peer_export(flivo_ctx* ctx, void* handle_out64);
 int flivo_peer_attach(flivo_ctx* ctx, const void* handles /* nranks * 64 bytes */, int rank, int nranks);
 int flivo_peer_detach(flivo_ctx* ctx);
+/* The same exchange between contexts of ONE process (one process driving several GPUs, or several ranks on one GPU as the
+ * tests do): cudaIpc handles cannot be opened by the exporting process, so the ranks pass their buffers as device
+ * pointers: flivo_peer_local_base on every context -> flivo_peer_attach_local(bases in rank order).  Across devices the
+ * caller enables peer access. */
+int flivo_peer_local_base(flivo_ctx* ctx, void** base_out);
+int flivo_peer_attach_local(flivo_ctx* ctx, void* const* bases /* nranks */, int rank, int nranks);
+/* A rank waits `seconds` (default 2) for a peer's record, then gives the update up: FLIVO_E_STATE, state and P untouched,
+ * and every later sharded update is refused until flivo_peer_reset.  flivo_peer_reset zeroes this rank's exchange counter
+ * and buffer; every rank calls it, between two barriers of the caller's (no update in flight, none started early). */
+int flivo_peer_set_timeout(flivo_ctx* ctx, double seconds);
+int flivo_peer_reset(flivo_ctx* ctx);
 
 /* ---- introspection used by bench.py ------------------------------------------------------------ */
 typedef struct flivo_stats {

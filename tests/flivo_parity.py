@@ -121,7 +121,8 @@ def check_trip(pkg, F, map_xyz, body, x, mode, verbose=False):
     cache = {}
     o = oracle_trip(map_xyz, body, x, True, cache, mode)
     assert cache["ties"] == 0, "synthetic data has a float32 tie straddling rank 5; re-seed"
-    bad, want_ids = compare_neighbours(g["nbr_id"], cache["ids"], cache["sqd"], cache["cnt"])
+    # V3 searches with the far-neighbour gate as its bound (equivalent there); V1 searches unbounded like the reference
+    bad, want_ids = compare_neighbours(g["nbr_id"], cache["ids"], cache["sqd"], cache["cnt"], np.inf if mode == orc.MODE_V1 else GATE_SQ)
     assert bad == 0, "%d / %d neighbour rows differ" % (bad, len(body))
     assert np.array_equal(g["world"], o["world"]), "feats_down_world differs"
     sqd_want = np.where(want_ids >= 0, cache["sqd"], np.inf).astype(np.float32)
@@ -245,3 +246,71 @@ def check_ivox_golden(gold, nearby, add_points, num_grids, knn):
         assert has.sum() > 300 and (~has).sum() > 20
         assert np.array_equal(xyz[has, 0], gold["first_%d_%s" % (nearby, tag)][has]), (nearby, tag)
         assert np.array_equal(lexsorted_rows(xyz, cnt), gold["set_%d_%s" % (nearby, tag)]), (nearby, tag)
+
+
+# ---- sharded update with every rank in THIS process ---------------------------------------------
+def sharded_update_in_process(pkg, world, scan, nranks=2, mode=0, max_iter=4, device=0, verbose=False, delay_rank=None,
+                              delay_s=0.0, timeout_s=None, ctxs=None, sort_scan=True):
+    """The scan is cut into `nranks` contiguous blocks (sharding.shard_range); every rank = one context with the whole map
+    and its block, driven by its own host thread; the per-trip exchange goes through the ranks' exchange buffers
+    (flivo_peer_attach_local: the peer phase of the solve, exactly as between GPUs, minus the NVLink hop).  Checks: every
+    rank ends with the bit-identical posterior, and that posterior is the oracle's for the WHOLE scan (x <= 1e-6, same
+    trips / searches / n_eff).  Returns dict(x, P, reps, oracle, errors)."""
+    import threading
+    from importlib import import_module
+    shard_range = import_module(pkg.__name__ + ".sharding").shard_range
+    map_xyz, body = world["points"], scan["body"]
+    npd = 18 if mode == pkg.MODE_V1 else 23
+    P0 = np.eye(npd) * 1e-4
+    cfg = pkg.make_cfg(mode=mode, max_iter=max_iter, laser_point_cov=0.001)
+    own = ctxs is None
+    if own:
+        ctxs = [pkg.Flivo(device=device, downsample_size=world["ds"], initial_points=len(map_xyz), sort_scan=sort_scan) for _ in range(nranks)]
+        for F in ctxs:
+            F.Build(map_xyz)
+        bases = [F.peer_local_base() for F in ctxs]
+        for r, F in enumerate(ctxs):
+            F.peer_attach_local(bases, r, nranks)
+    if timeout_s is not None:
+        for F in ctxs:
+            F.peer_set_timeout(timeout_s)
+    for r, F in enumerate(ctxs):
+        lo, hi = shard_range(len(body), r, nranks)
+        F.scan_upload(np.ascontiguousarray(body[lo:hi]))
+    out, errs = [None] * nranks, [None] * nranks
+
+    def run(r):
+        import time
+        try:
+            if delay_rank == r:
+                time.sleep(delay_s)
+            out[r] = ctxs[r].iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+        except pkg.FlivoError as e:
+            errs[r] = e
+
+    th = [threading.Thread(target=run, args=(r,)) for r in range(nranks)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    res = dict(ctxs=ctxs, errors=errs, out=out)
+    if any(errs):
+        return res
+    x0, Pm0, rep0 = out[0]
+    for r in range(1, nranks):
+        assert np.array_equal(out[r][0].as_array(), x0.as_array()), "rank %d posterior differs from rank 0 (must be bit-identical)" % r
+        assert np.array_equal(out[r][1], Pm0)
+    o = oracle_update(map_xyz, body, scan["x_prior"], P0, mode, max_iter, 0.001, None, False)
+    assert rep0.trips == o["trips"] and rep0.searches == o["searches"], "trips/searches %d/%d vs oracle %d/%d" % (rep0.trips, rep0.searches, o["trips"], o["searches"])
+    assert rep0.n_eff == o["n_eff"], "n_eff (all ranks) %d vs oracle %d" % (rep0.n_eff, o["n_eff"])
+    x_err = np.abs(x0.as_array() - o["x"]).max()
+    assert x_err <= 1e-6, "sharded posterior differs from the oracle's by %g" % x_err
+    p_err = np.abs(Pm0 - o["P"]).max() / np.abs(o["P"]).max()
+    assert p_err <= 1e-6
+    if verbose:
+        print("sharded in-process: ranks=%d trips=%d n_eff=%d x_err=%.2e P_err=%.2e" % (nranks, rep0.trips, rep0.n_eff, x_err, p_err))
+    res.update(x=x0, P=Pm0, rep=rep0, oracle=o, x_err=x_err)
+    if own:
+        for F in ctxs:
+            F.close()
+    return res
