@@ -72,6 +72,7 @@ struct SearchStats {
 };
 
 
+#ifndef FLIVO_HOST_EMU   // (tests/cpp/solve_emu.cpp compiles solve_dev.cuh for the host: layouts only, no device helpers)
 // ---- strict float helpers (explicit rounding; immune to contraction even without -fmad=false) -----
 __device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
@@ -166,5 +167,6 @@ __device__ __forceinline__ bool in_box1(float p, float lo, float hi) { return lo
 __device__ __forceinline__ bool same_point3(float ax, float ay, float az, float bx, float by, float bz) {
     return (double)fabsf(fsub(ax, bx)) < 1e-6 && (double)fabsf(fsub(ay, by)) < 1e-6 && (double)fabsf(fsub(az, bz)) < 1e-6;
 }
+#endif  // FLIVO_HOST_EMU
 
 }  // namespace flivo

@@ -35,7 +35,7 @@ struct Ctl {
     unsigned int epoch;          // bumped whenever the counters are rearmed; far_list entries carry epoch+1 as their tag
     unsigned int pad_epoch;
 };
-#ifdef __CUDACC__
+#if defined(__CUDACC__) || defined(FLIVO_HOST_EMU)
 __device__ __forceinline__ void ctl_next_trip(Ctl* ctl) {
     ctl->tile_counter = 0; ctl->tiles_done = 0; ctl->far_count = 0; ctl->far_taken = 0;
     ctl->epoch += 1;

@@ -381,12 +381,14 @@ struct SolveSmem {
 };
 
 SDEV void solve_stamp(const SolveParams& S, int trip, int k) {
+#ifndef FLIVO_HOST_EMU
     if (S.stamps && threadIdx.x == 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         trip = trip < 0 ? 0 : (trip < MAX_TRIPS ? trip : MAX_TRIPS - 1);
         S.stamps[trip * 16 + k] = t;
     }
+#endif
 }
 
 // ---- state-only half of the NEXT trip's solve: needs x and P_prop, not H^T H -------------------------------------
@@ -463,6 +465,7 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
     solve_stamp(S, trip_no, 0);
 
     // ---- 0. normal equations of all ranks ----------------------------------------------------------------------
+#ifndef FLIVO_HOST_EMU
     if (S.phase == SOLVE_PHASE_PEER) {
         // fused reduce + exchange over peer memory: every rank holds the same state, so all ranks run the same trips
         // and their exchange counters agree.  My record goes straight into every rank's buffer (NVLink stores), then a
@@ -511,7 +514,9 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
             if (tid == 0) { ctl->nan_guard = 2; ctl->stopped = 1; ctl->trips += 1; ctl_next_trip(ctl); }
             return;
         }
-    } else if (S.phase == SOLVE_PHASE_FROM_RANKS) {
+    } else
+#endif
+    if (S.phase == SOLVE_PHASE_FROM_RANKS) {
         // multi-GPU, NCCL variant: every rank's 92-term block was gathered; sum in rank order
         if (tid < NTERMS) {
             double s = 0.0;
@@ -526,10 +531,10 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
         if (tid == 0) ctl_next_trip(ctl);
         return;
     }
-    if (tid < 144) {
-        const int a = tid / 12, b = tid % 12;
+    for (int e = tid; e < 144; e += NT) {   // (NT = 128 < 144: a plain `tid < 144` would leave the last 16 entries stale)
+        const int a = e / 12, b = e % 12;
         const int i = a < b ? a : b, j = a < b ? b : a;
-        M.H[tid] = M.sum[i * 12 - (i * (i - 1)) / 2 + (j - i)];   // index of (i, j), i <= j, in the 78 upper terms
+        M.H[e] = M.sum[i * 12 - (i * (i - 1)) / 2 + (j - i)];   // index of (i, j), i <= j, in the 78 upper terms
     }
     if (tid < 12) M.z[tid] = M.sum[78 + tid];
     if (tid == 0) {
