@@ -297,6 +297,7 @@ def run_flivo(args, rank, world_size, local_rank):
     t_wall0 = time.time()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     trips_total, launches, fused_search_ms, fused_reuse_ms, solve_ms, last = 0, 0, [], [], [], None
+    solve_us = []
     for k in range(args.steps):
         flush.zero_()
         torch.cuda.synchronize()
@@ -343,8 +344,11 @@ def run_flivo(args, rank, world_size, local_rank):
             stamps = F.solve_stamps(repp.trips)
             for t in range(repp.trips):
                 row = stamps[t].astype(np.int64)
-                d = [(int(row[i]) - int(row[i - 1])) / 1e3 if row[i] and row[i - 1] else None for i in range(1, 10)]
-                print(f"[solve phases trip {t}] us: reduce={d[0]} load={d[1]} manifold={d[2]} applyT={d[3]} aug={d[4]} gj={d[5]} gain={d[6]} plus+ctl={d[7]} tail={d[8]}", file=sys.stderr)
+                d = [(int(row[i]) - int(row[i - 1])) / 1e3 if row[i] and row[i - 1] else None for i in range(1, 8)]
+                tot = (int(row[7]) - int(row[0])) / 1e3 if row[7] and row[0] else None
+                xw = (int(row[11]) - int(row[10])) / 1e3 if row[11] and row[10] else None
+                print(f"[solve inside k_fused, trip {t}] us: exchange={d[0]} unpack={d[1]} aug={d[2]} gj={d[3]} gain={d[4]} plus+ctl={d[5]} cov|next-pre={d[6]} total={tot} peer-wait={xw}", file=sys.stderr)
+                solve_us.append(tot)
 
     # ---- e2e: host buffers through the C ABI, wall clock, H2D + D2H inside ----
     for w in range(min(args.warmup, 2)):
@@ -521,9 +525,15 @@ def main():
         return 0
     import torch
     import torch.distributed as dist
+    one_device = os.environ.get("FLIVO_BENCH_ONE_DEVICE") == "1"   # tests: every rank on cuda:0 (cudaIpc across processes on one GPU)
+    if one_device:
+        local_rank = 0
     if world_size > 1:
         torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local_rank))
+        if one_device:
+            dist.init_process_group("gloo")     # NCCL refuses two ranks on one device; only rendezvous / timings travel here
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local_rank))
     r = run_flivo(args, rank, world_size, local_rank)
     n_scan, n_map, ds, kind, cfg_idx = WORKLOADS[args.workload]
     peak, peak_src = peaks()

@@ -206,7 +206,10 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 
 constexpr size_t FUSED_SMEM_DOUBLES = (sizeof(SolveSmem) + 7) / 8 > (size_t)UNIT_WARPS * 16 * HT_PITCH ? (sizeof(SolveSmem) + 7) / 8 : (size_t)UNIT_WARPS * 16 * HT_PITCH;
 
-__global__ void __launch_bounds__(UNIT_POINTS, 8) k_fused(const __grid_constant__ FusedParams P, const __grid_constant__ SolveParams SP) {
+#ifndef FLIVO_FUSED_CTAS_PER_SM
+#define FLIVO_FUSED_CTAS_PER_SM 8   // 64 registers; the solve inside it spills under this cap (A/B: profiles/r2_ab_solve.txt)
+#endif
+__global__ void __launch_bounds__(UNIT_POINTS, FLIVO_FUSED_CTAS_PER_SM) k_fused(const __grid_constant__ FusedParams P, const __grid_constant__ SolveParams SP) {
     // per warp: Ht[16][36]; reused for the final fold and, in the one CTA that solves, as the solve's workspace
     __shared__ __align__(16) double s_raw[FUSED_SMEM_DOUBLES];
     double (*s_ht)[16 * HT_PITCH] = reinterpret_cast<double (*)[16 * HT_PITCH]>(s_raw);

@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_ctl_reset(const __grid_consta
         if (stats) { stats->far_queries = 0; stats->candidates = 0; stats->sweeps = 0; }
     }
     __syncthreads();
-    solve_pre(S, M, mode, tid, SOLVE_THREADS);
+    solve_pre(S, M, mode, tid, SOLVE_THREADS, false);
 }
 void launch_ctl_reset(const SolveParams& S, double* x_prop, SearchStats* stats, cudaStream_t stream) {
     k_ctl_reset<<<1, SOLVE_THREADS, 0, stream>>>(S, x_prop, stats);

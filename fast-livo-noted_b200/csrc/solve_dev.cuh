@@ -27,6 +27,15 @@
 namespace flivo {
 
 #define SDEV static __device__ __forceinline__
+// The solve is executed ONCE per launch by one CTA: its instruction lines are cold, and a helper shared by several call
+// sites / several single-lane warps (SO(3) exp / log, A_matrix, the S2 charts with their sin / cos / atan2 bodies) is
+// fetched once when it is a real function but once per copy when inlined.  FLIVO_SOLVE_INLINE=1 inlines them instead
+// (measured: profiles/r2_ab_solve.txt).
+#if defined(FLIVO_SOLVE_INLINE) && FLIVO_SOLVE_INLINE
+#define SHELP static __device__ __forceinline__
+#else
+#define SHELP static __device__ __noinline__
+#endif
 
 // ---- small dense helpers ------------------------------------------------------------------------------
 SDEV void d_hat(const double* v, double* H) {
@@ -39,7 +48,7 @@ SDEV void d_mat3mul(const double* A, const double* B, double* C) {
         for (int j = 0; j < 3; ++j) C[i * 3 + j] = A[i * 3] * B[j] + A[i * 3 + 1] * B[3 + j] + A[i * 3 + 2] * B[6 + j];
 }
 // MTK::A_matrix (mtkmath.hpp:236-247)
-SDEV void d_A_matrix(const double* v, double* A) {
+SHELP void d_A_matrix(const double* v, double* A) {
     double sq = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
     double nrm = sqrt(sq);
 #pragma unroll
@@ -55,7 +64,7 @@ SDEV void d_A_matrix(const double* v, double* A) {
 }
 // rotation-matrix form of SO3::exp (SOn.hpp:293-297 via MTK::exp / cos_sinc_sqrt, mtkmath.hpp:139-171,249-256):
 // Rodrigues with series near zero.  The reference composes unit quaternions; identical up to rounding.
-SDEV void d_so3_exp(const double* v, double* R) {
+SHELP void d_so3_exp(const double* v, double* R) {
     double t2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
     double a, b;  // sin(t)/t, (1-cos t)/t^2
     if (t2 < 1e-8) {
@@ -75,7 +84,7 @@ SDEV void d_so3_exp(const double* v, double* R) {
 }
 // SO3 log of a rotation matrix, accurate for small angles (SOn.hpp:300-304 / MTK::log computes the same
 // vector from the unit quaternion: 2*atan(|v|/w)/|v| * v).
-SDEV void d_so3_log(const double* R, double* o) {
+SHELP void d_so3_log(const double* R, double* o) {
     double vx = 0.5 * (R[7] - R[5]), vy = 0.5 * (R[2] - R[6]), vz = 0.5 * (R[3] - R[1]);  // sin(t) * axis
     double s = sqrt(vx * vx + vy * vy + vz * vz);
     double c = 0.5 * (R[0] + R[4] + R[8] - 1.0);
@@ -85,7 +94,7 @@ SDEV void d_so3_log(const double* R, double* o) {
     o[0] = f * vx; o[1] = f * vy; o[2] = f * vz;
 }
 // V1 Exp / Log (include/so3_math.h:62-91)
-SDEV void d_Exp_v1(double v1, double v2, double v3, double* R) {
+SHELP void d_Exp_v1(double v1, double v2, double v3, double* R) {
     double nrm = sqrt(v1 * v1 + v2 * v2 + v3 * v3);
 #pragma unroll
     for (int i = 0; i < 9; ++i) R[i] = 0;
@@ -100,7 +109,7 @@ SDEV void d_Exp_v1(double v1, double v2, double v3, double* R) {
         for (int i = 0; i < 9; ++i) R[i] += s * K[i] + c * K2[i];
     }
 }
-SDEV void d_Log_v1(const double* R, double* o) {
+SHELP void d_Log_v1(const double* R, double* o) {
     double tr = R[0] + R[4] + R[8];
     double theta = (tr > 3.0 - 1e-6) ? 0.0 : acos(0.5 * (tr - 1));
     double K[3] = {R[7] - R[5], R[2] - R[6], R[3] - R[1]};
@@ -129,7 +138,7 @@ SDEV void d_s2_Bx(const double* vec, double* Bx) {  // 3x2 row-major, S2_typ == 
 SDEV void d_cross(const double* a, const double* b, double* o) {
     o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
 }
-SDEV void d_s2_boxminus(const double* vec, const double* other, double* res2) {  // S2.hpp:136-160
+SHELP void d_s2_boxminus(const double* vec, const double* other, double* res2) {  // S2.hpp:136-160
     double cr[3];
     d_cross(vec, other, cr);
     double v_sin = sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]);
@@ -147,7 +156,7 @@ SDEV void d_s2_boxminus(const double* vec, const double* other, double* res2) { 
         for (int c = 0; c < 2; ++c) res2[c] = f * (Bx[c] * hv[0] + Bx[2 + c] * hv[1] + Bx[4 + c] * hv[2]);
     }
 }
-SDEV void d_s2_boxplus(double* vec, const double* delta2) {  // S2.hpp:128-134
+SHELP void d_s2_boxplus(double* vec, const double* delta2) {  // S2.hpp:128-134
     double Bx[6], Bu[3], R[9], o[3];
     d_s2_Bx(vec, Bx);
 #pragma unroll
@@ -157,7 +166,7 @@ SDEV void d_s2_boxplus(double* vec, const double* delta2) {  // S2.hpp:128-134
     for (int r = 0; r < 3; ++r) o[r] = R[r * 3] * vec[0] + R[r * 3 + 1] * vec[1] + R[r * 3 + 2] * vec[2];
     vec[0] = o[0]; vec[1] = o[1]; vec[2] = o[2];
 }
-SDEV void d_s2_Nx_yy(const double* vec, double* Nx) {  // 2x3, S2.hpp:259-264
+SHELP void d_s2_Nx_yy(const double* vec, double* Nx) {  // 2x3, S2.hpp:259-264
     double Bx[6], H[9];
     d_s2_Bx(vec, Bx);
     d_hat(vec, H);
@@ -168,7 +177,7 @@ SDEV void d_s2_Nx_yy(const double* vec, double* Nx) {  // 2x3, S2.hpp:259-264
             Nx[r * 3 + c] = 1 / S2_LEN / S2_LEN * (Bx[r] * H[c] + Bx[2 + r] * H[3 + c] + Bx[4 + r] * H[6 + c]);
 }
 // S2_Mx (S2.hpp:266-280).  "scalar(1/2)" there is integer division == 0, so exp_delta is the identity.
-SDEV void d_s2_Mx(const double* vec, const double* delta2, double* Mx /*3x2*/) {
+SHELP void d_s2_Mx(const double* vec, const double* delta2, double* Mx /*3x2*/) {
     double Bx[6], H[9];
     d_s2_Bx(vec, Bx);
     d_hat(vec, H);
@@ -207,7 +216,7 @@ SDEV void d_mat3_AtB(const double* a, const double* b, double* Rd) {
 
 // x (-) y, state_ikfom order pos, rot, offR, offT, vel, bg, ba, grav(S2).  The three parts touch disjoint
 // fields (0: pos, rot; 1: offR, offT, vel, bg, ba; 2: grav) so three lanes of different warps run them at once.
-SDEV void d_boxminus_v3_part(const double* x, const double* y, double* d, int part) {
+SHELP void d_boxminus_v3_part(const double* x, const double* y, double* d, int part) {
     double Rd[9];
     if (part == 0) {
 #pragma unroll
@@ -228,7 +237,7 @@ SDEV void d_boxminus_v3_part(const double* x, const double* y, double* d, int pa
         d_s2_boxminus(x + S_GRAV, y + S_GRAV, d + 21);
     }
 }
-SDEV void d_boxplus_v3_part(double* x, const double* d, int part) {
+SHELP void d_boxplus_v3_part(double* x, const double* d, int part) {
     double E[9], Rn[9];
     if (part == 0) {
 #pragma unroll
@@ -254,7 +263,7 @@ SDEV void d_boxplus_v3_part(double* x, const double* d, int part) {
     }
 }
 // J = A_matrix(v)^T and seg <- J * seg  (esekfom.hpp:1663-1672)
-SDEV void d_so3_jac(const double* v, double* J, double* seg) {
+SHELP void d_so3_jac(const double* v, double* J, double* seg) {
     double A[9];
     d_A_matrix(v, A);
 #pragma unroll
@@ -269,7 +278,7 @@ SDEV void d_so3_jac(const double* v, double* J, double* seg) {
     }
 }
 // J2 = Nx(x.grav) * Mx(x_prop.grav, d2) and seg <- J2 * seg  (esekfom.hpp:1684-1695)
-SDEV void d_s2_jac(const double* xg, const double* xpg, const double* d2, double* J2, double* seg) {
+SHELP void d_s2_jac(const double* xg, const double* xpg, const double* d2, double* J2, double* seg) {
     double Nx[6], Mx[6];
     d_s2_Nx_yy(xg, Nx);
     d_s2_Mx(xpg, d2, Mx);
@@ -322,14 +331,34 @@ SDEV void apply_T_cols(double* M, int n, const BlockT& T, int tid, int nthreads)
     }
 }
 
-// Solve S^T X = B by Gauss-Jordan with partial pivoting on the M x W array A = [S^T | B] (W = M + nrhs) in shared
+// Solve S^T X = B by Gauss-Jordan with partial pivoting on the M x W array A = [S^T | B] (W = M + nrhs <= 65) in shared
 // memory, by ONE warp, in place; on return columns M..W-1 hold X (columns 0..M-1 are dead: a pivot column is never
-// read again once its pivot is done, so it is not even written).  Lane per column of the active window k+1..W-1; the
-// pivot search reads column k by broadcast loads in every lane (no shuffles), the row swap p <-> k is applied by index.
-// Same operations per entry as the textbook order: pivot row scaled by 1/piv (a division), other rows
-// a_ic - a_ik * (scaled pivot row)_c; first maximum wins pivot ties.  Returns false on a zero pivot.
+// read again once its pivot is done, so it is not even written).  The time of this routine is the length of its
+// dependent chain per pivot, so: every lane reads pivot column k itself (broadcast loads, no shuffles) and finds the
+// pivot row by INTEGER compares of the magnitudes' bit patterns (non-negative doubles order like their bits), two
+// interleaved half-chains; one reciprocal per pivot (correctly rounded, then multiplies); a lane owns columns
+// k+1+lane and k+33+lane and updates both at once; the row swap p <-> k is applied by index.  First maximum wins
+// pivot ties.  Returns false on a zero pivot (the caller then leaves state and covariance untouched).
+SDEV unsigned long long d_mag_bits(double v) {
+#ifdef __CUDA_ARCH__
+    return (unsigned long long)__double_as_longlong(v) & 0x7FFFFFFFFFFFFFFFull;
+#else
+    unsigned long long b;
+    memcpy(&b, &v, 8);
+    return b & 0x7FFFFFFFFFFFFFFFull;
+#endif
+}
+SDEV double d_rcp(double v) {
+#ifdef __CUDA_ARCH__
+    return __drcp_rn(v);
+#else
+    return 1.0 / v;
+#endif
+}
 template <int M, int W>
 SDEV bool warp_gauss_jordan(double* A, int lane) {
+    static_assert(W <= 65 && M >= 2, "a lane owns at most two columns");
+    constexpr int HALF = M / 2;
     bool ok = true;
 #pragma unroll 1
     for (int k = 0; k < M; ++k) {
@@ -337,28 +366,36 @@ SDEV bool warp_gauss_jordan(double* A, int lane) {
 #pragma unroll
         for (int i = 0; i < M; ++i) colk[i] = A[i * W + k];
         const double mk = A[k * W + k];   // multiplier of the row that lands at position p after the swap
-        int p = k;
-        double best = fabs(mk);
+        // rows k..M-1 compete; rows above the pivot row carry key 0 and the lower index wins ties
+        unsigned long long ba = 0ull, bb = 0ull;
+        int pa = k, pb = k;
 #pragma unroll
-        for (int i = 1; i < M; ++i) {
-            const double v = fabs(colk[i]);
-            if (i > k && v > best) { best = v; p = i; }
+        for (int i = 0; i < HALF; ++i) {
+            const unsigned long long key = i >= k ? d_mag_bits(colk[i]) : 0ull;
+            if (key > ba) { ba = key; pa = i; }
         }
-        if (best == 0.0) ok = false;
-        const double piv = A[p * W + k];
-        for (int c = k + 1 + lane; c < W; c += 32) {
-            const double prow = A[p * W + c] / piv;
-            const double ak = A[k * W + c];
 #pragma unroll
-            for (int i = 0; i < M; ++i) {
-                if (i == k) continue;
-                const bool sw = (i == p);
-                const double a = sw ? ak : A[i * W + c];
-                const double m = sw ? mk : colk[i];
-                A[i * W + c] = a - m * prow;
-            }
-            A[k * W + c] = prow;
+        for (int i = HALF; i < M; ++i) {
+            const unsigned long long key = i >= k ? d_mag_bits(colk[i]) : 0ull;
+            if (key > bb) { bb = key; pb = i; }
         }
+        const int p = bb > ba ? pb : pa;
+        if ((bb > ba ? bb : ba) == 0ull) ok = false;
+        const double r = d_rcp(A[p * W + k]);
+        const int c0 = k + 1 + lane, c1 = c0 + 32;
+        const bool h0 = c0 < W, h1 = c1 < W;
+        const double p0 = h0 ? A[p * W + c0] * r : 0.0, p1 = h1 ? A[p * W + c1] * r : 0.0;
+        const double ak0 = h0 ? A[k * W + c0] : 0.0, ak1 = h1 ? A[k * W + c1] : 0.0;
+#pragma unroll
+        for (int i = 0; i < M; ++i) {
+            if (i == k) continue;
+            const bool sw = (i == p);
+            const double m = sw ? mk : colk[i];
+            if (h0) { const double a = sw ? ak0 : A[i * W + c0]; A[i * W + c0] = a - m * p0; }
+            if (h1) { const double a = sw ? ak1 : A[i * W + c1]; A[i * W + c1] = a - m * p1; }
+        }
+        if (h0) A[k * W + c0] = p0;
+        if (h1) A[k * W + c1] = p1;
         __syncwarp();
     }
     return ok;
@@ -395,9 +432,10 @@ SDEV void solve_stamp(const SolveParams& S, int trip, int k) {
 // V3: dx = x (-) x_prop, the SO(3) / S2 Jacobians and T P T^T (esekfom.hpp:1646-1695) -> S.pre->{Pt, dxnew};
 // V1: vec = state_propagat - state (common_lib.h:576-587) -> S.pre->vec.  M.x / M.xp hold the two states.
 // All threads of the CTA call it (NT >= 96); ends with a barrier.
-static __device__ __noinline__ void solve_pre(const SolveParams& S, SolveSmem& M, int mode, int tid, int NT) {
+// p_loaded: M.L already holds P_prop (solve_trip fetches it at its very start, long before it gets here).
+static __device__ __noinline__ void solve_pre(const SolveParams& S, SolveSmem& M, int mode, int tid, int NT, bool p_loaded) {
     if (mode == 0) {
-        for (int e = tid; e < 23 * 23; e += NT) M.P[e] = S.P_prop[e];
+        if (!p_loaded) for (int e = tid; e < 23 * 23; e += NT) M.L[e] = S.P_prop[e];
         if ((tid & 31) == 0 && tid < 96) {
             const int part = tid >> 5;                                        // three warps, one lane each
             d_boxminus_v3_part(M.x, M.xp, M.dx, part);                        // esekfom.hpp:1646
@@ -413,11 +451,11 @@ static __device__ __noinline__ void solve_pre(const SolveParams& S, SolveSmem& M
             }
         }
         __syncthreads();
-        apply_T_rows(M.P, 23, 23, M.T, tid, NT);                              // :1665-1672, :1688-1695
+        apply_T_rows(M.L, 23, 23, M.T, tid, NT);                              // :1665-1672, :1688-1695
         __syncthreads();
-        apply_T_cols(M.P, 23, M.T, tid, NT);
+        apply_T_cols(M.L, 23, M.T, tid, NT);
         __syncthreads();
-        for (int e = tid; e < 23 * 23; e += NT) S.pre->Pt[e] = M.P[e];
+        for (int e = tid; e < 23 * 23; e += NT) S.pre->Pt[e] = M.L[e];
         if (tid < 23) S.pre->dxnew[tid] = M.dxnew[tid];
     } else if (tid == 0) {
         double rotd[9], vec[18];
@@ -452,7 +490,10 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
         if (tid < 36) { M.x[tid] = S.x[tid]; M.xp[tid] = S.x_prop[tid]; }
         const double* Psrc = (mode == 1) ? S.P_prop : S.pre->Pt;
         for (int e = tid; e < n * n; e += NT) M.P[e] = Psrc[e];
-        if (mode == 0) { if (tid < 23) M.dxnew[tid] = S.pre->dxnew[tid]; }
+        if (mode == 0) {
+            if (tid < 23) M.dxnew[tid] = S.pre->dxnew[tid];
+            for (int e = tid; e < 23 * 23; e += NT) M.L[e] = S.P_prop[e];   // for solve_pre at the end of this trip
+        }
         else if (tid < 18) M.vec[tid] = S.pre->vec[tid];
         if (warp == 3 && lane < 23) r_lim = S.job->limit[lane];
         if (tid == 96 || tid == 0) {   // lane 0 of the decision warp (V3) / thread 0 (V1)
@@ -574,6 +615,10 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
         }
         __syncthreads();
         solve_stamp(S, trip_no, 4);
+        if (!M.flag[1]) {   // singular system (cannot happen for SPD H and P; NaN guard of SURVEY §5): x and P untouched
+            if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl_next_trip(ctl); }
+            return;
+        }
         // W[i][a] = X[a][i] = Aug[a][12 + i];  K_h = W * HTz (:1801);  K_x[:, :12] = W * HTH (:1806)
         for (int e = tid; e < 23 * 12 + 23; e += NT) {
             if (e < 23 * 12) {
@@ -650,7 +695,7 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
             }
             solve_stamp(S, trip_no, 7);
         } else {
-            solve_pre(S, M, 0, tid, NT);     // the next trip's state-only half, while nothing else can run anyway
+            solve_pre(S, M, 0, tid, NT, true);     // the next trip's state-only half, while nothing else can run anyway
             solve_stamp(S, trip_no, 7);
         }
     } else {
@@ -716,6 +761,10 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
         }
         __syncthreads();
         solve_stamp(S, trip_no, 4);
+        if (!M.flag[1]) {
+            if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl_next_trip(ctl); }
+            return;
+        }
         for (int e = tid; e < 18 * 6; e += NT) {                             // G[:, :6] = K_1[:, :6] * HPH (:191), K_1[i][a] = Aug[a][6 + i]
             const int i = e / 6, b = e % 6;
             double s = 0.0;
@@ -774,11 +823,12 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
                 S.P_out[e] = M.P[e] - s;
             }
         } else {
-            solve_pre(S, M, 1, tid, NT);
+            solve_pre(S, M, 1, tid, NT, false);
         }
         solve_stamp(S, trip_no, 7);
     }
 }
 
 #undef SDEV
+#undef SHELP
 }  // namespace flivo

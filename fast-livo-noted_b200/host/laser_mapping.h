@@ -1,7 +1,8 @@
 // laser_mapping.h — ROS-free drop-in for the LIO half of the reference's LaserMapping
 // (include/laser_mapping.h:62-241, src/laser_mapping.cpp).  Class, member and method names follow the
 // reference so that its call sites read the same; what is kept is exactly the hot path:
-//   Run()             step 5 of LaserMapping::Run (src/laser_mapping.cpp:129-251): first scan -> ikdtree.Build,
+//   Run()             step 5 of LaserMapping::Run (src/laser_mapping.cpp:129-251): first scan -> ikdtree.Build (from
+//                     feats_down_body as it is, > 5 points, as the reference does),
 //                     otherwise the iterated update (on the device, one call) and map_incremental()
 //   h_share_model()   src/laser_mapping.cpp:485-645: one trip; returns the 9x9 HPH / 9 HPL of the compiled V1 path
 //   map_incremental() src/laser_mapping.cpp:329-389, ikd-Tree branch (:384)
@@ -53,19 +54,15 @@ public:
         if (feats_down_size == 0) return false;
         scan_on_device_ = false;   // consumed by this frame
         state_propagat = state;                                                      // :59
-        if (ikdtree.Root_Node == nullptr) {                                          // :134-142 first scan: world points, Build
-            flivo_state st = to_flivo(state);
-            std::vector<float> w((size_t)feats_down_size * 3);
-            double HTH[144], HTz[12];
-            // an empty map yields no neighbours; the trip is used only for its world-transformed points
-            ck(flivo_h_share_model(ikdtree.ctx(), &st, FLIVO_MODE_V1, 1, HTH, HTz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
-                                   nullptr, w.data()), "Run/first scan");
-            PointVector world(feats_down_size);
-            for (int i = 0; i < feats_down_size; ++i) {
-                if ((size_t)i < feats_down_body.size()) world[i] = feats_down_body[i];
-                world[i].x = w[3 * i]; world[i].y = w[3 * i + 1]; world[i].z = w[3 * i + 2];
+        if (ikdtree.Root_Node == nullptr) {
+            // :134-142: the first usable scan becomes the map exactly as the reference builds it — from feats_down_body,
+            // i.e. in the LIDAR frame (the node starts at the identity pose and ignores the extrinsic here), more than 5
+            // points required, set_downsample_param first — and the frame ends without an update.
+            if (feats_down_size > 5) {
+                if ((int)feats_down_body.size() != feats_down_size) fetch_scan_to_host();   // scan came from downsample_on_device
+                ikdtree.set_downsample_param((float)filter_size_map_min);
+                ikdtree.Build(feats_down_body);
             }
-            ikdtree.Build(world);
             return false;
         }
         // :165-242, whole loop on the device (V1: 18-DOF StatesGroup, 1x6 rows, rematch policy)
@@ -121,62 +118,67 @@ public:
         scan_uploaded_ = true;
         scan_on_device_ = true;
         feats_down_body.clear();
-        if (want_host_copy && n) {
-            std::vector<float> buf(n * 4);
-            ck(flivo_scan_download(ikdtree.ctx(), buf.data(), n, &n), "scan download");
-            feats_down_body.resize(n);
-            for (size_t i = 0; i < n; ++i) {
-                feats_down_body[i].x = buf[4 * i]; feats_down_body[i].y = buf[4 * i + 1]; feats_down_body[i].z = buf[4 * i + 2];
-                feats_down_body[i].intensity = buf[4 * i + 3];
-            }
-        }
+        if (want_host_copy && n) fetch_scan_to_host();
         return (int)n;
     }
+    // feats_down_body <- the current device-resident scan (x, y, z, intensity), caller's order
+    void fetch_scan_to_host() {
+        size_t n = (size_t)feats_down_size;
+        std::vector<float> buf(n * 4);
+        ck(flivo_scan_download(ikdtree.ctx(), buf.data(), n, &n), "scan download");
+        feats_down_body.assign(n, PointType());
+        for (size_t i = 0; i < n; ++i) {
+            feats_down_body[i].x = buf[4 * i]; feats_down_body[i].y = buf[4 * i + 1]; feats_down_body[i].z = buf[4 * i + 2];
+            feats_down_body[i].intensity = buf[4 * i + 3];
+        }
+    }
 
-    // src/origin_laserMapping.cpp:367-429.  pos_LiD: position of the lidar in the world (state.pos_end in the non-IKFOM
-    // branch, :381).  Slides the local-map cube when the lidar comes within MOV_THRESHOLD * DET_RANGE of a face and
-    // deletes the slabs that left it.
+    // The sliding local map of the upstream-style main (behaviour of src/origin_laserMapping.cpp:367-429).  pos_LiD: position
+    // of the lidar in the world (state.pos_end in the non-IKFOM branch, :381).  The map is kept inside an axis-aligned cube
+    // of side cube_len; when the lidar comes within MOV_THRESHOLD * DET_RANGE of a face the cube slides away from that face
+    // by slide_step() and the slab of the old cube that is no longer covered is deleted from the map, one slab per axis
+    // that moved (each slab spans the OLD cube on the other two axes, as the reference's boxes do).
+    static float MOV_THRESHOLD() { return 1.5f; }                                    // :96
+    // -1: slide toward the lower face, +1: toward the upper face, 0: stay (the lower face wins when both are near)
+    int slide_direction(int axis, const double pos_LiD[3]) const {
+        const float reach = MOV_THRESHOLD() * DET_RANGE;
+        const float to_lower = fabs(pos_LiD[axis] - LocalMap_Points.vertex_min[axis]);
+        const float to_upper = fabs(pos_LiD[axis] - LocalMap_Points.vertex_max[axis]);
+        return to_lower <= reach ? -1 : (to_upper <= reach ? +1 : 0);
+    }
+    // 90 % of the room the cube has beyond the detection reach, but at least DET_RANGE * (MOV_THRESHOLD - 1)   (:403)
+    float slide_step() const {
+        const double room = (cube_len - 2.0 * MOV_THRESHOLD() * DET_RANGE) * 0.5 * 0.9;
+        const double least = double(DET_RANGE * (MOV_THRESHOLD() - 1));
+        return (float)(room > least ? room : least);
+    }
     void lasermap_fov_segment(const double pos_LiD[3]) {
-        const float MOV_THRESHOLD = 1.5f;                                            // :96
         cub_needrm.clear();
         kdtree_delete_counter = 0;
-        if (!Localmap_Initialized) {                                                 // :383-390
-            for (int i = 0; i < 3; i++) {
-                LocalMap_Points.vertex_min[i] = pos_LiD[i] - cube_len / 2.0;
-                LocalMap_Points.vertex_max[i] = pos_LiD[i] + cube_len / 2.0;
+        if (!Localmap_Initialized) {                       // first call: centre the cube on the lidar, nothing to delete
+            for (int axis = 0; axis < 3; ++axis) {
+                LocalMap_Points.vertex_min[axis] = pos_LiD[axis] - cube_len / 2.0;
+                LocalMap_Points.vertex_max[axis] = pos_LiD[axis] + cube_len / 2.0;
             }
             Localmap_Initialized = true;
             return;
         }
-        float dist_to_map_edge[3][2];
-        bool need_move = false;
-        for (int i = 0; i < 3; i++) {                                                // :394-399
-            dist_to_map_edge[i][0] = fabs(pos_LiD[i] - LocalMap_Points.vertex_min[i]);
-            dist_to_map_edge[i][1] = fabs(pos_LiD[i] - LocalMap_Points.vertex_max[i]);
-            if (dist_to_map_edge[i][0] <= MOV_THRESHOLD * DET_RANGE || dist_to_map_edge[i][1] <= MOV_THRESHOLD * DET_RANGE) need_move = true;
+        int dir[3];
+        for (int axis = 0; axis < 3; ++axis) dir[axis] = slide_direction(axis, pos_LiD);
+        if (!dir[0] && !dir[1] && !dir[2]) return;
+        const float step = slide_step();
+        const BoxPointType before = LocalMap_Points;
+        for (int axis = 0; axis < 3; ++axis) {
+            if (!dir[axis]) continue;
+            BoxPointType slab = before;                    // what the cube leaves behind along this axis
+            if (dir[axis] < 0) slab.vertex_min[axis] = before.vertex_max[axis] - step;
+            else slab.vertex_max[axis] = before.vertex_min[axis] + step;
+            cub_needrm.push_back(slab);
+            if (dir[axis] < 0) { LocalMap_Points.vertex_min[axis] -= step; LocalMap_Points.vertex_max[axis] -= step; }
+            else { LocalMap_Points.vertex_min[axis] += step; LocalMap_Points.vertex_max[axis] += step; }
         }
-        if (!need_move) return;
-        BoxPointType New_LocalMap_Points, tmp_boxpoints;
-        New_LocalMap_Points = LocalMap_Points;
-        const double a = (cube_len - 2.0 * MOV_THRESHOLD * DET_RANGE) * 0.5 * 0.9, b = double(DET_RANGE * (MOV_THRESHOLD - 1));
-        float mov_dist = (float)(a > b ? a : b);                                     // :403
-        for (int i = 0; i < 3; i++) {                                                // :404-419
-            tmp_boxpoints = LocalMap_Points;
-            if (dist_to_map_edge[i][0] <= MOV_THRESHOLD * DET_RANGE) {
-                New_LocalMap_Points.vertex_max[i] -= mov_dist;
-                New_LocalMap_Points.vertex_min[i] -= mov_dist;
-                tmp_boxpoints.vertex_min[i] = LocalMap_Points.vertex_max[i] - mov_dist;
-                cub_needrm.push_back(tmp_boxpoints);
-            } else if (dist_to_map_edge[i][1] <= MOV_THRESHOLD * DET_RANGE) {
-                New_LocalMap_Points.vertex_max[i] += mov_dist;
-                New_LocalMap_Points.vertex_min[i] += mov_dist;
-                tmp_boxpoints.vertex_max[i] = LocalMap_Points.vertex_min[i] + mov_dist;
-                cub_needrm.push_back(tmp_boxpoints);
-            }
-        }
-        LocalMap_Points = New_LocalMap_Points;
-        points_cache_collect();                                                      // :422
-        if (cub_needrm.size() > 0) kdtree_delete_counter = ikdtree.Delete_Point_Boxes(cub_needrm);   // :424
+        points_cache_collect();                            // (:422) hand out what earlier deletes removed
+        kdtree_delete_counter = ikdtree.Delete_Point_Boxes(cub_needrm);              // (:424)
     }
     // src/origin_laserMapping.cpp:332-337
     void points_cache_collect() {

@@ -95,7 +95,7 @@ int main(int argc, char** argv) {
         if (tid < 36) { x_prop[tid] = x[tid]; M.x[tid] = x[tid]; M.xp[tid] = x[tid]; }
         if (tid == 0) { ctl.search = 1; ctl.stopped = 0; ctl.iter = -1; ctl_next_trip(&ctl); }
         __syncthreads();
-        solve_pre(S, M, mode, tid, EMU_THREADS);
+        solve_pre(S, M, mode, tid, EMU_THREADS, false);
         // ---- the trips: what the solving CTA of k_fused does after it has summed the group records ----
         for (int t = 0; t < ntrips; ++t) {
             __syncthreads();
