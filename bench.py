@@ -52,7 +52,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="flivo", choices=["flivo", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
-    ap.add_argument("--scans", type=int, default=4, help="distinct scans (poses) rotated through the steps")
+    ap.add_argument("--scans", type=int, default=8, help="distinct scans (poses) rotated through the steps")
     ap.add_argument("--mode", type=int, default=0, help="0 = V3 (1x12 row, 23-DOF), 1 = V1 (compiled 18-DOF)")
     ap.add_argument("--force-search", type=int, default=0, help="1: kNN on every trip (worst case)")
     ap.add_argument("--sort-scan", type=int, default=1)
@@ -62,7 +62,8 @@ def parse_args():
     ap.add_argument("--no-ivox", action="store_true", help="skip the informational iVox-mode (SURVEY 8f rank 4) timing")
     ap.add_argument("--no-frontend", action="store_true", help="skip the informational front-end (undistort + voxel grid) timing")
     ap.add_argument("--cpu-steps", type=int, default=3)
-    ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5)")
+    ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5) for the whole run")
+    ap.add_argument("--no-sharded", action="store_true", help="N>1 replica run: skip the `sharded` block (config 5 on the same contexts)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="sharded mode: how the per-trip 96-double records travel")
     return ap.parse_args()
 
@@ -133,7 +134,7 @@ def make_workload(name, rank, n_scans, device):
 # reference CPU path: the reference's OWN ikd-Tree (oracle/_ref, compiled unmodified from /root/reference at
 # build time) under the reference's OpenMP loop + the restated plane fit / Jacobian / solve (oracle/).
 # ---------------------------------------------------------------------------------------------------------
-def cpu_reference_run(world_xyz, scans_host, ds, mode, force_search, steps, warmup, threads, also_threads=None):
+def cpu_reference_run(world_xyz, scans_host, ds, mode, force_search, steps, warmup, threads, also_threads=None, trip_check=None):
     """-> dict(points_per_s, ms_per_step, trips, kind, cores, results[list of dict(x, n_eff, trips)]).
     also_threads: a second thread count timed on the same tree (MP_PROC_NUM = 4, what the reference's CMake
     picks on a host with more than 5 cores, CMakeLists.txt:33-36) -> keys alt_threads / alt_ms_per_step / alt_points_per_s."""
@@ -173,6 +174,7 @@ def cpu_reference_run(world_xyz, scans_host, ds, mode, force_search, steps, warm
                 pts += len(sc["body"]) * r["trips"]; secs += dt
         n_alt = max(1, min(steps, 2))
         alt = dict(alt_threads=also_threads, alt_ms_per_step=1e3 * secs / n_alt, alt_points_per_s=pts / secs)
+    trip_parity = trip_check(tree) if trip_check else None   # (before Add_Points below changes the tree)
     # map_incremental of the last scan (src/laser_mapping.cpp:329-389): world transform with the posterior + Add_Points(true)
     sc = scans_host[results[-1]["scan"]]
     wpts = orc.body_to_world(sc["body"], orc.State.from_array(results[-1]["x"]))
@@ -181,7 +183,15 @@ def cpu_reference_run(world_xyz, scans_host, ds, mode, force_search, steps, warm
     add_ms = (time.perf_counter() - t0) * 1e3
     tree.close()
     return dict(points_per_s=total_pts / total_s, ms_per_step=1e3 * total_s / steps, kind=kind, cores=threads,
-                build_s=build_s, results=results, add_points_ms=add_ms, add_points_added=int(added), **alt)
+                build_s=build_s, results=results, add_points_ms=add_ms, add_points_added=int(added), trip_parity=trip_parity, **alt)
+
+
+def bench_config(args):
+    """The `config` of the JSON line: identical in both arms (the driver compares the dicts)."""
+    n_scan, n_map, ds, kind, cfg_idx = WORKLOADS[args.workload]
+    return {"workload": args.workload, "scan_points": n_scan, "map_points": n_map, "downsample_size": ds, "k": 5,
+            "max_iter": MAX_ITER, "mode": "V1" if args.mode else "V3",
+            "policy": "force_search" if args.force_search else "reference_rematch", "scans_rotated": args.scans}
 
 
 def run_reference(args, rank, world_size):
@@ -202,15 +212,110 @@ def run_reference(args, rank, world_size):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 kNN/plane + f64 rows/solve",
         "data": "synthetic",
-        "config": {"workload": args.workload, "scan_points": n_scan, "map_points": n_map, "downsample_size": ds,
-                   "k": 5, "max_iter": MAX_ITER, "mode": "V1" if args.mode else "V3", "policy": "force_search" if args.force_search else "reference_rematch",
-                   "scans_rotated": args.scans},
+        "config": bench_config(args),
         "cpu_baseline": {"value": r["points_per_s"], "unit": "points/s", "cores": threads, "kind": r["kind"], "sample": sample,
                          "tree_build_s": r["build_s"]},
         "e2e": {"value": r["points_per_s"], "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     return line
+
+
+def full_size_trip_parity(F, pkg, tree, body, x_prior, mode):
+    """One searched h_share_model trip of the WHOLE bench scan on the GPU against the reference's own ikd-Tree
+    (oracle/_ref Nearest_Search, k = 6 so that a float32 tie across rank 5 is seen) + the restated plane fit / gates:
+    rows of neighbour ids that differ, point_selected_surf / effective-row flags that differ, ties, and the oracle's count
+    of points whose plane test or s > 0.9 gate sits within rounding distance of its threshold (`borderline`)."""
+    from oracle import pyoracle as orc
+    import flivo_parity as par
+    st = orc.State.from_array(x_prior)
+    wpts = orc.body_to_world(body, st)
+    oid, osq, oxyz, ocnt = tree.knn(wpts, 6, np.inf)
+    ties = int(((ocnt >= 6) & (osq[:, 4] == osq[:, 5])).sum())
+    cnt5 = np.minimum(ocnt, 5).astype(np.int32)
+    d5 = np.where(cnt5 >= 5, osq[:, 4], np.inf).astype(np.float32)
+    o = orc.h_share_model(body, st, np.ascontiguousarray(oxyz[:, :5]), cnt5, d5, True, mode, None)
+    g = F.h_share_model(pkg.State.from_array(x_prior), mode, True, want=("selected", "eff", "nbr_id"))
+    bound = np.inf if mode == 1 else par.GATE_SQ      # V3 searches with the far-neighbour gate as its bound
+    want = np.where((osq[:, :5] <= np.float32(bound)) & (np.arange(5)[None, :] < cnt5[:, None]), oid[:, :5], -1)
+    bad_rows = np.any(want != g["nbr_id"], axis=1)
+    # a row may legitimately differ only where a tie straddles rank 5 (ikd-Tree keeps the candidate it visited first)
+    tie_rows = (ocnt >= 6) & (osq[:, 4] == osq[:, 5])
+    return {"points": int(len(body)), "ids_mismatch_rows": int(bad_rows.sum()), "ids_mismatch_rows_not_explained_by_ties": int((bad_rows & ~tie_rows).sum()),
+            "mask_mismatch": int((g["selected"] != o["mask"]).sum()), "eff_mismatch": int((g["eff"] != o["eff"]).sum()),
+            "n_eff_gpu": int(g["n_eff"]), "n_eff_cpu": int(o["n_eff"]), "ties_across_rank5": ties, "borderline": int(o["borderline"]),
+            "HTH_rel_err": float(par.rel_err_block(g["HTH"], o["HTH"])), "HTz_rel_err": float(par.rel_err_block(g["HTz"], o["HTz"])),
+            "against": "reference ikd_Tree.cpp Nearest_Search (oracle/_ref) + restated esti_plane / gates / rows"}
+
+
+def sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev, barrier, wxyz_host, ds):
+    """BASELINE config 5 on the contexts of a replica run (N > 1): ONE scan split over the ranks (contiguous blocks of the
+    caller's order, sharding.shard_range), every rank holding the whole map; per trip each rank's 96-double record is
+    stored into every peer's exchange buffer from inside k_fused's solving CTA (NVLink peer memory), summed in rank
+    order, solved redundantly.  Returns the `sharded` object of the JSON line (rank 0) — device time per update (max
+    over ranks), exchange cost per trip from the solve's own globaltimer stamps, and the posterior checked against the
+    reference-tree CPU path (oracle/_ref) on the WHOLE scan."""
+    import torch
+    import torch.distributed as dist
+    from importlib import import_module
+    shard_range = import_module(pkg.__name__ + ".sharding").shard_range
+    handles = [None] * world_size
+    dist.all_gather_object(handles, F.peer_export())
+    F.peer_attach(handles, rank, world_size)
+    parts = []
+    for s in shared:
+        lo, hi = shard_range(len(s["body"]), rank, world_size)
+        b4 = torch.zeros((hi - lo, 4), dtype=torch.float32, device=dev)
+        b4[:, :3] = s["body"][lo:hi]
+        parts.append(b4)
+    S = len(shared)
+
+    def step(i, c=cfg):
+        barrier()                                       # the ranks enter the update together (the exchange waits at most 2 s)
+        F.scan_set_device(parts[i].data_ptr(), parts[i].shape[0])
+        return F.iekf_update(pkg.State.from_array(shared[i]["x_prior"]), P0, c)
+
+    for w in range(max(args.warmup, 3)):
+        step(w % S)
+    ms, trips = [], 0
+    for k in range(args.steps):
+        _, _, rp = step(k % S)
+        ms.append(rp.gpu_ms); trips += rp.trips
+    xphase, xwait = [], []
+    for k in range(3):                                  # profile mode: plain launches, globaltimer stamps inside the solve
+        _, _, rp = step(k % S, cfg_prof)
+        st = F.solve_stamps(rp.trips).astype(np.int64)
+        for t in range(rp.trips):
+            if st[t][0] and st[t][1]:
+                xphase.append((st[t][1] - st[t][0]) / 1e3)
+            if st[t][10] and st[t][11]:
+                xwait.append((st[t][11] - st[t][10]) / 1e3)
+    tt = torch.tensor([sum(ms), float(np.mean(xphase)) if xphase else 0.0, float(np.mean(xwait)) if xwait else 0.0], dtype=torch.float64, device=dev)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    xs, Ps, reps = step(0)
+    out = None
+    if rank == 0:
+        n_full = len(shared[0]["body"])
+        out = {"workload": args.workload, "scan_points": n_full, "ranks": world_size, "exchange": "peer memory (stores into the peers' HBM + release/acquire sequence flags inside k_fused)",
+               "ms_per_step": float(tt[0]) / args.steps, "points_per_sec": n_full * trips / (float(tt[0]) * 1e-3), "trips_per_step": trips / args.steps,
+               "exchange_us_per_trip": float(tt[1]), "exchange_wait_us_per_trip": float(tt[2]),
+               "note": "ms_per_step: in-graph device time (staging + update), max over ranks; exchange_us_per_trip: record stores + flag + wait for all peers + rank-order sum (globaltimer stamps, profile mode, max over ranks); the wait share includes the ranks' arrival skew"}
+        if not args.no_cpu_baseline:
+            from oracle import pyoracle as orc
+            tree = orc.RefTree(ds)
+            tree.build(wxyz_host)
+            body = np.ascontiguousarray(shared[0]["body"].cpu().numpy())
+            o = tree.iekf_update(body, orc.State.from_array(shared[0]["x_prior"]), P0, mode=args.mode, max_iter=MAX_ITER,
+                                 laser_point_cov=LASER_POINT_COV, nthreads=os.cpu_count() or 1, force_search=bool(args.force_search))
+            tree.close()
+            out["shard_check"] = {"against": "reference ikd_Tree.cpp + restated loop on the whole scan (oracle/_ref), CPU",
+                                  "x_max_abs_diff": float(np.abs(xs.as_array() - o["x"].as_array()).max()),
+                                  "P_max_rel_diff": float(np.abs(np.asarray(Ps) - o["P"]).max() / np.abs(o["P"]).max()),
+                                  "n_eff_sharded": int(reps.n_eff), "n_eff_cpu": int(o["n_eff"]),
+                                  "trips_sharded": int(reps.trips), "trips_cpu": int(o["trips"])}
+    barrier()
+    F.peer_detach()
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -242,6 +347,12 @@ def run_flivo(args, rank, world_size, local_rank):
     F.Build(wxyz_host)
     F.sync()
     map_build_s = time.time() - t0
+    shared = None
+    if world_size > 1 and not shard and not args.no_sharded:
+        # the scans of the `sharded` block: the same two on every rank (rank 0's first poses), see sharded_block
+        import flivo_scenes as scenes
+        p0 = scenes.street_positions(world, args.scans)[:2]
+        shared = [scenes.make_scan_torch(world, seed=i, n_points=n_scan, kind=kind, pos=p0[i], device=dev) for i in range(2)]
     del world
     if shard:   # config 5: contiguous block of every scan per rank + allgather of the normal-equation block per trip
         if args.exchange == "peer":   # records written straight into the peers' HBM by the solve kernel (NVLink)
@@ -297,7 +408,7 @@ def run_flivo(args, rank, world_size, local_rank):
     t_wall0 = time.time()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     trips_total, launches, fused_search_ms, fused_reuse_ms, solve_ms, last = 0, 0, [], [], [], None
-    solve_us = []
+    solve_us, graph_ms = [], []
     for k in range(args.steps):
         flush.zero_()
         torch.cuda.synchronize()
@@ -305,10 +416,14 @@ def run_flivo(args, rank, world_size, local_rank):
         x, P, rep = step_resident(k % S)
         ev[k][1].record(ext)
         trips_total += rep.trips
-        launches += rep.kernel_launches + (2 if args.sort_scan else 0)   # own kernels: the update graph's + k_scan_keys, k_gather4 (the four CUB radix-sort kernels of the staging graph are library code and not counted)
+        launches += rep.kernel_launches   # own kernels only: k_scan_prepare, k_gather4, k_ctl_reset, (k_search, k_fused) per trip; the CUB radix-sort kernels of the staging graph are library code and not counted
+        graph_ms.append(rep.gpu_ms)       # event-record NODES at the head of the staging graph and the tail of the update graph
         last = (k % S, x, P, rep)
     barrier()
-    step_ms = sorted(a.elapsed_time(b) for a, b in ev)   # this rank's per-step device times (median + p99)
+    host_ev_ms = sorted(a.elapsed_time(b) for a, b in ev)   # events recorded from the host around the call (r1's method; moves when the host is busy)
+    # a step = scan staging + update; its device time is read between two stamps the GPU takes itself (first node of the
+    # staging graph, last node of the update graph), so host scheduling noise between the two graph launches cannot enter it
+    step_ms = sorted(graph_ms)   # this rank's per-step device times (median + p99)
     dev_ms = sum(step_ms)
     tt = torch.tensor([dev_ms, float(trips_total) * pts_per_scan, float(launches)], dtype=torch.float64, device=dev)
     if world_size > 1:
@@ -350,17 +465,50 @@ def run_flivo(args, rank, world_size, local_rank):
                 print(f"[solve inside k_fused, trip {t}] us: exchange={d[0]} unpack={d[1]} aug={d[2]} gj={d[3]} gain={d[4]} plus+ctl={d[5]} cov|next-pre={d[6]} total={tot} peer-wait={xw}", file=sys.stderr)
                 solve_us.append(tot)
 
-    # ---- e2e: host buffers through the C ABI, wall clock, H2D + D2H inside ----
+    # ---- e2e: host buffers through the C ABI, wall clock, H2D + D2H inside the timed region ----
+    # (a) serial (r1's number, kept for comparison): flivo_scan_upload of the 48-byte AoS from pageable memory, then
+    #     flivo_iekf_update, one after the other; L2 flushed (untimed) between steps.
     for w in range(min(args.warmup, 2)):
         step_e2e(w % S)
-    e2e_s, e2e_work = 0.0, 0.0
-    for k in range(args.steps):
+    ser_s, ser_work = 0.0, 0.0
+    for k in range(min(args.steps, 10)):
         flush.zero_()
         barrier()
         t0 = time.perf_counter()
         x2, P2, rep2 = step_e2e(k % S)
-        e2e_s += time.perf_counter() - t0
-        e2e_work += rep2.trips * host_scans[k % S].shape[0]
+        ser_s += time.perf_counter() - t0
+        ser_work += rep2.trips * host_scans[k % S].shape[0]
+    e2e_serial = ser_work / ser_s
+    # (b) pipelined (the headline e2e): the node hands one feats_down_body over per frame (src/laser_mapping.cpp:129-130,
+    #     165-167) in a buffer it reuses, so the buffers are registered once (flivo_host_register) and travel as they are —
+    #     whole 48-byte records, one DMA, xyz gathered on the device.  While update k runs (flivo_iekf_update_begin), scan
+    #     k+1 travels on the copy stream (flivo_scan_upload_async); flivo_iekf_update_end reads x, P and the report back.
+    #     Wall clock over K back-to-back steps: K uploads (scan k+1 during step k), K updates, K result read-backs inside.
+    #     No flush here: the rotated scans stand at different poses and together touch more of the map than L2 holds.
+    for h in host_scans:
+        F._ck(L.flivo_host_register(h.ctypes.data, h.nbytes))
+    states = [pkg.State.from_array(s["x_prior"]) for s in scans]
+
+    def pipelined(n_steps):
+        work = 0.0
+        F.scan_upload_async(host_scans[0], 48)
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(n_steps):
+            F.scan_commit()
+            F.iekf_update_begin(states[k % S], P0, cfg)
+            F.scan_upload_async(host_scans[(k + 1) % S], 48)
+            _, _, r = F.iekf_update_end()
+            work += r.trips * host_scans[k % S].shape[0]
+        dt = time.perf_counter() - t0
+        F.scan_commit()   # retire the scan staged during the last step
+        return dt, work
+
+    pipelined(min(args.warmup, 3))
+    e2e_s, e2e_work = pipelined(args.steps)
+    for h in host_scans:
+        L.flivo_host_unregister(h.ctypes.data)
+    sharded = sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev, barrier, wxyz_host, ds) if shared else None
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None   # covers the device-resident, profile and e2e timed loops
     te = torch.tensor([e2e_s, e2e_work], dtype=torch.float64, device=dev)
@@ -488,13 +636,14 @@ def run_flivo(args, rank, world_size, local_rank):
                            "trips_sharded": int(reps.trips), "trips_single": int(rep1.trips)}
             del F1
         barrier()
-    h2d = int(pts_per_scan * 16 + 36 * 8 + npd * npd * 8)
+    h2d = int(pts_per_scan * 48 + 36 * 8 + npd * npd * 8 + 512)   # the raw 48-byte records travel + the job / state / P block
     d2h = int(36 * 8 + npd * npd * 8 + 512)
     return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
                 trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add, ivox=ivox,
                 step_ms_median=float(np.median(step_ms)), step_ms_p99=float(np.percentile(step_ms, 99)), step_ms_min=float(step_ms[0]),
+                host_ev_ms_mean=float(np.mean(host_ev_ms)), sharded=sharded, solve_us=[v for v in solve_us if v is not None], e2e_serial=e2e_serial,
                 search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
@@ -542,12 +691,13 @@ def main():
     ms_r = float(np.mean(r["fused_reuse_ms"])) if r["fused_reuse_ms"] else None
     n_local = r["pts_per_scan"]
     ach = SEARCH_BYTES * n_local / (ms_s * 1e-3) / 1e9 if ms_s else None
-    roof = {"bound": "hbm", "kernel": "k_search + k_fused (search trip)", "achieved": ach, "peak": peak, "unit": "GB/s",
+    roof = {"bound": "hbm", "kernel": "k_search + k_fused of a search trip (the trip's solve runs inside k_fused's last CTA)", "achieved": ach, "peak": peak, "unit": "GB/s",
             "frac": (ach / peak) if ach else None, "traffic": None, "peak_source": peak_src,
             "bytes_per_point_trip": SEARCH_BYTES, "points_per_launch": n_local, "avg_launch_ms": ms_s,
             "reuse_trip": {"bytes_per_point_trip": REUSE_BYTES, "avg_launch_ms": ms_r,
                            "achieved": (REUSE_BYTES * n_local / (ms_r * 1e-3) / 1e9) if ms_r else None},
-            "solve_avg_ms": float(np.mean(r["solve_ms"])) if r["solve_ms"] else None}
+            "k_fused_incl_solve_avg_ms": float(np.mean(r["solve_ms"])) if r["solve_ms"] else None,
+            "solve_inside_k_fused_us": (float(np.mean(r["solve_us"])) if r["solve_us"] else None)}
     tp = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu --set full capture
     if os.path.exists(tp):
         try:
@@ -559,7 +709,13 @@ def main():
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         scans_host = [dict(body=r["host_xyz"][i], x_prior=r["scans"][i]["x_prior"]) for i in range(len(r["scans"]))]
         threads = os.cpu_count() or 1
-        c = cpu_reference_run(r["wxyz_host"], scans_host, ds, args.mode, args.force_search, args.cpu_steps, 1, threads, also_threads=4)
+        F_, pkg_ = r["F"], r["pkg"]
+
+        def trip_check(tree):   # whole scan 0, one searched trip: ids / masks of all points against the reference tree
+            F_.scan_upload(r["host_xyz"][0])
+            return full_size_trip_parity(F_, pkg_, tree, r["host_xyz"][0], r["scans"][0]["x_prior"], args.mode)
+
+        c = cpu_reference_run(r["wxyz_host"], scans_host, ds, args.mode, args.force_search, args.cpu_steps, 1, threads, also_threads=4, trip_check=trip_check)
         cpu = {"value": c["points_per_s"], "unit": "points/s", "cores": threads, "kind": c["kind"],
                "mp_proc_num_4": ({"value": c["alt_points_per_s"], "ms_per_scan": c["alt_ms_per_step"], "cores": c["alt_threads"],
                                   "note": "MP_PROC_NUM = 4: the thread count the reference's own CMake picks (CMakeLists.txt:33-36); "
@@ -579,24 +735,27 @@ def main():
             cands = [c["results"][-1]]
         q = cands[-1]
         parity = {"scan": j, "x_max_abs_diff": float(np.abs(xg.as_array() - q["x"]).max()), "n_eff_gpu": int(rep.n_eff),
-                  "n_eff_cpu": int(q["n_eff"]), "trips_gpu": int(rep.trips), "trips_cpu": int(q["trips"])}
+                  "n_eff_cpu": int(q["n_eff"]), "trips_gpu": int(rep.trips), "trips_cpu": int(q["trips"]),
+                  "first_trip_all_points": c["trip_parity"]}
     if rank == 0:
         line = {
             "metric": "iekf_measurement_update_points_per_sec", "value": r["value"], "unit": "points/s", "n_gpus": world_size,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["dev_ms"] / args.steps, "higher_is_better": True,
             "scaling": "strong" if r["shard"] else "weak", "vs_baseline": None, "dtype": "f32 kNN/plane + f64 rows/solve", "data": "synthetic",
-            "config": {"workload": args.workload, "scan_points": n_scan, "map_points": n_map, "downsample_size": ds, "k": 5,
-                       "max_iter": MAX_ITER, "mode": "V1" if args.mode else "V3",
-                       "policy": "force_search" if args.force_search else "reference_rematch", "scans_rotated": args.scans,
-                       "trips_per_step": r["trips_per_step"], "sort_scan": bool(args.sort_scan),
-                       "l2": "512 MiB buffer written between timed steps (untimed); map 20M pts > L2",
-                       "multi_gpu": (("one scan sharded over ranks; per trip 96 doubles per rank, " + ("stored into the peers' HBM by the solve kernel (NVLink peer memory)" if args.exchange == "peer" else "ncclAllGather")) if r["shard"] else
-                                     "map replica + own scans per rank, no collective")},
+            "config": bench_config(args),
+            "run": {"trips_per_step": r["trips_per_step"], "sort_scan": bool(args.sort_scan),
+                    "l2": "value: 512 MiB buffer written between timed steps (untimed). e2e: no flush, %d rotated scans at different poses (map %d pts = %.1f GB of buckets > 126 MB L2)" % (args.scans, n_map, n_map * 40 / 1e9),
+                    "timing": "value: per step, CUDA event-record nodes at the head of the staging graph and the tail of the update graph, summed over the steps, max over ranks. e2e: wall clock over the K pipelined steps, max over ranks",
+                    "multi_gpu": (("one scan sharded over ranks; per trip 96 doubles per rank, " + ("stored into the peers' HBM from inside k_fused's solving CTA (NVLink peer memory)" if args.exchange == "peer" else "ncclAllGather")) if r["shard"] else
+                                  "map replica + own scans per rank, no collective")},
             "latency_ms_per_scan": r["dev_ms"] / args.steps,
             "latency_ms_per_scan_stats": {"median": r["step_ms_median"], "p99": r["step_ms_p99"], "min": r["step_ms_min"],
-                                          "note": "per-step CUDA-event times of rank 0 over the timed steps"},
-            "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
-            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
+                                          "host_recorded_events_mean": r["host_ev_ms_mean"],
+                                          "note": "per-step device times of rank 0 over the timed steps (in-graph event nodes); host_recorded_events_mean = the same steps between events recorded from the host around the call"},
+            "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (registered host buffer) during flivo_iekf_update_begin/_end of the current one",
+                    "serial_value": r["e2e_serial"], "serial_how": "flivo_scan_upload (pageable buffer, host repack) then flivo_iekf_update, L2 flushed between steps"},
+            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "sharded": r["sharded"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
         }
         print(json.dumps(line), file=out, flush=True)

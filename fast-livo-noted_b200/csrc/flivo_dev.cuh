@@ -31,7 +31,26 @@ constexpr int EMPTY_ID = -1;
 constexpr int COORD_BIAS = 1 << 20;  // voxel keys are biased into [0, 2^21)
 constexpr uint32_t INF_BITS = 0x7F800000u;
 
+// Search record of one directory slot, derived from dir_keys / blk_mask / cell_tab (which stay authoritative for the
+// insert / delete pipelines) and kept in step with them by map.cu (k_block_records).  One aligned 32-byte sector answers
+// "is this the block, which of its cells are occupied, where are their buckets": a shell probe costs ONE dependent
+// round trip per block instead of three (key -> occupancy -> cell table).
+//   base != NONE32 : the block is COMPACT — the buckets of its occupied cells are consecutive in cell-offset order, so
+//                    bucket(cell off) = base + popc(mask & ((1 << off) - 1)) and the cell table is not read at all.
+//                    Every block whose cells were all created by one insert batch is (Build; new ground of a scan).
+//   base == NONE32 : cells were added to the block by a later batch; their buckets are looked up in cell_tab.
+struct __align__(32) BlockRec {
+    unsigned long long key;        // packed block coordinates, DIR_EMPTY = free slot (same as dir_keys[slot])
+    unsigned long long mask;       // occupancy bits (same as blk_mask[slot])
+    uint32_t base;
+    uint32_t pad[3];
+};
+// work-list / queue entries of the search name a cell either by its bucket (compact block) or by its cell_tab index
+constexpr uint32_t CELL_DIRECT = 0x80000000u;
+constexpr size_t DIR_CAP_MAX = 1ull << 25;   // cell_tab indices (slot * 64 + off) must stay below CELL_DIRECT
+
 struct MapView {
+    const BlockRec* rec;           // [dir_cap] search records
     unsigned long long* dir_keys;  // [dir_cap]
     uint32_t* cell_tab;            // [dir_cap * 64]
     unsigned long long* blk_mask;  // [dir_cap]
@@ -121,6 +140,31 @@ __device__ __forceinline__ uint32_t hash_block(unsigned long long k) {
     return (uint32_t)k;
 }
 __device__ __forceinline__ int cell_off(int cx, int cy, int cz) { return ((cx & 3) << 4) | ((cy & 3) << 2) | (cz & 3); }
+
+// directory lookup through the search records: slot index or -1; mask / base of the block on success.  One 32-byte load
+// per probe (ld.global.nc.v4.u64 on sm_100: the whole record in one instruction).
+__device__ __forceinline__ void ld_rec(const BlockRec* p, unsigned long long& key, unsigned long long& mask, uint32_t& base) {
+    unsigned long long w2, w3;
+    asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(key), "=l"(mask), "=l"(w2), "=l"(w3) : "l"(p));
+    base = (uint32_t)w2;
+}
+__device__ __forceinline__ int rec_find(const MapView& m, unsigned long long key, unsigned long long& mask, uint32_t& base) {
+    uint32_t s = hash_block(key) & m.dir_mask;
+    while (true) {
+        unsigned long long k;
+        ld_rec(m.rec + s, k, mask, base);
+        if (k == key) return (int)s;
+        if (k == DIR_EMPTY) { mask = 0ull; return -1; }
+        s = (s + 1) & m.dir_mask;
+    }
+}
+// cell `off` of a found block as a work-list entry (see CELL_DIRECT)
+__device__ __forceinline__ uint32_t cell_entry(int slot, unsigned long long mask, uint32_t base, int off) {
+    return base != NONE32 ? (CELL_DIRECT | (base + (uint32_t)__popcll(mask & ((1ull << off) - 1ull)))) : ((uint32_t)slot * 64u + (uint32_t)off);
+}
+__device__ __forceinline__ uint32_t entry_bucket(const MapView& m, uint32_t e) {
+    return (e & CELL_DIRECT) ? (e & ~CELL_DIRECT) : __ldg(m.cell_tab + e);
+}
 
 // directory lookup: slot index or -1
 __device__ __forceinline__ int dir_find(const MapView& m, unsigned long long key) {

@@ -158,12 +158,19 @@ __global__ void k_count_unique(const unsigned long long* __restrict__ keys, size
     }
 }
 
-// one thread per cell head: make sure block, cell and (for non-downsampled inserts) enough chained
-// buckets exist before any point is stored
-__global__ void k_create_cells(const unsigned long long* __restrict__ keys, size_t n, MapView m, MapCounters* cnt,
-                               int prealloc_chain) {
+// Cell creation of an insert batch, in three steps so that the NEW cells of the batch receive consecutive buckets in
+// sorted-key order (block, then cell offset): a block whose cells all come from one batch is then "compact" — its
+// buckets are base + rank of the cell among the block's occupied cells — and the search needs no cell table for it
+// (BlockRec, flivo_dev.cuh).
+//   k_cells_mark   : one thread per cell head: block slot (created if missing), flag = the cell does not exist yet
+//   (exclusive scan of the flags -> rank of every new cell; k_cells_reserve takes the bucket range in one step)
+//   k_cells_create : new cell -> bucket = range start + rank; then, for non-downsampled inserts, enough chained
+//                    buckets for the incoming points (taken from the bump allocator behind the range)
+__global__ void k_cells_mark(const unsigned long long* __restrict__ keys, size_t n, MapView m, MapCounters* cnt,
+                             unsigned int* __restrict__ is_new) {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
+    is_new[i] = 0;
     unsigned long long key = keys[i];
     if (key == INVALID_KEY) return;
     if (i != 0 && (key >> 6) == (keys[i - 1] >> 6)) return;
@@ -172,16 +179,42 @@ __global__ void k_create_cells(const unsigned long long* __restrict__ keys, size
     int cx = kx >> m.gshift, cy = ky >> m.gshift, cz = kz >> m.gshift;
     int slot = dir_find_or_insert(m, pack_block(cx >> 2, cy >> 2, cz >> 2), cnt);
     if (slot < 0) return;
+    if (m.cell_tab[(size_t)slot * 64 + cell_off(cx, cy, cz)] == NONE32) is_new[i] = 1;
+}
+// misc[4] = first bucket of the batch's new cells; the bump allocator moves past them
+__global__ void k_cells_reserve(const unsigned int* __restrict__ is_new, const unsigned int* __restrict__ rank, size_t n,
+                                MapView m, MapCounters* cnt, unsigned int* misc) {
+    if (threadIdx.x || blockIdx.x) return;
+    const unsigned int total = rank[n - 1] + is_new[n - 1];
+    const unsigned int first = cnt->buckets_used;
+    misc[4] = first;
+    cnt->buckets_used = first + total;
+    cnt->cells_used += total;
+    if ((size_t)first + total > m.bucket_cap) cnt->error = 3;
+}
+__global__ void k_cells_create(const unsigned long long* __restrict__ keys, size_t n, MapView m, MapCounters* cnt,
+                               const unsigned int* __restrict__ is_new, const unsigned int* __restrict__ rank,
+                               const unsigned int* __restrict__ misc, int prealloc_chain) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long key = keys[i];
+    if (key == INVALID_KEY) return;
+    if (i != 0 && (key >> 6) == (keys[i - 1] >> 6)) return;
+    int kx, ky, kz;
+    decode_sort_key(key, m.gshift, kx, ky, kz);
+    int cx = kx >> m.gshift, cy = ky >> m.gshift, cz = kz >> m.gshift;
+    int slot = dir_find_rw(m, pack_block(cx >> 2, cy >> 2, cz >> 2));
+    if (slot < 0) return;
     int off = cell_off(cx, cy, cz);
     uint32_t* entry = m.cell_tab + (size_t)slot * 64 + off;
     uint32_t b = *entry;
-    if (b == NONE32) {
-        b = atomicAdd(&cnt->buckets_used, 1u);
+    if (is_new[i]) {
+        b = misc[4] + rank[i];
         if (b >= m.bucket_cap) { atomicExch(&cnt->error, 3); return; }
         *entry = b;
         atomicOr(m.blk_mask + slot, 1ull << off);
-        atomicAdd(&cnt->cells_used, 1u);
     }
+    if (b == NONE32) return;
     if (!prealloc_chain) return;
     // count incoming points of this cell and free slots of its chain; append what is missing
     size_t j = i + 1;
@@ -202,6 +235,45 @@ __global__ void k_create_cells(const unsigned long long* __restrict__ keys, size
         last = nb;
         need -= BUCKET_SLOTS;
     }
+}
+
+// search record of one directory slot from the authoritative tables (see BlockRec)
+__device__ __forceinline__ void write_record(const MapView& m, BlockRec* rec, uint32_t slot) {
+    const unsigned long long key = m.dir_keys[slot], mask = m.blk_mask[slot];
+    uint32_t base = NONE32;
+    if (key != DIR_EMPTY && mask) {
+        const uint32_t* tab = m.cell_tab + (size_t)slot * 64;
+        unsigned long long bits = mask;
+        base = tab[__ffsll((long long)bits) - 1];
+        uint32_t r = 0;
+        while (bits) {
+            const int off = __ffsll((long long)bits) - 1;
+            bits &= bits - 1;
+            if (tab[off] != base + r) { base = NONE32; break; }
+            ++r;
+        }
+        if (base != NONE32 && (base + 64u) >= CELL_DIRECT) base = NONE32;
+    }
+    BlockRec v;
+    v.key = key; v.mask = mask; v.base = base; v.pad[0] = v.pad[1] = v.pad[2] = 0;
+    rec[slot] = v;
+}
+// after the cells of a batch exist: one thread per block head of the sorted batch refreshes that block's record
+__global__ void k_block_records(const unsigned long long* __restrict__ keys, size_t n, MapView m, BlockRec* rec) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long key = keys[i];
+    if (key == INVALID_KEY) return;
+    if (i != 0 && (key >> 12) == (keys[i - 1] >> 12)) return;
+    int kx, ky, kz;
+    decode_sort_key(key, m.gshift, kx, ky, kz);
+    int slot = dir_find_rw(m, pack_block((kx >> m.gshift) >> 2, (ky >> m.gshift) >> 2, (kz >> m.gshift) >> 2));
+    if (slot >= 0) write_record(m, rec, (uint32_t)slot);
+}
+// every slot (after the directory was rehashed into a larger table)
+__global__ void k_all_records(MapView m, size_t dir_cap, BlockRec* rec) {
+    size_t s = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (s < dir_cap) write_record(m, rec, (uint32_t)s);
 }
 
 // non-downsampled insert: every point is stored
@@ -672,6 +744,7 @@ MapStore::~MapStore() { release(); }
 
 void MapStore::release() {
     cudaFree(v_.dir_keys); cudaFree(v_.cell_tab); cudaFree(v_.blk_mask); cudaFree(v_.buckets); cudaFree(v_.bucket_next);
+    cudaFree(const_cast<BlockRec*>(v_.rec));
     v_ = MapView{};
     cudaFree(d_cnt_); d_cnt_ = nullptr;
     if (h_pinned_) cudaFreeHost(h_pinned_);
@@ -688,6 +761,8 @@ int MapStore::alloc_tables(size_t dir_cap, size_t bucket_cap, std::string& err) 
     CK(cudaMalloc(&v_.dir_keys, dir_cap * sizeof(unsigned long long)));
     CK(cudaMalloc(&v_.cell_tab, dir_cap * 64 * sizeof(uint32_t)));
     CK(cudaMalloc(&v_.blk_mask, dir_cap * sizeof(unsigned long long)));
+    CK(cudaMalloc((void**)&v_.rec, dir_cap * sizeof(BlockRec)));
+    CK(cudaMemsetAsync((void*)v_.rec, 0xFF, dir_cap * sizeof(BlockRec), stream_));   // key = DIR_EMPTY everywhere
     CK(cudaMalloc(&v_.buckets, bucket_cap * BUCKET_SLOTS * sizeof(float4)));
     CK(cudaMalloc(&v_.bucket_next, bucket_cap * sizeof(uint32_t)));
     CK(cudaMemsetAsync(v_.dir_keys, 0xFF, dir_cap * sizeof(unsigned long long), stream_));
@@ -762,11 +837,13 @@ int MapStore::grow_dir(size_t new_cap, std::string& err) {
     CK(cudaMemsetAsync(nv.dir_keys, 0xFF, new_cap * sizeof(unsigned long long), stream_));
     CK(cudaMemsetAsync(nv.cell_tab, 0xFF, new_cap * 64 * sizeof(uint32_t), stream_));
     CK(cudaMemsetAsync(nv.blk_mask, 0, new_cap * sizeof(unsigned long long), stream_));
+    CK(cudaMalloc((void**)&nv.rec, new_cap * sizeof(BlockRec)));
     nv.dir_mask = (uint32_t)(new_cap - 1);
     k_rehash<<<nblk(old_cap * 32, 256), 256, 0, stream_>>>(oldv, old_cap, nv, d_cnt_);
+    k_all_records<<<nblk(new_cap, 256), 256, 0, stream_>>>(nv, new_cap, const_cast<BlockRec*>(nv.rec));
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(stream_));
-    cudaFree(oldv.dir_keys); cudaFree(oldv.cell_tab); cudaFree(oldv.blk_mask);
+    cudaFree(oldv.dir_keys); cudaFree(oldv.cell_tab); cudaFree(oldv.blk_mask); cudaFree(const_cast<BlockRec*>(oldv.rec));
     v_ = nv;
     dir_cap_ = new_cap;
     return 0;
@@ -793,7 +870,7 @@ int MapStore::ensure_capacity(size_t new_blocks_ub, size_t new_buckets_ub, std::
     size_t need_dir = (blocks_ub_ + new_blocks_ub) * 5 / 2 + 64;  // load factor <= 0.4
     if (need_dir > dir_cap_) {
         size_t nc = next_pow2(need_dir);
-        if (nc > (1ull << 31)) { err = "block directory would exceed 2^31 slots"; return -3; }
+        if (nc > DIR_CAP_MAX) { err = "block directory would exceed 2^25 slots"; return -3; }
         if (grow_dir(nc, err)) return -1;
     }
     size_t need_b = buckets_ub_ + new_buckets_ub + 64;
@@ -825,7 +902,9 @@ int MapStore::ensure_scratch(size_t n, std::string& err) {
     cub::DeviceRadixSort::SortPairs(nullptr, b1, keys_a_, keys_b_, idx_a_, idx_b_, (int)std::min<size_t>(cap, 0x7FFFFFFF), 0, 63, stream_);
     cub::DeviceSelect::Flagged(nullptr, b2, thrust::counting_iterator<unsigned int>(0), defer_flag_, defer_list_, d_misc_ + 3,
                                (int)std::min<size_t>(cap, 0x7FFFFFFF), stream_);
-    cub_tmp_bytes_ = std::max(b1, b2) + 256;
+    size_t b3 = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, b3, idx_a_, idx_b_, (int)std::min<size_t>(cap, 0x7FFFFFFF), stream_);
+    cub_tmp_bytes_ = std::max(std::max(b1, b2), b3) + 256;
     CK(cudaMalloc(&cub_tmp_, cub_tmp_bytes_));
     scratch_n_ = cap;
     return 0;
@@ -864,7 +943,16 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
     size_t chain_extra = downsample_on ? 64 : n / BUCKET_SLOTS + 64;
     if (ensure_capacity(new_blocks, new_cells + chain_extra, err)) return -1;
     CK(cudaMemsetAsync(d_misc_, 0, 16 * sizeof(unsigned int), stream_));
-    k_create_cells<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, d_cnt_, downsample_on ? 0 : 1);
+    // cells of the batch (new ones get consecutive buckets in key order), then the search records of the touched blocks;
+    // idx_a_ / keys_a_ are free once the sort has produced keys_b_ / idx_b_
+    unsigned int* is_new = idx_a_;
+    unsigned int* rank = reinterpret_cast<unsigned int*>(keys_a_);
+    k_cells_mark<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, d_cnt_, is_new);
+    tmp = cub_tmp_bytes_;
+    CK(cub::DeviceScan::ExclusiveSum(cub_tmp_, tmp, is_new, rank, (int)n, stream_));
+    k_cells_reserve<<<1, 32, 0, stream_>>>(is_new, rank, n, v_, d_cnt_, d_misc_);
+    k_cells_create<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, d_cnt_, is_new, rank, d_misc_, downsample_on ? 0 : 1);
+    k_block_records<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, const_cast<BlockRec*>(v_.rec));
     CK(cudaGetLastError());
     if (!downsample_on) {
         k_insert_all<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, d_cnt_);
@@ -895,6 +983,7 @@ int MapStore::build(const float4* d_pts, size_t n, std::string& err) {
     CK(cudaMemsetAsync(v_.dir_keys, 0xFF, dir_cap_ * sizeof(unsigned long long), stream_));
     CK(cudaMemsetAsync(v_.cell_tab, 0xFF, dir_cap_ * 64 * sizeof(uint32_t), stream_));
     CK(cudaMemsetAsync(v_.blk_mask, 0, dir_cap_ * sizeof(unsigned long long), stream_));
+    CK(cudaMemsetAsync((void*)v_.rec, 0xFF, dir_cap_ * sizeof(BlockRec), stream_));
     size_t used = std::min<size_t>(bucket_cap_, (size_t)buckets_ub_ + 64);
     CK(cudaMemsetAsync(v_.buckets, 0xFF, used * BUCKET_SLOTS * sizeof(float4), stream_));
     CK(cudaMemsetAsync(v_.bucket_next, 0xFF, used * sizeof(uint32_t), stream_));
@@ -1049,6 +1138,7 @@ int MapStore::set_downsample(float ds, std::string& err) {
     CK(cudaMemsetAsync(v_.dir_keys, 0xFF, dir_cap_ * sizeof(unsigned long long), stream_));
     CK(cudaMemsetAsync(v_.cell_tab, 0xFF, dir_cap_ * 64 * sizeof(uint32_t), stream_));
     CK(cudaMemsetAsync(v_.blk_mask, 0, dir_cap_ * sizeof(unsigned long long), stream_));
+    CK(cudaMemsetAsync((void*)v_.rec, 0xFF, dir_cap_ * sizeof(BlockRec), stream_));
     CK(cudaMemsetAsync(v_.buckets, 0xFF, bucket_cap_ * BUCKET_SLOTS * sizeof(float4), stream_));
     CK(cudaMemsetAsync(v_.bucket_next, 0xFF, bucket_cap_ * sizeof(uint32_t), stream_));
     unsigned int rc_keep = h_cnt_.removed_count;

@@ -401,7 +401,9 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
     const int nbx = ((cqx + 1) >> 2) - bx0, nby = ((cqy + 1) >> 2) - by0, nbz = ((cqz + 1) >> 2) - bz0;   // 0 or 1
     int slots[8];
     unsigned long long occs[8];
+    uint32_t bases[8];
     if (PAR_PROBES) {
+        // eight independent record loads (one 32-byte sector each): ONE global-memory round trip for the whole shell
         unsigned long long bkey[8], k0[8];
         uint32_t hs[8];
 #pragma unroll
@@ -412,24 +414,25 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
             hs[ib] = hash_block(bkey[ib]) & m.dir_mask;
         }
 #pragma unroll
-        for (int ib = 0; ib < 8; ++ib) k0[ib] = (bkey[ib] != DIR_EMPTY) ? __ldg(m.dir_keys + hs[ib]) : DIR_EMPTY;
+        for (int ib = 0; ib < 8; ++ib) {
+            k0[ib] = DIR_EMPTY; occs[ib] = 0ull; bases[ib] = NONE32;
+            if (bkey[ib] != DIR_EMPTY) ld_rec(m.rec + hs[ib], k0[ib], occs[ib], bases[ib]);
+        }
 #pragma unroll
         for (int ib = 0; ib < 8; ++ib) {
             int sl = -1;
             if (bkey[ib] != DIR_EMPTY) {
                 uint32_t h = hs[ib];
-                unsigned long long k = k0[ib];
                 while (true) {                       // linear probing: the first slot answers almost always
-                    if (k == bkey[ib]) { sl = (int)h; break; }
-                    if (k == DIR_EMPTY) break;
+                    if (k0[ib] == bkey[ib]) { sl = (int)h; break; }
+                    if (k0[ib] == DIR_EMPTY) break;
                     h = (h + 1) & m.dir_mask;
-                    k = __ldg(m.dir_keys + h);
+                    ld_rec(m.rec + h, k0[ib], occs[ib], bases[ib]);
                 }
             }
             slots[ib] = sl;
+            if (sl < 0) occs[ib] = 0ull;
         }
-#pragma unroll
-        for (int ib = 0; ib < 8; ++ib) occs[ib] = slots[ib] >= 0 ? __ldg(m.blk_mask + slots[ib]) : 0ull;
     }
     // (unrolled only where the probe results sit in register arrays: eight copies of the list construction cost the
     // serial flavour 7 % of the search trip in instruction fetch)
@@ -439,24 +442,24 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
         if (ix > nbx || iy > nby || iz > nbz) continue;
         const int bx = bx0 + ix, by = by0 + iy, bz = bz0 + iz;
         int slot;
-        unsigned long long occ;
+        unsigned long long full, occ;   // all occupied cells of the block / those inside the shell
+        uint32_t base;
         if (PAR_PROBES) {
             slot = slots[ib];
             if (slot < 0) continue;
-            occ = occs[ib] & shell_bits(cqx, cqy, cqz, bx, by, bz);
+            full = occs[ib]; base = bases[ib];
         } else {
-            slot = dir_find(m, pack_block(bx, by, bz));
+            slot = rec_find(m, pack_block(bx, by, bz), full, base);   // key, occupancy and bucket base in one load
             if (slot < 0) continue;
-            occ = __ldg(m.blk_mask + slot) & shell_bits(cqx, cqy, cqz, bx, by, bz);
         }
+        occ = full & shell_bits(cqx, cqy, cqz, bx, by, bz);
         if (!occ) continue;
         const unsigned long long octant = box_bits(oxl, oxh, oyl, oyh, ozl, ozh, bx, by, bz);
-        const uint32_t base_idx = (uint32_t)slot * 64u;
         unsigned long long oa = occ & octant, ob = occ & ~octant;
         while (oa) {                                  // nearest octant: always visited, no gap needed
             const int off = __ffsll((long long)oa) - 1;
             oa &= oa - 1;
-            s_idx[nA * tstride] = base_idx + (uint32_t)off;
+            s_idx[nA * tstride] = cell_entry(slot, full, base, off);
             ++nA;
         }
         const int ox = bx * 4 - cqx, oy = by * 4 - cqy, oz = bz * 4 - cqz;
@@ -468,7 +471,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
                               (dz < 0 ? glo[2] : dz > 0 ? ghi[2] : 0.f);
             const int pos = (SHELL_CELLS - 1) - nB;
             ++nB;
-            s_idx[pos * tstride] = base_idx + (uint32_t)off;
+            s_idx[pos * tstride] = cell_entry(slot, full, base, off);
             s_gap[pos * tstride] = gap;
         }
     }
@@ -481,7 +484,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
     for (int t = 0; t < total; ++t) {
         const int pos = (t < nA) ? t : SHELL_CELLS - 1 - (t - nA);
         if (t >= nA && s_gap[pos * tstride] > __uint_as_float((uint32_t)(worst >> 32))) continue;
-        uint32_t b = __ldg(m.cell_tab + s_idx[pos * tstride]);
+        uint32_t b = entry_bucket(m, s_idx[pos * tstride]);   // compact block: the entry IS the bucket, no table read
         while (b != NONE32) {
             float4 p[BUCKET_SLOTS];
 #pragma unroll
@@ -549,12 +552,13 @@ __device__ __forceinline__ void ring_scan_cell(const MapView& m, uint2 ent, int 
                                                float qx, float qy, float qz,
                                                double edge, double slack, double gworst, Top5& loc, unsigned long long& lworst,
                                                int& lfound, unsigned& ncand) {
-    // ent.x = cell_tab index (slot * 64 + cell offset in block), ent.y = linear index of the block in the step's block box
-    const int bi = (int)ent.y, off = (int)(ent.x & 63u);
+    // ent.x = cell entry (bucket or cell_tab index, see CELL_DIRECT), ent.y = linear index of the block in the step's
+    // block box << 6 | cell offset in the block
+    const int bi = (int)(ent.y >> 6), off = (int)(ent.y & 63u);
     const int cx = (bx0 + bi / (nby * nbz)) * 4 + ((off >> 4) & 3), cy = (by0 + (bi / nbz) % nby) * 4 + ((off >> 2) & 3),
               cz = (bz0 + bi % nbz) * 4 + (off & 3);
     if (cell_gap_sq(edge, cx, cy, cz, qx, qy, qz, slack) > gworst) return;
-    uint32_t b = __ldg(m.cell_tab + ent.x);
+    uint32_t b = entry_bucket(m, ent.x);
     while (b != NONE32) {
         float4 pt[BUCKET_SLOTS];
 #pragma unroll
@@ -624,13 +628,14 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView m /* by value: 
             // stage 1: one block per lane -> directory slot and the occupancy bits of its cells in ring n
             const int bi = base + lane;
             int slot = -1, bx = 0, by = 0, bz = 0;
-            unsigned long long occ = 0;
+            unsigned long long occ = 0, full = 0;
+            uint32_t bbase = NONE32;
             if (bi < nb) {
                 bx = bx0 + bi / (nby * nbz); by = by0 + (bi / nbz) % nby; bz = bz0 + bi % nbz;
                 const unsigned long long want = cube_bits(cqx, cqy, cqz, bx, by, bz, n) & ~cube_bits(cqx, cqy, cqz, bx, by, bz, p);
                 if (want) {
-                    slot = dir_find(m, pack_block(bx, by, bz));
-                    if (slot >= 0) occ = __ldg(m.blk_mask + slot) & want;
+                    slot = rec_find(m, pack_block(bx, by, bz), full, bbase);
+                    if (slot >= 0) occ = full & want;
                 }
             }
             // stage 2: the occupied cells of all 32 blocks go through one queue so that every lane scans one cell per
@@ -645,7 +650,7 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView m /* by value: 
                 for (int t = 0; t < take; ++t) {
                     const int off = __ffsll((long long)occ) - 1;
                     occ &= occ - 1;
-                    queue[pos++] = make_uint2((uint32_t)slot * 64u + (uint32_t)off, (uint32_t)bi);
+                    queue[pos++] = make_uint2(cell_entry(slot, full, bbase, off), ((uint32_t)bi << 6) | (uint32_t)off);
                 }
                 qn += total;
                 __syncwarp();
