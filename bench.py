@@ -489,20 +489,32 @@ def run_flivo(args, rank, world_size, local_rank):
         F._ck(L.flivo_host_register(h.ctypes.data, h.nbytes))
     states = [pkg.State.from_array(s["x_prior"]) for s in scans]
 
+    # the four C-ABI calls of a frame, with their argument objects built once (what a C++ caller's loop looks like; the
+    # convenience wrappers of the ctypes view copy the state and P on every call, which costs more than the calls)
+    P_in = np.ascontiguousarray(P0, dtype=np.float64)
+    P_out = np.zeros_like(P_in)
+    x_out, rep_out = pkg.State(), pkg.Report()
+    ptrs = [(C.c_void_p(h.ctypes.data), h.shape[0]) for h in host_scans]
+    hctx, p_in, p_out = F.h, C.c_void_p(P_in.ctypes.data), C.c_void_p(P_out.ctypes.data)
+    ref_cfg, ref_x, ref_rep = C.byref(cfg), C.byref(x_out), C.byref(rep_out)
+    ref_states = [C.byref(s) for s in states]
+
     def pipelined(n_steps):
-        work = 0.0
-        F.scan_upload_async(host_scans[0], 48)
+        work = 0
+        ck = F._ck
+        ck(L.flivo_scan_upload_async(hctx, ptrs[0][0], ptrs[0][1], 48))
         barrier()
         t0 = time.perf_counter()
         for k in range(n_steps):
-            F.scan_commit()
-            F.iekf_update_begin(states[k % S], P0, cfg)
-            F.scan_upload_async(host_scans[(k + 1) % S], 48)
-            _, _, r = F.iekf_update_end()
-            work += r.trips * host_scans[k % S].shape[0]
+            i, j = k % S, (k + 1) % S
+            ck(L.flivo_scan_commit(hctx))
+            ck(L.flivo_iekf_update_begin(hctx, ref_states[i], p_in, ref_cfg))
+            ck(L.flivo_scan_upload_async(hctx, ptrs[j][0], ptrs[j][1], 48))
+            ck(L.flivo_iekf_update_end(hctx, ref_x, p_out, ref_rep))
+            work += rep_out.trips * ptrs[i][1]
         dt = time.perf_counter() - t0
-        F.scan_commit()   # retire the scan staged during the last step
-        return dt, work
+        ck(L.flivo_scan_commit(hctx))   # retire the scan staged during the last step
+        return dt, float(work)
 
     pipelined(min(args.warmup, 3))
     e2e_s, e2e_work = pipelined(args.steps)

@@ -147,6 +147,7 @@ __device__ __forceinline__ void ld_rec(const BlockRec* p, unsigned long long& ke
     unsigned long long w2, w3;
     asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(key), "=l"(mask), "=l"(w2), "=l"(w3) : "l"(p));
     base = (uint32_t)w2;
+    (void)w3;
 }
 __device__ __forceinline__ int rec_find(const MapView& m, unsigned long long key, unsigned long long& mask, uint32_t& base) {
     uint32_t s = hash_block(key) & m.dir_mask;

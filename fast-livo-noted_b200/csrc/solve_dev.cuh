@@ -29,9 +29,10 @@ namespace flivo {
 #define SDEV static __device__ __forceinline__
 // The solve is executed ONCE per launch by one CTA: its instruction lines are cold, and a helper shared by several call
 // sites / several single-lane warps (SO(3) exp / log, A_matrix, the S2 charts with their sin / cos / atan2 bodies) is
-// fetched once when it is a real function but once per copy when inlined.  FLIVO_SOLVE_INLINE=1 inlines them instead
-// (measured: profiles/r2_ab_solve.txt).
-#if defined(FLIVO_SOLVE_INLINE) && FLIVO_SOLVE_INLINE
+// fetched once when it is a real function but once per copy when inlined — in theory.  Measured (profiles/r2_ab_solve.txt)
+// the inlined build is the faster one (update phase 2.8 vs 3.4 us, whole solve 23-28 vs 27-34 us): default.
+// -DFLIVO_SOLVE_INLINE=0 builds the out-of-line flavour.
+#if !defined(FLIVO_SOLVE_INLINE) || FLIVO_SOLVE_INLINE
 #define SHELP static __device__ __forceinline__
 #else
 #define SHELP static __device__ __noinline__
@@ -331,14 +332,20 @@ SDEV void apply_T_cols(double* M, int n, const BlockT& T, int tid, int nthreads)
     }
 }
 
-// Solve S^T X = B by Gauss-Jordan with partial pivoting on the M x W array A = [S^T | B] (W = M + nrhs <= 65) in shared
-// memory, by ONE warp, in place; on return columns M..W-1 hold X (columns 0..M-1 are dead: a pivot column is never
-// read again once its pivot is done, so it is not even written).  The time of this routine is the length of its
-// dependent chain per pivot, so: every lane reads pivot column k itself (broadcast loads, no shuffles) and finds the
-// pivot row by INTEGER compares of the magnitudes' bit patterns (non-negative doubles order like their bits), two
-// interleaved half-chains; one reciprocal per pivot (correctly rounded, then multiplies); a lane owns columns
-// k+1+lane and k+33+lane and updates both at once; the row swap p <-> k is applied by index.  First maximum wins
-// pivot ties.  Returns false on a zero pivot (the caller then leaves state and covariance untouched).
+// Solve S Y = B by Gauss-Jordan with partial pivoting on the M x W array A = [S | B] (W = M + nrhs <= 32) in shared
+// memory, by ONE warp with the matrix in REGISTERS: lane c holds column c (M doubles).  On return columns M..W-1 of A
+// hold Y.  The routine is a chain of dependent instructions executed by a single warp, so what counts is the number of
+// instructions per pivot, not parallel width (a first version that kept the matrix in shared memory, 13 elements per
+// lane and pivot, took 15.8 us for 12 pivots on B200; the block-wide version of round 1, one barrier per pivot, 6.7 us):
+//   * pivot k: lane k finds the pivot row of its own column among the rows not yet used — INTEGER compares of the
+//     magnitudes' bit patterns (non-negative doubles order like their bits), two interleaved half-chains; first
+//     maximum wins ties — and the warp learns the row by one shuffle;
+//   * rows are never swapped: the pivot row stays where it is and is marked used; pos[i] remembers which unknown row i
+//     ended up solving, and the final store puts it there;
+//   * every lane fetches column k (the multipliers) by M shuffles, scales its pivot-row entry by ONE reciprocal
+//     (correctly rounded) and updates its M - 1 other entries.
+// Same operations per entry as the textbook order.  Returns false on a zero pivot (the caller then leaves state and
+// covariance untouched).
 SDEV unsigned long long d_mag_bits(double v) {
 #ifdef __CUDA_ARCH__
     return (unsigned long long)__double_as_longlong(v) & 0x7FFFFFFFFFFFFFFFull;
@@ -357,47 +364,51 @@ SDEV double d_rcp(double v) {
 }
 template <int M, int W>
 SDEV bool warp_gauss_jordan(double* A, int lane) {
-    static_assert(W <= 65 && M >= 2, "a lane owns at most two columns");
+    static_assert(W <= 32 && M >= 2 && M <= 16, "one column per lane");
+    constexpr unsigned FULLW = 0xFFFFFFFFu;
     constexpr int HALF = M / 2;
+    double a[M];
+    int pos[M];
+#pragma unroll
+    for (int i = 0; i < M; ++i) { a[i] = lane < W ? A[i * W + lane] : 0.0; pos[i] = 0; }
+    unsigned used = 0u;
     bool ok = true;
 #pragma unroll 1
     for (int k = 0; k < M; ++k) {
-        double colk[M];
-#pragma unroll
-        for (int i = 0; i < M; ++i) colk[i] = A[i * W + k];
-        const double mk = A[k * W + k];   // multiplier of the row that lands at position p after the swap
-        // rows k..M-1 compete; rows above the pivot row carry key 0 and the lower index wins ties
+        // pivot row of column k (computed by every lane on its own column; lane k's answer counts)
         unsigned long long ba = 0ull, bb = 0ull;
-        int pa = k, pb = k;
+        int pa = __ffs(~used) - 1, pb = pa;   // (a row that is still free, should every candidate be zero)
 #pragma unroll
         for (int i = 0; i < HALF; ++i) {
-            const unsigned long long key = i >= k ? d_mag_bits(colk[i]) : 0ull;
+            const unsigned long long key = ((used >> i) & 1u) ? 0ull : d_mag_bits(a[i]);
             if (key > ba) { ba = key; pa = i; }
         }
 #pragma unroll
         for (int i = HALF; i < M; ++i) {
-            const unsigned long long key = i >= k ? d_mag_bits(colk[i]) : 0ull;
+            const unsigned long long key = ((used >> i) & 1u) ? 0ull : d_mag_bits(a[i]);
             if (key > bb) { bb = key; pb = i; }
         }
-        const int p = bb > ba ? pb : pa;
-        if ((bb > ba ? bb : ba) == 0ull) ok = false;
-        const double r = d_rcp(A[p * W + k]);
-        const int c0 = k + 1 + lane, c1 = c0 + 32;
-        const bool h0 = c0 < W, h1 = c1 < W;
-        const double p0 = h0 ? A[p * W + c0] * r : 0.0, p1 = h1 ? A[p * W + c1] * r : 0.0;
-        const double ak0 = h0 ? A[k * W + c0] : 0.0, ak1 = h1 ? A[k * W + c1] : 0.0;
+        const int p = __shfl_sync(FULLW, bb > ba ? pb : pa, k);
+        const bool zero = __shfl_sync(FULLW, (int)((bb > ba ? bb : ba) == 0ull), k) != 0;
+        if (zero) ok = false;
+        used |= 1u << p;
+        double ap = a[0];                      // this lane's entry of the pivot row
+#pragma unroll
+        for (int i = 1; i < M; ++i) if (i == p) ap = a[i];
+        const double r = d_rcp(__shfl_sync(FULLW, ap, k));
+        const double prow = ap * r;
 #pragma unroll
         for (int i = 0; i < M; ++i) {
-            if (i == k) continue;
-            const bool sw = (i == p);
-            const double m = sw ? mk : colk[i];
-            if (h0) { const double a = sw ? ak0 : A[i * W + c0]; A[i * W + c0] = a - m * p0; }
-            if (h1) { const double a = sw ? ak1 : A[i * W + c1]; A[i * W + c1] = a - m * p1; }
+            const double m = __shfl_sync(FULLW, a[i], k);   // column k, row i
+            if (i == p) { a[i] = prow; pos[i] = k; }
+            else a[i] = a[i] - m * prow;
         }
-        if (h0) A[k * W + c0] = p0;
-        if (h1) A[k * W + c1] = p1;
-        __syncwarp();
     }
+    if (lane >= M && lane < W) {
+#pragma unroll
+        for (int i = 0; i < M; ++i) A[pos[i] * W + lane] = a[i];
+    }
+    __syncwarp();
     return ok;
 }
 
@@ -406,7 +417,7 @@ struct SolveSmem {
     double sum[PSTRIDE];          // reduced normal equations: 78 upper H^T H, 12 H^T z, res_sum, n_eff
     double H[144], z[12];
     double P[23 * 23], L[23 * 23];
-    double Aug[12 * 35];
+    double Aug[12 * 25];          // [S | H | z] of the trip's 12x12 system (V1: 6 x 13)
     double Kx[23 * 12];
     double x[36], xp[36];
     double dxnew[24], dxo[24], Kh[24], dx[24];
@@ -592,25 +603,27 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
 
     if (mode == 0) {
         // ================= V3: esekfom.hpp:1633-1927 ==================================================
-        // Aug = [S^T | Q1^T],  S = I + HTH * Q11,  Q = P / R
+        // The gain needs W = Q1 S^-1 (23 x 12), S = I + HTH * Q11, Q = P / R, only through K_x = W HTH and K_h = W HTz:
+        // solve S Y = [HTH | HTz] (13 right-hand sides: the 12 x 25 system fits one warp, a column per lane) and form
+        // K_x | K_h = Q1 Y afterwards with all threads.  Aug = [S | HTH | HTz].
         const double invR = 1.0 / S.job->R;
-        for (int e = tid; e < 12 * 35; e += NT) {
-            const int r = e / 35, c = e % 35;
+        for (int e = tid; e < 12 * 25; e += NT) {
+            const int r = e / 25, c = e % 25;
             double v;
-            if (c < 12) {  // S^T[r][c] = S[c][r] = delta + sum_k H[c][k] Q[k][r]
+            if (c < 12) {  // S[r][c] = delta + sum_k H[r][k] Q[k][c]
                 double s = 0.0;
 #pragma unroll
-                for (int k = 0; k < 12; ++k) s += M.H[c * 12 + k] * (M.P[k * 23 + r] * invR);
+                for (int k = 0; k < 12; ++k) s += M.H[r * 12 + k] * (M.P[k * 23 + c] * invR);
                 v = s + (r == c ? 1.0 : 0.0);
-            } else {       // Q1^T[r][i] = Q[i][r]
-                v = M.P[(c - 12) * 23 + r] * invR;
+            } else {
+                v = c < 24 ? M.H[r * 12 + (c - 12)] : M.z[r];
             }
             M.Aug[e] = v;
         }
         __syncthreads();
         solve_stamp(S, trip_no, 3);
         if (warp == 0) {
-            const bool ok = warp_gauss_jordan<12, 35>(M.Aug, lane);
+            const bool ok = warp_gauss_jordan<12, 25>(M.Aug, lane);
             if (lane == 0) M.flag[1] = ok ? 1 : 0;
         }
         __syncthreads();
@@ -619,21 +632,14 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
             if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl_next_trip(ctl); }
             return;
         }
-        // W[i][a] = X[a][i] = Aug[a][12 + i];  K_h = W * HTz (:1801);  K_x[:, :12] = W * HTH (:1806)
-        for (int e = tid; e < 23 * 12 + 23; e += NT) {
-            if (e < 23 * 12) {
-                const int i = e / 12, b = e % 12;
-                double s = 0.0;
+        // Y = Aug[:, 12:25];  K_x[:, :12] = Q1 Y[:, :12] (:1806);  K_h = Q1 Y[:, 12] (:1801)
+        for (int e = tid; e < 23 * 13; e += NT) {
+            const int i = e / 13, b = e % 13;
+            double s = 0.0;
 #pragma unroll
-                for (int a = 0; a < 12; ++a) s += M.Aug[a * 35 + 12 + i] * M.H[a * 12 + b];
-                M.Kx[e] = s;
-            } else {
-                const int i = e - 23 * 12;
-                double s = 0.0;
-#pragma unroll
-                for (int a = 0; a < 12; ++a) s += M.Aug[a * 35 + 12 + i] * M.z[a];
-                M.Kh[i] = s;
-            }
+            for (int a = 0; a < 12; ++a) s += (M.P[i * 23 + a] * invR) * M.Aug[a * 25 + 12 + b];
+            if (b < 12) M.Kx[i * 12 + b] = s;
+            else M.Kh[i] = s;
         }
         __syncthreads();
         if (tid < 23) {                                                       // :1812
@@ -739,24 +745,25 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
             }
             __syncthreads();
         }
-        // Aug (6 x 24) = [S^T | C1^T],  S = I + H6 * C11,  C = state.cov
-        for (int e = tid; e < 6 * 24; e += NT) {
-            const int r = e / 24, c = e % 24;
+        // K_1[:, :6] = C1 S^-1 with S = I + H6 * C11, C = state.cov, enters only through G = K_1 HPH and K_1 HPL:
+        // solve S Y = [H6 | z6] (6 x 13 system), then G | K_1 HPL = C1 Y.  Aug = [S | H6 | z6].
+        for (int e = tid; e < 6 * 13; e += NT) {
+            const int r = e / 13, c = e % 13;
             double v;
             if (c < 6) {
                 double s = 0.0;
 #pragma unroll
-                for (int k = 0; k < 6; ++k) s += M.H6[c * 6 + k] * M.P[k * 18 + r];
+                for (int k = 0; k < 6; ++k) s += M.H6[r * 6 + k] * M.P[k * 18 + c];
                 v = s + (r == c ? 1.0 : 0.0);
             } else {
-                v = M.P[(c - 6) * 18 + r];
+                v = c < 12 ? M.H6[r * 6 + (c - 6)] : M.z6[r];
             }
             M.Aug[e] = v;
         }
         __syncthreads();
         solve_stamp(S, trip_no, 3);
         if (warp == 0) {
-            const bool ok = warp_gauss_jordan<6, 24>(M.Aug, lane);
+            const bool ok = warp_gauss_jordan<6, 13>(M.Aug, lane);
             if (lane == 0) M.flag[1] = ok ? 1 : 0;
         }
         __syncthreads();
@@ -765,19 +772,20 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
             if (tid == 0) { ctl->nan_guard = 1; ctl->stopped = 1; ctl->trips += 1; ctl_next_trip(ctl); }
             return;
         }
-        for (int e = tid; e < 18 * 6; e += NT) {                             // G[:, :6] = K_1[:, :6] * HPH (:191), K_1[i][a] = Aug[a][6 + i]
-            const int i = e / 6, b = e % 6;
+        for (int e = tid; e < 18 * 7; e += NT) {                             // G[:, :6] = K_1[:, :6] * HPH (:191);  Kh = K_1[:, :6] * HPL
+            const int i = e / 7, b = e % 7;
             double s = 0.0;
 #pragma unroll
-            for (int a = 0; a < 6; ++a) s += M.Aug[a * 24 + 6 + i] * M.H6[a * 6 + b];
-            M.G[e] = s;
+            for (int a = 0; a < 6; ++a) s += M.P[i * 18 + a] * M.Aug[a * 13 + 6 + b];
+            if (b < 6) M.G[i * 6 + b] = s;
+            else M.Kh[i] = s;
         }
         __syncthreads();
         if (tid < 18) {                                                      // :193
-            double s1 = 0.0, s2 = 0.0;
+            double s2 = 0.0;
 #pragma unroll
-            for (int a = 0; a < 6; ++a) { s1 += M.Aug[a * 24 + 6 + tid] * M.z6[a]; s2 += M.G[tid * 6 + a] * M.vec[a]; }
-            M.sol[tid] = s1 + M.vec[tid] - s2;
+            for (int a = 0; a < 6; ++a) s2 += M.G[tid * 6 + a] * M.vec[a];
+            M.sol[tid] = M.Kh[tid] + M.vec[tid] - s2;
         }
         __syncthreads();
         solve_stamp(S, trip_no, 5);

@@ -11,7 +11,7 @@ for w in ouster260k_map20M avia24k_map1M; do
 import json,sys
 try:
     d=json.loads(open('gpurun_out/b_%s.%s.json'%(sys.argv[1],sys.argv[2])).read().strip().splitlines()[-1])
-    print(sys.argv[1], sys.argv[2], 'ms/step', round(d['ms_per_step'],4), 'median', round(d['latency_ms_per_scan_stats']['median'],4), 'e2e', '%.4g'%d['e2e']['value'], 'search trip ms', d['roofline']['avg_launch_ms'], 'reuse', d['roofline']['reuse_trip']['avg_launch_ms'], 'trips', d['config']['trips_per_step'], 'launches', d['gpu_launches'])
+    print(sys.argv[1], sys.argv[2], 'ms/step', round(d['ms_per_step'],4), 'median', round(d['latency_ms_per_scan_stats']['median'],4), 'e2e', '%.4g'%d['e2e']['value'], 'search trip ms', d['roofline']['avg_launch_ms'], 'reuse', d['roofline']['reuse_trip']['avg_launch_ms'], 'trips', d["run"]["trips_per_step"], 'launches', d['gpu_launches'])
 except Exception as e:
     print('FAILED', e)
 EOP

@@ -54,6 +54,23 @@ static inline int __all_sync(unsigned, int pred) {
     return r;
 }
 
+static unsigned long long g_shfl[EMU_THREADS / 32][32];
+template <class T>
+static inline T __shfl_sync(unsigned, T v, int src) {
+    static_assert(sizeof(T) <= 8, "shuffle of at most 8 bytes");
+    unsigned long long* buf = g_shfl[t_tid >> 5];
+    unsigned long long w = 0;
+    memcpy(&w, &v, sizeof(T));
+    buf[t_tid & 31] = w;
+    __syncwarp();
+    w = buf[src & 31];
+    __syncwarp();
+    T out;
+    memcpy(&out, &w, sizeof(T));
+    return out;
+}
+static inline int __ffs(int v) { return __builtin_ffs(v); }
+
 #include "../../fast-livo-noted_b200/csrc/solve_dev.cuh"
 
 using namespace flivo;

@@ -159,6 +159,9 @@ def test_frontend_through_dropin_classes(pkg, tmp_path):
     assert nd == len(wd) and np.array_equal(down, wd)
     lines = {l.split()[0]: l.split()[1:] for l in r.stdout.strip().splitlines() if not l.startswith("fov")}
     assert lines["run"][1] == "0" and int(lines["run"][3]) > 0 and lines["run"][5] == "1"      # first frame built the map
+    # ... from feats_down_body as it is (lidar frame, no down-sampling, non-identity extrinsics ignored), as
+    # src/laser_mapping.cpp:134-142 does: one map point per scan point
+    assert int(lines["run"][3]) == nd
     # sliding local map
     fov = [l.split() for l in r.stdout.strip().splitlines() if l.startswith("fov")]
     exp = _fov_python(cloud, walk, cube_len, det_range)
