@@ -107,7 +107,7 @@ SYMBOLS = [
     "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach", "flivo_set_gnss",
     "flivo_peer_local_base", "flivo_peer_attach_local", "flivo_peer_set_timeout", "flivo_peer_reset",
     "flivo_scan_upload_async", "flivo_scan_commit", "flivo_host_register", "flivo_host_unregister",
-    "flivo_iekf_update_begin", "flivo_iekf_update_end",
+    "flivo_iekf_update_begin", "flivo_iekf_update_end", "flivo_knn_noalloc",
 ]
 
 _lib = None
@@ -144,6 +144,7 @@ def lib():
     L.flivo_map_flatten.argtypes = [vp, vp, vp, sz, C.POINTER(sz)]
     L.flivo_map_acquire_removed.argtypes = [vp, vp, sz, C.POINTER(sz)]
     L.flivo_knn.argtypes = [vp, vp, sz, sz, C.c_int, C.c_double, vp, vp, vp, vp]
+    L.flivo_knn_noalloc.argtypes = [vp, vp, sz, sz, C.c_int, C.c_double, vp, vp, vp, vp]
     L.flivo_scan_upload.argtypes = [vp, vp, sz, sz]
     L.flivo_scan_set_device.argtypes = [vp, vp, sz]
     L.flivo_scan_upload_async.argtypes = [vp, vp, sz, sz]
@@ -318,6 +319,16 @@ class Flivo:
         oxyz = np.zeros((n, k, 3), np.float32)
         ocnt = np.zeros(n, np.int32)
         self._ck(self._L.flivo_knn(self.h, _ptr(a), n, st, k, float(max_dist), _ptr(oxyz), _ptr(osq), _ptr(oid), _ptr(ocnt)))
+        return oid, osq, oxyz, ocnt
+
+    def Nearest_Search_noalloc(self, queries, k=K, max_dist=np.inf):
+        """flivo_knn_noalloc: the same search through the library's static device scratch (no allocation in the call)."""
+        a, n, st = _pts(queries)
+        oid = np.full((n, k), -1, np.int32)
+        osq = np.full((n, k), np.inf, np.float32)
+        oxyz = np.zeros((n, k, 3), np.float32)
+        ocnt = np.zeros(n, np.int32)
+        self._ck(self._L.flivo_knn_noalloc(self.h, _ptr(a), n, st, k, float(max_dist), _ptr(oxyz), _ptr(osq), _ptr(oid), _ptr(ocnt)))
         return oid, osq, oxyz, ocnt
 
     # ---- scan + update ----

@@ -635,6 +635,72 @@ extern "C" int flivo_knn(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t s
     return fetch_stats(ctx);
 }
 
+// ---- batched Nearest_Search without any allocation -------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels as flivo_knn (k_knn /
+// k_knn_ivox), but the staged queries and the result rows live in ONE file-scope device array instead of the context's
+// growable cudaMalloc buffers, and the host copies go straight from / to the caller's memory (no pinned staging buffer).
+//   * limit: FLIVO_KNN_NOALLOC_MAX_QUERIES queries per call (beyond it: FLIVO_E_CAPACITY, nothing launched);
+//   * the array (about 3.8 MB) is held by every GPU that loads the library until the process exits;
+//   * every call on a device shares it and it keeps the last call's contents.  Nothing in it has to start at zero: the
+//     kernel writes every result row of the call (xyz, distance, id, count for all nq queries) before it is read back.
+//     Calls that overlap on one GPU (two contexts, two threads) race on it: serialise them.
+// In host code the array's name is only a stand-in: the device address comes from cudaGetSymbolAddress, looked up once
+// per device with that device current.
+constexpr size_t KNN_NA_MAXQ = FLIVO_KNN_NOALLOC_MAX_QUERIES;
+constexpr size_t KNN_NA_ROW = (size_t)FLIVO_K * (3 + 1 + 1) * 4 + 4;            // result bytes per query at k = FLIVO_K
+constexpr size_t KNN_NA_BYTES = KNN_NA_MAXQ * (sizeof(float4) + KNN_NA_ROW) + 1024;
+static __device__ __align__(256) unsigned char g_knn_noalloc_scratch[KNN_NA_BYTES];
+constexpr int KNN_NA_MAXDEV = 64;
+static void* g_knn_noalloc_ptr[KNN_NA_MAXDEV] = {};
+
+extern "C" int flivo_knn_noalloc(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t stride_bytes, int k, double max_dist,
+                                 float* out_xyz, float* out_sqd, int32_t* out_id, int32_t* out_count) {
+    ENTER();   // (makes the context's device current)
+    NEED(k >= 1 && k <= FLIVO_K, FLIVO_E_ARG, "k must be in 1..5");
+    NEED(nq == 0 || (q_xyz && stride_ok(stride_bytes)), FLIVO_E_ARG, "bad queries / stride");
+    NEED(nq <= KNN_NA_MAXQ, FLIVO_E_CAPACITY, "flivo_knn_noalloc: more than FLIVO_KNN_NOALLOC_MAX_QUERIES (32768) queries; split the batch or use flivo_knn");
+    NEED(ctx->device >= 0 && ctx->device < KNN_NA_MAXDEV, FLIVO_E_ARG, "device index out of range");
+    NEED(!ctx->upd.active, FLIVO_E_STATE, "an update is in flight (flivo_iekf_update_end first)");
+    if (nq == 0) return FLIVO_OK;
+    uint32_t bits = 0;
+    if (!bound_bits(max_dist, &bits)) {   // negative or NaN bound: nothing can match
+        for (size_t i = 0; i < nq * (size_t)k; ++i) {
+            if (out_id) out_id[i] = -1;
+            if (out_sqd) out_sqd[i] = INFINITY;
+            if (out_xyz) out_xyz[3 * i] = out_xyz[3 * i + 1] = out_xyz[3 * i + 2] = 0.f;
+        }
+        if (out_count) memset(out_count, 0, nq * sizeof(int32_t));
+        return FLIVO_OK;
+    }
+    if (!g_knn_noalloc_ptr[ctx->device]) {   // set-up, once per device, this device current
+        void* p = nullptr;
+        CKC(cudaGetSymbolAddress(&p, g_knn_noalloc_scratch));
+        NEED(p != nullptr, FLIVO_E_CUDA, "cudaGetSymbolAddress returned no address");
+        g_knn_noalloc_ptr[ctx->device] = p;
+    }
+    unsigned char* base = static_cast<unsigned char*>(g_knn_noalloc_ptr[ctx->device]);
+    float4* d_q = reinterpret_cast<float4*>(base);
+    float* d_xyz = reinterpret_cast<float*>(base + KNN_NA_MAXQ * sizeof(float4));
+    float* d_sqd = d_xyz + nq * k * 3;
+    int* d_id = reinterpret_cast<int*>(d_sqd + nq * k);
+    int* d_cnt = d_id + nq * k;
+    cudaStream_t s = ctx->stream;
+    // queries: x y z of every record -> the first 12 bytes of a float4 slot (w is never read by the kernels)
+    if (stride_bytes == 16) CKC(cudaMemcpyAsync(d_q, q_xyz, nq * 16, cudaMemcpyHostToDevice, s));
+    else CKC(cudaMemcpy2DAsync(d_q, 16, q_xyz, stride_bytes, 12, nq, cudaMemcpyHostToDevice, s));
+    const int grid = (int)std::min<size_t>((nq + 3) / 4, (size_t)ctx->sm_count * 16);
+    if (ctx->opt.ivox_nearby) launch_knn_ivox(ctx->map.view(), d_q, (int)nq, k, max_dist, d_xyz, d_sqd, d_id, d_cnt, nullptr, s);
+    else launch_knn(ctx->map.view(), d_q, (int)nq, k, bits, d_xyz, d_sqd, d_id, d_cnt, nullptr, grid, s);
+    CKC(cudaGetLastError());
+    if (out_xyz) CKC(cudaMemcpyAsync(out_xyz, d_xyz, nq * k * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (out_sqd) CKC(cudaMemcpyAsync(out_sqd, d_sqd, nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (out_id) CKC(cudaMemcpyAsync(out_id, d_id, nq * k * sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (out_count) CKC(cudaMemcpyAsync(out_count, d_cnt, nq * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CKC(cudaStreamSynchronize(s));
+    return FLIVO_OK;
+}
+
 // ---- scan ---------------------------------------------------------------------------------------------------
 static int ensure_scan(flivo_ctx* ctx, size_t n) {
     if (n > ctx->scan_cap) {

@@ -145,6 +145,19 @@ int flivo_knn(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t stride_bytes
               float* out_xyz /* nq*k*3 */, float* out_sqd /* nq*k */, int32_t* out_id /* nq*k */,
               int32_t* out_count /* nq */);
 
+/* flivo_knn without any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same search,
+ * same arguments and results as flivo_knn (the search statistics of flivo_get_stats are not updated), but the staged
+ * queries and result rows live in one static device array of the library (about 3.8 MB, held by every GPU that loads
+ * the library until the process exits) and the call performs no cudaMalloc / cudaMallocHost / cudaFree.
+ * At most FLIVO_KNN_NOALLOC_MAX_QUERIES queries per call: more -> FLIVO_E_CAPACITY, nothing launched.  All calls on a
+ * device share the array (it keeps the last call's contents; every row a call reads back is written by that call first):
+ * calls that overlap on one GPU race on it, so serialise them. */
+#define FLIVO_KNN_NOALLOC_MAX_QUERIES 32768
+int flivo_knn_noalloc(flivo_ctx* ctx, const float* q_xyz, size_t nq, size_t stride_bytes, int k, double max_dist,
+                      float* out_xyz /* nq*k*3 */, float* out_sqd /* nq*k */, int32_t* out_id /* nq*k */,
+                      int32_t* out_count /* nq */);
+
 /* ---- scan + measurement update ---------------------------------------------------------------- */
 /* feats_down_body (src/laser_mapping.cpp:129-130): lidar-frame scan; copied to the device. */
 int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes);
