@@ -480,13 +480,11 @@ def run_flivo(args, rank, world_size, local_rank):
         ser_work += rep2.trips * host_scans[k % S].shape[0]
     e2e_serial = ser_work / ser_s
     # (b) pipelined (the headline e2e): the node hands one feats_down_body over per frame (src/laser_mapping.cpp:129-130,
-    #     165-167) in a buffer it reuses, so the buffers are registered once (flivo_host_register) and travel as they are —
-    #     whole 48-byte records, one DMA, xyz gathered on the device.  While update k runs (flivo_iekf_update_begin), scan
-    #     k+1 travels on the copy stream (flivo_scan_upload_async); flivo_iekf_update_end reads x, P and the report back.
+    #     165-167).  While update k runs (flivo_iekf_update_begin), scan k+1 is staged (flivo_scan_upload_async: the
+    #     48-byte records are repacked to float4 by host threads and travel on the copy stream — shipping the raw records
+    #     was measured copy-bound, 12.5 MB per step over PCIe); flivo_iekf_update_end reads x, P and the report back.
     #     Wall clock over K back-to-back steps: K uploads (scan k+1 during step k), K updates, K result read-backs inside.
     #     No flush here: the rotated scans stand at different poses and together touch more of the map than L2 holds.
-    for h in host_scans:
-        F._ck(L.flivo_host_register(h.ctypes.data, h.nbytes))
     states = [pkg.State.from_array(s["x_prior"]) for s in scans]
 
     # the four C-ABI calls of a frame, with their argument objects built once (what a C++ caller's loop looks like; the
@@ -518,8 +516,6 @@ def run_flivo(args, rank, world_size, local_rank):
 
     pipelined(min(args.warmup, 3))
     e2e_s, e2e_work = pipelined(args.steps)
-    for h in host_scans:
-        L.flivo_host_unregister(h.ctypes.data)
     sharded = sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev, barrier, wxyz_host, ds) if shared else None
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None   # covers the device-resident, profile and e2e timed loops
@@ -648,7 +644,7 @@ def run_flivo(args, rank, world_size, local_rank):
                            "trips_sharded": int(reps.trips), "trips_single": int(rep1.trips)}
             del F1
         barrier()
-    h2d = int(pts_per_scan * 48 + 36 * 8 + npd * npd * 8 + 512)   # the raw 48-byte records travel + the job / state / P block
+    h2d = int(pts_per_scan * 16 + 36 * 8 + npd * npd * 8 + 512)   # xyz as float4 (repacked from the 48-byte records on the host) + the job / state / P block
     d2h = int(36 * 8 + npd * npd * 8 + 512)
     return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
@@ -765,7 +761,7 @@ def main():
                                           "host_recorded_events_mean": r["host_ev_ms_mean"],
                                           "note": "per-step device times of rank 0 over the timed steps (in-graph event nodes); host_recorded_events_mean = the same steps between events recorded from the host around the call"},
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (registered host buffer) during flivo_iekf_update_begin/_end of the current one",
+                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (host repack to float4 + copy stream) during flivo_iekf_update_begin/_end of the current one",
                     "serial_value": r["e2e_serial"], "serial_how": "flivo_scan_upload (pageable buffer, host repack) then flivo_iekf_update, L2 flushed between steps"},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "sharded": r["sharded"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],

@@ -839,16 +839,21 @@ static bool host_pinned(const void* p) {
 }
 
 // feats_down_body of the NEXT frame (src/laser_mapping.cpp:129-130,165-167 hands one over per frame): the records travel on
-// the copy stream into the back slot while the update of the current scan runs.  Pinned / registered sources
-// (cudaHostRegister, flivo_host_register) are copied as they are — whole records, one DMA, no host work; the xyz gather
-// happens on the device (k_scan_prepare).  Pageable sources are repacked to float4 into a pinned buffer by a few host
-// threads first (chunked, each chunk's copy overlapping the repack of the next).
+// the copy stream into the back slot while the update of the current scan runs.  Pinned / registered sources of packed
+// xyz or float4 records (cudaHostRegister, flivo_host_register) are copied as they are — one DMA, no host work; the xyz
+// gather happens on the device (k_scan_prepare).  Everything else (pageable memory, or wide records such as the 48-byte
+// PointXYZINormal) is repacked to float4 into a pinned buffer by a few host threads first (chunked, each chunk's copy
+// overlapping the repack of the next); with the update of the current scan in flight that work is hidden.
 extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes) {
     ENTER();
     NEED(n > 0 && body_xyz && stride_ok(stride_bytes), FLIVO_E_ARG, "bad scan / stride");
     NEED(n < 0x7FFFFFF0ull / 8, FLIVO_E_ARG, "scan too large");
     ScanSlot& sl = ctx->slot[ctx->back];
-    const bool pinned = host_pinned(body_xyz);
+    // whole records by DMA only when that does not inflate the PCIe traffic: a pinned float4 / packed-xyz buffer goes as it
+    // is; the 48-byte PointXYZINormal records would triple the bytes (measured on B200 / PCIe 5: 12.5 MB per 260 k-point scan
+    // took longer than the whole update and made the pipelined step copy-bound, 0.74 ms against 0.49), so they are repacked
+    // to float4 by host threads — which now happens while the previous update runs
+    const bool pinned = stride_bytes <= 16 && host_pinned(body_xyz);
     const size_t stride = pinned ? stride_bytes : 16, bytes = n * stride;
     if (sl.copy_pending) { CKC(cudaEventSynchronize(sl.copied)); sl.copy_pending = false; }
     if (bytes > sl.d_bytes) {
@@ -972,7 +977,12 @@ static int search_grid(flivo_ctx* ctx) {
 // scans whose tiles fill at most half of the resident CTAs leave the GPU under-filled: the search is then bound by each
 // thread's chain of dependent loads and the probe-all-blocks-at-once flavour wins (search.cuh, PAR_PROBES).  A function
 // of the search grid alone, so the captured graph's cache key covers it.
-static bool par_probes(flivo_ctx* ctx, int sgrid) { return sgrid * 2 <= ctx->search_resident; }
+static bool par_probes(flivo_ctx* ctx, int sgrid) {
+    static int force = -2;   // FLIVO_PAR_PROBES=0/1 overrides the choice (development A/B)
+    if (force == -2) { const char* e = getenv("FLIVO_PAR_PROBES"); force = e ? atoi(e) : -1; }
+    if (force >= 0) return force != 0;
+    return sgrid * 2 <= ctx->search_resident;
+}
 static int fused_grid(flivo_ctx* ctx) {
     const int units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
     return std::max(1, std::min(((units + 255) / 256) * 256, ctx->sm_count * 8));

@@ -39,14 +39,20 @@ constexpr uint32_t INF_BITS = 0x7F800000u;
 //                    bucket(cell off) = base + popc(mask & ((1 << off) - 1)) and the cell table is not read at all.
 //                    Every block whose cells were all created by one insert batch is (Build; new ground of a scan).
 //   base == NONE32 : cells were added to the block by a later batch; their buckets are looked up in cell_tab.
+//   chained        : some cell of the block has an overflow chain (more than 8 live points: dense, not down-sampled
+//                    input only).  For the other blocks the search never reads bucket_next.
 struct __align__(32) BlockRec {
     unsigned long long key;        // packed block coordinates, DIR_EMPTY = free slot (same as dir_keys[slot])
     unsigned long long mask;       // occupancy bits (same as blk_mask[slot])
     uint32_t base;
-    uint32_t pad[3];
+    uint32_t chained;
+    uint32_t pad[2];
 };
-// work-list / queue entries of the search name a cell either by its bucket (compact block) or by its cell_tab index
+// work-list / queue entries of the search name a cell either by its bucket (compact block) or by its cell_tab index;
+// CELL_NOCHAIN on a direct entry: the bucket is the cell's only one
 constexpr uint32_t CELL_DIRECT = 0x80000000u;
+constexpr uint32_t CELL_NOCHAIN = 0x40000000u;
+constexpr uint32_t CELL_BUCKET_BITS = 0x3FFFFFFFu;
 constexpr size_t DIR_CAP_MAX = 1ull << 25;   // cell_tab indices (slot * 64 + off) must stay below CELL_DIRECT
 
 struct MapView {
@@ -143,28 +149,46 @@ __device__ __forceinline__ int cell_off(int cx, int cy, int cz) { return ((cx & 
 
 // directory lookup through the search records: slot index or -1; mask / base of the block on success.  One 32-byte load
 // per probe (ld.global.nc.v4.u64 on sm_100: the whole record in one instruction).
-__device__ __forceinline__ void ld_rec(const BlockRec* p, unsigned long long& key, unsigned long long& mask, uint32_t& base) {
-    unsigned long long w2, w3;
-    asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(key), "=l"(mask), "=l"(w2), "=l"(w3) : "l"(p));
-    base = (uint32_t)w2;
+// (base comes back with the chained flag in bit 31 .. see rec_base / rec_chained)
+__device__ __forceinline__ void ld_rec(const BlockRec* p, unsigned long long& key, unsigned long long& mask, unsigned long long& bc) {
+    unsigned long long w3;
+    asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(key), "=l"(mask), "=l"(bc), "=l"(w3) : "l"(p));
     (void)w3;
 }
-__device__ __forceinline__ int rec_find(const MapView& m, unsigned long long key, unsigned long long& mask, uint32_t& base) {
+// One bucket = 8 x float4 = one 128-byte line, fetched by FOUR 256-bit loads.  The search is bound by the L1 wavefront
+// queue (every load instruction costs ~2 cycles per distinct line its lanes touch, B300_MICROARCH "LDG"): half the
+// load instructions per bucket is half the wavefronts.
+__device__ __forceinline__ void ld_bucket(const float4* __restrict__ line, float4 (&p)[BUCKET_SLOTS]) {
+#pragma unroll
+    for (int h = 0; h < BUCKET_SLOTS / 2; ++h) {
+        unsigned long long a, b, c, d;
+        asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(line + 2 * h));
+        p[2 * h] = make_float4(__uint_as_float((uint32_t)a), __uint_as_float((uint32_t)(a >> 32)), __uint_as_float((uint32_t)b), __uint_as_float((uint32_t)(b >> 32)));
+        p[2 * h + 1] = make_float4(__uint_as_float((uint32_t)c), __uint_as_float((uint32_t)(c >> 32)), __uint_as_float((uint32_t)d), __uint_as_float((uint32_t)(d >> 32)));
+    }
+}
+// bc = {base (low word), chained (high word)} as loaded from the record
+__device__ __forceinline__ int rec_find(const MapView& m, unsigned long long key, unsigned long long& mask, unsigned long long& bc) {
     uint32_t s = hash_block(key) & m.dir_mask;
     while (true) {
         unsigned long long k;
-        ld_rec(m.rec + s, k, mask, base);
+        ld_rec(m.rec + s, k, mask, bc);
         if (k == key) return (int)s;
         if (k == DIR_EMPTY) { mask = 0ull; return -1; }
         s = (s + 1) & m.dir_mask;
     }
 }
 // cell `off` of a found block as a work-list entry (see CELL_DIRECT)
-__device__ __forceinline__ uint32_t cell_entry(int slot, unsigned long long mask, uint32_t base, int off) {
-    return base != NONE32 ? (CELL_DIRECT | (base + (uint32_t)__popcll(mask & ((1ull << off) - 1ull)))) : ((uint32_t)slot * 64u + (uint32_t)off);
+__device__ __forceinline__ uint32_t cell_entry(int slot, unsigned long long mask, unsigned long long bc, int off) {
+    const uint32_t base = (uint32_t)bc;
+    if (base == NONE32) return (uint32_t)slot * 64u + (uint32_t)off;
+    return CELL_DIRECT | ((bc >> 32) ? 0u : CELL_NOCHAIN) | (base + (uint32_t)__popcll(mask & ((1ull << off) - 1ull)));
 }
 __device__ __forceinline__ uint32_t entry_bucket(const MapView& m, uint32_t e) {
-    return (e & CELL_DIRECT) ? (e & ~CELL_DIRECT) : __ldg(m.cell_tab + e);
+    return (e & CELL_DIRECT) ? (e & CELL_BUCKET_BITS) : __ldg(m.cell_tab + e);
+}
+__device__ __forceinline__ uint32_t entry_next(const MapView& m, uint32_t e, uint32_t b) {
+    return ((e & (CELL_DIRECT | CELL_NOCHAIN)) == (CELL_DIRECT | CELL_NOCHAIN)) ? NONE32 : __ldg(m.bucket_next + b);
 }
 
 // directory lookup: slot index or -1

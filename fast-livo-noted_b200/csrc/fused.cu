@@ -435,7 +435,10 @@ constexpr int SEARCH_THREADS = 128;
 constexpr int SEARCH_WARPS = SEARCH_THREADS / 32;
 // register budget of k_search: 5 CTAs/SM = 96 registers (68 B of spills); 6 (80 registers, 140 B) and 4 (116, none) measured
 // 1-2 % slower, 7 (72 registers, 112 B) 4 % slower (profiles/r1_ab_launch_structure.txt)
-constexpr int SEARCH_CTAS_PER_SM = 5;
+#ifndef FLIVO_SEARCH_CTAS
+#define FLIVO_SEARCH_CTAS 5
+#endif
+constexpr int SEARCH_CTAS_PER_SM = FLIVO_SEARCH_CTAS;
 constexpr int FAR_BATCH = 32;   // far points a warp finishes before its lanes fit their planes (one lane per point)
 
 // shared memory of k_search: the two phases of a CTA never overlap, so their buffers share the space

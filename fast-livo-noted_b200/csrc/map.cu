@@ -240,22 +240,24 @@ __global__ void k_cells_create(const unsigned long long* __restrict__ keys, size
 // search record of one directory slot from the authoritative tables (see BlockRec)
 __device__ __forceinline__ void write_record(const MapView& m, BlockRec* rec, uint32_t slot) {
     const unsigned long long key = m.dir_keys[slot], mask = m.blk_mask[slot];
-    uint32_t base = NONE32;
+    uint32_t base = NONE32, chained = 0;
     if (key != DIR_EMPTY && mask) {
         const uint32_t* tab = m.cell_tab + (size_t)slot * 64;
         unsigned long long bits = mask;
         base = tab[__ffsll((long long)bits) - 1];
+        const uint32_t first = base;
         uint32_t r = 0;
         while (bits) {
             const int off = __ffsll((long long)bits) - 1;
             bits &= bits - 1;
-            if (tab[off] != base + r) { base = NONE32; break; }
+            if (tab[off] != first + r) base = NONE32;
+            if (m.bucket_next[tab[off]] != NONE32) chained = 1;
             ++r;
         }
-        if (base != NONE32 && (base + 64u) >= CELL_DIRECT) base = NONE32;
+        if (base != NONE32 && (base + 64u) > CELL_BUCKET_BITS) base = NONE32;
     }
     BlockRec v;
-    v.key = key; v.mask = mask; v.base = base; v.pad[0] = v.pad[1] = v.pad[2] = 0;
+    v.key = key; v.mask = mask; v.base = base; v.chained = chained; v.pad[0] = v.pad[1] = 0;
     rec[slot] = v;
 }
 // after the cells of a batch exist: one thread per block head of the sorted batch refreshes that block's record
@@ -952,7 +954,6 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
     CK(cub::DeviceScan::ExclusiveSum(cub_tmp_, tmp, is_new, rank, (int)n, stream_));
     k_cells_reserve<<<1, 32, 0, stream_>>>(is_new, rank, n, v_, d_cnt_, d_misc_);
     k_cells_create<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, d_cnt_, is_new, rank, d_misc_, downsample_on ? 0 : 1);
-    k_block_records<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, const_cast<BlockRec*>(v_.rec));
     CK(cudaGetLastError());
     if (!downsample_on) {
         k_insert_all<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, d_cnt_);
@@ -970,6 +971,9 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
         k_ds_serial<<<1, 32, 0, stream_>>>(defer_list_, d_misc_, d_pts_id, v_, d_cnt_);
         CK(cudaGetLastError());
     }
+    // search records of the touched blocks, once the batch is stored (storing may still append overflow buckets)
+    k_block_records<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, const_cast<BlockRec*>(v_.rec));
+    CK(cudaGetLastError());
     int rc = refresh_counters(err);
     if (n_added) *n_added = h_cnt_.add_counter;
     int zero = 0;

@@ -401,7 +401,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
     const int nbx = ((cqx + 1) >> 2) - bx0, nby = ((cqy + 1) >> 2) - by0, nbz = ((cqz + 1) >> 2) - bz0;   // 0 or 1
     int slots[8];
     unsigned long long occs[8];
-    uint32_t bases[8];
+    unsigned long long bases[8];
     if (PAR_PROBES) {
         // eight independent record loads (one 32-byte sector each): ONE global-memory round trip for the whole shell
         unsigned long long bkey[8], k0[8];
@@ -415,7 +415,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
         }
 #pragma unroll
         for (int ib = 0; ib < 8; ++ib) {
-            k0[ib] = DIR_EMPTY; occs[ib] = 0ull; bases[ib] = NONE32;
+            k0[ib] = DIR_EMPTY; occs[ib] = 0ull; bases[ib] = NONE32;   // (base NONE32, chained 0)
             if (bkey[ib] != DIR_EMPTY) ld_rec(m.rec + hs[ib], k0[ib], occs[ib], bases[ib]);
         }
 #pragma unroll
@@ -443,7 +443,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
         const int bx = bx0 + ix, by = by0 + iy, bz = bz0 + iz;
         int slot;
         unsigned long long full, occ;   // all occupied cells of the block / those inside the shell
-        uint32_t base;
+        unsigned long long base;        // {bucket base, chained} of the block's record
         if (PAR_PROBES) {
             slot = slots[ib];
             if (slot < 0) continue;
@@ -484,12 +484,12 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
     for (int t = 0; t < total; ++t) {
         const int pos = (t < nA) ? t : SHELL_CELLS - 1 - (t - nA);
         if (t >= nA && s_gap[pos * tstride] > __uint_as_float((uint32_t)(worst >> 32))) continue;
-        uint32_t b = entry_bucket(m, s_idx[pos * tstride]);   // compact block: the entry IS the bucket, no table read
+        const uint32_t ent = s_idx[pos * tstride];
+        uint32_t b = entry_bucket(m, ent);   // compact block: the entry IS the bucket, no table read
         while (b != NONE32) {
             float4 p[BUCKET_SLOTS];
-#pragma unroll
-            for (int s = 0; s < BUCKET_SLOTS; ++s) p[s] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
-            const uint32_t nxt = __ldg(m.bucket_next + b);
+            ld_bucket(m.buckets + (size_t)b * BUCKET_SLOTS, p);
+            const uint32_t nxt = entry_next(m, ent, b);
 #pragma unroll
             for (int s = 0; s < BUCKET_SLOTS; ++s) {
                 const int pid = __float_as_int(p[s].w);
@@ -561,9 +561,8 @@ __device__ __forceinline__ void ring_scan_cell(const MapView& m, uint2 ent, int 
     uint32_t b = entry_bucket(m, ent.x);
     while (b != NONE32) {
         float4 pt[BUCKET_SLOTS];
-#pragma unroll
-        for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) pt[s2] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s2);
-        const uint32_t nxt = __ldg(m.bucket_next + b);
+        ld_bucket(m.buckets + (size_t)b * BUCKET_SLOTS, pt);
+        const uint32_t nxt = entry_next(m, ent.x, b);
 #pragma unroll
         for (int s2 = 0; s2 < BUCKET_SLOTS; ++s2) {
             const int pid = __float_as_int(pt[s2].w);
@@ -628,8 +627,7 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView m /* by value: 
             // stage 1: one block per lane -> directory slot and the occupancy bits of its cells in ring n
             const int bi = base + lane;
             int slot = -1, bx = 0, by = 0, bz = 0;
-            unsigned long long occ = 0, full = 0;
-            uint32_t bbase = NONE32;
+            unsigned long long occ = 0, full = 0, bbase = NONE32;
             if (bi < nb) {
                 bx = bx0 + bi / (nby * nbz); by = by0 + (bi / nbz) % nby; bz = bz0 + bi % nbz;
                 const unsigned long long want = cube_bits(cqx, cqy, cqz, bx, by, bz, n) & ~cube_bits(cqx, cqy, cqz, bx, by, bz, p);
@@ -735,8 +733,7 @@ __device__ __forceinline__ void thread_knn5_ivox(const MapView& m, float qx, flo
         uint32_t b = __ldg(m.cell_tab + (size_t)last_slot * 64 + cell_off(cx, cy, cz));
         while (b != NONE32) {
             float4 p[BUCKET_SLOTS];
-#pragma unroll
-            for (int s = 0; s < BUCKET_SLOTS; ++s) p[s] = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
+            ld_bucket(m.buckets + (size_t)b * BUCKET_SLOTS, p);
             const uint32_t nxt = __ldg(m.bucket_next + b);
 #pragma unroll
             for (int s = 0; s < BUCKET_SLOTS; ++s) {
