@@ -375,27 +375,31 @@ SDEV bool warp_gauss_jordan(double* A, int lane) {
     bool ok = true;
 #pragma unroll 1
     for (int k = 0; k < M; ++k) {
-        // pivot row of column k (computed by every lane on its own column; lane k's answer counts)
-        unsigned long long ba = 0ull, bb = 0ull;
+        // pivot row of column k (computed by every lane on its own column; lane k's answer counts).  The magnitudes are
+        // compared by the HIGH words of their bit patterns (sign stripped): a pivot within 2^-20 of the largest entry is as
+        // good as the largest; the value travels with the key so that the reciprocal can start as soon as the row is known
+        unsigned ba = 0u, bb = 0u;
         int pa = __ffs(~used) - 1, pb = pa;   // (a row that is still free, should every candidate be zero)
+        double va = 0.0, vb = 0.0;
 #pragma unroll
         for (int i = 0; i < HALF; ++i) {
-            const unsigned long long key = ((used >> i) & 1u) ? 0ull : d_mag_bits(a[i]);
-            if (key > ba) { ba = key; pa = i; }
+            const unsigned key = ((used >> i) & 1u) ? 0u : (unsigned)(d_mag_bits(a[i]) >> 32);
+            if (key > ba) { ba = key; pa = i; va = a[i]; }
         }
 #pragma unroll
         for (int i = HALF; i < M; ++i) {
-            const unsigned long long key = ((used >> i) & 1u) ? 0ull : d_mag_bits(a[i]);
-            if (key > bb) { bb = key; pb = i; }
+            const unsigned key = ((used >> i) & 1u) ? 0u : (unsigned)(d_mag_bits(a[i]) >> 32);
+            if (key > bb) { bb = key; pb = i; vb = a[i]; }
         }
-        const int p = __shfl_sync(FULLW, bb > ba ? pb : pa, k);
-        const bool zero = __shfl_sync(FULLW, (int)((bb > ba ? bb : ba) == 0ull), k) != 0;
-        if (zero) ok = false;
+        const bool second = bb > ba;
+        const int pz = __shfl_sync(FULLW, (second ? pb : pa) | (((second ? bb : ba) == 0u) ? 256 : 0), k);
+        const double r = d_rcp(__shfl_sync(FULLW, second ? vb : va, k));
+        const int p = pz & 255;
+        if (pz & 256) ok = false;
         used |= 1u << p;
-        double ap = a[0];                      // this lane's entry of the pivot row
+        double ap = a[0];                      // this lane's entry of the pivot row (selected while the reciprocal runs)
 #pragma unroll
         for (int i = 1; i < M; ++i) if (i == p) ap = a[i];
-        const double r = d_rcp(__shfl_sync(FULLW, ap, k));
         const double prow = ap * r;
 #pragma unroll
         for (int i = 0; i < M; ++i) {

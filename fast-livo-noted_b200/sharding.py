@@ -76,21 +76,33 @@ def replay_sequences(pkg, sequences, rank, world_size, P0, cfg, ds, device=0, in
 
 
 def _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_ratio, sort_scan):
-    """One sequence through its own context (see replay_sequences)."""
+    """One sequence through its own context (see replay_sequences).
+
+    The frame loop is the pipelined form of LaserMapping::Run's step 5: while the update of frame k runs on the GPU, frame
+    k+1 is staged (flivo_scan_upload_async on the context's copy stream); then map_incremental with the posterior.
+    Stated deviation from src/laser_mapping.cpp:134-142: the reference starts at the identity pose and builds its first map
+    from feats_down_body as it is; a replayed synthetic sequence starts at a known pose of a larger world, so the first
+    scan is placed with that pose (LaserMapping::Run of host/laser_mapping.h follows the reference)."""
     with pkg.Flivo(device=device, downsample_size=ds, cell_ratio=cell_ratio, initial_points=initial_points, sort_scan=sort_scan) as F:
-        res = dict(x=None, map_points=0, updates=0, trips=0, work=0, added=[])
-        for k, scan in enumerate(sequences[s]):
-            st = pkg.State.from_array(scan["x_prior"])
-            F.scan_upload(scan["body"])
-            if k == 0:
-                w = F.h_share_model(st, mode=cfg.mode, do_search=True, want=("world",))["world"]
-                F.Build(w)
-                continue
-            x, _, rep = F.iekf_update(st, P0, cfg)
+        res = dict(x=None, map_points=0, updates=0, trips=0, work=0, added=[], device_ms=0.0)
+        frames = sequences[s]
+        bodies = [np.ascontiguousarray(fr["body"], dtype=np.float32) for fr in frames]
+        F.scan_upload(bodies[0])
+        w = F.h_share_model(pkg.State.from_array(frames[0]["x_prior"]), mode=cfg.mode, do_search=True, want=("world",))["world"]
+        F.Build(w)
+        if len(frames) > 1:
+            F.scan_upload_async(bodies[1])
+        for k in range(1, len(frames)):
+            F.scan_commit()
+            F.iekf_update_begin(pkg.State.from_array(frames[k]["x_prior"]), P0, cfg)
+            if k + 1 < len(frames):
+                F.scan_upload_async(bodies[k + 1])        # travels while the update runs
+            x, _, rep = F.iekf_update_end()
             res["added"].append(F.map_add_scan(x))
             res["updates"] += 1
             res["trips"] += rep.trips
-            res["work"] += rep.trips * len(scan["body"])
+            res["work"] += rep.trips * len(bodies[k])
+            res["device_ms"] += getattr(rep, "gpu_ms", 0.0)
             res["x"] = x.as_array()
         res["map_points"] = F.size()
     return res

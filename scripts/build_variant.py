@@ -14,6 +14,11 @@ ge.load_package()
 from importlib import import_module  # noqa: E402
 B = import_module(ge.PKG_NAME + ".build")
 name, extra = sys.argv[1], sys.argv[2:]
+# --src DIR: compile a (patched) copy of csrc/ instead of the tree's, so that an experiment never leaves the tree half-edited
+SRC = B.CSRC
+if "--src" in extra:
+    i = extra.index("--src"); SRC = os.path.abspath(extra[i + 1]); extra = extra[:i] + extra[i + 2:]
+FLAGS = [("-I" + SRC) if fl == "-I" + B.CSRC else fl for fl in B.FLAGS]
 out_dir = os.path.join(B.HERE, "variants")
 obj_dir = os.path.join(B.OBJ, "variant_" + name)
 os.makedirs(out_dir, exist_ok=True)
@@ -22,7 +27,7 @@ os.makedirs(obj_dir, exist_ok=True)
 
 def cc(src):
     obj = os.path.join(obj_dir, src.replace(".cu", ".o"))
-    subprocess.check_call([B.NVCC] + B.FLAGS + extra + ["-c", os.path.join(B.CSRC, src), "-o", obj])
+    subprocess.check_call([B.NVCC] + FLAGS + extra + ["-c", os.path.join(SRC, src), "-o", obj])
     return obj
 
 

@@ -66,6 +66,7 @@ def main():
         print(json.dumps({"metric": "replay_points_per_sec", "value": work / dt, "unit": "points/s", "n_gpus": world,
                           "sequences": a.sequences, "frames_per_sequence": a.frames, "scan_points": a.scan_points, "concurrent_per_rank": a.concurrent, "updates": int(upd),
                           "ms_per_frame_wall": 1e3 * dt * world / max(upd, 1.0), "mode": "V1" if a.mode == 1 else "V3",
+                          "frames_per_sec": upd / dt, "gpu_busy_updates_rank0": sum(v["device_ms"] for v in r.values()) * 1e-3 / dt,
                           "map_points_seq0": r[min(r)]["map_points"], "scaling": "weak per sequence, no collective",
                           "note": "wall clock through the public API (host scans, upload, update, map_incremental, per-sequence context create/destroy)"}))
     if world > 1:

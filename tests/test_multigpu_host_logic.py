@@ -137,8 +137,19 @@ class _FakeFlivo:
         self.calls.append("build")
         self.n += len(w)
 
-    def iekf_update(self, st, P0, cfg):
-        self.calls.append("update")
+    def scan_upload_async(self, body):
+        self.calls.append(("stage", len(body)))
+
+    def scan_commit(self):
+        self.calls.append("commit")
+
+    def iekf_update_begin(self, st, P0, cfg):
+        self.calls.append("begin")
+        self._pending = (st, P0)
+
+    def iekf_update_end(self):
+        self.calls.append("end")
+        st, P0 = self._pending
         return _FakeState(st.as_array() + 1.0), P0, _FakeReport()
 
     def map_add_scan(self, x):
@@ -167,7 +178,11 @@ def test_replay_sequences_control_flow(pkg):
         for calls, s in zip(_FakeFlivo.log, sorted(r)):
             frames = len(seqs[s])
             assert calls[:3] == [("upload", 10 + s), "trip", "build"]
-            assert calls[3:] == [("upload", 10 + s), "update", "add"] * (frames - 1) + ["close"]
+            # pipelined frame loop: the next scan is staged between begin and end of the running update
+            want = [("stage", 10 + s)]
+            for k in range(1, frames):
+                want += ["commit", "begin"] + ([("stage", 10 + s)] if k + 1 < frames else []) + ["end", "add"]
+            assert calls[3:] == want + ["close"]
             assert r[s]["updates"] == frames - 1 and r[s]["trips"] == 4 * (frames - 1)
             assert r[s]["work"] == 4 * (frames - 1) * (10 + s) and r[s]["added"] == [2] * (frames - 1)
             assert r[s]["map_points"] == 3 + 2 * (frames - 1)
