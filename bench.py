@@ -236,7 +236,7 @@ def full_size_trip_parity(F, pkg, tree, body, x_prior, mode):
     d5 = np.where(cnt5 >= 5, osq[:, 4], np.inf).astype(np.float32)
     o = orc.h_share_model(body, st, np.ascontiguousarray(oxyz[:, :5]), cnt5, d5, True, mode, None)
     g = F.h_share_model(pkg.State.from_array(x_prior), mode, True, want=("selected", "eff", "nbr_id"))
-    bound = np.inf if mode == 1 else par.GATE_SQ      # V3 searches with the far-neighbour gate as its bound
+    bound = pkg.v1_search_bound_sq(F.ds, F.cell_ratio) if mode == 1 else par.GATE_SQ      # V3 searches with the far-neighbour gate as its bound
     want = np.where((osq[:, :5] <= np.float32(bound)) & (np.arange(5)[None, :] < cnt5[:, None]), oid[:, :5], -1)
     bad_rows = np.any(want != g["nbr_id"], axis=1)
     # a row may legitimately differ only where a tie straddles rank 5 (ikd-Tree keeps the candidate it visited first)

@@ -195,6 +195,14 @@ def _ptr(a):
 
 
 CFG_PROFILE = 1
+V1_RANGE_CELLS = 24   # FLIVO_V1_RANGE_CELLS
+
+
+def v1_search_bound_sq(ds, cell_ratio=2):
+    """Squared range up to which V1 keeps neighbours (float32 arithmetic of api.cu: search_bound_bits)."""
+    edge = np.float32(ds) * np.float32(cell_ratio)
+    r = np.float32(V1_RANGE_CELLS) * edge
+    return float(max(np.float32(5.0), np.float32(r * r)))
 
 
 def make_cfg(mode=MODE_V3, max_iter=4, laser_point_cov=0.001, limit=None, force_search=False, profile=False):
@@ -220,6 +228,7 @@ class Flivo:
             raise FlivoError(rc, "flivo_ctx_create failed (no CUDA device? this library has no CPU fallback)")
         self.h = h
         self.n_scan = 0
+        self.ds, self.cell_ratio = float(downsample_size), int(cell_ratio) or 2
 
     def close(self):
         if getattr(self, "h", None):

@@ -994,11 +994,21 @@ static uint32_t gate_bits() { float f = 5.0f; uint32_t b; memcpy(&b, &f, 4); ret
 // the next search (origin:963).  In V1 (the compiled path) the flags are a LOCAL vector<bool>(n, true) rebuilt on every call
 // (src/laser_mapping.cpp:490) and the gate is applied on search trips only (:518): on re-use trips a point whose fifth
 // neighbour lies beyond the gate still enters with its cached Nearest_Points if esti_plane accepts them.  V1 therefore
-// searches unbounded, exactly as the reference's Nearest_Search call (max_dist = INFINITY, ikd_Tree.h:174), keeps the five
-// neighbours and records the gate in PF_GATE alone.  (Sparse-fringe queries then walk more cells; iVox mode bounds the
-// range itself.)
+// keeps neighbours beyond the gate and records the gate in PF_GATE alone — up to a range of FLIVO_V1_RANGE_CELLS search
+// cells (24: 9.6 m at filter_size_map 0.2, 24 m at 0.5).  Stated deviation: the reference's Nearest_Search is unbounded
+// (max_dist = INFINITY, ikd_Tree.h:174); a point whose fifth neighbour lies beyond that range counts as having fewer than
+// five here (masked), where the reference would fit a plane through points that far away.  The bound is what keeps a
+// scan that looks into unmapped space fast: an unbounded search ends in a sweep of the whole block directory per query
+// (measured on a map grown from one scan: 5.6 ms per 24 k-point update; profiles/r2_ab_search.txt).  iVox mode bounds the
+// range itself.
 static uint32_t search_bound_bits(const flivo_ctx* ctx, int mode) {
-    return (mode == FLIVO_MODE_V1 && !ctx->opt.ivox_nearby) ? INF_BITS : gate_bits();
+    if (mode != FLIVO_MODE_V1 || ctx->opt.ivox_nearby) return gate_bits();
+    const float R = (float)FLIVO_V1_RANGE_CELLS * ctx->map.view().cell_edge;
+    float b = R * R;
+    if (!(b > 5.0f)) b = 5.0f;
+    uint32_t bits;
+    memcpy(&bits, &b, 4);
+    return bits;
 }
 
 // copy a per-point device array to the host in the caller's order

@@ -391,9 +391,16 @@ __global__ void __launch_bounds__(UNIT_POINTS, FLIVO_FUSED_CTAS_PER_SM) k_fused(
     __threadfence();
     SolveSmem& M = *reinterpret_cast<SolveSmem*>(s_raw);
     if (threadIdx.x < NTERMS) {
+        // group order, sixteen independent loads in flight at a time (absent records add +0.0, which changes nothing)
         const double* src = P.gpartials + threadIdx.x;
         double sum = 0.0;
-        for (unsigned g = 0; g < ngroups; ++g) sum += __ldcg(src + (size_t)g * PSTRIDE);
+        for (unsigned g0 = 0; g0 < ngroups; g0 += 16) {
+            double v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = (g0 + j < ngroups) ? __ldcg(src + (size_t)(g0 + j) * PSTRIDE) : 0.0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) sum += v[j];
+        }
         M.sum[threadIdx.x] = sum;
     }
     __syncthreads();

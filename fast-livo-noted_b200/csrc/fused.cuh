@@ -9,7 +9,7 @@ constexpr int UNIT_POINTS = UNIT_WARPS * 32;     // scan points per work unit
 constexpr int NTERMS = 92;                       // 78 (H^T H upper) + 12 (H^T z) + res_sum + n_eff
 constexpr int PSTRIDE = 96;                      // doubles per partial record
 constexpr int GROUP_UNITS = 32;                  // (capacity sizing of group_cnt)
-constexpr int FOLD_CTAS = 16;                    // CTA records of k_fused folded into one group record by the last CTA of the group
+constexpr int FOLD_CTAS = 32;                    // CTA records of k_fused folded into one group record by the last CTA of the group
 constexpr int MAX_TRIPS = 16;
 
 // Device-resident control block of one iterated update (written by the solve kernel, read by the fused kernel).

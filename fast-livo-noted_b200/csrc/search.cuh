@@ -521,7 +521,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
 // RING_MAX_CELLS (or unbounded searches in empty space) fall back to warp_knn5's directory sweep.
 // Output convention of warp_knn5: lanes 0..4 hold rank 0..4 in `out`; returns the number found.
 // ----------------------------------------------------------------------------------------------------
-constexpr int RING_MAX_CELLS = 8;
+constexpr int RING_MAX_CELLS = 32;   // covers the V1 search range of 24 cells (api.cu: search_bound_bits)
 
 __device__ __forceinline__ unsigned axis_bits_n(int cq, int b, int n) {
     int lo = max(cq - n, b * 4) - b * 4, hi = min(cq + n, b * 4 + 3) - b * 4;
@@ -692,10 +692,12 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView m /* by value: 
             gworst = fmin(gworst, (double)__uint_as_float(d5));
             const float need = __uint_as_float(d5);
             do { ++n; } while (n < RING_MAX_CELLS && covered_sq(m.cell_edge, (float)n, qabs) < need);
-        } else if (n < 2) {
-            n = 2;
         } else {
-            do { ++n; } while (n < RING_MAX_CELLS && covered_sq(m.cell_edge, (float)n, qabs) < max_sq);
+            // fewer than five known: a nearby bound (the V3 gate: <= 8 cells) is covered in one more step; a wide one
+            // (V1: 24 cells) by doubling cubes, so that a point a few metres from the map does not pay for the whole range
+            int nb_ = n;
+            do { ++nb_; } while (nb_ < RING_MAX_CELLS && covered_sq(m.cell_edge, (float)nb_, qabs) < max_sq);
+            n = (n < 2) ? 2 : ((nb_ <= 8) ? nb_ : min(2 * n, nb_));
         }
     }
     // not final within RING_MAX_CELLS cells: the generic search (block rings + directory sweep)

@@ -42,6 +42,10 @@ extern "C" {
  * 1x6 row = columns [3:6|0:3] of the V3 row, 18-DOF StatesGroup). */
 #define FLIVO_MODE_V3     0
 #define FLIVO_MODE_V1     1
+/* V1 keeps a point's five neighbours beyond the far-neighbour gate (they re-enter on re-use trips, src/laser_mapping.cpp:490,518)
+ * up to this many search cells (cell = cell_ratio * downsample_size); farther than that a point counts as having fewer than
+ * five neighbours.  The reference's search is unbounded: stated deviation, see DESIGN.md §4. */
+#define FLIVO_V1_RANGE_CELLS 24
 
 typedef struct flivo_ctx flivo_ctx;
 

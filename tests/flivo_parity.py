@@ -24,7 +24,7 @@ def oracle_knn(map_xyz, queries, k=5, max_dist=np.inf, ids=None, alive=None):
     return orc.knn_bruteforce(map_xyz, queries, k, max_dist, ids, alive)
 
 
-def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids=None, ivox=None):
+def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids=None, ivox=None, v1_bound=None):
     """One h_share_model trip on the CPU.  cache: dict carrying Nearest_Points between trips.
     ivox: an orc.OracleIVox — the search is then IVox::GetClosestPoint (src/laser_mapping.cpp:520) and the
     far-neighbour gate of the ikd-Tree branch (:518) does not exist."""
@@ -41,7 +41,8 @@ def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids
         cache.update(ids=oid, sqd=osq, xyz=oxyz, cnt=ocnt, ties=ties + cache.get("ties", 0))
     elif searched:
         wpts = orc.body_to_world(body, st)
-        oid, osq, oxyz, ocnt, ties = oracle_knn(map_xyz, wpts, 5, np.inf, ids=map_ids)
+        # V1 keeps neighbours up to FLIVO_V1_RANGE_CELLS cells only (stated deviation, include/flivo.h): same bound here
+        oid, osq, oxyz, ocnt, ties = oracle_knn(map_xyz, wpts, 5, np.inf if (mode != orc.MODE_V1 or v1_bound is None) else v1_bound, ids=map_ids)
         cache.update(ids=oid, sqd=osq, xyz=oxyz, cnt=ocnt, ties=ties)
     if ivox is not None:
         d5 = np.zeros(len(body), np.float32)
@@ -52,7 +53,7 @@ def oracle_trip(map_xyz, body, x, searched, cache, mode, mask_prev=None, map_ids
 
 
 def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.001, limit=None, force_search=False,
-                  ivox=None, gnss=None):
+                  ivox=None, gnss=None, v1_bound=None):
     """The whole iterated update with the restated reference loop (V3: esekfom.hpp:1619-1928; V1:
     src/laser_mapping.cpp:165-242).  Returns dict(x, P, trips, searches, dx (per trip), masks, eff, ids)."""
     limit = np.full(23, 0.001) if limit is None else np.asarray(limit, float)
@@ -69,7 +70,7 @@ def oracle_update(map_xyz, body, x_prior, P, mode, max_iter, laser_point_cov=0.0
     out = None
     while it < max_iter and not stopped:
         do_search = bool(search or force_search)
-        out = oracle_trip(map_xyz, body, x.as_array(), do_search, cache, mode, mask, ivox=ivox)
+        out = oracle_trip(map_xyz, body, x.as_array(), do_search, cache, mode, mask, ivox=ivox, v1_bound=v1_bound)
         mask = out["mask"]
         searches += int(do_search)
         if mode == orc.MODE_V1:
@@ -119,10 +120,11 @@ def check_trip(pkg, F, map_xyz, body, x, mode, verbose=False):
     st = pkg.State.from_array(x)
     g = F.h_share_model(st, mode, True, want=("selected", "eff", "nbr_id", "nbr_sqd", "plane", "world"))
     cache = {}
-    o = oracle_trip(map_xyz, body, x, True, cache, mode)
+    o = oracle_trip(map_xyz, body, x, True, cache, mode, v1_bound=pkg.v1_search_bound_sq(F.ds, F.cell_ratio))
     assert cache["ties"] == 0, "synthetic data has a float32 tie straddling rank 5; re-seed"
     # V3 searches with the far-neighbour gate as its bound (equivalent there); V1 searches unbounded like the reference
-    bad, want_ids = compare_neighbours(g["nbr_id"], cache["ids"], cache["sqd"], cache["cnt"], np.inf if mode == orc.MODE_V1 else GATE_SQ)
+    bad, want_ids = compare_neighbours(g["nbr_id"], cache["ids"], cache["sqd"], cache["cnt"],
+                                       pkg.v1_search_bound_sq(F.ds, F.cell_ratio) if mode == orc.MODE_V1 else GATE_SQ)
     assert bad == 0, "%d / %d neighbour rows differ" % (bad, len(body))
     assert np.array_equal(g["world"], o["world"]), "feats_down_world differs"
     sqd_want = np.where(want_ids >= 0, cache["sqd"], np.inf).astype(np.float32)
@@ -153,7 +155,8 @@ def check_update_against_oracle(pkg, world, scan, mode=0, max_iter=4, force_sear
         check_trip(pkg, F, map_xyz, body, scan["x_prior"], mode, verbose)
         cfg = pkg.make_cfg(mode=mode, max_iter=max_iter, laser_point_cov=0.001, force_search=force_search)
         xg, Pg, rep = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
-        o = oracle_update(map_xyz, body, scan["x_prior"], P0, mode, max_iter, 0.001, None, force_search)
+        o = oracle_update(map_xyz, body, scan["x_prior"], P0, mode, max_iter, 0.001, None, force_search,
+                          v1_bound=pkg.v1_search_bound_sq(world["ds"], cell_ratio))
         assert rep.trips == o["trips"], "trips %d vs oracle %d" % (rep.trips, o["trips"])
         assert rep.searches == o["searches"], "searches %d vs oracle %d" % (rep.searches, o["searches"])
         assert rep.n_eff == o["n_eff"], "n_eff %d vs oracle %d" % (rep.n_eff, o["n_eff"])
@@ -300,7 +303,7 @@ def sharded_update_in_process(pkg, world, scan, nranks=2, mode=0, max_iter=4, de
     for r in range(1, nranks):
         assert np.array_equal(out[r][0].as_array(), x0.as_array()), "rank %d posterior differs from rank 0 (must be bit-identical)" % r
         assert np.array_equal(out[r][1], Pm0)
-    o = oracle_update(map_xyz, body, scan["x_prior"], P0, mode, max_iter, 0.001, None, False)
+    o = oracle_update(map_xyz, body, scan["x_prior"], P0, mode, max_iter, 0.001, None, False, v1_bound=pkg.v1_search_bound_sq(world["ds"]))
     assert rep0.trips == o["trips"] and rep0.searches == o["searches"], "trips/searches %d/%d vs oracle %d/%d" % (rep0.trips, rep0.searches, o["trips"], o["searches"])
     assert rep0.n_eff == o["n_eff"], "n_eff (all ranks) %d vs oracle %d" % (rep0.n_eff, o["n_eff"])
     x_err = np.abs(x0.as_array() - o["x"]).max()

@@ -58,7 +58,7 @@ def test_dropin_matches_oracle(pkg, tmp_path):
     M.build(pts)
     cur = pts.copy()
     for i, s in enumerate(frames):
-        o = par.oracle_update(cur, s["body"], s["x_prior"], np.eye(18) * 1e-4, orc.MODE_V1, max_iter)
+        o = par.oracle_update(cur, s["body"], s["x_prior"], np.eye(18) * 1e-4, orc.MODE_V1, max_iter, v1_bound=pkg.v1_search_bound_sq(world["ds"]))
         fr = kv["frame"][i]
         got = dict(zip(fr[1::2], fr[2::2]))
         assert int(got["trips"]) == o["trips"] and int(got["searches"]) == o["searches"] and int(got["n_eff"]) == o["n_eff"]

@@ -82,6 +82,8 @@ def test_v1_reuse_trips_keep_points_beyond_the_far_neighbour_gate(pkg):
         fringe = (cache["cnt"] >= 5) & (cache["sqd"][:, 4] > 5.0)
         assert fringe.sum() > 200, "scene has no fringe points"
         g_s = F.h_share_model(st, pkg.MODE_V1, True, want=("selected", "eff", "nbr_id"))
+        bound = pkg.v1_search_bound_sq(world["ds"])      # V1 keeps neighbours up to 24 cells (12 m here): beyond the gate
+        assert bound > 100.0 and (cache["sqd"][fringe][:, 4] < bound).all()
         assert np.array_equal(g_s["nbr_id"], np.where(np.arange(5)[None, :] < cache["cnt"][:, None], cache["ids"], -1))
         assert np.array_equal(g_s["selected"], o_s["mask"]) and g_s["n_eff"] == o_s["n_eff"]
         assert not o_s["eff"][fringe].any()                      # search trip: gated out

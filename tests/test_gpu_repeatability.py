@@ -1,0 +1,39 @@
+"""-m gpu: run-to-run bit-repeatability of the whole iterated update — the stand-in for a racecheck record
+(compute-sanitizer is closed on this GPU pool by its operators; profiles/r2_sanitizer_unavailable.txt).
+
+Inside one update the order of events is NOT deterministic: tiles and chunks are dealt by atomic counters, far points are
+published to an epoch-tagged queue and taken by whichever warp is free, the last CTA of every fold group and the last
+group folder are whoever arrives last, and in sharded mode the ranks' records arrive in any order.  The RESULTS must not
+depend on any of it: neighbour lists are canonical, every sum is folded in a fixed order.  A race or an ordering
+dependence in those mechanisms would show up as a run that differs in some bit; 40 runs per case, none may."""
+import numpy as np
+import pytest
+
+import flivo_scenes as scenes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("mode,force", [(0, False), (0, True), (1, False)])
+def test_update_is_bit_repeatable(pkg, mode, force):
+    # a sparse-ish map so that many points take the far (warp-per-query, queue-fed) path
+    world = scenes.make_world(seed=5, n_points=120000, ds=0.5)
+    scan = scenes.make_scan(world, seed=6, n_points=30000, kind="ouster")
+    npd = 18 if mode == 1 else 23
+    P0 = np.eye(npd) * 1e-4
+    cfg = pkg.make_cfg(mode=mode, max_iter=4, laser_point_cov=0.001, force_search=force)
+    with pkg.Flivo(downsample_size=world["ds"], initial_points=len(world["points"]), sort_scan=True) as F:
+        F.Build(world["points"])
+        ref = None
+        for it in range(40):
+            F.scan_upload(scan["body"])
+            x, P, rep = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+            g = F.h_share_model(x, mode, True, want=("nbr_id", "eff", "plane"))
+            cur = (x.as_array().tobytes(), np.asarray(P).tobytes(), rep.trips, rep.searches, rep.n_eff, bytes(np.asarray(rep.dx_last)),
+                   g["nbr_id"].tobytes(), g["eff"].tobytes(), g["plane"].tobytes(), g["HTH"].tobytes(), g["HTz"].tobytes())
+            if ref is None:
+                ref = cur
+                assert F.stats().last_far_queries > 50, "scene has too few far queries to exercise the queue"
+            else:
+                for a, b, name in zip(ref, cur, ("x", "P", "trips", "searches", "n_eff", "dx", "ids", "eff", "plane", "HTH", "HTz")):
+                    assert a == b, "run %d differs from run 0 in %s" % (it, name)

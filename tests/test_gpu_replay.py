@@ -52,7 +52,7 @@ def test_one_sequence_follows_the_oracle(pkg):
     added, x = [], None
     for scan in seqs[0][1:]:
         cur, _ = M.live()
-        o = par.oracle_update(cur, scan["body"], scan["x_prior"], P0, mode, 4)
+        o = par.oracle_update(cur, scan["body"], scan["x_prior"], P0, mode, 4, v1_bound=pkg.v1_search_bound_sq(world["ds"]))
         x = o["x"]
         added.append(M.add_points(orc.body_to_world(scan["body"], orc.State.from_array(o["x"])), True))
     assert np.abs(got["x"] - x).max() < 1e-6

@@ -24,7 +24,7 @@ def test_trajectory_update_then_add_points(pkg, mode):
         for k, pos in enumerate(poses):
             scan = scenes.make_scan(world, seed=300 + k, n_points=2500, pos=pos)
             P0 = np.eye(npd) * 1e-4
-            o = par.oracle_update(cur, scan["body"], scan["x_prior"], P0, mode, 4)
+            o = par.oracle_update(cur, scan["body"], scan["x_prior"], P0, mode, 4, v1_bound=pkg.v1_search_bound_sq(world["ds"]))
             F.scan_upload(scan["body"])
             x, P, rep = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, mode=mode, max_iter=4)
             assert (rep.trips, rep.searches, rep.n_eff) == (o["trips"], o["searches"], o["n_eff"]), "frame %d" % k
