@@ -64,6 +64,11 @@ def parse_args():
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5) for the whole run")
     ap.add_argument("--no-sharded", action="store_true", help="N>1 replica run: skip the `sharded` block (config 5 on the same contexts)")
+    ap.add_argument("--no-mega", action="store_true", help="N>1: skip the 4 M-point / 100 M-point part of the `sharded` block")
+    ap.add_argument("--no-replay", action="store_true", help="skip the `replay` block (config 4 in miniature)")
+    ap.add_argument("--replay-sequences", type=int, default=8, help="sequences PER RANK of the replay block")
+    ap.add_argument("--replay-frames", type=int, default=60)
+    ap.add_argument("--replay-concurrent", type=int, default=4)
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="sharded mode: how the per-trip 96-double records travel")
     return ap.parse_args()
 
@@ -248,7 +253,51 @@ def full_size_trip_parity(F, pkg, tree, body, x_prior, mode):
             "against": "reference ikd_Tree.cpp Nearest_Search (oracle/_ref) + restated esti_plane / gates / rows"}
 
 
-def sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev, barrier, wxyz_host, ds):
+def replay_block(args, pkg, rank, world_size, local_rank, dev, barrier):
+    """BASELINE config 4 in miniature, inside the default run so that the scaling runs see it: independent sequences of
+    24 k-point Avia-like frames, maps grown from the first scan, sequence s -> rank s mod G (sharding.replay_sequences:
+    per frame flivo_scan_upload_async / commit, flivo_iekf_update_begin/_end, flivo_map_add_scan; one context and one host
+    thread per sequence in flight, no collective).  Wall clock between two barriers, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from importlib import import_module
+    import flivo_scenes as scenes
+    sh = import_module(pkg.__name__ + ".sharding")
+    n_seq, n_frames, pool_n = args.replay_sequences * world_size, args.replay_frames, 16
+    w = scenes.make_world_torch(seed=1, n_points=1_000_000, ds=0.5, device=dev)
+    # a drive along a street: consecutive frames about 2 m apart (a sequence starts anywhere on the loop and wraps around)
+    ends = scenes.street_positions(w, 2)
+    poses = [ends[0] + (ends[1] - ends[0]) * (i / pool_n) for i in range(pool_n)]
+    pool = []
+    for i in range(pool_n):
+        s = scenes.make_scan_torch(w, seed=5000 + i, n_points=24_000, kind="avia", pos=poses[i], device=dev)
+        pool.append({"body": s["body"].cpu().numpy(), "x_prior": np.asarray(s["x_prior"])})
+    del w
+    seqs = [[pool[(s + k) % pool_n] for k in range(n_frames)] for s in range(n_seq)]
+    P18, cfg1 = np.eye(18) * 1e-4, pkg.make_cfg(mode=pkg.MODE_V1, max_iter=MAX_ITER, laser_point_cov=LASER_POINT_COV)
+    sh.replay_sequences(pkg, [s[:6] for s in seqs[:world_size]], rank, world_size, P18, cfg1, ds=0.5, device=local_rank)   # warm-up
+    barrier()
+    t0 = time.perf_counter()
+    r = sh.replay_sequences(pkg, seqs, rank, world_size, P18, cfg1, ds=0.5, device=local_rank, concurrent=args.replay_concurrent)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt, float(sum(v["work"] for v in r.values())), float(sum(v["updates"] for v in r.values())),
+                      float(sum(v["device_ms"] for v in r.values()))], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        mx, sm = t.clone(), t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dt, work, upd, busy = float(mx[0]), float(sm[1]), float(sm[2]), float(sm[3])
+    else:
+        dt, work, upd, busy = (float(v) for v in t)
+    return {"workload": "config 4 in miniature: %d sequences x %d frames of 24 k points, V1, map grown from the first scan" % (n_seq, n_frames),
+            "sequences": n_seq, "frames_per_sequence": n_frames, "concurrent_per_rank": args.replay_concurrent,
+            "points_per_sec": work / dt, "frames_per_sec": upd / dt, "ms_per_frame_per_rank": 1e3 * dt * world_size / max(upd, 1.0),
+            "update_device_ms_mean": busy / max(upd, 1.0), "gpu_busy_updates": busy * 1e-3 / (dt * world_size),
+            "note": "wall clock through the public API, host scans, per-sequence context create / destroy included; no collective"}
+
+
+def sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev, barrier, wxyz_host, ds, workload=None, cpu_check=True):
     """BASELINE config 5 on the contexts of a replica run (N > 1): ONE scan split over the ranks (contiguous blocks of the
     caller's order, sharding.shard_range), every rank holding the whole map; per trip each rank's 96-double record is
     stored into every peer's exchange buffer from inside k_fused's solving CTA (NVLink peer memory), summed in rank
@@ -293,14 +342,30 @@ def sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev
     tt = torch.tensor([sum(ms), float(np.mean(xphase)) if xphase else 0.0, float(np.mean(xwait)) if xwait else 0.0], dtype=torch.float64, device=dev)
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     xs, Ps, reps = step(0)
+    barrier()
+    F.peer_detach()          # (the single-context cross-check below must not wait for peers)
     out = None
     if rank == 0:
         n_full = len(shared[0]["body"])
-        out = {"workload": args.workload, "scan_points": n_full, "ranks": world_size, "exchange": "peer memory (stores into the peers' HBM + release/acquire sequence flags inside k_fused)",
+        out = {"workload": workload or args.workload, "scan_points": n_full, "ranks": world_size, "exchange": "peer memory (stores into the peers' HBM + release/acquire sequence flags inside k_fused)",
                "ms_per_step": float(tt[0]) / args.steps, "points_per_sec": n_full * trips / (float(tt[0]) * 1e-3), "trips_per_step": trips / args.steps,
                "exchange_us_per_trip": float(tt[1]), "exchange_wait_us_per_trip": float(tt[2]),
                "note": "ms_per_step: in-graph device time (staging + update), max over ranks; exchange_us_per_trip: record stores + flag + wait for all peers + rank-order sum (globaltimer stamps, profile mode, max over ranks); the wait share includes the ranks' arrival skew"}
-        if not args.no_cpu_baseline:
+        if not cpu_check:
+            # too large for the CPU tree within the bench's time: the sharded posterior against a single-context update of
+            # the WHOLE scan on this rank's own map replica (the single-GPU path is the one the oracle tests pin)
+            full4 = torch.zeros((n_full, 4), dtype=torch.float32, device=dev)
+            full4[:, :3] = shared[0]["body"]
+            F.scan_set_device(full4.data_ptr(), n_full)
+            x1, P1, rep1 = F.iekf_update(pkg.State.from_array(shared[0]["x_prior"]), P0, cfg)
+            out["shard_check"] = {"against": "single-GPU update of the whole scan (same library, one context)",
+                                  "x_max_abs_diff": float(np.abs(xs.as_array() - x1.as_array()).max()),
+                                  "P_max_rel_diff": float(np.abs(np.asarray(Ps) - np.asarray(P1)).max() / np.abs(np.asarray(P1)).max()),
+                                  "n_eff_sharded": int(reps.n_eff), "n_eff_single": int(rep1.n_eff),
+                                  "trips_sharded": int(reps.trips), "trips_single": int(rep1.trips),
+                                  "single_gpu_ms_per_step": float(rep1.gpu_ms)}
+            del full4
+        elif not args.no_cpu_baseline:
             from oracle import pyoracle as orc
             tree = orc.RefTree(ds)
             tree.build(wxyz_host)
@@ -314,7 +379,6 @@ def sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev
                                   "n_eff_sharded": int(reps.n_eff), "n_eff_cpu": int(o["n_eff"]),
                                   "trips_sharded": int(reps.trips), "trips_cpu": int(o["trips"])}
     barrier()
-    F.peer_detach()
     return out
 
 
@@ -517,6 +581,22 @@ def run_flivo(args, rank, world_size, local_rank):
     pipelined(min(args.warmup, 3))
     e2e_s, e2e_work = pipelined(args.steps)
     sharded = sharded_block(args, F, pkg, shared, P0, cfg, cfg_prof, rank, world_size, dev, barrier, wxyz_host, ds) if shared else None
+    if shared and not args.no_mega:
+        # BASELINE config 5 proper: the 4 M-point mega-scan against the 100 M-point map (replicated: 5 GB of buckets per GPU)
+        import flivo_scenes as scenes
+        mn_scan, mn_map, mds, mkind, midx = WORKLOADS["mega4M_map100M"]
+        mworld = scenes.make_world_torch(seed=midx + 1, n_points=mn_map, ds=mds, device=dev)
+        mp0 = scenes.street_positions(mworld, 2)[:2]
+        mshared = [scenes.make_scan_torch(mworld, seed=i, n_points=mn_scan, kind=mkind, pos=mp0[i], device=dev) for i in range(2)]
+        Fm = pkg.Flivo(device=local_rank, downsample_size=mds, cell_ratio=args.cell_ratio, initial_points=mn_map, sort_scan=bool(args.sort_scan))
+        Fm.Build(mworld["points"].cpu().numpy())
+        del mworld
+        mega = sharded_block(args, Fm, pkg, mshared, P0, cfg, cfg_prof, rank, world_size, dev, barrier, None, mds, workload="mega4M_map100M", cpu_check=False)
+        Fm.close()
+        del mshared
+        if sharded is not None:
+            sharded = {"scan260k": sharded, "mega4M_map100M": mega}
+    replay = replay_block(args, pkg, rank, world_size, local_rank, dev, barrier) if not args.no_replay else None
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None   # covers the device-resident, profile and e2e timed loops
     te = torch.tensor([e2e_s, e2e_work], dtype=torch.float64, device=dev)
@@ -651,7 +731,7 @@ def run_flivo(args, rank, world_size, local_rank):
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
                 trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add, ivox=ivox,
                 step_ms_median=float(np.median(step_ms)), step_ms_p99=float(np.percentile(step_ms, 99)), step_ms_min=float(step_ms[0]),
-                host_ev_ms_mean=float(np.mean(host_ev_ms)), sharded=sharded, solve_us=[v for v in solve_us if v is not None], e2e_serial=e2e_serial,
+                host_ev_ms_mean=float(np.mean(host_ev_ms)), sharded=sharded, replay=replay, solve_us=[v for v in solve_us if v is not None], e2e_serial=e2e_serial,
                 search_stats={"far_queries_last_step": far_q, "candidates_last_step": cand})
 
 
@@ -767,7 +847,7 @@ def main():
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                     "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (host repack to float4 + copy stream) during flivo_iekf_update_begin/_end of the current one",
                     "serial_value": r["e2e_serial"], "serial_how": "flivo_scan_upload (pageable buffer, host repack) then flivo_iekf_update, L2 flushed between steps"},
-            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "sharded": r["sharded"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
+            "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "sharded": r["sharded"], "replay": r["replay"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],
         }
         print(json.dumps(line), file=out, flush=True)

@@ -21,7 +21,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--sequences", type=int, default=64)
     ap.add_argument("--frames", type=int, default=20)
-    ap.add_argument("--pool", type=int, default=24)
+    ap.add_argument("--pool", type=int, default=16)
     ap.add_argument("--scan-points", type=int, default=24000)
     ap.add_argument("--mode", type=int, default=1)
     ap.add_argument("--concurrent", type=int, default=1, help="sequences of a rank driven at a time (host threads)")
@@ -38,7 +38,8 @@ def main():
     sh = importlib.import_module("fast_livo_noted_b200.sharding")
     import flivo_scenes as scenes
     w = scenes.make_world_torch(seed=1, n_points=1000000, ds=0.5, device="cuda")
-    poses = scenes.street_positions(w, a.pool)
+    ends = scenes.street_positions(w, 2)      # a drive along a street: consecutive frames (30 m / pool) apart
+    poses = [ends[0] + (ends[1] - ends[0]) * (i / a.pool) for i in range(a.pool)]
     pool = []
     for i in range(a.pool):
         s = scenes.make_scan_torch(w, seed=5000 + i, n_points=a.scan_points, kind="avia", pos=poses[i], device="cuda")

@@ -19,6 +19,7 @@ def test_update_is_bit_repeatable(pkg, mode, force):
     # a sparse-ish map so that many points take the far (warp-per-query, queue-fed) path
     world = scenes.make_world(seed=5, n_points=120000, ds=0.5)
     scan = scenes.make_scan(world, seed=6, n_points=30000, kind="ouster")
+    world = dict(world, points=np.ascontiguousarray(world["points"][::4]))   # thinned: few cells hold five points within reach
     npd = 18 if mode == 1 else 23
     P0 = np.eye(npd) * 1e-4
     cfg = pkg.make_cfg(mode=mode, max_iter=4, laser_point_cov=0.001, force_search=force)
@@ -28,12 +29,13 @@ def test_update_is_bit_repeatable(pkg, mode, force):
         for it in range(40):
             F.scan_upload(scan["body"])
             x, P, rep = F.iekf_update(pkg.State.from_array(scan["x_prior"]), P0, cfg)
+            far = F.stats().last_far_queries
             g = F.h_share_model(x, mode, True, want=("nbr_id", "eff", "plane"))
             cur = (x.as_array().tobytes(), np.asarray(P).tobytes(), rep.trips, rep.searches, rep.n_eff, bytes(np.asarray(rep.dx_last)),
                    g["nbr_id"].tobytes(), g["eff"].tobytes(), g["plane"].tobytes(), g["HTH"].tobytes(), g["HTz"].tobytes())
             if ref is None:
                 ref = cur
-                assert F.stats().last_far_queries > 50, "scene has too few far queries to exercise the queue"
+                assert far > 500, "scene has too few far queries (%d) to exercise the queue" % far
             else:
                 for a, b, name in zip(ref, cur, ("x", "P", "trips", "searches", "n_eff", "dx", "ids", "eff", "plane", "HTH", "HTz")):
                     assert a == b, "run %d differs from run 0 in %s" % (it, name)
