@@ -107,7 +107,7 @@ SYMBOLS = [
     "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach", "flivo_set_gnss",
     "flivo_peer_local_base", "flivo_peer_attach_local", "flivo_peer_set_timeout", "flivo_peer_reset",
     "flivo_scan_upload_async", "flivo_scan_commit", "flivo_host_register", "flivo_host_unregister",
-    "flivo_iekf_update_begin", "flivo_iekf_update_end", "flivo_knn_noalloc",
+    "flivo_iekf_update_begin", "flivo_iekf_update_end", "flivo_knn_noalloc", "flivo_frame",
 ]
 
 _lib = None
@@ -153,6 +153,7 @@ def lib():
     L.flivo_host_unregister.argtypes = [vp]
     L.flivo_iekf_update_begin.argtypes = [vp, C.POINTER(State), vp, C.POINTER(Cfg)]
     L.flivo_iekf_update_end.argtypes = [vp, C.POINTER(State), vp, C.POINTER(Report)]
+    L.flivo_frame.argtypes = [vp, C.POINTER(State), vp, C.POINTER(Cfg), vp, sz, sz, C.POINTER(Report), C.POINTER(i32)]
     L.flivo_h_share_model.argtypes = [vp, C.POINTER(State), C.c_int, C.c_int, vp, vp, C.POINTER(i32),
                                       C.POINTER(C.c_double), vp, vp, vp, vp, vp, vp]
     L.flivo_repack_v1.argtypes = [vp, vp, C.c_double, vp, vp]
@@ -367,6 +368,24 @@ class Flivo:
         rep = Report()
         self._ck(self._L.flivo_iekf_update_end(self.h, C.byref(x), _ptr(Pm), C.byref(rep)))
         return x, Pm, rep
+
+    def frame(self, st, P, cfg, next_body=None):
+        """flivo_frame: commit the staged scan, update, stage `next_body` meanwhile, map_incremental.
+        Returns (state, P, Report, points added)."""
+        x = st.copy()
+        np_ = 18 if cfg.mode == MODE_V1 else 23
+        Pm = np.ascontiguousarray(P, dtype=np.float64).reshape(np_, np_).copy()
+        rep, added = Report(), C.c_int32(0)
+        n_cur = self._next_scan.shape[0]
+        if next_body is not None:
+            assert next_body.dtype == np.float32 and next_body.flags["C_CONTIGUOUS"] and next_body.ndim == 2
+        self._ck(self._L.flivo_frame(self.h, C.byref(x), _ptr(Pm), C.byref(cfg), _ptr(next_body),
+                                     0 if next_body is None else next_body.shape[0], 0 if next_body is None else next_body.strides[0],
+                                     C.byref(rep), C.byref(added)))
+        self.n_scan = n_cur
+        if next_body is not None:
+            self._next_scan = next_body
+        return x, Pm, rep, added.value
 
     def scan_set_device(self, dev_ptr, n):
         self._ck(self._L.flivo_scan_set_device(self.h, C.c_void_p(dev_ptr), n))

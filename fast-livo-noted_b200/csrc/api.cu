@@ -883,7 +883,9 @@ extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, si
             if (stride_bytes == 16) {
                 memcpy(h + c0, src + c0 * 16, m * 16);
             } else {
-#pragma omp parallel for num_threads(nt) schedule(static) if (m >= 8192 && nt > 1)
+                // a thread team only for large scans: a 24 k-point repack is ~50 us on one thread, and replay drives several
+                // contexts from several host threads at once (8 teams of 16 threads were measured to halve the throughput)
+#pragma omp parallel for num_threads(nt) schedule(static) if (n >= 65536 && m >= 8192 && nt > 1)
                 for (long i = 0; i < (long)m; ++i) {
                     const float* p = reinterpret_cast<const float*>(src + (c0 + (size_t)i) * stride_bytes);
                     h[c0 + i] = make_float4(p[0], p[1], p[2], 0.f);
@@ -1372,6 +1374,21 @@ extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t
     int rc = ctx->map.add_points(ctx->d_world, ctx->scan_n, true, &added, ctx->err);
     if (n_added) *n_added = added;
     return map_rc(ctx, rc);
+}
+
+// One frame of LaserMapping::Run's step 5 (src/laser_mapping.cpp:165-251) in one call, for replay loops and bindings whose
+// per-call overhead matters: the scan staged by the previous frame (or by flivo_scan_upload_async) becomes current, the
+// update runs, the NEXT frame's scan is staged meanwhile, then map_incremental with the posterior.
+extern "C" int flivo_frame(flivo_ctx* ctx, flivo_state* x, double* P, const flivo_cfg* cfg, const float* next_body_xyz, size_t n_next,
+                           size_t stride_bytes, flivo_report* rep, int32_t* n_added) {
+    int rc = flivo_scan_commit(ctx);
+    if (rc != FLIVO_OK) return rc;
+    if ((rc = flivo_iekf_update_begin(ctx, x, P, cfg)) != FLIVO_OK) return rc;
+    int rc_up = FLIVO_OK;
+    if (next_body_xyz && n_next) rc_up = flivo_scan_upload_async(ctx, next_body_xyz, n_next, stride_bytes);
+    if ((rc = flivo_iekf_update_end(ctx, x, P, rep)) != FLIVO_OK) return rc;
+    if (rc_up != FLIVO_OK) return rc_up;
+    return flivo_map_add_scan(ctx, x, n_added);
 }
 
 // ---- multi-GPU ----------------------------------------------------------------------------------------------

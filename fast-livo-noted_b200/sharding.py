@@ -93,12 +93,9 @@ def _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_rat
         if len(frames) > 1:
             F.scan_upload_async(bodies[1])
         for k in range(1, len(frames)):
-            F.scan_commit()
-            F.iekf_update_begin(pkg.State.from_array(frames[k]["x_prior"]), P0, cfg)
-            if k + 1 < len(frames):
-                F.scan_upload_async(bodies[k + 1])        # travels while the update runs
-            x, _, rep = F.iekf_update_end()
-            res["added"].append(F.map_add_scan(x))
+            # flivo_frame: commit, update, stage the next scan while the update runs, map_incremental — one call
+            x, _, rep, n_add = F.frame(pkg.State.from_array(frames[k]["x_prior"]), P0, cfg, bodies[k + 1] if k + 1 < len(frames) else None)
+            res["added"].append(n_add)
             res["updates"] += 1
             res["trips"] += rep.trips
             res["work"] += rep.trips * len(bodies[k])

@@ -234,6 +234,12 @@ int flivo_iekf_update(flivo_ctx* ctx, flivo_state* inout, double* P, const flivo
 int flivo_iekf_update_begin(flivo_ctx* ctx, const flivo_state* x, const double* P, const flivo_cfg* cfg);
 int flivo_iekf_update_end(flivo_ctx* ctx, flivo_state* x_out, double* P_out, flivo_report* rep);
 
+/* One frame of step 5 of LaserMapping::Run (src/laser_mapping.cpp:165-251) in ONE call: flivo_scan_commit (the scan staged
+ * earlier becomes current), flivo_iekf_update_begin, flivo_scan_upload_async of the NEXT frame's scan (next_body_xyz may be
+ * NULL), flivo_iekf_update_end, flivo_map_add_scan with the posterior.  x and P are in/out as in flivo_iekf_update. */
+int flivo_frame(flivo_ctx* ctx, flivo_state* x, double* P, const flivo_cfg* cfg, const float* next_body_xyz, size_t n_next,
+                size_t stride_bytes, flivo_report* rep, int32_t* n_added);
+
 /* The GNSS position observation of the compiled (V1) path: `if (bgnss_en && p_gnss->new_gnss_) { computeH(...);
  * HPH.block<6,6>(0,0) += gnss_HPH; HPL.block<6,1>(0,0) += gnss_HPL; }` (src/laser_mapping.cpp:612-617) with
  * GNSSProcessing::computeH (src/GNSS_Processing.cpp:204-237) evaluated on the device at every trip's iterate.

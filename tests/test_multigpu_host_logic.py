@@ -143,6 +143,11 @@ class _FakeFlivo:
     def scan_commit(self):
         self.calls.append("commit")
 
+    def frame(self, st, P0, cfg, next_body=None):
+        self.calls.append(("frame", None if next_body is None else len(next_body)))
+        self.n += 2
+        return _FakeState(st.as_array() + 1.0), P0, _FakeReport(), 2
+
     def iekf_update_begin(self, st, P0, cfg):
         self.calls.append("begin")
         self._pending = (st, P0)
@@ -179,9 +184,7 @@ def test_replay_sequences_control_flow(pkg):
             frames = len(seqs[s])
             assert calls[:3] == [("upload", 10 + s), "trip", "build"]
             # pipelined frame loop: the next scan is staged between begin and end of the running update
-            want = [("stage", 10 + s)]
-            for k in range(1, frames):
-                want += ["commit", "begin"] + ([("stage", 10 + s)] if k + 1 < frames else []) + ["end", "add"]
+            want = [("stage", 10 + s)] + [("frame", 10 + s if k + 1 < frames else None) for k in range(1, frames)]
             assert calls[3:] == want + ["close"]
             assert r[s]["updates"] == frames - 1 and r[s]["trips"] == 4 * (frames - 1)
             assert r[s]["work"] == 4 * (frames - 1) * (10 + s) and r[s]["added"] == [2] * (frames - 1)
