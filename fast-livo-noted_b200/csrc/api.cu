@@ -1129,8 +1129,15 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
     cudaError_t cio = cudaEventRecordWithFlags(ctx->ev_upd0, s, cudaEventRecordExternal);
     if (cio == cudaSuccess) cio = cudaMemcpyAsync(ctx->d_blk, ctx->h_blk, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s);
     launch_ctl_reset(S, ctx->d_blk->x_prop, ctx->d_stats, s);
+    // from the second trip on, k_search is a programmatic dependent of the previous trip's k_fused: it starts as soon as
+    // that kernel's solving CTA has published state + control block, i.e. beside the covariance update / the next trip's
+    // state-only half, and its launch latency is off the critical path (FLIVO_PDL=0 turns it off)
+    static int pdl_on = -1;
+    if (pdl_on < 0) { const char* e = getenv("FLIVO_PDL"); pdl_on = e ? (atoi(e) != 0) : 1; }
     for (int t = 0; t < trips && t <= MAX_TRIPS; ++t) {
-        launch_search(P, sgrid, s, par_probes(ctx, sgrid));
+        FusedParams Pt = P;
+        Pt.trip = t; Pt.pdl = (t > 0 && pdl_on) ? 1 : 0;
+        launch_search(Pt, sgrid, s, par_probes(ctx, sgrid), Pt.pdl != 0);
         launch_fused(P, S, fgrid, s);
     }
     if (cio == cudaSuccess)

@@ -492,17 +492,37 @@ __global__ void __launch_bounds__(SEARCH_THREADS, IVOX ? 6 : SEARCH_CTAS_PER_SM)
     __shared__ unsigned s_bid[SEARCH_WARPS][FAR_BATCH];
     __shared__ float2 s_bmeta[SEARCH_WARPS][FAR_BATCH];
     Ctl* ctl = P.ctl;
+    // Programmatic dependent launch: this grid may have started while the previous trip's k_fused still runs its last CTA
+    // (covariance update / next trip's state-only half).  What it needs from that trip — state and control block — is
+    // published by solve_publish with a release store of ctl->ready; one thread per CTA acquires it, the barrier hands the
+    // ordering to the others, and the loads below bypass L1 (__ldcg).  A loop that has stopped never advances `ready`.
+    if (P.pdl) {
+        if (threadIdx.x == 0) {
+            for (;;) {
+                unsigned r, st;
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(r) : "l"(&ctl->ready) : "memory");
+                if (r >= (unsigned)P.trip) break;
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(st) : "l"(&ctl->stopped) : "memory");
+                if (st) break;
+            }
+        }
+        __syncthreads();
+    }
     // exit test of re-use trips and stopped trips; every word of the prologue is fetched ahead of it by independent
     // loads (one global-memory latency instead of three)
-    const int2 ss = *reinterpret_cast<const int2*>(&ctl->search);   // {search, stopped}: the first two words of Ctl
+    const int2 ss = __ldcg(reinterpret_cast<const int2*>(&ctl->search));   // {search, stopped}: the first two words of Ctl
     const int fs = P.job->force_search;
     const int n = P.job->n;
     const uint32_t max_sq_bits = P.job->max_sq_bits;
-    const unsigned tag = ctl->epoch + 1u;
-    const int searches_before = ctl->searches;
+    const unsigned tag = __ldcg(&ctl->epoch) + 1u;
+    const int searches_before = __ldcg(&ctl->searches);
     double st0 = 0.0;
-    if (threadIdx.x < 24) st0 = P.state[threadIdx.x];
-    if (ss.y || !(ss.x != 0 || fs != 0)) return;
+    if (threadIdx.x < 24) st0 = __ldcg(P.state + threadIdx.x);
+    if (ss.y || !(ss.x != 0 || fs != 0)) {
+        // (this grid must not complete before the previous trip's k_fused has: the next k_fused reads what that one writes)
+        if (threadIdx.x == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
+        return;
+    }
     unsigned long long t_start = 0, t_p1 = 0;
     const bool stamp_on = P.search_stamps != nullptr && searches_before == 0;   // first search trip of the update
     if (stamp_on && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
@@ -671,6 +691,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS, IVOX ? 6 : SEARCH_CTAS_PER_SM)
             if (tot) atomicAdd(&P.stats->candidates, (unsigned long long)tot);
         }
     }
+    if (threadIdx.x == 0) asm volatile("griddepcontrol.wait;" ::: "memory");   // see the early exit above
 }
 
 // ----------------------------------------------------------------------------------------------------
@@ -789,10 +810,16 @@ __global__ void k_ivox_map_filter(const float4* __restrict__ body, int n, const 
 void launch_fused(const FusedParams& P, const SolveParams& S, int grid, cudaStream_t stream) {
     k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P, S);
 }
-void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, bool par_probes) {
-    if (P.map.ivox) k_search<true, false><<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
-    else if (par_probes) k_search<false, true><<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
-    else k_search<false, false><<<search_grid, SEARCH_THREADS, 0, stream>>>(P);
+void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, bool par_probes, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)search_grid); cfg.blockDim = dim3(SEARCH_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    if (P.map.ivox) cudaLaunchKernelEx(&cfg, k_search<true, false>, P);
+    else if (par_probes) cudaLaunchKernelEx(&cfg, k_search<false, true>, P);
+    else cudaLaunchKernelEx(&cfg, k_search<false, false>, P);
 }
 // CTAs of k_search that fit on one SM (its grid never needs to exceed the resident set: tiles are dealt dynamically)
 int search_tile_points() { return SEARCH_THREADS; }

@@ -33,7 +33,7 @@ struct Ctl {
     unsigned int far_count;      // far_list entries published
     unsigned int far_taken;      // far_list tickets handed to consumer warps
     unsigned int epoch;          // bumped whenever the counters are rearmed; far_list entries carry epoch+1 as their tag
-    unsigned int pad_epoch;
+    unsigned int ready;          // trips whose solve has published state + control block (release; see k_search's PDL entry)
 };
 #if defined(__CUDACC__) || defined(FLIVO_HOST_EMU)
 __device__ __forceinline__ void ctl_next_trip(Ctl* ctl) {
@@ -137,6 +137,8 @@ struct FusedParams {
     unsigned int* total_cnt;   // arrival ticket of the group folders: the last one sums the group records and solves
     Ctl* ctl;
     SearchStats* stats;
+    int trip;                  // position of this launch in the update's trip sequence (k_search under PDL waits for ctl->ready >= trip)
+    int pdl;                   // 1: k_search was launched as a programmatic dependent of the previous trip's k_fused
     unsigned long long* search_stamps;   // profile mode only: [grid][4] globaltimer of CTA start / end of phase 1 / end, far queries done
 };
 

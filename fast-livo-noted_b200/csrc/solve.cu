@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_ctl_reset(const __grid_consta
     if (tid < 36) { const double v = S.x[tid]; x_prop[tid] = v; M.x[tid] = v; M.xp[tid] = v; }
     if (tid == 0) {
         ctl->search = 1; ctl->stopped = 0; ctl->iter = -1; ctl->t = 0; ctl->rematch = 0; ctl->trips = 0;
-        ctl->searches = 0; ctl->converged = 0; ctl->n_eff = 0; ctl->nan_guard = 0; ctl->res_mean = 0.0;
+        ctl->searches = 0; ctl->converged = 0; ctl->n_eff = 0; ctl->nan_guard = 0; ctl->res_mean = 0.0; ctl->ready = 0;
         ctl_next_trip(ctl);
         for (int i = 0; i < MAX_TRIPS; ++i) ctl->trip_searched[i] = 0;
         for (int i = 0; i < 23; ++i) ctl->dx_last[i] = 0.0;

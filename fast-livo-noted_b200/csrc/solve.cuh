@@ -6,7 +6,7 @@ namespace flivo {
 
 void upload_term_table();
 void launch_fused(const FusedParams& P, const SolveParams& S, int grid, cudaStream_t stream);
-void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, bool par_probes = false);
+void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, bool par_probes = false, bool pdl = false);
 int search_ctas_per_sm(bool ivox);
 int search_tile_points();
 void launch_knn(const MapView& map, const float4* q, int nq, int k, uint32_t max_sq_bits, float* out_xyz, float* out_sqd,
