@@ -123,6 +123,7 @@ struct flivo_ctx {
     // an update launched by flivo_iekf_update_begin and not yet collected by flivo_iekf_update_end
     struct { bool active = false; int np = 0, trips = 0, launches = 0; bool timed = false, staged = false; } upd;
     int graph_skip = 0;             // calls left on plain launches after the graph cache kept missing
+    unsigned int useq = 0;          // updates started on this context (Job::useq)
     unsigned int* d_perm = nullptr; // processing index -> caller's index
     unsigned long long *d_skey_a = nullptr, *d_skey_b = nullptr;
     unsigned int* d_sidx_a = nullptr;
@@ -963,6 +964,7 @@ static void fill_job(flivo_ctx* ctx, int mode, int max_iter, int force_search, d
     j.units = (int)((ctx->scan_n + UNIT_POINTS - 1) / UNIT_POINTS);
     j.groups = (fused_grid(ctx) + FOLD_CTAS - 1) / FOLD_CTAS;   // group records of k_fused summed by k_solve
     j.mode = mode; j.max_iter = max_iter; j.force_search = force_search; j.nranks = ctx->nranks; j.max_sq_bits = max_sq_bits; j.aux_out = aux_out;
+    j.useq = (++ctx->useq) & 0xFFFFFFu;
     j.R = R;
     for (int i = 0; i < 23; ++i) j.limit[i] = limit23 ? limit23[i] : 0.001;
     j.gnss_on = (ctx->gnss_on && mode == FLIVO_MODE_V1) ? 1 : 0; j.gnss_pad = 0;
@@ -1129,14 +1131,14 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
     cudaError_t cio = cudaEventRecordWithFlags(ctx->ev_upd0, s, cudaEventRecordExternal);
     if (cio == cudaSuccess) cio = cudaMemcpyAsync(ctx->d_blk, ctx->h_blk, offsetof(DevBlock, P_out), cudaMemcpyHostToDevice, s);
     launch_ctl_reset(S, ctx->d_blk->x_prop, ctx->d_stats, s);
-    // from the second trip on, k_search is a programmatic dependent of the previous trip's k_fused: it starts as soon as
-    // that kernel's solving CTA has published state + control block, i.e. beside the covariance update / the next trip's
-    // state-only half, and its launch latency is off the critical path (FLIVO_PDL=0 turns it off)
+    // k_search is a programmatic dependent of the kernel before it (k_ctl_reset, then the previous trip's k_fused): it starts
+    // as soon as that kernel's solving CTA has published state + control block, i.e. beside the covariance update / the next
+    // trip's state-only half, and its launch latency is off the critical path (FLIVO_PDL=0 turns it off)
     static int pdl_on = -1;
-    if (pdl_on < 0) { const char* e = getenv("FLIVO_PDL"); pdl_on = e ? (atoi(e) != 0) : 1; }
+    if (pdl_on < 0) { const char* e = getenv("FLIVO_PDL"); pdl_on = e ? atoi(e) : 1; }          // 2: from the second trip on only (A/B)
     for (int t = 0; t < trips && t <= MAX_TRIPS; ++t) {
         FusedParams Pt = P;
-        Pt.trip = t; Pt.pdl = (t > 0 && pdl_on) ? 1 : 0;
+        Pt.trip = t; Pt.pdl = (pdl_on == 1 || (pdl_on == 2 && t > 0)) ? 1 : 0;     // (trip 0 is the dependent of k_ctl_reset)
         launch_search(Pt, sgrid, s, par_probes(ctx, sgrid), Pt.pdl != 0);
         launch_fused(P, S, fgrid, s);
     }

@@ -495,13 +495,17 @@ __global__ void __launch_bounds__(SEARCH_THREADS, IVOX ? 6 : SEARCH_CTAS_PER_SM)
     // Programmatic dependent launch: this grid may have started while the previous trip's k_fused still runs its last CTA
     // (covariance update / next trip's state-only half).  What it needs from that trip — state and control block — is
     // published by solve_publish with a release store of ctl->ready; one thread per CTA acquires it, the barrier hands the
-    // ordering to the others, and the loads below bypass L1 (__ldcg).  A loop that has stopped never advances `ready`.
+    // ordering to the others, and the loads below bypass L1 (__ldcg).  A loop that has stopped never advances `ready`.  The
+    // word carries the update's sequence number, so the first trip (dependent of k_ctl_reset) cannot take the previous
+    // update's final word — or its `stopped` — for its own.
     if (P.pdl) {
         if (threadIdx.x == 0) {
+            const unsigned useq = __ldcg(&P.job->useq) & 0xFFFFFFu;
             for (;;) {
                 unsigned r, st;
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(r) : "l"(&ctl->ready) : "memory");
-                if (r >= (unsigned)P.trip) break;
+                if ((r >> 8) != useq) continue;              // still the previous update's word: k_ctl_reset has not armed this one
+                if ((r & 255u) >= (unsigned)P.trip) break;
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(st) : "l"(&ctl->stopped) : "memory");
                 if (st) break;
             }

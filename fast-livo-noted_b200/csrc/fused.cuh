@@ -33,7 +33,8 @@ struct Ctl {
     unsigned int far_count;      // far_list entries published
     unsigned int far_taken;      // far_list tickets handed to consumer warps
     unsigned int epoch;          // bumped whenever the counters are rearmed; far_list entries carry epoch+1 as their tag
-    unsigned int ready;          // trips whose solve has published state + control block (release; see k_search's PDL entry)
+    unsigned int ready;          // (update sequence number << 8) | trips whose solve has published state + control block
+                                 // (release store; k_search's PDL entry acquires it)
 };
 #if defined(__CUDACC__) || defined(FLIVO_HOST_EMU)
 __device__ __forceinline__ void ctl_next_trip(Ctl* ctl) {
@@ -52,6 +53,7 @@ struct Job {
     int force_search;
     int nranks;
     int aux_out;               // 1: k_fused also writes eff / normvec / world (flivo_h_share_model outputs)
+    unsigned int useq;         // sequence number of this update (24 bits used): tells a fresh ctl->ready from the previous update's
     uint32_t max_sq_bits;      // kNN distance bound as float bits (INF_BITS = unbounded)
     double R;                  // laser_point_cov
     double limit[23];

@@ -5,7 +5,7 @@
 //   k_solve_ranks : second half of a trip in the NCCL variant of the sharded update (after ncclAllGather of the ranks'
 //                   92-double records): sum in rank order + the same solve_trip;
 //   k_ctl_reset   : start of an update: control block, x_prop <- x, P_out <- P_prop, and the state-only half of the first
-//                   trip's solve (solve_pre).
+//                   trip's solve (solve_pre), which the first k_search overlaps (programmatic dependent launch).
 #include "solve_dev.cuh"
 
 namespace flivo {
@@ -28,13 +28,15 @@ __global__ void __launch_bounds__(SOLVE_THREADS) k_ctl_reset(const __grid_consta
     if (tid < 36) { const double v = S.x[tid]; x_prop[tid] = v; M.x[tid] = v; M.xp[tid] = v; }
     if (tid == 0) {
         ctl->search = 1; ctl->stopped = 0; ctl->iter = -1; ctl->t = 0; ctl->rematch = 0; ctl->trips = 0;
-        ctl->searches = 0; ctl->converged = 0; ctl->n_eff = 0; ctl->nan_guard = 0; ctl->res_mean = 0.0; ctl->ready = 0;
+        ctl->searches = 0; ctl->converged = 0; ctl->n_eff = 0; ctl->nan_guard = 0; ctl->res_mean = 0.0;
         ctl_next_trip(ctl);
         for (int i = 0; i < MAX_TRIPS; ++i) ctl->trip_searched[i] = 0;
         for (int i = 0; i < 23; ++i) ctl->dx_last[i] = 0.0;
         if (stats) { stats->far_queries = 0; stats->candidates = 0; stats->sweeps = 0; }
     }
-    __syncthreads();
+    // the control block is armed: the first trip's k_search (a programmatic dependent of this grid) may start beside the
+    // state-only half of the first solve
+    solve_publish(ctl, S.job, tid);
     solve_pre(S, M, mode, tid, SOLVE_THREADS, false);
 }
 void launch_ctl_reset(const SolveParams& S, double* x_prop, SearchStats* stats, cudaStream_t stream) {

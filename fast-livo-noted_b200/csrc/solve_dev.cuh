@@ -446,12 +446,12 @@ SDEV void solve_stamp(const SolveParams& S, int trip, int k) {
 // The state and the control block of the trip are final: publish them (release) and let the next trip's k_search start
 // while this CTA goes on with the covariance update or the next trip's state-only half.  k_search, launched as a
 // programmatic dependent of this grid, waits for ctl->ready (acquire) before it reads either (fused.cu).
-SDEV void solve_publish(Ctl* ctl, int tid) {
+SDEV void solve_publish(Ctl* ctl, const Job* job, int tid) {
 #ifndef FLIVO_HOST_EMU
     __syncthreads();                      // x (36 threads) and the control block (decision lane) are written
     if (tid == 0) {
         __threadfence();
-        const unsigned v = (unsigned)ctl->trips;
+        const unsigned v = (job->useq << 8) | ((unsigned)ctl->trips & 255u);
         asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&ctl->ready), "r"(v) : "memory");
     }
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -696,7 +696,7 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
         __syncthreads();
         solve_stamp(S, trip_no, 6);
         if (tid < 36) S.x[tid] = M.x[tid];
-        solve_publish(ctl, tid);
+        solve_publish(ctl, S.job, tid);
         if (M.flag[0]) {
             if (lane == 0 && warp < 3) {
                 if (warp == 0) d_so3_jac(M.dxo + 3, M.T.J3, nullptr);             // :1842
@@ -842,7 +842,7 @@ static __device__ __noinline__ void solve_trip(const SolveParams& S, SolveSmem& 
         __syncthreads();
         solve_stamp(S, trip_no, 6);
         if (tid < 36) S.x[tid] = M.x[tid];
-        solve_publish(ctl, tid);
+        solve_publish(ctl, S.job, tid);
         if (M.flag[0]) {                                                     // state.cov = (I - G) * state.cov (:229)
             for (int e = tid; e < 18 * 18; e += NT) {
                 const int i = e / 18, j = e % 18;
