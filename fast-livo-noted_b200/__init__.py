@@ -102,7 +102,7 @@ SYMBOLS = [
     "flivo_map_add_boxes", "flivo_map_delete_points", "flivo_map_size", "flivo_map_range", "flivo_map_flatten",
     "flivo_map_acquire_removed", "flivo_knn", "flivo_scan_upload", "flivo_scan_set_device", "flivo_h_share_model",
     "flivo_repack_v1", "flivo_iekf_update", "flivo_map_add_scan", "flivo_comm_unique_id", "flivo_comm_init",
-    "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps", "flivo_debug_search_stamps",
+    "flivo_comm_destroy", "flivo_get_stats", "flivo_debug_solve_stamps", "flivo_debug_search_stamps", "flivo_debug_scan_order",
     "flivo_raw_upload", "flivo_raw_set_device", "flivo_raw_undistort", "flivo_raw_downsample", "flivo_raw_download",
     "flivo_scan_download", "flivo_peer_export", "flivo_peer_attach", "flivo_peer_detach", "flivo_set_gnss",
     "flivo_peer_local_base", "flivo_peer_attach_local", "flivo_peer_set_timeout", "flivo_peer_reset",
@@ -166,6 +166,7 @@ def lib():
     L.flivo_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.flivo_debug_solve_stamps.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
     L.flivo_debug_search_stamps.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int, C.POINTER(C.c_int)]
+    L.flivo_debug_scan_order.argtypes = [vp, C.POINTER(C.c_uint32), C.c_size_t]
     L.flivo_peer_export.argtypes = [vp, vp]
     L.flivo_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
     L.flivo_peer_detach.argtypes = [vp]
@@ -485,6 +486,12 @@ class Flivo:
 
     def scan_download(self):
         return self._download(self._L.flivo_scan_download)
+
+    def scan_order(self, n):
+        """Processing order of the current scan of n points: out[q] = caller index of the point processed q-th."""
+        out = np.empty(n, np.uint32)
+        self._ck(self._L.flivo_debug_scan_order(self.h, out.ctypes.data_as(C.POINTER(C.c_uint32)), n))
+        return out
 
     def solve_stamps(self, trips=16):
         """[trips][16] device globaltimer stamps (ns) of the solve kernel's phases (profile mode only)."""

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libflivo_b200.so")
-SOURCES = ["map.cu", "fused.cu", "solve.cu", "frontend.cu", "api.cu"]
+SOURCES = ["map.cu", "fused.cu", "solve.cu", "stage.cu", "frontend.cu", "api.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: every float that feeds a comparison must round as separate mul/add (see csrc/flivo_dev.cuh)
 FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",

@@ -7,6 +7,7 @@
 #include "../../include/flivo.h"
 #include "map.cuh"
 #include "solve.cuh"
+#include "stage.cuh"
 #include "frontend.cuh"
 
 #include <cub/cub.cuh>
@@ -17,6 +18,7 @@
 #include <math.h>
 #include <string.h>
 #include <algorithm>
+#include <chrono>
 #include <string>
 #include <vector>
 
@@ -62,17 +64,6 @@ struct DevBlock {
 };
 
 constexpr int SSTAMP_CTAS = 4096;
-
-// Per-scan scalars of the staging sequence (keys -> radix sort -> gather), resident in HBM so that the captured graph of
-// the sequence never changes its kernel parameters: a call rewrites this block through the graph's own H2D copy node.
-struct ScanJob {
-    const char* src;      // the scan in the caller's order: n records of `stride` bytes, x y z in the first 12
-    unsigned int stride;
-    unsigned int n;       // scan points
-    unsigned int n_pad;   // items handed to the radix sort: n rounded up to SCAN_PAD (padding keys sort last)
-    float inv_edge;
-};
-constexpr unsigned int SCAN_PAD = 8192;
 
 // One of the two landing buffers of flivo_scan_upload_async: while the update of the current scan runs on the context's
 // stream, the next scan travels host -> device on the copy stream into the other slot.
@@ -124,9 +115,13 @@ struct flivo_ctx {
     struct { bool active = false; int np = 0, trips = 0, launches = 0; bool timed = false, staged = false; } upd;
     int graph_skip = 0;             // calls left on plain launches after the graph cache kept missing
     unsigned int useq = 0;          // updates started on this context (Job::useq)
+    double frame_s[5] = {0, 0, 0, 0, 0};   // FLIVO_FRAME_TRACE=1: host seconds spent in flivo_frame's commit / begin / upload / end / map_add
+    long frame_calls = 0;
     unsigned int* d_perm = nullptr; // processing index -> caller's index
     unsigned long long *d_skey_a = nullptr, *d_skey_b = nullptr;
     unsigned int* d_sidx_a = nullptr;
+    unsigned int* d_stage_ticket = nullptr;   // CTA tickets of the staging sort (stage.cu), zero between launches
+    int stage_launches = 0;                   // own kernels the last staging sequence launched
     void* d_cub = nullptr;
     size_t cub_bytes = 0;
     ScanJob* d_sjob = nullptr;          // staging scalars (device) and their pinned mirror
@@ -284,17 +279,6 @@ static bool stride_ok(size_t s) { return s >= 12 && (s % 4) == 0; }
 __global__ void k_ctl_set(Ctl* ctl, int search) {
     if (threadIdx.x == 0) { ctl->search = search; ctl->stopped = 0; ctl_next_trip(ctl); }
 }
-// Morton key of the scan point's cell in the lidar frame (a rigid transform preserves locality, so points
-// that are neighbours here query neighbouring map cells whatever the state is)
-__device__ __forceinline__ unsigned long long spread21(unsigned int v) {
-    unsigned long long x = v & 0x1FFFFF;
-    x = (x | x << 32) & 0x1F00000000FFFFull;
-    x = (x | x << 16) & 0x1F0000FF0000FFull;
-    x = (x | x << 8) & 0x100F00F00F00F00Full;
-    x = (x | x << 4) & 0x10C30C30C30C30C3ull;
-    x = (x | x << 2) & 0x1249249249249249ull;
-    return x;
-}
 // caller's records (any stride: the 48-byte PointXYZINormal AoS arrives as it is) -> float4 in the caller's order, plus,
 // when the scan is sorted (keys != nullptr), the Morton key of the point's cell and the identity index
 __global__ void k_scan_prepare(const ScanJob* __restrict__ J, float4* __restrict__ in4, unsigned long long* keys, unsigned int* idx) {
@@ -303,22 +287,9 @@ __global__ void k_scan_prepare(const ScanJob* __restrict__ J, float4* __restrict
     if (i >= J->n_pad) return;
     if (keys) idx[i] = (unsigned int)i;
     if (i >= n) { if (keys) keys[i] = 0xFFFFFFFFFFFFFFFFull; return; }   // padding: largest key, and (stable sort) behind every real point
-    const float inv_edge = J->inv_edge;
-    const unsigned stride = J->stride;
-    float4 p;
-    if (stride == 16) {
-        p = reinterpret_cast<const float4*>(J->src)[i];
-    } else {
-        const float* r = reinterpret_cast<const float*>(J->src + i * (size_t)stride);
-        p = make_float4(r[0], r[1], r[2], 0.f);
-    }
+    const float4 p = scan_record(J, i);
     in4[i] = p;
-    if (!keys) return;
-    float fx = fminf(fmaxf(floorf(p.x * inv_edge), -1048575.f), 1048575.f);
-    float fy = fminf(fmaxf(floorf(p.y * inv_edge), -1048575.f), 1048575.f);
-    float fz = fminf(fmaxf(floorf(p.z * inv_edge), -1048575.f), 1048575.f);
-    unsigned int ux = (unsigned int)((int)fx + (1 << 20)), uy = (unsigned int)((int)fy + (1 << 20)), uz = (unsigned int)((int)fz + (1 << 20));
-    keys[i] = (spread21(ux) << 2) | (spread21(uy) << 1) | spread21(uz);
+    if (keys) keys[i] = scan_morton(p, J->inv_edge);
 }
 // gather the scan into processing order and (when the arrays are given) reset the per-point flags of a fresh scan in
 // the same pass: sel = 1, eff = 0, pflags = 0 (see finish_scan)
@@ -436,6 +407,7 @@ static void free_scan(flivo_ctx* ctx) {
     if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; ctx->sort_npad = 0; }   // holds the old pointers
     cudaFree(ctx->d_body_own);
     cudaFree(ctx->d_body_in); cudaFree(ctx->d_perm); cudaFree(ctx->d_skey_a); cudaFree(ctx->d_skey_b); cudaFree(ctx->d_sidx_a);
+    cudaFree(ctx->d_stage_ticket); ctx->d_stage_ticket = nullptr;
     cudaFree(ctx->d_cub); cudaFree(ctx->d_near); cudaFree(ctx->d_near_meta); cudaFree(ctx->d_sel); cudaFree(ctx->d_eff);
     cudaFree(ctx->d_normvec); cudaFree(ctx->d_world); cudaFree(ctx->d_partials); cudaFree(ctx->d_gpartials); cudaFree(ctx->d_group_cnt); cudaFree(ctx->d_far_list); cudaFree(ctx->d_plane); cudaFree(ctx->d_pflags);
     ctx->d_body = ctx->d_body_own = ctx->d_body_in = nullptr; ctx->d_perm = nullptr; ctx->d_skey_a = ctx->d_skey_b = nullptr; ctx->d_sidx_a = nullptr;
@@ -446,6 +418,10 @@ static void free_scan(flivo_ctx* ctx) {
 
 static void free_raw(flivo_ctx* ctx);
 extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
+    if (ctx && ctx->frame_calls > 0)
+        fprintf(stderr, "[flivo_frame trace] %ld frames, host us per frame: commit %.1f  update_begin %.1f  upload_next %.1f  update_end(wait) %.1f  map_add_scan %.1f\n",
+                ctx->frame_calls, 1e6 * ctx->frame_s[0] / ctx->frame_calls, 1e6 * ctx->frame_s[1] / ctx->frame_calls, 1e6 * ctx->frame_s[2] / ctx->frame_calls,
+                1e6 * ctx->frame_s[3] / ctx->frame_calls, 1e6 * ctx->frame_s[4] / ctx->frame_calls);
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
@@ -715,6 +691,8 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
         CKC(cudaMalloc(&ctx->d_skey_a, cap * sizeof(unsigned long long)));
         CKC(cudaMalloc(&ctx->d_skey_b, cap * sizeof(unsigned long long)));
         CKC(cudaMalloc(&ctx->d_sidx_a, cap * sizeof(unsigned int)));
+        CKC(cudaMalloc(&ctx->d_stage_ticket, 2 * sizeof(unsigned int)));
+        CKC(cudaMemsetAsync(ctx->d_stage_ticket, 0, 2 * sizeof(unsigned int), ctx->stream));
         size_t b = 0;
         cub::DeviceRadixSort::SortPairs(nullptr, b, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)cap, 0, 63, ctx->stream);
         ctx->cub_bytes = b + 256;
@@ -756,8 +734,8 @@ static int finish_scan(flivo_ctx* ctx, const char* src, size_t stride, size_t n,
 }
 
 // The staging sequence of the current scan, if it has not run yet:
-//   sorted scans : k_scan_prepare (records -> float4 in the caller's order + Morton keys) -> radix sort -> k_gather4
-//                  (processing order + flag reset) as ONE captured graph (H2D of the ScanJob block included): a single
+//   sorted scans : the staging sort of stage.cu (records -> float4 in the caller's order + 16-bit keys, two stable 8-bit
+//                  passes, gather into processing order + flag reset: three own kernels) as ONE captured graph (H2D of the ScanJob block included): a single
 //                  launch, no launch gaps between the short kernels.  The graph depends only on the padded item count and
 //                  the device pointers of this context; source pointer, stride and n travel in ScanJob.
 //   unsorted     : k_scan_prepare alone (nothing at all for a float4 device pointer, which is used in place).
@@ -772,17 +750,30 @@ static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
     if (ctx->todo_slot >= 0) CKC(cudaStreamWaitEvent(s, ctx->slot[ctx->todo_slot].copied, 0));   // the records have landed
     const bool in_place = !sort && ctx->d_body != ctx->d_body_own;
     if (!in_place) {
-        static int sb0 = -1, sb1 = -1;
-        if (sb0 < 0) { const char* e = getenv("FLIVO_SORT_BITS"); if (!e || sscanf(e, "%d,%d", &sb0, &sb1) != 2) { sb0 = 6; sb1 = 22; } }
-        // 16 of the Morton bits = two radix passes: cell bits 2..6 of x and y, 2..7 of z.  The two lowest bits per axis carry no
+        // The sort key: 16 of the Morton bits — cell bits 2..6 of x and y, 2..7 of z.  The two lowest bits per axis carry no
         // locality a 128-point tile can use; the bits above repeat every 51 m (102 m in z), so a tile may mix two or three
-        // far-apart regions, which costs less than a third pass (0.5257 vs 0.5279 ms per 260 k-point update, 0.325 vs 0.334 at
-        // 24 k points; dropping fine bits instead — 9..25 — loses 8 us of search time).  FLIVO_SORT_BITS=lo,hi overrides.
+        // far-apart regions, which costs less than a third radix pass (0.5257 vs 0.5279 ms per 260 k-point update, 0.325 vs
+        // 0.334 at 24 k points; dropping fine bits instead — 9..25 — loses 8 us of search time).  FLIVO_SORT_BITS=lo,hi
+        // overrides.  Two implementations of the same stable sort (identical permutation): the own three-kernel sort of
+        // stage.cu for scans up to STAGE_OWN_MAX points, where it is faster (24 k points: step 0.266 vs 0.276 ms), and the
+        // library's onesweep radix sort above that, where its decoupled look-back beats the own kernels' histogram scans
+        // (260 k points: 0.472 vs 0.492 ms) — profiles/r2_ab_stage_sort.txt.  FLIVO_SORT=own|cub forces one of them;
+        // a key width other than 16 bits always takes the library sort.
+        static int sb0 = -1, sb1 = -1, sort_mode = 0;   // 0: by size, 1: own, 2: library
+        if (sb0 < 0) {
+            const char* e = getenv("FLIVO_SORT_BITS");
+            if (!e || sscanf(e, "%d,%d", &sb0, &sb1) != 2) { sb0 = 6; sb1 = 22; }
+            const char* m = getenv("FLIVO_SORT");
+            sort_mode = (sb1 - sb0 != 16) ? 2 : (m && !strcmp(m, "cub")) ? 2 : (m && !strcmp(m, "own")) ? 1 : 0;
+        }
         const unsigned n_pad = sort ? (unsigned)(((n + SCAN_PAD - 1) / SCAN_PAD) * SCAN_PAD) : (unsigned)n;
+        constexpr unsigned STAGE_OWN_MAX = 65536;
+        const bool own_sort = sort_mode == 1 || (sort_mode == 0 && n_pad <= STAGE_OWN_MAX);
         if (ctx->sjob_pending) { CKC(cudaEventSynchronize(ctx->sjob_ev)); ctx->sjob_pending = false; }
         ScanJob* J = ctx->h_sjob;
         J->src = ctx->todo_src; J->stride = (unsigned)ctx->todo_stride; J->n = (unsigned)n; J->n_pad = n_pad;
         J->inv_edge = 1.0f / ctx->map.view().cell_edge;
+        J->key_shift = (unsigned)sb0;
         if (sort) {
             if (!ctx->sort_exec || ctx->sort_npad != n_pad) {
                 if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; }
@@ -790,10 +781,22 @@ static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
                 CKC(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
                 cudaError_t ce = cudaEventRecordWithFlags(ctx->ev_stage0, s, cudaEventRecordExternal);
                 if (ce == cudaSuccess) ce = cudaMemcpyAsync(ctx->d_sjob, ctx->h_sjob, sizeof(ScanJob), cudaMemcpyHostToDevice, s);
-                k_scan_prepare<<<nblk(n_pad, 256), 256, 0, s>>>(ctx->d_sjob, ctx->d_body_in, ctx->d_skey_a, ctx->d_sidx_a);
-                size_t tmp = ctx->cub_bytes;
-                if (ce == cudaSuccess) ce = cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n_pad, sb0, sb1, s);
-                k_gather4<<<nblk(n_pad, 256), 256, 0, s>>>(ctx->d_sjob, ctx->d_body_in, ctx->d_perm, ctx->d_body_own, ctx->d_sel, ctx->d_eff, ctx->d_pflags);
+                if (own_sort) {
+                    // (the work buffers alias the library sort's key / index arrays: 8 bytes per point cover the key16 array,
+                    // and the two histogram matrices take n_pad bytes of the alternate key array)
+                    StageWork W;
+                    W.key16 = reinterpret_cast<unsigned short*>(ctx->d_skey_a);
+                    W.order1 = ctx->d_sidx_a;
+                    W.hist = reinterpret_cast<unsigned int*>(ctx->d_skey_b);
+                    W.ticket = ctx->d_stage_ticket;
+                    if (stage_hist_bytes(n_pad) > (size_t)n_pad * sizeof(unsigned long long)) ce = cudaErrorInvalidValue;
+                    if (ce == cudaSuccess) launch_stage_sort(ctx->d_sjob, n_pad, ctx->d_body_in, ctx->d_body_own, ctx->d_perm, ctx->d_sel, ctx->d_eff, ctx->d_pflags, W, s);
+                } else {
+                    k_scan_prepare<<<nblk(n_pad, 256), 256, 0, s>>>(ctx->d_sjob, ctx->d_body_in, ctx->d_skey_a, ctx->d_sidx_a);
+                    size_t tmp = ctx->cub_bytes;
+                    if (ce == cudaSuccess) ce = cub::DeviceRadixSort::SortPairs(ctx->d_cub, tmp, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)n_pad, sb0, sb1, s);
+                    k_gather4<<<nblk(n_pad, 256), 256, 0, s>>>(ctx->d_sjob, ctx->d_body_in, ctx->d_perm, ctx->d_body_own, ctx->d_sel, ctx->d_eff, ctx->d_pflags);
+                }
                 cudaError_t ce2 = cudaStreamEndCapture(s, &g);
                 if (ce != cudaSuccess || ce2 != cudaSuccess) {
                     if (g) cudaGraphDestroy(g);
@@ -814,6 +817,7 @@ static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
         }
         CKC(cudaEventRecord(ctx->sjob_ev, s));
         ctx->sjob_pending = true;
+        ctx->stage_launches = sort ? (own_sort ? 3 : 2) : 1;
         if (staged) *staged = true;
     }
     if (ctx->todo_slot >= 0) CKC(cudaEventRecord(ctx->slot[ctx->todo_slot].consumed, s));   // the slot may be refilled
@@ -1257,7 +1261,7 @@ extern "C" int flivo_iekf_update_begin(flivo_ctx* ctx, const flivo_state* inout,
         CKC(cudaMemcpyAsync(h->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s));   // x, P_out, ctl, stats
         CKC(cudaEventRecord(ctx->ev_upd1, s));
     }
-    ctx->upd.active = true; ctx->upd.np = np; ctx->upd.trips = trips; ctx->upd.launches = launches + (staged ? 2 : 0);
+    ctx->upd.active = true; ctx->upd.np = np; ctx->upd.trips = trips; ctx->upd.launches = launches + (staged ? ctx->stage_launches : 0);
     ctx->upd.timed = timed; ctx->upd.staged = staged;
     return FLIVO_OK;
 }
@@ -1294,7 +1298,7 @@ extern "C" int flivo_iekf_update_end(flivo_ctx* ctx, flivo_state* inout, double*
         for (int i = 0; i < 23; ++i) rep->dx_last[i] = c.dx_last[i];
         // device time from the first staging node (when this update staged its scan) to the last node of the update
         cudaEventElapsedTime(&rep->gpu_ms, ctx->upd.staged ? ctx->ev_stage0 : ctx->ev_upd0, ctx->ev_upd1);
-        rep->kernel_launches = launches;   // own kernels: k_ctl_reset + 2 per trip (+ k_scan_prepare, k_gather4 when the scan was staged here)
+        rep->kernel_launches = launches;   // own kernels: k_ctl_reset + 2 per trip (+ the staging kernels when the scan was staged here)
     }
     if (c.nan_guard == 2) {
         ctx->peer_broken = true;
@@ -1390,14 +1394,27 @@ extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t
 // update runs, the NEXT frame's scan is staged meanwhile, then map_incremental with the posterior.
 extern "C" int flivo_frame(flivo_ctx* ctx, flivo_state* x, double* P, const flivo_cfg* cfg, const float* next_body_xyz, size_t n_next,
                            size_t stride_bytes, flivo_report* rep, int32_t* n_added) {
+    static const bool trace = getenv("FLIVO_FRAME_TRACE") != nullptr;   // where a frame's host time goes (printed by flivo_ctx_destroy)
+    using clk = std::chrono::steady_clock;
+    clk::time_point t0;
+    int phase = 0;
+    auto lap = [&]() { if (trace && ctx) { const clk::time_point t1 = clk::now(); ctx->frame_s[phase] += std::chrono::duration<double>(t1 - t0).count(); t0 = t1; } ++phase; };
+    if (trace) t0 = clk::now();
     int rc = flivo_scan_commit(ctx);
     if (rc != FLIVO_OK) return rc;
+    lap();
     if ((rc = flivo_iekf_update_begin(ctx, x, P, cfg)) != FLIVO_OK) return rc;
+    lap();
     int rc_up = FLIVO_OK;
     if (next_body_xyz && n_next) rc_up = flivo_scan_upload_async(ctx, next_body_xyz, n_next, stride_bytes);
+    lap();
     if ((rc = flivo_iekf_update_end(ctx, x, P, rep)) != FLIVO_OK) return rc;
+    lap();
     if (rc_up != FLIVO_OK) return rc_up;
-    return flivo_map_add_scan(ctx, x, n_added);
+    rc = flivo_map_add_scan(ctx, x, n_added);
+    lap();
+    if (trace) ++ctx->frame_calls;
+    return rc;
 }
 
 // ---- multi-GPU ----------------------------------------------------------------------------------------------
@@ -1752,6 +1769,21 @@ extern "C" int flivo_raw_download(flivo_ctx* ctx, float* out_xyzi, size_t cap, s
     NEED(cap >= n, FLIVO_E_CAPACITY, "output too small");
     CKC(cudaMemcpyAsync(out_xyzi, ctx->d_raw, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     CKC(cudaStreamSynchronize(ctx->stream));
+    return FLIVO_OK;
+}
+
+extern "C" int flivo_debug_scan_order(flivo_ctx* ctx, uint32_t* out, size_t cap) {
+    ENTER();
+    NEED(out, FLIVO_E_ARG, "null output");
+    NEED(ctx->scan_n > 0, FLIVO_E_STATE, "no scan uploaded");
+    NEED(cap >= ctx->scan_n, FLIVO_E_ARG, "output smaller than the scan");
+    { int rcs = ensure_staged(ctx); if (rcs) return rcs; }
+    if (ctx->scan_sorted) {
+        CKC(cudaMemcpyAsync(out, ctx->d_perm, ctx->scan_n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        CKC(cudaStreamSynchronize(ctx->stream));
+    } else {
+        for (size_t i = 0; i < ctx->scan_n; ++i) out[i] = (uint32_t)i;
+    }
     return FLIVO_OK;
 }
 

@@ -300,6 +300,11 @@ int flivo_get_stats(flivo_ctx* ctx, flivo_stats* out);
 int flivo_debug_solve_stamps(flivo_ctx* ctx, uint64_t* out, int trips_cap);
 /* Same for the search kernel: per CTA {start, end of the tile phase, end, far queries finished} of the first search trip. */
 int flivo_debug_search_stamps(flivo_ctx* ctx, uint64_t* out, int ctas_cap, int* n_ctas);
+/* Diagnostic only: the processing order of the current scan (stages it if that has not happened yet):
+ * out[q] = index in the caller's order of the point processed q-th; identity for an unsorted scan.  The order is the
+ * stable sort of the scan by bits [6, 22) of the Morton code of each point's search cell in the lidar frame
+ * (csrc/stage.cuh); the reference walks feats_down_body in PCL's voxel-grid order (src/laser_mapping.cpp:499-503). */
+int flivo_debug_scan_order(flivo_ctx* ctx, uint32_t* out, size_t cap);
 
 #ifdef __cplusplus
 }
