@@ -1122,6 +1122,7 @@ extern "C" int flivo_repack_v1(const double HTH[144], const double HTz[12], doub
 // One update as a CUDA graph: the fixed sequence of max_iter+1 trips captured from the stream; kernels of skipped
 // phases (re-use trips, trips after the stop) exit at once.  (A device-side WHILE/IF conditional graph was measured
 // slower, profiles/r1_ab_launch_structure.txt.)
+constexpr size_t PDL_FUSED_MAX_POINTS = 65536;
 static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveParams& S0, int sgrid, int fgrid, int trips) {
     cudaStream_t s = ctx->stream;
     cudaGraph_t g = nullptr;
@@ -1139,12 +1140,16 @@ static int build_update_graph(flivo_ctx* ctx, const FusedParams& P, const SolveP
     // as soon as that kernel's solving CTA has published state + control block, i.e. beside the covariance update / the next
     // trip's state-only half, and its launch latency is off the critical path (FLIVO_PDL=0 turns it off)
     static int pdl_on = -1;
-    if (pdl_on < 0) { const char* e = getenv("FLIVO_PDL"); pdl_on = e ? atoi(e) : 1; }          // 2: from the second trip on only (A/B)
+    if (pdl_on < 0) { const char* e = getenv("FLIVO_PDL"); pdl_on = e ? atoi(e) : 1; }          // A/B: 3 = k_search only, 2 = k_search from the second trip on only
     for (int t = 0; t < trips && t <= MAX_TRIPS; ++t) {
         FusedParams Pt = P;
-        Pt.trip = t; Pt.pdl = (pdl_on == 1 || (pdl_on == 2 && t > 0)) ? 1 : 0;     // (trip 0 is the dependent of k_ctl_reset)
+        Pt.trip = t; Pt.pdl = (pdl_on == 1 || pdl_on == 3 || pdl_on == 4 || (pdl_on == 2 && t > 0)) ? 1 : 0;     // (trip 0 is the dependent of k_ctl_reset)
+        // k_fused behind its own trip's k_search (early on re-use trips): pays for small scans, where the per-trip serial chain
+        // dominates (24 k points: 0.268 -> 0.255 ms per step), and costs a little once the early CTAs crowd the solving CTA's
+        // SM (100 k: +2.5 us, 260 k: +4 us; profiles/r2_ab_pdl.txt) — so by scan size.  FLIVO_PDL=4 forces it, 3 turns it off.
+        Pt.pdl_fused = ((pdl_on == 1 && ctx->scan_n <= PDL_FUSED_MAX_POINTS) || pdl_on == 4) ? 1 : 0;
         launch_search(Pt, sgrid, s, par_probes(ctx, sgrid), Pt.pdl != 0);
-        launch_fused(P, S, fgrid, s);
+        launch_fused(Pt, S, fgrid, s);
     }
     if (cio == cudaSuccess)
         cio = cudaMemcpyAsync(ctx->h_blk->x, ctx->d_blk->x, offsetof(DevBlock, x_prop) - offsetof(DevBlock, x), cudaMemcpyDeviceToHost, s);

@@ -216,13 +216,34 @@ __global__ void __launch_bounds__(UNIT_POINTS, FLIVO_FUSED_CTAS_PER_SM) k_fused(
     __shared__ double s_state[36];
 
     Ctl* ctl = P.ctl;
+    // Programmatic dependent launch (P.pdl_fused): on a re-use trip this trip's k_search lets its dependents go as soon as it
+    // has seen the previous solve's release of state + control block, so this grid may run beside the tail of the previous
+    // trip's k_fused (state-only half of the next solve / covariance update).  The per-point part below needs only what
+    // that release published — acquired here by one thread per CTA, read with L1-bypassing loads — and the scan's cached
+    // planes; what the tail still writes (SolvePre, P_out) is read by the solving CTA alone, behind griddepcontrol.wait.
+    // On a search trip k_search never releases its dependents early, and the wait right below makes its results visible.
+    if (P.pdl_fused) {
+        if (threadIdx.x == 0) {
+            const unsigned useq = __ldcg(&P.job->useq) & 0xFFFFFFu;
+            for (;;) {
+                unsigned r, st;
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(r) : "l"(&ctl->ready) : "memory");
+                if ((r >> 8) != useq) continue;
+                if ((r & 255u) >= (unsigned)P.trip) break;
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(st) : "l"(&ctl->stopped) : "memory");
+                if (st) break;
+            }
+        }
+        __syncthreads();
+    }
     // every word the prologue needs is fetched before the exit test: independent loads, one global-memory latency
-    const int2 ss = *reinterpret_cast<const int2*>(&ctl->search);   // {search, stopped}
+    const int2 ss = __ldcg(reinterpret_cast<const int2*>(&ctl->search));   // {search, stopped}
     const int n_pts = P.job->n, mode = P.job->mode, aux_out = P.job->aux_out, fsearch = P.job->force_search;
     double st0 = 0.0;
-    if (threadIdx.x < 36) st0 = P.state[threadIdx.x];
+    if (threadIdx.x < 36) st0 = __ldcg(P.state + threadIdx.x);
     if (ss.y) return;
     const bool search = (ss.x != 0) || (fsearch != 0);
+    if (P.pdl_fused && search) asm volatile("griddepcontrol.wait;" ::: "memory");   // this trip's neighbours, planes and flags
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 36) s_state[threadIdx.x] = st0;
     __syncthreads();
@@ -403,6 +424,7 @@ __global__ void __launch_bounds__(UNIT_POINTS, FLIVO_FUSED_CTAS_PER_SM) k_fused(
         }
         M.sum[threadIdx.x] = sum;
     }
+    if (P.pdl_fused) asm volatile("griddepcontrol.wait;" ::: "memory");   // the previous trip's k_fused is complete: SolvePre / P_out are final
     __syncthreads();
     solve_trip(SP, M, threadIdx.x, UNIT_POINTS);
 }
@@ -523,8 +545,13 @@ __global__ void __launch_bounds__(SEARCH_THREADS, IVOX ? 6 : SEARCH_CTAS_PER_SM)
     double st0 = 0.0;
     if (threadIdx.x < 24) st0 = __ldcg(P.state + threadIdx.x);
     if (ss.y || !(ss.x != 0 || fs != 0)) {
-        // (this grid must not complete before the previous trip's k_fused has: the next k_fused reads what that one writes)
-        if (threadIdx.x == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
+        // Nothing to search.  This trip's k_fused may start now (it is a programmatic dependent of this grid when P.pdl_fused
+        // is set) — but this grid must not COMPLETE before the previous trip's k_fused has: the solving CTA of the next
+        // k_fused takes the completion of this grid as the completion of that one.
+        if (threadIdx.x == 0) {
+            asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+        }
         return;
     }
     unsigned long long t_start = 0, t_p1 = 0;
@@ -812,7 +839,13 @@ __global__ void k_ivox_map_filter(const float4* __restrict__ body, int n, const 
 
 // ---- host launchers ---------------------------------------------------------------------------------
 void launch_fused(const FusedParams& P, const SolveParams& S, int grid, cudaStream_t stream) {
-    k_fused<<<grid, UNIT_POINTS, 0, stream>>>(P, S);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(UNIT_POINTS); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = P.pdl_fused ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, k_fused, P, S);
 }
 void launch_search(const FusedParams& P, int search_grid, cudaStream_t stream, bool par_probes, bool pdl) {
     cudaLaunchConfig_t cfg = {};

@@ -141,6 +141,7 @@ struct FusedParams {
     SearchStats* stats;
     int trip;                  // position of this launch in the update's trip sequence (k_search under PDL waits for ctl->ready >= trip)
     int pdl;                   // 1: k_search was launched as a programmatic dependent of the previous trip's k_fused
+    int pdl_fused;            // 1: k_fused is a programmatic dependent of this trip's k_search, which lets it go early on re-use trips
     unsigned long long* search_stamps;   // profile mode only: [grid][4] globaltimer of CTA start / end of phase 1 / end, far queries done
 };
 

@@ -17,6 +17,8 @@
 #include <cub/cub.cuh>
 #include <thrust/iterator/counting_iterator.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 #include <vector>
 
 namespace flivo {
@@ -123,18 +125,23 @@ __device__ bool claim_slot(const MapView& m, uint32_t b, float4 p, MapCounters* 
 // ------------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------------
-__global__ void k_stamp_ids(const float4* __restrict__ in, float4* __restrict__ out, size_t n, int base_id) {
+__global__ void k_stamp_ids(const float4* __restrict__ in, float4* __restrict__ out, size_t n, int base_id, const BatchJob* job) {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (job) {
+        base_id = job->base_id;
+        if (i >= job->n) { const float qn = __int_as_float(0x7FC00000); out[i] = make_float4(qn, qn, qn, __int_as_float(EMPTY_ID)); return; }   // padding: no stage takes it for a point
+    }
     float4 p = in[i];
     p.w = __int_as_float(base_id + (int)i);
     out[i] = p;
 }
 
 __global__ void k_point_keys(const float4* __restrict__ pts, size_t n, MapView m, unsigned long long* __restrict__ keys,
-                             unsigned int* __restrict__ idx, MapCounters* cnt) {
+                             unsigned int* __restrict__ idx, MapCounters* cnt, const BatchJob* job) {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (job && i >= job->n) { keys[i] = INVALID_KEY; idx[i] = (unsigned int)i; return; }   // padding, not an error
     float4 p = pts[i];
     int kx, ky, kz;
     bool ok = point_ok(m, p, kx, ky, kz);
@@ -350,14 +357,30 @@ __global__ void k_ds_decide(const unsigned long long* __restrict__ keys, const u
     int best_id = 0x7FFFFFFF;
     float bx = 0.f, by = 0.f, bz = 0.f;
     if (!defer) {
+        // The cells come through the blocks' search records (one 32-byte load answers "which cells of this block hold
+        // points and where are their buckets"; the cells of one voxel's neighbourhood share one or two blocks).  The records
+        // are those of the map BEFORE this batch (k_block_records runs at the end of insert_batch): cells and blocks the
+        // batch itself created are missing from them, and they hold no stored point yet.
         int g = m.gshift;
+        bool have_rec = false;
+        unsigned long long rec_key = 0ull, full = 0ull, bc = 0ull;
+        int slot = -1;
         for (int cx = (kx - 1) >> g; cx <= (kx + 1) >> g && !defer; ++cx)
             for (int cy = (ky - 1) >> g; cy <= (ky + 1) >> g && !defer; ++cy)
                 for (int cz = (kz - 1) >> g; cz <= (kz + 1) >> g && !defer; ++cz) {
-                    uint32_t b = cell_bucket(m, cx, cy, cz);
+                    const unsigned long long bkey = pack_block(cx >> 2, cy >> 2, cz >> 2);
+                    if (!have_rec || bkey != rec_key) { slot = rec_find(m, bkey, full, bc); rec_key = bkey; have_rec = true; }
+                    if (slot < 0) continue;
+                    const int off = cell_off(cx, cy, cz);
+                    if (!((full >> off) & 1ull)) continue;
+                    const uint32_t ent = cell_entry(slot, full, bc, off);
+                    uint32_t b = entry_bucket(m, ent);
                     while (b != NONE32 && !defer) {
+                        float4 line[BUCKET_SLOTS];
+                        ld_bucket(m.buckets + (size_t)b * BUCKET_SLOTS, line);
+                        const uint32_t nxt = entry_next(m, ent, b);
                         for (int s = 0; s < BUCKET_SLOTS; ++s) {
-                            float4 x = __ldg(m.buckets + (size_t)b * BUCKET_SLOTS + s);
+                            float4 x = line[s];
                             int id = __float_as_int(x.w);
                             if (id < 0) continue;
                             bool inb = in_box3(box, x.x, x.y, x.z);
@@ -370,7 +393,7 @@ __global__ void k_ds_decide(const unsigned long long* __restrict__ keys, const u
                             float d = sqdist3(x.x, x.y, x.z, box.mid[0], box.mid[1], box.mid[2]);
                             if (d < best_d || (d == best_d && id < best_id)) { best_d = d; best_id = id; bx = x.x; by = x.y; bz = x.z; }
                         }
-                        b = __ldg(m.bucket_next + b);
+                        b = nxt;
                     }
                 }
     }
@@ -748,6 +771,10 @@ void MapStore::release() {
     cudaFree(v_.dir_keys); cudaFree(v_.cell_tab); cudaFree(v_.blk_mask); cudaFree(v_.buckets); cudaFree(v_.bucket_next);
     cudaFree(const_cast<BlockRec*>(v_.rec));
     v_ = MapView{};
+    drop_add_graph();
+    cudaFree(d_bjob_); d_bjob_ = nullptr;
+    if (h_bjob_) cudaFreeHost(h_bjob_);
+    h_bjob_ = nullptr;
     cudaFree(d_cnt_); d_cnt_ = nullptr;
     if (h_pinned_) cudaFreeHost(h_pinned_);
     h_pinned_ = nullptr;
@@ -815,6 +842,9 @@ int MapStore::init(cudaStream_t stream, float ds, int cell_ratio, size_t initial
 int MapStore::refresh_counters(std::string& err) {
     CK(cudaMemcpyAsync(h_pinned_, d_cnt_, sizeof(MapCounters), cudaMemcpyDeviceToHost, stream_));
     CK(cudaStreamSynchronize(stream_));
+    return finish_counters(err);
+}
+int MapStore::finish_counters(std::string& err) {
     h_cnt_ = *h_pinned_;
     blocks_ub_ = h_cnt_.blocks_used;
     buckets_ub_ = h_cnt_.buckets_used;
@@ -822,8 +852,7 @@ int MapStore::refresh_counters(std::string& err) {
         int e = h_cnt_.error;
         err = e == 1 ? "point coordinate not finite or outside the addressable range" :
               e == 2 ? "block directory full" : "bucket pool exhausted";
-        int zero = 0;
-        cudaMemcpyAsync(&d_cnt_->error, &zero, sizeof(int), cudaMemcpyHostToDevice, stream_);
+        cudaMemsetAsync(&d_cnt_->error, 0, sizeof(int), stream_);
         return e == 1 ? -2 : -3;
     }
     return 0;
@@ -914,7 +943,7 @@ int MapStore::ensure_scratch(size_t n, std::string& err) {
 
 int MapStore::stamp_ids(const float4* d_pts, size_t n, int base_id, std::string& err) {
     if (ensure_scratch(n, err)) return -1;
-    k_stamp_ids<<<nblk(n, 256), 256, 0, stream_>>>(d_pts, scratch_pts_, n, base_id);
+    k_stamp_ids<<<nblk(n, 256), 256, 0, stream_>>>(d_pts, scratch_pts_, n, base_id, nullptr);
     CK(cudaGetLastError());
     return 0;
 }
@@ -926,13 +955,13 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
     if (n > 0x7FFFFFF0ull) { err = "batch too large"; return -2; }
     if (ensure_scratch(n, err)) return -1;
     const int T = 256;
-    k_point_keys<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, keys_a_, idx_a_, d_cnt_);
-    CK(cudaGetLastError());
-    size_t tmp = cub_tmp_bytes_;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp_, tmp, keys_a_, keys_b_, idx_a_, idx_b_, (int)n, 0, 63, stream_));
     // sizing: exact unique counts for large batches (one extra sync), conservative bound otherwise
     size_t new_blocks = n, new_cells = n;
-    if (n > (1u << 18)) {
+    if (n > ADD_GRAPH_MAX) {
+        k_point_keys<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, keys_a_, idx_a_, d_cnt_, nullptr);
+        CK(cudaGetLastError());
+        size_t tmp = cub_tmp_bytes_;
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_, tmp, keys_a_, keys_b_, idx_a_, idx_b_, (int)n, 0, 63, stream_));
         CK(cudaMemsetAsync(d_misc_, 0, 16 * sizeof(unsigned int), stream_));
         k_count_unique<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, d_misc_);
         CK(cudaGetLastError());
@@ -944,6 +973,22 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
     }
     size_t chain_extra = downsample_on ? 64 : n / BUCKET_SLOTS + 64;
     if (ensure_capacity(new_blocks, new_cells + chain_extra, err)) return -1;
+    if (enqueue_insert(d_pts_id, n, downsample_on, nullptr, n > ADD_GRAPH_MAX, err)) return -1;
+    int rc = refresh_counters(err);
+    if (n_added) *n_added = h_cnt_.add_counter;
+    CK(cudaMemsetAsync(&d_cnt_->add_counter, 0, sizeof(int), stream_));
+    CK(cudaMemsetAsync(&d_cnt_->deferred, 0, sizeof(int), stream_));
+    return rc;
+}
+
+int MapStore::enqueue_insert(const float4* d_pts_id, size_t n, bool downsample_on, const BatchJob* job, bool keys_sorted, std::string& err) {
+    const int T = 256;
+    size_t tmp = cub_tmp_bytes_;
+    if (!keys_sorted) {   // (a large batch was keyed and sorted by the caller already, to size the tables)
+        k_point_keys<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, keys_a_, idx_a_, d_cnt_, job);
+        CK(cudaGetLastError());
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_, tmp, keys_a_, keys_b_, idx_a_, idx_b_, (int)n, 0, 63, stream_));
+    }
     CK(cudaMemsetAsync(d_misc_, 0, 16 * sizeof(unsigned int), stream_));
     // cells of the batch (new ones get consecutive buckets in key order), then the search records of the touched blocks;
     // idx_a_ / keys_a_ are free once the sort has produced keys_b_ / idx_b_
@@ -974,11 +1019,55 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
     // search records of the touched blocks, once the batch is stored (storing may still append overflow buckets)
     k_block_records<<<nblk(n, T), T, 0, stream_>>>(keys_b_, n, v_, const_cast<BlockRec*>(v_.rec));
     CK(cudaGetLastError());
-    int rc = refresh_counters(err);
+    return 0;
+}
+
+void MapStore::drop_add_graph() {
+    if (add_exec_) { cudaGraphExecDestroy(add_exec_); add_exec_ = nullptr; }
+    add_src_ = nullptr; add_npad_ = 0; add_scratch_ = nullptr;
+}
+
+// Add_Points(…, true) of a scan-sized batch: the whole sequence (job block H2D, ids, keys, sort, cells, down-sample decision,
+// store, records, counters D2H, counter reset) replayed as one graph.  The graph is rebuilt when the padded size, the
+// source buffer, the scratch buffers or the map's tables (growth) change.
+int MapStore::add_points_graph(const float4* d_pts, size_t n, int* n_added, std::string& err) {
+    const size_t n_pad = ((n + ADD_PAD - 1) / ADD_PAD) * ADD_PAD;
+    if (ensure_scratch(n_pad, err)) return -1;
+    if (ensure_capacity(n_pad, n_pad + 64, err)) return -1;
+    if (!d_bjob_) {
+        CK(cudaMalloc(&d_bjob_, sizeof(BatchJob)));
+        CK(cudaMallocHost(&h_bjob_, sizeof(BatchJob)));
+    }
+    h_bjob_->n = (unsigned int)n;
+    h_bjob_->base_id = next_id_;
+    if (!add_exec_ || add_src_ != d_pts || add_npad_ != n_pad || add_scratch_ != scratch_pts_ || memcmp(&add_view_, &v_, sizeof(MapView)) != 0) {
+        drop_add_graph();
+        cudaGraph_t g = nullptr;
+        CK(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal));
+        cudaError_t ce = cudaMemcpyAsync(d_bjob_, h_bjob_, sizeof(BatchJob), cudaMemcpyHostToDevice, stream_);
+        k_stamp_ids<<<nblk(n_pad, 256), 256, 0, stream_>>>(d_pts, scratch_pts_, n_pad, 0, d_bjob_);
+        std::string cerr;
+        int rc = enqueue_insert(scratch_pts_, n_pad, true, d_bjob_, false, cerr);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_pinned_, d_cnt_, sizeof(MapCounters), cudaMemcpyDeviceToHost, stream_);
+        if (ce == cudaSuccess) ce = cudaMemsetAsync(&d_cnt_->add_counter, 0, sizeof(int), stream_);
+        if (ce == cudaSuccess) ce = cudaMemsetAsync(&d_cnt_->deferred, 0, sizeof(int), stream_);
+        cudaError_t ce2 = cudaStreamEndCapture(stream_, &g);
+        if (rc || ce != cudaSuccess || ce2 != cudaSuccess) {
+            if (g) cudaGraphDestroy(g);
+            cudaGetLastError();
+            err = "capture of the Add_Points graph: " + (rc ? cerr : std::string(cudaGetErrorString(ce != cudaSuccess ? ce : ce2)));
+            return -4;   // the caller falls back to plain launches
+        }
+        ce = cudaGraphInstantiate(&add_exec_, g, 0);
+        cudaGraphDestroy(g);
+        if (ce != cudaSuccess) { add_exec_ = nullptr; cudaGetLastError(); err = std::string("cudaGraphInstantiate (Add_Points): ") + cudaGetErrorString(ce); return -4; }
+        add_src_ = d_pts; add_npad_ = n_pad; add_scratch_ = scratch_pts_; add_view_ = v_;
+    }
+    CK(cudaGraphLaunch(add_exec_, stream_));
+    CK(cudaStreamSynchronize(stream_));
+    next_id_ += (int)n;
+    int rc = finish_counters(err);
     if (n_added) *n_added = h_cnt_.add_counter;
-    int zero = 0;
-    CK(cudaMemcpyAsync(&d_cnt_->add_counter, &zero, sizeof(int), cudaMemcpyHostToDevice, stream_));
-    CK(cudaMemcpyAsync(&d_cnt_->deferred, &zero, sizeof(int), cudaMemcpyHostToDevice, stream_));
     return rc;
 }
 
@@ -1006,6 +1095,13 @@ int MapStore::add_points(const float4* d_pts, size_t n, bool downsample_on, int*
     if (n == 0) return 0;
     if ((size_t)next_id_ + n > 0x7FFFFFF0ull) { err = "insertion ids exhausted (2^31)"; return -3; }
     if (v_.ivox && downsample_on) { err = "iVox mode: AddPoints keeps every point (no voxel down-sampling)"; return -2; }
+    static const bool graph_on = !(getenv("FLIVO_ADD_GRAPH") && atoi(getenv("FLIVO_ADD_GRAPH")) == 0);
+    if (downsample_on && graph_on && n <= ADD_GRAPH_MAX && add_graph_fail_ < 3) {
+        const int rc = add_points_graph(d_pts, n, n_added, err);
+        if (rc != -4) { add_graph_fail_ = 0; return rc; }
+        ++add_graph_fail_;   // could not be captured: plain launches (and no further attempts after three failures in a row)
+        err.clear();
+    }
     if (stamp_ids(d_pts, n, next_id_, err)) return -1;
     next_id_ += (int)n;
     return insert_batch(scratch_pts_, n, downsample_on, n_added, err);

@@ -14,6 +14,14 @@ struct SegInfo {      // decision of one voxel segment of an Add_Points batch
     int flags;        // bit0: segment head, bit1: deferred to the serial pass, bit2: something changes
 };
 
+// per-call scalars of a captured insert sequence
+struct BatchJob {
+    unsigned int n;   // real points of the batch (the sequence runs on n rounded up to ADD_PAD items)
+    int base_id;      // insertion id of the first point
+};
+constexpr size_t ADD_PAD = 8192;
+constexpr size_t ADD_GRAPH_MAX = 1u << 18;   // batches up to this size are sized conservatively (no mid-sequence sync) and may be captured
+
 class MapStore {
 public:
     MapStore() = default;
@@ -53,6 +61,12 @@ private:
     // common pipeline; d_pts_id: float4 with w = id bits
     int insert_batch(const float4* d_pts_id, size_t n, bool downsample_on, int* n_added, std::string& err);
     int stamp_ids(const float4* d_pts, size_t n, int base_id, std::string& err);  // -> scratch_pts_
+    // the kernels of one insert batch, k_point_keys .. k_block_records, for n items; with a job block the items at and
+    // beyond job->n are padding (invalid keys, skipped by every stage)
+    int enqueue_insert(const float4* d_pts_id, size_t n, bool downsample_on, const BatchJob* job, bool keys_sorted, std::string& err);
+    int add_points_graph(const float4* d_pts, size_t n, int* n_added, std::string& err);
+    int finish_counters(std::string& err);   // host mirror <- pinned copy of the device counters
+    void drop_add_graph();
 
     cudaStream_t stream_ = nullptr;
     MapView v_{};
@@ -77,6 +91,17 @@ private:
     void* cub_tmp_ = nullptr;
     size_t cub_tmp_bytes_ = 0;
     unsigned int* d_misc_ = nullptr;  // [0]=unique blocks, [1]=unique cells, [2]=slop count, [3]=deferred points
+    // Add_Points(…, true) of a scan-sized batch as ONE captured graph (map_incremental is ~30 launches otherwise and
+    // launch-bound): per-call scalars travel in a BatchJob block, the graph depends on the padded size, the source
+    // pointer and the map's tables only
+    BatchJob* d_bjob_ = nullptr;
+    BatchJob* h_bjob_ = nullptr;      // pinned
+    cudaGraphExec_t add_exec_ = nullptr;
+    const float4* add_src_ = nullptr;
+    size_t add_npad_ = 0;
+    MapView add_view_{};
+    const void* add_scratch_ = nullptr;
+    int add_graph_fail_ = 0;
 };
 
 constexpr int SLOP_LIST_CAP = 4096;
