@@ -270,7 +270,7 @@ def replay_block(args, pkg, rank, world_size, local_rank, dev, barrier):
     poses = [ends[0] + (ends[1] - ends[0]) * (i / pool_n) for i in range(pool_n)]
     pool = []
     for i in range(pool_n):
-        s = scenes.make_scan_torch(w, seed=5000 + i, n_points=24_000, kind="avia", pos=poses[i], device=dev)
+        s = scenes.make_down_scan_torch(w, seed=5000 + i, n_points=24_000, leaf=0.3, kind="avia", pos=poses[i], device=dev)   # feats_down_body is voxel-filtered (src/laser_mapping.cpp:129-130); leaf 0.3: the synthetic world shows only ~12 k distinct 0.5 m voxels from one pose
         pool.append({"body": s["body"].cpu().numpy(), "x_prior": np.asarray(s["x_prior"])})
     del w
     seqs = [[pool[(s + k) % pool_n] for k in range(n_frames)] for s in range(n_seq)]

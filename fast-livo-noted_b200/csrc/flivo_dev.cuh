@@ -62,6 +62,11 @@ struct MapView {
     unsigned long long* blk_mask;  // [dir_cap]
     float4* buckets;               // [bucket_cap * 8]
     uint32_t* bucket_next;         // [bucket_cap]
+    // coarse occupancy: a SUPER-BLOCK is 4x4x4 blocks (16 cells a side); sup_keys / sup_mask are an open-addressing table of
+    // the same capacity as the directory (packed super-block coordinates -> one bit per block that exists).  A wide search
+    // cube asks ~1/64 as many questions of it as of the block directory, and only blocks that exist are then probed.
+    unsigned long long* sup_keys;  // [dir_cap]
+    unsigned long long* sup_mask;  // [dir_cap]
     uint32_t dir_mask;             // dir_cap - 1 (dir_cap is a power of two)
     uint32_t bucket_cap;
     float ds;                      // downsample_size
@@ -202,6 +207,32 @@ __device__ __forceinline__ int dir_find(const MapView& m, unsigned long long key
     }
 }
 // find-or-insert; returns slot (never fails while load factor < 1; callers keep it <= 0.5)
+// a block came into existence: set its bit in its super-block's mask (the table has the directory's capacity and holds at
+// most as many entries as the directory has blocks, so it cannot fill up before the directory does)
+__device__ __forceinline__ void sup_mark(const MapView& m, unsigned long long block_key) {
+    int bx, by, bz;
+    unpack_block(block_key, bx, by, bz);
+    const unsigned long long skey = pack_block(bx >> 2, by >> 2, bz >> 2);
+    const unsigned long long bit = 1ull << cell_off(bx, by, bz);
+    uint32_t s = hash_block(skey ^ 0x9E3779B97F4A7C15ull) & m.dir_mask;
+    for (uint32_t probe = 0; probe <= m.dir_mask; ++probe) {
+        unsigned long long k = m.sup_keys[s];
+        if (k == DIR_EMPTY) k = atomicCAS(m.sup_keys + s, DIR_EMPTY, skey);
+        if (k == DIR_EMPTY || k == skey) { atomicOr(m.sup_mask + s, bit); return; }
+        s = (s + 1) & m.dir_mask;
+    }
+}
+// bits of the blocks that exist in super-block (sx, sy, sz); 0 when none does
+__device__ __forceinline__ unsigned long long sup_find(const MapView& m, int sx, int sy, int sz) {
+    const unsigned long long skey = pack_block(sx, sy, sz);
+    uint32_t s = hash_block(skey ^ 0x9E3779B97F4A7C15ull) & m.dir_mask;
+    while (true) {
+        const unsigned long long k = __ldg(m.sup_keys + s);
+        if (k == skey) return __ldg(m.sup_mask + s);
+        if (k == DIR_EMPTY) return 0ull;
+        s = (s + 1) & m.dir_mask;
+    }
+}
 __device__ __forceinline__ int dir_find_or_insert(const MapView& m, unsigned long long key, MapCounters* cnt) {
     uint32_t s = hash_block(key) & m.dir_mask;
     for (uint32_t probe = 0; probe <= m.dir_mask; ++probe) {
@@ -209,7 +240,7 @@ __device__ __forceinline__ int dir_find_or_insert(const MapView& m, unsigned lon
         if (k == key) return (int)s;
         if (k == DIR_EMPTY) {
             unsigned long long old = atomicCAS(m.dir_keys + s, DIR_EMPTY, key);
-            if (old == DIR_EMPTY) { atomicAdd(&cnt->blocks_used, 1u); return (int)s; }
+            if (old == DIR_EMPTY) { atomicAdd(&cnt->blocks_used, 1u); sup_mark(m, key); return (int)s; }
             if (old == key) return (int)s;
         }
         s = (s + 1) & m.dir_mask;

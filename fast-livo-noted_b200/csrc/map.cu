@@ -688,6 +688,7 @@ __global__ void k_rehash(MapView oldm, size_t old_cap, MapView newm, MapCounters
         }
         slot = (int)s;
         newm.blk_mask[s] = oldm.blk_mask[warp];
+        sup_mark(newm, key);
     }
     slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
     newm.cell_tab[(size_t)slot * 64 + lane] = oldm.cell_tab[warp * 64 + lane];
@@ -770,6 +771,7 @@ MapStore::~MapStore() { release(); }
 void MapStore::release() {
     cudaFree(v_.dir_keys); cudaFree(v_.cell_tab); cudaFree(v_.blk_mask); cudaFree(v_.buckets); cudaFree(v_.bucket_next);
     cudaFree(const_cast<BlockRec*>(v_.rec));
+    cudaFree(v_.sup_keys); cudaFree(v_.sup_mask);
     v_ = MapView{};
     drop_add_graph();
     cudaFree(d_bjob_); d_bjob_ = nullptr;
@@ -792,6 +794,10 @@ int MapStore::alloc_tables(size_t dir_cap, size_t bucket_cap, std::string& err) 
     CK(cudaMalloc(&v_.blk_mask, dir_cap * sizeof(unsigned long long)));
     CK(cudaMalloc((void**)&v_.rec, dir_cap * sizeof(BlockRec)));
     CK(cudaMemsetAsync((void*)v_.rec, 0xFF, dir_cap * sizeof(BlockRec), stream_));   // key = DIR_EMPTY everywhere
+    CK(cudaMalloc(&v_.sup_keys, dir_cap * sizeof(unsigned long long)));
+    CK(cudaMalloc(&v_.sup_mask, dir_cap * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(v_.sup_keys, 0xFF, dir_cap * sizeof(unsigned long long), stream_));
+    CK(cudaMemsetAsync(v_.sup_mask, 0, dir_cap * sizeof(unsigned long long), stream_));
     CK(cudaMalloc(&v_.buckets, bucket_cap * BUCKET_SLOTS * sizeof(float4)));
     CK(cudaMalloc(&v_.bucket_next, bucket_cap * sizeof(uint32_t)));
     CK(cudaMemsetAsync(v_.dir_keys, 0xFF, dir_cap * sizeof(unsigned long long), stream_));
@@ -869,12 +875,17 @@ int MapStore::grow_dir(size_t new_cap, std::string& err) {
     CK(cudaMemsetAsync(nv.cell_tab, 0xFF, new_cap * 64 * sizeof(uint32_t), stream_));
     CK(cudaMemsetAsync(nv.blk_mask, 0, new_cap * sizeof(unsigned long long), stream_));
     CK(cudaMalloc((void**)&nv.rec, new_cap * sizeof(BlockRec)));
+    CK(cudaMalloc(&nv.sup_keys, new_cap * sizeof(unsigned long long)));
+    CK(cudaMalloc(&nv.sup_mask, new_cap * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(nv.sup_keys, 0xFF, new_cap * sizeof(unsigned long long), stream_));
+    CK(cudaMemsetAsync(nv.sup_mask, 0, new_cap * sizeof(unsigned long long), stream_));
     nv.dir_mask = (uint32_t)(new_cap - 1);
     k_rehash<<<nblk(old_cap * 32, 256), 256, 0, stream_>>>(oldv, old_cap, nv, d_cnt_);
     k_all_records<<<nblk(new_cap, 256), 256, 0, stream_>>>(nv, new_cap, const_cast<BlockRec*>(nv.rec));
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(stream_));
     cudaFree(oldv.dir_keys); cudaFree(oldv.cell_tab); cudaFree(oldv.blk_mask); cudaFree(const_cast<BlockRec*>(oldv.rec));
+    cudaFree(oldv.sup_keys); cudaFree(oldv.sup_mask);
     v_ = nv;
     dir_cap_ = new_cap;
     return 0;
@@ -1077,6 +1088,8 @@ int MapStore::build(const float4* d_pts, size_t n, std::string& err) {
     CK(cudaMemsetAsync(v_.cell_tab, 0xFF, dir_cap_ * 64 * sizeof(uint32_t), stream_));
     CK(cudaMemsetAsync(v_.blk_mask, 0, dir_cap_ * sizeof(unsigned long long), stream_));
     CK(cudaMemsetAsync((void*)v_.rec, 0xFF, dir_cap_ * sizeof(BlockRec), stream_));
+    CK(cudaMemsetAsync(v_.sup_keys, 0xFF, dir_cap_ * sizeof(unsigned long long), stream_));
+    CK(cudaMemsetAsync(v_.sup_mask, 0, dir_cap_ * sizeof(unsigned long long), stream_));
     size_t used = std::min<size_t>(bucket_cap_, (size_t)buckets_ub_ + 64);
     CK(cudaMemsetAsync(v_.buckets, 0xFF, used * BUCKET_SLOTS * sizeof(float4), stream_));
     CK(cudaMemsetAsync(v_.bucket_next, 0xFF, used * sizeof(uint32_t), stream_));
@@ -1239,6 +1252,8 @@ int MapStore::set_downsample(float ds, std::string& err) {
     CK(cudaMemsetAsync(v_.cell_tab, 0xFF, dir_cap_ * 64 * sizeof(uint32_t), stream_));
     CK(cudaMemsetAsync(v_.blk_mask, 0, dir_cap_ * sizeof(unsigned long long), stream_));
     CK(cudaMemsetAsync((void*)v_.rec, 0xFF, dir_cap_ * sizeof(BlockRec), stream_));
+    CK(cudaMemsetAsync(v_.sup_keys, 0xFF, dir_cap_ * sizeof(unsigned long long), stream_));
+    CK(cudaMemsetAsync(v_.sup_mask, 0, dir_cap_ * sizeof(unsigned long long), stream_));
     CK(cudaMemsetAsync(v_.buckets, 0xFF, bucket_cap_ * BUCKET_SLOTS * sizeof(float4), stream_));
     CK(cudaMemsetAsync(v_.bucket_next, 0xFF, bucket_cap_ * sizeof(uint32_t), stream_));
     unsigned int rc_keep = h_cnt_.removed_count;

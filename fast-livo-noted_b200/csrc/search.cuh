@@ -522,6 +522,7 @@ __device__ __forceinline__ bool thread_knn5_shell(const MapView& m, float qx, fl
 // Output convention of warp_knn5: lanes 0..4 hold rank 0..4 in `out`; returns the number found.
 // ----------------------------------------------------------------------------------------------------
 constexpr int RING_MAX_CELLS = 32;   // covers the V1 search range of 24 cells (api.cu: search_bound_bits)
+constexpr int RING_SPARSE_MIN_BLOCKS = 64;   // steps with more blocks than this go through the super-block table
 
 __device__ __forceinline__ unsigned axis_bits_n(int cq, int b, int n) {
     int lo = max(cq - n, b * 4) - b * 4, hi = min(cq + n, b * 4 + 3) - b * 4;
@@ -623,13 +624,48 @@ static __device__ __noinline__ int warp_knn5_rings(const MapView m /* by value: 
         const int nb = nbx * nby * nbz;
         const double slack = ((double)qabs + (double)(n + 1) * edge) * 4.8e-7;
         int qn = 0;   // warp-uniform queue length
-        for (int base = 0; base < nb; base += 32) {
+        // Block candidates of the step, 32 at a time.  Small cubes: every block of the box, one per lane.  Wide cubes
+        // (V1's range of 24 cells: 13^3 = 2197 blocks, mostly absent where the query looks into unmapped space): the
+        // SUPER-BLOCKS of the box, one per lane (<= 125 questions), then only the blocks that exist, taken from the
+        // lanes' masks bit by bit.
+        const bool sparse = nb > RING_SPARSE_MIN_BLOCKS;
+        const int bx1 = bx0 + nbx - 1, by1 = by0 + nby - 1, bz1 = bz0 + nbz - 1;
+        const int sx0 = bx0 >> 2, sy0 = by0 >> 2, sz0 = bz0 >> 2;
+        const int nsy = (by1 >> 2) - sy0 + 1, nsz = (bz1 >> 2) - sz0 + 1;
+        const int nsb = ((bx1 >> 2) - sx0 + 1) * nsy * nsz;
+        unsigned long long smask = 0ull;   // sparse: blocks of this lane's current super-block still to visit
+        int ssx = 0, ssy = 0, ssz = 0;
+        for (int base = 0;;) {
             // stage 1: one block per lane -> directory slot and the occupancy bits of its cells in ring n
-            const int bi = base + lane;
+            int bi = -1;
             int slot = -1, bx = 0, by = 0, bz = 0;
             unsigned long long occ = 0, full = 0, bbase = NONE32;
-            if (bi < nb) {
-                bx = bx0 + bi / (nby * nbz); by = by0 + (bi / nbz) % nby; bz = bz0 + bi % nbz;
+            if (!sparse) {
+                if (base >= nb) break;
+                bi = base + lane;
+                base += 32;
+                if (bi < nb) { bx = bx0 + bi / (nby * nbz); by = by0 + (bi / nbz) % nby; bz = bz0 + bi % nbz; }
+                else bi = -1;
+            } else {
+                if (!__any_sync(FULL, smask != 0ull)) {
+                    if (base >= nsb) break;
+                    const int si = base + lane;
+                    base += 32;
+                    if (si < nsb) {
+                        ssx = sx0 + si / (nsy * nsz); ssy = sy0 + (si / nsz) % nsy; ssz = sz0 + si % nsz;
+                        const unsigned long long inbox = mask3(range_bits(bx0, bx1, ssx), range_bits(by0, by1, ssy), range_bits(bz0, bz1, ssz));
+                        smask = inbox ? (sup_find(m, ssx, ssy, ssz) & inbox) : 0ull;
+                    }
+                    continue;
+                }
+                if (smask) {
+                    const int o = __ffsll((long long)smask) - 1;
+                    smask &= smask - 1;
+                    bx = ssx * 4 + ((o >> 4) & 3); by = ssy * 4 + ((o >> 2) & 3); bz = ssz * 4 + (o & 3);
+                    bi = ((bx - bx0) * nby + (by - by0)) * nbz + (bz - bz0);
+                }
+            }
+            if (bi >= 0) {
                 const unsigned long long want = cube_bits(cqx, cqy, cqz, bx, by, bz, n) & ~cube_bits(cqx, cqy, cqz, bx, by, bz, p);
                 if (want) {
                     slot = rec_find(m, pack_block(bx, by, bz), full, bbase);

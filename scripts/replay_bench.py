@@ -42,7 +42,7 @@ def main():
     poses = [ends[0] + (ends[1] - ends[0]) * (i / a.pool) for i in range(a.pool)]
     pool = []
     for i in range(a.pool):
-        s = scenes.make_scan_torch(w, seed=5000 + i, n_points=a.scan_points, kind="avia", pos=poses[i], device="cuda")
+        s = scenes.make_down_scan_torch(w, seed=5000 + i, n_points=a.scan_points, leaf=0.3, kind="avia", pos=poses[i], device="cuda")   # feats_down_body is voxel-filtered (src/laser_mapping.cpp:129-130); leaf 0.3: the synthetic world shows only ~12 k distinct 0.5 m voxels from one pose
         pool.append({"body": s["body"].cpu().numpy(), "x_prior": np.asarray(s["x_prior"])})
     seqs = [[pool[(s + k) % a.pool] for k in range(a.frames)] for s in range(a.sequences)]
     npd = 18 if a.mode == 1 else 23

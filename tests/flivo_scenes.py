@@ -306,6 +306,32 @@ def make_scan_torch(world, seed, n_points, kind="ouster", pos=None, device="cuda
     return dict(body=body, x_true=x_true, x_prior=x_prior, P=np.eye(23) * 1e-4, kind=kind, seed=seed)
 
 
+def make_down_scan_torch(world, seed, n_points, leaf, kind="avia", pos=None, device="cuda", prior_noise=True):
+    """A scan as the node hands it over: feats_down_body, i.e. voxel-filtered at filter_size_surf (src/laser_mapping.cpp:129-130)
+    — at most one point per `leaf` voxel of the lidar frame.  Raw ray hits (make_scan_torch) are thinned to the first hit of
+    every voxel, oversampling until n_points survive; an evenly spaced subset brings the count to exactly n_points.  Without
+    this a map built from the first scan holds thousands of points per search cell next to the sensor, which no map of the
+    reference pipeline ever does."""
+    import torch
+    over = 6
+    for _ in range(6):
+        s = make_scan_torch(world, seed, n_points * over, kind=kind, pos=pos, device=device, prior_noise=prior_noise)
+        b = s["body"]
+        k = torch.floor(b.double() / leaf).long() + (1 << 20)
+        key = (k[:, 0] << 42) | (k[:, 1] << 21) | k[:, 2]
+        order = torch.sort(key, stable=True).indices
+        ks = key[order]
+        head = torch.ones(len(ks), dtype=torch.bool, device=b.device)
+        head[1:] = ks[1:] != ks[:-1]
+        first = torch.sort(order[head]).values          # first hit of every voxel, in the scan's own order
+        if len(first) >= n_points:
+            pick = first[torch.linspace(0, len(first) - 1, n_points, device=b.device).round().long()]
+            s["body"] = b[pick].contiguous()
+            return s
+        over *= 2
+    raise RuntimeError("down-sampled scan generator starved")
+
+
 def street_positions(world, count, pitch=30.0):
     """Sensor positions on street intersections of the box grid (free of buildings), nearest the origin first."""
     nb = max(int(world["extent"] // pitch), 1)
