@@ -66,9 +66,9 @@ def parse_args():
     ap.add_argument("--no-sharded", action="store_true", help="N>1 replica run: skip the `sharded` block (config 5 on the same contexts)")
     ap.add_argument("--no-mega", action="store_true", help="N>1: skip the 4 M-point / 100 M-point part of the `sharded` block")
     ap.add_argument("--no-replay", action="store_true", help="skip the `replay` block (config 4 in miniature)")
-    ap.add_argument("--replay-sequences", type=int, default=8, help="sequences PER RANK of the replay block")
-    ap.add_argument("--replay-frames", type=int, default=60)
-    ap.add_argument("--replay-concurrent", type=int, default=4)
+    ap.add_argument("--replay-sequences", type=int, default=16, help="sequences PER RANK of the replay block")
+    ap.add_argument("--replay-frames", type=int, default=120)
+    ap.add_argument("--replay-concurrent", type=int, default=8)
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="sharded mode: how the per-trip 96-double records travel")
     return ap.parse_args()
 
@@ -268,17 +268,20 @@ def replay_block(args, pkg, rank, world_size, local_rank, dev, barrier):
     # a drive along a street: consecutive frames about 2 m apart (a sequence starts anywhere on the loop and wraps around)
     ends = scenes.street_positions(w, 2)
     poses = [ends[0] + (ends[1] - ends[0]) * (i / pool_n) for i in range(pool_n)]
-    pool = []
-    for i in range(pool_n):
-        s = scenes.make_down_scan_torch(w, seed=5000 + i, n_points=24_000, leaf=0.3, kind="avia", pos=poses[i], device=dev)   # feats_down_body is voxel-filtered (src/laser_mapping.cpp:129-130); leaf 0.3: the synthetic world shows only ~12 k distinct 0.5 m voxels from one pose
-        pool.append({"body": s["body"].cpu().numpy(), "x_prior": np.asarray(s["x_prior"])})
+    # feats_down_body is voxel-filtered (src/laser_mapping.cpp:129-130); leaf 0.3: the synthetic world shows only ~12 k distinct 0.5 m voxels from one pose
+    pool = [{"body": s["body"].cpu().numpy(), "x_prior": np.asarray(s["x_prior"])}
+            for s in scenes.make_replay_pool(w, poses, n_points=24_000, leaf=0.3, kind="avia", device=dev)]
     del w
     seqs = [[pool[(s + k) % pool_n] for k in range(n_frames)] for s in range(n_seq)]
     P18, cfg1 = np.eye(18) * 1e-4, pkg.make_cfg(mode=pkg.MODE_V1, max_iter=MAX_ITER, laser_point_cov=LASER_POINT_COV)
     sh.replay_sequences(pkg, [s[:6] for s in seqs[:world_size]], rank, world_size, P18, cfg1, ds=0.5, device=local_rank)   # warm-up
     barrier()
     t0 = time.perf_counter()
-    r = sh.replay_sequences(pkg, seqs, rank, world_size, P18, cfg1, ds=0.5, device=local_rank, concurrent=args.replay_concurrent)
+    # sequences in flight per rank: every driving thread spins in cudaStreamSynchronize while its frame runs, so never more of
+    # them than this rank's share of the host cores (N = 8 on a 32-core host: 4; measured with 8: 1300 frames/s per GPU
+    # against 4400 at N = 1)
+    conc = max(1, min(args.replay_concurrent, len(os.sched_getaffinity(0)) // max(1, world_size)))
+    r = sh.replay_sequences(pkg, seqs, rank, world_size, P18, cfg1, ds=0.5, device=local_rank, concurrent=conc)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     t = torch.tensor([dt, float(sum(v["work"] for v in r.values())), float(sum(v["updates"] for v in r.values())),
@@ -290,8 +293,8 @@ def replay_block(args, pkg, rank, world_size, local_rank, dev, barrier):
         dt, work, upd, busy = float(mx[0]), float(sm[1]), float(sm[2]), float(sm[3])
     else:
         dt, work, upd, busy = (float(v) for v in t)
-    return {"workload": "config 4 in miniature: %d sequences x %d frames of 24 k points, V1, map grown from the first scan" % (n_seq, n_frames),
-            "sequences": n_seq, "frames_per_sequence": n_frames, "concurrent_per_rank": args.replay_concurrent,
+    return {"workload": "config 4 in miniature: %d sequences x %d frames of 24 k voxel-filtered points (feats_down_body), V1, map grown from the first scan" % (n_seq, n_frames),
+            "sequences": n_seq, "frames_per_sequence": n_frames, "concurrent_per_rank": conc,
             "points_per_sec": work / dt, "frames_per_sec": upd / dt, "ms_per_frame_per_rank": 1e3 * dt * world_size / max(upd, 1.0),
             "update_device_ms_mean": busy / max(upd, 1.0), "gpu_busy_updates": busy * 1e-3 / (dt * world_size),
             "note": "wall clock through the public API, host scans, per-sequence context create / destroy included; no collective"}
@@ -557,6 +560,11 @@ def run_flivo(args, rank, world_size, local_rank):
     P_out = np.zeros_like(P_in)
     x_out, rep_out = pkg.State(), pkg.Report()
     ptrs = [(C.c_void_p(h.ctypes.data), h.shape[0]) for h in host_scans]
+    # the node's scan buffers registered once (cudaHostRegister through the ABI): the contract's "pinned host memory".  With
+    # many host threads to itself the library still repacks the 48-byte records to float4 (a third of the PCIe bytes);
+    # with few (8 ranks on one host) it sends the pinned records as they are.
+    for h in host_scans:
+        F._ck(L.flivo_host_register(C.c_void_p(h.ctypes.data), h.nbytes))
     hctx, p_in, p_out = F.h, C.c_void_p(P_in.ctypes.data), C.c_void_p(P_out.ctypes.data)
     ref_cfg, ref_x, ref_rep = C.byref(cfg), C.byref(x_out), C.byref(rep_out)
     ref_states = [C.byref(s) for s in states]
@@ -726,9 +734,14 @@ def run_flivo(args, rank, world_size, local_rank):
                            "trips_sharded": int(reps.trips), "trips_single": int(rep1.trips)}
             del F1
         barrier()
-    h2d = int(pts_per_scan * 16 + 36 * 8 + npd * npd * 8 + 512)   # xyz as float4 (repacked from the 48-byte records on the host) + the job / state / P block
+    # xyz as float4 (repacked from the 48-byte records on the host) — or the pinned 48-byte records as they are when the process
+    # has few host threads to itself (the library's rule, flivo_scan_upload_async) — + the job / state / P block
+    raw_env = os.environ.get("FLIVO_RAW_DMA")
+    nt_host = int(os.environ.get("FLIVO_HOST_THREADS") or min(16, max(1, len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))))
+    raw_dma = (raw_env == "1") or (raw_env is None and nt_host <= 4 and pts_per_scan >= 65536)
+    h2d = int(pts_per_scan * (48 if raw_dma else 16) + 36 * 8 + npd * npd * 8 + 512)
     d2h = int(36 * 8 + npd * npd * 8 + 512)
-    return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, launches=launches, clocks=clocks,
+    return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, raw_dma=raw_dma, nt_host=nt_host, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
                 trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add, ivox=ivox,
@@ -847,7 +860,8 @@ def main():
                                           "host_recorded_events_mean": r["host_ev_ms_mean"],
                                           "note": "per-step device times of rank 0 over the timed steps (in-graph event nodes); host_recorded_events_mean = the same steps between events recorded from the host around the call"},
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (host repack to float4 + copy stream) during flivo_iekf_update_begin/_end of the current one",
+                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (registered host buffer; " + ("the pinned records sent as they are, copy stream" if r["raw_dma"] else "host repack to float4 + copy stream") + ") during flivo_iekf_update_begin/_end of the current one",
+                    "host_threads_per_rank": r["nt_host"],
                     "serial_value": r["e2e_serial"], "serial_how": "flivo_scan_upload (pageable buffer, host repack) then flivo_iekf_update, L2 flushed between steps"},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "sharded": r["sharded"], "replay": r["replay"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],
             "map_build_s": r["map_build_s"], "search_stats": r["search_stats"],

@@ -46,10 +46,23 @@ __device__ __forceinline__ unsigned long long make_sort_key(int kx, int ky, int 
     key = (key << 6) | (unsigned)(((kx & gm) << 4) | ((ky & gm) << 2) | (kz & gm));
     return key;
 }
-__device__ __forceinline__ void decode_sort_key(unsigned long long key, int gshift, int& kx, int& ky, int& kz) {
+// Slot-keyed flavour (bit 63 set): [directory slot of the block][cell offset:6][voxel in cell:6].  The block is named by its
+// slot in the directory instead of its coordinates, so a batch sorts on 13 + log2(dir_cap) bits (4 radix passes for a scan
+// instead of 8); the block must exist before the key is made (k_point_keys creates it), which needs the directory sized
+// beforehand — scan-sized batches only.  Both flavours keep block / cell / voxel identity at the same shifts (>> 12, >> 6).
+constexpr unsigned long long SLOT_KEY = 1ull << 63;
+__device__ __forceinline__ unsigned long long make_slot_key(int slot, int kx, int ky, int kz, int gshift) {
+    const int gm = (1 << gshift) - 1;
+    return SLOT_KEY | ((unsigned long long)(unsigned)slot << 12) | ((unsigned long long)(unsigned)cell_off(kx >> gshift, ky >> gshift, kz >> gshift) << 6) |
+           (unsigned)(((kx & gm) << 4) | ((ky & gm) << 2) | (kz & gm));
+}
+__device__ __forceinline__ void decode_sort_key(const MapView& m, unsigned long long key, int& kx, int& ky, int& kz) {
+    const int gshift = m.gshift;
     int sub = (int)(key & 63), off = (int)((key >> 6) & 63);
     unsigned long long b = key >> 12;
-    int bz = (int)(b & 0x1FFFF) - (1 << 16), by = (int)((b >> 17) & 0x1FFFF) - (1 << 16), bx = (int)((b >> 34) & 0x1FFFF) - (1 << 16);
+    int bx, by, bz;
+    if (key & SLOT_KEY) unpack_block(m.dir_keys[(uint32_t)b & m.dir_mask], bx, by, bz);
+    else { bz = (int)(b & 0x1FFFF) - (1 << 16); by = (int)((b >> 17) & 0x1FFFF) - (1 << 16); bx = (int)((b >> 34) & 0x1FFFF) - (1 << 16); }
     int cx = bx * 4 + ((off >> 4) & 3), cy = by * 4 + ((off >> 2) & 3), cz = bz * 4 + (off & 3);
     kx = (cx << gshift) | ((sub >> 4) & 3);
     ky = (cy << gshift) | ((sub >> 2) & 3);
@@ -138,7 +151,7 @@ __global__ void k_stamp_ids(const float4* __restrict__ in, float4* __restrict__ 
 }
 
 __global__ void k_point_keys(const float4* __restrict__ pts, size_t n, MapView m, unsigned long long* __restrict__ keys,
-                             unsigned int* __restrict__ idx, MapCounters* cnt, const BatchJob* job) {
+                             unsigned int* __restrict__ idx, MapCounters* cnt, const BatchJob* job, int slot_keys) {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     if (job && i >= job->n) { keys[i] = INVALID_KEY; idx[i] = (unsigned int)i; return; }   // padding, not an error
@@ -146,7 +159,15 @@ __global__ void k_point_keys(const float4* __restrict__ pts, size_t n, MapView m
     int kx, ky, kz;
     bool ok = point_ok(m, p, kx, ky, kz);
     if (!ok) atomicExch(&cnt->error, 1);
-    keys[i] = ok ? make_sort_key(kx, ky, kz, m.gshift) : INVALID_KEY;
+    unsigned long long key = INVALID_KEY;
+    if (ok && slot_keys) {
+        const int cx = kx >> m.gshift, cy = ky >> m.gshift, cz = kz >> m.gshift;
+        const int slot = dir_find_or_insert(m, pack_block(cx >> 2, cy >> 2, cz >> 2), cnt);   // (a full directory is reported through cnt->error)
+        if (slot >= 0) key = make_slot_key(slot, kx, ky, kz, m.gshift);
+    } else if (ok) {
+        key = make_sort_key(kx, ky, kz, m.gshift);
+    }
+    keys[i] = key;
     idx[i] = (unsigned int)i;
 }
 
@@ -182,7 +203,7 @@ __global__ void k_cells_mark(const unsigned long long* __restrict__ keys, size_t
     if (key == INVALID_KEY) return;
     if (i != 0 && (key >> 6) == (keys[i - 1] >> 6)) return;
     int kx, ky, kz;
-    decode_sort_key(key, m.gshift, kx, ky, kz);
+    decode_sort_key(m, key, kx, ky, kz);
     int cx = kx >> m.gshift, cy = ky >> m.gshift, cz = kz >> m.gshift;
     int slot = dir_find_or_insert(m, pack_block(cx >> 2, cy >> 2, cz >> 2), cnt);
     if (slot < 0) return;
@@ -208,7 +229,7 @@ __global__ void k_cells_create(const unsigned long long* __restrict__ keys, size
     if (key == INVALID_KEY) return;
     if (i != 0 && (key >> 6) == (keys[i - 1] >> 6)) return;
     int kx, ky, kz;
-    decode_sort_key(key, m.gshift, kx, ky, kz);
+    decode_sort_key(m, key, kx, ky, kz);
     int cx = kx >> m.gshift, cy = ky >> m.gshift, cz = kz >> m.gshift;
     int slot = dir_find_rw(m, pack_block(cx >> 2, cy >> 2, cz >> 2));
     if (slot < 0) return;
@@ -275,7 +296,7 @@ __global__ void k_block_records(const unsigned long long* __restrict__ keys, siz
     if (key == INVALID_KEY) return;
     if (i != 0 && (key >> 12) == (keys[i - 1] >> 12)) return;
     int kx, ky, kz;
-    decode_sort_key(key, m.gshift, kx, ky, kz);
+    decode_sort_key(m, key, kx, ky, kz);
     int slot = dir_find_rw(m, pack_block((kx >> m.gshift) >> 2, (ky >> m.gshift) >> 2, (kz >> m.gshift) >> 2));
     if (slot >= 0) write_record(m, rec, (uint32_t)slot);
 }
@@ -338,7 +359,7 @@ __global__ void k_ds_decide(const unsigned long long* __restrict__ keys, const u
     if (key == INVALID_KEY || (i != 0 && key == keys[i - 1])) { seg[i] = si; return; }
     si.flags = 1;
     int kx, ky, kz;
-    decode_sort_key(key, m.gshift, kx, ky, kz);
+    decode_sort_key(m, key, kx, ky, kz);
     const float ds = m.ds;
     VoxBox box = make_box(kx, ky, kz, ds);
     unsigned int nslop = misc[2];
@@ -441,7 +462,7 @@ __global__ void k_ds_clear(const unsigned long long* __restrict__ keys, size_t n
     SegInfo si = seg[i];
     if ((si.flags & 7) != 5) return;  // head, not deferred, changed
     int kx, ky, kz;
-    decode_sort_key(keys[i], m.gshift, kx, ky, kz);
+    decode_sort_key(m, keys[i], kx, ky, kz);
     VoxBox box = make_box(kx, ky, kz, m.ds);
     uint32_t b = cell_bucket_rw(m, kx >> m.gshift, ky >> m.gshift, kz >> m.gshift);
     int cleared = 0;
@@ -469,7 +490,7 @@ __global__ void k_ds_store(const unsigned long long* __restrict__ keys, size_t n
     SegInfo si = seg[i];
     if ((si.flags & 7) != 5 || si.new_idx < 0) return;
     int kx, ky, kz;
-    decode_sort_key(keys[i], m.gshift, kx, ky, kz);
+    decode_sort_key(m, keys[i], kx, ky, kz);
     uint32_t b = cell_bucket_rw(m, kx >> m.gshift, ky >> m.gshift, kz >> m.gshift);
     if (b == NONE32) { atomicExch(&cnt->error, 3); return; }
     if (claim_slot(m, b, pts[si.new_idx], cnt, true)) atomicAdd(&cnt->live, 1ull);
@@ -969,7 +990,7 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
     // sizing: exact unique counts for large batches (one extra sync), conservative bound otherwise
     size_t new_blocks = n, new_cells = n;
     if (n > ADD_GRAPH_MAX) {
-        k_point_keys<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, keys_a_, idx_a_, d_cnt_, nullptr);
+        k_point_keys<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, keys_a_, idx_a_, d_cnt_, nullptr, 0);
         CK(cudaGetLastError());
         size_t tmp = cub_tmp_bytes_;
         CK(cub::DeviceRadixSort::SortPairs(cub_tmp_, tmp, keys_a_, keys_b_, idx_a_, idx_b_, (int)n, 0, 63, stream_));
@@ -995,10 +1016,15 @@ int MapStore::insert_batch(const float4* d_pts_id, size_t n, bool downsample_on,
 int MapStore::enqueue_insert(const float4* d_pts_id, size_t n, bool downsample_on, const BatchJob* job, bool keys_sorted, std::string& err) {
     const int T = 256;
     size_t tmp = cub_tmp_bytes_;
-    if (!keys_sorted) {   // (a large batch was keyed and sorted by the caller already, to size the tables)
-        k_point_keys<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, keys_a_, idx_a_, d_cnt_, job);
+    if (!keys_sorted) {   // (a large batch was keyed by coordinates and sorted by the caller already, to size the tables)
+        // scan-sized batch: the directory has room for every block it can create (ensure_capacity ran), so the keys name blocks
+        // by directory slot and the sort covers 13 + log2(dir_cap) bits (the top one puts the padding's invalid keys last)
+        static const bool slot_on = !(getenv("FLIVO_SLOT_KEYS") && atoi(getenv("FLIVO_SLOT_KEYS")) == 0);
+        int end_bit = 63;
+        if (slot_on) { end_bit = 13; for (size_t c = dir_cap_; c > 1; c >>= 1) ++end_bit; }
+        k_point_keys<<<nblk(n, T), T, 0, stream_>>>(d_pts_id, n, v_, keys_a_, idx_a_, d_cnt_, job, slot_on ? 1 : 0);
         CK(cudaGetLastError());
-        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_, tmp, keys_a_, keys_b_, idx_a_, idx_b_, (int)n, 0, 63, stream_));
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_, tmp, keys_a_, keys_b_, idx_a_, idx_b_, (int)n, 0, end_bit, stream_));
     }
     CK(cudaMemsetAsync(d_misc_, 0, 16 * sizeof(unsigned int), stream_));
     // cells of the batch (new ones get consecutive buckets in key order), then the search records of the touched blocks;

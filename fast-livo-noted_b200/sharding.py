@@ -83,15 +83,22 @@ def _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_rat
     Stated deviation from src/laser_mapping.cpp:134-142: the reference starts at the identity pose and builds its first map
     from feats_down_body as it is; a replayed synthetic sequence starts at a known pose of a larger world, so the first
     scan is placed with that pose (LaserMapping::Run of host/laser_mapping.h follows the reference)."""
+    import os
+    import sys
+    import time
+    trace = os.environ.get("FLIVO_REPLAY_TRACE")     # per-sequence wall-clock phases on stderr
+    t0 = time.perf_counter()
     with pkg.Flivo(device=device, downsample_size=ds, cell_ratio=cell_ratio, initial_points=initial_points, sort_scan=sort_scan) as F:
         res = dict(x=None, map_points=0, updates=0, trips=0, work=0, added=[], device_ms=0.0)
         frames = sequences[s]
         bodies = [np.ascontiguousarray(fr["body"], dtype=np.float32) for fr in frames]
+        t1 = time.perf_counter()
         F.scan_upload(bodies[0])
         w = F.h_share_model(pkg.State.from_array(frames[0]["x_prior"]), mode=cfg.mode, do_search=True, want=("world",))["world"]
         F.Build(w)
         if len(frames) > 1:
             F.scan_upload_async(bodies[1])
+        t2 = time.perf_counter()
         for k in range(1, len(frames)):
             # flivo_frame: commit, update, stage the next scan while the update runs, map_incremental — one call
             x, _, rep, n_add = F.frame(pkg.State.from_array(frames[k]["x_prior"]), P0, cfg, bodies[k + 1] if k + 1 < len(frames) else None)
@@ -101,5 +108,10 @@ def _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_rat
             res["work"] += rep.trips * len(bodies[k])
             res["device_ms"] += getattr(rep, "gpu_ms", 0.0)
             res["x"] = x.as_array()
+        t3 = time.perf_counter()
         res["map_points"] = F.size()
+    if trace:
+        t4 = time.perf_counter()
+        print("[replay trace] seq %d: start %.3f s, create %.1f ms, first scan + Build %.1f ms, %d frames %.1f ms, close %.1f ms"
+              % (s, t0, 1e3 * (t1 - t0), 1e3 * (t2 - t1), len(frames) - 1, 1e3 * (t3 - t2), 1e3 * (t4 - t3)), file=sys.stderr)
     return res

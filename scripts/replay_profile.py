@@ -27,10 +27,9 @@ def main():
     w = scenes.make_world_torch(seed=1, n_points=1000000, ds=0.5, device="cuda")
     ends = scenes.street_positions(w, 2)
     poses = [ends[0] + (ends[1] - ends[0]) * (i / a.pool) for i in range(a.pool)]
-    pool = []
-    for i in range(a.pool):
-        s = scenes.make_down_scan_torch(w, seed=5000 + i, n_points=a.scan_points, leaf=0.3, kind="avia", pos=poses[i], device="cuda")   # feats_down_body is voxel-filtered (src/laser_mapping.cpp:129-130); leaf 0.3: the synthetic world shows only ~12 k distinct 0.5 m voxels from one pose
-        pool.append({"body": s["body"].cpu().numpy(), "x_prior": np.asarray(s["x_prior"])})
+    # feats_down_body is voxel-filtered (src/laser_mapping.cpp:129-130); leaf 0.3: the synthetic world shows only ~12 k distinct 0.5 m voxels from one pose
+    pool = [{"body": s["body"].cpu().numpy(), "x_prior": np.asarray(s["x_prior"])}
+            for s in scenes.make_replay_pool(w, poses, n_points=a.scan_points, leaf=0.3, kind="avia", device="cuda")]
     frames = [pool[k % a.pool] for k in range(a.frames)]
     npd = 18 if a.mode == 1 else 23
     P0 = np.eye(npd) * 1e-4

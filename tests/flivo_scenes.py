@@ -306,17 +306,17 @@ def make_scan_torch(world, seed, n_points, kind="ouster", pos=None, device="cuda
     return dict(body=body, x_true=x_true, x_prior=x_prior, P=np.eye(23) * 1e-4, kind=kind, seed=seed)
 
 
-def make_down_scan_torch(world, seed, n_points, leaf, kind="avia", pos=None, device="cuda", prior_noise=True):
+def make_down_scan_torch(world, seed, n_points, leaf, kind="avia", pos=None, device="cuda", prior_noise=True, oversample=48):
     """A scan as the node hands it over: feats_down_body, i.e. voxel-filtered at filter_size_surf (src/laser_mapping.cpp:129-130)
-    — at most one point per `leaf` voxel of the lidar frame.  Raw ray hits (make_scan_torch) are thinned to the first hit of
-    every voxel, oversampling until n_points survive; an evenly spaced subset brings the count to exactly n_points.  Without
-    this a map built from the first scan holds thousands of points per search cell next to the sensor, which no map of the
-    reference pipeline ever does."""
+    — at most one point per voxel of the lidar frame.  oversample x n_points raw ray hits (make_scan_torch) are thinned to
+    the first hit of every `leaf` voxel; where a pose does not show n_points distinct voxels the leaf shrinks by 15 % until
+    it does (the leaf used is returned as s["leaf"]); an evenly spaced subset brings the count to exactly n_points.
+    Without this a map built from the first scan holds thousands of points per search cell next to the sensor, which no
+    map of the reference pipeline ever does."""
     import torch
-    over = 6
-    for _ in range(6):
-        s = make_scan_torch(world, seed, n_points * over, kind=kind, pos=pos, device=device, prior_noise=prior_noise)
-        b = s["body"]
+    s = make_scan_torch(world, seed, n_points * oversample, kind=kind, pos=pos, device=device, prior_noise=prior_noise)
+    b = s["body"]
+    for _ in range(40):
         k = torch.floor(b.double() / leaf).long() + (1 << 20)
         key = (k[:, 0] << 42) | (k[:, 1] << 21) | k[:, 2]
         order = torch.sort(key, stable=True).indices
@@ -327,9 +327,27 @@ def make_down_scan_torch(world, seed, n_points, leaf, kind="avia", pos=None, dev
         if len(first) >= n_points:
             pick = first[torch.linspace(0, len(first) - 1, n_points, device=b.device).round().long()]
             s["body"] = b[pick].contiguous()
+            s["leaf"] = leaf
             return s
-        over *= 2
+        leaf *= 0.85
     raise RuntimeError("down-sampled scan generator starved")
+
+
+def make_replay_pool(world, poses, n_points, leaf, kind="avia", device="cuda", seed0=5000, tries=8):
+    """One voxel-filtered scan per pose (make_down_scan_torch).  The heading of a synthetic scan is drawn from its seed; a
+    heading that faces a nearby wall does not show n_points distinct voxels, so up to `tries` seeds are tried per pose and
+    the scan that kept the largest leaf is taken (first one that keeps >= 80 % of the requested leaf)."""
+    pool = []
+    for i, pos in enumerate(poses):
+        best = None
+        for t in range(tries):
+            s = make_down_scan_torch(world, seed=seed0 + i + 1000 * t, n_points=n_points, leaf=leaf, kind=kind, pos=pos, device=device)
+            if best is None or s["leaf"] > best["leaf"]:
+                best = s
+            if s["leaf"] >= 0.8 * leaf:
+                break
+        pool.append(best)
+    return pool
 
 
 def street_positions(world, count, pitch=30.0):
