@@ -862,12 +862,11 @@ extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, si
     // at N = 8: 1.13 ms per pipelined step against 0.48 ms of update — and pinned wide records travel as they are
     // (FLIVO_RAW_DMA=1 / 0 forces / forbids it).
     static const int raw_mode = getenv("FLIVO_RAW_DMA") ? atoi(getenv("FLIVO_RAW_DMA")) : -1;
-    const bool raw_ok = raw_mode == 1 || raw_mode == 2 || (raw_mode < 0 && host_threads() <= 4 && n >= 65536);
+    // (Letting the copy engine gather the xyz itself — a 2-D copy of 12-byte rows at the record pitch — was measured too: 1.2 G
+    // points/s pipelined at N = 1 against 2.07 G for the repack and 1.52 G for the raw records; profiles/r2_ab_upload.txt.)
+    const bool raw_ok = raw_mode == 1 || (raw_mode < 0 && host_threads() <= 4 && n >= 65536);
     const bool pinned = (stride_bytes <= 16 || raw_ok) && host_pinned(body_xyz);
-    // (experiment, FLIVO_RAW_DMA=2: the copy engine gathers the xyz of every record itself — a 2-D copy of 12-byte rows at the
-    // record pitch into packed xyz)
-    const bool gather2d = pinned && raw_mode == 2 && stride_bytes > 16;
-    const size_t stride = gather2d ? 12 : (pinned ? stride_bytes : 16), bytes = n * stride;
+    const size_t stride = pinned ? stride_bytes : 16, bytes = n * stride;
     if (sl.copy_pending) { CKC(cudaEventSynchronize(sl.copied)); sl.copy_pending = false; }
     if (bytes > sl.d_bytes) {
         CKC(cudaEventSynchronize(sl.consumed));                 // (no-op for a never recorded event)
@@ -877,9 +876,7 @@ extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, si
         sl.d_bytes = cap;
     }
     CKC(cudaStreamWaitEvent(ctx->copy, sl.consumed, 0));        // the staging that read this slot's previous content has run
-    if (gather2d) {
-        CKC(cudaMemcpy2DAsync(sl.d_in, 12, body_xyz, stride_bytes, 12, n, cudaMemcpyHostToDevice, ctx->copy));
-    } else if (pinned) {
+    if (pinned) {
         CKC(cudaMemcpyAsync(sl.d_in, body_xyz, bytes, cudaMemcpyHostToDevice, ctx->copy));
     } else {
         if (n > sl.h_n) {

@@ -460,7 +460,10 @@ __device__ __forceinline__ void store_plane(const FusedParams& P, int i, const f
 }
 
 constexpr double IVOX_MAX_RANGE_SQ = 25.0;   // max_range = 5.0 default of GetClosestPoint (ivox3d.h:79), squared in double (ivox3d_node.hpp:162)
-constexpr int SEARCH_THREADS = 128;
+#ifndef FLIVO_SEARCH_THREADS
+#define FLIVO_SEARCH_THREADS 128   // points per tile = threads per CTA (64 measured: profiles/r2_ab_search.txt)
+#endif
+constexpr int SEARCH_THREADS = FLIVO_SEARCH_THREADS;
 constexpr int SEARCH_WARPS = SEARCH_THREADS / 32;
 // register budget of k_search: 5 CTAs/SM = 96 registers (68 B of spills); 6 (80 registers, 140 B) and 4 (116, none) measured
 // 1-2 % slower, 7 (72 registers, 112 B) 4 % slower (profiles/r1_ab_launch_structure.txt)
