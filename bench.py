@@ -277,10 +277,10 @@ def replay_block(args, pkg, rank, world_size, local_rank, dev, barrier):
     sh.replay_sequences(pkg, [s[:6] for s in seqs[:world_size]], rank, world_size, P18, cfg1, ds=0.5, device=local_rank)   # warm-up
     barrier()
     t0 = time.perf_counter()
-    # sequences in flight per rank: every driving thread spins in cudaStreamSynchronize while its frame runs, so never more of
-    # them than this rank's share of the host cores (N = 8 on a 32-core host: 4; measured with 8: 1300 frames/s per GPU
-    # against 4400 at N = 1)
-    conc = max(1, min(args.replay_concurrent, len(os.sched_getaffinity(0)) // max(1, world_size)))
+    # sequences in flight per rank.  (At N = 8 on one 32-core host the replay is host-bound either way: 8 in flight per rank
+    # 10.6 k frames/s over the eight GPUs, 4 in flight 9.4 k, against 4.4 k on ONE GPU alone — every driving thread spins in
+    # cudaStreamSynchronize while its frame runs.)
+    conc = max(1, args.replay_concurrent)
     r = sh.replay_sequences(pkg, seqs, rank, world_size, P18, cfg1, ds=0.5, device=local_rank, concurrent=conc)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
