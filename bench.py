@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--shard-scan", action="store_true", help="N>1: shard ONE scan over the ranks (config 5) for the whole run")
     ap.add_argument("--no-sharded", action="store_true", help="N>1 replica run: skip the `sharded` block (config 5 on the same contexts)")
     ap.add_argument("--no-mega", action="store_true", help="N>1: skip the 4 M-point / 100 M-point part of the `sharded` block")
+    ap.add_argument("--host-mem", choices=["registered", "pinned", "pageable"], default="registered",
+                    help="where the e2e loop's host scans live: the node's own buffers registered with cudaHostRegister (default), "
+                         "cudaHostAlloc memory (torch pin_memory), or plain pageable memory")
     ap.add_argument("--no-replay", action="store_true", help="skip the `replay` block (config 4 in miniature)")
     ap.add_argument("--replay-sequences", type=int, default=16, help="sequences PER RANK of the replay block")
     ap.add_argument("--replay-frames", type=int, default=120)
@@ -436,12 +439,17 @@ def run_flivo(args, rank, world_size, local_rank):
             s["body_full"] = s["body"]
             s["body"] = s["body"][lo:hi].contiguous()
     # device-resident scans (float4) and the reference-layout host copies (48-byte PointXYZINormal AoS) for e2e
-    dev_scans, host_scans, host_xyz = [], [], []
+    dev_scans, host_scans, host_xyz, pinned_keep = [], [], [], []
     for s in scans:
         b4 = torch.zeros((len(s["body"]), 4), dtype=torch.float32, device=dev)
         b4[:, :3] = s["body"]
         dev_scans.append(b4)
-        h = np.zeros((len(s["body"]), 12), np.float32)
+        if args.host_mem == "pinned":
+            hp = torch.zeros((len(s["body"]), 12), dtype=torch.float32).pin_memory()
+            pinned_keep.append(hp)
+            h = hp.numpy()
+        else:
+            h = np.zeros((len(s["body"]), 12), np.float32)
         h[:, :3] = s["body"].cpu().numpy()
         host_scans.append(h)
         host_xyz.append(np.ascontiguousarray(h[:, :3]))
@@ -563,8 +571,9 @@ def run_flivo(args, rank, world_size, local_rank):
     # the node's scan buffers registered once (cudaHostRegister through the ABI): the contract's "pinned host memory".  With
     # many host threads to itself the library still repacks the 48-byte records to float4 (a third of the PCIe bytes);
     # with few (8 ranks on one host) it sends the pinned records as they are.
-    for h in host_scans:
-        F._ck(L.flivo_host_register(C.c_void_p(h.ctypes.data), h.nbytes))
+    if args.host_mem == "registered":
+        for h in host_scans:
+            F._ck(L.flivo_host_register(C.c_void_p(h.ctypes.data), h.nbytes))
     hctx, p_in, p_out = F.h, C.c_void_p(P_in.ctypes.data), C.c_void_p(P_out.ctypes.data)
     ref_cfg, ref_x, ref_rep = C.byref(cfg), C.byref(x_out), C.byref(rep_out)
     ref_states = [C.byref(s) for s in states]
@@ -738,10 +747,10 @@ def run_flivo(args, rank, world_size, local_rank):
     # has few host threads to itself (the library's rule, flivo_scan_upload_async) — + the job / state / P block
     raw_env = os.environ.get("FLIVO_RAW_DMA")
     nt_host = int(os.environ.get("FLIVO_HOST_THREADS") or min(16, max(1, len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))))
-    raw_dma = (raw_env == "1") or (raw_env is None and nt_host <= 4 and pts_per_scan >= 65536)
+    raw_dma = args.host_mem != "pageable" and ((raw_env == "1") or (raw_env is None and nt_host <= 4 and pts_per_scan >= 65536))
     h2d = int(pts_per_scan * (48 if raw_dma else 16) + 36 * 8 + npd * npd * 8 + 512)
     d2h = int(36 * 8 + npd * npd * 8 + 512)
-    return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, raw_dma=raw_dma, nt_host=nt_host, launches=launches, clocks=clocks,
+    return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, raw_dma=raw_dma, nt_host=nt_host, host_mem=args.host_mem, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
                 trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add, ivox=ivox,
@@ -860,7 +869,7 @@ def main():
                                           "host_recorded_events_mean": r["host_ev_ms_mean"],
                                           "note": "per-step device times of rank 0 over the timed steps (in-graph event nodes); host_recorded_events_mean = the same steps between events recorded from the host around the call"},
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (registered host buffer; " + ("the pinned records sent as they are, copy stream" if r["raw_dma"] else "host repack to float4 + copy stream") + ") during flivo_iekf_update_begin/_end of the current one",
+                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (" + r["host_mem"] + " host buffer; " + ("the pinned records sent as they are, copy stream" if r["raw_dma"] else "host repack to float4 + copy stream") + ") during flivo_iekf_update_begin/_end of the current one",
                     "host_threads_per_rank": r["nt_host"],
                     "serial_value": r["e2e_serial"], "serial_how": "flivo_scan_upload (pageable buffer, host repack) then flivo_iekf_update, L2 flushed between steps"},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "sharded": r["sharded"], "replay": r["replay"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],

@@ -674,7 +674,7 @@ __global__ void __launch_bounds__(SEARCH_THREADS, IVOX ? 6 : SEARCH_CTAS_PER_SM)
             unsigned long long* G = P.search_stamps + (size_t)4096 * 4;
             atomicAdd(G + 0, tq1 - tq0); atomicAdd(G + 1, 1ull); atomicAdd(G + 2, (unsigned long long)(dbg >> 8));
             atomicAdd(G + 3 + min(dbg & 255, 12), 1ull);
-            atomicAdd(G + 16 + min(seed_cnt, 5), 1ull);
+            atomicAdd(G + 16 + min(max(seed_cnt, 0), 5), 1ull);
             atomicMax(G + 22, tq1 - tq0);
             atomicAdd(G + 23 + min(dbg & 255, 8), tq1 - tq0);   // duration by final radius
         }
