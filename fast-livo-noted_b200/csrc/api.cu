@@ -120,7 +120,6 @@ struct flivo_ctx {
     unsigned int* d_perm = nullptr; // processing index -> caller's index
     unsigned long long *d_skey_a = nullptr, *d_skey_b = nullptr;
     unsigned int* d_sidx_a = nullptr;
-    unsigned int* d_stage_ticket = nullptr;   // CTA tickets of the staging sort (stage.cu), zero between launches
     int stage_launches = 0;                   // own kernels the last staging sequence launched
     void* d_cub = nullptr;
     size_t cub_bytes = 0;
@@ -407,7 +406,6 @@ static void free_scan(flivo_ctx* ctx) {
     if (ctx->sort_exec) { cudaGraphExecDestroy(ctx->sort_exec); ctx->sort_exec = nullptr; ctx->sort_npad = 0; }   // holds the old pointers
     cudaFree(ctx->d_body_own);
     cudaFree(ctx->d_body_in); cudaFree(ctx->d_perm); cudaFree(ctx->d_skey_a); cudaFree(ctx->d_skey_b); cudaFree(ctx->d_sidx_a);
-    cudaFree(ctx->d_stage_ticket); ctx->d_stage_ticket = nullptr;
     cudaFree(ctx->d_cub); cudaFree(ctx->d_near); cudaFree(ctx->d_near_meta); cudaFree(ctx->d_sel); cudaFree(ctx->d_eff);
     cudaFree(ctx->d_normvec); cudaFree(ctx->d_world); cudaFree(ctx->d_partials); cudaFree(ctx->d_gpartials); cudaFree(ctx->d_group_cnt); cudaFree(ctx->d_far_list); cudaFree(ctx->d_plane); cudaFree(ctx->d_pflags);
     ctx->d_body = ctx->d_body_own = ctx->d_body_in = nullptr; ctx->d_perm = nullptr; ctx->d_skey_a = ctx->d_skey_b = nullptr; ctx->d_sidx_a = nullptr;
@@ -691,8 +689,6 @@ static int ensure_scan(flivo_ctx* ctx, size_t n) {
         CKC(cudaMalloc(&ctx->d_skey_a, cap * sizeof(unsigned long long)));
         CKC(cudaMalloc(&ctx->d_skey_b, cap * sizeof(unsigned long long)));
         CKC(cudaMalloc(&ctx->d_sidx_a, cap * sizeof(unsigned int)));
-        CKC(cudaMalloc(&ctx->d_stage_ticket, 2 * sizeof(unsigned int)));
-        CKC(cudaMemsetAsync(ctx->d_stage_ticket, 0, 2 * sizeof(unsigned int), ctx->stream));
         size_t b = 0;
         cub::DeviceRadixSort::SortPairs(nullptr, b, ctx->d_skey_a, ctx->d_skey_b, ctx->d_sidx_a, ctx->d_perm, (int)cap, 0, 63, ctx->stream);
         ctx->cub_bytes = b + 256;
@@ -755,9 +751,9 @@ static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
         // far-apart regions, which costs less than a third radix pass (0.5257 vs 0.5279 ms per 260 k-point update, 0.325 vs
         // 0.334 at 24 k points; dropping fine bits instead — 9..25 — loses 8 us of search time).  FLIVO_SORT_BITS=lo,hi
         // overrides.  Two implementations of the same stable sort (identical permutation): the own three-kernel sort of
-        // stage.cu for scans up to STAGE_OWN_MAX points, where it is faster (24 k points: step 0.266 vs 0.276 ms), and the
-        // library's onesweep radix sort above that, where its decoupled look-back beats the own kernels' histogram scans
-        // (260 k points: 0.472 vs 0.492 ms) — profiles/r2_ab_stage_sort.txt.  FLIVO_SORT=own|cub forces one of them;
+        // stage.cu for scans up to STAGE_OWN_MAX points — no library kernel on the step, and faster (step time own / library:
+        // 24 k points 0.244 / 0.262 ms, 100 k 0.337 / 0.351, 260 k 0.470 / 0.479) — and the library's onesweep radix sort
+        // above that (4 M points: 3.22 / 3.10 ms) — profiles/r2_ab_stage_sort.txt.  FLIVO_SORT=own|cub forces one of them;
         // a key width other than 16 bits always takes the library sort.
         static int sb0 = -1, sb1 = -1, sort_mode = 0;   // 0: by size, 1: own, 2: library
         if (sb0 < 0) {
@@ -767,7 +763,7 @@ static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
             sort_mode = (sb1 - sb0 != 16) ? 2 : (m && !strcmp(m, "cub")) ? 2 : (m && !strcmp(m, "own")) ? 1 : 0;
         }
         const unsigned n_pad = sort ? (unsigned)(((n + SCAN_PAD - 1) / SCAN_PAD) * SCAN_PAD) : (unsigned)n;
-        constexpr unsigned STAGE_OWN_MAX = 65536;
+        constexpr unsigned STAGE_OWN_MAX = 1u << 20;
         const bool own_sort = sort_mode == 1 || (sort_mode == 0 && n_pad <= STAGE_OWN_MAX);
         if (ctx->sjob_pending) { CKC(cudaEventSynchronize(ctx->sjob_ev)); ctx->sjob_pending = false; }
         ScanJob* J = ctx->h_sjob;
@@ -788,7 +784,6 @@ static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
                     W.key16 = reinterpret_cast<unsigned short*>(ctx->d_skey_a);
                     W.order1 = ctx->d_sidx_a;
                     W.hist = reinterpret_cast<unsigned int*>(ctx->d_skey_b);
-                    W.ticket = ctx->d_stage_ticket;
                     if (stage_hist_bytes(n_pad) > (size_t)n_pad * sizeof(unsigned long long)) ce = cudaErrorInvalidValue;
                     if (ce == cudaSuccess) launch_stage_sort(ctx->d_sjob, n_pad, ctx->d_body_in, ctx->d_body_own, ctx->d_perm, ctx->d_sel, ctx->d_eff, ctx->d_pflags, W, s);
                 } else {

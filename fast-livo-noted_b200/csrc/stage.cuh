@@ -53,8 +53,7 @@ __device__ __forceinline__ float4 scan_record(const ScanJob* J, size_t i) {
 struct StageWork {
     unsigned short* key16;   // [cap] sort key per point, caller's order
     unsigned int* order1;    // [cap] caller index of the points after the first pass (sorted by the low digit)
-    unsigned int* hist;      // [2][256 * tiles] digit-major tile histograms, turned into exclusive bases in place
-    unsigned int* ticket;    // [2] CTA tickets of the two histogram scans; zero between launches
+    unsigned int* hist;      // [2][tiles][256] tile histograms of the low and of the high digit
 };
 size_t stage_hist_bytes(size_t n_pad);   // bytes `hist` needs for a scan of n_pad items
 

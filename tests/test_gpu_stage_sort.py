@@ -70,7 +70,7 @@ CASES = [("street", 1), ("street", 777), ("room", 2048), ("street", 24000), ("ro
 
 @pytest.mark.parametrize("kind,n", CASES)
 def test_processing_order_is_the_stable_sort_by_cell_key(pkg, kind, n):
-    """Default choice of implementation: the own sort up to 65536 points, the library's above."""
+    """Default choice of implementation: the own sort up to 2^20 points, the library's above."""
     _check_order(pkg, kind, n)
 
 
