@@ -22,8 +22,13 @@ def test_wide_cubes_after_growth_and_rehash(pkg, ds, ratio):
         cap0 = F.stats().dir_capacity
         first = (centres[0] + rng.uniform(-3, 3, (400, 3)) * cell).astype(np.float32)
         F.Build(first)
-        for c in centres[1:]:
+        for c in centres[1:15]:
             F.Add_Points((c + rng.uniform(-6, 6, (1500, 3)) * cell).astype(np.float32), downsample_on=True)
+        # one batch large enough that its conservative sizing outgrows the 65536-slot directory: the blocks made so far are
+        # rehashed (k_rehash marks them in the new super-block table), the rest is added afterwards
+        big = np.concatenate([c + rng.uniform(-6, 6, (2700, 3)) * cell for c in centres[15:30]]).astype(np.float32)
+        assert len(big) > 30000
+        F.Add_Points(big, downsample_on=True)
         assert F.stats().dir_capacity > cap0, "the directory never grew: the test does not cover the rehash"
         mxyz, mid = F.flatten()
         # queries 5 .. 30 cells away from an island, looking at it across empty space, and a few inside
