@@ -747,10 +747,13 @@ def run_flivo(args, rank, world_size, local_rank):
     # has few host threads to itself (the library's rule, flivo_scan_upload_async) — + the job / state / P block
     raw_env = os.environ.get("FLIVO_RAW_DMA")
     nt_host = int(os.environ.get("FLIVO_HOST_THREADS") or min(16, max(1, len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))))
-    raw_dma = args.host_mem != "pageable" and ((raw_env == "1") or (raw_env is None and nt_host <= 4 and pts_per_scan >= 65536))
-    h2d = int(pts_per_scan * (48 if raw_dma else 16) + 36 * 8 + npd * npd * 8 + 512)
+    few = raw_env is None and nt_host <= 4 and pts_per_scan >= 65536
+    raw_dma = args.host_mem != "pageable" and (raw_env in ("1", "2") or few)
+    split_pct = 0 if raw_env == "1" else min(100, max(0, int(os.environ.get("FLIVO_RAW_SPLIT", "50"))))   # per cent of a scan repacked by the host
+    bytes_per_point = (16 * split_pct + 48 * (100 - split_pct)) / 100.0 if raw_dma else 16
+    h2d = int(pts_per_scan * bytes_per_point + 36 * 8 + npd * npd * 8 + 512)
     d2h = int(36 * 8 + npd * npd * 8 + 512)
-    return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, raw_dma=raw_dma, nt_host=nt_host, host_mem=args.host_mem, launches=launches, clocks=clocks,
+    return dict(F=F, pkg=pkg, value=value, dev_ms=dev_ms, e2e=e2e_work / e2e_s, h2d=h2d, d2h=d2h, raw_dma=raw_dma, split_pct=split_pct, nt_host=nt_host, host_mem=args.host_mem, launches=launches, clocks=clocks,
                 fused_search_ms=fused_search_ms, fused_reuse_ms=fused_reuse_ms, solve_ms=solve_ms, last=last, scans=scans,
                 host_xyz=host_xyz, wxyz_host=wxyz_host, map_build_s=map_build_s, pts_per_scan=pts_per_scan,
                 trips_per_step=trips_total / args.steps, shard=shard, shard_check=shard_check, frontend=frontend, map_add=map_add, ivox=ivox,
@@ -869,7 +872,7 @@ def main():
                                           "host_recorded_events_mean": r["host_ev_ms_mean"],
                                           "note": "per-step device times of rank 0 over the timed steps (in-graph event nodes); host_recorded_events_mean = the same steps between events recorded from the host around the call"},
             "e2e": {"value": r["e2e"], "unit": "points/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (" + r["host_mem"] + " host buffer; " + ("the pinned records sent as they are, copy stream" if r["raw_dma"] else "host repack to float4 + copy stream") + ") during flivo_iekf_update_begin/_end of the current one",
+                    "how": "flivo_scan_upload_async of the next 48-byte-AoS scan (" + r["host_mem"] + " host buffer; " + (("%d %% of the scan repacked to float4 by the host, the rest of the pinned records sent as they are, both on the copy stream" % r["split_pct"]) if r["raw_dma"] else "host repack to float4 + copy stream") + ") during flivo_iekf_update_begin/_end of the current one",
                     "host_threads_per_rank": r["nt_host"],
                     "serial_value": r["e2e_serial"], "serial_how": "flivo_scan_upload (pageable buffer, host repack) then flivo_iekf_update, L2 flushed between steps"},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "cpu_baseline": cpu, "parity_check": parity, "shard_check": r["shard_check"], "sharded": r["sharded"], "replay": r["replay"], "frontend": r["frontend"], "map_add": r["map_add"], "ivox": r["ivox"],

@@ -76,6 +76,7 @@ struct ScanSlot {
     cudaEvent_t consumed = nullptr; // the staging sequence that reads d_in has run (context stream)
     bool copy_pending = false, filled = false;
     size_t n = 0, stride = 0;
+    size_t n_a = 0, stride_b = 0;   // split upload: records [0, n_a) are float4 at d_in, [n_a, n) raw records of stride_b behind them
 };
 
 struct flivo_ctx {
@@ -107,8 +108,8 @@ struct flivo_ctx {
     // a committed / set scan is staged (keys, sort, gather, flag reset) lazily, right before its first consumer, so that
     // the staging graph and the update graph are launched back to back from inside one call
     bool stage_todo = false;
-    const char* todo_src = nullptr;
-    size_t todo_stride = 0;
+    const char* todo_src = nullptr, *todo_src_b = nullptr;
+    size_t todo_stride = 0, todo_stride_b = 0, todo_n_a = 0;
     int todo_slot = -1;
     cudaEvent_t ev_stage0 = nullptr, ev_upd0 = nullptr, ev_upd1 = nullptr;   // in-graph time stamps (external event nodes)
     // an update launched by flivo_iekf_update_begin and not yet collected by flivo_iekf_update_end
@@ -724,6 +725,7 @@ static int finish_scan(flivo_ctx* ctx, const char* src, size_t stride, size_t n,
     ctx->scan_n = n;
     ctx->stage_todo = true;
     ctx->todo_src = src; ctx->todo_stride = stride; ctx->todo_slot = slot;
+    ctx->todo_n_a = n; ctx->todo_src_b = src; ctx->todo_stride_b = stride;   // one piece (flivo_scan_commit overrides for a split upload)
     ctx->d_body = ctx->d_body_own;
     if (!ctx->scan_sorted && external && stride == 16) ctx->d_body = (float4*)src;   // used in place, no copy
     return FLIVO_OK;
@@ -768,6 +770,7 @@ static int ensure_staged(flivo_ctx* ctx, bool* staged = nullptr) {
         if (ctx->sjob_pending) { CKC(cudaEventSynchronize(ctx->sjob_ev)); ctx->sjob_pending = false; }
         ScanJob* J = ctx->h_sjob;
         J->src = ctx->todo_src; J->stride = (unsigned)ctx->todo_stride; J->n = (unsigned)n; J->n_pad = n_pad;
+        J->n_a = (unsigned)ctx->todo_n_a; J->src_b = ctx->todo_src_b; J->stride_b = (unsigned)ctx->todo_stride_b;
         J->inv_edge = 1.0f / ctx->map.view().cell_edge;
         J->key_shift = (unsigned)sb0;
         if (sort) {
@@ -859,9 +862,16 @@ extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, si
     static const int raw_mode = getenv("FLIVO_RAW_DMA") ? atoi(getenv("FLIVO_RAW_DMA")) : -1;
     // (Letting the copy engine gather the xyz itself — a 2-D copy of 12-byte rows at the record pitch — was measured too: 1.2 G
     // points/s pipelined at N = 1 against 2.07 G for the repack and 1.52 G for the raw records; profiles/r2_ab_upload.txt.)
-    const bool raw_ok = raw_mode == 1 || (raw_mode < 0 && host_threads() <= 4 && n >= 65536);
-    const bool pinned = (stride_bytes <= 16 || raw_ok) && host_pinned(body_xyz);
-    const size_t stride = pinned ? stride_bytes : 16, bytes = n * stride;
+    // Best with few threads is BOTH at once (FLIVO_RAW_SPLIT = per cent of the scan repacked, default 50): the copy engine
+    // moves the tail of the scan raw while the host threads repack its head, each doing about half of what bounds it.
+    static const int split_pct = getenv("FLIVO_RAW_SPLIT") ? std::min(100, std::max(0, atoi(getenv("FLIVO_RAW_SPLIT")))) : 50;
+    const bool few = raw_mode < 0 && host_threads() <= 4 && n >= 65536;
+    const bool wide_pinned = stride_bytes > 16 && (raw_mode == 1 || few || (raw_mode == 2)) && host_pinned(body_xyz);
+    const bool pinned = (stride_bytes <= 16 && host_pinned(body_xyz)) || (wide_pinned && (raw_mode == 1 || split_pct == 0));
+    const bool split = wide_pinned && !pinned;
+    const size_t n_a = split ? std::min(n, ((n * (size_t)split_pct / 100 + 63) / 64) * 64) : n;   // points repacked by the host
+    const size_t stride = pinned ? stride_bytes : 16;
+    const size_t bytes = split ? n_a * 16 + (n - n_a) * stride_bytes : n * stride;
     if (sl.copy_pending) { CKC(cudaEventSynchronize(sl.copied)); sl.copy_pending = false; }
     if (bytes > sl.d_bytes) {
         CKC(cudaEventSynchronize(sl.consumed));                 // (no-op for a never recorded event)
@@ -871,9 +881,13 @@ extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, si
         sl.d_bytes = cap;
     }
     CKC(cudaStreamWaitEvent(ctx->copy, sl.consumed, 0));        // the staging that read this slot's previous content has run
+    if (split && n_a < n)   // the raw tail first: it travels while the host repacks the head
+        CKC(cudaMemcpyAsync(sl.d_in + n_a * 16, reinterpret_cast<const char*>(body_xyz) + n_a * stride_bytes, (n - n_a) * stride_bytes,
+                            cudaMemcpyHostToDevice, ctx->copy));
     if (pinned) {
         CKC(cudaMemcpyAsync(sl.d_in, body_xyz, bytes, cudaMemcpyHostToDevice, ctx->copy));
     } else {
+        const size_t n = n_a;   // (the part the host repacks: all of the scan unless the upload is split)
         if (n > sl.h_n) {
             if (sl.h_pin) cudaFreeHost(sl.h_pin);
             sl.h_pin = nullptr; sl.h_n = 0;
@@ -903,6 +917,7 @@ extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, si
     }
     CKC(cudaEventRecord(sl.copied, ctx->copy));
     sl.copy_pending = true; sl.filled = true; sl.n = n; sl.stride = stride;
+    sl.n_a = split ? n_a : n; sl.stride_b = split ? stride_bytes : stride;
     return FLIVO_OK;
 }
 
@@ -917,7 +932,9 @@ extern "C" int flivo_scan_commit(flivo_ctx* ctx) {
     sl.filled = false;
     const int slot = ctx->back;
     ctx->back ^= 1;
-    return finish_scan(ctx, sl.d_in, sl.stride, sl.n, false, slot);
+    rc = finish_scan(ctx, sl.d_in, sl.stride, sl.n, false, slot);
+    if (sl.n_a < sl.n) { ctx->todo_n_a = sl.n_a; ctx->todo_src_b = sl.d_in + sl.n_a * 16; ctx->todo_stride_b = sl.stride_b; }
+    return rc;
 }
 
 extern "C" int flivo_scan_upload(flivo_ctx* ctx, const float* body_xyz, size_t n, size_t stride_bytes) {

@@ -20,6 +20,11 @@ struct ScanJob {
     unsigned int n_pad;   // n rounded up to SCAN_PAD: the item count the staging graph is built for
     float inv_edge;       // 1 / search cell edge
     unsigned int key_shift;   // the sort key is bits [key_shift, key_shift + 16) of the 63-bit Morton code
+    // a scan may arrive in two pieces (flivo_scan_upload_async with few host threads: the head repacked to float4 by the host,
+    // the tail as the caller's raw records by DMA): records [0, n_a) at src / stride, records [n_a, n) at src_b / stride_b
+    unsigned int n_a;         // = n for a scan in one piece
+    unsigned int stride_b;
+    const char* src_b;
 };
 constexpr unsigned int SCAN_PAD = 8192;
 
@@ -43,8 +48,11 @@ __device__ __forceinline__ unsigned long long scan_morton(float4 p, float inv_ed
     return (spread21(ux) << 2) | (spread21(uy) << 1) | spread21(uz);
 }
 __device__ __forceinline__ float4 scan_record(const ScanJob* J, size_t i) {
-    if (J->stride == 16) return reinterpret_cast<const float4*>(J->src)[i];
-    const float* r = reinterpret_cast<const float*>(J->src + i * (size_t)J->stride);
+    const char* src = J->src;
+    unsigned int stride = J->stride;
+    if (i >= J->n_a) { src = J->src_b; stride = J->stride_b; i -= J->n_a; }
+    if (stride == 16) return reinterpret_cast<const float4*>(src)[i];
+    const float* r = reinterpret_cast<const float*>(src + i * (size_t)stride);
     return make_float4(r[0], r[1], r[2], 0.f);
 }
 #endif

@@ -1,6 +1,7 @@
 """-m gpu: the three ways a scan of 48-byte PointXYZINormal-like records reaches the GPU through flivo_scan_upload_async
 (csrc/api.cu) must give the same update, bit for bit: pageable memory (host repack to float4), registered memory with the
-repack (many host threads), registered memory sent as it is (FLIVO_RAW_DMA=1: what a rank with few host threads does).
+repack (many host threads), registered memory sent as it is (FLIVO_RAW_DMA=1), and the split a rank with few host threads
+uses (FLIVO_RAW_DMA=2: head of the scan repacked by the host, tail sent raw).
 FLIVO_RAW_DMA is read once per process, so every flavour runs in a process of its own and prints its posterior as hex."""
 import os
 import subprocess
@@ -20,6 +21,9 @@ def _run(flavour):
         env["FLIVO_RAW_DMA"] = "1"
     elif flavour == "registered_repack":
         env["FLIVO_RAW_DMA"] = "0"
+    elif flavour == "split":                       # head repacked by the host, tail raw: what a rank with few host threads does
+        env["FLIVO_RAW_DMA"] = "2"
+        env["FLIVO_RAW_SPLIT"] = "37"
     r = subprocess.run([sys.executable, os.path.abspath(__file__), flavour], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1].split()
@@ -29,7 +33,7 @@ def _run(flavour):
 def test_upload_flavours_give_the_same_update():
     ref = _run("pageable")
     assert int(ref[0]) > 1000                      # n_eff: the update saw the scan
-    for flavour in ("registered_repack", "raw"):
+    for flavour in ("registered_repack", "raw", "split"):
         got = _run(flavour)
         assert got == ref, flavour
 
