@@ -747,9 +747,9 @@ def run_flivo(args, rank, world_size, local_rank):
     # has few host threads to itself (the library's rule, flivo_scan_upload_async) — + the job / state / P block
     raw_env = os.environ.get("FLIVO_RAW_DMA")
     nt_host = int(os.environ.get("FLIVO_HOST_THREADS") or min(16, max(1, len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))))
-    few = raw_env is None and nt_host <= 4 and pts_per_scan >= 65536
+    few = raw_env is None and nt_host <= 8 and pts_per_scan >= 65536
     raw_dma = args.host_mem != "pageable" and (raw_env in ("1", "2") or few)
-    split_pct = 0 if raw_env == "1" else min(100, max(0, int(os.environ.get("FLIVO_RAW_SPLIT", "50"))))   # per cent of a scan repacked by the host
+    split_pct = 0 if raw_env == "1" else min(100, max(0, int(os.environ.get("FLIVO_RAW_SPLIT", "50" if nt_host <= 4 else "80"))))   # per cent of a scan repacked by the host
     bytes_per_point = (16 * split_pct + 48 * (100 - split_pct)) / 100.0 if raw_dma else 16
     h2d = int(pts_per_scan * bytes_per_point + 36 * 8 + npd * npd * 8 + 512)
     d2h = int(36 * 8 + npd * npd * 8 + 512)

@@ -864,8 +864,9 @@ extern "C" int flivo_scan_upload_async(flivo_ctx* ctx, const float* body_xyz, si
     // points/s pipelined at N = 1 against 2.07 G for the repack and 1.52 G for the raw records; profiles/r2_ab_upload.txt.)
     // Best with few threads is BOTH at once (FLIVO_RAW_SPLIT = per cent of the scan repacked, default 50): the copy engine
     // moves the tail of the scan raw while the host threads repack its head, each doing about half of what bounds it.
-    static const int split_pct = getenv("FLIVO_RAW_SPLIT") ? std::min(100, std::max(0, atoi(getenv("FLIVO_RAW_SPLIT")))) : 50;
-    const bool few = raw_mode < 0 && host_threads() <= 4 && n >= 65536;
+    // (by team size when not forced: 4 threads repack half, 8 threads four fifths, more than 8 everything)
+    static const int split_pct = getenv("FLIVO_RAW_SPLIT") ? std::min(100, std::max(0, atoi(getenv("FLIVO_RAW_SPLIT")))) : (host_threads() <= 4 ? 50 : 80);
+    const bool few = raw_mode < 0 && host_threads() <= 8 && n >= 65536;
     const bool wide_pinned = stride_bytes > 16 && (raw_mode == 1 || few || (raw_mode == 2)) && host_pinned(body_xyz);
     const bool pinned = (stride_bytes <= 16 && host_pinned(body_xyz)) || (wide_pinned && (raw_mode == 1 || split_pct == 0));
     const bool split = wide_pinned && !pinned;
