@@ -50,7 +50,7 @@ def combine_rank_blocks(blocks):
 
 
 def replay_sequences(pkg, sequences, rank, world_size, P0, cfg, ds, device=0, initial_points=0, cell_ratio=2, sort_scan=True,
-                     concurrent=1):
+                     concurrent=1, reuse_contexts=False):
     """Batched replay of independent scan sequences (BASELINE config 4): sequence s belongs to rank
     s mod G, every sequence gets its own context (its own map in HBM) and no rank ever talks to another.
 
@@ -65,14 +65,62 @@ def replay_sequences(pkg, sequences, rank, world_size, P0, cfg, ds, device=0, in
     concurrent > 1 drives that many of the rank's sequences at a time, one host thread and one context (one stream) each:
     contexts share nothing, so the results are those of concurrent = 1; the GPU then overlaps the single-CTA solve and
     the search tails of one sequence with the kernels of another.
+
+    reuse_contexts: every driving thread keeps ONE context for all the sequences it is dealt (sequence s of the rank's list
+    goes to thread s mod concurrent) instead of creating and destroying one per sequence — Build replaces the map, the
+    insertion ids restart at 0, so a sequence's results do not depend on what the context held before
+    (tests/test_gpu_replay.py); what is saved is ~17 ms of cudaMalloc / cudaFree per sequence, several times that when
+    eight threads contend for the allocator, and the occasional second-long stall of a context teardown.
     """
     mine = sequences_of_rank(len(sequences), rank, world_size)
+    if reuse_contexts and mine:
+        workers = max(1, min(int(concurrent), len(mine)))
+        chunks = [mine[w::workers] for w in range(workers)]
+
+        def work(chunk):
+            out = {}
+            with pkg.Flivo(device=device, downsample_size=ds, cell_ratio=cell_ratio, initial_points=initial_points, sort_scan=sort_scan) as F:
+                for s in chunk:
+                    out[s] = _replay_seq(pkg, F, sequences[s], s, P0, cfg)
+            return out
+        if workers > 1:
+            from concurrent.futures import ThreadPoolExecutor
+            with ThreadPoolExecutor(max_workers=workers) as ex:
+                parts = list(ex.map(work, chunks))
+        else:
+            parts = [work(chunks[0])]
+        merged = {}
+        for part in parts:
+            merged.update(part)
+        return {s: merged[s] for s in mine}
     if concurrent > 1 and len(mine) > 1:
         from concurrent.futures import ThreadPoolExecutor
         with ThreadPoolExecutor(max_workers=concurrent) as ex:
             parts = list(ex.map(lambda s: _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_ratio, sort_scan), mine))
         return dict(zip(mine, parts))
     return {s: _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_ratio, sort_scan) for s in mine}
+
+
+def _replay_seq(pkg, F, frames, s, P0, cfg):
+    """The frames of one sequence through context F (see _replay_one for the loop's form)."""
+    res = dict(x=None, map_points=0, updates=0, trips=0, work=0, added=[], device_ms=0.0)
+    bodies = [np.ascontiguousarray(fr["body"], dtype=np.float32) for fr in frames]
+    F.scan_upload(bodies[0])
+    w = F.h_share_model(pkg.State.from_array(frames[0]["x_prior"]), mode=cfg.mode, do_search=True, want=("world",))["world"]
+    F.Build(w)
+    if len(frames) > 1:
+        F.scan_upload_async(bodies[1])
+    for k in range(1, len(frames)):
+        # flivo_frame: commit, update, stage the next scan while the update runs, map_incremental — one call
+        x, _, rep, n_add = F.frame(pkg.State.from_array(frames[k]["x_prior"]), P0, cfg, bodies[k + 1] if k + 1 < len(frames) else None)
+        res["added"].append(n_add)
+        res["updates"] += 1
+        res["trips"] += rep.trips
+        res["work"] += rep.trips * len(bodies[k])
+        res["device_ms"] += getattr(rep, "gpu_ms", 0.0)
+        res["x"] = x.as_array()
+    res["map_points"] = F.size()
+    return res
 
 
 def _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_ratio, sort_scan):
@@ -89,29 +137,11 @@ def _replay_one(pkg, sequences, s, P0, cfg, ds, device, initial_points, cell_rat
     trace = os.environ.get("FLIVO_REPLAY_TRACE")     # per-sequence wall-clock phases on stderr
     t0 = time.perf_counter()
     with pkg.Flivo(device=device, downsample_size=ds, cell_ratio=cell_ratio, initial_points=initial_points, sort_scan=sort_scan) as F:
-        res = dict(x=None, map_points=0, updates=0, trips=0, work=0, added=[], device_ms=0.0)
-        frames = sequences[s]
-        bodies = [np.ascontiguousarray(fr["body"], dtype=np.float32) for fr in frames]
         t1 = time.perf_counter()
-        F.scan_upload(bodies[0])
-        w = F.h_share_model(pkg.State.from_array(frames[0]["x_prior"]), mode=cfg.mode, do_search=True, want=("world",))["world"]
-        F.Build(w)
-        if len(frames) > 1:
-            F.scan_upload_async(bodies[1])
+        res = _replay_seq(pkg, F, sequences[s], s, P0, cfg)
         t2 = time.perf_counter()
-        for k in range(1, len(frames)):
-            # flivo_frame: commit, update, stage the next scan while the update runs, map_incremental — one call
-            x, _, rep, n_add = F.frame(pkg.State.from_array(frames[k]["x_prior"]), P0, cfg, bodies[k + 1] if k + 1 < len(frames) else None)
-            res["added"].append(n_add)
-            res["updates"] += 1
-            res["trips"] += rep.trips
-            res["work"] += rep.trips * len(bodies[k])
-            res["device_ms"] += getattr(rep, "gpu_ms", 0.0)
-            res["x"] = x.as_array()
-        t3 = time.perf_counter()
-        res["map_points"] = F.size()
     if trace:
-        t4 = time.perf_counter()
-        print("[replay trace] seq %d: start %.3f s, create %.1f ms, first scan + Build %.1f ms, %d frames %.1f ms, close %.1f ms"
-              % (s, t0, 1e3 * (t1 - t0), 1e3 * (t2 - t1), len(frames) - 1, 1e3 * (t3 - t2), 1e3 * (t4 - t3)), file=sys.stderr)
+        t3 = time.perf_counter()
+        print("[replay trace] seq %d: start %.3f s, create %.1f ms, %d frames (first scan + Build included) %.1f ms, close %.1f ms"
+              % (s, t0, 1e3 * (t1 - t0), len(sequences[s]), 1e3 * (t2 - t1), 1e3 * (t3 - t2)), file=sys.stderr)
     return res

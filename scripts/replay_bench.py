@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--scan-points", type=int, default=24000)
     ap.add_argument("--mode", type=int, default=1)
     ap.add_argument("--concurrent", type=int, default=1, help="sequences of a rank driven at a time (host threads)")
+    ap.add_argument("--reuse", type=int, default=1, help="1: every driving thread keeps one context for all its sequences (Build replaces the map); 0: one context per sequence")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     dev = int(os.environ.get("LOCAL_RANK", 0))
@@ -51,7 +52,7 @@ def main():
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    r = sh.replay_sequences(pkg, seqs, rank, world, P0, cfg, ds=0.5, device=dev, concurrent=a.concurrent)
+    r = sh.replay_sequences(pkg, seqs, rank, world, P0, cfg, ds=0.5, device=dev, concurrent=a.concurrent, reuse_contexts=bool(a.reuse))
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     t = torch.tensor([dt, float(sum(v["work"] for v in r.values())), float(sum(v["updates"] for v in r.values()))], dtype=torch.float64, device=torch.device("cuda", dev))

@@ -39,6 +39,23 @@ def test_partition_does_not_change_a_sequence(pkg, mode):
         assert (whole[s]["map_points"], whole[s]["trips"], whole[s]["added"]) == (parts[s]["map_points"], parts[s]["trips"], parts[s]["added"])
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_reused_contexts_give_the_same_sequences(pkg, mode):
+    """reuse_contexts: a driving thread keeps one context for all its sequences (Build replaces the map).  Every sequence
+    must come out bitwise as from a context of its own — whatever the context held before — with 1, 2 and 3 threads."""
+    sh = importlib.import_module("fast_livo_noted_b200.sharding")
+    world, seqs = _sequences(5, 4)
+    npd = 18 if mode == 1 else 23
+    P0, cfg = np.eye(npd) * 1e-4, pkg.make_cfg(mode=mode, max_iter=4)
+    fresh = sh.replay_sequences(pkg, seqs, 0, 1, P0, cfg, ds=world["ds"])
+    for conc in (1, 2, 3):
+        got = sh.replay_sequences(pkg, seqs, 0, 1, P0, cfg, ds=world["ds"], concurrent=conc, reuse_contexts=True)
+        assert sorted(got) == sorted(fresh)
+        for s in fresh:
+            assert np.array_equal(got[s]["x"], fresh[s]["x"]), (conc, s)
+            assert (got[s]["map_points"], got[s]["trips"], got[s]["added"]) == (fresh[s]["map_points"], fresh[s]["trips"], fresh[s]["added"]), (conc, s)
+
+
 def test_one_sequence_follows_the_oracle(pkg):
     sh = importlib.import_module("fast_livo_noted_b200.sharding")
     world, seqs = _sequences(1, 4)

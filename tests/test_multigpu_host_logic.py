@@ -200,3 +200,11 @@ def test_replay_sequences_control_flow(pkg):
         assert r[s]["updates"] == seen[s]["updates"] and r[s]["work"] == seen[s]["work"] and np.array_equal(r[s]["x"], seen[s]["x"])
     for calls in _FakeFlivo.log:
         assert calls[1:3] == ["trip", "build"] and calls[-1] == "close"      # no interleaving inside a context
+    # reuse_contexts: one context per driving thread, sequence s of the rank's list -> thread s mod concurrent, Build per sequence
+    for conc, n_ctx in ((1, 1), (2, 2), (8, 5)):
+        _FakeFlivo.log = []
+        r = sh.replay_sequences(fake, seqs, 0, 1, np.eye(18), cfg, ds=0.5, concurrent=conc, reuse_contexts=True)
+        assert sorted(r) == list(range(5)) and len(_FakeFlivo.log) == n_ctx
+        assert sum(calls.count("build") for calls in _FakeFlivo.log) == 5 and all(calls[-1] == "close" for calls in _FakeFlivo.log)
+        for s in range(5):
+            assert r[s]["updates"] == seen[s]["updates"] and r[s]["work"] == seen[s]["work"] and np.array_equal(r[s]["x"], seen[s]["x"])
