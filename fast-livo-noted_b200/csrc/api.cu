@@ -116,6 +116,8 @@ struct flivo_ctx {
     struct { bool active = false; int np = 0, trips = 0, launches = 0; bool timed = false, staged = false; } upd;
     int graph_skip = 0;             // calls left on plain launches after the graph cache kept missing
     unsigned int useq = 0;          // updates started on this context (Job::useq)
+    bool block_wait = false;        // the update's final wait sleeps on block_ev instead of spinning (set by flivo_frame)
+    cudaEvent_t block_ev = nullptr;
     double frame_s[5] = {0, 0, 0, 0, 0};   // FLIVO_FRAME_TRACE=1: host seconds spent in flivo_frame's commit / begin / upload / end / map_add
     long frame_calls = 0;
     unsigned int* d_perm = nullptr; // processing index -> caller's index
@@ -441,6 +443,7 @@ extern "C" void flivo_ctx_destroy(flivo_ctx* ctx) {
     cudaFree(ctx->d_sjob);
     if (ctx->h_sjob) cudaFreeHost(ctx->h_sjob);
     if (ctx->sjob_ev) cudaEventDestroy(ctx->sjob_ev);
+    if (ctx->block_ev) cudaEventDestroy(ctx->block_ev);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->stage_ev) cudaEventDestroy(ctx->stage_ev);
     if (ctx->copy) { cudaStreamSynchronize(ctx->copy); cudaStreamDestroy(ctx->copy); }
@@ -1299,7 +1302,13 @@ extern "C" int flivo_iekf_update_end(flivo_ctx* ctx, flivo_state* inout, double*
     const int np = ctx->upd.np, trips = ctx->upd.trips, launches = ctx->upd.launches;
     const bool timed = ctx->upd.timed;
     DevBlock* h = ctx->h_blk;
-    CKC(cudaStreamSynchronize(ctx->stream));
+    if (ctx->block_wait) {   // (flivo_frame with more driving threads than cores: sleep instead of spinning)
+        if (!ctx->block_ev) CKC(cudaEventCreateWithFlags(&ctx->block_ev, cudaEventBlockingSync | cudaEventDisableTiming));
+        CKC(cudaEventRecord(ctx->block_ev, ctx->stream));
+        CKC(cudaEventSynchronize(ctx->block_ev));
+    } else {
+        CKC(cudaStreamSynchronize(ctx->stream));
+    }
     const Ctl& c = h->ctl;
     if (c.nan_guard != 2) {   // (a timed-out peer exchange may have stopped the loop after some trips: nothing is handed back)
         memcpy(inout, h->x, sizeof(flivo_state));
@@ -1420,6 +1429,12 @@ extern "C" int flivo_map_add_scan(flivo_ctx* ctx, const flivo_state* st, int32_t
 extern "C" int flivo_frame(flivo_ctx* ctx, flivo_state* x, double* P, const flivo_cfg* cfg, const float* next_body_xyz, size_t n_next,
                            size_t stride_bytes, flivo_report* rep, int32_t* n_added) {
     static const bool trace = getenv("FLIVO_FRAME_TRACE") != nullptr;   // where a frame's host time goes (printed by flivo_ctx_destroy)
+    // A replay drives several contexts from as many host threads; where a process has few cores to itself (eight ranks on
+    // one host) spinning waits starve each other, so the frame's two waits sleep on an event instead (FLIVO_BLOCKING_SYNC=0/1
+    // overrides; the price is the wake-up latency, which a loop with several frames in flight does not see).
+    static const int block_mode = getenv("FLIVO_BLOCKING_SYNC") ? atoi(getenv("FLIVO_BLOCKING_SYNC")) : (host_threads() <= 4 ? 1 : 0);
+    if (ctx) { ctx->block_wait = block_mode != 0; ctx->map.set_blocking_wait(block_mode != 0); }
+    struct Unblock { flivo_ctx* c; ~Unblock() { if (c) { c->block_wait = false; c->map.set_blocking_wait(false); } } } unblock{ctx};
     using clk = std::chrono::steady_clock;
     clk::time_point t0;
     int phase = 0;

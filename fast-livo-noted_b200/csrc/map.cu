@@ -795,6 +795,7 @@ void MapStore::release() {
     cudaFree(v_.sup_keys); cudaFree(v_.sup_mask);
     v_ = MapView{};
     drop_add_graph();
+    if (block_ev_) { cudaEventDestroy(block_ev_); block_ev_ = nullptr; }
     cudaFree(d_bjob_); d_bjob_ = nullptr;
     if (h_bjob_) cudaFreeHost(h_bjob_);
     h_bjob_ = nullptr;
@@ -1059,6 +1060,14 @@ int MapStore::enqueue_insert(const float4* d_pts_id, size_t n, bool downsample_o
     return 0;
 }
 
+int MapStore::wait_stream(std::string& err) {
+    if (!block_wait_) { CK(cudaStreamSynchronize(stream_)); return 0; }
+    if (!block_ev_) CK(cudaEventCreateWithFlags(&block_ev_, cudaEventBlockingSync | cudaEventDisableTiming));
+    CK(cudaEventRecord(block_ev_, stream_));
+    CK(cudaEventSynchronize(block_ev_));
+    return 0;
+}
+
 void MapStore::drop_add_graph() {
     if (add_exec_) { cudaGraphExecDestroy(add_exec_); add_exec_ = nullptr; }
     add_src_ = nullptr; add_npad_ = 0; add_scratch_ = nullptr;
@@ -1101,7 +1110,7 @@ int MapStore::add_points_graph(const float4* d_pts, size_t n, int* n_added, std:
         add_src_ = d_pts; add_npad_ = n_pad; add_scratch_ = scratch_pts_; add_view_ = v_;
     }
     CK(cudaGraphLaunch(add_exec_, stream_));
-    CK(cudaStreamSynchronize(stream_));
+    if (wait_stream(err)) return -1;
     next_id_ += (int)n;
     int rc = finish_counters(err);
     if (n_added) *n_added = h_cnt_.add_counter;

@@ -51,6 +51,9 @@ public:
     size_t bucket_cap() const { return bucket_cap_; }
     bool empty() const { return h_cnt_.live == 0; }
     int next_id() const { return next_id_; }
+    // the waits of Add_Points sleep on an event (cudaEventBlockingSync) instead of spinning in cudaStreamSynchronize: for
+    // callers that drive many contexts from more host threads than they have cores (flivo_frame, see api.cu)
+    void set_blocking_wait(bool on) { block_wait_ = on; }
 
 private:
     int alloc_tables(size_t dir_cap, size_t bucket_cap, std::string& err);
@@ -102,6 +105,9 @@ private:
     MapView add_view_{};
     const void* add_scratch_ = nullptr;
     int add_graph_fail_ = 0;
+    bool block_wait_ = false;
+    cudaEvent_t block_ev_ = nullptr;
+    int wait_stream(std::string& err);   // cudaStreamSynchronize(stream_), or the blocking event wait
 };
 
 constexpr int SLOP_LIST_CAP = 4096;
