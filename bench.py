@@ -69,8 +69,8 @@ def parse_args():
                     help="where the e2e loop's host scans live: the node's own buffers registered with cudaHostRegister (default), "
                          "cudaHostAlloc memory (torch pin_memory), or plain pageable memory")
     ap.add_argument("--no-replay", action="store_true", help="skip the `replay` block (config 4 in miniature)")
-    ap.add_argument("--replay-sequences", type=int, default=16, help="sequences PER RANK of the replay block")
-    ap.add_argument("--replay-frames", type=int, default=120)
+    ap.add_argument("--replay-sequences", type=int, default=32, help="sequences PER RANK of the replay block")
+    ap.add_argument("--replay-frames", type=int, default=150)
     ap.add_argument("--replay-concurrent", type=int, default=8)
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="sharded mode: how the per-trip 96-double records travel")
     return ap.parse_args()
